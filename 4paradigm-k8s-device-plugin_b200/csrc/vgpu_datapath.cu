@@ -1,0 +1,609 @@
+// Host side of the data-path C-ABI declared in include/vgpu.h: launch logic,
+// per-(device,stream) scratch, the AUTO policy table, tier slabs, memtest
+// drivers.  No CPU fallback: every entry point either launches the sm_100a
+// kernels in vgpu_kernels.cuh (or, for VGPU_XFER_CE, the copy engine plus the
+// checksum kernel) or fails.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <vector>
+
+#include "vgpu_internal.h"
+#include "vgpu_kernels.cuh"
+
+namespace vgpu {
+
+char *err_buf() {
+    static thread_local char buf[kErrLen] = {0};
+    return buf;
+}
+
+namespace {
+
+constexpr int kMaxDev = 16;  // reference cap: "Max Gpus Per Node can't excced 16" (libvgpu.so@0x27f0d)
+
+struct Scratch {
+    ChunkAcc *acc = nullptr;  // self-cleaning per-chunk accumulators
+    size_t acc_cap = 0;
+    vgpu_memtest_dev_result_t *mt = nullptr;
+    vgpu_cksum_t *cksum = nullptr;  // staging for the host-buffer forms
+    size_t cksum_cap = 0;
+    vgpu_restore_result_t *rr = nullptr;
+};
+
+struct DevState {
+    int sm_count = 0;
+    std::map<void *, Scratch> scratch;  // keyed by stream
+};
+
+std::mutex g_mu;
+DevState g_dev[kMaxDev];
+
+int cur_device(int *dev) {
+    VGPU_CUDA(cudaGetDevice(dev));
+    if (*dev < 0 || *dev >= kMaxDev) return fail(VGPU_E_INVAL, "device %d out of range", *dev);
+    return VGPU_OK;
+}
+
+int sm_count(int dev, int *out) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_dev[dev].sm_count)
+        VGPU_CUDA(cudaDeviceGetAttribute(&g_dev[dev].sm_count, cudaDevAttrMultiProcessorCount, dev));
+    *out = g_dev[dev].sm_count;
+    return VGPU_OK;
+}
+
+// Scratch is allocated lazily, zeroed once, and kept until process exit.
+int get_acc(int dev, void *stream, size_t nchunks, ChunkAcc **out) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    Scratch &s = g_dev[dev].scratch[stream];
+    if (s.acc_cap < nchunks) {
+        size_t cap = std::max<size_t>(4096, nchunks);
+        ChunkAcc *p = nullptr;
+        VGPU_CUDA(cudaMalloc(&p, cap * sizeof(ChunkAcc)));
+        VGPU_CUDA(cudaMemset(p, 0, cap * sizeof(ChunkAcc)));
+        if (s.acc) {
+            // the old block may still be in use by launches queued on this stream
+            VGPU_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+            VGPU_CUDA(cudaFree(s.acc));
+        }
+        s.acc = p;
+        s.acc_cap = cap;
+    }
+    *out = s.acc;
+    return VGPU_OK;
+}
+
+int get_mt(int dev, void *stream, vgpu_memtest_dev_result_t **out) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    Scratch &s = g_dev[dev].scratch[stream];
+    if (!s.mt) VGPU_CUDA(cudaMalloc(&s.mt, sizeof(*s.mt)));
+    *out = s.mt;
+    return VGPU_OK;
+}
+
+int get_stage(int dev, void *stream, size_t nchunks, vgpu_cksum_t **ck, vgpu_restore_result_t **rr) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    Scratch &s = g_dev[dev].scratch[stream];
+    if (s.cksum_cap < nchunks) {
+        if (s.cksum) VGPU_CUDA(cudaFree(s.cksum));
+        s.cksum = nullptr;
+        size_t cap = std::max<size_t>(4096, nchunks);
+        VGPU_CUDA(cudaMalloc(&s.cksum, cap * sizeof(vgpu_cksum_t)));
+        s.cksum_cap = cap;
+    }
+    if (!s.rr) VGPU_CUDA(cudaMalloc(&s.rr, sizeof(*s.rr)));
+    *ck = s.cksum;
+    *rr = s.rr;
+    return VGPU_OK;
+}
+
+// ---- AUTO policy ----------------------------------------------------------
+// policy[tier] is a list of (min_chunks, variant), highest matching min wins.
+// Defaults come from profiles/ (first GPU measurements); vgpu_calibrate
+// overwrites them with what it measures on the box at hand.
+struct Rule {
+    size_t min_chunks;
+    int variant;
+};
+std::vector<Rule> g_policy[3] = {
+    {{0, VGPU_XFER_LDST}},
+    {{0, VGPU_XFER_LDST}},
+    {{0, VGPU_XFER_LDST}},
+};
+
+int policy_lookup(int tier, size_t nchunks) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    int v = VGPU_XFER_LDST;
+    size_t best = 0;
+    for (const Rule &r : g_policy[tier])
+        if (r.min_chunks <= nchunks && r.min_chunks >= best) {
+            best = r.min_chunks;
+            v = r.variant;
+        }
+    return v;
+}
+
+// ---- transfer launch --------------------------------------------------------
+constexpr int kLdstU = 4;                   // 4 x 32 B per thread in flight => 32 KiB tiles
+constexpr int kTmaTile = 16384, kTmaStages = 4, kTmaThreads = 128;
+
+bool aligned32(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 31u) == 0; }
+
+int host_readable(const void *p, bool *ok) {
+    cudaPointerAttributes at{};
+    cudaError_t e = cudaPointerGetAttributes(&at, p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        *ok = false;
+        return VGPU_OK;
+    }
+    *ok = at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged ||
+          at.type == cudaMemoryTypeUnregistered;
+    return VGPU_OK;
+}
+
+int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
+                const uint32_t *src_slot, const uint32_t *dst_slot, size_t nchunks,
+                size_t chunk_bytes, const vgpu_cksum_t *expect, vgpu_cksum_t *cksum,
+                vgpu_restore_result_t *result, void *stream, bool restore) {
+    if (nchunks == 0) return VGPU_OK;
+    if (!src || (copy && !dst)) return fail(VGPU_E_INVAL, "null slab pointer");
+    if (!aligned32(src) || (copy && !aligned32(dst)))
+        return fail(VGPU_E_INVAL, "slab base must be 32-byte aligned");
+    if (chunk_bytes == 0 || chunk_bytes % 32 != 0 || chunk_bytes > (1ull << 30))
+        return fail(VGPU_E_INVAL, "chunk_bytes=%zu must be a multiple of 32 in (0, 1 GiB]", chunk_bytes);
+    if (nchunks > (1u << 24)) return fail(VGPU_E_INVAL, "nchunks=%zu too large", nchunks);
+    if (expect && !result) return fail(VGPU_E_INVAL, "expect given without a result block");
+    if (tier < 0 || tier > 2) return fail(VGPU_E_INVAL, "tier=%d", tier);
+    if (variant == VGPU_XFER_AUTO) variant = policy_lookup(tier, nchunks);
+    if (variant < VGPU_XFER_LDST || variant > VGPU_XFER_CE) return fail(VGPU_E_INVAL, "variant=%d", variant);
+
+    int dev, sms;
+    if (int rc = cur_device(&dev)) return rc;
+    if (int rc = sm_count(dev, &sms)) return rc;
+    XferArgs a{};
+    a.src = static_cast<const unsigned char *>(src);
+    a.dst = static_cast<unsigned char *>(dst);
+    a.src_slot = src_slot;
+    a.dst_slot = dst_slot;
+    a.chunk_bytes = chunk_bytes;
+    a.nchunks = (uint32_t)nchunks;
+    a.cksum = cksum;
+    a.expect = expect;
+    a.result = result;
+    if (int rc = get_acc(dev, stream, nchunks, &a.acc)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+    if (variant == VGPU_XFER_CE && copy) {
+        // Copy engine moves the bytes; the checksum kernel then reads the
+        // local side (src for a spill, dst for a restore) at HBM speed.
+        if (!src_slot && !dst_slot) {
+            VGPU_CUDA(cudaMemcpyAsync(dst, src, nchunks * chunk_bytes, cudaMemcpyDefault, st));
+        } else {
+            bool ok1 = true, ok2 = true;
+            if (src_slot) host_readable(src_slot, &ok1);
+            if (dst_slot) host_readable(dst_slot, &ok2);
+            if (!ok1 || !ok2)
+                return fail(VGPU_E_UNSUPPORTED, "VGPU_XFER_CE needs host-readable slot tables");
+            // coalesce runs of consecutive slots into one copy each
+            size_t c = 0;
+            while (c < nchunks) {
+                size_t s0 = src_slot ? src_slot[c] : c, d0 = dst_slot ? dst_slot[c] : c, n = 1;
+                while (c + n < nchunks && (src_slot ? src_slot[c + n] : c + n) == s0 + n &&
+                       (dst_slot ? dst_slot[c + n] : c + n) == d0 + n)
+                    ++n;
+                VGPU_CUDA(cudaMemcpyAsync(a.dst + d0 * chunk_bytes, a.src + s0 * chunk_bytes,
+                                          n * chunk_bytes, cudaMemcpyDefault, st));
+                c += n;
+            }
+        }
+        if (restore) {  // checksum what arrived
+            a.src = a.dst;
+            a.src_slot = a.dst_slot;
+        }
+        copy = false;
+        variant = VGPU_XFER_LDST;
+    }
+
+    if (variant == VGPU_XFER_LDST || !copy) {
+        constexpr uint32_t tile = LdstTile<kLdstU>::bytes;
+        a.tiles_per_chunk = (uint32_t)((chunk_bytes + tile - 1) / tile);
+        const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
+        const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * 8);
+        if (copy) k_xfer_ldst<kLdstU, true><<<grid, kXfThreads, 0, st>>>(a);
+        else k_xfer_ldst<kLdstU, false><<<grid, kXfThreads, 0, st>>>(a);
+    } else {  // VGPU_XFER_TMA
+        a.tiles_per_chunk = (uint32_t)((chunk_bytes + kTmaTile - 1) / kTmaTile);
+        const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
+        constexpr size_t smem = (size_t)kTmaTile * kTmaStages;
+        auto kfn = k_xfer_tma<kTmaTile, kTmaStages, kTmaThreads, true>;
+        static bool attr_done[kMaxDev] = {false};
+        if (!attr_done[dev]) {
+            VGPU_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_done[dev] = true;
+        }
+        const unsigned per_sm = (unsigned)std::max<size_t>(1, (220 * 1024) / (smem + 1024));
+        const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * per_sm);
+        kfn<<<grid, kTmaThreads, smem, st>>>(a);
+    }
+    VGPU_CUDA(cudaGetLastError());
+    return VGPU_OK;
+}
+
+}  // namespace
+}  // namespace vgpu
+
+using namespace vgpu;
+
+extern "C" {
+
+int vgpu_abi_version(void) { return VGPU_ABI_VERSION; }
+const char *vgpu_last_error(void) { return err_buf(); }
+
+int vgpu_checksum(const void *src, const uint32_t *src_slot, size_t nchunks, size_t chunk_bytes,
+                  vgpu_cksum_t *cksum, void *stream) {
+    if (!cksum && nchunks) return fail(VGPU_E_INVAL, "cksum is NULL");
+    return launch_xfer(VGPU_XFER_LDST, VGPU_TIER_LOCAL, false, src, nullptr, src_slot, nullptr,
+                       nchunks, chunk_bytes, nullptr, cksum, nullptr, stream, false);
+}
+
+int vgpu_spill(int variant, int tier, const void *src, void *dst, const uint32_t *src_slot,
+               const uint32_t *dst_slot, size_t nchunks, size_t chunk_bytes, vgpu_cksum_t *cksum,
+               void *stream) {
+    if (!cksum && nchunks) return fail(VGPU_E_INVAL, "cksum is NULL");
+    return launch_xfer(variant, tier, true, src, dst, src_slot, dst_slot, nchunks, chunk_bytes,
+                       nullptr, cksum, nullptr, stream, false);
+}
+
+int vgpu_restore(int variant, int tier, const void *src, void *dst, const uint32_t *src_slot,
+                 const uint32_t *dst_slot, size_t nchunks, size_t chunk_bytes,
+                 const vgpu_cksum_t *expect, vgpu_cksum_t *cksum, vgpu_restore_result_t *result,
+                 void *stream) {
+    return launch_xfer(variant, tier, true, src, dst, src_slot, dst_slot, nchunks, chunk_bytes,
+                       expect, cksum, result, stream, true);
+}
+
+// ---- host-buffer forms ------------------------------------------------------
+static int pin_if_needed(const void *host, size_t bytes, bool *registered) {
+    *registered = false;
+    cudaPointerAttributes at{};
+    cudaError_t e = cudaPointerGetAttributes(&at, host);
+    if (e != cudaSuccess) cudaGetLastError();
+    if (e == cudaSuccess && at.type == cudaMemoryTypeHost) return VGPU_OK;
+    VGPU_CUDA(cudaHostRegister(const_cast<void *>(host), bytes, cudaHostRegisterPortable | cudaHostRegisterMapped));
+    *registered = true;
+    return VGPU_OK;
+}
+
+int vgpu_spill_to_host(int variant, int device, const void *d_src, void *host, size_t nchunks,
+                       size_t chunk_bytes, vgpu_cksum_t *h_cksum) {
+    if (!host || !h_cksum) return fail(VGPU_E_INVAL, "null host pointer");
+    VGPU_CUDA(cudaSetDevice(device));
+    bool reg = false;
+    if (int rc = pin_if_needed(host, nchunks * chunk_bytes, &reg)) return rc;
+    void *h_dev = nullptr;
+    vgpu_cksum_t *ck;
+    vgpu_restore_result_t *rr;
+    int rc = VGPU_OK;
+    cudaError_t e = cudaHostGetDevicePointer(&h_dev, host, 0);
+    if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaHostGetDevicePointer: %s", cudaGetErrorString(e));
+    if (!rc) rc = get_stage(device, nullptr, nchunks, &ck, &rr);
+    if (!rc) rc = vgpu_spill(variant, VGPU_TIER_HOST, d_src, h_dev, nullptr, nullptr, nchunks, chunk_bytes, ck, nullptr);
+    if (!rc) {
+        e = cudaMemcpy(h_cksum, ck, nchunks * sizeof(vgpu_cksum_t), cudaMemcpyDeviceToHost);  // syncs stream 0
+        if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaMemcpy cksum: %s", cudaGetErrorString(e));
+    }
+    if (reg) cudaHostUnregister(host);
+    return rc;
+}
+
+int vgpu_restore_from_host(int variant, int device, const void *host, void *d_dst, size_t nchunks,
+                           size_t chunk_bytes, const vgpu_cksum_t *h_expect, uint64_t *bad_chunks) {
+    if (!host || !h_expect || !bad_chunks) return fail(VGPU_E_INVAL, "null host pointer");
+    VGPU_CUDA(cudaSetDevice(device));
+    bool reg = false;
+    if (int rc = pin_if_needed(host, nchunks * chunk_bytes, &reg)) return rc;
+    void *h_dev = nullptr;
+    vgpu_cksum_t *ck;
+    vgpu_restore_result_t *rr;
+    vgpu_restore_result_t hres{};
+    int rc = VGPU_OK;
+    cudaError_t e = cudaHostGetDevicePointer(&h_dev, const_cast<void *>(host), 0);
+    if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaHostGetDevicePointer: %s", cudaGetErrorString(e));
+    if (!rc) rc = get_stage(device, nullptr, nchunks, &ck, &rr);
+    if (!rc) {
+        e = cudaMemcpyAsync(ck, h_expect, nchunks * sizeof(vgpu_cksum_t), cudaMemcpyHostToDevice, 0);
+        if (e == cudaSuccess) e = cudaMemsetAsync(rr, 0, sizeof(*rr), 0);
+        if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "stage expect: %s", cudaGetErrorString(e));
+    }
+    if (!rc) rc = vgpu_restore(variant, VGPU_TIER_HOST, h_dev, d_dst, nullptr, nullptr, nchunks, chunk_bytes, ck, nullptr, rr, nullptr);
+    if (!rc) {
+        e = cudaMemcpy(&hres, rr, sizeof(hres), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaMemcpy result: %s", cudaGetErrorString(e));
+    }
+    if (reg) cudaHostUnregister(const_cast<void *>(host));
+    if (rc) return rc;
+    *bad_chunks = hres.bad_chunks;
+    if (hres.bad_chunks)
+        return fail(VGPU_E_MISMATCH, "%llu chunk(s) failed checksum, first %llu",
+                    (unsigned long long)hres.bad_chunks, (unsigned long long)~hres.first_bad_inv);
+    return VGPU_OK;
+}
+
+// ---- slabs --------------------------------------------------------------------
+int vgpu_slab_alloc(int tier, int device, int peer_device, size_t bytes, void **out) {
+    if (!out || !bytes) return fail(VGPU_E_INVAL, "bad slab request");
+    *out = nullptr;
+    switch (tier) {
+        case VGPU_TIER_LOCAL:
+            VGPU_CUDA(cudaSetDevice(device));
+            VGPU_CUDA(cudaMalloc(out, bytes));
+            return VGPU_OK;
+        case VGPU_TIER_PEER: {
+            if (peer_device == device) return fail(VGPU_E_INVAL, "peer == device");
+            int can = 0;
+            VGPU_CUDA(cudaDeviceCanAccessPeer(&can, device, peer_device));
+            if (!can) return fail(VGPU_E_UNSUPPORTED, "GPU %d cannot access GPU %d", device, peer_device);
+            VGPU_CUDA(cudaSetDevice(peer_device));
+            VGPU_CUDA(cudaMalloc(out, bytes));
+            VGPU_CUDA(cudaSetDevice(device));
+            cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess)
+                return fail(VGPU_E_CUDA, "cudaDeviceEnablePeerAccess(%d): %s", peer_device, cudaGetErrorString(e));
+            return VGPU_OK;
+        }
+        case VGPU_TIER_HOST:
+            VGPU_CUDA(cudaSetDevice(device));
+            VGPU_CUDA(cudaHostAlloc(out, bytes, cudaHostAllocPortable | cudaHostAllocMapped));
+            return VGPU_OK;
+    }
+    return fail(VGPU_E_INVAL, "tier=%d", tier);
+}
+
+int vgpu_slab_free(int tier, int device, int peer_device, void *p) {
+    if (!p) return VGPU_OK;
+    switch (tier) {
+        case VGPU_TIER_LOCAL:
+            VGPU_CUDA(cudaSetDevice(device));
+            VGPU_CUDA(cudaFree(p));
+            return VGPU_OK;
+        case VGPU_TIER_PEER:
+            VGPU_CUDA(cudaSetDevice(peer_device));
+            VGPU_CUDA(cudaFree(p));
+            VGPU_CUDA(cudaSetDevice(device));
+            return VGPU_OK;
+        case VGPU_TIER_HOST:
+            VGPU_CUDA(cudaFreeHost(p));
+            return VGPU_OK;
+    }
+    return fail(VGPU_E_INVAL, "tier=%d", tier);
+}
+
+// ---- policy -------------------------------------------------------------------
+int vgpu_policy_get(int tier, size_t nchunks) {
+    if (tier < 0 || tier > 2) return fail(VGPU_E_INVAL, "tier=%d", tier);
+    return policy_lookup(tier, nchunks);
+}
+
+int vgpu_policy_set(int tier, size_t min_chunks, int variant) {
+    if (tier < 0 || tier > 2 || variant < VGPU_XFER_LDST || variant > VGPU_XFER_CE)
+        return fail(VGPU_E_INVAL, "tier=%d variant=%d", tier, variant);
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (Rule &r : g_policy[tier])
+        if (r.min_chunks == min_chunks) {
+            r.variant = variant;
+            return VGPU_OK;
+        }
+    g_policy[tier].push_back({min_chunks, variant});
+    return VGPU_OK;
+}
+
+int vgpu_calibrate(int device, int tier, int peer_device, size_t max_chunks) {
+    if (tier < 0 || tier > 2) return fail(VGPU_E_INVAL, "tier=%d", tier);
+    if (max_chunks == 0) max_chunks = 512;
+    const size_t chunk = VGPU_CHUNK_BYTES;
+    void *near_slab = nullptr, *far_slab = nullptr;
+    vgpu_cksum_t *ck = nullptr;
+    int rc = vgpu_slab_alloc(VGPU_TIER_LOCAL, device, -1, max_chunks * chunk, &near_slab);
+    if (!rc) rc = vgpu_slab_alloc(tier, device, peer_device, max_chunks * chunk, &far_slab);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (!rc && cudaMalloc(&ck, max_chunks * sizeof(*ck)) != cudaSuccess) rc = fail(VGPU_E_NOMEM, "cksum alloc");
+    if (!rc && (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess))
+        rc = fail(VGPU_E_CUDA, "event create");
+    if (!rc) rc = vgpu_memtest_fill(near_slab, max_chunks * chunk, VGPU_PAT_RANDOM, 0, 0, nullptr);
+    for (size_t n = 1; !rc && n <= max_chunks; n *= 8) {
+        float best_ms = 0;
+        int best = VGPU_XFER_LDST;
+        for (int v = VGPU_XFER_LDST; v <= VGPU_XFER_CE && !rc; ++v) {
+            float ms_min = 1e30f;
+            for (int it = 0; it < 4 && !rc; ++it) {  // first iteration is warm-up
+                cudaEventRecord(e0, 0);
+                rc = vgpu_spill(v, tier, near_slab, far_slab, nullptr, nullptr, n, chunk, ck, nullptr);
+                cudaEventRecord(e1, 0);
+                if (cudaEventSynchronize(e1) != cudaSuccess) rc = fail(VGPU_E_CUDA, "calibrate sync");
+                float ms = 0;
+                cudaEventElapsedTime(&ms, e0, e1);
+                if (it) ms_min = std::min(ms_min, ms);
+            }
+            if (v == VGPU_XFER_LDST || ms_min < best_ms) {
+                best_ms = ms_min;
+                best = v;
+            }
+        }
+        if (!rc) vgpu_policy_set(tier, n == 1 ? 0 : n, best);
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (ck) cudaFree(ck);
+    vgpu_slab_free(tier, device, peer_device, far_slab);
+    vgpu_slab_free(VGPU_TIER_LOCAL, device, -1, near_slab);
+    return rc;
+}
+
+// ---- memtest ------------------------------------------------------------------
+static int mt_geom(const void *buf, uint64_t bytes, uint64_t *head, uint64_t *nvec, uint64_t *tail) {
+    if (!buf) return fail(VGPU_E_INVAL, "null buffer");
+    if ((reinterpret_cast<uintptr_t>(buf) & 7u) || (bytes & 7u))
+        return fail(VGPU_E_INVAL, "buffer and size must be 8-byte aligned");
+    const uint64_t words = bytes / 8;
+    uint64_t h = ((32 - (reinterpret_cast<uintptr_t>(buf) & 31u)) & 31u) / 8;
+    if (h > words) h = words;
+    *head = h;
+    *nvec = (words - h) / 4;
+    *tail = (words - h) % 4;
+    return VGPU_OK;
+}
+
+static uint64_t mt_key(int pattern, uint64_t pass, uint64_t seed) {
+    return pattern == VGPU_PAT_WALKING_ONES ? pass : (kGolden ^ pass ^ seed);
+}
+
+static int mt_grid(uint64_t nvec, unsigned *grid) {
+    int dev, sms;
+    if (int rc = cur_device(&dev)) return rc;
+    if (int rc = sm_count(dev, &sms)) return rc;
+    const uint64_t want = (nvec + kMtThreads * kMtUnroll - 1) / (kMtThreads * kMtUnroll);
+    *grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)sms * 8));
+    return VGPU_OK;
+}
+
+int vgpu_memtest_fill(void *buf, uint64_t bytes, int pattern, uint64_t pass, uint64_t seed, void *stream) {
+    if (bytes == 0) return VGPU_OK;
+    uint64_t head = 0, nvec = 0, tail = 0;
+    unsigned grid;
+    if (int rc = mt_geom(buf, bytes, &head, &nvec, &tail)) return rc;
+    if (int rc = mt_grid(nvec, &grid)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint64_t *p = static_cast<uint64_t *>(buf);
+    const uint64_t key = mt_key(pattern, pass, seed);
+    if (pattern == VGPU_PAT_WALKING_ONES)
+        k_memtest_fill<VGPU_PAT_WALKING_ONES><<<grid, kMtThreads, 0, st>>>(p, head, nvec, tail, key);
+    else if (pattern == VGPU_PAT_RANDOM)
+        k_memtest_fill<VGPU_PAT_RANDOM><<<grid, kMtThreads, 0, st>>>(p, head, nvec, tail, key);
+    else
+        return fail(VGPU_E_INVAL, "pattern=%d", pattern);
+    VGPU_CUDA(cudaGetLastError());
+    return VGPU_OK;
+}
+
+int vgpu_memtest_verify(const void *buf, uint64_t bytes, int pattern, uint64_t pass, uint64_t seed,
+                        vgpu_memtest_dev_result_t *d_result, void *stream) {
+    if (!d_result) return fail(VGPU_E_INVAL, "null result");
+    if (bytes == 0) return VGPU_OK;
+    uint64_t head = 0, nvec = 0, tail = 0;
+    unsigned grid;
+    if (int rc = mt_geom(buf, bytes, &head, &nvec, &tail)) return rc;
+    if (int rc = mt_grid(nvec, &grid)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const uint64_t *p = static_cast<const uint64_t *>(buf);
+    const uint64_t key = mt_key(pattern, pass, seed);
+    if (pattern == VGPU_PAT_WALKING_ONES)
+        k_memtest_verify<VGPU_PAT_WALKING_ONES><<<grid, kMtThreads, 0, st>>>(p, head, nvec, tail, key, d_result);
+    else if (pattern == VGPU_PAT_RANDOM)
+        k_memtest_verify<VGPU_PAT_RANDOM><<<grid, kMtThreads, 0, st>>>(p, head, nvec, tail, key, d_result);
+    else
+        return fail(VGPU_E_INVAL, "pattern=%d", pattern);
+    VGPU_CUDA(cudaGetLastError());
+    return VGPU_OK;
+}
+
+int vgpu_memtest_run(void *buf, uint64_t bytes, int pattern, uint64_t first_pass, uint64_t npasses,
+                     uint64_t seed, void *stream, vgpu_memtest_result_t *out) {
+    if (!out) return fail(VGPU_E_INVAL, "null result");
+    int dev;
+    if (int rc = cur_device(&dev)) return rc;
+    vgpu_memtest_dev_result_t *d_res;
+    if (int rc = get_mt(dev, stream, &d_res)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    cudaEvent_t ev[3];
+    for (auto &e : ev) VGPU_CUDA(cudaEventCreate(&e));
+    vgpu_memtest_result_t r{};
+    r.bytes = bytes;
+    r.first_bad_word = ~0ull;
+    r.first_bad_pattern = r.first_bad_pass = -1;
+    int rc = VGPU_OK;
+    for (uint64_t p = first_pass; p < first_pass + npasses && !rc; ++p) {
+        vgpu_memtest_dev_result_t h{};
+        cudaMemsetAsync(d_res, 0, sizeof(*d_res), st);
+        cudaEventRecord(ev[0], st);
+        rc = vgpu_memtest_fill(buf, bytes, pattern, p, seed, stream);
+        cudaEventRecord(ev[1], st);
+        if (!rc) rc = vgpu_memtest_verify(buf, bytes, pattern, p, seed, d_res, stream);
+        cudaEventRecord(ev[2], st);
+        if (!rc) {
+            cudaError_t e = cudaMemcpyAsync(&h, d_res, sizeof(h), cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "memtest pass %llu: %s", (unsigned long long)p, cudaGetErrorString(e));
+        }
+        if (rc) break;
+        float f = 0, v = 0;
+        cudaEventElapsedTime(&f, ev[0], ev[1]);
+        cudaEventElapsedTime(&v, ev[1], ev[2]);
+        r.fill_ms += f;
+        r.verify_ms += v;
+        r.passes += 1;
+        r.mismatches += h.mismatches;
+        r.bad_bits |= h.bad_bits;
+        if (h.mismatches && r.first_bad_pattern < 0) {
+            r.first_bad_pattern = pattern;
+            r.first_bad_pass = (int32_t)p;
+            r.first_bad_word = ~h.first_bad_inv;
+        }
+    }
+    for (auto &e : ev) cudaEventDestroy(e);
+    if (rc) return rc;
+    const double ms = r.fill_ms + r.verify_ms;
+    r.gbps = ms > 0 ? 2.0 * (double)bytes * (double)r.passes / (ms * 1e6) : 0.0;
+    *out = r;
+    return VGPU_OK;
+}
+
+int vgpu_memtest(int device, uint64_t bytes, unsigned patterns, uint64_t random_passes, uint64_t seed,
+                 vgpu_memtest_result_t *out) {
+    if (!out) return fail(VGPU_E_INVAL, "null result");
+    if (!(patterns & 3u)) return fail(VGPU_E_INVAL, "patterns mask selects nothing");
+    VGPU_CUDA(cudaSetDevice(device));
+    void *buf = nullptr;
+    cudaError_t e = cudaMalloc(&buf, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(VGPU_E_NOMEM, "cudaMalloc(%llu): %s", (unsigned long long)bytes, cudaGetErrorString(e));
+    }
+    vgpu_memtest_result_t total{};
+    total.bytes = bytes;
+    total.first_bad_word = ~0ull;
+    total.first_bad_pattern = total.first_bad_pass = -1;
+    int rc = VGPU_OK;
+    for (int pat = 0; pat < 2 && !rc; ++pat) {
+        if (!(patterns & (1u << pat))) continue;
+        vgpu_memtest_result_t r{};
+        rc = vgpu_memtest_run(buf, bytes, pat, 0, pat == VGPU_PAT_WALKING_ONES ? 64 : random_passes, seed, nullptr, &r);
+        if (rc) break;
+        total.passes += r.passes;
+        total.mismatches += r.mismatches;
+        total.bad_bits |= r.bad_bits;
+        total.fill_ms += r.fill_ms;
+        total.verify_ms += r.verify_ms;
+        if (r.mismatches && total.first_bad_pattern < 0) {
+            total.first_bad_pattern = r.first_bad_pattern;
+            total.first_bad_pass = r.first_bad_pass;
+            total.first_bad_word = r.first_bad_word;
+        }
+    }
+    cudaFree(buf);
+    if (rc) return rc;
+    const double ms = total.fill_ms + total.verify_ms;
+    total.gbps = ms > 0 ? 2.0 * (double)bytes * (double)total.passes / (ms * 1e6) : 0.0;
+    *out = total;
+    return total.mismatches ? fail(VGPU_E_MISMATCH, "%llu mismatching words", (unsigned long long)total.mismatches) : VGPU_OK;
+}
+
+}  // extern "C"

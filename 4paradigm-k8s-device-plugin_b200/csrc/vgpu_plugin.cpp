@@ -1,0 +1,185 @@
+// Contract A helpers (include/vgpu.h): the arithmetic and string building the
+// Go plugin does in Device2VDevice / VDevicesByIDs / UniqueDeviceIDs / Allocate,
+// restated behind a C-ABI so server.go and vdevice.go can call them with cgo.
+// Pure functions over caller-owned memory: thread-safe, nothing allocated that
+// outlives the call.  Reference: vdevice.go:36-90, server.go:459-524, 565-616.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "vgpu_internal.h"
+
+using namespace vgpu;
+
+namespace {
+
+bool copy_str(char *dst, size_t cap, const std::string &s) {
+    if (s.size() + 1 > cap) return false;
+    memcpy(dst, s.c_str(), s.size() + 1);
+    return true;
+}
+
+// uuid4 text from /dev/urandom, same shape as github.com/google/uuid NewString()
+// (server.go:503): 8-4-4-4-12 lower-case hex, version nibble 4, variant 10xx.
+int random_uuid4(char out[37]) {
+    unsigned char b[16];
+    FILE *f = fopen("/dev/urandom", "rb");
+    if (!f || fread(b, 1, 16, f) != 16) {
+        if (f) fclose(f);
+        return fail(VGPU_E_INVAL, "cannot read /dev/urandom");
+    }
+    fclose(f);
+    b[6] = (b[6] & 0x0f) | 0x40;
+    b[8] = (b[8] & 0x3f) | 0x80;
+    snprintf(out, 37, "%02x%02x%02x%02x-%02x%02x-%02x%02x-%02x%02x-%02x%02x%02x%02x%02x%02x", b[0], b[1],
+             b[2], b[3], b[4], b[5], b[6], b[7], b[8], b[9], b[10], b[11], b[12], b[13], b[14], b[15]);
+    return VGPU_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int vgpu_split(const char *uuid, uint64_t total_mib, unsigned split, double mem_scaling, vgpu_desc_t *out,
+               size_t out_cap) {
+    if (!uuid || !out) return fail(VGPU_E_INVAL, "null argument");
+    if (split < 1) return fail(VGPU_E_INVAL, "invalid --device-split-count option: %u", split);  // main.go:151-153
+    if (!(mem_scaling > 0)) return fail(VGPU_E_INVAL, "invalid --device-memory-scaling option: %g", mem_scaling);  // main.go:154-156
+    const std::string u(uuid);
+    const bool mig = u.find("MIG") != std::string::npos;  // vdevice.go:40
+    const unsigned n = mig ? 1 : split;
+    if (out_cap < n) return fail(VGPU_E_RANGE, "need room for %u descriptors", n);
+    // vdevice.go:49 — float64 multiply, divide, truncate.
+    const uint64_t mem = mig ? 0 : (uint64_t)((double)total_mib * mem_scaling / (double)split);
+    for (unsigned i = 0; i < n; ++i) {
+        vgpu_desc_t &d = out[i];
+        memset(&d, 0, sizeof(d));
+        if (!copy_str(d.id, sizeof(d.id), u + "-" + std::to_string(i)) || !copy_str(d.uuid, sizeof(d.uuid), u))
+            return fail(VGPU_E_RANGE, "uuid too long");
+        d.memory_mib = mem;
+        d.index = i;
+        d.healthy = 1;
+    }
+    return (int)n;
+}
+
+int vgpu_sm_limit(unsigned split, double cores_scaling) {
+    if (split < 1) return fail(VGPU_E_INVAL, "invalid --device-split-count option: %u", split);
+    if (!(cores_scaling > 0)) return fail(VGPU_E_INVAL, "invalid --device-core-scaling option: %g", cores_scaling);  // main.go:157-159
+    return (int)(100 * cores_scaling / (double)split);  // server.go:492
+}
+
+int vgpu_lookup(const vgpu_desc_t *all, size_t n_all, const char *const *ids, size_t n_ids,
+                const vgpu_desc_t **out) {
+    if ((!all && n_all) || (!ids && n_ids) || (!out && n_ids)) return fail(VGPU_E_INVAL, "null argument");
+    for (size_t i = 0; i < n_ids; ++i) {
+        const vgpu_desc_t *hit = nullptr;
+        for (size_t j = 0; j < n_all && !hit; ++j)
+            if (strcmp(all[j].id, ids[i]) == 0) hit = &all[j];
+        if (!hit) return fail(VGPU_E_UNKNOWN_ID, "unknown device: %s", ids[i]);  // vdevice.go:72
+        out[i] = hit;
+    }
+    return VGPU_OK;
+}
+
+int vgpu_allocate_env(const vgpu_plugin_cfg_t *cfg, const vgpu_desc_t *const *req, size_t n_req,
+                      const char *const *phys_uuids, const char *const *phys_index, size_t n_phys,
+                      const char *cache_uuid, vgpu_kv_t *envs, size_t *n_envs, vgpu_mount_t *mounts,
+                      size_t *n_mounts) {
+    if (!cfg || (!req && n_req) || !envs || !n_envs || !mounts || !n_mounts)
+        return fail(VGPU_E_INVAL, "null argument");
+    const int sm = vgpu_sm_limit(cfg->split, cfg->cores_scaling);
+    if (sm < 0) return sm;
+
+    // UniqueDeviceIDs (vdevice.go:78-90): physical UUIDs, first-seen order.
+    std::vector<std::string> uuids;
+    for (size_t i = 0; i < n_req; ++i) {
+        bool seen = false;
+        for (const auto &u : uuids) seen = seen || u == req[i]->uuid;
+        if (!seen) uuids.emplace_back(req[i]->uuid);
+    }
+    // deviceIDsFromUUIDs (server.go:565-581)
+    std::vector<std::string> device_ids;
+    if (cfg->id_strategy == 0) {
+        device_ids = uuids;
+    } else if (cfg->id_strategy == 1) {
+        for (size_t d = 0; d < n_phys; ++d)  // cachedDevices order, not request order
+            for (const auto &u : uuids)
+                if (u == phys_uuids[d]) device_ids.emplace_back(phys_index[d]);
+    } else {
+        return fail(VGPU_E_INVAL, "invalid --device-id-strategy option: %d", cfg->id_strategy);
+    }
+
+    std::vector<std::pair<std::string, std::string>> kv;
+    std::vector<vgpu_mount_t> mv;
+    auto join = [](const std::vector<std::string> &v, const char *sep) {
+        std::string s;
+        for (size_t i = 0; i < v.size(); ++i) s += (i ? sep : "") + v[i];
+        return s;
+    };
+    auto add_mount = [&](const std::string &cpath, const std::string &hpath, bool ro) -> bool {
+        vgpu_mount_t m;
+        memset(&m, 0, sizeof(m));
+        if (!copy_str(m.container_path, sizeof(m.container_path), cpath) ||
+            !copy_str(m.host_path, sizeof(m.host_path), hpath))
+            return false;
+        m.read_only = ro ? 1 : 0;
+        mv.push_back(m);
+        return true;
+    };
+
+    const char *root = "/var/run/nvidia-container-devices";  // server.go:58
+    if (cfg->list_strategy == 0) {                            // envvar, server.go:469-471
+        kv.emplace_back("NVIDIA_VISIBLE_DEVICES", join(device_ids, ","));
+    } else if (cfg->list_strategy == 1) {                     // volume-mounts, server.go:472-475, 604-616
+        kv.emplace_back("NVIDIA_VISIBLE_DEVICES", root);
+        for (const auto &id : device_ids)
+            if (!add_mount(std::string(root) + "/" + id, "/dev/null", false)) return fail(VGPU_E_RANGE, "path too long");
+    } else {
+        return fail(VGPU_E_INVAL, "invalid --device-list-strategy option: %d", cfg->list_strategy);
+    }
+
+    std::vector<std::string> map_envs;
+    for (size_t i = 0; i < n_req; ++i) {  // server.go:487-491
+        kv.emplace_back("CUDA_DEVICE_MEMORY_LIMIT_" + std::to_string(i), std::to_string(req[i]->memory_mib) + "m");
+        map_envs.push_back(std::to_string(i) + ":" + req[i]->uuid);
+    }
+    kv.emplace_back("CUDA_DEVICE_SM_LIMIT", std::to_string(sm));        // server.go:492
+    kv.emplace_back("NVIDIA_DEVICE_MAP", join(map_envs, " "));          // server.go:493
+    char u4[37];
+    if (cache_uuid) {
+        if (strlen(cache_uuid) != 36) return fail(VGPU_E_INVAL, "cache_uuid must be 36 characters");
+        memcpy(u4, cache_uuid, 37);
+    } else if (int rc = random_uuid4(u4)) {
+        return rc;
+    }
+    kv.emplace_back("CUDA_DEVICE_MEMORY_SHARED_CACHE", std::string("/tmp/") + u4 + ".cache");  // server.go:503
+    if (cfg->mem_scaling > 1) kv.emplace_back("CUDA_OVERSUBSCRIBE", "true");                  // server.go:505-507
+
+    // server.go:511-522, in this order, all read-only
+    if (!add_mount("/usr/local/vgpu/libvgpu.so", "/usr/local/vgpu/libvgpu.so", true) ||
+        !add_mount("/etc/ld.so.preload", "/usr/local/vgpu/ld.so.preload", true) ||
+        !add_mount("/usr/local/vgpu/pciinfo.vgpu", cfg->pcibusfile, true) ||
+        !add_mount("/usr/bin/vgpuvalidator", "/usr/local/vgpu/vgpuvalidator", true) ||
+        !add_mount("/vgpu", "/usr/local/vgpu/license", true))
+        return fail(VGPU_E_RANGE, "path too long");
+
+    if (kv.size() > *n_envs || mv.size() > *n_mounts) {
+        *n_envs = kv.size();
+        *n_mounts = mv.size();
+        return fail(VGPU_E_RANGE, "need %zu envs and %zu mounts", kv.size(), mv.size());
+    }
+    for (size_t i = 0; i < kv.size(); ++i) {
+        memset(&envs[i], 0, sizeof(envs[i]));
+        if (!copy_str(envs[i].key, sizeof(envs[i].key), kv[i].first) ||
+            !copy_str(envs[i].val, sizeof(envs[i].val), kv[i].second))
+            return fail(VGPU_E_RANGE, "env %s too long", kv[i].first.c_str());
+    }
+    for (size_t i = 0; i < mv.size(); ++i) mounts[i] = mv[i];
+    *n_envs = kv.size();
+    *n_mounts = mv.size();
+    return VGPU_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,327 @@
+"""Host-side mirror of the reference device plugin for the hot path (Contract A).
+
+Same names, argument meaning and error behaviour as the Go code it mirrors
+(server.go, vdevice.go, nvidia.go, main.go flags), so that the parity tests read
+like tests of the reference.  All arithmetic and string building happens behind
+the C-ABI (vgpu_split / vgpu_lookup / vgpu_sm_limit / vgpu_allocate_env in
+include/vgpu.h) — this module only marshals.  MIG strategies, monitor mode and the
+legacy VDeviceController are out of scope.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Callable, Dict, Iterator, List, Optional, Sequence
+
+from . import capi
+
+# pluginapi constants (vendor/k8s.io/kubelet/pkg/apis/deviceplugin/v1beta1/constants.go:19-37)
+Healthy = "Healthy"
+Unhealthy = "Unhealthy"
+Version = "v1beta1"
+DevicePluginPath = "/var/lib/kubelet/device-plugins/"
+KubeletSocket = DevicePluginPath + "kubelet.sock"
+
+# server.go:44-58
+DeviceListStrategyEnvvar = "envvar"
+DeviceListStrategyVolumeMounts = "volume-mounts"
+DeviceIDStrategyUUID = "uuid"
+DeviceIDStrategyIndex = "index"
+
+
+@dataclass
+class Flags:
+    """CLI flags that shape Contract A, defaults as in main.go:55-133."""
+    migStrategy: str = "none"
+    passDeviceSpecs: bool = False
+    deviceListStrategy: str = DeviceListStrategyEnvvar
+    deviceIDStrategy: str = DeviceIDStrategyUUID
+    nvidiaDriverRoot: str = "/"
+    deviceSplitCount: int = 2
+    deviceMemoryScaling: float = 1.0
+    deviceCoresScaling: float = 1.0
+    enableLegacyPreferred: bool = False
+    pcibusfile: str = "/usr/local/vgpu/pciinfo.vgpu"  # $PCIBUSFILE, main.go:164-185
+
+
+def validateFlags(f: Flags) -> None:
+    """main.go:143-161 — same messages."""
+    if f.deviceListStrategy not in (DeviceListStrategyEnvvar, DeviceListStrategyVolumeMounts):
+        raise ValueError(f"invalid --device-list-strategy option: {f.deviceListStrategy}")
+    if f.deviceIDStrategy not in (DeviceIDStrategyUUID, DeviceIDStrategyIndex):
+        raise ValueError(f"invalid --device-id-strategy option: {f.deviceIDStrategy}")
+    if f.deviceSplitCount < 1:
+        raise ValueError(f"invalid --device-split-count option: {f.deviceSplitCount}")
+    if f.deviceMemoryScaling <= 0:
+        raise ValueError(f"invalid --device-memory-scaling option: {f.deviceMemoryScaling}")
+    if f.deviceCoresScaling <= 0:
+        raise ValueError(f"invalid --device-core-scaling option: {f.deviceCoresScaling}")
+
+
+@dataclass
+class Device:
+    """nvidia.go:36-41 + buildDevice (148-164).  `memory_mib` stands in for the NVML
+    lookup Device2VDevice does (vdevice.go:47; nvml bindings.go:504-507, MiB)."""
+    ID: str
+    Index: str = "0"
+    Paths: List[str] = field(default_factory=list)
+    Health: str = Healthy
+    numa: Optional[int] = None
+    memory_mib: int = 0
+
+
+@dataclass
+class VDevice:
+    """vdevice.go:29-33."""
+    ID: str
+    dev: Device
+    memory: int
+    Health: str = Healthy
+    _desc: Optional[capi.Desc] = None
+
+    @property
+    def Topology(self):
+        return None if self.dev.numa is None else {"Nodes": [{"ID": self.dev.numa}]}
+
+
+@dataclass
+class Mount:
+    ContainerPath: str
+    HostPath: str
+    ReadOnly: bool = False
+
+
+@dataclass
+class DeviceSpec:
+    ContainerPath: str
+    HostPath: str
+    Permissions: str
+
+
+@dataclass
+class ContainerAllocateResponse:
+    Envs: Dict[str, str] = field(default_factory=dict)
+    Mounts: List[Mount] = field(default_factory=list)
+    Devices: List[DeviceSpec] = field(default_factory=list)
+    Annotations: Dict[str, str] = field(default_factory=dict)
+
+
+class PluginError(Exception):
+    """Stands in for the gRPC error a failing RPC returns; str() is the Go error text."""
+
+
+def Device2VDevice(devices: Sequence[Device], flags: Flags) -> List[VDevice]:
+    """vdevice.go:36-58 via vgpu_split."""
+    out: List[VDevice] = []
+    for d in devices:
+        arr = (capi.Desc * max(1, flags.deviceSplitCount))()
+        n = capi.check(capi.lib.vgpu_split(d.ID.encode(), d.memory_mib, flags.deviceSplitCount,
+                                           flags.deviceMemoryScaling, arr, len(arr)))
+        for i in range(n):
+            desc = capi.Desc.from_buffer_copy(arr[i])
+            out.append(VDevice(ID=desc.id.decode(), dev=d, memory=desc.memory_mib, Health=d.Health, _desc=desc))
+    return out
+
+
+def _desc_array(vdevices: Sequence[VDevice]):
+    arr = (capi.Desc * max(1, len(vdevices)))()
+    for i, vd in enumerate(vdevices):
+        arr[i] = vd._desc
+    return arr
+
+
+def VDevicesByIDs(vdevices: Sequence[VDevice], ids: Sequence[str]) -> List[VDevice]:
+    """vdevice.go:61-75 via vgpu_lookup; raises PluginError('unknown device: <id>')."""
+    arr = _desc_array(vdevices)
+    cids = (C.c_char_p * max(1, len(ids)))(*[s.encode() for s in ids])
+    out = (C.POINTER(capi.Desc) * max(1, len(ids)))()
+    rc = capi.lib.vgpu_lookup(arr, len(vdevices), cids, len(ids), out)
+    if rc == capi.E_UNKNOWN_ID:
+        raise PluginError(capi.last_error())
+    capi.check(rc)
+    base = C.addressof(arr)
+    res = []
+    for i in range(len(ids)):
+        idx = (C.addressof(out[i].contents) - base) // C.sizeof(capi.Desc)
+        res.append(vdevices[idx])
+    return res
+
+
+def UniqueDeviceIDs(vdevices: Sequence[VDevice]) -> List[str]:
+    """vdevice.go:78-90 (first-seen order)."""
+    ids: List[str] = []
+    for vd in vdevices:
+        if vd.dev.ID not in ids:
+            ids.append(vd.dev.ID)
+    return ids
+
+
+def simplePolicy(available: List[str], required: List[str], size: int) -> List[str]:
+    """Stand-in for gpuallocator.NewBestEffortPolicy (besteffort_policy.go:34-90) over
+    *physical* UUIDs.  The NVLink-topology scoring is out of scope (SURVEY.md §2 row
+    20); the edge cases the reference's callers rely on are kept: size<=0, fewer
+    available than size, or required not within available -> empty result."""
+    if size <= 0 or len(available) < size or len(required) > size:
+        return []
+    if any(r not in available for r in required):
+        return []
+    chosen = list(required)
+    for a in available:
+        if len(chosen) >= size:
+            break
+        if a not in chosen:
+            chosen.append(a)
+    return chosen
+
+
+class ResourceManager:
+    """nvidia.go:43-46; here a list supplied by the caller (a mock NVML in tests)."""
+
+    def __init__(self, devices: Sequence[Device]):
+        self._devices = list(devices)
+
+    def Devices(self) -> List[Device]:
+        return list(self._devices)
+
+
+class NvidiaDevicePlugin:
+    """server.go:62-655, non-MIG / non-monitor / non-legacy path."""
+
+    def __init__(self, resourceName: str, resourceManager: ResourceManager, deviceListEnvvar: str,
+                 allocatePolicy: Optional[Callable[[List[str], List[str], int], List[str]]], socket: str,
+                 flags: Optional[Flags] = None):
+        self.resourceName = resourceName
+        self.resourceManager = resourceManager
+        self.deviceListEnvvar = deviceListEnvvar
+        self.allocatePolicy = allocatePolicy
+        self.socket = socket
+        self.flags = flags or Flags()
+        validateFlags(self.flags)
+        self.migStrategy = self.flags.migStrategy
+        self.vDeviceController = None  # legacy mode: out of scope
+        self.cachedDevices: List[Device] = []
+        self.vDevices: List[VDevice] = []
+        self._health_events: List[Device] = []
+
+    # server.go:98-115
+    def initialize(self) -> None:
+        self.cachedDevices = self.resourceManager.Devices()
+        self.vDevices = Device2VDevice(self.cachedDevices, self.flags)
+
+    # server.go:221-243 — what Register sends to kubelet
+    def Register(self) -> dict:
+        return {
+            "Version": Version,
+            "Endpoint": self.socket.rsplit("/", 1)[-1],
+            "ResourceName": self.resourceName,
+            "Options": {"GetPreferredAllocationAvailable": self.allocatePolicy is not None and self.vDeviceController is None},
+        }
+
+    # server.go:246-251
+    def GetDevicePluginOptions(self) -> dict:
+        return {"GetPreferredAllocationAvailable": self.allocatePolicy is not None}
+
+    # server.go:583-596
+    def apiDevices(self) -> List[dict]:
+        out = []
+        if self.migStrategy == "none":
+            for d in self.vDevices:
+                d.Health = d.dev.Health
+                out.append({"ID": d.ID, "Health": d.Health, "Topology": d.Topology})
+        else:
+            for d in self.cachedDevices:
+                out.append({"ID": d.ID, "Health": d.Health, "Topology": None})
+        return out
+
+    def markUnhealthy(self, dev: Device) -> None:
+        """What checkHealth does through the m.health channel (nvidia.go:166-237)."""
+        self._health_events.append(dev)
+
+    # server.go:254-268 — yields the initial list, then one list per health event
+    def ListAndWatch(self) -> Iterator[List[dict]]:
+        yield self.apiDevices()
+        while self._health_events:
+            d = self._health_events.pop(0)
+            d.Health = Unhealthy  # "no way to recover from the Unhealthy state"
+            yield self.apiDevices()
+
+    # server.go:271-326
+    def GetPreferredAllocation(self, containerRequests: Sequence[dict]) -> Optional[List[List[str]]]:
+        if self.migStrategy == "mixed":
+            return None
+        responses = []
+        for req in containerRequests:
+            try:
+                availableVDev = VDevicesByIDs(self.vDevices, req.get("AvailableDeviceIDs", []))
+            except PluginError as e:
+                raise PluginError(f"Unable to retrieve list of available vdevices: {e}")
+            available = UniqueDeviceIDs(availableVDev)
+            try:
+                requiredVDev = VDevicesByIDs(self.vDevices, req.get("MustIncludeDeviceIDs", []))
+            except PluginError as e:
+                raise PluginError(f"Unable to retrieve list of available vdevices: {e}")
+            required = UniqueDeviceIDs(requiredVDev)
+            size = int(req.get("AllocationSize", 0))
+            allocated = self.allocatePolicy(available, required, size)
+            if len(allocated) == 0 and len(available) >= size:
+                allocated = available[0:size]
+            deviceIds = []
+            for uuid in allocated:
+                for vd in availableVDev:
+                    if vd.dev.ID == uuid:
+                        deviceIds.append(vd.ID)
+                        break
+            responses.append(deviceIds)
+        return responses
+
+    # server.go:361-533
+    def Allocate(self, containerRequests: Sequence[Sequence[str]], _cache_uuid: Optional[str] = None) -> List[ContainerAllocateResponse]:
+        f = self.flags
+        cfg = capi.PluginCfg(split=f.deviceSplitCount, mem_scaling=f.deviceMemoryScaling,
+                             cores_scaling=f.deviceCoresScaling,
+                             id_strategy=0 if f.deviceIDStrategy == DeviceIDStrategyUUID else 1,
+                             list_strategy=0 if f.deviceListStrategy == DeviceListStrategyEnvvar else 1,
+                             pcibusfile=f.pcibusfile.encode())
+        n_phys = len(self.cachedDevices)
+        phys_uuid = (C.c_char_p * max(1, n_phys))(*[d.ID.encode() for d in self.cachedDevices])
+        phys_idx = (C.c_char_p * max(1, n_phys))(*[d.Index.encode() for d in self.cachedDevices])
+        responses = []
+        for ids in containerRequests:
+            vdevices = VDevicesByIDs(self.vDevices, list(ids))
+            req = (C.POINTER(capi.Desc) * max(1, len(vdevices)))(*[C.pointer(vd._desc) for vd in vdevices])
+            envs = (capi.KV * 64)()
+            mounts = (capi.Mount * 64)()
+            n_envs, n_mounts = C.c_size_t(64), C.c_size_t(64)
+            capi.check(capi.lib.vgpu_allocate_env(C.byref(cfg), req, len(vdevices), phys_uuid, phys_idx, n_phys,
+                                                  _cache_uuid.encode() if _cache_uuid else None,
+                                                  envs, C.byref(n_envs), mounts, C.byref(n_mounts)))
+            resp = ContainerAllocateResponse()
+            for i in range(n_envs.value):
+                resp.Envs[envs[i].key.decode()] = envs[i].val.decode()
+            for i in range(n_mounts.value):
+                resp.Mounts.append(Mount(mounts[i].container_path.decode(), mounts[i].host_path.decode(), bool(mounts[i].read_only)))
+            if f.passDeviceSpecs:
+                resp.Devices = self.apiDeviceSpecs(f.nvidiaDriverRoot, UniqueDeviceIDs(vdevices))
+            responses.append(resp)
+        return responses
+
+    # server.go:618-655 (the four control nodes are included only if they exist on the host)
+    def apiDeviceSpecs(self, driverRoot: str, uuids: Sequence[str], _exists=None) -> List[DeviceSpec]:
+        import os
+        exists = _exists or os.path.exists
+        specs = []
+        for p in ("/dev/nvidiactl", "/dev/nvidia-uvm", "/dev/nvidia-uvm-tools", "/dev/nvidia-modeset"):
+            if exists(p):
+                specs.append(DeviceSpec(p, os.path.join(driverRoot, p.lstrip("/")) if driverRoot != "/" else p, "rw"))
+        for d in self.cachedDevices:
+            for u in uuids:
+                if d.ID == u:
+                    for p in d.Paths:
+                        specs.append(DeviceSpec(p, os.path.join(driverRoot, p.lstrip("/")) if driverRoot != "/" else p, "rw"))
+        return specs
+
+
+def NewNvidiaDevicePlugin(resourceManager: ResourceManager, flags: Optional[Flags] = None) -> NvidiaDevicePlugin:
+    """migStrategyNone.GetPlugins (mig-strategy.go:62-71)."""
+    return NvidiaDevicePlugin("nvidia.com/gpu", resourceManager, "NVIDIA_VISIBLE_DEVICES", simplePolicy,
+                              DevicePluginPath + "nvidia-gpu.sock", flags)

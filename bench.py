@@ -1,0 +1,454 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json's metric on BASELINE.json's configs.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Headline (`value`): vgpuvalidator memtest HBM GB/s on config 2 — 4 vGPUs x 40 GiB on each
+B200, each vGPU in its own 25 % green-context SM partition, one step = one walking-ones
+pass + one random pass (fill kernel, then verify kernel) over every vGPU buffer;
+algorithmic bytes = 2N per pass.  `spill_restore` carries the other half
+of the metric: 2 MiB-chunk spill/restore GB/s per tier (local HBM, pinned host, and for
+N>1 the peer GPU over NVLink in a ring g -> g+1) and per kernel variant.
+One JSON line on stdout (rank 0).  See DESIGN.md §Measurement.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "vGPU spill/restore GB/s per GPU + 8-GPU aggregate; memtest HBM GB/s vs peak"
+GIB = 1 << 30
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--vgpus", type=int, default=4, help="vGPUs per GPU (config 2: 4)")
+    ap.add_argument("--vgpu-gib", type=float, default=40.0, help="memtest buffer per vGPU in GiB (config 2: 40)")
+    ap.add_argument("--spill-chunks", type=int, default=4096, help="largest batch of the 2 MiB chunk sweep (config 4: 4096)")
+    ap.add_argument("--no-spill", action="store_true", help="skip the spill/restore sweep")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-gib", type=float, default=2.0, help="host buffer of the CPU memtest sample")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    except Exception:
+        return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc:
+            self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 6] or [r for _, r in self.rows if len(r) >= 6]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        mhz = [int(r[0]) for r in rows if r[0].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(mhz) if mhz else None, "sm_max_mhz": int(rows[0][1]) if rows[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(rows)}
+
+
+# ----------------------------------------------------------------------------- CPU legs (oracle)
+def cpu_memtest_sample(gib, threads, passes_each=1):
+    """The oracle's fill+verify (walking-ones pass + random pass) over a host buffer: the
+    same math the GPU runs, on the host cores.  Returns (GB/s counted as 2N per pass, seconds)."""
+    import numpy as np
+    from oracle import cpu
+    nwords = int(gib * GIB) // 8
+    buf = np.zeros(nwords, dtype=np.uint64)  # touch pages before timing
+    sec = 0.0
+    bad = 0
+    for pat in (cpu.PAT_WALKING_ONES, cpu.PAT_RANDOM):
+        s, b = cpu.memtest_mt(buf, pat, 0, passes_each, 0, threads)
+        sec += s
+        bad += b
+    assert bad == 0
+    return 2.0 * nwords * 8 * 2 * passes_each / sec / 1e9, sec
+
+
+def cpu_spill_sample(nchunks, threads):
+    import numpy as np
+    from oracle import cpu
+    cb = 2097152
+    src = cpu.fill(nchunks * cb // 8, cpu.PAT_RANDOM, 0).copy()
+    dst = np.zeros_like(src)
+    best = 0.0
+    for _ in range(3):
+        sec, _xs = cpu.spill_mt(src, dst, nchunks, cb, threads)
+        best = max(best, nchunks * cb / sec / 1e9)
+    return best
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference has no CPU (or any) implementation of memtest or
+    explicit spill — its vgpuvalidator is a license tool and its oversubscription is UVM
+    paging inside the NVIDIA driver.  Per the task's tier rules the arm then
+    times the oracle port of the path on all host cores, on a bounded sample per step."""
+    if rank != 0:
+        return
+    cores = len(os.sched_getaffinity(0))
+    gib = args.cpu_gib
+    for _ in range(max(1, min(args.warmup, 1))):
+        cpu_memtest_sample(min(gib, 0.25), cores)
+    t0 = time.perf_counter()
+    vals = [cpu_memtest_sample(gib, cores)[0] for _ in range(args.steps)]
+    dt = time.perf_counter() - t0
+    v = statistics.mean(vals)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(1e3 * dt / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "config 2 memtest (walking-ones + random, fill+verify, 2N bytes/pass), CPU oracle port on host cores",
+                   "sample": f"{gib} GiB host buffer per step instead of 4 x 40 GiB"},
+        "cpu_baseline": {"value": round(v, 3), "unit": "GB/s", "cores": cores, "kind": "port",
+                         "sample": f"{gib} GiB buffer, 1 walking-ones + 1 random pass per step, {args.steps} steps"},
+        "e2e": {"value": round(v, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- GPU legs
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import vgpu_b200  # noqa: F401
+    from vgpu_b200 import capi, datapath as dp
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: the vGPU data path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    hbm_peak, peak_src = peaks()
+    out_extra = {}
+
+    # ---------------- phase A: spill / restore sweep (config 4; peer ring of config 5) --------
+    if not args.no_spill:
+        out_extra["spill_restore"] = spill_sweep(args, capi, dp, torch, dev, local, world, barrier, max_over_ranks, sum_over_ranks)
+
+    # ---------------- phase B: memtest (config 2) ---------------------------------------
+    nv = args.vgpus
+    free, total = torch.cuda.mem_get_info(dev)
+    per = int(args.vgpu_gib * GIB)
+    note = None
+    if per * nv > free - 4 * GIB:
+        per = max(GIB, ((free - 4 * GIB) // nv) // (2 << 20) * (2 << 20))
+        note = f"scaled to {per / GIB:.2f} GiB per vGPU: only {free / GIB:.1f} GiB free"
+    bufs = [torch.empty(per, dtype=torch.uint8, device=dev) for _ in range(nv)]
+
+    parts = (capi.SmPartition * nv)()
+    pct = int(100 / nv)
+    rc = capi.lib.vgpu_sm_partition_create(local, pct, nv, parts)
+    if rc == 0:
+        streams = [torch.cuda.ExternalStream(p.stream, device=dev) for p in parts]
+        partition = {"kind": "green_ctx", "percent": pct, "sm_per_vgpu": [p.sm_count for p in parts], "sm_total": parts[0].sm_total}
+    else:  # measured and reported as such, not hidden
+        streams = [torch.cuda.Stream(device=dev) for _ in range(nv)]
+        partition = {"kind": "plain_streams", "why": capi.last_error()}
+    results = [torch.zeros(3, dtype=torch.int64, device=dev) for _ in range(nv)]
+
+    def step(s):
+        for i in range(nv):
+            st = streams[i]
+            for pat, p in ((capi.PAT_WALKING_ONES, s % 64), (capi.PAT_RANDOM, s)):
+                dp.memtest_fill(bufs[i], pat, p, stream=st)
+                dp.memtest_verify(bufs[i], pat, p, result=results[i], stream=st)
+
+    main_stream = torch.cuda.current_stream()
+
+    def timed(nsteps, first):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ends = [torch.cuda.Event() for _ in range(nv)]
+        ev0.record(main_stream)
+        for st in streams:
+            st.wait_event(ev0)
+        for s in range(first, first + nsteps):
+            step(s)
+        for st, e in zip(streams, ends):
+            e.record(st)
+            main_stream.wait_event(e)
+        ev1.record(main_stream)
+        return ev0, ev1
+
+    timed(args.warmup, 0)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.3)
+    barrier()
+    t0 = time.perf_counter()
+    ev0, ev1 = timed(args.steps, args.warmup)
+    barrier()
+    t1 = time.perf_counter()
+    clocks = sampler.stop(t0, t1)
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    bad = sum(int(r[0].item()) for r in results)
+    if bad:
+        raise SystemExit(f"memtest found {bad} mismatching words: not a valid bench run")
+    bytes_per_step_rank = 2 * per * 2 * nv  # (fill+verify) x 2 patterns x vGPUs
+    value = world * bytes_per_step_rank * args.steps / (ms * 1e6)
+    launches = args.steps * nv * 4
+
+    # per-kernel durations, each timed alone on vGPU 0's stream (CUDA events on that stream)
+    kern = {}
+    st0 = streams[0]
+    for name, pat, fn in (("fill_walking", capi.PAT_WALKING_ONES, "f"), ("verify_walking", capi.PAT_WALKING_ONES, "v"),
+                          ("fill_random", capi.PAT_RANDOM, "f"), ("verify_random", capi.PAT_RANDOM, "v")):
+        dp.memtest_fill(bufs[0], pat, 1, stream=st0)
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        for k in range(3):
+            e[k].record(st0)
+            if fn == "f":
+                dp.memtest_fill(bufs[0], pat, 1, stream=st0)
+            else:
+                dp.memtest_verify(bufs[0], pat, 1, result=results[0], stream=st0)
+        e[3].record(st0)
+        torch.cuda.synchronize()
+        kms = e[0].elapsed_time(e[3]) / 3
+        kern[name] = {"ms": round(kms, 4), "GBps": round(per / (kms * 1e6), 1)}
+    # whole-GPU (no partition) numbers for the same four kernels, one vGPU buffer at a time
+    whole = {}
+    for name, pat, fn in (("fill_walking", capi.PAT_WALKING_ONES, "f"), ("verify_walking", capi.PAT_WALKING_ONES, "v"),
+                          ("fill_random", capi.PAT_RANDOM, "f"), ("verify_random", capi.PAT_RANDOM, "v")):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dp.memtest_fill(bufs[0], pat, 1)
+        e0.record()
+        for k in range(3):
+            if fn == "f":
+                dp.memtest_fill(bufs[0], pat, 1)
+            else:
+                dp.memtest_verify(bufs[0], pat, 1, result=results[0])
+        e1.record()
+        torch.cuda.synchronize()
+        kms = e0.elapsed_time(e1) / 3
+        whole[name] = {"ms": round(kms, 4), "GBps": round(per / (kms * 1e6), 1)}
+    dom = max(whole, key=lambda k: whole[k]["ms"])
+
+    # e2e: the blocking C-ABI call a user of vgpuvalidator makes (vgpu_memtest_run), one host
+    # thread per vGPU, result blocks read back to the host every pass; wall clock.
+    def e2e_worker(i, s0, n):
+        torch.cuda.set_device(local)
+        for s in range(s0, s0 + n):
+            for pat, p in ((capi.PAT_WALKING_ONES, s % 64), (capi.PAT_RANDOM, s)):
+                r = dp.memtest_run(bufs[i], pat, p, 1, stream=streams[i])
+                assert r.mismatches == 0
+
+    def e2e_run(s0, n):
+        th = [threading.Thread(target=e2e_worker, args=(i, s0, n)) for i in range(nv)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+
+    e2e_run(0, 1)
+    barrier()
+    w0 = time.perf_counter()
+    e2e_run(1, args.steps)
+    barrier()
+    e2e_ms = max_over_ranks((time.perf_counter() - w0) * 1e3)
+    e2e_value = world * bytes_per_step_rank * args.steps / (e2e_ms * 1e6)
+
+    line = None
+    if rank == 0:
+        cpu_base = None
+        if not args.no_cpu:
+            cores = len(os.sched_getaffinity(0))
+            v, sec = cpu_memtest_sample(args.cpu_gib, cores, passes_each=2)
+            v1, _ = cpu_memtest_sample(min(args.cpu_gib, 0.5), 1)
+            cpu_base = {"value": round(v, 3), "unit": "GB/s", "cores": cores, "kind": "port",
+                        "sample": f"oracle memtest, {args.cpu_gib} GiB host buffer, 2 walking-ones + 2 random passes ({sec:.1f} s)",
+                        "one_thread_GBps": round(v1, 3),
+                        "host_memcpy_spill_GBps": {"1_thread": round(cpu_spill_sample(64, 1), 2), f"{cores}_threads": round(cpu_spill_sample(256, cores), 2)}}
+        line = {
+            "metric": METRIC, "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": f"config 2: vgpuvalidator memtest, {nv} vGPUs x {per / GIB:.2f} GiB per B200, walking-ones + random, fill+verify, bit-exact",
+                       "bytes_counted": "2N per pass (N written by fill + N read by verify)", "l2": "inputs (>=1 GiB per vGPU) larger than the 126 MB L2",
+                       "sm_partition": partition, "note": note},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_value, 2), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": nv * 2 * 24,
+                    "call": "vgpu_memtest_run (blocking C-ABI, one host thread per vGPU, result block read back each pass)",
+                    "note": "a memtest has no host input: patterns are generated on the device by definition; host<->device e2e numbers for the spill path are in spill_restore.host.e2e_*"},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "achieved": whole[dom]["GBps"], "peak": hbm_peak, "unit": "GB/s",
+                         "frac": round(whole[dom]["GBps"] / hbm_peak, 4), "traffic": None, "kernel": f"k_memtest_{dom} (whole GPU, timed alone)",
+                         "peak_source": peak_src, "whole_gpu": whole, "one_partition": kern,
+                         "step_aggregate": {"GBps": round(value / world, 1), "frac": round(value / world / hbm_peak, 4),
+                                            "frac_of_8TBps_spec": round(value / world / 8000.0, 4)}},
+            "cpu_baseline": cpu_base,
+        }
+        line.update(out_extra)
+        print(json.dumps(line), flush=True)
+    if rc == 0:
+        torch.cuda.synchronize()
+        capi.lib.vgpu_sm_partition_destroy(parts, nv)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def spill_sweep(args, capi, dp, torch, dev, local, world, barrier, max_over_ranks, sum_over_ranks):
+    """Config 4 sweep: batches of 1..4096 x 2 MiB chunks, per tier and kernel variant, device-timed
+    with CUDA events (max over ranks, summed over GPUs).  Restores verify checksums in-kernel and
+    the round trip is checked bit-exact once per tier."""
+    cb = capi.CHUNK_BYTES
+    nmax = args.spill_chunks
+    sizes = [n for n in (1, 8, 64, 512, 4096) if n <= nmax]
+    variants = {"ldst": capi.XFER_LDST, "tma": capi.XFER_TMA, "ce": capi.XFER_CE}
+    hbm = torch.empty(nmax * cb, dtype=torch.uint8, device=dev)
+    dp.memtest_fill(hbm, capi.PAT_RANDOM, 1000 + local)
+    back = torch.empty_like(hbm)
+    ck = torch.zeros((nmax, 2), dtype=torch.int64, device=dev)
+    res = torch.zeros(2, dtype=torch.int64, device=dev)
+    tiers = {}
+    local_slab = torch.empty_like(hbm)
+    tiers["local"] = (capi.TIER_LOCAL, local_slab.data_ptr(), None)
+    host = torch.empty(min(nmax, 1024) * cb, dtype=torch.uint8).pin_memory()
+    tiers["host"] = (capi.TIER_HOST, host.data_ptr(), min(nmax, 1024))
+    peer_slab = C.c_void_p()
+    if world > 1:
+        peer = (local + 1) % world
+        rc = capi.lib.vgpu_slab_alloc(capi.TIER_PEER, local, peer, nmax * cb, C.byref(peer_slab))
+        if rc != 0:
+            raise SystemExit("peer slab: " + capi.last_error())
+        tiers["peer"] = (capi.TIER_PEER, peer_slab.value, None)
+    out = {"chunk_bytes": cb, "bytes_counted": "payload once per chunk per direction", "timing": "CUDA events on the launch stream, best of 5 after 2 warm-ups, max over ranks"}
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def time_call(fn, reps=5, warm=2):
+        for _ in range(warm):
+            fn()
+        best = 1e30
+        for _ in range(reps):
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, max_over_ranks(e0.elapsed_time(e1)))
+        return best
+
+    for tname, (tier, slab, cap) in tiers.items():
+        tout = {}
+        for n in sizes:
+            if cap is not None and n > cap:
+                continue
+            row = {}
+            for vname, v in variants.items():
+                def do_spill():
+                    capi.check(capi.lib.vgpu_spill(v, tier, hbm.data_ptr(), slab, None, None, n, cb, ck.data_ptr(), stream))
+
+                def do_restore():
+                    capi.check(capi.lib.vgpu_restore(v, tier, slab, back.data_ptr(), None, None, n, cb, ck.data_ptr(), None, res.data_ptr(), stream))
+                ms_s = time_call(do_spill)
+                ms_r = time_call(do_restore)
+                row[vname] = {"spill_GBps": round(world * n * cb / (ms_s * 1e6), 1), "restore_GBps": round(world * n * cb / (ms_r * 1e6), 1)}
+            tout[str(n)] = row
+        # bit-exactness of the round trip on the largest batch of this tier
+        n = max(int(k) for k in tout)
+        back[: n * cb].zero_()
+        res.zero_()
+        capi.check(capi.lib.vgpu_spill(capi.XFER_AUTO, tier, hbm.data_ptr(), slab, None, None, n, cb, ck.data_ptr(), stream))
+        capi.check(capi.lib.vgpu_restore(capi.XFER_AUTO, tier, slab, back.data_ptr(), None, None, n, cb, ck.data_ptr(), None, res.data_ptr(), stream))
+        torch.cuda.synchronize()
+        ok = res.cpu().tolist() == [0, 0] and torch.equal(back[: n * cb], hbm[: n * cb])
+        if not ok:
+            raise SystemExit(f"spill/restore round trip on tier {tname} is not bit-exact")
+        tout["round_trip_bit_exact"] = True
+        out[tname] = tout
+    # e2e host-buffer entry points (blocking, wall clock): vgpu_spill_to_host / vgpu_restore_from_host
+    n = min(nmax, 1024)
+    hck = (capi.Cksum * n)()
+    bad = C.c_uint64(0)
+    e2e = {}
+    for vname, v in variants.items():
+        for _ in range(2):
+            capi.check(capi.lib.vgpu_spill_to_host(v, local, hbm.data_ptr(), host.data_ptr(), n, cb, hck))
+        barrier()
+        w0 = time.perf_counter()
+        for _ in range(3):
+            capi.check(capi.lib.vgpu_spill_to_host(v, local, hbm.data_ptr(), host.data_ptr(), n, cb, hck))
+        ws = max_over_ranks((time.perf_counter() - w0) / 3)
+        barrier()
+        w0 = time.perf_counter()
+        for _ in range(3):
+            capi.check(capi.lib.vgpu_restore_from_host(v, local, host.data_ptr(), back.data_ptr(), n, cb, hck, C.byref(bad)))
+        wr = max_over_ranks((time.perf_counter() - w0) / 3)
+        e2e[vname] = {"spill_GBps": round(world * n * cb / ws / 1e9, 2), "restore_GBps": round(world * n * cb / wr / 1e9, 2)}
+    out["host"]["e2e_host_buffer_calls"] = {"chunks": n, "d2h_bytes_per_call": n * cb + n * 16, "h2d_bytes_per_call": n * cb + n * 16, **e2e}
+    if peer_slab.value:
+        barrier()
+        capi.lib.vgpu_slab_free(capi.TIER_PEER, local, (local + 1) % world, peer_slab)
+    del hbm, back, local_slab, host
+    torch.cuda.empty_cache()
+    return out
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,243 @@
+/*
+ * vgpu.h — C-ABI of the B200-native vGPU data path and plugin helpers.
+ *
+ * This is the boundary a maintainer of gpues/4paradigm-k8s-device-plugin binds
+ * from Go with cgo.  Everything is `extern "C"`, plain
+ * pointers and sizes; no C++ or torch types cross it.  Citations are to the
+ * reference tree (`/root/reference/...`) or, for the prebuilt shim, to
+ * `vgpu/libvgpu.so@<vaddr> <symbol>` as in SURVEY.md §8.
+ *
+ * Conventions
+ *   - return 0 on success; negative values are VGPU_E_*; vgpu_last_error()
+ *     returns a thread-local message for the last failure on this thread.
+ *   - "device pointer" means any address the launching GPU can dereference:
+ *     its own HBM, a P2P-enabled peer's HBM, or mapped pinned host memory.
+ *   - `stream` is a cudaStream_t / CUstream passed as void* (NULL = default).
+ *   - data-path calls are asynchronous on `stream` unless stated otherwise.
+ *   - there is NO CPU fallback anywhere behind this header.
+ */
+#ifndef VGPU_H_
+#define VGPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VGPU_ABI_VERSION 1
+
+/* ---- error codes ------------------------------------------------------- */
+#define VGPU_OK            0
+#define VGPU_E_INVAL      (-1)  /* bad argument (alignment, size, NULL) */
+#define VGPU_E_CUDA       (-2)  /* a CUDA runtime/driver call failed */
+#define VGPU_E_NOMEM      (-3)  /* allocation failed / capacity exceeded */
+#define VGPU_E_UNKNOWN_ID (-4)  /* "unknown device: <id>" (vdevice.go:72) */
+#define VGPU_E_RANGE      (-5)  /* caller array too small */
+#define VGPU_E_MISMATCH   (-6)  /* checksum / pattern mismatch detected */
+#define VGPU_E_UNSUPPORTED (-7)
+
+int         vgpu_abi_version(void);
+const char *vgpu_last_error(void);
+
+/* ======================================================================== *
+ *  Contract A — what Allocate/ListAndWatch hand to kubelet
+ * ======================================================================== */
+
+#define VGPU_ID_LEN    128
+#define VGPU_KEY_LEN    64
+#define VGPU_VAL_LEN  1024
+#define VGPU_PATH_LEN  256
+
+/* One virtual device.  Replaces `type VDevice` (vdevice.go:29-33). */
+typedef struct vgpu_desc {
+    char     id[VGPU_ID_LEN];    /* "<UUID>-<i>"            vdevice.go:52 */
+    char     uuid[VGPU_ID_LEN];  /* physical GPU UUID       nvidia.go:150 */
+    uint64_t memory_mib;         /* per-vGPU quota in MiB   vdevice.go:49 */
+    uint32_t index;              /* i within the physical GPU */
+    uint32_t healthy;            /* 1 = "Healthy"           nvidia.go:151 */
+} vgpu_desc_t;
+
+typedef struct vgpu_kv    { char key[VGPU_KEY_LEN]; char val[VGPU_VAL_LEN]; } vgpu_kv_t;
+typedef struct vgpu_mount { char container_path[VGPU_PATH_LEN]; char host_path[VGPU_PATH_LEN]; int32_t read_only; } vgpu_mount_t;
+
+/* Plugin flags that shape Contract A (main.go:98-118, 70-96). */
+typedef struct vgpu_plugin_cfg {
+    uint32_t split;              /* --device-split-count    main.go:98-103  */
+    double   mem_scaling;        /* --device-memory-scaling main.go:105-110 */
+    double   cores_scaling;      /* --device-cores-scaling  main.go:112-117 */
+    int32_t  id_strategy;        /* 0 uuid, 1 index         main.go:84-89   */
+    int32_t  list_strategy;      /* 0 envvar, 1 volume-mounts main.go:77-82 */
+    char     pcibusfile[VGPU_PATH_LEN]; /* $PCIBUSFILE      server.go:516   */
+} vgpu_plugin_cfg_t;
+
+/* Replaces Device2VDevice (vdevice.go:36-58) for one physical GPU.
+ * Writes `split` descriptors (1 with memory 0 if uuid contains "MIG",
+ * vdevice.go:40-46).  Returns the number written or VGPU_E_*. */
+int vgpu_split(const char *uuid, uint64_t total_mib, unsigned split,
+               double mem_scaling, vgpu_desc_t *out, size_t out_cap);
+
+/* CUDA_DEVICE_SM_LIMIT value: int(100*coresScaling/float64(split)), server.go:492. */
+int vgpu_sm_limit(unsigned split, double cores_scaling);
+
+/* Replaces VDevicesByIDs (vdevice.go:61-75): order-preserving lookup.
+ * On an unknown id returns VGPU_E_UNKNOWN_ID and vgpu_last_error() is
+ * exactly "unknown device: <id>". */
+int vgpu_lookup(const vgpu_desc_t *all, size_t n_all, const char *const *ids,
+                size_t n_ids, const vgpu_desc_t **out);
+
+/* Replaces the per-container body of Allocate (server.go:459-524) for the
+ * non-MIG, non-monitor, non-legacy path: env map (insertion order is not
+ * significant in the reference — Go map — we emit a fixed order) and the
+ * mount list in the reference's order.  `phys_uuids`/`phys_index` describe
+ * cachedDevices for the index strategy (server.go:565-581).
+ * `cache_uuid` is the 36-char uuid4 string for CUDA_DEVICE_MEMORY_SHARED_CACHE
+ * (server.go:503); NULL = generate one from /dev/urandom. */
+int vgpu_allocate_env(const vgpu_plugin_cfg_t *cfg,
+                      const vgpu_desc_t *const *req, size_t n_req,
+                      const char *const *phys_uuids, const char *const *phys_index, size_t n_phys,
+                      const char *cache_uuid,
+                      vgpu_kv_t *envs, size_t *n_envs,      /* in: capacity, out: count */
+                      vgpu_mount_t *mounts, size_t *n_mounts);
+
+/* ======================================================================== *
+ *  Virtual-device-memory data path: 2 MiB chunk spill / restore
+ *  (new mechanism behind CUDA_OVERSUBSCRIBE, server.go:505-507; the reference
+ *  delegates to cuMemAllocManaged, libvgpu.so@0x32146 cuMemoryAllocate.)
+ * ======================================================================== */
+
+#define VGPU_CHUNK_BYTES 2097152u   /* IPCSIZE, libvgpu.so .data@0x620c8 */
+
+/* kernel variant selector */
+#define VGPU_XFER_AUTO 0   /* policy table: measured best for (tier, batch) */
+#define VGPU_XFER_LDST 1   /* 256-bit vectorised coalesced loads/stores */
+#define VGPU_XFER_TMA  2   /* cp.async.bulk global->smem->global ring */
+#define VGPU_XFER_CE   3   /* copy engine (cudaMemcpyAsync) + checksum kernel */
+
+/* tier of the far side of a transfer (used by the AUTO policy and stats) */
+#define VGPU_TIER_LOCAL 0  /* same-GPU HBM */
+#define VGPU_TIER_PEER  1  /* peer GPU HBM over NVLink P2P */
+#define VGPU_TIER_HOST  2  /* pinned host RAM over PCIe */
+
+/* Per-chunk checksum (X,S): X = xor of the chunk's u64 words,
+ * S = sum of w[i]*(2i+1) mod 2^64, i = word index within the chunk. */
+typedef struct vgpu_cksum { uint64_t x, s; } vgpu_cksum_t;
+
+/* Result block of a restore (device-accessible memory, written by the kernel). */
+typedef struct vgpu_restore_result {
+    uint64_t bad_chunks;        /* chunks whose (X,S) != expected */
+    uint64_t first_bad_inv;     /* ~(lowest bad chunk number); 0 = none */
+} vgpu_restore_result_t;
+
+/* Checksum only: cksum[c] = (X,S) of chunk c of `src`.  */
+int vgpu_checksum(const void *src, const uint32_t *src_slot, size_t nchunks,
+                  size_t chunk_bytes, vgpu_cksum_t *cksum, void *stream);
+
+/* Spill: for c in [0,nchunks): copy chunk src_slot[c] of slab `src` to chunk
+ * dst_slot[c] of slab `dst` (NULL slot table = identity) and write its
+ * checksum to cksum[c].  One fused kernel; `tier` names where `dst` lives. */
+int vgpu_spill(int variant, int tier, const void *src, void *dst,
+               const uint32_t *src_slot, const uint32_t *dst_slot,
+               size_t nchunks, size_t chunk_bytes,
+               vgpu_cksum_t *cksum, void *stream);
+
+/* Restore: same movement in the other direction; the checksum of what
+ * arrived is compared with expect[c] inside the kernel and mismatches are
+ * accumulated into *result (device-accessible; caller zeroes it).  `cksum`
+ * may be NULL.  `tier` names where `src` lives. */
+int vgpu_restore(int variant, int tier, const void *src, void *dst,
+                 const uint32_t *src_slot, const uint32_t *dst_slot,
+                 size_t nchunks, size_t chunk_bytes,
+                 const vgpu_cksum_t *expect, vgpu_cksum_t *cksum,
+                 vgpu_restore_result_t *result, void *stream);
+
+/* Host-buffer forms (synchronous): `host` is caller memory.  If it is not
+ * already pinned it is pinned for the duration of the call.  The checksums
+ * land in host memory.  These are the calls bench.py's `e2e` leg times. */
+int vgpu_spill_to_host(int variant, int device, const void *d_src, void *host,
+                       size_t nchunks, size_t chunk_bytes, vgpu_cksum_t *h_cksum);
+int vgpu_restore_from_host(int variant, int device, const void *host, void *d_dst,
+                           size_t nchunks, size_t chunk_bytes,
+                           const vgpu_cksum_t *h_expect, uint64_t *bad_chunks);
+
+/* Spill-tier slabs (helpers for vgpuvalidator / bench / the vmem manager). */
+int vgpu_slab_alloc(int tier, int device, int peer_device, size_t bytes, void **out);
+int vgpu_slab_free(int tier, int device, int peer_device, void *p);
+
+/* AUTO policy: which variant wins for (tier, nchunks).  vgpu_calibrate
+ * measures the variants on scratch slabs of `device` (and `peer_device` for
+ * VGPU_TIER_PEER) and fills the table; vgpu_policy_get reads it. */
+int vgpu_calibrate(int device, int tier, int peer_device, size_t max_chunks);
+int vgpu_policy_get(int tier, size_t nchunks);
+int vgpu_policy_set(int tier, size_t min_chunks, int variant);
+
+/* ======================================================================== *
+ *  vgpuvalidator memtest (new capability under the reference's mount name
+ *  /usr/bin/vgpuvalidator, server.go:518-519; the reference binary is a
+ *  license tool, vgpuvalidator@0x4022e0 main — no memtest exists there).
+ * ======================================================================== */
+
+#define VGPU_PAT_WALKING_ONES 0  /* word i = 1ull << ((i+pass)&63) */
+#define VGPU_PAT_RANDOM       1  /* word i = splitmix64((GOLDEN^pass^seed)+i) */
+
+typedef struct vgpu_memtest_dev_result {   /* device-side accumulator */
+    uint64_t mismatches;        /* mismatching u64 words */
+    uint64_t first_bad_inv;     /* ~(lowest mismatching word index); 0 = none */
+    uint64_t bad_bits;          /* OR of got^expected */
+} vgpu_memtest_dev_result_t;
+
+typedef struct vgpu_memtest_result {
+    uint64_t bytes;             /* buffer bytes per pass */
+    uint64_t passes;            /* (fill,verify) pairs executed */
+    uint64_t mismatches;
+    uint64_t first_bad_word;    /* UINT64_MAX if none */
+    uint64_t bad_bits;
+    int32_t  first_bad_pattern; /* -1 if none */
+    int32_t  first_bad_pass;
+    double   fill_ms;           /* summed device time (CUDA events) */
+    double   verify_ms;
+    double   gbps;              /* 2*bytes*passes / (fill_ms+verify_ms) */
+} vgpu_memtest_result_t;
+
+/* Asynchronous single kernels on a caller buffer (16-byte aligned, bytes%16==0). */
+int vgpu_memtest_fill(void *buf, uint64_t bytes, int pattern, uint64_t pass,
+                      uint64_t seed, void *stream);
+int vgpu_memtest_verify(const void *buf, uint64_t bytes, int pattern, uint64_t pass,
+                        uint64_t seed, vgpu_memtest_dev_result_t *d_result, void *stream);
+
+/* Synchronous: run `npasses` passes of `pattern` over a caller device buffer
+ * on the current device, timing with CUDA events; fills *out (host). */
+int vgpu_memtest_run(void *buf, uint64_t bytes, int pattern, uint64_t first_pass,
+                     uint64_t npasses, uint64_t seed, void *stream,
+                     vgpu_memtest_result_t *out);
+
+/* Synchronous, self-allocating: what `vgpuvalidator --memtest` calls.
+ * `patterns` is a bit mask (1<<VGPU_PAT_*); walking-ones runs 64 passes,
+ * random runs `random_passes`. */
+int vgpu_memtest(int device, uint64_t bytes, unsigned patterns, uint64_t random_passes,
+                 uint64_t seed, vgpu_memtest_result_t *out);
+
+/* ======================================================================== *
+ *  SM partitioning (replaces rate_limiter, libvgpu.so@0x463b1, with Blackwell
+ *  green contexts).  Implemented over the driver API.
+ * ======================================================================== */
+
+typedef struct vgpu_sm_partition {
+    void    *green_ctx;   /* CUgreenCtx */
+    void    *ctx;         /* CUcontext from cuCtxFromGreenCtx */
+    void    *stream;      /* CUstream created on the green context */
+    uint32_t sm_count;    /* SMs actually granted */
+    uint32_t sm_total;    /* SMs on the device */
+} vgpu_sm_partition_t;
+
+/* Split `device` into `n` partitions of floor(total*percent/100) SMs each
+ * (rounded by the driver to its granule).  percent = CUDA_DEVICE_SM_LIMIT. */
+int vgpu_sm_partition_create(int device, unsigned percent, unsigned n,
+                             vgpu_sm_partition_t *out);
+int vgpu_sm_partition_destroy(vgpu_sm_partition_t *parts, unsigned n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VGPU_H_ */
