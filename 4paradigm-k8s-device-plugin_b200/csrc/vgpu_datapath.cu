@@ -136,7 +136,7 @@ constexpr int kTmaTile = 16384, kTmaStages = 4, kTmaThreads = 128;
 
 bool aligned32(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 31u) == 0; }
 
-int host_readable(const void *p, bool *ok) {
+int host_and_device_readable(const void *p, bool *ok) {
     cudaPointerAttributes at{};
     cudaError_t e = cudaPointerGetAttributes(&at, p);
     if (e != cudaSuccess) {
@@ -144,8 +144,8 @@ int host_readable(const void *p, bool *ok) {
         *ok = false;
         return VGPU_OK;
     }
-    *ok = at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged ||
-          at.type == cudaMemoryTypeUnregistered;
+    // pinned or managed: the host walks it to issue the copies AND the checksum kernel reads it
+    *ok = at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
     return VGPU_OK;
 }
 
@@ -188,10 +188,10 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
             VGPU_CUDA(cudaMemcpyAsync(dst, src, nchunks * chunk_bytes, cudaMemcpyDefault, st));
         } else {
             bool ok1 = true, ok2 = true;
-            if (src_slot) host_readable(src_slot, &ok1);
-            if (dst_slot) host_readable(dst_slot, &ok2);
+            if (src_slot) host_and_device_readable(src_slot, &ok1);
+            if (dst_slot) host_and_device_readable(dst_slot, &ok2);
             if (!ok1 || !ok2)
-                return fail(VGPU_E_UNSUPPORTED, "VGPU_XFER_CE needs host-readable slot tables");
+                return fail(VGPU_E_UNSUPPORTED, "VGPU_XFER_CE needs slot tables in pinned or managed memory (read by host and GPU)");
             // coalesce runs of consecutive slots into one copy each
             size_t c = 0;
             while (c < nchunks) {

@@ -86,11 +86,23 @@ int vgpu_sm_partition_create(int device, unsigned percent, unsigned n, vgpu_sm_p
     const unsigned total = all.sm.smCount;
     unsigned want = total * percent / 100;
     if (want < 1) want = 1;
+    // The driver rounds minCount up to its granule (8 SMs on sm_90+), which can leave fewer
+    // than n groups (148 SMs, 25 %: 37 -> 40 -> only 3 groups).  A vGPU must never get MORE
+    // than its share, so step the ask down to the largest count that still yields n
+    // disjoint groups (148 SMs, 25 %, n=4: 4 x 32).  Co-scheduling (clusters, cta_group::2)
+    // is kept: flags = 0.
     CUdevResource groups[64], rest;
-    unsigned nb = n;
-    r = g_drv.DevSmResourceSplitByCount(groups, &nb, &all, &rest, 0, want);
-    if (r != CUDA_SUCCESS) return drv_fail("cuDevSmResourceSplitByCount", r);
-    if (nb < n) return fail(VGPU_E_NOMEM, "driver formed %u partitions of >=%u SMs, %u requested", nb, want, n);
+    unsigned nb = 0;
+    for (;; --want) {
+        nb = n;
+        r = g_drv.DevSmResourceSplitByCount(groups, &nb, &all, &rest, 0, want);
+        const bool formed = r == CUDA_SUCCESS && nb >= n;
+        if (formed && (groups[0].sm.smCount <= total * percent / 100 || want <= 1)) break;
+        if (want <= 1) {
+            if (r != CUDA_SUCCESS) return drv_fail("cuDevSmResourceSplitByCount", r);
+            return fail(VGPU_E_NOMEM, "driver formed %u partitions, %u requested", nb, n);
+        }
+    }
     memset(out, 0, sizeof(*out) * n);
     for (unsigned i = 0; i < n; ++i) {
         CUdevResourceDesc desc;

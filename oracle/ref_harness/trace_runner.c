@@ -1,0 +1,117 @@
+/* trace_runner.c — plays a quota trace against whatever libvgpu is LD_PRELOADed, over the
+ * mock driver.  TEST INFRASTRUCTURE ONLY.  Reads one op per line on stdin, answers one line
+ * per op on stdout (flushed), so a parent can interleave several runners deterministically.
+ *
+ *   total [dev]            cuDeviceTotalMem_v2            -> rc bytes
+ *   info                   cuMemGetInfo_v2                -> rc free total
+ *   alloc <bytes> <tag>    cuMemAlloc_v2                  -> rc
+ *   managed <bytes> <tag>  cuMemAllocManaged(flags=1)     -> rc
+ *   pitch <w> <h> <elem> <tag>  cuMemAllocPitch_v2        -> rc
+ *   free <tag>             cuMemFree_v2(ptr of tag)       -> rc
+ *   freeptr <hex>          cuMemFree_v2(raw value)        -> rc
+ *   hostalloc <bytes> <tag> cuMemAllocHost_v2             -> rc
+ *   freehost <tag>         cuMemFreeHost                  -> rc
+ *   launch <grid> <block>  cuLaunchKernel                 -> rc
+ *   nvmlmem                nvmlDeviceGetMemoryInfo(dev0)  -> rc total free used
+ *   quit
+ */
+#define _GNU_SOURCE
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef int CUresult;
+typedef unsigned long long CUdeviceptr;
+CUresult cuInit(unsigned);
+CUresult cuDeviceGet(int *, int);
+CUresult cuDeviceTotalMem_v2(size_t *, int);
+CUresult cuMemGetInfo_v2(size_t *, size_t *);
+CUresult cuMemAlloc_v2(CUdeviceptr *, size_t);
+CUresult cuMemAllocManaged(CUdeviceptr *, size_t, unsigned);
+CUresult cuMemAllocPitch_v2(CUdeviceptr *, size_t *, size_t, size_t, unsigned);
+CUresult cuMemFree_v2(CUdeviceptr);
+CUresult cuMemAllocHost_v2(void **, size_t);
+CUresult cuMemFreeHost(void *);
+CUresult cuLaunchKernel(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **);
+
+#define MAXTAG 200000
+static CUdeviceptr tags[MAXTAG];
+static void *htags[MAXTAG];
+
+int main(void) {
+    char line[256];
+    CUresult rc = cuInit(0);
+    printf("init %d\n", rc);
+    fflush(stdout);
+    while (fgets(line, sizeof(line), stdin)) {
+        char op[32] = {0};
+        unsigned long long a = 0, b = 0, c = 0, d = 0;
+        int n = sscanf(line, "%31s %lli %lli %lli %lli", op, (long long *)&a, (long long *)&b, (long long *)&c, (long long *)&d);
+        if (n < 1) continue;
+        if (!strcmp(op, "quit")) break;
+        if (!strcmp(op, "total")) {
+            size_t bytes = 0;
+            rc = cuDeviceTotalMem_v2(&bytes, (int)a);
+            printf("%d %zu\n", rc, bytes);
+        } else if (!strcmp(op, "info")) {
+            size_t f = 0, t = 0;
+            rc = cuMemGetInfo_v2(&f, &t);
+            printf("%d %zu %zu\n", rc, f, t);
+        } else if (!strcmp(op, "alloc")) {
+            CUdeviceptr p = 0;
+            rc = cuMemAlloc_v2(&p, (size_t)a);
+            if (rc == 0 && b < MAXTAG) tags[b] = p;
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "managed")) {
+            CUdeviceptr p = 0;
+            rc = cuMemAllocManaged(&p, (size_t)a, 1);
+            if (rc == 0 && b < MAXTAG) tags[b] = p;
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "pitch")) {
+            CUdeviceptr p = 0;
+            size_t pitch = 0;
+            rc = cuMemAllocPitch_v2(&p, &pitch, (size_t)a, (size_t)b, (unsigned)c);
+            if (rc == 0 && d < MAXTAG) tags[d] = p;
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "free")) {
+            rc = cuMemFree_v2(a < MAXTAG ? tags[a] : 0);
+            if (rc == 0 && a < MAXTAG) tags[a] = 0;
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "freeptr")) {
+            rc = cuMemFree_v2((CUdeviceptr)a);
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "hostalloc")) {
+            void *p = NULL;
+            rc = cuMemAllocHost_v2(&p, (size_t)a);
+            if (rc == 0 && b < MAXTAG) htags[b] = p;
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "freehost")) {
+            rc = cuMemFreeHost(a < MAXTAG ? htags[a] : NULL);
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "launch")) {
+            rc = cuLaunchKernel(NULL, (unsigned)a, 1, 1, (unsigned)b, 1, 1, 0, NULL, NULL, NULL);
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "nvmlmem")) {
+            typedef int (*init_t)(void);
+            typedef int (*byidx_t)(unsigned, void **);
+            typedef int (*mem_t)(void *, unsigned long long *);
+            init_t ini = (init_t)dlsym(RTLD_DEFAULT, "nvmlInit_v2");
+            byidx_t gi = (byidx_t)dlsym(RTLD_DEFAULT, "nvmlDeviceGetHandleByIndex_v2");
+            mem_t gm = (mem_t)dlsym(RTLD_DEFAULT, "nvmlDeviceGetMemoryInfo");
+            unsigned long long m[3] = {0, 0, 0};
+            void *h = NULL;
+            rc = -100;
+            if (ini && gi && gm) {
+                ini();
+                rc = gi(0, &h);
+                if (rc == 0) rc = gm(h, m);
+            }
+            printf("%d %llu %llu %llu\n", rc, m[0], m[1], m[2]);
+        } else {
+            printf("? %s\n", op);
+        }
+        fflush(stdout);
+    }
+    return 0;
+}

@@ -148,13 +148,15 @@ def test_spill_with_slot_tables(vgpu, cuda_dev, variant):
 def test_ce_variant_with_host_slot_tables(vgpu, cuda_dev):
     capi = vgpu.capi
     cb, slots, n = 65536, 10, 6
-    ss = np.array([4, 5, 6, 0, 9, 2], dtype=np.uint32)  # 4,5,6 -> 1,2,3 coalesces into one copy
-    ds = np.array([1, 2, 3, 7, 0, 5], dtype=np.uint32)
+    # slot tables in pinned memory: the host walks them to issue copies, the checksum kernel reads them
+    pss = torch.tensor([4, 5, 6, 0, 9, 2], dtype=torch.int32).pin_memory()  # 4,5,6 -> 1,2,3 coalesces into one copy
+    pds = torch.tensor([1, 2, 3, 7, 0, 5], dtype=torch.int32).pin_memory()
+    ss, ds = pss.numpy().view(np.uint32), pds.numpy().view(np.uint32)
     words = rand_words(slots * cb // 8, npass=1)
     src = to_dev(words, cuda_dev)
     dst = torch.zeros(slots * cb, dtype=torch.uint8, device=cuda_dev)
     ck = torch.zeros((n, 2), dtype=torch.int64, device=cuda_dev)
-    rc = capi.lib.vgpu_spill(capi.XFER_CE, capi.TIER_LOCAL, src.data_ptr(), dst.data_ptr(), ss.ctypes.data, ds.ctypes.data,
+    rc = capi.lib.vgpu_spill(capi.XFER_CE, capi.TIER_LOCAL, src.data_ptr(), dst.data_ptr(), pss.data_ptr(), pds.data_ptr(),
                              n, cb, ck.data_ptr(), None)
     assert rc == 0, capi.last_error()
     torch.cuda.synchronize()
@@ -162,7 +164,7 @@ def test_ce_variant_with_host_slot_tables(vgpu, cuda_dev):
     want = cpu.spill(words, o_dst, n, cb, ss, ds)
     assert np.array_equal(as_pairs(ck), want) and np.array_equal(dev_bytes(dst), o_dst.view(np.uint8))
     # device-resident slot tables cannot be walked by the host for per-chunk copies
-    dss = torch.from_numpy(ss.view(np.int32)).to(cuda_dev)
+    dss = pss.to(cuda_dev)
     rc = capi.lib.vgpu_spill(capi.XFER_CE, capi.TIER_LOCAL, src.data_ptr(), dst.data_ptr(), dss.data_ptr(), None, n, cb, ck.data_ptr(), None)
     assert rc == capi.E_UNSUPPORTED
 
@@ -220,7 +222,9 @@ def test_host_entry_point_pins_pageable_memory(vgpu, cuda_dev):
     cb, n = 65536, 4
     words = rand_words(n * cb // 8)
     hbm = to_dev(words, cuda_dev)
-    host = np.zeros(n * cb, dtype=np.uint8)  # pageable
+    raw = np.zeros(n * cb + 64, dtype=np.uint8)  # pageable; the slab base must be 32-byte aligned
+    off = (-raw.ctypes.data) % 32
+    host = raw[off:off + n * cb]
     hck = np.zeros((n, 2), dtype=np.uint64)
     rc = capi.lib.vgpu_spill_to_host(capi.XFER_LDST, 0, hbm.data_ptr(), host.ctypes.data, n, cb, hck.ctypes.data)
     assert rc == 0, capi.last_error()
@@ -310,7 +314,7 @@ def test_sm_partitions_are_spatial(vgpu, cuda_dev):
         total = parts[0].sm_total
         assert total >= 100
         for p in parts:
-            assert 0 < p.sm_count <= total * 25 // 100 + 8 and p.stream
+            assert 0 < p.sm_count <= total * 25 // 100 and p.stream
         assert sum(p.sm_count for p in parts) <= total
         bufs = [torch.empty(64 << 20, dtype=torch.uint8, device=cuda_dev) for _ in parts]
         res = [torch.zeros(3, dtype=torch.int64, device=cuda_dev) for _ in parts]
