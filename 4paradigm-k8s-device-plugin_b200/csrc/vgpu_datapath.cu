@@ -32,6 +32,9 @@ struct Scratch {
     ChunkAcc *acc = nullptr;  // self-cleaning per-chunk accumulators
     size_t acc_cap = 0;
     vgpu_memtest_dev_result_t *mt = nullptr;
+    vgpu_memtest_dev_result_t *mt_host = nullptr;  // pinned: a pageable D2H copy would hold the
+                                                   // context lock until the stream drains and
+                                                   // serialise the other vGPUs' host threads
     vgpu_cksum_t *cksum = nullptr;  // staging for the host-buffer forms
     size_t cksum_cap = 0;
     vgpu_restore_result_t *rr = nullptr;
@@ -80,11 +83,13 @@ int get_acc(int dev, void *stream, size_t nchunks, ChunkAcc **out) {
     return VGPU_OK;
 }
 
-int get_mt(int dev, void *stream, vgpu_memtest_dev_result_t **out) {
+int get_mt(int dev, void *stream, vgpu_memtest_dev_result_t **out, vgpu_memtest_dev_result_t **host) {
     std::lock_guard<std::mutex> lk(g_mu);
     Scratch &s = g_dev[dev].scratch[stream];
     if (!s.mt) VGPU_CUDA(cudaMalloc(&s.mt, sizeof(*s.mt)));
+    if (!s.mt_host) VGPU_CUDA(cudaHostAlloc(&s.mt_host, sizeof(*s.mt_host), cudaHostAllocDefault));
     *out = s.mt;
+    *host = s.mt_host;
     return VGPU_OK;
 }
 
@@ -133,6 +138,19 @@ int policy_lookup(int tier, size_t nchunks) {
 // ---- transfer launch --------------------------------------------------------
 constexpr int kLdstU = 4;                   // 4 x 32 B per thread in flight => 32 KiB tiles
 constexpr int kTmaTile = 16384, kTmaStages = 4, kTmaThreads = 128;
+
+// CTAs per launch of the LD/ST copy variant: a grid-stride loop over 32 KiB tiles with
+// 32 CTAs per SM (4 waves of the 8 resident).  Unlike the write-only / read-only memtest
+// kernels, the mixed read+write copy is FASTER with some persistence: 3276 GB/s payload at
+// 32/SM vs 2520 GB/s with one tile per CTA (4096 chunks, profiles/r01_memtest_sweeps.md).
+// VGPU_XFER_CTAS_PER_SM overrides for experiments.
+uint64_t ldst_grid_cap(int sms) {
+    static const long cap = [] {
+        const char *e = getenv("VGPU_XFER_CTAS_PER_SM");
+        return e ? atol(e) : 0L;
+    }();
+    return (uint64_t)sms * (uint64_t)(cap > 0 ? cap : 32);
+}
 
 bool aligned32(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 31u) == 0; }
 
@@ -213,11 +231,14 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
     }
 
     if (variant == VGPU_XFER_LDST || !copy) {
-        constexpr uint32_t tile = LdstTile<kLdstU>::bytes;
+        static const int u_exp = [] { const char *e = getenv("VGPU_XFER_U"); return e ? atoi(e) : kLdstU; }();
+        const uint32_t tile = u_exp == 8 ? LdstTile<8>::bytes : u_exp == 2 ? LdstTile<2>::bytes : LdstTile<kLdstU>::bytes;
         a.tiles_per_chunk = (uint32_t)((chunk_bytes + tile - 1) / tile);
         const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
-        const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * 8);
-        if (copy) k_xfer_ldst<kLdstU, true><<<grid, kXfThreads, 0, st>>>(a);
+        const unsigned grid = (unsigned)std::min<uint64_t>(total, ldst_grid_cap(sms));
+        if (copy && u_exp == 8) k_xfer_ldst<8, true><<<grid, kXfThreads, 0, st>>>(a);
+        else if (copy && u_exp == 2) k_xfer_ldst<2, true><<<grid, kXfThreads, 0, st>>>(a);
+        else if (copy) k_xfer_ldst<kLdstU, true><<<grid, kXfThreads, 0, st>>>(a);
         else k_xfer_ldst<kLdstU, false><<<grid, kXfThreads, 0, st>>>(a);
     } else {  // VGPU_XFER_TMA
         a.tiles_per_chunk = (uint32_t)((chunk_bytes + kTmaTile - 1) / kTmaTile);
@@ -466,30 +487,28 @@ static uint64_t mt_key(int pattern, uint64_t pass, uint64_t seed) {
     return pattern == VGPU_PAT_WALKING_ONES ? pass : (kGolden ^ pass ^ seed);
 }
 
-static int mt_grid(uint64_t nvec, unsigned *grid) {
-    int dev, sms;
-    if (int rc = cur_device(&dev)) return rc;
-    if (int rc = sm_count(dev, &sms)) return rc;
-    const uint64_t want = (nvec + kMtThreads * kMtUnroll - 1) / (kMtThreads * kMtUnroll);
-    *grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)sms * 8));
+static int mt_grid(uint64_t nvec, int threads, unsigned *grid) {
+    const uint64_t per = (uint64_t)threads * kMtU;
+    const uint64_t want = std::max<uint64_t>(1, (nvec + per - 1) / per);
+    if (want > 0x7fffffffull) return fail(VGPU_E_INVAL, "buffer too large for one launch");
+    *grid = (unsigned)want;
     return VGPU_OK;
 }
 
 int vgpu_memtest_fill(void *buf, uint64_t bytes, int pattern, uint64_t pass, uint64_t seed, void *stream) {
     if (bytes == 0) return VGPU_OK;
     uint64_t head = 0, nvec = 0, tail = 0;
-    unsigned grid;
+    unsigned grid = 0;
     if (int rc = mt_geom(buf, bytes, &head, &nvec, &tail)) return rc;
-    if (int rc = mt_grid(nvec, &grid)) return rc;
+    if (pattern != VGPU_PAT_WALKING_ONES && pattern != VGPU_PAT_RANDOM) return fail(VGPU_E_INVAL, "pattern=%d", pattern);
+    if (int rc = mt_grid(nvec, pattern == VGPU_PAT_RANDOM ? kMtThreadsR : kMtThreadsW, &grid)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     uint64_t *p = static_cast<uint64_t *>(buf);
     const uint64_t key = mt_key(pattern, pass, seed);
     if (pattern == VGPU_PAT_WALKING_ONES)
-        k_memtest_fill<VGPU_PAT_WALKING_ONES><<<grid, kMtThreads, 0, st>>>(p, head, nvec, tail, key);
-    else if (pattern == VGPU_PAT_RANDOM)
-        k_memtest_fill<VGPU_PAT_RANDOM><<<grid, kMtThreads, 0, st>>>(p, head, nvec, tail, key);
+        k_memtest_fill<VGPU_PAT_WALKING_ONES, kMtThreadsW><<<grid, kMtThreadsW, 0, st>>>(p, head, nvec, tail, key);
     else
-        return fail(VGPU_E_INVAL, "pattern=%d", pattern);
+        k_memtest_fill<VGPU_PAT_RANDOM, kMtThreadsR><<<grid, kMtThreadsR, 0, st>>>(p, head, nvec, tail, key);
     VGPU_CUDA(cudaGetLastError());
     return VGPU_OK;
 }
@@ -499,18 +518,17 @@ int vgpu_memtest_verify(const void *buf, uint64_t bytes, int pattern, uint64_t p
     if (!d_result) return fail(VGPU_E_INVAL, "null result");
     if (bytes == 0) return VGPU_OK;
     uint64_t head = 0, nvec = 0, tail = 0;
-    unsigned grid;
+    unsigned grid = 0;
     if (int rc = mt_geom(buf, bytes, &head, &nvec, &tail)) return rc;
-    if (int rc = mt_grid(nvec, &grid)) return rc;
+    if (pattern != VGPU_PAT_WALKING_ONES && pattern != VGPU_PAT_RANDOM) return fail(VGPU_E_INVAL, "pattern=%d", pattern);
+    if (int rc = mt_grid(nvec, pattern == VGPU_PAT_RANDOM ? kMtThreadsR : kMtThreadsW, &grid)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const uint64_t *p = static_cast<const uint64_t *>(buf);
     const uint64_t key = mt_key(pattern, pass, seed);
     if (pattern == VGPU_PAT_WALKING_ONES)
-        k_memtest_verify<VGPU_PAT_WALKING_ONES><<<grid, kMtThreads, 0, st>>>(p, head, nvec, tail, key, d_result);
-    else if (pattern == VGPU_PAT_RANDOM)
-        k_memtest_verify<VGPU_PAT_RANDOM><<<grid, kMtThreads, 0, st>>>(p, head, nvec, tail, key, d_result);
+        k_memtest_verify<VGPU_PAT_WALKING_ONES, kMtThreadsW><<<grid, kMtThreadsW, 0, st>>>(p, head, nvec, tail, key, d_result);
     else
-        return fail(VGPU_E_INVAL, "pattern=%d", pattern);
+        k_memtest_verify<VGPU_PAT_RANDOM, kMtThreadsR><<<grid, kMtThreadsR, 0, st>>>(p, head, nvec, tail, key, d_result);
     VGPU_CUDA(cudaGetLastError());
     return VGPU_OK;
 }
@@ -520,8 +538,8 @@ int vgpu_memtest_run(void *buf, uint64_t bytes, int pattern, uint64_t first_pass
     if (!out) return fail(VGPU_E_INVAL, "null result");
     int dev;
     if (int rc = cur_device(&dev)) return rc;
-    vgpu_memtest_dev_result_t *d_res;
-    if (int rc = get_mt(dev, stream, &d_res)) return rc;
+    vgpu_memtest_dev_result_t *d_res, *h_res;
+    if (int rc = get_mt(dev, stream, &d_res, &h_res)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     cudaEvent_t ev[3];
     for (auto &e : ev) VGPU_CUDA(cudaEventCreate(&e));
@@ -531,7 +549,6 @@ int vgpu_memtest_run(void *buf, uint64_t bytes, int pattern, uint64_t first_pass
     r.first_bad_pattern = r.first_bad_pass = -1;
     int rc = VGPU_OK;
     for (uint64_t p = first_pass; p < first_pass + npasses && !rc; ++p) {
-        vgpu_memtest_dev_result_t h{};
         cudaMemsetAsync(d_res, 0, sizeof(*d_res), st);
         cudaEventRecord(ev[0], st);
         rc = vgpu_memtest_fill(buf, bytes, pattern, p, seed, stream);
@@ -539,11 +556,12 @@ int vgpu_memtest_run(void *buf, uint64_t bytes, int pattern, uint64_t first_pass
         if (!rc) rc = vgpu_memtest_verify(buf, bytes, pattern, p, seed, d_res, stream);
         cudaEventRecord(ev[2], st);
         if (!rc) {
-            cudaError_t e = cudaMemcpyAsync(&h, d_res, sizeof(h), cudaMemcpyDeviceToHost, st);
+            cudaError_t e = cudaMemcpyAsync(h_res, d_res, sizeof(*h_res), cudaMemcpyDeviceToHost, st);
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
             if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "memtest pass %llu: %s", (unsigned long long)p, cudaGetErrorString(e));
         }
         if (rc) break;
+        const vgpu_memtest_dev_result_t h = *h_res;
         float f = 0, v = 0;
         cudaEventElapsedTime(&f, ev[0], ev[1]);
         cudaEventElapsedTime(&v, ev[1], ev[2]);

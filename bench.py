@@ -37,6 +37,9 @@ def parse():
     ap.add_argument("--vgpus", type=int, default=4, help="vGPUs per GPU (config 2: 4)")
     ap.add_argument("--vgpu-gib", type=float, default=40.0, help="memtest buffer per vGPU in GiB (config 2: 40)")
     ap.add_argument("--spill-chunks", type=int, default=4096, help="largest batch of the 2 MiB chunk sweep (config 4: 4096)")
+    ap.add_argument("--partition", default="green", choices=["green", "streams"],
+                    help="green: one 25%% green-context SM partition per vGPU (default); streams: plain streams "
+                         "(ncu cannot profile launches into green contexts)")
     ap.add_argument("--no-spill", action="store_true", help="skip the spill/restore sweep")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-gib", type=float, default=2.0, help="host buffer of the CPU memtest sample")
@@ -205,13 +208,13 @@ def main():
 
     parts = (capi.SmPartition * nv)()
     pct = int(100 / nv)
-    rc = capi.lib.vgpu_sm_partition_create(local, pct, nv, parts)
+    rc = capi.lib.vgpu_sm_partition_create(local, pct, nv, parts) if args.partition == "green" else 1
     if rc == 0:
         streams = [torch.cuda.ExternalStream(p.stream, device=dev) for p in parts]
         partition = {"kind": "green_ctx", "percent": pct, "sm_per_vgpu": [p.sm_count for p in parts], "sm_total": parts[0].sm_total}
     else:  # measured and reported as such, not hidden
         streams = [torch.cuda.Stream(device=dev) for _ in range(nv)]
-        partition = {"kind": "plain_streams", "why": capi.last_error()}
+        partition = {"kind": "plain_streams", "why": capi.last_error() if args.partition == "green" else "--partition streams"}
     results = [torch.zeros(3, dtype=torch.int64, device=dev) for _ in range(nv)]
 
     def step(s):

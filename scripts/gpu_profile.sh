@@ -4,7 +4,8 @@
 # Outputs land in gpurun_out/; summaries are copied into profiles/ by hand afterwards.
 set -u
 TAG=${1:-r1}
-ARGS="--steps 2 --warmup 3 --no-cpu --vgpu-gib 4 --spill-chunks 64"
+# --partition streams: ncu fails with "Failed to prepare kernel for profiling" on launches into green contexts
+ARGS="--steps 2 --warmup 3 --no-cpu --vgpu-gib 4 --spill-chunks 64 --partition streams"
 mkdir -p gpurun_out
 python bench.py $ARGS > gpurun_out/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
