@@ -20,6 +20,7 @@ lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
 # ---- constants (mirror vgpu.h) -------------------------------------------------
 OK, E_INVAL, E_CUDA, E_NOMEM, E_UNKNOWN_ID, E_RANGE, E_MISMATCH, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5, -6, -7
 CHUNK_BYTES = 2097152
+NOALLOC_MAX_CHUNKS = 4096
 XFER_AUTO, XFER_LDST, XFER_TMA, XFER_CE = 0, 1, 2, 3
 TIER_LOCAL, TIER_PEER, TIER_HOST = 0, 1, 2
 PAT_WALKING_ONES, PAT_RANDOM = 0, 1
@@ -84,6 +85,7 @@ SIGNATURES = {
     "vgpu_checksum": (_i, [_vp, _vp, _sz, _sz, _vp, _vp]),
     "vgpu_spill": (_i, [_i, _i, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _vp]),
     "vgpu_restore": (_i, [_i, _i, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _vp, _vp, _vp]),
+    "vgpu_spill_noalloc": (_i, [_vp, _vp, _vp, _vp, _sz, _sz, _vp, _vp]),
     "vgpu_spill_to_host": (_i, [_i, _i, _vp, _vp, _sz, _sz, _vp]),
     "vgpu_restore_from_host": (_i, [_i, _i, _vp, _vp, _sz, _sz, _vp, _pp(_u64)]),
     "vgpu_slab_alloc": (_i, [_i, _i, _i, _sz, _pp(_vp)]),

@@ -19,9 +19,9 @@ ORACLE   := oracle/liboracle.so
 
 all: $(DP_SO) $(ORACLE)
 
-$(DP_SO): $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_kernels.cuh $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp \
+$(DP_SO): $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_kernels.cuh $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp \
           $(CSRC)/vgpu_internal.h include/vgpu.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp -ldl
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp -ldl
 
 $(ORACLE): oracle/vgpu_oracle.c oracle/vgpu_oracle.h
 	$(CC) -O3 -fPIC -shared -Wall -Wextra -o $@ oracle/vgpu_oracle.c -lpthread

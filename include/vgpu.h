@@ -152,6 +152,20 @@ int vgpu_restore(int variant, int tier, const void *src, void *dst,
                  const vgpu_cksum_t *expect, vgpu_cksum_t *cksum,
                  vgpu_restore_result_t *result, void *stream);
 
+/* Spill for callers that cannot allocate device memory: the eviction path of a vGPU
+ * whose HBM slice is already full, and code running inside the preload shim's own
+ * allocation hooks (an allocation there would be charged to the vGPU being relieved, or
+ * simply fail).  Same result as vgpu_spill(VGPU_XFER_LDST, ...), but the per-chunk scratch
+ * is a fixed 128 KiB array inside the library, so: at most VGPU_NOALLOC_MAX_CHUNKS chunks
+ * per call (VGPU_E_RANGE beyond that); calls that overlap on one GPU race on the shared
+ * array — serialise them; the first call on each GPU resolves the array's address and
+ * should be made at start-up, before any stream capture.  Allocates nothing.
+ * No counterpart in the reference (it has no spill path of its own at all). */
+#define VGPU_NOALLOC_MAX_CHUNKS 4096
+int vgpu_spill_noalloc(const void *src, void *dst, const uint32_t *src_slot,
+                       const uint32_t *dst_slot, size_t nchunks, size_t chunk_bytes,
+                       vgpu_cksum_t *cksum, void *stream);
+
 /* Host-buffer forms (synchronous): `host` is caller memory.  If it is not
  * already pinned it is pinned for the duration of the call.  The checksums
  * land in host memory.  These are the calls bench.py's `e2e` leg times. */
