@@ -1,0 +1,597 @@
+/*
+ * shim.c — the new libvgpu.so: LD_PRELOAD interposer for the CUDA driver API and NVML.
+ *
+ * Same boundary as the reference's vgpu/libvgpu.so (Contract B): same hooked
+ * symbol names, same environment variables, same CUresult quirks, same shared-cache file.
+ * What is behind it differs: no launch throttle (spatial green-context SM partition instead,
+ * see greenctx section), no getenv+atoi at every log site, no popen("ps ax") on OOM, and the
+ * real dlsym is found with dlvsym (glibc >= 2.34 has no _dl_sym@GLIBC_PRIVATE, which is why the
+ * reference binary needs a helper to even start on this image).
+ *
+ * Hooked on the quota path (★ rows of SURVEY §8a):
+ *   cuInit, cuDeviceTotalMem_v2, cuMemGetInfo_v2, cuMemAlloc_v2, cuMemAllocManaged,
+ *   cuMemAllocPitch_v2, cuMemFree_v2, cuMemAllocHost_v2, cuMemHostAlloc, cuMemHostRegister_v2,
+ *   cuDevicePrimaryCtxRetain, cuLaunchKernel, cuGetProcAddress(_v2), nvmlDeviceGetMemoryInfo(_v2),
+ *   dlsym.  Everything else resolves straight to the real driver.
+ */
+#define _GNU_SOURCE
+#include <dlfcn.h>
+#include <errno.h>
+#include <pthread.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <unistd.h>
+
+#include "region.h"
+#include "shimlog.h"
+
+#define EXPORT __attribute__((visibility("default")))
+
+typedef int CUresult;
+typedef int CUdevice;
+typedef unsigned long long CUdeviceptr;
+typedef void *CUcontext;
+
+#define IPCSIZE 0x200000ull  /* .data@0x620c8: allocations above this take the oversubscribe route */
+
+/* ------------------------------------------------------------------ logging level */
+int shim_log_level(void) {
+    static int lvl = -2;
+    if (lvl == -2) {
+        const char *e = getenv("LIBCUDA_LOG_LEVEL");
+        lvl = e ? atoi(e) : -1;
+    }
+    return lvl;
+}
+
+/* ------------------------------------------------------------------ real entry points */
+typedef void *(*dlsym_fn)(void *, const char *);
+static dlsym_fn real_dlsym;
+static void *g_cuda, *g_nvml;
+
+static void find_real_dlsym(void) {
+    if (real_dlsym) return;
+    real_dlsym = (dlsym_fn)dlvsym(RTLD_NEXT, "dlsym", "GLIBC_2.2.5");
+    if (!real_dlsym) real_dlsym = (dlsym_fn)dlvsym(RTLD_NEXT, "dlsym", "GLIBC_2.34");
+    if (!real_dlsym) {
+        SHIM_ERR("cannot find the real dlsym: %s", dlerror());
+        abort();
+    }
+}
+
+static void *cuda_sym(const char *name) {
+    find_real_dlsym();
+    if (!g_cuda) {
+        g_cuda = dlopen("libcuda.so.1", RTLD_NOW | RTLD_NODELETE);  /* load_cuda_libraries@0x2e66c, flags 0x1002 */
+        if (!g_cuda) {
+            SHIM_ERR("can't dlopen libcuda.so.1: %s", dlerror());
+            return NULL;
+        }
+    }
+    void *p = real_dlsym(g_cuda, name);
+    if (!p) SHIM_INFO("can't find function %s in libcuda.so.1", name);
+    return p;
+}
+
+static void *nvml_sym(const char *name) {
+    find_real_dlsym();
+    if (!g_nvml) {
+        g_nvml = dlopen("libnvidia-ml.so.1", RTLD_NOW | RTLD_NODELETE);
+        if (!g_nvml) return NULL;
+    }
+    return real_dlsym(g_nvml, name);
+}
+
+#define REAL(ret, name, ...)                                   \
+    typedef ret (*name##_t)(__VA_ARGS__);                      \
+    static name##_t real_##name;                               \
+    static inline name##_t get_##name(void) {                  \
+        if (!real_##name) real_##name = (name##_t)cuda_sym(#name); \
+        return real_##name;                                    \
+    }
+
+REAL(CUresult, cuInit, unsigned)
+REAL(CUresult, cuDeviceGetCount, int *)
+REAL(CUresult, cuCtxGetDevice, CUdevice *)
+REAL(CUresult, cuCtxGetCurrent, CUcontext *)
+REAL(CUresult, cuDeviceTotalMem_v2, size_t *, CUdevice)
+REAL(CUresult, cuMemGetInfo_v2, size_t *, size_t *)
+REAL(CUresult, cuMemAlloc_v2, CUdeviceptr *, size_t)
+REAL(CUresult, cuMemAllocManaged, CUdeviceptr *, size_t, unsigned)
+REAL(CUresult, cuMemAllocPitch_v2, CUdeviceptr *, size_t *, size_t, size_t, unsigned)
+REAL(CUresult, cuMemFree_v2, CUdeviceptr)
+REAL(CUresult, cuMemAllocHost_v2, void **, size_t)
+REAL(CUresult, cuMemHostAlloc, void **, size_t, unsigned)
+REAL(CUresult, cuMemFreeHost, void *)
+REAL(CUresult, cuMemHostRegister_v2, void *, size_t, unsigned)
+REAL(CUresult, cuMemHostUnregister, void *)
+REAL(CUresult, cuDevicePrimaryCtxRetain, CUcontext *, CUdevice)
+REAL(CUresult, cuLaunchKernel, void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **)
+REAL(CUresult, cuGetProcAddress, const char *, void **, int, unsigned long long)
+REAL(CUresult, cuGetProcAddress_v2, const char *, void **, int, unsigned long long, int *)
+
+/* ------------------------------------------------------------------ env (a10, a11) */
+/* get_limit_from_env@0x4186c: <n>[GgMmKk], strtoul base 0; unset/empty/0/overflow -> 0 */
+static uint64_t limit_from_env(const char *name) {
+    const char *v = getenv(name);
+    if (!v || !*v) return 0;
+    char *end = NULL;
+    errno = 0;
+    unsigned long n = strtoul(v, &end, 0);
+    if (end == v) return 0;
+    uint64_t scale = 1;
+    switch (*end) {
+        case 'G': case 'g': scale = 1ull << 30; break;
+        case 'M': case 'm': scale = 1ull << 20; break;
+        case 'K': case 'k': scale = 1ull << 10; break;
+        default: break;
+    }
+    uint64_t res = (uint64_t)n * scale;
+    if (n != 0 && res / scale != n) return 0;  /* overflow check, same as the reference */
+    if (res == 0) {
+        if (name[12] == 'S') SHIM_INFO("device core util limit set to 0, which means no limit: %s=%s", name, v);
+        else if (name[12] == 'M') SHIM_WARN("invalid device memory limit %s=%s", name, v);
+    }
+    return res;
+}
+
+static void init_limits(vgpu_region_init_t *init) {
+    /* do_init_device_memory_limits@0x4232e / do_init_device_sm_limits@0x4246e */
+    uint64_t mem_all = limit_from_env("CUDA_DEVICE_MEMORY_LIMIT");
+    uint64_t sm_all = limit_from_env("CUDA_DEVICE_SM_LIMIT");
+    if (sm_all == 0) sm_all = 100;
+    for (int i = 0; i < VGPU_MAX_DEVICES; ++i) {
+        char key[64];
+        snprintf(key, sizeof(key), "CUDA_DEVICE_MEMORY_LIMIT_%d", i);
+        uint64_t v = limit_from_env(key);
+        init->limit[i] = v ? v : mem_all;
+        snprintf(key, sizeof(key), "CUDA_DEVICE_SM_LIMIT_%d", i);
+        v = limit_from_env(key);
+        init->sm_limit[i] = v ? v : sm_all;
+    }
+}
+
+/* ------------------------------------------------------------------ init (a26) */
+static pthread_once_t g_pre_once = PTHREAD_ONCE_INIT, g_post_once = PTHREAD_ONCE_INIT;
+static int g_virtual_devices = -1;  /* entries of NVIDIA_DEVICE_MAP, else the real device count */
+static int g_allocmode = 2;         /* 0: oversubscribe route, 2: plain cuMemAlloc (postInit@0x16ded) */
+static int g_region_ok = 0;
+
+static int count_device_map(void) {
+    const char *m = getenv("NVIDIA_DEVICE_MAP");
+    if (!m || !*m) return -1;
+    int n = 0;
+    const char *p = m;
+    while (*p) {
+        while (*p == ' ') ++p;
+        if (!*p) break;
+        ++n;
+        while (*p && *p != ' ') ++p;
+    }
+    return n;
+}
+
+static void pre_init(void) {
+    vgpu_region_init_t init;
+    memset(&init, 0, sizeof(init));
+    init_limits(&init);
+    const char *prio = getenv("CUDA_TASK_PRIORITY");
+    init.priority = prio ? atoi(prio) : 1;
+
+    int real_count = 0;
+    if (get_cuDeviceGetCount()) {
+        /* cuDeviceGetCount before cuInit fails on a real driver; retried in post_init */
+        if (real_cuDeviceGetCount(&real_count) != 0) real_count = 0;
+    }
+    int mapped = count_device_map();
+    g_virtual_devices = mapped > 0 ? mapped : real_count;
+
+    /* put_device_info@0x41e2e: UUIDs through NVML */
+    typedef int (*nv_init_t)(void);
+    typedef int (*nv_count_t)(unsigned *);
+    typedef int (*nv_byidx_t)(unsigned, void **);
+    typedef int (*nv_uuid_t)(void *, char *, unsigned);
+    nv_init_t nv_init = (nv_init_t)nvml_sym("nvmlInit_v2");
+    if (!nv_init) nv_init = (nv_init_t)nvml_sym("nvmlInit");
+    nv_byidx_t nv_byidx = (nv_byidx_t)nvml_sym("nvmlDeviceGetHandleByIndex_v2");
+    if (!nv_byidx) nv_byidx = (nv_byidx_t)nvml_sym("nvmlDeviceGetHandleByIndex");
+    nv_uuid_t nv_uuid = (nv_uuid_t)nvml_sym("nvmlDeviceGetUUID");
+    nv_count_t nv_count = (nv_count_t)nvml_sym("nvmlDeviceGetCount_v2");
+    if (nv_init && nv_byidx && nv_uuid && nv_init() == 0) {
+        unsigned n = 0;
+        if (g_virtual_devices <= 0 && nv_count && nv_count(&n) == 0) g_virtual_devices = (int)n;
+        for (int i = 0; i < g_virtual_devices && i < VGPU_MAX_DEVICES; ++i) {
+            void *h = NULL;
+            if (nv_byidx((unsigned)i, &h) != 0) break;
+            if (nv_uuid(h, init.uuids[i], VGPU_UUID_LEN) != 0) break;
+        }
+    }
+    init.device_num = g_virtual_devices > 0 ? (uint64_t)g_virtual_devices : 0;
+
+    const char *path = getenv("CUDA_DEVICE_MEMORY_SHARED_CACHE");
+    if (!path) path = "/tmp/cudevshr.cache";  /* .rodata@0x56ac0 */
+    g_region_ok = region_attach(path, &init) == 0;
+    if (!g_region_ok) SHIM_ERR("shared cache %s unavailable: quota disabled", path);
+}
+
+static void post_init(void) {
+    const char *o = getenv("CUDA_OVERSUBSCRIBE");
+    g_allocmode = (o && strcmp(o, "true") == 0) ? 0 : 2;
+    if (g_virtual_devices <= 0 && get_cuDeviceGetCount()) {
+        int n = 0;
+        if (real_cuDeviceGetCount(&n) == 0) g_virtual_devices = n;
+    }
+}
+
+static void ensure_initialized(void) { pthread_once(&g_pre_once, pre_init); }
+
+/* suspend gate: wait_status_self@0x45ff5 — sleep while an external monitor has us at status 2 */
+static void wait_running(void) {
+    while (g_region_ok && region_my_status() != 1) sleep(1);
+}
+
+/* ------------------------------------------------------------------ allocation list (a13, a15) */
+typedef struct alloc_node {
+    CUdeviceptr addr;
+    size_t len;
+    int dev;
+    struct alloc_node *next, *prev;
+} alloc_node_t;
+static alloc_node_t *g_head, *g_tail;
+static size_t g_nalloc;
+static pthread_mutex_t g_alloc_mu = PTHREAD_MUTEX_INITIALIZER;
+
+static void track(CUdeviceptr p, size_t n, int dev) {
+    alloc_node_t *a = (alloc_node_t *)malloc(sizeof(*a));
+    a->addr = p;
+    a->len = n;
+    a->dev = dev;
+    a->next = NULL;
+    a->prev = g_tail;
+    if (g_tail) g_tail->next = a; else g_head = a;
+    g_tail = a;
+    ++g_nalloc;
+}
+
+static int cur_dev(int *dev) {
+    cuCtxGetDevice_t f = get_cuCtxGetDevice();
+    if (!f) return 3;
+    return f(dev);
+}
+
+/* oom_check@0x40528 */
+static int oom_check(int dev, size_t addon) {
+    if (!g_region_ok) return 0;
+    int count = 0;
+    if (get_cuDeviceGetCount() && real_cuDeviceGetCount(&count) == 0 && count != g_virtual_devices) return 0;
+    if (dev == -1 && cur_dev(&dev) != 0) return 0;
+    for (;;) {
+        uint64_t limit = region_limit(dev);
+        if (limit == 0) return 0;
+        uint64_t usage = region_usage(dev);
+        if (usage + addon > limit) {  /* u64 add, no overflow guard, as in the reference */
+            SHIM_ERR("Device %d OOM %lu / %lu", dev, (unsigned long)(usage + addon), (unsigned long)limit);
+            if (region_reap_dead() > 0) continue;  /* rm_quitted_process: retry once per reaped process */
+            return 1;
+        }
+        return 0;
+    }
+}
+
+/* add_chunk@0x40b73 (route = 0) and add_chunk_only@0x41011 (route = 1: caller already allocated) */
+static int add_chunk(CUdeviceptr *p, size_t n) {
+    int dev = 0;
+    CUresult rc = cur_dev(&dev);
+    if (rc != 0) return rc;
+    if (oom_check(dev, n)) return -1;
+    if (n <= IPCSIZE || g_allocmode == 2) {
+        cuMemAlloc_v2_t f = get_cuMemAlloc_v2();
+        rc = f ? f(p, n) : 3;
+    } else {
+        /* cuMemoryAllocate@0x32146, allocmode 0.  The reference hands the allocation to
+         * UVM here; the explicit spill/restore data path (libvgpu_dp.so) takes this route
+         * over when the VMM manager is attached (vmem section). */
+        cuMemAllocManaged_t f = get_cuMemAllocManaged();
+        rc = f ? f(p, n, 1 /* CU_MEM_ATTACH_GLOBAL */) : 3;
+    }
+    if (rc != 0) return rc;
+    track(*p, n, dev);
+    region_add_usage(dev, n, VGPU_USE_DATA);
+    return 0;
+}
+
+static int add_chunk_only(CUdeviceptr p, size_t n) {
+    int dev = 0;
+    CUresult rc = cur_dev(&dev);
+    if (rc != 0) return rc;
+    track(p, n, dev);
+    region_add_usage(dev, n, VGPU_USE_DATA);
+    return 0;
+}
+
+/* ------------------------------------------------------------------ hooks */
+EXPORT CUresult cuInit(unsigned flags) {
+    ensure_initialized();
+    cuInit_t f = get_cuInit();
+    CUresult rc = f ? f(flags) : 3;
+    if (rc == 0) pthread_once(&g_post_once, post_init);
+    return rc;
+}
+
+EXPORT CUresult cuMemAlloc_v2(CUdeviceptr *dptr, size_t bytesize) {
+    ensure_initialized();
+    pthread_once(&g_post_once, post_init);
+    wait_running();
+    pthread_mutex_lock(&g_alloc_mu);
+    int rc = add_chunk(dptr, bytesize);  /* allocate_raw@0x4157c: -1 on quota OOM, returned verbatim */
+    pthread_mutex_unlock(&g_alloc_mu);
+    return rc;
+}
+EXPORT CUresult cuMemAlloc(CUdeviceptr *dptr, size_t bytesize) { return cuMemAlloc_v2(dptr, bytesize); }
+
+EXPORT CUresult cuMemAllocManaged(CUdeviceptr *dptr, size_t bytesize, unsigned flags) {
+    ensure_initialized();
+    pthread_once(&g_post_once, post_init);
+    wait_running();
+    if (oom_check(-1, bytesize)) return 2;  /* CUDA_ERROR_OUT_OF_MEMORY, @0x3281d */
+    cuMemAllocManaged_t f = get_cuMemAllocManaged();
+    CUresult rc = f ? f(dptr, bytesize, flags) : 3;
+    if (rc != 0) return rc;
+    pthread_mutex_lock(&g_alloc_mu);
+    add_chunk_only(*dptr, bytesize);
+    pthread_mutex_unlock(&g_alloc_mu);
+    return 0;
+}
+
+EXPORT CUresult cuMemAllocPitch_v2(CUdeviceptr *dptr, size_t *pitch, size_t w, size_t h, unsigned elem) {
+    ensure_initialized();
+    pthread_once(&g_post_once, post_init);
+    wait_running();
+    /* bytes = ((W-1)/Elem+1)*Elem * H, @0x32bd7-0x32c02 */
+    size_t bytes = elem ? (((w - 1) / elem + 1) * elem) * h : w * h;
+    if (oom_check(-1, bytes)) return 2;
+    cuMemAllocPitch_v2_t f = get_cuMemAllocPitch_v2();
+    CUresult rc = f ? f(dptr, pitch, w, h, elem) : 3;
+    if (rc != 0) return rc;
+    pthread_mutex_lock(&g_alloc_mu);
+    add_chunk_only(*dptr, bytes);
+    pthread_mutex_unlock(&g_alloc_mu);
+    return 0;
+}
+EXPORT CUresult cuMemAllocPitch(CUdeviceptr *dptr, size_t *pitch, size_t w, size_t h, unsigned elem) {
+    return cuMemAllocPitch_v2(dptr, pitch, w, h, elem);
+}
+
+EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
+    ensure_initialized();
+    if (dptr == 0) return 0;  /* cuMemFree_v2@0x32e5d */
+    pthread_mutex_lock(&g_alloc_mu);
+    alloc_node_t *a = g_head;
+    while (a && a->addr != dptr) a = a->next;  /* remove_chunk@0x413dd: exact base match */
+    if (!a) {
+        pthread_mutex_unlock(&g_alloc_mu);
+        return -1;
+    }
+    cuMemFree_v2_t f = get_cuMemFree_v2();
+    CUresult rc = f ? f(dptr) : 3;
+    if (a->prev) a->prev->next = a->next; else g_head = a->next;
+    if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
+    --g_nalloc;
+    int dev = a->dev;
+    size_t len = a->len;
+    free(a);
+    pthread_mutex_unlock(&g_alloc_mu);
+    region_rm_usage(dev, len, VGPU_USE_DATA);
+    return rc;
+}
+EXPORT CUresult cuMemFree(CUdeviceptr dptr) { return cuMemFree_v2(dptr); }
+
+EXPORT CUresult cuMemGetInfo_v2(size_t *free_b, size_t *total_b) {
+    ensure_initialized();
+    int dev = 0;
+    CUresult rc = cur_dev(&dev);
+    if (rc != 0) return rc;
+    uint64_t usage = g_region_ok ? region_usage(dev) : 0;
+    uint64_t limit = g_region_ok ? region_limit(dev) : 0;
+    cuMemGetInfo_v2_t f = get_cuMemGetInfo_v2();
+    if (limit == 0) {
+        rc = f ? f(free_b, total_b) : 3;
+        *free_b = *total_b - usage;  /* quirk a17: free = total - usage when unlimited */
+        return rc;
+    }
+    if (limit < usage) return 1;
+    if (f) f(free_b, total_b);  /* the reference calls through and overwrites (@0x377c9) */
+    *free_b = limit - usage;
+    *total_b = limit;
+    return 0;
+}
+EXPORT CUresult cuMemGetInfo(size_t *free_b, size_t *total_b) { return cuMemGetInfo_v2(free_b, total_b); }
+
+EXPORT CUresult cuDeviceTotalMem_v2(size_t *bytes, CUdevice dev) {
+    ensure_initialized();
+    if (!g_region_ok) {
+        cuDeviceTotalMem_v2_t f = get_cuDeviceTotalMem_v2();
+        return f ? f(bytes, dev) : 3;
+    }
+    *bytes = region_limit(dev);  /* quirk a18: the limit, unconditionally (0 when unlimited) */
+    return 0;
+}
+EXPORT CUresult cuDeviceTotalMem(size_t *bytes, CUdevice dev) { return cuDeviceTotalMem_v2(bytes, dev); }
+
+/* host-memory hooks (a20): allocate first, then check_oom@0x311bd == oom_check(cur, 0) */
+EXPORT CUresult cuMemAllocHost_v2(void **pp, size_t n) {
+    ensure_initialized();
+    cuMemAllocHost_v2_t f = get_cuMemAllocHost_v2();
+    CUresult rc = f ? f(pp, n) : 3;
+    if (rc != 0) return rc;
+    if (oom_check(-1, 0)) {
+        if (get_cuMemFreeHost()) real_cuMemFreeHost(*pp);
+        return 2;
+    }
+    return 0;
+}
+EXPORT CUresult cuMemAllocHost(void **pp, size_t n) { return cuMemAllocHost_v2(pp, n); }
+
+EXPORT CUresult cuMemHostAlloc(void **pp, size_t n, unsigned flags) {
+    ensure_initialized();
+    cuMemHostAlloc_t f = get_cuMemHostAlloc();
+    CUresult rc = f ? f(pp, n, flags) : 3;
+    if (rc != 0) return rc;
+    if (oom_check(-1, 0)) {
+        if (get_cuMemFreeHost()) real_cuMemFreeHost(*pp);
+        return 2;
+    }
+    return 0;
+}
+
+EXPORT CUresult cuMemHostRegister_v2(void *p, size_t n, unsigned flags) {
+    ensure_initialized();
+    cuMemHostRegister_v2_t f = get_cuMemHostRegister_v2();
+    CUresult rc = f ? f(p, n, flags) : 3;
+    if (rc != 0) return rc;
+    if (oom_check(-1, 0)) {
+        if (get_cuMemHostUnregister()) real_cuMemHostUnregister(p);
+        return 2;
+    }
+    return 0;
+}
+EXPORT CUresult cuMemHostRegister(void *p, size_t n, unsigned flags) { return cuMemHostRegister_v2(p, n, flags); }
+
+EXPORT CUresult cuDevicePrimaryCtxRetain(CUcontext *pctx, CUdevice dev) {
+    ensure_initialized();
+    cuDevicePrimaryCtxRetain_t f = get_cuDevicePrimaryCtxRetain();
+    return f ? f(pctx, dev) : 3;
+}
+
+/* cuLaunchKernel@0x37c2b: the suspend gate stays; rate_limiter@0x463b1 is gone — the SM cap is
+ * spatial (green context), so there is nothing to do per launch. */
+EXPORT CUresult cuLaunchKernel(void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by,
+                               unsigned bz, unsigned shm, void *stream, void **params, void **extra) {
+    ensure_initialized();
+    wait_running();
+    cuLaunchKernel_t f = get_cuLaunchKernel();
+    return f ? f(fn, gx, gy, gz, bx, by, bz, shm, stream, params, extra) : 3;
+}
+
+/* ------------------------------------------------------------------ NVML (a23) */
+typedef struct { unsigned long long total, free, used; } nvmlMemory_t;
+typedef struct { unsigned version; unsigned long long total, reserved, free, used; } nvmlMemory_v2_t;
+
+static int nvml_dev_index(void *handle) {
+    typedef int (*idx_t)(void *, unsigned *);
+    idx_t f = (idx_t)nvml_sym("nvmlDeviceGetIndex");
+    unsigned i = 0;
+    if (!f || f(handle, &i) != 0) return -1;
+    return (int)i;
+}
+
+EXPORT int nvmlDeviceGetMemoryInfo(void *handle, nvmlMemory_t *m) {
+    ensure_initialized();
+    typedef int (*fn_t)(void *, nvmlMemory_t *);
+    fn_t f = (fn_t)nvml_sym("nvmlDeviceGetMemoryInfo");
+    int rc = f ? f(handle, m) : 3;
+    if (rc != 0 || !g_region_ok) return rc;
+    int dev = nvml_dev_index(handle);
+    if (dev < 0) return rc;
+    uint64_t usage = region_usage(dev), limit = region_limit(dev);
+    if (limit == 0) {
+        m->used = usage;  /* hook.c:328-334: only `used` is overwritten when unlimited */
+    } else {
+        m->total = limit;
+        m->free = limit - usage;
+        m->used = usage;
+    }
+    return 0;
+}
+
+EXPORT int nvmlDeviceGetMemoryInfo_v2(void *handle, nvmlMemory_v2_t *m) {
+    ensure_initialized();
+    typedef int (*fn_t)(void *, nvmlMemory_v2_t *);
+    fn_t f = (fn_t)nvml_sym("nvmlDeviceGetMemoryInfo_v2");
+    int rc = f ? f(handle, m) : 3;
+    if (rc != 0 || !g_region_ok) return rc;
+    int dev = nvml_dev_index(handle);
+    if (dev < 0) return rc;
+    uint64_t usage = region_usage(dev), limit = region_limit(dev);
+    if (limit == 0) {
+        m->used = usage;
+    } else {
+        m->total = limit;
+        m->free = limit - usage;
+        m->used = usage;
+    }
+    return 0;
+}
+
+/* ------------------------------------------------------------------ dispatch: dlsym / cuGetProcAddress */
+typedef struct { const char *name; void *fn; } hook_t;
+EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsigned long long flags);
+EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, unsigned long long flags, int *status);
+
+static const hook_t g_hooks[] = {
+    {"cuInit", (void *)cuInit},
+    {"cuMemAlloc", (void *)cuMemAlloc_v2}, {"cuMemAlloc_v2", (void *)cuMemAlloc_v2},
+    {"cuMemAllocManaged", (void *)cuMemAllocManaged},
+    {"cuMemAllocPitch", (void *)cuMemAllocPitch_v2}, {"cuMemAllocPitch_v2", (void *)cuMemAllocPitch_v2},
+    {"cuMemFree", (void *)cuMemFree_v2}, {"cuMemFree_v2", (void *)cuMemFree_v2},
+    {"cuMemGetInfo", (void *)cuMemGetInfo_v2}, {"cuMemGetInfo_v2", (void *)cuMemGetInfo_v2},
+    {"cuDeviceTotalMem", (void *)cuDeviceTotalMem_v2}, {"cuDeviceTotalMem_v2", (void *)cuDeviceTotalMem_v2},
+    {"cuMemAllocHost", (void *)cuMemAllocHost_v2}, {"cuMemAllocHost_v2", (void *)cuMemAllocHost_v2},
+    {"cuMemHostAlloc", (void *)cuMemHostAlloc},
+    {"cuMemHostRegister", (void *)cuMemHostRegister_v2}, {"cuMemHostRegister_v2", (void *)cuMemHostRegister_v2},
+    {"cuDevicePrimaryCtxRetain", (void *)cuDevicePrimaryCtxRetain},
+    {"cuLaunchKernel", (void *)cuLaunchKernel},
+    {"cuGetProcAddress", (void *)cuGetProcAddress}, {"cuGetProcAddress_v2", (void *)cuGetProcAddress_v2},
+    {"nvmlDeviceGetMemoryInfo", (void *)nvmlDeviceGetMemoryInfo},
+    {"nvmlDeviceGetMemoryInfo_v2", (void *)nvmlDeviceGetMemoryInfo_v2},
+};
+
+static void *find_hook(const char *name) {
+    for (size_t i = 0; i < sizeof(g_hooks) / sizeof(g_hooks[0]); ++i)
+        if (strcmp(g_hooks[i].name, name) == 0) return g_hooks[i].fn;
+    return NULL;
+}
+
+/* dlsym@0x12bb6: every cu, nvml lookup that names a hooked symbol lands in the shim */
+EXPORT void *dlsym(void *handle, const char *symbol) {
+    find_real_dlsym();
+    if ((symbol[0] == 'c' && symbol[1] == 'u') || strncmp(symbol, "nvml", 4) == 0) {
+        void *h = find_hook(symbol);
+        if (h) return h;
+    }
+    return real_dlsym(handle, symbol);
+}
+
+EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsigned long long flags) {
+    ensure_initialized();
+    void *h = symbol ? find_hook(symbol) : NULL;
+    if (h) {
+        *pfn = h;
+        return 0;
+    }
+    cuGetProcAddress_t f = get_cuGetProcAddress();
+    return f ? f(symbol, pfn, ver, flags) : 500;
+}
+
+EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, unsigned long long flags, int *status) {
+    ensure_initialized();
+    void *h = symbol ? find_hook(symbol) : NULL;
+    if (h) {
+        *pfn = h;
+        if (status) *status = 0;  /* CU_GET_PROC_ADDRESS_SUCCESS */
+        return 0;
+    }
+    cuGetProcAddress_v2_t f = get_cuGetProcAddress_v2();
+    return f ? f(symbol, pfn, ver, flags, status) : 500;
+}
+
+/* cuVGPUViewAllocator@0x16c80: dump the tracked allocations */
+EXPORT void cuVGPUViewAllocator(void) {
+    pthread_mutex_lock(&g_alloc_mu);
+    fprintf(stderr, "[4pdvGPU] %zu tracked allocations\n", g_nalloc);
+    for (alloc_node_t *a = g_head; a; a = a->next)
+        fprintf(stderr, "  dev %d  0x%llx  %zu bytes\n", a->dev, a->addr, a->len);
+    pthread_mutex_unlock(&g_alloc_mu);
+}

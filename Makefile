@@ -15,19 +15,25 @@ NVFLAGS  := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall -Iinclude -I
 CFLAGS   := -O2 -g -fPIC -Wall -Wextra -Iinclude
 
 DP_SO    := $(PKG)/libvgpu_dp.so
+SHIM_SO  := $(PKG)/libvgpu.so
+SHIM_SRC := $(CSRC)/libvgpu/shim.c $(CSRC)/libvgpu/region.c
 ORACLE   := oracle/liboracle.so
 
-all: $(DP_SO) $(ORACLE)
+all: $(DP_SO) $(SHIM_SO) $(ORACLE)
 
 $(DP_SO): $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_kernels.cuh $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp \
           $(CSRC)/vgpu_internal.h include/vgpu.h
 	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp -ldl
 
+# the LD_PRELOAD shim: plain C, no CUDA toolkit needed at run time (driver reached by dlopen)
+$(SHIM_SO): $(SHIM_SRC) $(CSRC)/libvgpu/region.h $(CSRC)/libvgpu/shimlog.h
+	$(CC) -O2 -g -fPIC -shared -fvisibility=hidden -Wall -Wextra -Wl,-soname,libvgpu.so -o $@ $(SHIM_SRC) -ldl -lpthread
+
 $(ORACLE): oracle/vgpu_oracle.c oracle/vgpu_oracle.h
 	$(CC) -O3 -fPIC -shared -Wall -Wextra -o $@ oracle/vgpu_oracle.c -lpthread
 
 clean:
-	rm -f $(DP_SO) $(ORACLE)
+	rm -f $(DP_SO) $(SHIM_SO) $(ORACLE)
 
 .PHONY: all clean
 

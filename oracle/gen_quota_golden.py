@@ -1,0 +1,57 @@
+#!/usr/bin/env python
+"""Captures golden quota vectors FROM THE REFERENCE BINARY (/root/reference/vgpu/libvgpu.so)
+run under the mock driver, and writes them to tests/golden/quota_*.json.gz.  Run in the build
+container (the reference is not available on the GPU box); the fixtures are committed.
+
+  python oracle/gen_quota_golden.py
+"""
+import gzip
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import quota_harness as H  # noqa: E402
+
+MAP = {"NVIDIA_DEVICE_MAP": "0:" + H.UUID0}
+OUT = os.path.join(ROOT, "tests", "golden")
+
+CASES = [
+    # name, trace, env, nprocs, mock physical MiB
+    ("c3_golden", H.golden_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", "CUDA_DEVICE_SM_LIMIT": "10", **MAP}, 1),
+    ("c3_golden_oversub", H.golden_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", "CUDA_DEVICE_SM_LIMIT": "10", "CUDA_OVERSUBSCRIBE": "true", **MAP}, 1),
+    ("appA_nolimit", H.appendix_a_trace(), {}, 1),
+    ("appA_1g", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT": "1g"}, 1),
+    ("appA_perdev_wins", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1048576k", "CUDA_DEVICE_MEMORY_LIMIT": "2g"}, 1),
+    ("appA_nosuffix", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1073741824"}, 1),
+    ("appA_hex", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "0x40000000"}, 1),
+    ("appA_50m", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "50m"}, 1),
+    ("appA_overflow", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "17179869184g"}, 1),
+    ("appA_garbage", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "abc"}, 1),
+    ("random_5EED_1p", H.random_trace(0x5EED, 10000), {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m", "CUDA_DEVICE_SM_LIMIT": "10", **MAP}, 1),
+    ("random_5EED_1p_oversub", H.random_trace(0x5EED, 10000), {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m", "CUDA_DEVICE_SM_LIMIT": "10", "CUDA_OVERSUBSCRIBE": "true", **MAP}, 1),
+    ("random_5EED_4p", H.random_trace(0x5EED + 1, 10000, 4), {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m", "CUDA_DEVICE_SM_LIMIT": "10", **MAP}, 4),
+    ("random_5EED_4p_oversub_tight", H.random_trace(0x5EED + 2, 4000, 4, 1 << 26), {"CUDA_DEVICE_MEMORY_LIMIT_0": "300m", "CUDA_OVERSUBSCRIBE": "true", **MAP}, 4),
+]
+
+
+def main():
+    if not H.have_reference():
+        sys.exit("reference binary not present: golden vectors can only be captured where /root/reference exists")
+    H.build()
+    os.makedirs(OUT, exist_ok=True)
+    for name, trace, env, nprocs in CASES:
+        env = {"MOCK_TOTAL_MIB": "184320", **env}
+        r = H.run_trace(H.REFERENCE_LIB, trace, env, nprocs)
+        doc = {"name": name, "source": "vgpu/libvgpu.so (sha256 d48e2b4c...c0c1ff1) under oracle/ref_harness mocks",
+               "env": env, "nprocs": nprocs, "trace": trace, "replies": r["replies"], "oom": r["oom"], "calls": r["calls"],
+               "region": H.region_summary(r["region"])}
+        path = os.path.join(OUT, f"quota_{name}.json.gz")
+        with gzip.GzipFile(path, "wb", mtime=0) as f:
+            f.write(json.dumps(doc, separators=(",", ":")).encode())
+        print(f"{name}: {len(trace)} ops, {len(r['oom'])} OOMs, {os.path.getsize(path)} bytes")
+
+
+if __name__ == "__main__":
+    main()

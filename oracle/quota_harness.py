@@ -1,0 +1,182 @@
+"""Runs quota traces through a libvgpu (the reference binary or the new shim) over the mock
+driver built by oracle/ref_harness.  TEST INFRASTRUCTURE ONLY.
+
+A trace is a list of (proc, op) pairs; `op` is a line of trace_runner's little language.
+Runners are driven in lock step (one reply per op), so multi-process interleavings are
+deterministic and identical for both libraries."""
+import os
+import random
+import re
+import struct
+import subprocess
+import tempfile
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_DIR = os.path.join(HERE, "_ref")
+REFERENCE_LIB = "/root/reference/vgpu/libvgpu.so"
+NEW_LIB = os.path.join(os.path.dirname(HERE), "4paradigm-k8s-device-plugin_b200", "libvgpu.so")
+UUID0 = "GPU-00000000-0000-0000-0000-000000000001"
+
+REGION_SIZE = 0xC4748
+SLOT0, STRIDE, NSLOT = 0x738, 0x310, 1024
+OOM_RE = re.compile(r"Device (\d+) OOM (\d+) / (\d+)")
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "ref_harness")])
+
+
+def have_reference():
+    return os.path.exists(REFERENCE_LIB)
+
+
+def _env(lib, cache, extra, mock_log):
+    env = {
+        "PATH": os.environ.get("PATH", "/usr/bin:/bin"),
+        "LD_LIBRARY_PATH": REF_DIR,
+        "LD_PRELOAD": f"{os.path.join(REF_DIR, 'libdlsymshim.so')} {lib}",
+        "CUDA_DEVICE_MEMORY_SHARED_CACHE": cache,
+        "LIBCUDA_LOG_LEVEL": "0",
+        "MOCK_CUDA_LOG": mock_log,
+    }
+    env.update(extra)
+    return env
+
+
+def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True):
+    """-> dict(replies=[str...] in trace order, oom=[(dev,need,limit)...], calls=[str...], region=bytes)"""
+    os.makedirs("/tmp/vgpulock", exist_ok=True)  # the reference spins forever without this dir
+    try:
+        os.unlink("/tmp/vgpulock/lock")
+    except FileNotFoundError:
+        pass
+    with tempfile.TemporaryDirectory(prefix="vgpuq") as td:
+        cache = os.path.join(td, "shr.cache")
+        mock_log = os.path.join(td, "mock.log")
+        errs = [open(os.path.join(td, f"err{p}"), "w+") for p in range(nprocs)]
+        procs = []
+        replies = []
+        try:
+            for p in range(nprocs):
+                pr = subprocess.Popen([os.path.join(REF_DIR, "trace_runner")], stdin=subprocess.PIPE, stdout=subprocess.PIPE,
+                                      stderr=errs[p], env=_env(lib, cache, env_extra, mock_log), text=True, bufsize=1)
+                first = pr.stdout.readline().strip()  # "init <rc>"
+                if not first.startswith("init"):
+                    raise RuntimeError(f"runner {p} did not start: {first!r}")
+                procs.append(pr)
+            for p, op in trace:
+                procs[p].stdin.write(op + "\n")
+                procs[p].stdin.flush()
+                line = procs[p].stdout.readline()
+                if not line:
+                    raise RuntimeError(f"runner {p} died on {op!r}")
+                replies.append(line.strip())
+            for pr in procs:  # deterministic exit order
+                pr.stdin.write("quit\n")
+                pr.stdin.flush()
+                pr.wait(timeout=20)
+        finally:
+            for pr in procs:
+                if pr.poll() is None:
+                    pr.kill()
+        oom = []
+        for f in errs:
+            f.seek(0)
+            oom += [tuple(int(x) for x in m.groups()) for m in OOM_RE.finditer(f.read())]
+            f.close()
+        calls = []
+        if os.path.exists(mock_log):
+            for line in open(mock_log):
+                line = line.strip()
+                # the reference probes NVML/primary-context at init to find its host pid; not part of the quota path
+                if line.startswith(("cuInit", "cuDevicePrimaryCtxRetain")):
+                    continue
+                calls.append(line)
+        region = open(cache, "rb").read() if keep_region and os.path.exists(cache) else b""
+    return {"replies": replies, "oom": sorted(oom), "calls": calls, "region": region}
+
+
+def mask_region(b: bytes) -> bytes:
+    """Zero what legitimately differs between runs: pids (slot.pid, slot.hostpid)."""
+    if not b:
+        return b
+    a = bytearray(b[:REGION_SIZE])
+    for s in range(NSLOT):
+        o = SLOT0 + s * STRIDE
+        a[o:o + 8] = b"\0" * 8
+    return bytes(a)
+
+
+def region_summary(b: bytes) -> dict:
+    if not b:
+        return {}
+    return {
+        "size": len(b),
+        "magic": struct.unpack_from("<i", b, 0)[0],
+        "owner_pid": struct.unpack_from("<Q", b, 8)[0],
+        "device_num": struct.unpack_from("<Q", b, 0x30)[0],
+        "uuid0": b[0x38:0x38 + 96].split(b"\0")[0].decode(),
+        "limit": list(struct.unpack_from("<16Q", b, 0x638)),
+        "sm_limit": list(struct.unpack_from("<16Q", b, 0x6B8)),
+        "proc_num": struct.unpack_from("<i", b, 0xC4738)[0],
+        "utilization_switch": struct.unpack_from("<i", b, 0xC473C)[0],
+        "recent_kernel": struct.unpack_from("<i", b, 0xC4740)[0],
+        "priority": struct.unpack_from("<i", b, 0xC4744)[0],
+        "masked_crc": __import__("zlib").crc32(mask_region(b)),
+    }
+
+
+# ------------------------------------------------------------------------------ trace generators
+def golden_trace():
+    """alloc 1, 3, 500, 400, 200 MiB; free the 500 MiB; info after each."""
+    MiB = 1 << 20
+    ops = ["total 0", "info"]
+    for tag, mib in enumerate([1, 3, 500, 400, 200], 1):
+        ops += [f"alloc {mib * MiB} {tag}", "info"]
+    ops += ["free 3", "info", "nvmlmem"]
+    return [(0, o) for o in ops]
+
+
+def appendix_a_trace():
+    """SURVEY Appendix A op script."""
+    ops = ["total 0", "info", f"alloc {100 << 20} 1", "info", "freeptr 0xdeadbeef000", "freeptr 0", "free 1", "free 1",
+           "alloc 0 2", "info"]
+    return [(0, o) for o in ops]
+
+
+def random_trace(seed, nops, nprocs=1, max_bytes=1 << 30, kinds=True):
+    """60 % alloc / 40 % free-of-random-live, sizes log-uniform in [256 B, 1 GiB];
+    sprinkled with info/total/managed/pitch/host ops."""
+    rng = random.Random(seed)
+    live = [[] for _ in range(nprocs)]
+    next_tag = [1] * nprocs
+    out = []
+    import math
+    lo, hi = math.log(256), math.log(max_bytes)
+    for _ in range(nops):
+        p = rng.randrange(nprocs)
+        r = rng.random()
+        if kinds and r < 0.08:
+            out.append((p, rng.choice(["info", "info", "total 0", "nvmlmem"])))
+            continue
+        if r < 0.63 or not live[p]:
+            size = int(math.exp(rng.uniform(lo, hi)))
+            tag = next_tag[p]
+            next_tag[p] += 1
+            k = rng.random() if kinds else 1.0
+            if k < 0.08:
+                out.append((p, f"managed {size} {tag}"))
+            elif k < 0.12:
+                w = rng.randrange(1, 1 << 16)
+                h = rng.randrange(1, 1 << 10)
+                out.append((p, f"pitch {w} {h} {rng.choice([4, 8, 16])} {tag}"))
+            elif k < 0.15:
+                out.append((p, f"hostalloc {min(size, 1 << 20)} {tag}"))
+                continue  # host memory: not tracked as live device memory
+            else:
+                out.append((p, f"alloc {size} {tag}"))
+            live[p].append(tag)  # may have failed (OOM): then the later free exercises the unknown-pointer path
+        else:
+            tag = live[p].pop(rng.randrange(len(live[p])))
+            out.append((p, f"free {tag}"))
+    return out

@@ -75,8 +75,7 @@ int main(void) {
             if (rc == 0 && d < MAXTAG) tags[d] = p;
             printf("%d\n", rc);
         } else if (!strcmp(op, "free")) {
-            rc = cuMemFree_v2(a < MAXTAG ? tags[a] : 0);
-            if (rc == 0 && a < MAXTAG) tags[a] = 0;
+            rc = cuMemFree_v2(a < MAXTAG ? tags[a] : 0); /* the tag keeps its pointer: a second free is a double free */
             printf("%d\n", rc);
         } else if (!strcmp(op, "freeptr")) {
             rc = cuMemFree_v2((CUdeviceptr)a);

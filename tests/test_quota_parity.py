@@ -1,0 +1,147 @@
+"""Quota / accounting parity of the new preload shim (libvgpu.so) with the reference.
+
+Three layers, all on the mock driver of oracle/ref_harness (CPU only):
+ 1. golden replay — tests/golden/quota_*.json.gz were captured from the reference binary
+    (oracle/gen_quota_golden.py); the new shim must reproduce every reply, every OOM log line,
+    the real-driver call log and the final shared-cache file (pids masked);
+ 2. the Python restatement oracle/quota_model.py must reproduce the same goldens (pins it);
+ 3. where the reference binary is present (/root/reference, build container only), fresh
+    random traces run through both libraries and are compared live.
+The vectors of SURVEY.md §8 c.3 and Appendix A are asserted literally as well."""
+import glob
+import gzip
+import json
+import os
+import struct
+
+import pytest
+
+from oracle import quota_harness as H
+from oracle.quota_model import Model, limit_from_env
+
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "quota_*.json.gz")))
+MAP = {"NVIDIA_DEVICE_MAP": "0:" + H.UUID0}
+
+
+@pytest.fixture(scope="module", autouse=True)
+def harness():
+    H.build()
+    assert os.path.exists(H.NEW_LIB), "libvgpu.so not built: run `make`"
+
+
+def load(path):
+    return json.loads(gzip.open(path).read())
+
+
+@pytest.mark.parametrize("path", GOLD, ids=lambda p: os.path.basename(p)[6:-8])
+def test_new_shim_reproduces_reference_golden(path):
+    g = load(path)
+    trace = [tuple(x) for x in g["trace"]]
+    r = H.run_trace(H.NEW_LIB, trace, g["env"], g["nprocs"])
+    bad = [(i, trace[i], g["replies"][i], r["replies"][i]) for i in range(len(trace)) if g["replies"][i] != r["replies"][i]]
+    assert not bad, bad[:5]
+    assert [list(x) for x in r["oom"]] == g["oom"], "OOM log lines (Device d OOM need / limit) differ"
+    assert r["calls"] == g["calls"], "real-driver call trace differs"
+    assert H.region_summary(r["region"]) == g["region"], "final shared-cache file differs"
+
+
+@pytest.mark.parametrize("path", GOLD, ids=lambda p: os.path.basename(p)[6:-8])
+def test_python_model_reproduces_reference_golden(path):
+    g = load(path)
+    m = Model(g["env"], int(g["env"].get("MOCK_TOTAL_MIB", "16384")) << 20, g["nprocs"])
+    for i, (p, op) in enumerate(g["trace"]):
+        got = m.op(p, op)
+        assert got == g["replies"][i], (i, op, got, g["replies"][i])
+    assert m.calls == g["calls"]
+
+
+def test_survey_c3_vector_literally():
+    """SURVEY §8 c.3, observed from the reference binary: limit 1024m."""
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", "CUDA_DEVICE_SM_LIMIT": "10", **MAP}
+    r = H.run_trace(H.NEW_LIB, H.golden_trace(), env)
+    rep = r["replies"]
+    assert rep[0] == "0 1073741824"                          # cuDeviceTotalMem_v2 -> the limit
+    frees = [int(x.split()[1]) for x in rep if x.count(" ") == 2 and x.startswith("0 ")]
+    assert frees == [1073741824, 1072693248, 1069547520, 545259520, 125829120, 125829120, 650117120]
+    assert rep[10] == "-1"                                   # 5th alloc: (CUresult)-1, not 2
+    assert r["oom"] == [(0, 1157627904, 1073741824)]
+    assert rep[-1] == "0 1073741824 650117120 423624704"     # nvmlDeviceGetMemoryInfo: total=limit, free, used
+    b = r["region"]
+    assert len(b) == 804681 and struct.unpack_from("<i", b, 0)[0] == 19920718
+    assert struct.unpack_from("<16Q", b, 0x6B8) == (10,) * 16
+    assert struct.unpack_from("<4i", b, 0xC4738) == (0, 1, 2, 1)  # proc_num, utilization_switch, recent_kernel, priority
+    # the reference leaves its (zeroed) slot behind with status 1 after exit
+    assert struct.unpack_from("<i", b, 0x738 + 0x308)[0] == 1
+    # oversubscribe: same decisions, allocations > 2 MiB take the managed route
+    r2 = H.run_trace(H.NEW_LIB, H.golden_trace(), {**env, "CUDA_OVERSUBSCRIBE": "true"})
+    assert r2["replies"] == rep
+    allocs = [c.split(" ->")[0] for c in r2["calls"] if c.startswith("cuMemAlloc")]
+    assert allocs == ["cuMemAlloc_v2 size=1048576 flags=0", "cuMemAllocManaged size=3145728 flags=1",
+                      "cuMemAllocManaged size=524288000 flags=1", "cuMemAllocManaged size=419430400 flags=1"]
+
+
+@pytest.mark.parametrize("env,total,free2,alloc_rc,free_p", [
+    ({}, 0, 17179869184 - 104857600, "0", "0"),                                     # quirk a18: TotalMem -> 0 when unlimited
+    ({"CUDA_DEVICE_MEMORY_LIMIT": "1g"}, 1073741824, 968884224, "0", "0"),
+    ({"CUDA_DEVICE_MEMORY_LIMIT_0": "1048576k", "CUDA_DEVICE_MEMORY_LIMIT": "2g"}, 1073741824, 968884224, "0", "0"),
+    ({"CUDA_DEVICE_MEMORY_LIMIT_0": "0x40000000"}, 1073741824, 968884224, "0", "0"),  # strtoul base 0
+    ({"CUDA_DEVICE_MEMORY_LIMIT_0": "50m"}, 52428800, 52428800, "-1", "0"),
+])
+def test_survey_appendix_a_rows(env, total, free2, alloc_rc, free_p):
+    r = H.run_trace(H.NEW_LIB, H.appendix_a_trace(), env)["replies"]
+    assert r[0] == f"0 {total}"
+    assert r[2] == alloc_rc
+    assert int(r[3].split()[1]) == free2
+    assert r[4] == "-1" and r[5] == "0"            # unknown pointer -> -1, NULL -> 0
+    assert r[6] == free_p                           # free(p); after a failed alloc the runner holds 0 -> free(0) -> 0
+    assert r[7] == ("0" if alloc_rc == "-1" else "-1")  # free(p) again: no longer tracked -> -1
+    assert r[8] == "0"                              # alloc 0 bytes succeeds
+
+
+def test_two_processes_share_one_cache_file():
+    """SURVEY c.3: A holds 500 MiB, B allocates 100 MiB and reads free = 1024-500-100 MiB;
+    managed 900 MiB -> 2 in both; after both exit a third process sees everything free."""
+    MiB = 1 << 20
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", **MAP}
+    trace = [(0, f"alloc {500 * MiB} 1"), (1, f"alloc {100 * MiB} 1"), (1, "info"), (0, "info"),
+             (0, f"managed {900 * MiB} 2"), (1, f"managed {900 * MiB} 2")]
+    r = H.run_trace(H.NEW_LIB, trace, env, nprocs=2)
+    assert r["replies"] == ["0", "0", "0 444596224 1073741824", "0 444596224 1073741824", "2", "2"]
+
+
+def test_limit_parser_matches_reference_rules():
+    for v, want in [("1024m", 1 << 30), ("1g", 1 << 30), ("1G", 1 << 30), ("1048576k", 1 << 30), ("1073741824", 1 << 30),
+                    ("0x40000000", 1 << 30), ("0", 0), ("", 0), (None, 0), ("abc", 0), ("17179869184g", 0), ("010", 8)]:
+        assert limit_from_env(v) == want, v
+
+
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+@pytest.mark.parametrize("seed,nprocs,env", [
+    (101, 1, {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m"}),
+    (102, 1, {"CUDA_DEVICE_MEMORY_LIMIT_0": "2g", "CUDA_OVERSUBSCRIBE": "true"}),
+    (103, 4, {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m", "CUDA_OVERSUBSCRIBE": "true"}),
+    (104, 3, {"CUDA_DEVICE_MEMORY_LIMIT": "512m"}),
+    (105, 2, {}),
+])
+def test_live_differential_against_reference_binary(seed, nprocs, env):
+    trace = H.random_trace(seed, 2000, nprocs, 1 << 28)
+    env = {**env, **MAP}
+    a = H.run_trace(H.REFERENCE_LIB, trace, env, nprocs)
+    b = H.run_trace(H.NEW_LIB, trace, env, nprocs)
+    assert a["replies"] == b["replies"]
+    assert a["oom"] == b["oom"]
+    assert a["calls"] == b["calls"]
+    assert H.mask_region(a["region"]) == H.mask_region(b["region"]), "final shared-cache bytes differ"
+
+
+def test_shim_exports_the_hooked_driver_symbols():
+    import subprocess
+    out = subprocess.run(["nm", "-D", "--defined-only", H.NEW_LIB], capture_output=True, text=True).stdout
+    names = {line.split()[-1] for line in out.splitlines() if line.strip()}
+    for n in ["cuInit", "cuMemAlloc_v2", "cuMemAllocManaged", "cuMemAllocPitch_v2", "cuMemFree_v2", "cuMemGetInfo_v2",
+              "cuDeviceTotalMem_v2", "cuMemAllocHost_v2", "cuMemHostAlloc", "cuMemHostRegister_v2", "cuLaunchKernel",
+              "cuGetProcAddress", "cuGetProcAddress_v2", "cuDevicePrimaryCtxRetain", "nvmlDeviceGetMemoryInfo", "dlsym",
+              "cuVGPUViewAllocator"]:
+        assert n in names, n
+    internal = [n for n in names if n.startswith(("region_", "shim_", "oom_", "add_chunk"))]
+    assert not internal, f"internal helpers leak into the dynamic symbol table: {internal}"
