@@ -108,6 +108,8 @@ REAL(CUresult, cuMemFreeHost, void *)
 REAL(CUresult, cuMemHostRegister_v2, void *, size_t, unsigned)
 REAL(CUresult, cuMemHostUnregister, void *)
 REAL(CUresult, cuDevicePrimaryCtxRetain, CUcontext *, CUdevice)
+REAL(CUresult, cuCtxSetCurrent, CUcontext)
+REAL(CUresult, cuCtxPushCurrent_v2, CUcontext)
 REAL(CUresult, cuLaunchKernel, void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **)
 REAL(CUresult, cuGetProcAddress, const char *, void **, int, unsigned long long)
 REAL(CUresult, cuGetProcAddress_v2, const char *, void **, int, unsigned long long, int *)
@@ -459,11 +461,191 @@ EXPORT CUresult cuMemHostRegister_v2(void *p, size_t n, unsigned flags) {
 }
 EXPORT CUresult cuMemHostRegister(void *p, size_t n, unsigned flags) { return cuMemHostRegister_v2(p, n, flags); }
 
+/* ------------------------------------------------------------------ SM cap: green contexts
+ * Replaces rate_limiter@0x463b1 / utilization_watcher@0x471a7 (a25).  CUDA_DEVICE_SM_LIMIT=p
+ * with 0 < p < 100 turns into a green context of floor(SMs*p/100) SMs (stepped down to the
+ * driver's granule so the vGPU never exceeds its share); its CUcontext is handed to the
+ * application wherever it asks for the device's primary context, so the runtime API and
+ * every library on top of it run inside the partition.  Which of the disjoint partitions a
+ * container gets: VGPU_SM_PARTITION_INDEX if the plugin provides it, else a hash of the
+ * container's shared-cache path (Contract A carries no vGPU index into the pod).
+ * VGPU_SM_PARTITION=off disables the cap. */
+typedef struct {
+    int type;
+    unsigned char pad[92];
+    union { struct { unsigned smCount; } sm; unsigned char oversize[48]; };
+} shim_dev_resource_t;
+_Static_assert(sizeof(shim_dev_resource_t) == 144, "CUdevResource ABI v1");
+typedef void *CUgreenCtx;
+typedef void *CUdevResourceDesc;
+
+static CUcontext g_green_ctx[VGPU_MAX_DEVICES];
+static CUcontext g_primary_ctx[VGPU_MAX_DEVICES];  /* the real primary context the green one stands in for */
+static int g_green_state[VGPU_MAX_DEVICES];  /* 0 untried, 1 active, -1 unavailable */
+static unsigned g_green_sms[VGPU_MAX_DEVICES];
+static pthread_mutex_t g_green_mu = PTHREAD_MUTEX_INITIALIZER;
+
+static unsigned partition_pick(unsigned nb) {
+    const char *e = getenv("VGPU_SM_PARTITION_INDEX");
+    if (e && *e) return (unsigned)strtoul(e, NULL, 0) % nb;
+    const char *path = getenv("CUDA_DEVICE_MEMORY_SHARED_CACHE");
+    unsigned h = 2166136261u;
+    for (const char *c = path ? path : ""; *c; ++c) h = (h ^ (unsigned char)*c) * 16777619u;
+    return h % nb;
+}
+
+static CUcontext green_ctx_for(CUdevice dev) {
+    if (dev < 0 || dev >= VGPU_MAX_DEVICES || !g_region_ok) return NULL;
+    uint64_t pct = region_sm_limit(dev);
+    const char *sw = getenv("VGPU_SM_PARTITION");
+    if (pct == 0 || pct >= 100 || (sw && strcmp(sw, "off") == 0)) return NULL;
+    pthread_mutex_lock(&g_green_mu);
+    if (g_green_state[dev] == 0) {
+        g_green_state[dev] = -1;
+        typedef CUresult (*getres_t)(CUdevice, shim_dev_resource_t *, int);
+        typedef CUresult (*split_t)(shim_dev_resource_t *, unsigned *, const shim_dev_resource_t *, shim_dev_resource_t *, unsigned, unsigned);
+        typedef CUresult (*gendesc_t)(CUdevResourceDesc *, shim_dev_resource_t *, unsigned);
+        typedef CUresult (*create_t)(CUgreenCtx *, CUdevResourceDesc, CUdevice, unsigned);
+        typedef CUresult (*fromg_t)(CUcontext *, CUgreenCtx);
+        getres_t getres = (getres_t)cuda_sym("cuDeviceGetDevResource");
+        split_t split = (split_t)cuda_sym("cuDevSmResourceSplitByCount");
+        gendesc_t gendesc = (gendesc_t)cuda_sym("cuDevResourceGenerateDesc");
+        create_t create = (create_t)cuda_sym("cuGreenCtxCreate");
+        fromg_t fromg = (fromg_t)cuda_sym("cuCtxFromGreenCtx");
+        shim_dev_resource_t all, groups[64], rest;
+        if (getres && split && gendesc && create && fromg && getres(dev, &all, 1 /* CU_DEV_RESOURCE_TYPE_SM */) == 0) {
+            unsigned total = all.sm.smCount, share = (unsigned)(total * pct / 100), nb = 0, want;
+            for (want = share ? share : 1; want >= 1; --want) {
+                nb = 64;
+                if (split(groups, &nb, &all, &rest, 0, want) == 0 && nb >= 1 && (groups[0].sm.smCount <= share || want == 1)) break;
+                nb = 0;
+            }
+            if (nb) {
+                unsigned k = partition_pick(nb);
+                CUdevResourceDesc desc;
+                CUgreenCtx g;
+                CUcontext c;
+                if (gendesc(&desc, &groups[k], 1) == 0 && create(&g, desc, dev, 1 /* CU_GREEN_CTX_DEFAULT_STREAM */) == 0 &&
+                    fromg(&c, g) == 0) {
+                    g_green_ctx[dev] = c;
+                    g_green_sms[dev] = groups[k].sm.smCount;
+                    g_green_state[dev] = 1;
+                    SHIM_INFO("device %d: SM limit %lu%% -> green context %u of %u, %u of %u SMs", dev, (unsigned long)pct,
+                              k, nb, groups[k].sm.smCount, total);
+                }
+            }
+        }
+        if (g_green_state[dev] != 1)
+            SHIM_ERR("device %d: cannot create a green context for SM limit %lu%%: the SM cap is NOT enforced", dev,
+                     (unsigned long)pct);
+    }
+    CUcontext c = g_green_state[dev] == 1 ? g_green_ctx[dev] : NULL;
+    pthread_mutex_unlock(&g_green_mu);
+    return c;
+}
+
+/* exported for tests / vgpuvalidator: SMs of the partition this process runs in (0 = uncapped) */
+EXPORT unsigned cuVGPUPartitionSmCount(CUdevice dev) {
+    return (dev >= 0 && dev < VGPU_MAX_DEVICES && g_green_state[dev] == 1) ? g_green_sms[dev] : 0;
+}
+
+EXPORT void *cuVGPUPartitionCtx(CUdevice dev) {
+    return (dev >= 0 && dev < VGPU_MAX_DEVICES && g_green_state[dev] == 1) ? g_green_ctx[dev] : NULL;
+}
+
 EXPORT CUresult cuDevicePrimaryCtxRetain(CUcontext *pctx, CUdevice dev) {
     ensure_initialized();
+    SHIM_DEBUG("cuDevicePrimaryCtxRetain(dev=%d)", dev);
     cuDevicePrimaryCtxRetain_t f = get_cuDevicePrimaryCtxRetain();
-    return f ? f(pctx, dev) : 3;
+    CUresult rc = f ? f(pctx, dev) : 3;
+    if (rc != 0) return rc;
+    if (dev >= 0 && dev < VGPU_MAX_DEVICES) {
+        g_primary_ctx[dev] = *pctx;
+        green_ctx_for(dev);  /* created here; bound in place of the primary by the cuCtx* hooks */
+    }
+    return 0;
 }
+
+/* cudart keeps its own handle on the primary context (it has it before it ever calls
+ * cuDevicePrimaryCtxRetain) and binds THAT.  So: whenever a context is bound, find out whether
+ * it is a capped device's primary context and, if so, bind the partition in its place; and
+ * when the application asks which context is current, answer with the primary it expects. */
+static CUcontext partition_after_bind(CUcontext ctx) {
+    /* called with `ctx` already current */
+    int dev = -1;
+    if (!ctx || cur_dev(&dev) != 0 || dev < 0 || dev >= VGPU_MAX_DEVICES) return NULL;
+    if (g_green_state[dev] == 0) {
+        CUcontext p = NULL;
+        cuDevicePrimaryCtxRetain_t f = get_cuDevicePrimaryCtxRetain();
+        if (f && f(&p, dev) == 0) {
+            g_primary_ctx[dev] = p;
+            green_ctx_for(dev);
+        }
+    }
+    return (g_green_state[dev] == 1 && g_primary_ctx[dev] == ctx) ? g_green_ctx[dev] : NULL;
+}
+
+static int caps_possible(void) {
+    static int v = -1;
+    if (v < 0) {
+        const char *sw = getenv("VGPU_SM_PARTITION");
+        v = 0;
+        if (g_region_ok && !(sw && strcmp(sw, "off") == 0))
+            for (int d = 0; d < VGPU_MAX_DEVICES; ++d) {
+                uint64_t p = region_sm_limit(d);
+                if (p > 0 && p < 100) v = 1;
+            }
+    }
+    return v;
+}
+
+EXPORT CUresult cuCtxSetCurrent(CUcontext ctx) {
+    ensure_initialized();
+    cuCtxSetCurrent_t f = get_cuCtxSetCurrent();
+    CUresult rc = f ? f(ctx) : 3;
+    if (rc != 0 || !caps_possible()) return rc;
+    CUcontext g = partition_after_bind(ctx);
+    SHIM_DEBUG("cuCtxSetCurrent(%p) -> %p", ctx, g ? g : ctx);
+    return g ? f(g) : rc;
+}
+
+EXPORT CUresult cuCtxPushCurrent_v2(CUcontext ctx) {
+    ensure_initialized();
+    cuCtxPushCurrent_v2_t f = get_cuCtxPushCurrent_v2();
+    CUresult rc = f ? f(ctx) : 3;
+    if (rc != 0 || !caps_possible()) return rc;
+    CUcontext g = partition_after_bind(ctx);
+    SHIM_DEBUG("cuCtxPushCurrent(%p) -> %p", ctx, g ? g : ctx);
+    if (g) {  /* replace the top of the stack */
+        cuCtxSetCurrent_t set = get_cuCtxSetCurrent();
+        if (set) return set(g);
+    }
+    return rc;
+}
+
+EXPORT CUresult cuCtxGetCurrent(CUcontext *pctx) {
+    ensure_initialized();
+    cuCtxGetCurrent_t f = get_cuCtxGetCurrent();
+    CUresult rc = f ? f(pctx) : 3;
+    if (rc == 0 && *pctx)
+        for (int d = 0; d < VGPU_MAX_DEVICES; ++d)
+            if (g_green_state[d] == 1 && g_green_ctx[d] == *pctx) *pctx = g_primary_ctx[d];
+    return rc;
+}
+
+EXPORT CUresult cuCtxPopCurrent_v2(CUcontext *pctx) {
+    ensure_initialized();
+    typedef CUresult (*pop_t)(CUcontext *);
+    static pop_t f;
+    if (!f) f = (pop_t)cuda_sym("cuCtxPopCurrent_v2");
+    CUresult rc = f ? f(pctx) : 3;
+    if (rc == 0 && pctx && *pctx)
+        for (int d = 0; d < VGPU_MAX_DEVICES; ++d)
+            if (g_green_state[d] == 1 && g_green_ctx[d] == *pctx) *pctx = g_primary_ctx[d];
+    return rc;
+}
+EXPORT CUresult cuCtxPopCurrent(CUcontext *pctx) { return cuCtxPopCurrent_v2(pctx); }
+EXPORT CUresult cuCtxPushCurrent(CUcontext ctx) { return cuCtxPushCurrent_v2(ctx); }
 
 /* cuLaunchKernel@0x37c2b: the suspend gate stays; rate_limiter@0x463b1 is gone — the SM cap is
  * spatial (green context), so there is nothing to do per launch. */
@@ -542,6 +724,10 @@ static const hook_t g_hooks[] = {
     {"cuMemHostAlloc", (void *)cuMemHostAlloc},
     {"cuMemHostRegister", (void *)cuMemHostRegister_v2}, {"cuMemHostRegister_v2", (void *)cuMemHostRegister_v2},
     {"cuDevicePrimaryCtxRetain", (void *)cuDevicePrimaryCtxRetain},
+    {"cuCtxSetCurrent", (void *)cuCtxSetCurrent},
+    {"cuCtxGetCurrent", (void *)cuCtxGetCurrent},
+    {"cuCtxPopCurrent", (void *)cuCtxPopCurrent_v2}, {"cuCtxPopCurrent_v2", (void *)cuCtxPopCurrent_v2},
+    {"cuCtxPushCurrent", (void *)cuCtxPushCurrent_v2}, {"cuCtxPushCurrent_v2", (void *)cuCtxPushCurrent_v2},
     {"cuLaunchKernel", (void *)cuLaunchKernel},
     {"cuGetProcAddress", (void *)cuGetProcAddress}, {"cuGetProcAddress_v2", (void *)cuGetProcAddress_v2},
     {"nvmlDeviceGetMemoryInfo", (void *)nvmlDeviceGetMemoryInfo},
@@ -567,6 +753,7 @@ EXPORT void *dlsym(void *handle, const char *symbol) {
 EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsigned long long flags) {
     ensure_initialized();
     void *h = symbol ? find_hook(symbol) : NULL;
+    if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;
         return 0;
@@ -578,6 +765,7 @@ EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsign
 EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, unsigned long long flags, int *status) {
     ensure_initialized();
     void *h = symbol ? find_hook(symbol) : NULL;
+    if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress_v2(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;
         if (status) *status = 0;  /* CU_GET_PROC_ADDRESS_SUCCESS */

@@ -1,0 +1,134 @@
+"""The preload shim under the REAL driver: a PyTorch process with LD_PRELOAD=libvgpu.so and the
+env vars the plugin's Allocate would set (Contract A).  Checks that the runtime API really lands
+in the hooks (cudart resolves everything through dlsym + cuGetProcAddress), that the quota numbers
+are the reference's, and that CUDA_DEVICE_SM_LIMIT becomes a spatial green-context partition."""
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import textwrap
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SHIM = os.path.join(ROOT, "4paradigm-k8s-device-plugin_b200", "libvgpu.so")
+GiB = 1 << 30
+
+
+def run_under_shim(code, env_extra, cache=None, timeout=300):
+    td = tempfile.mkdtemp(prefix="vgpushim")
+    env = dict(os.environ)
+    env.update({"LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": cache or os.path.join(td, "shr.cache"),
+                "LIBCUDA_LOG_LEVEL": "0"})
+    env.update(env_extra)
+    p = subprocess.run([sys.executable, "-c", textwrap.dedent(code)], env=env, capture_output=True, text=True, timeout=timeout)
+    return p
+
+
+def last_json(p):
+    assert p.returncode == 0, p.stderr[-3000:]
+    return json.loads(p.stdout.strip().splitlines()[-1])
+
+
+def test_quota_is_enforced_through_the_runtime_api(cuda_dev):
+    code = """
+        import json, torch
+        out = {}
+        torch.cuda.init()
+        out["total_prop"] = torch.cuda.get_device_properties(0).total_memory
+        f0, t0 = torch.cuda.mem_get_info()
+        a = torch.empty(3 << 30, dtype=torch.uint8, device="cuda")
+        f1, t1 = torch.cuda.mem_get_info()
+        try:
+            b = torch.empty(2 << 30, dtype=torch.uint8, device="cuda")
+            out["second"] = "allocated"
+        except Exception as e:
+            out["second"] = type(e).__name__
+        f2, _ = torch.cuda.mem_get_info()
+        del a
+        torch.cuda.empty_cache()
+        f3, _ = torch.cuda.mem_get_info()
+        out.update(f0=f0, t0=t0, f1=f1, t1=t1, f2=f2, f3=f3)
+        print(json.dumps(out))
+    """
+    p = run_under_shim(code, {"CUDA_DEVICE_MEMORY_LIMIT_0": "4096m"})
+    o = last_json(p)
+    assert o["t0"] == 4 * GiB == o["t1"] == o["total_prop"]         # cuMemGetInfo total and cuDeviceTotalMem are the limit
+    assert o["f0"] <= 4 * GiB and o["f0"] - o["f1"] == 3 * GiB      # free = limit - usage
+    assert o["second"] != "allocated"                                # 3 GiB + 2 GiB > 4 GiB
+    assert "Device 0 OOM" in p.stderr                                # same ERROR line as the reference (allocator.c:53)
+    assert o["f2"] == o["f1"] and o["f3"] == o["f0"]
+
+
+def test_nvml_memory_info_shows_the_limit(cuda_dev):
+    code = """
+        import json, torch, pynvml
+        torch.cuda.init()
+        a = torch.empty(1 << 30, dtype=torch.uint8, device="cuda")
+        pynvml.nvmlInit()
+        m = pynvml.nvmlDeviceGetMemoryInfo(pynvml.nvmlDeviceGetHandleByIndex(0))
+        print(json.dumps({"total": m.total, "free": m.free, "used": m.used}))
+    """
+    o = last_json(run_under_shim(code, {"CUDA_DEVICE_MEMORY_LIMIT_0": "8g"}))
+    assert o["total"] == 8 * GiB and o["used"] >= 1 * GiB and o["free"] == o["total"] - o["used"]
+
+
+def test_two_processes_share_the_quota_through_the_cache_file(cuda_dev):
+    cache = os.path.join(tempfile.mkdtemp(prefix="vgpushim"), "shared.cache")
+    holder = subprocess.Popen([sys.executable, "-c", textwrap.dedent("""
+        import sys, torch
+        a = torch.empty(3 << 30, dtype=torch.uint8, device="cuda")
+        print("holding", flush=True)
+        sys.stdin.readline()
+    """)], env={**os.environ, "LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": cache, "CUDA_DEVICE_MEMORY_LIMIT_0": "4096m",
+               "LIBCUDA_LOG_LEVEL": "0"}, stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True)
+    try:
+        assert holder.stdout.readline().strip() == "holding"
+        code = """
+            import json, torch
+            f, t = torch.cuda.mem_get_info()
+            try:
+                b = torch.empty(2 << 30, dtype=torch.uint8, device="cuda"); r = "allocated"
+            except Exception as e:
+                r = type(e).__name__
+            print(json.dumps({"free": f, "total": t, "second": r}))
+        """
+        o = last_json(run_under_shim(code, {"CUDA_DEVICE_MEMORY_LIMIT_0": "4096m"}, cache=cache))
+        assert o["total"] == 4 * GiB and o["free"] <= 1 * GiB and o["second"] != "allocated"
+    finally:
+        holder.stdin.write("\n")
+        holder.stdin.flush()
+        holder.wait(timeout=60)
+    # after the holder exits its slot is cleared: a new process sees the whole limit again
+    code = "import json, torch; f, t = torch.cuda.mem_get_info(); print(json.dumps({'free': f, 'total': t}))"
+    o = last_json(run_under_shim(code, {"CUDA_DEVICE_MEMORY_LIMIT_0": "4096m"}, cache=cache))
+    assert o["total"] == 4 * GiB and o["free"] > 3 * GiB
+
+
+def test_sm_limit_becomes_a_green_context_partition(cuda_dev):
+    code = """
+        import ctypes, json, time, torch
+        torch.cuda.init()
+        x = torch.randn(8192, 8192, device="cuda", dtype=torch.bfloat16)
+        y = x @ x
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(10):
+            y = x @ x
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / 10
+        ref = (x[:64].float() @ x.float())
+        ok = bool(torch.allclose(y[:64].float(), ref, rtol=2e-2, atol=2.0))
+        sms = ctypes.CDLL(None).cuVGPUPartitionSmCount(0)
+        print(json.dumps({"sms": sms, "tflops": 2 * 8192**3 / dt / 1e12, "ok": ok,
+                          "mp": torch.cuda.get_device_properties(0).multi_processor_count}))
+    """
+    capped = last_json(run_under_shim(code, {"CUDA_DEVICE_SM_LIMIT": "25", "CUDA_DEVICE_MEMORY_LIMIT_0": "16g"}))
+    free = last_json(run_under_shim(code, {"CUDA_DEVICE_SM_LIMIT": "100", "CUDA_DEVICE_MEMORY_LIMIT_0": "16g"}))
+    assert capped["ok"] and free["ok"]
+    assert free["sms"] == 0 and 0 < capped["sms"] <= 37            # 25 % of 148, granule-rounded down (32)
+    # spatial cap: a compute-bound GEMM gets roughly sms/148 of the machine, not all of it
+    assert capped["tflops"] < 0.45 * free["tflops"], (capped, free)
