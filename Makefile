@@ -19,7 +19,8 @@ SHIM_SO  := $(PKG)/libvgpu.so
 SHIM_SRC := $(CSRC)/libvgpu/shim.c $(CSRC)/libvgpu/region.c
 ORACLE   := oracle/liboracle.so
 
-all: $(DP_SO) $(SHIM_SO) $(ORACLE)
+VALIDATOR := $(PKG)/vgpuvalidator
+all: $(DP_SO) $(SHIM_SO) $(VALIDATOR) $(ORACLE)
 
 $(DP_SO): $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_kernels.cuh $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp \
           $(CSRC)/vgpu_internal.h include/vgpu.h
@@ -29,11 +30,14 @@ $(DP_SO): $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_kernels.
 $(SHIM_SO): $(SHIM_SRC) $(CSRC)/libvgpu/region.h $(CSRC)/libvgpu/shimlog.h
 	$(CC) -O2 -g -fPIC -shared -fvisibility=hidden -Wall -Wextra -Wl,-soname,libvgpu.so -o $@ $(SHIM_SRC) -ldl -lpthread
 
+$(VALIDATOR): $(CSRC)/validator/vgpuvalidator.cpp $(DP_SO) include/vgpu.h
+	$(CXX) -O2 -g -Wall -Wextra -Iinclude -o $@ $(CSRC)/validator/vgpuvalidator.cpp -L$(PKG) -lvgpu_dp -Wl,-rpath,'$$ORIGIN'
+
 $(ORACLE): oracle/vgpu_oracle.c oracle/vgpu_oracle.h
 	$(CC) -O3 -fPIC -shared -Wall -Wextra -o $@ oracle/vgpu_oracle.c -lpthread
 
 clean:
-	rm -f $(DP_SO) $(SHIM_SO) $(ORACLE)
+	rm -f $(DP_SO) $(SHIM_SO) $(VALIDATOR) $(ORACLE)
 
 .PHONY: all clean
 
