@@ -65,6 +65,12 @@ class MemtestResult(C.Structure):
                 ("gbps", C.c_double)]
 
 
+class VmemStats(C.Structure):
+    _fields_ = [("chunks_total", C.c_uint64), ("chunks_resident", C.c_uint64), ("chunks_spilled", C.c_uint64),
+                ("resident_limit", C.c_uint64), ("tier_slots", C.c_uint64), ("evictions", C.c_uint64),
+                ("fetches", C.c_uint64), ("checksum_failures", C.c_uint64), ("evict_ms", C.c_double), ("fetch_ms", C.c_double)]
+
+
 class SmPartition(C.Structure):
     _fields_ = [("green_ctx", C.c_void_p), ("ctx", C.c_void_p), ("stream", C.c_void_p),
                 ("sm_count", C.c_uint32), ("sm_total", C.c_uint32)]
@@ -93,6 +99,12 @@ SIGNATURES = {
     "vgpu_calibrate": (_i, [_i, _i, _i, _sz]),
     "vgpu_policy_get": (_i, [_i, _sz]),
     "vgpu_policy_set": (_i, [_i, _sz, _i]),
+    "vgpu_vmem_create": (_i, [_i, _u64, _u64, _i, _i, _u64, _pp(_vp)]),
+    "vgpu_vmem_base": (_i, [_vp, _pp(_vp)]),
+    "vgpu_vmem_ensure": (_i, [_vp, _u64, _u64]),
+    "vgpu_vmem_evict": (_i, [_vp, _u64, _u64]),
+    "vgpu_vmem_stats": (_i, [_vp, _pp(VmemStats)]),
+    "vgpu_vmem_destroy": (_i, [_vp]),
     "vgpu_memtest_fill": (_i, [_vp, _u64, _i, _u64, _u64, _vp]),
     "vgpu_memtest_verify": (_i, [_vp, _u64, _i, _u64, _u64, _vp, _vp]),
     "vgpu_memtest_run": (_i, [_vp, _u64, _i, _u64, _u64, _u64, _vp, _pp(MemtestResult)]),

@@ -22,9 +22,9 @@ ORACLE   := oracle/liboracle.so
 VALIDATOR := $(PKG)/vgpuvalidator
 all: $(DP_SO) $(SHIM_SO) $(VALIDATOR) $(ORACLE)
 
-$(DP_SO): $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_kernels.cuh $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp \
+$(DP_SO): $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_kernels.cuh $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp $(CSRC)/vgpu_vmem.cpp \
           $(CSRC)/vgpu_internal.h include/vgpu.h
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp -ldl
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(CSRC)/vgpu_datapath.cu $(CSRC)/vgpu_noalloc.cu $(CSRC)/vgpu_plugin.cpp $(CSRC)/vgpu_greenctx.cpp $(CSRC)/vgpu_vmem.cpp -ldl
 
 # the LD_PRELOAD shim: plain C, no CUDA toolkit needed at run time (driver reached by dlopen)
 $(SHIM_SO): $(SHIM_SRC) $(CSRC)/libvgpu/region.h $(CSRC)/libvgpu/shimlog.h

@@ -187,6 +187,43 @@ int vgpu_policy_get(int tier, size_t nchunks);
 int vgpu_policy_set(int tier, size_t min_chunks, int variant);
 
 /* ======================================================================== *
+ *  Virtual device memory manager: a vGPU address range larger than its resident
+ *  HBM.  Replaces the reference's allocmode-0 route (cuMemoryAllocate@0x32146 ->
+ *  cuMemAllocManaged, i.e. UVM demand paging) and finishes its dead allocmode-1
+ *  VMM branch (@0x3225f-0x322a0, cuMapMemory@0x31b28 / cuUnmapMemory@0x37f8f,
+ *  whose helpers are undefined symbols in the shipped binary): the range is
+ *  reserved with cuMemAddressReserve, backed per 2 MiB chunk with
+ *  cuMemCreate/cuMemMap, and chunks move to/from the spill tier with the
+ *  kernels above while the application's pointers stay valid.
+ * ======================================================================== */
+typedef struct vgpu_vmem_stats {
+    uint64_t chunks_total;      /* size of the virtual range in chunks */
+    uint64_t chunks_resident;   /* backed by HBM right now */
+    uint64_t chunks_spilled;    /* living in the tier */
+    uint64_t resident_limit;    /* max chunks that may be resident (the vGPU's HBM quota) */
+    uint64_t tier_slots;        /* capacity of the tier in chunks */
+    uint64_t evictions, fetches;          /* chunks moved out / in so far */
+    uint64_t checksum_failures;           /* chunks whose (X,S) did not match on restore */
+    double   evict_ms, fetch_ms;          /* wall time spent in evict / fetch incl. map/unmap */
+} vgpu_vmem_stats_t;
+
+/* Create a range of `virtual_bytes` (rounded up to 2 MiB) on `device`, of which at most
+ * `resident_bytes` are backed by HBM at any time; the rest lives in a tier slab of
+ * `tier_bytes` (VGPU_TIER_PEER on `peer_device`, or VGPU_TIER_HOST). */
+int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes, int tier,
+                     int peer_device, uint64_t tier_bytes, void **handle);
+int vgpu_vmem_base(void *handle, void **base);
+/* Make chunks [first, first+n) resident: evicts least-recently-used chunks if the resident
+ * limit would be exceeded, maps fresh memory for never-touched chunks, restores (and
+ * checksum-verifies) spilled ones.  Synchronous.  VGPU_E_MISMATCH if a restore fails its
+ * checksum, VGPU_E_NOMEM if n exceeds the resident limit or the tier is full. */
+int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n);
+/* Push chunks [first, first+n) that are resident out to the tier and release their HBM. */
+int vgpu_vmem_evict(void *handle, uint64_t first, uint64_t n);
+int vgpu_vmem_stats(void *handle, vgpu_vmem_stats_t *out);
+int vgpu_vmem_destroy(void *handle);
+
+/* ======================================================================== *
  *  vgpuvalidator memtest (new capability under the reference's mount name
  *  /usr/bin/vgpuvalidator, server.go:518-519; the reference binary is a
  *  license tool, vgpuvalidator@0x4022e0 main — no memtest exists there).

@@ -132,3 +132,20 @@ def test_sm_limit_becomes_a_green_context_partition(cuda_dev):
     assert free["sms"] == 0 and 0 < capped["sms"] <= 37            # 25 % of 148, granule-rounded down (32)
     # spatial cap: a compute-bound GEMM gets roughly sms/148 of the machine, not all of it
     assert capped["tflops"] < 0.45 * free["tflops"], (capped, free)
+
+
+def test_vgpuvalidator_cli_memtest_and_quota(cuda_dev):
+    exe = os.path.join(ROOT, "4paradigm-k8s-device-plugin_b200", "vgpuvalidator")
+    p = subprocess.run([exe, "--memtest", "--gib", "1", "--random-passes", "2"], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    o = json.loads(p.stdout.strip().splitlines()[-1])
+    assert o["mismatches"] == 0 and o["passes"] == 66 and o["bytes"] == GiB and o["GBps"] > 100
+    p = subprocess.run([exe, "--roundtrip", "--chunks", "32"], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0 and json.loads(p.stdout.strip().splitlines()[-1])["bad_chunks"] == 0, p.stderr
+    # inside a vGPU (under the shim) the validator cannot test more memory than the quota allows
+    td = tempfile.mkdtemp(prefix="vgpushim")
+    env = {**os.environ, "LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": os.path.join(td, "c"), "CUDA_DEVICE_MEMORY_LIMIT_0": "2g", "LIBCUDA_LOG_LEVEL": "0"}
+    p = subprocess.run([exe, "--memtest", "--gib", "4", "--patterns", "random", "--random-passes", "1"], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 2 and "Device 0 OOM" in p.stderr
+    p = subprocess.run([exe, "--memtest", "--gib", "1", "--patterns", "random", "--random-passes", "1"], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0, p.stderr
