@@ -46,6 +46,16 @@ def parse():
     return ap.parse_args()
 
 
+def traffic_per_launch(kernel, launch_bytes):
+    """DRAM bytes per launch from the committed ncu --set full capture (profiles/r01_traffic.json),
+    scaled from the profiled launch size to this run's launch size."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))["kernels"][kernel]
+        return int(t["traffic_ratio"] * launch_bytes), t["traffic_ratio"]
+    except Exception:
+        return None, None
+
+
 def peaks():
     try:
         p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -146,6 +156,53 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+# ----------------------------------------------------------------------------- ranks
+class Ranks:
+    """One process per GPU.  vGPUs are independent, so there is no data-path collective: the
+    process group only carries the barrier around timed regions and the max (time) / sum (bytes)
+    of per-rank scalars.  Works on `gloo` (CPU tests) and `nccl` alike."""
+
+    def __init__(self, world, device=None):
+        self.world, self.device = world, device
+
+    def _sync(self):
+        if self.device is not None and self.device.type == "cuda":
+            import torch
+            torch.cuda.synchronize()
+
+    def barrier(self):
+        self._sync()
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        self._sync()
+
+    def _reduce(self, x, op):
+        if self.world == 1:
+            return float(x)
+        import torch
+        import torch.distributed as dist
+        t = torch.tensor([x], dtype=torch.float64, device=self.device if self.device is not None else "cpu")
+        dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
+        return float(t.item())
+
+    def max(self, x):
+        return self._reduce(x, "MAX")
+
+    def sum(self, x):
+        return self._reduce(x, "SUM")
+
+
+def ring_peer(local, world):
+    """Spill tier pairing of config 5: GPU g spills to GPU (g+1) mod N."""
+    return (local + 1) % world
+
+
+def whole_job_gbps(bytes_per_rank_per_step, steps, world, max_ms):
+    """`value`: units all ranks processed / max-over-ranks device time."""
+    return world * bytes_per_rank_per_step * steps / (max_ms * 1e6)
+
+
 # ----------------------------------------------------------------------------- GPU legs
 def main():
     args = parse()
@@ -169,25 +226,8 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    ranks = Ranks(world, dev)
+    barrier, max_over_ranks, sum_over_ranks = ranks.barrier, ranks.max, ranks.sum
 
     hbm_peak, peak_src = peaks()
     out_extra = {}
@@ -256,7 +296,7 @@ def main():
     if bad:
         raise SystemExit(f"memtest found {bad} mismatching words: not a valid bench run")
     bytes_per_step_rank = 2 * per * 2 * nv  # (fill+verify) x 2 patterns x vGPUs
-    value = world * bytes_per_step_rank * args.steps / (ms * 1e6)
+    value = whole_job_gbps(bytes_per_step_rank, args.steps, world, ms)
     launches = args.steps * nv * 4
 
     # per-kernel durations, each timed alone on vGPU 0's stream (CUDA events on that stream)
@@ -293,6 +333,7 @@ def main():
         kms = e0.elapsed_time(e1) / 3
         whole[name] = {"ms": round(kms, 4), "GBps": round(per / (kms * 1e6), 1)}
     dom = max(whole, key=lambda k: whole[k]["ms"])
+    traffic, traffic_ratio = traffic_per_launch(dom, per)
 
     # e2e: the blocking C-ABI call a user of vgpuvalidator makes (vgpu_memtest_run), one host
     # thread per vGPU, result blocks read back to the host every pass; wall clock.
@@ -314,7 +355,7 @@ def main():
     e2e_run(1, args.steps)
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - w0) * 1e3)
-    e2e_value = world * bytes_per_step_rank * args.steps / (e2e_ms * 1e6)
+    e2e_value = whole_job_gbps(bytes_per_step_rank, args.steps, world, e2e_ms)
 
     line = None
     if rank == 0:
@@ -340,7 +381,9 @@ def main():
                     "note": "a memtest has no host input: patterns are generated on the device by definition; host<->device e2e numbers for the spill path are in spill_restore.host.e2e_*"},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": whole[dom]["GBps"], "peak": hbm_peak, "unit": "GB/s",
-                         "frac": round(whole[dom]["GBps"] / hbm_peak, 4), "traffic": None, "kernel": f"k_memtest_{dom} (whole GPU, timed alone)",
+                         "frac": round(whole[dom]["GBps"] / hbm_peak, 4), "traffic": traffic,
+                         "traffic_note": f"dram read+write bytes per {per / GIB:.0f} GiB launch = {traffic_ratio} x algorithmic bytes (ncu --set full, profiles/r01_traffic.json)",
+                         "algorithmic_bytes_per_launch": per, "kernel": f"k_memtest_{dom} (whole GPU, timed alone)",
                          "peak_source": peak_src, "whole_gpu": whole, "one_partition": kern,
                          "step_aggregate": {"GBps": round(value / world, 1), "frac": round(value / world / hbm_peak, 4),
                                             "frac_of_8TBps_spec": round(value / world / 8000.0, 4)}},
@@ -375,7 +418,7 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, barrier, max_over_rank
     tiers["host"] = (capi.TIER_HOST, host.data_ptr(), min(nmax, 1024))
     peer_slab = C.c_void_p()
     if world > 1:
-        peer = (local + 1) % world
+        peer = ring_peer(local, world)
         rc = capi.lib.vgpu_slab_alloc(capi.TIER_PEER, local, peer, nmax * cb, C.byref(peer_slab))
         if rc != 0:
             raise SystemExit("peer slab: " + capi.last_error())
@@ -447,7 +490,7 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, barrier, max_over_rank
     out["host"]["e2e_host_buffer_calls"] = {"chunks": n, "d2h_bytes_per_call": n * cb + n * 16, "h2d_bytes_per_call": n * cb + n * 16, **e2e}
     if peer_slab.value:
         barrier()
-        capi.lib.vgpu_slab_free(capi.TIER_PEER, local, (local + 1) % world, peer_slab)
+        capi.lib.vgpu_slab_free(capi.TIER_PEER, local, ring_peer(local, world), peer_slab)
     del hbm, back, local_slab, host
     torch.cuda.empty_cache()
     return out
