@@ -24,6 +24,7 @@ NOALLOC_MAX_CHUNKS = 4096
 XFER_AUTO, XFER_LDST, XFER_TMA, XFER_CE = 0, 1, 2, 3
 TIER_LOCAL, TIER_PEER, TIER_HOST = 0, 1, 2
 PAT_WALKING_ONES, PAT_RANDOM = 0, 1
+SM_FINE = 1
 ID_LEN, KEY_LEN, VAL_LEN, PATH_LEN = 128, 64, 1024, 256
 U64_MAX = (1 << 64) - 1
 
@@ -110,6 +111,7 @@ SIGNATURES = {
     "vgpu_memtest_run": (_i, [_vp, _u64, _i, _u64, _u64, _u64, _vp, _pp(MemtestResult)]),
     "vgpu_memtest": (_i, [_i, _u64, _u, _u64, _u64, _pp(MemtestResult)]),
     "vgpu_sm_partition_create": (_i, [_i, _u, _u, _pp(SmPartition)]),
+    "vgpu_sm_partition_create_ex": (_i, [_i, _u, _u, _u, _pp(SmPartition)]),
     "vgpu_sm_partition_destroy": (_i, [_pp(SmPartition), _u]),
 }
 for _name, (_res, _args) in SIGNATURES.items():

@@ -515,9 +515,13 @@ static CUcontext green_ctx_for(CUdevice dev) {
         shim_dev_resource_t all, groups[64], rest;
         if (getres && split && gendesc && create && fromg && getres(dev, &all, 1 /* CU_DEV_RESOURCE_TYPE_SM */) == 0) {
             unsigned total = all.sm.smCount, share = (unsigned)(total * pct / 100), nb = 0, want;
+            /* VGPU_SM_PARTITION_GRANULE=fine: SM-granular groups (IGNORE_SM_COSCHEDULING = 1), e.g.
+             * 10 % of 148 SMs -> 14 instead of 8; default keeps cluster co-scheduling inside the vGPU */
+            const char *gr = getenv("VGPU_SM_PARTITION_GRANULE");
+            const unsigned sflags = (gr && strcmp(gr, "fine") == 0) ? 1u : 0u;
             for (want = share ? share : 1; want >= 1; --want) {
                 nb = 64;
-                if (split(groups, &nb, &all, &rest, 0, want) == 0 && nb >= 1 && (groups[0].sm.smCount <= share || want == 1)) break;
+                if (split(groups, &nb, &all, &rest, sflags, want) == 0 && nb >= 1 && (groups[0].sm.smCount <= share || want == 1)) break;
                 nb = 0;
             }
             if (nb) {

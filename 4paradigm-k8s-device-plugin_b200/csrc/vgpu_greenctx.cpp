@@ -71,6 +71,11 @@ int drv_fail(const char *what, CUresult r) {
 extern "C" {
 
 int vgpu_sm_partition_create(int device, unsigned percent, unsigned n, vgpu_sm_partition_t *out) {
+    return vgpu_sm_partition_create_ex(device, percent, n, 0, out);
+}
+
+int vgpu_sm_partition_create_ex(int device, unsigned percent, unsigned n, unsigned flags, vgpu_sm_partition_t *out) {
+    const unsigned split_flags = (flags & VGPU_SM_FINE) ? CU_DEV_SM_RESOURCE_SPLIT_IGNORE_SM_COSCHEDULING : 0;
     if (!out || n == 0 || n > 64) return fail(VGPU_E_INVAL, "bad partition request");
     if (percent == 0 || percent > 100) return fail(VGPU_E_INVAL, "percent=%u must be in 1..100", percent);
     std::call_once(g_once, load_driver);
@@ -90,12 +95,12 @@ int vgpu_sm_partition_create(int device, unsigned percent, unsigned n, vgpu_sm_p
     // than n groups (148 SMs, 25 %: 37 -> 40 -> only 3 groups).  A vGPU must never get MORE
     // than its share, so step the ask down to the largest count that still yields n
     // disjoint groups (148 SMs, 25 %, n=4: 4 x 32).  Co-scheduling (clusters, cta_group::2)
-    // is kept: flags = 0.
+    // is kept unless the caller passes VGPU_SM_FINE.
     CUdevResource groups[64], rest;
     unsigned nb = 0;
     for (;; --want) {
         nb = n;
-        r = g_drv.DevSmResourceSplitByCount(groups, &nb, &all, &rest, 0, want);
+        r = g_drv.DevSmResourceSplitByCount(groups, &nb, &all, &rest, split_flags, want);
         const bool formed = r == CUDA_SUCCESS && nb >= n;
         if (formed && (groups[0].sm.smCount <= total * percent / 100 || want <= 1)) break;
         if (want <= 1) {

@@ -286,6 +286,12 @@ typedef struct vgpu_sm_partition {
  * (rounded by the driver to its granule).  percent = CUDA_DEVICE_SM_LIMIT. */
 int vgpu_sm_partition_create(int device, unsigned percent, unsigned n,
                              vgpu_sm_partition_t *out);
+/* Same with flags.  VGPU_SM_FINE asks the driver for SM-granular groups
+ * (CU_DEV_SM_RESOURCE_SPLIT_IGNORE_SM_COSCHEDULING): 148 SMs / 10 vGPUs gives 10 x 14 instead of
+ * 10 x 8, at the price of cluster co-scheduling guarantees inside a partition. */
+#define VGPU_SM_FINE 1u
+int vgpu_sm_partition_create_ex(int device, unsigned percent, unsigned n, unsigned flags,
+                                vgpu_sm_partition_t *out);
 int vgpu_sm_partition_destroy(vgpu_sm_partition_t *parts, unsigned n);
 
 #ifdef __cplusplus
