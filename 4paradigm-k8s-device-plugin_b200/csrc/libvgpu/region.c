@@ -101,8 +101,16 @@ int region_reap_dead(void) {
     return n;
 }
 
-static void on_sigusr2(int s) { (void)s; if (g_reg) for (int i = 0; i < g_reg->proc_num; ++i) if (g_reg->procs[i].pid == g_pid) g_reg->procs[i].status = 2; }
-static void on_sigusr1(int s) { (void)s; if (g_reg) for (int i = 0; i < g_reg->proc_num; ++i) if (g_reg->procs[i].pid == g_pid) g_reg->procs[i].status = 1; }
+void (*region_status_hook)(int status);  /* set by the shim; must be async-signal-safe */
+
+static void set_my_status(int st) {
+    if (g_reg)
+        for (int i = 0; i < g_reg->proc_num; ++i)
+            if (g_reg->procs[i].pid == g_pid) g_reg->procs[i].status = st;
+    if (region_status_hook) region_status_hook(st);
+}
+static void on_sigusr2(int s) { (void)s; set_my_status(2); }  /* sig_swap_stub: suspend */
+static void on_sigusr1(int s) { (void)s; set_my_status(1); }  /* sig_restore_stub: resume */
 
 /* init_proc_slot_withlock@0x44820 */
 static void claim_slot(void) {

@@ -218,9 +218,13 @@ static void pre_init(void) {
     if (!g_region_ok) SHIM_ERR("shared cache %s unavailable: quota disabled", path);
 }
 
+static void load_vmm_backend(void);
+static void start_mover(void);
+
 static void post_init(void) {
     const char *o = getenv("CUDA_OVERSUBSCRIBE");
     g_allocmode = (o && strcmp(o, "true") == 0) ? 0 : 2;
+    if (g_allocmode == 0) load_vmm_backend();
     if (g_virtual_devices <= 0 && get_cuDeviceGetCount()) {
         int n = 0;
         if (real_cuDeviceGetCount(&n) == 0) g_virtual_devices = n;
@@ -229,9 +233,60 @@ static void post_init(void) {
 
 static void ensure_initialized(void) { pthread_once(&g_pre_once, pre_init); }
 
-/* suspend gate: wait_status_self@0x45ff5 — sleep while an external monitor has us at status 2 */
+/* suspend gate: wait_status_self@0x45ff5 — wait while an external monitor has us at status 2,
+ * and (vmm backend) until the data that was spilled on suspend is back behind its pointers */
+static volatile int g_data_out;  /* 1 while VMM-backed allocations are (being) spilled */
 static void wait_running(void) {
-    while (g_region_ok && region_my_status() != 1) sleep(1);
+    while (g_region_ok && (region_my_status() != 1 || g_data_out)) usleep(g_data_out ? 1000 : 1000000);
+}
+
+/* ------------------------------------------------------------------ oversubscribe backend
+ * CUDA_OVERSUBSCRIBE=true routes allocations above 2 MiB away from plain cuMemAlloc.  The
+ * reference hands them to UVM (cuMemAllocManaged).  With VGPU_OVERSUB_BACKEND=vmm they are
+ * backed by the VMM manager of libvgpu_dp.so instead: the pointer the application holds stays
+ * valid while the chunks behind it are spilled to pinned host RAM by the spill kernel (suspend,
+ * SIGUSR2 / cuVGPUSuspend) and restored + checksum-verified by the restore kernel (resume,
+ * SIGUSR1 / cuVGPUResume), releasing the HBM to other vGPUs in between.
+ * While the shim itself calls into libvgpu_dp.so, that library's own driver calls must not be
+ * metered or re-enter the allocator lock: tl_bypass makes every hook a plain pass-through. */
+static __thread int tl_bypass;
+static struct {
+    void *lib;
+    int (*create)(int, uint64_t, uint64_t, int, int, uint64_t, void **);
+    int (*base)(void *, void **);
+    int (*ensure)(void *, uint64_t, uint64_t);
+    int (*evict)(void *, uint64_t, uint64_t);
+    int (*destroy)(void *);
+    const char *(*last_error)(void);
+} g_dp;
+static int g_backend_vmm;
+
+static void load_vmm_backend(void) {
+    const char *b = getenv("VGPU_OVERSUB_BACKEND");
+    if (!b || strcmp(b, "vmm") != 0) return;
+    find_real_dlsym();
+    Dl_info info;
+    char path[4096] = "libvgpu_dp.so";
+    if (dladdr((void *)load_vmm_backend, &info) && info.dli_fname) {  /* next to libvgpu.so */
+        const char *slash = strrchr(info.dli_fname, '/');
+        if (slash) snprintf(path, sizeof(path), "%.*s/libvgpu_dp.so", (int)(slash - info.dli_fname), info.dli_fname);
+    }
+    tl_bypass = 1;
+    g_dp.lib = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+    tl_bypass = 0;
+    if (!g_dp.lib) {
+        SHIM_ERR("VGPU_OVERSUB_BACKEND=vmm but %s cannot be loaded (%s): staying with managed memory", path, dlerror());
+        return;
+    }
+    g_dp.create = (int (*)(int, uint64_t, uint64_t, int, int, uint64_t, void **))real_dlsym(g_dp.lib, "vgpu_vmem_create");
+    g_dp.base = (int (*)(void *, void **))real_dlsym(g_dp.lib, "vgpu_vmem_base");
+    g_dp.ensure = (int (*)(void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_ensure");
+    g_dp.evict = (int (*)(void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_evict");
+    g_dp.destroy = (int (*)(void *))real_dlsym(g_dp.lib, "vgpu_vmem_destroy");
+    g_dp.last_error = (const char *(*)(void))real_dlsym(g_dp.lib, "vgpu_last_error");
+    g_backend_vmm = g_dp.create && g_dp.base && g_dp.ensure && g_dp.evict && g_dp.destroy && g_dp.last_error;
+    if (!g_backend_vmm) SHIM_ERR("%s lacks the vgpu_vmem_* entry points", path);
+    else start_mover();
 }
 
 /* ------------------------------------------------------------------ allocation list (a13, a15) */
@@ -239,17 +294,19 @@ typedef struct alloc_node {
     CUdeviceptr addr;
     size_t len;
     int dev;
+    void *vmem;  /* VMM-backed (oversubscribe backend) */
     struct alloc_node *next, *prev;
 } alloc_node_t;
 static alloc_node_t *g_head, *g_tail;
 static size_t g_nalloc;
 static pthread_mutex_t g_alloc_mu = PTHREAD_MUTEX_INITIALIZER;
 
-static void track(CUdeviceptr p, size_t n, int dev) {
+static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
     alloc_node_t *a = (alloc_node_t *)malloc(sizeof(*a));
     a->addr = p;
     a->len = n;
     a->dev = dev;
+    a->vmem = vmem;
     a->next = NULL;
     a->prev = g_tail;
     if (g_tail) g_tail->next = a; else g_head = a;
@@ -262,6 +319,8 @@ static int cur_dev(int *dev) {
     if (!f) return 3;
     return f(dev);
 }
+
+static void track(CUdeviceptr p, size_t n, int dev) { track_vmem(p, n, dev, NULL); }
 
 /* oom_check@0x40528 */
 static int oom_check(int dev, size_t addon) {
@@ -291,6 +350,23 @@ static int add_chunk(CUdeviceptr *p, size_t n) {
     if (n <= IPCSIZE || g_allocmode == 2) {
         cuMemAlloc_v2_t f = get_cuMemAlloc_v2();
         rc = f ? f(p, n) : 3;
+    } else if (g_backend_vmm) {
+        const uint64_t chunks = (n + IPCSIZE - 1) / IPCSIZE;
+        void *h = NULL, *base = NULL;
+        tl_bypass = 1;
+        int vrc = g_dp.create(dev, n, chunks * IPCSIZE, 2 /* VGPU_TIER_HOST */, -1, chunks * IPCSIZE, &h);
+        if (vrc == 0) vrc = g_dp.ensure(h, 0, chunks);
+        if (vrc == 0) vrc = g_dp.base(h, &base);
+        if (vrc != 0) {
+            SHIM_ERR("vmm backend: %s", g_dp.last_error());
+            if (h) g_dp.destroy(h);
+        }
+        tl_bypass = 0;
+        if (vrc != 0) return 2;
+        *p = (CUdeviceptr)(uintptr_t)base;
+        track_vmem(*p, n, dev, h);
+        region_add_usage(dev, n, VGPU_USE_DATA);
+        return 0;
     } else {
         /* cuMemoryAllocate@0x32146, allocmode 0.  The reference hands the allocation to
          * UVM here; the explicit spill/restore data path (libvgpu_dp.so) takes this route
@@ -323,6 +399,7 @@ EXPORT CUresult cuInit(unsigned flags) {
 }
 
 EXPORT CUresult cuMemAlloc_v2(CUdeviceptr *dptr, size_t bytesize) {
+    if (tl_bypass) return get_cuMemAlloc_v2()(dptr, bytesize);
     ensure_initialized();
     pthread_once(&g_post_once, post_init);
     wait_running();
@@ -334,6 +411,7 @@ EXPORT CUresult cuMemAlloc_v2(CUdeviceptr *dptr, size_t bytesize) {
 EXPORT CUresult cuMemAlloc(CUdeviceptr *dptr, size_t bytesize) { return cuMemAlloc_v2(dptr, bytesize); }
 
 EXPORT CUresult cuMemAllocManaged(CUdeviceptr *dptr, size_t bytesize, unsigned flags) {
+    if (tl_bypass) return get_cuMemAllocManaged()(dptr, bytesize, flags);
     ensure_initialized();
     pthread_once(&g_post_once, post_init);
     wait_running();
@@ -348,6 +426,7 @@ EXPORT CUresult cuMemAllocManaged(CUdeviceptr *dptr, size_t bytesize, unsigned f
 }
 
 EXPORT CUresult cuMemAllocPitch_v2(CUdeviceptr *dptr, size_t *pitch, size_t w, size_t h, unsigned elem) {
+    if (tl_bypass) return get_cuMemAllocPitch_v2()(dptr, pitch, w, h, elem);
     ensure_initialized();
     pthread_once(&g_post_once, post_init);
     wait_running();
@@ -367,6 +446,7 @@ EXPORT CUresult cuMemAllocPitch(CUdeviceptr *dptr, size_t *pitch, size_t w, size
 }
 
 EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
+    if (tl_bypass) return get_cuMemFree_v2()(dptr);
     ensure_initialized();
     if (dptr == 0) return 0;  /* cuMemFree_v2@0x32e5d */
     pthread_mutex_lock(&g_alloc_mu);
@@ -376,8 +456,15 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
         pthread_mutex_unlock(&g_alloc_mu);
         return -1;
     }
-    cuMemFree_v2_t f = get_cuMemFree_v2();
-    CUresult rc = f ? f(dptr) : 3;
+    CUresult rc;
+    if (a->vmem) {
+        tl_bypass = 1;
+        rc = g_dp.destroy(a->vmem) == 0 ? 0 : 999;
+        tl_bypass = 0;
+    } else {
+        cuMemFree_v2_t f = get_cuMemFree_v2();
+        rc = f ? f(dptr) : 3;
+    }
     if (a->prev) a->prev->next = a->next; else g_head = a->next;
     if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
     --g_nalloc;
@@ -391,6 +478,7 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
 EXPORT CUresult cuMemFree(CUdeviceptr dptr) { return cuMemFree_v2(dptr); }
 
 EXPORT CUresult cuMemGetInfo_v2(size_t *free_b, size_t *total_b) {
+    if (tl_bypass) return get_cuMemGetInfo_v2()(free_b, total_b);
     ensure_initialized();
     int dev = 0;
     CUresult rc = cur_dev(&dev);
@@ -424,6 +512,7 @@ EXPORT CUresult cuDeviceTotalMem(size_t *bytes, CUdevice dev) { return cuDeviceT
 
 /* host-memory hooks (a20): allocate first, then check_oom@0x311bd == oom_check(cur, 0) */
 EXPORT CUresult cuMemAllocHost_v2(void **pp, size_t n) {
+    if (tl_bypass) return get_cuMemAllocHost_v2()(pp, n);
     ensure_initialized();
     cuMemAllocHost_v2_t f = get_cuMemAllocHost_v2();
     CUresult rc = f ? f(pp, n) : 3;
@@ -437,6 +526,7 @@ EXPORT CUresult cuMemAllocHost_v2(void **pp, size_t n) {
 EXPORT CUresult cuMemAllocHost(void **pp, size_t n) { return cuMemAllocHost_v2(pp, n); }
 
 EXPORT CUresult cuMemHostAlloc(void **pp, size_t n, unsigned flags) {
+    if (tl_bypass) return get_cuMemHostAlloc()(pp, n, flags);
     ensure_initialized();
     cuMemHostAlloc_t f = get_cuMemHostAlloc();
     CUresult rc = f ? f(pp, n, flags) : 3;
@@ -449,6 +539,7 @@ EXPORT CUresult cuMemHostAlloc(void **pp, size_t n, unsigned flags) {
 }
 
 EXPORT CUresult cuMemHostRegister_v2(void *p, size_t n, unsigned flags) {
+    if (tl_bypass) return get_cuMemHostRegister_v2()(p, n, flags);
     ensure_initialized();
     cuMemHostRegister_v2_t f = get_cuMemHostRegister_v2();
     CUresult rc = f ? f(p, n, flags) : 3;
@@ -655,10 +746,22 @@ EXPORT CUresult cuCtxPushCurrent(CUcontext ctx) { return cuCtxPushCurrent_v2(ctx
  * spatial (green context), so there is nothing to do per launch. */
 EXPORT CUresult cuLaunchKernel(void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by,
                                unsigned bz, unsigned shm, void *stream, void **params, void **extra) {
+    if (tl_bypass) return get_cuLaunchKernel()(fn, gx, gy, gz, bx, by, bz, shm, stream, params, extra);
     ensure_initialized();
     wait_running();
     cuLaunchKernel_t f = get_cuLaunchKernel();
     return f ? f(fn, gx, gy, gz, bx, by, bz, shm, stream, params, extra) : 3;
+}
+
+EXPORT CUresult cuLaunchKernelEx(const void *config, void *fn, void **params, void **extra) {
+    typedef CUresult (*ex_t)(const void *, void *, void **, void **);
+    static ex_t f;
+    if (!f) f = (ex_t)cuda_sym("cuLaunchKernelEx");
+    if (!tl_bypass) {
+        ensure_initialized();
+        wait_running();
+    }
+    return f ? f(config, fn, params, extra) : 3;
 }
 
 /* ------------------------------------------------------------------ NVML (a23) */
@@ -733,6 +836,7 @@ static const hook_t g_hooks[] = {
     {"cuCtxPopCurrent", (void *)cuCtxPopCurrent_v2}, {"cuCtxPopCurrent_v2", (void *)cuCtxPopCurrent_v2},
     {"cuCtxPushCurrent", (void *)cuCtxPushCurrent_v2}, {"cuCtxPushCurrent_v2", (void *)cuCtxPushCurrent_v2},
     {"cuLaunchKernel", (void *)cuLaunchKernel},
+    {"cuLaunchKernelEx", (void *)cuLaunchKernelEx},
     {"cuGetProcAddress", (void *)cuGetProcAddress}, {"cuGetProcAddress_v2", (void *)cuGetProcAddress_v2},
     {"nvmlDeviceGetMemoryInfo", (void *)nvmlDeviceGetMemoryInfo},
     {"nvmlDeviceGetMemoryInfo_v2", (void *)nvmlDeviceGetMemoryInfo_v2},
@@ -777,6 +881,81 @@ EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, uns
     }
     cuGetProcAddress_v2_t f = get_cuGetProcAddress_v2();
     return f ? f(symbol, pfn, ver, flags, status) : 500;
+}
+
+/* Suspend / resume of a whole vGPU (the reference's dormant suspend_all@0x45ddf / resume_all
+ * @0x45eea only flip the status word; here they also move the data).  Suspend: drain the GPU,
+ * spill every VMM-backed allocation to the host tier and release its HBM.  Resume: map fresh
+ * HBM behind the same addresses, restore, verify checksums.  Returns chunks-level errors as
+ * CUDA_ERROR_UNKNOWN (999). */
+REAL(CUresult, cuCtxSynchronize, void)
+static CUresult move_all(int out) {
+    CUresult rc = 0;
+    pthread_mutex_lock(&g_alloc_mu);
+    tl_bypass = 1;
+    if (out && get_cuCtxSynchronize()) real_cuCtxSynchronize();
+    for (alloc_node_t *a = g_head; a; a = a->next)
+        if (a->vmem) {
+            const uint64_t chunks = (a->len + IPCSIZE - 1) / IPCSIZE;
+            int vrc = out ? g_dp.evict(a->vmem, 0, chunks) : g_dp.ensure(a->vmem, 0, chunks);
+            if (vrc != 0) {
+                SHIM_ERR("vmm backend %s: %s", out ? "suspend" : "resume", g_dp.last_error());
+                rc = 999;
+            }
+        }
+    tl_bypass = 0;
+    pthread_mutex_unlock(&g_alloc_mu);
+    return rc;
+}
+EXPORT CUresult cuVGPUSuspend(void) { return g_backend_vmm ? move_all(1) : 801 /* NOT_SUPPORTED */; }
+EXPORT CUresult cuVGPUResume(void) { return g_backend_vmm ? move_all(0) : 801; }
+
+/* Signal-driven form of the same (the reference's protocol: an external monitor sends SIGUSR2 to
+ * suspend a vGPU process and SIGUSR1 to resume it, sig_swap_stub / sig_restore_stub).  The
+ * handlers only flip the status word and post a semaphore; this thread does the work.  New
+ * launches and allocations of the application park at the gates (wait_running) from the moment
+ * the status turns 2 until the data is back. */
+#include <semaphore.h>
+static sem_t g_mover_sem;
+static volatile int g_mover_target = 1;
+static void mover_wake(int status) {
+    g_mover_target = status;
+    if (status == 2) g_data_out = 1;  /* close the gate before anything moves */
+    sem_post(&g_mover_sem);
+}
+static void *mover_main(void *arg) {
+    (void)arg;
+    int bound = 0, out = 0;
+    for (;;) {
+        while (sem_wait(&g_mover_sem) != 0) {}
+        if (!bound) {  /* work in the application's primary context of device 0 */
+            CUcontext ctx = NULL;
+            cuDevicePrimaryCtxRetain_t r = get_cuDevicePrimaryCtxRetain();
+            cuCtxSetCurrent_t set = get_cuCtxSetCurrent();
+            if (r && set && r(&ctx, 0) == 0 && set(ctx) == 0) bound = 1;
+        }
+        const int target = g_mover_target;
+        if (target == 2 && !out) {
+            usleep(20000);  /* let threads that were past the gate finish issuing */
+            move_all(1);
+            out = 1;
+        } else if (target == 1 && out) {
+            move_all(0);
+            out = 0;
+            g_data_out = 0;
+        } else if (target == 1) {
+            g_data_out = 0;
+        }
+    }
+    return NULL;
+}
+static void start_mover(void) {
+    pthread_t th;
+    sem_init(&g_mover_sem, 0, 0);
+    if (pthread_create(&th, NULL, mover_main, NULL) == 0) {
+        pthread_detach(th);
+        region_status_hook = mover_wake;
+    }
 }
 
 /* cuVGPUViewAllocator@0x16c80: dump the tracked allocations */

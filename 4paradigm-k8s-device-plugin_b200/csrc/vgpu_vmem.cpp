@@ -132,6 +132,8 @@ int set_access_runs(Vmem *v, const std::vector<size_t> &idx) {
 // Spill `victims` (resident chunk indices) to the tier, then unmap them and park or release their memory.
 int evict_list(Vmem *v, const std::vector<size_t> &victims, bool release) {
     if (victims.empty()) return VGPU_OK;
+    if (!v->tier_slab && v->tier_slots)
+        if (int rc = vgpu_slab_alloc(v->tier, v->device, v->peer, v->tier_slots * kCB, &v->tier_slab)) return rc;
     if (victims.size() > v->free_slots.size()) return fail(VGPU_E_NOMEM, "spill tier full: %zu victims, %zu free slots", victims.size(), v->free_slots.size());
     const double t0 = now_ms();
     for (size_t off = 0; off < victims.size(); off += kBatch) {
@@ -199,7 +201,7 @@ int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes
         delete v;
         return drv_fail("cuMemAddressReserve", r);
     }
-    int rc = v->tier_slots ? vgpu_slab_alloc(tier, device, peer_device, v->tier_slots * kCB, &v->tier_slab) : VGPU_OK;
+    int rc = VGPU_OK;  // the tier slab is allocated at the first eviction, not here
     if (!rc) {
         cudaError_t e = cudaHostAlloc(&v->src_slot, kBatch * sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable);
         if (e == cudaSuccess) e = cudaHostAlloc(&v->dst_slot, kBatch * sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable);

@@ -149,3 +149,95 @@ def test_vgpuvalidator_cli_memtest_and_quota(cuda_dev):
     assert p.returncode == 2 and "Device 0 OOM" in p.stderr
     p = subprocess.run([exe, "--memtest", "--gib", "1", "--patterns", "random", "--random-passes", "1"], capture_output=True, text=True, timeout=300, env=env)
     assert p.returncode == 0, p.stderr
+
+
+def test_oversubscribe_vmm_backend_suspend_releases_hbm_and_resume_restores(cuda_dev):
+    """CUDA_OVERSUBSCRIBE=true + VGPU_OVERSUB_BACKEND=vmm: large allocations are VMM-backed; a
+    suspend spills them to pinned host RAM with the spill kernel and gives the HBM back to the
+    device, a resume restores them behind the same pointers, checksum-verified."""
+    code = """
+        import ctypes, json, torch
+        shim = ctypes.CDLL(None)
+        real = ctypes.CDLL("libcuda.so.1")
+        torch.cuda.init()
+        a = torch.empty(6 << 30, dtype=torch.uint8, device="cuda")
+        a.view(torch.int64).copy_(torch.arange(a.numel() // 8, device="cuda", dtype=torch.int64) * 2654435761)
+        s0 = int(a.view(torch.int64).sum().item())
+        small = torch.ones(1024, device="cuda")               # <= 2 MiB: plain cuMemAlloc, stays put
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()                              # drop the temporaries' cached segments
+        import os, subprocess
+        def used_mib():
+            # physical view: run nvidia-smi WITHOUT the shim (under it, NVML shows the vGPU's quota usage)
+            env = {k: v for k, v in os.environ.items() if k != "LD_PRELOAD"}
+            o = subprocess.run(["nvidia-smi", "--query-gpu=memory.used", "--format=csv,noheader,nounits", "-i", "0"], capture_output=True, text=True, env=env).stdout
+            return int(o.strip().splitlines()[0])
+        u0 = used_mib()
+        rc1 = shim.cuVGPUSuspend()
+        u1 = used_mib()
+        rc2 = shim.cuVGPUResume()
+        u2 = used_mib()
+        s1 = int(a.view(torch.int64).sum().item())
+        print(json.dumps({"rc": [rc1, rc2], "used_mib": [u0, u1, u2], "same": s0 == s1, "small": float(small.sum())}))
+    """
+    p = run_under_shim(code, {"CUDA_DEVICE_MEMORY_LIMIT_0": "40g", "CUDA_OVERSUBSCRIBE": "true", "VGPU_OVERSUB_BACKEND": "vmm"})
+    o = last_json(p)
+    assert o["rc"] == [0, 0], p.stderr[-2000:]
+    u0, u1, u2 = o["used_mib"]
+    assert u0 - u1 >= 6 * 1024 - 64, o      # suspend released (at least) the 6 GiB of HBM behind `a`
+    assert u2 - u1 >= 6 * 1024 - 64, o      # resume took it back
+    assert o["same"] and o["small"] == 1024.0
+
+
+def test_sigusr2_suspends_and_sigusr1_resumes_a_running_vgpu_process(cuda_dev):
+    """The reference's monitor protocol (SIGUSR2 -> suspended, SIGUSR1 -> running) now also moves
+    the data: while suspended the process holds (almost) no HBM; after resume it carries on."""
+    import signal, time
+    td = tempfile.mkdtemp(prefix="vgpushim")
+    env = {**os.environ, "LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": os.path.join(td, "c"), "LIBCUDA_LOG_LEVEL": "0",
+           "CUDA_DEVICE_MEMORY_LIMIT_0": "40g", "CUDA_OVERSUBSCRIBE": "true", "VGPU_OVERSUB_BACKEND": "vmm"}
+    code = textwrap.dedent("""
+        import json, sys, torch
+        a = torch.empty(4 << 30, dtype=torch.uint8, device="cuda")
+        a.view(torch.int64).copy_(torch.arange(a.numel() // 8, device="cuda", dtype=torch.int64) * 40503)
+        s0 = int(a.view(torch.int64).sum().item())
+        torch.cuda.empty_cache()
+        print("ready", flush=True)
+        n = 0
+        while True:                      # keeps launching kernels; parks at the gate while suspended
+            line = sys.stdin.readline().strip()
+            if line == "stop":
+                break
+            s = int(a.view(torch.int64).sum().item()); n += 1
+            print(json.dumps({"same": s == s0, "n": n}), flush=True)
+    """)
+    p = subprocess.Popen([sys.executable, "-c", code], env=env, stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+
+    def used_mib():
+        o = subprocess.run(["nvidia-smi", "--query-gpu=memory.used", "--format=csv,noheader,nounits", "-i", "0"], capture_output=True, text=True).stdout
+        return int(o.strip().splitlines()[0])
+
+    def poke():
+        p.stdin.write("go\n"); p.stdin.flush()
+        return json.loads(p.stdout.readline())
+
+    try:
+        assert p.stdout.readline().strip() == "ready"
+        assert poke()["same"]
+        u0 = used_mib()
+        os.kill(p.pid, signal.SIGUSR2)
+        deadline = time.time() + 30
+        while time.time() < deadline and u0 - used_mib() < 4 * 1024 - 64:
+            time.sleep(0.2)
+        u1 = used_mib()
+        assert u0 - u1 >= 4 * 1024 - 64, (u0, u1)     # suspended: the 4 GiB went to pinned host RAM
+        os.kill(p.pid, signal.SIGUSR1)
+        r = poke()                                     # parks until the data is back, then computes on it
+        assert r["same"]
+        assert used_mib() - u1 >= 4 * 1024 - 64
+    finally:
+        try:
+            p.stdin.write("stop\n"); p.stdin.flush()
+            p.wait(timeout=30)
+        except Exception:
+            p.kill()
