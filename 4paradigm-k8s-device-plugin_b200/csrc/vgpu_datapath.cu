@@ -70,7 +70,9 @@ int get_acc(int dev, void *stream, size_t nchunks, ChunkAcc **out) {
         size_t cap = std::max<size_t>(4096, nchunks);
         ChunkAcc *p = nullptr;
         VGPU_CUDA(cudaMalloc(&p, cap * sizeof(ChunkAcc)));
-        VGPU_CUDA(cudaMemset(p, 0, cap * sizeof(ChunkAcc)));
+        // zero it ON THE CALLER'S STREAM: a memset on the legacy stream is not ordered before a
+        // kernel on a non-blocking stream (torch streams, green-context streams)
+        VGPU_CUDA(cudaMemsetAsync(p, 0, cap * sizeof(ChunkAcc), static_cast<cudaStream_t>(stream)));
         if (s.acc) {
             // the old block may still be in use by launches queued on this stream
             VGPU_CUDA(cudaStreamSynchronize((cudaStream_t)stream));

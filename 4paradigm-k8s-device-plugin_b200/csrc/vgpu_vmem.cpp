@@ -16,6 +16,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -60,107 +61,113 @@ int drv_fail(const char *what, CUresult r) {
     return fail(r == CUDA_ERROR_OUT_OF_MEMORY ? VGPU_E_NOMEM : VGPU_E_CUDA, "%s -> %d (%s)", what, (int)r, s ? s : "?");
 }
 
-enum ChunkState : uint8_t { kUntouched = 0, kResident = 1, kSpilled = 2 };
+// Residency unit = BLOCK of consecutive chunks (default 128 x 2 MiB = 256 MiB), transfer and
+// checksum unit = chunk.  Every VMM driver call costs 80-350 us whatever its size (measured on
+// B200: cuMemCreate 100, cuMemSetAccess 215, cuMemUnmap 90 us per call; profiles/r01_vmm_costs.md),
+// so mapping per 2 MiB chunk caps paging at ~5 GB/s; per 256 MiB block the calls cost ~0.4 ms
+// against 0.37 ms of NVLink transfer and are overlapped with the kernels of the neighbouring
+// blocks (launches are asynchronous; the host maps block k+1 while the GPU restores block k).
+enum BlockState : uint8_t { kUntouched = 0, kResident = 1, kSpilled = 2 };
 
-struct Chunk {
+struct Block {
     CUmemGenericAllocationHandle handle = 0;
     uint64_t last_use = 0;
-    uint32_t tier_slot = 0;
-    ChunkState state = kUntouched;
-    vgpu_cksum_t cksum{0, 0};
+    uint32_t tier_slot = 0;  // block-sized slot in the tier slab
+    BlockState state = kUntouched;
 };
 
 constexpr size_t kCB = VGPU_CHUNK_BYTES;
-constexpr size_t kBatch = 4096;  // chunks per kernel launch (8 GiB)
 
 struct Vmem {
     int device = 0, tier = 0, peer = -1;
     CUdeviceptr base = 0;
-    size_t nchunks = 0, resident_limit = 0, tier_slots = 0;
+    size_t nchunks = 0;         // as requested
+    size_t bc = 0;              // chunks per block
+    size_t nblocks = 0, resident_limit = 0 /* blocks */, tier_slots = 0 /* blocks */;
     void *tier_slab = nullptr;
-    std::vector<Chunk> chunks;
-    std::vector<CUmemGenericAllocationHandle> pool;  // parked physical chunks
+    std::vector<Block> blocks;
+    std::vector<CUmemGenericAllocationHandle> pool;  // parked physical blocks
     std::vector<uint32_t> free_slots;
-    size_t resident = 0, spilled = 0;
+    size_t resident = 0, spilled = 0;  // blocks
     uint64_t clock = 0;
-    // pinned + mapped staging (host writes, kernels read / write over PCIe; a few KiB per batch)
-    uint32_t *src_slot = nullptr, *dst_slot = nullptr;
-    vgpu_cksum_t *ck = nullptr;
-    vgpu_restore_result_t *res = nullptr;
+    vgpu_cksum_t *ck = nullptr;          // pinned + mapped: (X,S) of every chunk, written by the spill kernel,
+                                         // read as `expect` by the restore kernel
+    vgpu_restore_result_t *res = nullptr;  // pinned + mapped
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
     CUmemAllocationProp prop{};
     CUmemAccessDesc access{};
     vgpu_vmem_stats_t st{};
     std::mutex mu;
+    size_t block_bytes() const { return bc * kCB; }
 };
 
 double now_ms() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
-int map_chunk(Vmem *v, size_t c) {
-    Chunk &ch = v->chunks[c];
+int map_block(Vmem *v, size_t b) {
+    Block &bl = v->blocks[b];
     CUmemGenericAllocationHandle h;
     if (!v->pool.empty()) {
         h = v->pool.back();
         v->pool.pop_back();
     } else {
-        CUresult r = g_api.Create(&h, kCB, &v->prop, 0);
+        CUresult r = g_api.Create(&h, v->block_bytes(), &v->prop, 0);
         if (r != CUDA_SUCCESS) return drv_fail("cuMemCreate", r);
     }
-    CUresult r = g_api.Map(v->base + c * kCB, kCB, 0, h, 0);
+    const CUdeviceptr va = v->base + b * v->block_bytes();
+    CUresult r = g_api.Map(va, v->block_bytes(), 0, h, 0);
+    if (r == CUDA_SUCCESS) r = g_api.SetAccess(va, v->block_bytes(), &v->access, 1);
     if (r != CUDA_SUCCESS) {
         v->pool.push_back(h);
-        return drv_fail("cuMemMap", r);
+        return drv_fail("cuMemMap/cuMemSetAccess", r);
     }
-    ch.handle = h;
+    bl.handle = h;
     return VGPU_OK;
 }
 
-// cuMemSetAccess over maximal runs of consecutive chunk indices (sorted input)
-int set_access_runs(Vmem *v, const std::vector<size_t> &idx) {
-    size_t i = 0;
-    while (i < idx.size()) {
-        size_t j = i + 1;
-        while (j < idx.size() && idx[j] == idx[j - 1] + 1) ++j;
-        CUresult r = g_api.SetAccess(v->base + idx[i] * kCB, (j - i) * kCB, &v->access, 1);
-        if (r != CUDA_SUCCESS) return drv_fail("cuMemSetAccess", r);
-        i = j;
-    }
+int unmap_block(Vmem *v, size_t b, bool release) {
+    Block &bl = v->blocks[b];
+    CUresult r = g_api.Unmap(v->base + b * v->block_bytes(), v->block_bytes());
+    if (r != CUDA_SUCCESS) return drv_fail("cuMemUnmap", r);
+    if (release) g_api.Release(bl.handle);  // explicit evict: the HBM goes back to the device
+    else v->pool.push_back(bl.handle);      // making room inside ensure(): reused within microseconds
+    bl.handle = 0;
+    bl.state = kSpilled;
     return VGPU_OK;
 }
 
-// Spill `victims` (resident chunk indices) to the tier, then unmap them and park or release their memory.
-int evict_list(Vmem *v, const std::vector<size_t> &victims, bool release) {
+// Spill resident blocks `victims` to the tier, then unmap them and park or release their memory.
+// The unmap of block i-1 overlaps the spill kernel of block i.
+int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
     if (victims.empty()) return VGPU_OK;
     if (!v->tier_slab && v->tier_slots)
-        if (int rc = vgpu_slab_alloc(v->tier, v->device, v->peer, v->tier_slots * kCB, &v->tier_slab)) return rc;
-    if (victims.size() > v->free_slots.size()) return fail(VGPU_E_NOMEM, "spill tier full: %zu victims, %zu free slots", victims.size(), v->free_slots.size());
+        if (int rc = vgpu_slab_alloc(v->tier, v->device, v->peer, v->tier_slots * v->block_bytes(), &v->tier_slab)) return rc;
+    if (victims.size() > v->free_slots.size())
+        return fail(VGPU_E_NOMEM, "spill tier full: %zu blocks to evict, %zu free slots", victims.size(), v->free_slots.size());
     const double t0 = now_ms();
-    for (size_t off = 0; off < victims.size(); off += kBatch) {
-        const size_t n = std::min(kBatch, victims.size() - off);
-        for (size_t k = 0; k < n; ++k) {
-            v->src_slot[k] = (uint32_t)victims[off + k];
-            v->dst_slot[k] = v->free_slots[v->free_slots.size() - 1 - k];
-        }
-        int rc = vgpu_spill(VGPU_XFER_AUTO, v->tier, (const void *)v->base, v->tier_slab, v->src_slot, v->dst_slot, n, kCB, v->ck, nullptr);
+    VGPU_CUDA(cudaDeviceSynchronize());  // whatever the application queued on the victims must be done
+    for (size_t i = 0; i < victims.size(); ++i) {
+        const size_t b = victims[i];
+        Block &bl = v->blocks[b];
+        bl.tier_slot = v->free_slots.back();
+        v->free_slots.pop_back();
+        int rc = vgpu_spill(VGPU_XFER_AUTO, v->tier, (const void *)(v->base + b * v->block_bytes()),
+                            (char *)v->tier_slab + (size_t)bl.tier_slot * v->block_bytes(), nullptr, nullptr, v->bc, kCB,
+                            v->ck + b * v->bc, v->stream);
         if (rc) return rc;
-        VGPU_CUDA(cudaStreamSynchronize(nullptr));
-        for (size_t k = 0; k < n; ++k) {
-            Chunk &ch = v->chunks[victims[off + k]];
-            ch.cksum = v->ck[k];
-            ch.tier_slot = v->dst_slot[k];
-            CUresult r = g_api.Unmap(v->base + victims[off + k] * kCB, kCB);
-            if (r != CUDA_SUCCESS) return drv_fail("cuMemUnmap", r);
-            if (release) g_api.Release(ch.handle);  // explicit evict: the HBM goes back to the device
-            else v->pool.push_back(ch.handle);      // making room inside ensure(): reused within microseconds
-            ch.handle = 0;
-            ch.state = kSpilled;
+        VGPU_CUDA(cudaEventRecord(v->ev[i & 1], v->stream));
+        if (i > 0) {
+            VGPU_CUDA(cudaEventSynchronize(v->ev[(i - 1) & 1]));
+            if (int urc = unmap_block(v, victims[i - 1], release)) return urc;
         }
-        v->free_slots.resize(v->free_slots.size() - n);
-        v->resident -= n;
-        v->spilled += n;
-        v->st.evictions += n;
     }
+    VGPU_CUDA(cudaEventSynchronize(v->ev[(victims.size() - 1) & 1]));
+    if (int urc = unmap_block(v, victims.back(), release)) return urc;
+    v->resident -= victims.size();
+    v->spilled += victims.size();
+    v->st.evictions += victims.size() * v->bc;
     v->st.evict_ms += now_ms() - t0;
     return VGPU_OK;
 }
@@ -182,8 +189,12 @@ int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes
     v->tier = tier;
     v->peer = peer_device;
     v->nchunks = (virtual_bytes + kCB - 1) / kCB;
-    v->resident_limit = std::max<uint64_t>(1, resident_bytes / kCB);
-    v->tier_slots = tier_bytes / kCB;
+    size_t bc = 128;
+    if (const char *e = getenv("VGPU_VMEM_BLOCK_CHUNKS")) bc = std::max<long>(1, atol(e));
+    v->bc = std::min(bc, v->nchunks);
+    v->nblocks = (v->nchunks + v->bc - 1) / v->bc;
+    v->resident_limit = std::max<uint64_t>(1, (resident_bytes + v->block_bytes() - 1) / v->block_bytes());  // whole blocks
+    v->tier_slots = (tier_bytes + v->block_bytes() - 1) / v->block_bytes();
     v->prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
     v->prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
     v->prop.location.id = device;
@@ -196,24 +207,23 @@ int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes
         return r != CUDA_SUCCESS ? drv_fail("cuMemGetAllocationGranularity", r)
                                  : fail(VGPU_E_UNSUPPORTED, "allocation granularity %zu does not divide the 2 MiB chunk", gran);
     }
-    r = g_api.AddressReserve(&v->base, v->nchunks * kCB, kCB, 0, 0);
+    r = g_api.AddressReserve(&v->base, v->nblocks * v->block_bytes(), kCB, 0, 0);
     if (r != CUDA_SUCCESS) {
         delete v;
         return drv_fail("cuMemAddressReserve", r);
     }
     int rc = VGPU_OK;  // the tier slab is allocated at the first eviction, not here
-    if (!rc) {
-        cudaError_t e = cudaHostAlloc(&v->src_slot, kBatch * sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable);
-        if (e == cudaSuccess) e = cudaHostAlloc(&v->dst_slot, kBatch * sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable);
-        if (e == cudaSuccess) e = cudaHostAlloc(&v->ck, kBatch * sizeof(vgpu_cksum_t), cudaHostAllocMapped | cudaHostAllocPortable);
-        if (e == cudaSuccess) e = cudaHostAlloc(&v->res, sizeof(vgpu_restore_result_t), cudaHostAllocMapped | cudaHostAllocPortable);
-        if (e != cudaSuccess) rc = fail(VGPU_E_NOMEM, "pinned staging: %s", cudaGetErrorString(e));
-    }
+    cudaError_t e = cudaHostAlloc(&v->ck, v->nblocks * v->bc * sizeof(vgpu_cksum_t), cudaHostAllocMapped | cudaHostAllocPortable);
+    if (e == cudaSuccess) e = cudaHostAlloc(&v->res, sizeof(vgpu_restore_result_t), cudaHostAllocMapped | cudaHostAllocPortable);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&v->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&v->ev[0], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&v->ev[1], cudaEventDisableTiming);
+    if (e != cudaSuccess) rc = fail(VGPU_E_NOMEM, "vmem staging: %s", cudaGetErrorString(e));
     if (rc) {
         vgpu_vmem_destroy(v);
         return rc;
     }
-    v->chunks.resize(v->nchunks);
+    v->blocks.resize(v->nblocks);
     v->free_slots.resize(v->tier_slots);
     for (size_t i = 0; i < v->tier_slots; ++i) v->free_slots[i] = (uint32_t)(v->tier_slots - 1 - i);
     *handle = v;
@@ -229,12 +239,13 @@ int vgpu_vmem_base(void *handle, void **base) {
 int vgpu_vmem_evict(void *handle, uint64_t first, uint64_t n) {
     Vmem *v = static_cast<Vmem *>(handle);
     if (!v || first + n > v->nchunks) return fail(VGPU_E_INVAL, "chunk range out of bounds");
+    if (n == 0) return VGPU_OK;
     std::lock_guard<std::mutex> lk(v->mu);
     VGPU_CUDA(cudaSetDevice(v->device));
     std::vector<size_t> victims;
-    for (size_t c = first; c < first + n; ++c)
-        if (v->chunks[c].state == kResident) victims.push_back(c);
-    int rc = evict_list(v, victims, true);
+    for (size_t b = first / v->bc; b <= (first + n - 1) / v->bc; ++b)
+        if (v->blocks[b].state == kResident) victims.push_back(b);
+    int rc = evict_blocks(v, victims, true);
     for (auto h : v->pool) g_api.Release(h);
     v->pool.clear();
     return rc;
@@ -243,66 +254,65 @@ int vgpu_vmem_evict(void *handle, uint64_t first, uint64_t n) {
 int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
     Vmem *v = static_cast<Vmem *>(handle);
     if (!v || first + n > v->nchunks) return fail(VGPU_E_INVAL, "chunk range out of bounds");
-    if (n > v->resident_limit) return fail(VGPU_E_NOMEM, "%llu chunks requested, resident limit is %zu", (unsigned long long)n, v->resident_limit);
+    if (n == 0) return VGPU_OK;
+    const size_t b0 = first / v->bc, b1 = (first + n - 1) / v->bc;
+    if (b1 - b0 + 1 > v->resident_limit)
+        return fail(VGPU_E_NOMEM, "%llu chunks requested, resident limit is %zu", (unsigned long long)n, v->resident_limit * v->bc);
     std::lock_guard<std::mutex> lk(v->mu);
     VGPU_CUDA(cudaSetDevice(v->device));
     const uint64_t stamp = ++v->clock;
     std::vector<size_t> fresh, back;
-    for (size_t c = first; c < first + n; ++c) {
-        Chunk &ch = v->chunks[c];
-        ch.last_use = stamp;
-        if (ch.state == kUntouched) fresh.push_back(c);
-        else if (ch.state == kSpilled) back.push_back(c);
+    for (size_t b = b0; b <= b1; ++b) {
+        Block &bl = v->blocks[b];
+        bl.last_use = stamp;
+        if (bl.state == kUntouched) fresh.push_back(b);
+        else if (bl.state == kSpilled) back.push_back(b);
     }
     const size_t need = fresh.size() + back.size();
     if (v->resident + need > v->resident_limit) {
-        // least-recently-used resident chunks outside the requested range make room
+        // least-recently-used resident blocks outside the requested range make room
         size_t want = v->resident + need - v->resident_limit;
         std::vector<size_t> cand;
-        for (size_t c = 0; c < v->nchunks; ++c)
-            if (v->chunks[c].state == kResident && v->chunks[c].last_use != stamp) cand.push_back(c);
-        if (cand.size() < want) return fail(VGPU_E_NOMEM, "cannot make room: %zu needed, %zu evictable", want, cand.size());
-        std::nth_element(cand.begin(), cand.begin() + (want - 1), cand.end(),
-                         [&](size_t a, size_t b) { return v->chunks[a].last_use < v->chunks[b].last_use || (v->chunks[a].last_use == v->chunks[b].last_use && a < b); });
+        for (size_t b = 0; b < v->nblocks; ++b)
+            if (v->blocks[b].state == kResident && v->blocks[b].last_use != stamp) cand.push_back(b);
+        if (cand.size() < want) return fail(VGPU_E_NOMEM, "cannot make room: %zu blocks needed, %zu evictable", want, cand.size());
+        std::nth_element(cand.begin(), cand.begin() + (want - 1), cand.end(), [&](size_t a, size_t b) {
+            return v->blocks[a].last_use < v->blocks[b].last_use || (v->blocks[a].last_use == v->blocks[b].last_use && a < b);
+        });
         cand.resize(want);
         std::sort(cand.begin(), cand.end());
-        if (int rc = evict_list(v, cand, false)) return rc;
+        if (int rc = evict_blocks(v, cand, false)) return rc;
     }
     const double t0 = now_ms();
-    std::vector<size_t> all(fresh);
-    all.insert(all.end(), back.begin(), back.end());
-    std::sort(all.begin(), all.end());
-    for (size_t c : all)
-        if (int rc = map_chunk(v, c)) return rc;
-    if (int rc = set_access_runs(v, all)) return rc;
-    for (size_t c : fresh) v->chunks[c].state = kResident;
+    for (size_t b : fresh) {
+        if (int rc = map_block(v, b)) return rc;
+        v->blocks[b].state = kResident;
+    }
     v->resident += fresh.size();
-    int result = VGPU_OK;
-    for (size_t off = 0; off < back.size(); off += kBatch) {
-        const size_t m = std::min(kBatch, back.size() - off);
-        for (size_t k = 0; k < m; ++k) {
-            v->src_slot[k] = v->chunks[back[off + k]].tier_slot;
-            v->dst_slot[k] = (uint32_t)back[off + k];
-            v->ck[k] = v->chunks[back[off + k]].cksum;
-        }
-        v->res->bad_chunks = 0;
-        v->res->first_bad_inv = 0;
-        int rc = vgpu_restore(VGPU_XFER_AUTO, v->tier, v->tier_slab, (void *)v->base, v->src_slot, v->dst_slot, m, kCB, v->ck, nullptr, v->res, nullptr);
+    v->res->bad_chunks = 0;
+    v->res->first_bad_inv = 0;
+    for (size_t b : back) {  // map block k+1 on the host while the GPU restores block k
+        if (int rc = map_block(v, b)) return rc;
+        Block &bl = v->blocks[b];
+        int rc = vgpu_restore(VGPU_XFER_AUTO, v->tier, (const char *)v->tier_slab + (size_t)bl.tier_slot * v->block_bytes(),
+                              (void *)(v->base + b * v->block_bytes()), nullptr, nullptr, v->bc, kCB, v->ck + b * v->bc, nullptr,
+                              v->res, v->stream);
         if (rc) return rc;
-        VGPU_CUDA(cudaStreamSynchronize(nullptr));
+    }
+    int result = VGPU_OK;
+    if (!back.empty()) {
+        VGPU_CUDA(cudaStreamSynchronize(v->stream));
         if (v->res->bad_chunks) {
             v->st.checksum_failures += v->res->bad_chunks;
-            result = fail(VGPU_E_MISMATCH, "%llu restored chunk(s) failed their checksum (first: chunk %u)",
-                          (unsigned long long)v->res->bad_chunks, v->dst_slot[(size_t)~v->res->first_bad_inv]);
+            result = fail(VGPU_E_MISMATCH, "%llu restored chunk(s) failed their checksum", (unsigned long long)v->res->bad_chunks);
         }
-        for (size_t k = 0; k < m; ++k) {
-            Chunk &ch = v->chunks[back[off + k]];
-            v->free_slots.push_back(ch.tier_slot);
-            ch.state = kResident;
+        for (size_t b : back) {
+            v->free_slots.push_back(v->blocks[b].tier_slot);
+            v->blocks[b].state = kResident;
         }
-        v->resident += m;
-        v->spilled -= m;
-        v->st.fetches += m;
+        v->resident += back.size();
+        v->spilled -= back.size();
+        v->st.fetches += back.size() * v->bc;
     }
     v->st.fetch_ms += now_ms() - t0;
     return result;
@@ -314,10 +324,10 @@ int vgpu_vmem_stats(void *handle, vgpu_vmem_stats_t *out) {
     std::lock_guard<std::mutex> lk(v->mu);
     *out = v->st;
     out->chunks_total = v->nchunks;
-    out->chunks_resident = v->resident;
-    out->chunks_spilled = v->spilled;
-    out->resident_limit = v->resident_limit;
-    out->tier_slots = v->tier_slots;
+    out->chunks_resident = v->resident * v->bc;
+    out->chunks_spilled = v->spilled * v->bc;
+    out->resident_limit = v->resident_limit * v->bc;
+    out->tier_slots = v->tier_slots * v->bc;
     return VGPU_OK;
 }
 
@@ -326,18 +336,19 @@ int vgpu_vmem_destroy(void *handle) {
     if (!v) return VGPU_OK;
     cudaSetDevice(v->device);
     cudaDeviceSynchronize();
-    for (size_t c = 0; c < v->chunks.size(); ++c)
-        if (v->chunks[c].state == kResident && v->chunks[c].handle) {
-            g_api.Unmap(v->base + c * kCB, kCB);
-            g_api.Release(v->chunks[c].handle);
+    for (size_t b = 0; b < v->blocks.size(); ++b)
+        if (v->blocks[b].state == kResident && v->blocks[b].handle) {
+            g_api.Unmap(v->base + b * v->block_bytes(), v->block_bytes());
+            g_api.Release(v->blocks[b].handle);
         }
     for (auto h : v->pool) g_api.Release(h);
-    if (v->base) g_api.AddressFree(v->base, v->nchunks * kCB);
+    if (v->base) g_api.AddressFree(v->base, v->nblocks * v->block_bytes());
     if (v->tier_slab) vgpu_slab_free(v->tier, v->device, v->peer, v->tier_slab);
-    if (v->src_slot) cudaFreeHost(v->src_slot);
-    if (v->dst_slot) cudaFreeHost(v->dst_slot);
     if (v->ck) cudaFreeHost(v->ck);
     if (v->res) cudaFreeHost(v->res);
+    if (v->stream) cudaStreamDestroy(v->stream);
+    for (auto &e : v->ev)
+        if (e) cudaEventDestroy(e);
     delete v;
     return VGPU_OK;
 }

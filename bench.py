@@ -41,6 +41,13 @@ def parse():
                     help="green: one 25%% green-context SM partition per vGPU (default); streams: plain streams "
                          "(ncu cannot profile launches into green contexts)")
     ap.add_argument("--no-spill", action="store_true", help="skip the spill/restore sweep")
+    ap.add_argument("--config4", action="store_true",
+                    help="also run BASELINE config 4 through the virtual-device-memory manager: 1 vGPU, 180 GB quota + 120 GB "
+                         "oversubscribed, paged in 8 GiB windows (tier: GPU 1's HBM if --gpus >= 2, else pinned host at --config4-scale)")
+    ap.add_argument("--config4-scale", type=float, default=None, help="size factor for config 4 (default 1.0 with a peer GPU, 0.2 on the host tier)")
+    ap.add_argument("--config5", action="store_true",
+                    help="also run BASELINE config 5 per GPU: 10 vGPUs x 16 GiB memtest in 10 %% SM partitions, concurrent with a "
+                         "spill/restore loop (peer ring g->g+1 if --gpus >= 2, else pinned host)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-gib", type=float, default=2.0, help="host buffer of the CPU memtest sample")
     return ap.parse_args()
@@ -236,6 +243,11 @@ def main():
     if not args.no_spill:
         out_extra["spill_restore"] = spill_sweep(args, capi, dp, torch, dev, local, world, barrier, max_over_ranks, sum_over_ranks)
 
+    if args.config4:
+        out_extra["config4_vmem"] = config4_phase(args, capi, torch, local, world, ranks)
+    if args.config5:
+        out_extra["config5_concurrent"] = config5_phase(args, capi, dp, torch, dev, local, world, ranks)
+
     # ---------------- phase B: memtest (config 2) ---------------------------------------
     nv = args.vgpus
     free, total = torch.cuda.mem_get_info(dev)
@@ -396,6 +408,141 @@ def main():
         capi.lib.vgpu_sm_partition_destroy(parts, nv)
     if world > 1:
         dist.destroy_process_group()
+
+
+def config4_phase(args, capi, torch, local, world, ranks):
+    """Config 4: one vGPU whose virtual range (quota + oversubscription) exceeds what may be resident;
+    a write pass and a read-verify pass over the whole range in 8 GiB windows, paged by vgpu_vmem
+    (LRU evict -> spill kernel -> unmap; map -> restore kernel -> checksum verify).  Rank 0 only."""
+    out = None
+    if ranks is not None:
+        ranks.barrier()
+    if local == 0:
+        cb = capi.CHUNK_BYTES
+        tier, peer = (capi.TIER_PEER, 1) if world > 1 else (capi.TIER_HOST, -1)
+        scale = args.config4_scale if args.config4_scale else (1.0 if world > 1 else 0.2)
+        free, _ = torch.cuda.mem_get_info()
+        quota = int(180e9 * scale) // cb
+        over = int(120e9 * scale) // cb
+        resident = min(quota, (free - 6 * GIB) // cb)
+        total = quota + over
+        win = min(4096, resident // 2)
+        total -= total % win
+        h = C.c_void_p()
+        capi.check(capi.lib.vgpu_vmem_create(local, total * cb, resident * cb, tier, peer, (total - resident + win) * cb, C.byref(h)))
+        base = C.c_void_p()
+        capi.check(capi.lib.vgpu_vmem_base(h, C.byref(base)))
+        res = torch.zeros(3, dtype=torch.int64, device=torch.device("cuda", local))
+        try:
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for w in range(total // win):
+                capi.check(capi.lib.vgpu_vmem_ensure(h, w * win, win))
+                capi.check(capi.lib.vgpu_memtest_fill(base.value + w * win * cb, win * cb, capi.PAT_RANDOM, w, 4, None))
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            for w in range(total // win):
+                capi.check(capi.lib.vgpu_vmem_ensure(h, w * win, win))
+                capi.check(capi.lib.vgpu_memtest_verify(base.value + w * win * cb, win * cb, capi.PAT_RANDOM, w, 4, res.data_ptr(), None))
+            torch.cuda.synchronize()
+            t2 = time.perf_counter()
+            st = capi.VmemStats()
+            capi.check(capi.lib.vgpu_vmem_stats(h, C.byref(st)))
+            bad = res.cpu().tolist()
+            if bad != [0, 0, 0] or st.checksum_failures:
+                raise SystemExit(f"config 4: restored data is not bit-exact: {bad}, checksum failures {st.checksum_failures}")
+            out = {"tier": "peer HBM (GPU 1) over NVLink" if world > 1 else "pinned host over PCIe", "scale": scale,
+                   "virtual_GB": round(total * cb / 1e9, 1), "resident_limit_GB": round(resident * cb / 1e9, 1), "window_chunks": win,
+                   "chunks_spilled_total": st.evictions, "chunks_restored_total": st.fetches,
+                   "spill_GBps_incl_unmap": round(st.evictions * cb / (st.evict_ms * 1e6), 1) if st.evict_ms else None,
+                   "restore_GBps_incl_map": round(st.fetches * cb / (st.fetch_ms * 1e6), 1) if st.fetch_ms and st.fetches else None,
+                   "write_pass_GBps": round(total * cb / (t1 - t0) / 1e9, 1), "verify_pass_GBps": round(total * cb / (t2 - t1) / 1e9, 1),
+                   "bit_exact": True}
+        finally:
+            capi.lib.vgpu_vmem_destroy(h)
+            torch.cuda.empty_cache()
+    if ranks is not None:
+        ranks.barrier()
+    return out
+
+
+def config5_phase(args, capi, dp, torch, dev, local, world, ranks):
+    """Config 5 on every GPU at once: 10 vGPUs (10 % SM partitions) x 16 GiB memtest, concurrent with a
+    spill/restore loop on its own stream (whole GPU) to the next GPU in the ring, or to pinned host at N=1."""
+    cb = capi.CHUNK_BYTES
+    nv, per = 10, 16 * GIB
+    free, _ = torch.cuda.mem_get_info(dev)
+    if nv * per > free - 12 * GIB:
+        per = ((free - 12 * GIB) // nv) // cb * cb
+    bufs = [torch.empty(per, dtype=torch.uint8, device=dev) for _ in range(nv)]
+    parts = (capi.SmPartition * nv)()
+    capi.check(capi.lib.vgpu_sm_partition_create(local, 10, nv, parts))
+    streams = [torch.cuda.ExternalStream(p.stream, device=dev) for p in parts]
+    results = [torch.zeros(3, dtype=torch.int64, device=dev) for _ in range(nv)]
+    n = 1024
+    hbm = torch.empty(n * cb, dtype=torch.uint8, device=dev)
+    back = torch.empty_like(hbm)
+    dp.memtest_fill(hbm, capi.PAT_RANDOM, 77)
+    ck = torch.zeros((n, 2), dtype=torch.int64, device=dev)
+    rres = torch.zeros(2, dtype=torch.int64, device=dev)
+    slab = C.c_void_p()
+    if world > 1:
+        tier, peer = capi.TIER_PEER, ring_peer(local, world)
+    else:
+        tier, peer = capi.TIER_HOST, -1
+    capi.check(capi.lib.vgpu_slab_alloc(tier, local, peer, n * cb, C.byref(slab)))
+    xs = torch.cuda.Stream(device=dev)
+    xstream = C.c_void_p(xs.cuda_stream)
+    main = torch.cuda.current_stream()
+    reps_mt, reps_x = 2, (8 if world > 1 else 2)
+
+    def run(do_mt, do_x):
+        ranks.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ends = []
+        e0.record(main)
+        if do_mt:
+            for i, st in enumerate(streams):
+                st.wait_event(e0)
+                for s in range(reps_mt):
+                    for pat, p in ((capi.PAT_WALKING_ONES, s), (capi.PAT_RANDOM, s)):
+                        dp.memtest_fill(bufs[i], pat, p, stream=st)
+                        dp.memtest_verify(bufs[i], pat, p, result=results[i], stream=st)
+                e = torch.cuda.Event(); e.record(st); ends.append(e)
+        if do_x:
+            xs.wait_event(e0)
+            for _ in range(reps_x):
+                capi.check(capi.lib.vgpu_spill(capi.XFER_AUTO, tier, hbm.data_ptr(), slab, None, None, n, cb, ck.data_ptr(), xstream))
+                capi.check(capi.lib.vgpu_restore(capi.XFER_AUTO, tier, slab, back.data_ptr(), None, None, n, cb, ck.data_ptr(), None, rres.data_ptr(), xstream))
+            e = torch.cuda.Event(); e.record(xs); ends.append(e)
+        for e in ends:
+            main.wait_event(e)
+        e1.record(main)
+        torch.cuda.synchronize()
+        return ranks.max(e0.elapsed_time(e1))
+
+    run(True, True)  # warm-up
+    ms_both = run(True, True)
+    ms_mt = run(True, False)
+    ms_x = run(False, True)
+    ok = all(r.cpu().tolist() == [0, 0, 0] for r in results) and rres.cpu().tolist() == [0, 0] and torch.equal(back, hbm)
+    if not ok:
+        raise SystemExit("config 5: memtest mismatch or spill/restore round trip not bit-exact")
+    mt_bytes = world * nv * per * 2 * 2 * reps_mt
+    x_bytes = world * n * cb * 2 * reps_x
+    out = {"vgpus_per_gpu": nv, "vgpu_GiB": round(per / GIB, 2), "sm_per_vgpu": [p.sm_count for p in parts],
+           "spill_tier": "peer ring g->g+1 over NVLink" if world > 1 else "pinned host over PCIe", "spill_batch_chunks": n,
+           "concurrent": {"ms": round(ms_both, 2), "memtest_GBps": round(mt_bytes / (ms_both * 1e6), 1),
+                          "spill_plus_restore_GBps": round(x_bytes / (ms_both * 1e6), 1),
+                          "note": "both finish inside the same window; rates are bytes / window, so each is a lower bound"},
+           "memtest_alone_GBps": round(mt_bytes / (ms_mt * 1e6), 1), "spill_restore_alone_GBps": round(x_bytes / (ms_x * 1e6), 1),
+           "bit_exact": True}
+    torch.cuda.synchronize()
+    capi.lib.vgpu_sm_partition_destroy(parts, nv)
+    capi.lib.vgpu_slab_free(tier, local, peer, slab)
+    del bufs, hbm, back
+    torch.cuda.empty_cache()
+    return out
 
 
 def spill_sweep(args, capi, dp, torch, dev, local, world, barrier, max_over_ranks, sum_over_ranks):

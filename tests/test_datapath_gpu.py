@@ -291,6 +291,23 @@ def test_large_round_trip_properties(vgpu, cuda_dev):
     assert np.array_equal(xab, xa ^ xb)
 
 
+def test_first_launch_on_a_fresh_non_blocking_stream(vgpu, cuda_dev):
+    """The per-stream scratch is zeroed on the caller's stream: on a non-blocking stream (torch
+    streams, green-context streams) a legacy-stream memset would race with the first kernel."""
+    dp, capi = vgpu.datapath, vgpu.capi
+    cb, n = capi.CHUNK_BYTES, 512
+    src = torch.empty(n * cb, dtype=torch.uint8, device=cuda_dev)
+    dp.memtest_fill(src, capi.PAT_RANDOM, 31)
+    want = dp.checksum(src, n, cb)
+    torch.cuda.synchronize()
+    for _ in range(4):
+        st = torch.cuda.Stream(device=cuda_dev)          # cudaStreamNonBlocking
+        dst = torch.empty_like(src)
+        ck = dp.spill(src, dst, n, cb, variant=capi.XFER_LDST, stream=st)
+        st.synchronize()
+        assert torch.equal(ck, want) and torch.equal(dst, src)
+
+
 def test_argument_validation(vgpu, cuda_dev):
     capi = vgpu.capi
     a = torch.zeros(1 << 20, dtype=torch.uint8, device=cuda_dev)
