@@ -49,7 +49,7 @@ def parse():
                     help="also run BASELINE config 5 per GPU: 10 vGPUs x 16 GiB memtest in 10 %% SM partitions, concurrent with a "
                          "spill/restore loop (peer ring g->g+1 if --gpus >= 2, else pinned host)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--cpu-gib", type=float, default=2.0, help="host buffer of the CPU memtest sample")
+    ap.add_argument("--cpu-gib", type=float, default=4.0, help="host buffer of the CPU memtest sample")
     return ap.parse_args()
 
 
@@ -269,24 +269,21 @@ def main():
         partition = {"kind": "plain_streams", "why": capi.last_error() if args.partition == "green" else "--partition streams"}
     results = [torch.zeros(3, dtype=torch.int64, device=dev) for _ in range(nv)]
 
-    def step(s):
-        for i in range(nv):
-            st = streams[i]
-            for pat, p in ((capi.PAT_WALKING_ONES, s % 64), (capi.PAT_RANDOM, s)):
-                dp.memtest_fill(bufs[i], pat, p, stream=st)
-                dp.memtest_verify(bufs[i], pat, p, result=results[i], stream=st)
-
     main_stream = torch.cuda.current_stream()
 
-    def timed(nsteps, first):
+    def timed(nsteps, first, on=None):
+        sts = on or streams
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ends = [torch.cuda.Event() for _ in range(nv)]
         ev0.record(main_stream)
-        for st in streams:
+        for st in sts:
             st.wait_event(ev0)
         for s in range(first, first + nsteps):
-            step(s)
-        for st, e in zip(streams, ends):
+            for i in range(nv):
+                for pat, p in ((capi.PAT_WALKING_ONES, s % 64), (capi.PAT_RANDOM, s)):
+                    dp.memtest_fill(bufs[i], pat, p, stream=sts[i])
+                    dp.memtest_verify(bufs[i], pat, p, result=results[i], stream=sts[i])
+        for st, e in zip(sts, ends):
             e.record(st)
             main_stream.wait_event(e)
         ev1.record(main_stream)
@@ -310,6 +307,17 @@ def main():
     bytes_per_step_rank = 2 * per * 2 * nv  # (fill+verify) x 2 patterns x vGPUs
     value = whole_job_gbps(bytes_per_step_rank, args.steps, world, ms)
     launches = args.steps * nv * 4
+    # the same step without SM caps (plain streams sharing all SMs), for the record
+    uncapped = None
+    if rc == 0:
+        plain = [torch.cuda.Stream(device=dev) for _ in range(nv)]
+        timed(2, 0, plain)
+        barrier()
+        u0, u1 = timed(args.steps, args.warmup, plain)
+        barrier()
+        ums = max_over_ranks(u0.elapsed_time(u1))
+        uncapped = {"GBps": round(whole_job_gbps(bytes_per_step_rank, args.steps, world, ums), 2), "ms_per_step": round(ums / args.steps, 4),
+                    "note": "same buffers and kernels on plain streams: no green-context partition, all SMs shared"}
 
     # per-kernel durations, each timed alone on vGPU 0's stream (CUDA events on that stream)
     kern = {}
@@ -374,10 +382,10 @@ def main():
         cpu_base = None
         if not args.no_cpu:
             cores = len(os.sched_getaffinity(0))
-            v, sec = cpu_memtest_sample(args.cpu_gib, cores, passes_each=2)
+            v, sec = cpu_memtest_sample(args.cpu_gib, cores, passes_each=12)
             v1, _ = cpu_memtest_sample(min(args.cpu_gib, 0.5), 1)
             cpu_base = {"value": round(v, 3), "unit": "GB/s", "cores": cores, "kind": "port",
-                        "sample": f"oracle memtest, {args.cpu_gib} GiB host buffer, 2 walking-ones + 2 random passes ({sec:.1f} s)",
+                        "sample": f"oracle memtest, {args.cpu_gib} GiB host buffer, 12 walking-ones + 12 random passes ({sec:.1f} s)",
                         "one_thread_GBps": round(v1, 3),
                         "host_memcpy_spill_GBps": {"1_thread": round(cpu_spill_sample(64, 1), 2), f"{cores}_threads": round(cpu_spill_sample(256, cores), 2)}}
         line = {
@@ -398,7 +406,8 @@ def main():
                          "algorithmic_bytes_per_launch": per, "kernel": f"k_memtest_{dom} (whole GPU, timed alone)",
                          "peak_source": peak_src, "whole_gpu": whole, "one_partition": kern,
                          "step_aggregate": {"GBps": round(value / world, 1), "frac": round(value / world / hbm_peak, 4),
-                                            "frac_of_8TBps_spec": round(value / world / 8000.0, 4)}},
+                                            "frac_of_8TBps_spec": round(value / world / 8000.0, 4)},
+                         "step_aggregate_uncapped": uncapped},
             "cpu_baseline": cpu_base,
         }
         line.update(out_extra)

@@ -17,7 +17,7 @@ for rep in range(2):  # rep 0 = warm-up
     for pat in (capi.PAT_WALKING_ONES, capi.PAT_RANDOM):
         dp.memtest_fill(buf, pat, 1)
         dp.memtest_verify(buf, pat, 1, result=res)
-n = 512
+n = min(512, buf.numel() // (2 * capi.CHUNK_BYTES))
 src, dst = buf[: n * capi.CHUNK_BYTES], buf[n * capi.CHUNK_BYTES: 2 * n * capi.CHUNK_BYTES]
 for rep in range(2):
     for v in (capi.XFER_LDST, capi.XFER_TMA):
