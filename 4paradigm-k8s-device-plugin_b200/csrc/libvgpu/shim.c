@@ -510,6 +510,23 @@ EXPORT CUresult cuDeviceTotalMem_v2(size_t *bytes, CUdevice dev) {
 }
 EXPORT CUresult cuDeviceTotalMem(size_t *bytes, CUdevice dev) { return cuDeviceTotalMem_v2(bytes, dev); }
 
+/* cuPointerGetAttributes@0x33cf3 (a24): after the real call, IS_MANAGED (8) is forced to 0 so
+ * that frameworks do not notice the managed memory behind oversubscribed allocations. */
+EXPORT CUresult cuPointerGetAttributes(unsigned n, int *attrs, void **data, CUdeviceptr ptr) {
+    typedef CUresult (*fn_t)(unsigned, int *, void **, CUdeviceptr);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuPointerGetAttributes");
+    if (!tl_bypass) {
+        ensure_initialized();
+        wait_running();
+    }
+    CUresult rc = f ? f(n, attrs, data, ptr) : 3;
+    if (!tl_bypass)
+        for (unsigned i = 0; i < n; ++i)
+            if (attrs[i] == 8 && data[i]) *(unsigned *)data[i] = 0;
+    return rc;
+}
+
 /* host-memory hooks (a20): allocate first, then check_oom@0x311bd == oom_check(cur, 0) */
 EXPORT CUresult cuMemAllocHost_v2(void **pp, size_t n) {
     if (tl_bypass) return get_cuMemAllocHost_v2()(pp, n);
@@ -835,6 +852,7 @@ static const hook_t g_hooks[] = {
     {"cuCtxGetCurrent", (void *)cuCtxGetCurrent},
     {"cuCtxPopCurrent", (void *)cuCtxPopCurrent_v2}, {"cuCtxPopCurrent_v2", (void *)cuCtxPopCurrent_v2},
     {"cuCtxPushCurrent", (void *)cuCtxPushCurrent_v2}, {"cuCtxPushCurrent_v2", (void *)cuCtxPushCurrent_v2},
+    {"cuPointerGetAttributes", (void *)cuPointerGetAttributes},
     {"cuLaunchKernel", (void *)cuLaunchKernel},
     {"cuLaunchKernelEx", (void *)cuLaunchKernelEx},
     {"cuGetProcAddress", (void *)cuGetProcAddress}, {"cuGetProcAddress_v2", (void *)cuGetProcAddress_v2},

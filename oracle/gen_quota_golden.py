@@ -29,6 +29,8 @@ CASES = [
     ("appA_50m", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "50m"}, 1),
     ("appA_overflow", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "17179869184g"}, 1),
     ("appA_garbage", H.appendix_a_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "abc"}, 1),
+    ("sm_limits_per_device", H.golden_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", "CUDA_DEVICE_SM_LIMIT": "20", "CUDA_DEVICE_SM_LIMIT_0": "30",
+                                                "CUDA_DEVICE_SM_LIMIT_3": "0", "CUDA_TASK_PRIORITY": "0", **MAP}, 1),
     ("random_5EED_1p", H.random_trace(0x5EED, 10000), {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m", "CUDA_DEVICE_SM_LIMIT": "10", **MAP}, 1),
     ("random_5EED_1p_oversub", H.random_trace(0x5EED, 10000), {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m", "CUDA_DEVICE_SM_LIMIT": "10", "CUDA_OVERSUBSCRIBE": "true", **MAP}, 1),
     ("random_5EED_4p", H.random_trace(0x5EED + 1, 10000, 4), {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m", "CUDA_DEVICE_SM_LIMIT": "10", **MAP}, 4),

@@ -157,7 +157,8 @@ def random_trace(seed, nops, nprocs=1, max_bytes=1 << 30, kinds=True):
         p = rng.randrange(nprocs)
         r = rng.random()
         if kinds and r < 0.08:
-            out.append((p, rng.choice(["info", "info", "total 0", "nvmlmem"])))
+            q = rng.choice(["info", "info", "total 0", "nvmlmem", "ptrattrs"])
+            out.append((p, q if q != "ptrattrs" else f"ptrattrs {rng.choice(live[p]) if live[p] else 0}"))
             continue
         if r < 0.63 or not live[p]:
             size = int(math.exp(rng.uniform(lo, hi)))

@@ -54,7 +54,7 @@ static void cfg(void) {
 
 static void logf_(const char *fmt, ...) {
     const char *path = getenv("MOCK_CUDA_LOG");
-    if (!path) return;
+    if (!path || !*path) return;
     FILE *f = fopen(path, "a");
     if (!f) return;
     va_list ap;
@@ -177,6 +177,16 @@ CUresult cuMemRelease(unsigned long long h) { (void)h; return 0; }
 CUresult cuMemSetAccess(CUdeviceptr p, size_t n, const void *d, size_t c) { (void)p; (void)n; (void)d; (void)c; return 0; }
 CUresult cuMemUnmap(CUdeviceptr p, size_t n) { (void)p; (void)n; return 0; }
 CUresult cuPointerGetAttribute(void *data, int attr, CUdeviceptr p) { (void)p; if (attr == 8) *(unsigned *)data = 1; else memset(data, 0, 8); return 0; }
+CUresult cuPointerGetAttributes(unsigned n, int *attrs, void **data, CUdeviceptr p) {
+    (void)p;
+    for (unsigned i = 0; i < n; ++i) {
+        if (attrs[i] == 8) *(unsigned *)data[i] = 1;        /* IS_MANAGED: the mock says "managed" for everything */
+        else if (attrs[i] == 2) *(unsigned *)data[i] = 2;   /* MEMORY_TYPE: device */
+        else memset(data[i], 0, 4);
+    }
+    logf_("cuPointerGetAttributes n=%u", n);
+    return 0;
+}
 CUresult cuGetErrorString(CUresult e, const char **s) { (void)e; *s = "mock"; return 0; }
 CUresult cuGetErrorName(CUresult e, const char **s) { (void)e; *s = "MOCK"; return 0; }
 

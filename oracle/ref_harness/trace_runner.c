@@ -13,6 +13,8 @@
  *   freehost <tag>         cuMemFreeHost                  -> rc
  *   launch <grid> <block>  cuLaunchKernel                 -> rc
  *   nvmlmem                nvmlDeviceGetMemoryInfo(dev0)  -> rc total free used
+ *   ptrattrs <tag>         cuPointerGetAttributes{MEMORY_TYPE, IS_MANAGED} -> rc type managed
+ *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
  *   quit
  */
 #define _GNU_SOURCE
@@ -20,6 +22,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 typedef int CUresult;
 typedef unsigned long long CUdeviceptr;
@@ -33,6 +36,7 @@ CUresult cuMemAllocPitch_v2(CUdeviceptr *, size_t *, size_t, size_t, unsigned);
 CUresult cuMemFree_v2(CUdeviceptr);
 CUresult cuMemAllocHost_v2(void **, size_t);
 CUresult cuMemFreeHost(void *);
+CUresult cuPointerGetAttributes(unsigned, int *, void **, CUdeviceptr);
 CUresult cuLaunchKernel(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **);
 
 #define MAXTAG 200000
@@ -91,6 +95,25 @@ int main(void) {
         } else if (!strcmp(op, "launch")) {
             rc = cuLaunchKernel(NULL, (unsigned)a, 1, 1, (unsigned)b, 1, 1, 0, NULL, NULL, NULL);
             printf("%d\n", rc);
+        } else if (!strcmp(op, "loop")) {
+            struct timespec t0, t1;
+            size_t f = 0, t = 0;
+            CUdeviceptr p = 0;
+            rc = 0;
+            clock_gettime(CLOCK_MONOTONIC, &t0);
+            for (unsigned long long i = 0; i < a; ++i) {
+                rc |= cuMemAlloc_v2(&p, (size_t)b);
+                rc |= cuMemGetInfo_v2(&f, &t);
+                rc |= cuMemFree_v2(p);
+            }
+            clock_gettime(CLOCK_MONOTONIC, &t1);
+            printf("%d %lld\n", rc, (long long)(t1.tv_sec - t0.tv_sec) * 1000000000LL + (t1.tv_nsec - t0.tv_nsec));
+        } else if (!strcmp(op, "ptrattrs")) {
+            int attrs[2] = {2, 8};
+            unsigned type = 99, managed = 99;
+            void *data[2] = {&type, &managed};
+            rc = cuPointerGetAttributes(2, attrs, data, a < MAXTAG ? tags[a] : 0);
+            printf("%d %u %u\n", rc, type, managed);
         } else if (!strcmp(op, "nvmlmem")) {
             typedef int (*init_t)(void);
             typedef int (*byidx_t)(unsigned, void **);
