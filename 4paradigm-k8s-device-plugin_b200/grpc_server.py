@@ -160,6 +160,15 @@ def enc_allocate_response(resps: Iterable[P.ContainerAllocateResponse]) -> bytes
     return out
 
 
+def enc_allocate_container(r: P.ContainerAllocateResponse) -> bytes:
+    """One ContainerAllocateResponse (what the kubelet stores as AllocResp in its checkpoint)."""
+    return parse(enc_allocate_response([r]))[0][2]
+
+
+def dec_allocate_container(v: bytes) -> dict:
+    return dec_allocate_response(_f_bytes(1, v))[0]
+
+
 def dec_allocate_response(b: bytes) -> List[dict]:
     out = []
     for f, _, v in parse(b):

@@ -174,6 +174,93 @@ def simplePolicy(available: List[str], required: List[str], size: int) -> List[s
     return chosen
 
 
+# vdevice-controller.go:25-30
+annRequest = "4paradigm.com/vgpu-request"
+annUsing = "4paradigm.com/vgpu-using"
+annSep = ","
+kubeletDeviceManagerCheckpoint = "kubelet_internal_checkpoint"
+
+
+class VDeviceController:
+    """vdevice-controller.go:32-286 — the legacy preferred-allocation bookkeeping used with
+    --enable-legacy-preferred: idMap[vdevID] -> the request id it was handed out for ("" = free).
+    The pod lister and the kubelet checkpoint are injected (a fake lister and a checkpoint file in
+    tests); the kubelet's checkpoint checksum (a Go spew/fnv object hash) is not verified."""
+
+    def __init__(self, deviceIDs: Sequence[str], podLister: Optional[Callable[[], List[dict]]] = None,
+                 checkpointDir: str = DevicePluginPath):
+        self.idMap: Dict[str, str] = {v: "" for v in deviceIDs}   # insertion-ordered; Go's map order is random
+        self.podLister = podLister or (lambda: [])
+        self.checkpointDir = checkpointDir
+
+    # vdevice-controller.go:231-243
+    def available(self) -> List[str]:
+        return [k for k, v in self.idMap.items() if v == ""]
+
+    # vdevice-controller.go:246-261
+    def acquire(self, request: Sequence[str], using: Sequence[str]) -> None:
+        for i, v in enumerate(using):
+            if v not in self.idMap:
+                continue  # "Error: device %s unknown"
+            self.idMap[v] = request[i] if i < len(request) else "mismatched"
+
+    # vdevice-controller.go:264-274
+    def release(self, using: Sequence[str]) -> None:
+        for v in using:
+            if v in self.idMap:
+                self.idMap[v] = ""
+
+    # vdevice-controller.go:277-286
+    def releaseByRequest(self, request: Sequence[str]) -> None:
+        for k, v in self.idMap.items():
+            for r in request:
+                if v == r:          # "Error: device %s[%s] loss."
+                    self.idMap[k] = ""
+
+    # vdevice-controller.go:60-111
+    def updateFromCheckpoint(self) -> None:
+        import base64
+        import json
+        import os
+        from . import grpc_server as G
+        path = os.path.join(self.checkpointDir, kubeletDeviceManagerCheckpoint)
+        try:
+            cp = json.load(open(path))
+        except (OSError, ValueError) as e:
+            raise PluginError(f"read checkpoint error, {e}")
+        pods = self.podLister()
+        for pde in (cp.get("Data") or {}).get("PodDeviceEntries") or []:
+            if pde.get("ResourceName") != "nvidia.com/gpu":
+                continue
+            try:
+                resp = G.dec_allocate_container(base64.b64decode(pde.get("AllocResp") or ""))
+            except Exception:
+                continue  # "unmarshal container allocate response failed"
+            requestStr = resp["Annotations"].get(annRequest, "")
+            usingStr = resp["Annotations"].get(annUsing, "")
+            if requestStr == "" and usingStr == "":
+                continue
+            request, using = requestStr.split(annSep), usingStr.split(annSep)
+            pod = next((p for p in pods if p.get("uid") == pde.get("PodUID")), None)
+            if pod is not None and pod.get("phase") in ("Pending", "Running"):
+                self.acquire(request, using)
+            else:
+                self.release(using)
+
+    # vdevice-controller.go:114-159 (informer callbacks; dormant in the reference, kept for the mirror)
+    def onAddPod(self, pod: dict) -> None:
+        ann = pod.get("annotations", {})
+        requestStr, usingStr = ann.get(annRequest, ""), ann.get(annUsing, "")
+        if requestStr == "" and usingStr == "":
+            return
+        self.acquire(requestStr.split(annSep), usingStr.split(annSep))
+
+    def onDeletePod(self, pod: dict) -> None:
+        usingStr = pod.get("annotations", {}).get(annUsing, "")
+        if usingStr:
+            self.release(usingStr.split(annSep))
+
+
 class ResourceManager:
     """nvidia.go:43-46; here a list supplied by the caller (a mock NVML in tests)."""
 
@@ -198,7 +285,9 @@ class NvidiaDevicePlugin:
         self.flags = flags or Flags()
         validateFlags(self.flags)
         self.migStrategy = self.flags.migStrategy
-        self.vDeviceController = None  # legacy mode: out of scope
+        self.vDeviceController: Optional["VDeviceController"] = None  # --enable-legacy-preferred
+        self._podLister: Optional[Callable[[], List[dict]]] = None     # injected: client-go lister stand-in
+        self._checkpointDir = DevicePluginPath
         self.cachedDevices: List[Device] = []
         self.vDevices: List[VDevice] = []
         self._health_events: List[Device] = []
@@ -207,6 +296,8 @@ class NvidiaDevicePlugin:
     def initialize(self) -> None:
         self.cachedDevices = self.resourceManager.Devices()
         self.vDevices = Device2VDevice(self.cachedDevices, self.flags)
+        if self.flags.enableLegacyPreferred:  # server.go:104-111
+            self.vDeviceController = VDeviceController([vd.ID for vd in self.vDevices], self._podLister, self._checkpointDir)
 
     # server.go:221-243 — what Register sends to kubelet
     def Register(self) -> dict:
@@ -286,8 +377,23 @@ class NvidiaDevicePlugin:
         phys_uuid = (C.c_char_p * max(1, n_phys))(*[d.ID.encode() for d in self.cachedDevices])
         phys_idx = (C.c_char_p * max(1, n_phys))(*[d.Index.encode() for d in self.cachedDevices])
         responses = []
+        if self.vDeviceController is not None:
+            self.vDeviceController.updateFromCheckpoint()  # server.go:408-413: release devices of finished pods
         for ids in containerRequests:
-            vdevices = VDevicesByIDs(self.vDevices, list(ids))
+            reqDeviceIDs = list(ids)
+            if self.vDeviceController is not None:  # server.go:433-457
+                c = self.vDeviceController
+                c.releaseByRequest(ids)  # "fix kubelet shutdown after Allocate"
+                availableIds = c.available()
+                if len(availableIds) < len(ids):
+                    raise PluginError("no enough devices")
+                pref = self.GetPreferredAllocation([{"AllocationSize": len(ids), "AvailableDeviceIDs": availableIds}])
+                if pref is not None and len(pref[0]) == len(ids):
+                    reqDeviceIDs = pref[0]
+                else:
+                    reqDeviceIDs = availableIds[0:len(ids)]  # "Warn: get preferred failed"
+                c.acquire(ids, reqDeviceIDs)
+            vdevices = VDevicesByIDs(self.vDevices, reqDeviceIDs)
             req = (C.POINTER(capi.Desc) * max(1, len(vdevices)))(*[C.pointer(vd._desc) for vd in vdevices])
             envs = (capi.KV * 64)()
             mounts = (capi.Mount * 64)()
@@ -302,6 +408,10 @@ class NvidiaDevicePlugin:
                 resp.Mounts.append(Mount(mounts[i].container_path.decode(), mounts[i].host_path.decode(), bool(mounts[i].read_only)))
             if f.passDeviceSpecs:
                 resp.Devices = self.apiDeviceSpecs(f.nvidiaDriverRoot, UniqueDeviceIDs(vdevices))
+            if self.vDeviceController is not None:  # server.go:480-485
+                resp.Annotations[annRequest] = annSep.join(ids)
+                resp.Annotations[annUsing] = annSep.join(reqDeviceIDs)
+                self.vDeviceController.acquire(ids, reqDeviceIDs)
             responses.append(resp)
         return responses
 
