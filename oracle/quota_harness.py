@@ -43,8 +43,10 @@ def _env(lib, cache, extra, mock_log):
     return env
 
 
-def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True):
-    """-> dict(replies=[str...] in trace order, oom=[(dev,need,limit)...], calls=[str...], region=bytes)"""
+def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False):
+    """-> dict(replies=[str...] in trace order, oom=[(dev,need,limit)...], calls=[str...], region=bytes)
+    `lib` may be a list with one library per process (old and new library sharing one cache file).
+    parallel=True sends every op before reading any reply (processes really run concurrently)."""
     os.makedirs("/tmp/vgpulock", exist_ok=True)  # the reference spins forever without this dir
     try:
         os.unlink("/tmp/vgpulock/lock")
@@ -58,12 +60,23 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True):
         replies = []
         try:
             for p in range(nprocs):
+                plib = lib[p] if isinstance(lib, (list, tuple)) else lib
                 pr = subprocess.Popen([os.path.join(REF_DIR, "trace_runner")], stdin=subprocess.PIPE, stdout=subprocess.PIPE,
-                                      stderr=errs[p], env=_env(lib, cache, env_extra, mock_log), text=True, bufsize=1)
+                                      stderr=errs[p], env=_env(plib, cache, env_extra, mock_log), text=True, bufsize=1)
                 first = pr.stdout.readline().strip()  # "init <rc>"
                 if not first.startswith("init"):
                     raise RuntimeError(f"runner {p} did not start: {first!r}")
                 procs.append(pr)
+            if parallel:
+                for p, op in trace:
+                    procs[p].stdin.write(op + "\n")
+                    procs[p].stdin.flush()
+                for p, op in trace:
+                    line = procs[p].stdout.readline()
+                    if not line:
+                        raise RuntimeError(f"runner {p} died on {op!r}")
+                    replies.append(line.strip())
+                trace = []
             for p, op in trace:
                 procs[p].stdin.write(op + "\n")
                 procs[p].stdin.flush()

@@ -134,6 +134,45 @@ def test_live_differential_against_reference_binary(seed, nprocs, env):
     assert H.mask_region(a["region"]) == H.mask_region(b["region"]), "final shared-cache bytes differ"
 
 
+def _slots_clean(region):
+    """(proc_num, no live slot holds memory).  Slots beyond proc_num may hold stale bytes: the exit
+    handler moves the last slot into the leaver's and does not wipe the source (as in the reference)."""
+    proc_num = struct.unpack_from("<i", region, 0xC4738)[0]
+    used = [struct.unpack_from("<80Q", region, 0x738 + 0x310 * s + 8) for s in range(proc_num)]
+    return proc_num, all(not any(u) for u in used)
+
+
+def test_eight_processes_hammer_one_cache_file_concurrently():
+    """Not lock-step: 8 processes x 20 000 alloc/info/free triples at once on one shared cache.
+    The semaphore protocol must neither deadlock nor lose a counter update."""
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "18432m", "MOCK_CUDA_LOG": "", **MAP}
+    r = H.run_trace(H.NEW_LIB, [(p, "loop 20000 1048576") for p in range(8)], env, nprocs=8, parallel=True)
+    assert all(x.split()[0] == "0" for x in r["replies"])
+    assert _slots_clean(r["region"]) == (0, True)
+
+
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+def test_old_and_new_library_share_one_cache_file():
+    """Contract C interop: processes preloading the reference binary and processes preloading the new
+    shim attach to the same file, see each other's usage, and leave it clean."""
+    MiB = 1 << 20
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", **MAP}
+    libs = [H.REFERENCE_LIB, H.NEW_LIB, H.REFERENCE_LIB, H.NEW_LIB]
+    trace = [(0, f"alloc {300 * MiB} 1"), (1, f"alloc {200 * MiB} 1"), (2, "info"), (3, "info"),
+             (2, f"alloc {400 * MiB} 1"), (3, f"alloc {200 * MiB} 1"),      # 300+200+400 = 900; +200 > 1024 -> OOM in the new lib
+             (1, f"managed {200 * MiB} 2"), (0, "free 1"), (1, "info"), (3, f"alloc {200 * MiB} 2"), (0, "info")]
+    r = H.run_trace(libs, trace, env, nprocs=4)
+    free_after_two = str((1024 - 500) * MiB)
+    assert r["replies"][2].split()[1] == free_after_two and r["replies"][3].split()[1] == free_after_two
+    assert r["replies"][4] == "0" and r["replies"][5] == "-1" and r["replies"][6] == "2"
+    assert r["replies"][8].split()[1] == str((1024 - 600) * MiB)
+    assert r["replies"][9] == "0" and r["replies"][10].split()[1] == str((1024 - 800) * MiB)
+    assert _slots_clean(r["region"]) == (0, True)
+    # and a concurrent mixed hammer
+    r = H.run_trace(libs, [(p, "loop 5000 1048576") for p in range(4)], {**env, "MOCK_CUDA_LOG": ""}, nprocs=4, parallel=True)
+    assert all(x.split()[0] == "0" for x in r["replies"]) and _slots_clean(r["region"]) == (0, True)
+
+
 def test_shim_exports_the_hooked_driver_symbols():
     import subprocess
     out = subprocess.run(["nm", "-D", "--defined-only", H.NEW_LIB], capture_output=True, text=True).stdout
