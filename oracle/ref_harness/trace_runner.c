@@ -14,6 +14,7 @@
  *   launch <grid> <block>  cuLaunchKernel                 -> rc
  *   nvmlmem                nvmlDeviceGetMemoryInfo(dev0)  -> rc total free used
  *   ptrattrs <tag>         cuPointerGetAttributes{MEMORY_TYPE, IS_MANAGED} -> rc type managed
+ *   setdev <d>             cuDevicePrimaryCtxRetain(d) + cuCtxSetCurrent   -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
  *   quit
  */
@@ -37,6 +38,8 @@ CUresult cuMemFree_v2(CUdeviceptr);
 CUresult cuMemAllocHost_v2(void **, size_t);
 CUresult cuMemFreeHost(void *);
 CUresult cuPointerGetAttributes(unsigned, int *, void **, CUdeviceptr);
+CUresult cuDevicePrimaryCtxRetain(void **, int);
+CUresult cuCtxSetCurrent(void *);
 CUresult cuLaunchKernel(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **);
 
 #define MAXTAG 200000
@@ -94,6 +97,11 @@ int main(void) {
             printf("%d\n", rc);
         } else if (!strcmp(op, "launch")) {
             rc = cuLaunchKernel(NULL, (unsigned)a, 1, 1, (unsigned)b, 1, 1, 0, NULL, NULL, NULL);
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "setdev")) {
+            void *ctx = NULL;
+            rc = cuDevicePrimaryCtxRetain(&ctx, (int)a);
+            if (rc == 0) rc = cuCtxSetCurrent(ctx);
             printf("%d\n", rc);
         } else if (!strcmp(op, "loop")) {
             struct timespec t0, t1;

@@ -173,6 +173,31 @@ def test_old_and_new_library_share_one_cache_file():
     assert all(x.split()[0] == "0" for x in r["replies"]) and _slots_clean(r["region"]) == (0, True)
 
 
+def test_two_devices_in_one_container_have_separate_limits_and_usage():
+    """A container holding vGPUs of two physical GPUs: CUDA_DEVICE_MEMORY_LIMIT_0/_1 and
+    NVIDIA_DEVICE_MAP "0:<A> 1:<B>" (server.go:487-493).  New shim only: the reference's device
+    remap layer rejects contexts under the mock ("Ctx Not Found"), so this row has no live oracle;
+    expectations follow Appendix B (limit[d], usage(d) per device index)."""
+    MiB = 1 << 20
+    U2 = "GPU-00000000-0000-0000-0000-000000000002"
+    env = {"MOCK_GPU_COUNT": "2", "CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", "CUDA_DEVICE_MEMORY_LIMIT_1": "512m",
+           "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{U2}"}
+    tr = [(0, "setdev 0"), (0, f"alloc {600 * MiB} 1"), (0, "info"), (0, "setdev 1"), (0, "info"), (0, f"alloc {600 * MiB} 2"),
+          (0, f"alloc {300 * MiB} 3"), (0, "info"), (0, "total 1"), (0, "total 0"), (0, "setdev 0"), (0, "info"), (0, "free 3"),
+          (0, "setdev 1"), (0, "info")]
+    r = H.run_trace(H.NEW_LIB, tr, env)
+    rep = r["replies"]
+    assert rep[2] == f"0 {424 * MiB} {1024 * MiB}"            # device 0: 1024 - 600
+    assert rep[4] == f"0 {512 * MiB} {512 * MiB}"             # device 1 untouched
+    assert rep[5] == "-1" and r["oom"] == [(1, 600 * MiB, 512 * MiB)]   # 600 MiB does not fit device 1's 512 MiB
+    assert rep[6] == "0" and rep[7] == f"0 {212 * MiB} {512 * MiB}"
+    assert rep[8] == f"0 {512 * MiB}" and rep[9] == f"0 {1024 * MiB}"  # cuDeviceTotalMem per device
+    assert rep[11] == f"0 {424 * MiB} {1024 * MiB}"           # back on device 0: unchanged by device 1's allocation
+    assert rep[12] == "0" and rep[14] == f"0 {512 * MiB} {512 * MiB}"
+    s = H.region_summary(r["region"])
+    assert s["device_num"] == 2 and s["limit"][:3] == [1024 * MiB, 512 * MiB, 0]
+
+
 def test_shim_exports_the_hooked_driver_symbols():
     import subprocess
     out = subprocess.run(["nm", "-D", "--defined-only", H.NEW_LIB], capture_output=True, text=True).stdout
