@@ -193,7 +193,7 @@ int vgpu_policy_set(int tier, size_t min_chunks, int variant);
  *  VMM branch (@0x3225f-0x322a0, cuMapMemory@0x31b28 / cuUnmapMemory@0x37f8f,
  *  whose helpers are undefined symbols in the shipped binary): the range is
  *  reserved with cuMemAddressReserve, backed per 2 MiB chunk with
- *  cuMemCreate/cuMemMap in blocks of 128 chunks (256 MiB; VMM driver calls cost
+ *  cuMemCreate/cuMemMap in blocks of up to 512 chunks (1 GiB; VMM driver calls cost
  *  ~0.1-0.3 ms each whatever their size), and chunks move to/from the spill tier
  *  with the kernels above while the application's pointers stay valid.
  *  Residency is tracked per block: chunk ranges are rounded out to blocks.
