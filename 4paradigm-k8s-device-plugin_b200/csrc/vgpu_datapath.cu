@@ -139,7 +139,8 @@ int policy_lookup(int tier, size_t nchunks) {
 
 // ---- transfer launch --------------------------------------------------------
 constexpr int kLdstU = 4;                   // 4 x 32 B per thread in flight => 32 KiB tiles
-constexpr int kTmaTile = 16384, kTmaStages = 4, kTmaThreads = 128;
+constexpr int kTmaTile = 32768, kTmaStages = 3, kTmaThreads = 256;  // 96 KiB ring, 2 CTAs/SM: best of the shapes swept
+constexpr int kTmaGridMult = 16;  // CTAs per launch = resident CTAs x 16 (grid-stride over the rest)
 
 // CTAs per launch of the LD/ST copy variant: a grid-stride loop over 32 KiB tiles with
 // 32 CTAs per SM (4 waves of the 8 resident).  Unlike the write-only / read-only memtest
@@ -243,18 +244,30 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
         else if (copy) k_xfer_ldst<kLdstU, true><<<grid, kXfThreads, 0, st>>>(a);
         else k_xfer_ldst<kLdstU, false><<<grid, kXfThreads, 0, st>>>(a);
     } else {  // VGPU_XFER_TMA
-        a.tiles_per_chunk = (uint32_t)((chunk_bytes + kTmaTile - 1) / kTmaTile);
-        const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
-        constexpr size_t smem = (size_t)kTmaTile * kTmaStages;
-        auto kfn = k_xfer_tma<kTmaTile, kTmaStages, kTmaThreads, true>;
-        static bool attr_done[kMaxDev] = {false};
-        if (!attr_done[dev]) {
+        // ring shape: VGPU_TMA_CFG selects among the instantiations below (experiments); default = kTma*
+        static const int cfg = [] { const char *e = getenv("VGPU_TMA_CFG"); return e ? atoi(e) : 0; }();
+        auto go = [&](auto kfn, int tile, int stages, int threads) -> int {
+            a.tiles_per_chunk = (uint32_t)((chunk_bytes + tile - 1) / tile);
+            const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
+            const size_t smem = (size_t)tile * stages;
             VGPU_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr_done[dev] = true;
+            const unsigned per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>((220 * 1024) / (smem + 1024), 2048 / threads));
+            static const int mult = [] { const char *e = getenv("VGPU_TMA_GRID_MULT"); return e ? atoi(e) : kTmaGridMult; }();
+            const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * per_sm * mult);
+            kfn<<<grid, threads, smem, st>>>(a);
+            return VGPU_OK;
+        };
+        int rc;
+        switch (cfg) {
+            case 1: rc = go(k_xfer_tma<32768, 4, 256, true>, 32768, 4, 256); break;
+            case 2: rc = go(k_xfer_tma<16384, 4, 128, true>, 16384, 4, 128); break;
+            case 3: rc = go(k_xfer_tma<65536, 3, 256, true>, 65536, 3, 256); break;
+            case 4: rc = go(k_xfer_tma<8192, 8, 128, true>, 8192, 8, 128); break;
+            case 5: rc = go(k_xfer_tma<16384, 6, 128, true>, 16384, 6, 128); break;
+            case 6: rc = go(k_xfer_tma<32768, 6, 128, true>, 32768, 6, 128); break;
+            default: rc = go(k_xfer_tma<kTmaTile, kTmaStages, kTmaThreads, true>, kTmaTile, kTmaStages, kTmaThreads); break;
         }
-        const unsigned per_sm = (unsigned)std::max<size_t>(1, (220 * 1024) / (smem + 1024));
-        const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * per_sm);
-        kfn<<<grid, kTmaThreads, smem, st>>>(a);
+        if (rc) return rc;
     }
     VGPU_CUDA(cudaGetLastError());
     return VGPU_OK;
