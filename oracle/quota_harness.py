@@ -185,7 +185,8 @@ def random_trace(seed, nops, nprocs=1, max_bytes=1 << 30, kinds=True):
                 h = rng.randrange(1, 1 << 10)
                 out.append((p, f"pitch {w} {h} {rng.choice([4, 8, 16])} {tag}"))
             elif k < 0.15:
-                out.append((p, f"hostalloc {min(size, 1 << 20)} {tag}"))
+                hop = rng.choice(["hostalloc", "hostalloc2", "hostreg"])
+                out.append((p, f"{hop} {min(size, 1 << 20)}" + ("" if hop == "hostreg" else f" {tag}")))
                 continue  # host memory: not tracked as live device memory
             else:
                 out.append((p, f"alloc {size} {tag}"))

@@ -96,10 +96,12 @@ class Model:
             return "0"
         if k == "freeptr":
             return "0" if int(t[1], 0) == 0 else "-1"
-        if k == "hostalloc":
-            self.calls.append(f"cuMemAllocHost_v2 size={int(t[1], 0)}")
+        if k in ("hostalloc", "hostalloc2"):
+            self.calls.append(f"{'cuMemAllocHost_v2' if k == 'hostalloc' else 'cuMemHostAlloc'} size={int(t[1], 0)}")
             if self._oom(0):
                 self.calls.append("cuMemFreeHost")
                 return "2"
             return "0"
+        if k == "hostreg":
+            return "2" if self._oom(0) else "0"   # the mock does not log register / unregister
         raise ValueError(line)

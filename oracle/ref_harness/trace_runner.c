@@ -10,6 +10,8 @@
  *   free <tag>             cuMemFree_v2(ptr of tag)       -> rc
  *   freeptr <hex>          cuMemFree_v2(raw value)        -> rc
  *   hostalloc <bytes> <tag> cuMemAllocHost_v2             -> rc
+ *   hostalloc2 <bytes> <tag> cuMemHostAlloc(flags=0)      -> rc
+ *   hostreg <bytes>        cuMemHostRegister_v2 of a malloc'd block (unregistered + freed again) -> rc
  *   freehost <tag>         cuMemFreeHost                  -> rc
  *   launch <grid> <block>  cuLaunchKernel                 -> rc
  *   nvmlmem                nvmlDeviceGetMemoryInfo(dev0)  -> rc total free used
@@ -37,6 +39,9 @@ CUresult cuMemAllocPitch_v2(CUdeviceptr *, size_t *, size_t, size_t, unsigned);
 CUresult cuMemFree_v2(CUdeviceptr);
 CUresult cuMemAllocHost_v2(void **, size_t);
 CUresult cuMemFreeHost(void *);
+CUresult cuMemHostAlloc(void **, size_t, unsigned);
+CUresult cuMemHostRegister_v2(void *, size_t, unsigned);
+CUresult cuMemHostUnregister(void *);
 CUresult cuPointerGetAttributes(unsigned, int *, void **, CUdeviceptr);
 CUresult cuDevicePrimaryCtxRetain(void **, int);
 CUresult cuCtxSetCurrent(void *);
@@ -91,6 +96,17 @@ int main(void) {
             void *p = NULL;
             rc = cuMemAllocHost_v2(&p, (size_t)a);
             if (rc == 0 && b < MAXTAG) htags[b] = p;
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "hostalloc2")) {
+            void *p = NULL;
+            rc = cuMemHostAlloc(&p, (size_t)a, 0);
+            if (rc == 0 && b < MAXTAG) htags[b] = p;
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "hostreg")) {
+            void *p = malloc(a ? (size_t)a : 1);
+            rc = cuMemHostRegister_v2(p, (size_t)a, 0);
+            if (rc == 0) cuMemHostUnregister(p);
+            free(p);
             printf("%d\n", rc);
         } else if (!strcmp(op, "freehost")) {
             rc = cuMemFreeHost(a < MAXTAG ? htags[a] : NULL);

@@ -308,6 +308,26 @@ def test_first_launch_on_a_fresh_non_blocking_stream(vgpu, cuda_dev):
         assert torch.equal(ck, want) and torch.equal(dst, src)
 
 
+def test_calibrate_fills_the_auto_policy_from_measurements(vgpu, cuda_dev):
+    """vgpu_calibrate times the three variants on this box and rewrites the AUTO table
+    ("switch to the copy engine when measured bandwidth favours it")."""
+    capi, dp = vgpu.capi, vgpu.datapath
+    for tier in (capi.TIER_LOCAL, capi.TIER_HOST):
+        assert capi.lib.vgpu_calibrate(0, tier, -1, 64) == 0, capi.last_error()
+        for n in (1, 8, 64, 4096):
+            assert capi.lib.vgpu_policy_get(tier, n) in (capi.XFER_LDST, capi.XFER_TMA, capi.XFER_CE)
+    # whatever was chosen, AUTO still moves bytes exactly
+    cb, n = capi.CHUNK_BYTES, 64
+    src = torch.empty(n * cb, dtype=torch.uint8, device=cuda_dev)
+    dp.memtest_fill(src, capi.PAT_RANDOM, 3)
+    dst = torch.zeros_like(src)
+    ck = dp.spill(src, dst, n, cb, variant=capi.XFER_AUTO)
+    assert torch.equal(dst, src) and torch.equal(ck, dp.checksum(src, n, cb))
+    # explicit rules win over measured ones
+    assert capi.lib.vgpu_policy_set(capi.TIER_HOST, 8, capi.XFER_CE) == 0
+    assert capi.lib.vgpu_policy_get(capi.TIER_HOST, 100) == capi.XFER_CE
+
+
 def test_argument_validation(vgpu, cuda_dev):
     capi = vgpu.capi
     a = torch.zeros(1 << 20, dtype=torch.uint8, device=cuda_dev)
