@@ -198,6 +198,46 @@ def test_two_devices_in_one_container_have_separate_limits_and_usage():
     assert s["device_num"] == 2 and s["limit"][:3] == [1024 * MiB, 512 * MiB, 0]
 
 
+def test_monitor_reads_a_live_cache_file(vgpu):
+    """The external-agent view (monitor.py) of a cache two live processes are attached to."""
+    import subprocess
+    import tempfile
+    from vgpu_b200 import monitor
+    MiB = 1 << 20
+    td = tempfile.mkdtemp(prefix="mon")
+    cache = os.path.join(td, "shr.cache")
+    env = H._env(H.NEW_LIB, cache, {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", "CUDA_DEVICE_SM_LIMIT": "25", **MAP}, os.path.join(td, "mock.log"))
+    procs = [subprocess.Popen([os.path.join(H.REF_DIR, "trace_runner")], stdin=subprocess.PIPE, stdout=subprocess.PIPE,
+                              stderr=subprocess.DEVNULL, env=env, text=True, bufsize=1) for _ in range(2)]
+    try:
+        for i, p in enumerate(procs):
+            assert p.stdout.readline().startswith("init")
+            p.stdin.write(f"alloc {(100 + 50 * i) * MiB} 1\n"); p.stdin.flush()
+            assert p.stdout.readline().strip() == "0"
+        r = monitor.read_region(cache)
+        assert r["device_num"] == 1 and r["uuids"] == [H.UUID0] and r["limit"] == [1024 * MiB] and r["sm_limit"] == [25]
+        assert r["proc_num"] == 2 and sorted(p["pid"] for p in r["procs"]) == sorted(p.pid for p in procs)
+        assert sorted(p["used"][0]["total"] for p in r["procs"]) == [100 * MiB, 150 * MiB] and r["usage"] == [250 * MiB]
+        assert all(p["status"] == 1 for p in r["procs"])
+        monitor.suspend(cache)                      # SIGUSR2 -> status 2 in every slot
+        import time
+        for _ in range(50):
+            if all(p["status"] == 2 for p in monitor.read_region(cache)["procs"]):
+                break
+            time.sleep(0.05)
+        assert all(p["status"] == 2 for p in monitor.read_region(cache)["procs"])
+        monitor.resume(cache)
+        for _ in range(50):
+            if all(p["status"] == 1 for p in monitor.read_region(cache)["procs"]):
+                break
+            time.sleep(0.05)
+        assert all(p["status"] == 1 for p in monitor.read_region(cache)["procs"])
+    finally:
+        for p in procs:
+            p.stdin.write("quit\n"); p.stdin.flush(); p.wait(timeout=20)
+    assert monitor.read_region(cache)["proc_num"] == 0
+
+
 def test_shim_exports_the_hooked_driver_symbols():
     import subprocess
     out = subprocess.run(["nm", "-D", "--defined-only", H.NEW_LIB], capture_output=True, text=True).stdout
