@@ -234,40 +234,25 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
     }
 
     if (variant == VGPU_XFER_LDST || !copy) {
-        static const int u_exp = [] { const char *e = getenv("VGPU_XFER_U"); return e ? atoi(e) : kLdstU; }();
-        const uint32_t tile = u_exp == 8 ? LdstTile<8>::bytes : u_exp == 2 ? LdstTile<2>::bytes : LdstTile<kLdstU>::bytes;
+        constexpr uint32_t tile = LdstTile<kLdstU>::bytes;
         a.tiles_per_chunk = (uint32_t)((chunk_bytes + tile - 1) / tile);
         const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
         const unsigned grid = (unsigned)std::min<uint64_t>(total, ldst_grid_cap(sms));
-        if (copy && u_exp == 8) k_xfer_ldst<8, true><<<grid, kXfThreads, 0, st>>>(a);
-        else if (copy && u_exp == 2) k_xfer_ldst<2, true><<<grid, kXfThreads, 0, st>>>(a);
-        else if (copy) k_xfer_ldst<kLdstU, true><<<grid, kXfThreads, 0, st>>>(a);
+        if (copy) k_xfer_ldst<kLdstU, true><<<grid, kXfThreads, 0, st>>>(a);
         else k_xfer_ldst<kLdstU, false><<<grid, kXfThreads, 0, st>>>(a);
     } else {  // VGPU_XFER_TMA
-        // ring shape: VGPU_TMA_CFG selects among the instantiations below (experiments); default = kTma*
-        static const int cfg = [] { const char *e = getenv("VGPU_TMA_CFG"); return e ? atoi(e) : 0; }();
-        auto go = [&](auto kfn, int tile, int stages, int threads) -> int {
-            a.tiles_per_chunk = (uint32_t)((chunk_bytes + tile - 1) / tile);
-            const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
-            const size_t smem = (size_t)tile * stages;
+        a.tiles_per_chunk = (uint32_t)((chunk_bytes + kTmaTile - 1) / kTmaTile);
+        const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
+        constexpr size_t smem = (size_t)kTmaTile * kTmaStages;
+        auto kfn = k_xfer_tma<kTmaTile, kTmaStages, kTmaThreads, true>;
+        static bool attr_done[kMaxDev] = {false};
+        if (!attr_done[dev]) {
             VGPU_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            const unsigned per_sm = (unsigned)std::max<size_t>(1, std::min<size_t>((220 * 1024) / (smem + 1024), 2048 / threads));
-            static const int mult = [] { const char *e = getenv("VGPU_TMA_GRID_MULT"); return e ? atoi(e) : kTmaGridMult; }();
-            const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * per_sm * mult);
-            kfn<<<grid, threads, smem, st>>>(a);
-            return VGPU_OK;
-        };
-        int rc;
-        switch (cfg) {
-            case 1: rc = go(k_xfer_tma<32768, 4, 256, true>, 32768, 4, 256); break;
-            case 2: rc = go(k_xfer_tma<16384, 4, 128, true>, 16384, 4, 128); break;
-            case 3: rc = go(k_xfer_tma<65536, 3, 256, true>, 65536, 3, 256); break;
-            case 4: rc = go(k_xfer_tma<8192, 8, 128, true>, 8192, 8, 128); break;
-            case 5: rc = go(k_xfer_tma<16384, 6, 128, true>, 16384, 6, 128); break;
-            case 6: rc = go(k_xfer_tma<32768, 6, 128, true>, 32768, 6, 128); break;
-            default: rc = go(k_xfer_tma<kTmaTile, kTmaStages, kTmaThreads, true>, kTmaTile, kTmaStages, kTmaThreads); break;
+            attr_done[dev] = true;
         }
-        if (rc) return rc;
+        constexpr unsigned per_sm = (unsigned)((220 * 1024) / (smem + 1024));  // resident CTAs per SM (shared memory bound)
+        const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * per_sm * kTmaGridMult);
+        kfn<<<grid, kTmaThreads, smem, st>>>(a);
     }
     VGPU_CUDA(cudaGetLastError());
     return VGPU_OK;
