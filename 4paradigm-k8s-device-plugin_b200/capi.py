@@ -69,7 +69,8 @@ class MemtestResult(C.Structure):
 class VmemStats(C.Structure):
     _fields_ = [("chunks_total", C.c_uint64), ("chunks_resident", C.c_uint64), ("chunks_spilled", C.c_uint64),
                 ("resident_limit", C.c_uint64), ("tier_slots", C.c_uint64), ("evictions", C.c_uint64),
-                ("fetches", C.c_uint64), ("checksum_failures", C.c_uint64), ("evict_ms", C.c_double), ("fetch_ms", C.c_double)]
+                ("fetches", C.c_uint64), ("checksum_failures", C.c_uint64), ("evict_ms", C.c_double), ("fetch_ms", C.c_double),
+                ("evictions_peer", C.c_uint64), ("evictions_host", C.c_uint64)]
 
 
 class SmPartition(C.Structure):
@@ -101,6 +102,7 @@ SIGNATURES = {
     "vgpu_policy_get": (_i, [_i, _sz]),
     "vgpu_policy_set": (_i, [_i, _sz, _i]),
     "vgpu_vmem_create": (_i, [_i, _u64, _u64, _i, _i, _u64, _pp(_vp)]),
+    "vgpu_vmem_create_tiered": (_i, [_i, _u64, _u64, _i, _u64, _u64, _pp(_vp)]),
     "vgpu_vmem_base": (_i, [_vp, _pp(_vp)]),
     "vgpu_vmem_ensure": (_i, [_vp, _u64, _u64]),
     "vgpu_vmem_evict": (_i, [_vp, _u64, _u64]),

@@ -253,6 +253,7 @@ static __thread int tl_bypass;
 static struct {
     void *lib;
     int (*create)(int, uint64_t, uint64_t, int, int, uint64_t, void **);
+    int (*create_tiered)(int, uint64_t, uint64_t, int, uint64_t, uint64_t, void **);
     int (*base)(void *, void **);
     int (*ensure)(void *, uint64_t, uint64_t);
     int (*evict)(void *, uint64_t, uint64_t);
@@ -279,6 +280,7 @@ static void load_vmm_backend(void) {
         return;
     }
     g_dp.create = (int (*)(int, uint64_t, uint64_t, int, int, uint64_t, void **))real_dlsym(g_dp.lib, "vgpu_vmem_create");
+    g_dp.create_tiered = (int (*)(int, uint64_t, uint64_t, int, uint64_t, uint64_t, void **))real_dlsym(g_dp.lib, "vgpu_vmem_create_tiered");
     g_dp.base = (int (*)(void *, void **))real_dlsym(g_dp.lib, "vgpu_vmem_base");
     g_dp.ensure = (int (*)(void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_ensure");
     g_dp.evict = (int (*)(void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_evict");
@@ -354,7 +356,11 @@ static int add_chunk(CUdeviceptr *p, size_t n) {
         const uint64_t chunks = (n + IPCSIZE - 1) / IPCSIZE;
         void *h = NULL, *base = NULL;
         tl_bypass = 1;
-        int vrc = g_dp.create(dev, n, chunks * IPCSIZE, 2 /* VGPU_TIER_HOST */, -1, chunks * IPCSIZE, &h);
+        /* spill tiers: VGPU_OVERSUB_PEER=<gpu> puts an idle peer GPU's HBM (NVLink P2P) in front of pinned host RAM */
+        const char *pe = getenv("VGPU_OVERSUB_PEER");
+        int vrc = (pe && *pe && g_dp.create_tiered)
+                      ? g_dp.create_tiered(dev, n, chunks * IPCSIZE, atoi(pe), chunks * IPCSIZE, chunks * IPCSIZE, &h)
+                      : g_dp.create(dev, n, chunks * IPCSIZE, 2 /* VGPU_TIER_HOST */, -1, chunks * IPCSIZE, &h);
         if (vrc == 0) vrc = g_dp.ensure(h, 0, chunks);
         if (vrc == 0) vrc = g_dp.base(h, &base);
         if (vrc != 0) {

@@ -73,21 +73,30 @@ struct Block {
     CUmemGenericAllocationHandle handle = 0;
     uint64_t last_use = 0;
     uint32_t tier_slot = 0;  // block-sized slot in the tier slab
+    uint8_t tier_idx = 0;    // which of the manager's tiers holds it
     BlockState state = kUntouched;
 };
 
 constexpr size_t kCB = VGPU_CHUNK_BYTES;
 
 struct Vmem {
-    int device = 0, tier = 0, peer = -1;
+    int device = 0;
     CUdeviceptr base = 0;
     size_t nchunks = 0;         // as requested
     size_t bc = 0;              // chunks per block
-    size_t nblocks = 0, resident_limit = 0 /* blocks */, tier_slots = 0 /* blocks */;
-    void *tier_slab = nullptr;
+    size_t nblocks = 0, resident_limit = 0 /* blocks */;
+    // Spill tiers in order of preference (north_star: "first idle peer-GPU HBM over NVLink via P2P,
+    // then pinned host RAM"): a victim goes to the first tier that still has a free slot.
+    struct Tier {
+        int kind = 0, peer = -1;
+        void *slab = nullptr;       // allocated at the first eviction that needs it
+        size_t slots = 0;           // blocks
+        std::vector<uint32_t> free_slots;
+        uint64_t evictions = 0;     // chunks
+    };
+    std::vector<Tier> tiers;
     std::vector<Block> blocks;
     std::vector<CUmemGenericAllocationHandle> pool;  // parked physical blocks
-    std::vector<uint32_t> free_slots;
     size_t resident = 0, spilled = 0;  // blocks
     uint64_t clock = 0;
     vgpu_cksum_t *ck = nullptr;          // pinned + mapped: (X,S) of every chunk, written by the spill kernel,
@@ -142,19 +151,33 @@ int unmap_block(Vmem *v, size_t b, bool release) {
 // The unmap of block i-1 overlaps the spill kernel of block i.
 int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
     if (victims.empty()) return VGPU_OK;
-    if (!v->tier_slab && v->tier_slots)
-        if (int rc = vgpu_slab_alloc(v->tier, v->device, v->peer, v->tier_slots * v->block_bytes(), &v->tier_slab)) return rc;
-    if (victims.size() > v->free_slots.size())
-        return fail(VGPU_E_NOMEM, "spill tier full: %zu blocks to evict, %zu free slots", victims.size(), v->free_slots.size());
+    size_t free_total = 0;
+    for (auto &t : v->tiers) free_total += t.free_slots.size();
+    if (victims.size() > free_total)
+        return fail(VGPU_E_NOMEM, "spill tier full: %zu blocks to evict, %zu free slots", victims.size(), free_total);
     const double t0 = now_ms();
     VGPU_CUDA(cudaDeviceSynchronize());  // whatever the application queued on the victims must be done
     for (size_t i = 0; i < victims.size(); ++i) {
         const size_t b = victims[i];
         Block &bl = v->blocks[b];
-        bl.tier_slot = v->free_slots.back();
-        v->free_slots.pop_back();
-        int rc = vgpu_spill(VGPU_XFER_AUTO, v->tier, (const void *)(v->base + b * v->block_bytes()),
-                            (char *)v->tier_slab + (size_t)bl.tier_slot * v->block_bytes(), nullptr, nullptr, v->bc, kCB,
+        size_t ti = 0;
+        for (;; ++ti) {  // first tier with room whose slab can be had
+            if (ti == v->tiers.size()) return fail(VGPU_E_NOMEM, "spill tier full: no tier can take block %zu", b);
+            Vmem::Tier &c = v->tiers[ti];
+            if (c.free_slots.empty()) continue;
+            if (c.slab) break;
+            if (vgpu_slab_alloc(c.kind, v->device, c.peer, c.slots * v->block_bytes(), &c.slab) == VGPU_OK) break;
+            // e.g. the peer GPU is not idle after all: give this tier up and fall through to the next
+            c.free_slots.clear();
+            c.slots = 0;
+        }
+        Vmem::Tier &t = v->tiers[ti];
+        bl.tier_idx = (uint8_t)ti;
+        bl.tier_slot = t.free_slots.back();
+        t.free_slots.pop_back();
+        t.evictions += v->bc;
+        int rc = vgpu_spill(VGPU_XFER_AUTO, t.kind, (const void *)(v->base + b * v->block_bytes()),
+                            (char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(), nullptr, nullptr, v->bc, kCB,
                             v->ck + b * v->bc, v->stream);
         if (rc) return rc;
         VGPU_CUDA(cudaEventRecord(v->ev[i & 1], v->stream));
@@ -178,16 +201,21 @@ extern "C" {
 
 int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes, int tier, int peer_device,
                      uint64_t tier_bytes, void **handle) {
-    if (!handle || !virtual_bytes) return fail(VGPU_E_INVAL, "bad vmem request");
     if (tier != VGPU_TIER_PEER && tier != VGPU_TIER_HOST) return fail(VGPU_E_INVAL, "tier must be VGPU_TIER_PEER or VGPU_TIER_HOST");
+    return vgpu_vmem_create_tiered(device, virtual_bytes, resident_bytes, tier == VGPU_TIER_PEER ? peer_device : -1,
+                                   tier == VGPU_TIER_PEER ? tier_bytes : 0, tier == VGPU_TIER_HOST ? tier_bytes : 0, handle);
+}
+
+int vgpu_vmem_create_tiered(int device, uint64_t virtual_bytes, uint64_t resident_bytes, int peer_device,
+                            uint64_t peer_bytes, uint64_t host_bytes, void **handle) {
+    if (!handle || !virtual_bytes) return fail(VGPU_E_INVAL, "bad vmem request");
+    if (peer_bytes && (peer_device < 0 || peer_device == device)) return fail(VGPU_E_INVAL, "peer tier needs another GPU");
     std::call_once(g_once, load_api);
     if (!g_api.ok) return fail(VGPU_E_UNSUPPORTED, "CUDA VMM driver API not available");
     VGPU_CUDA(cudaSetDevice(device));
     VGPU_CUDA(cudaFree(0));
     Vmem *v = new Vmem();
     v->device = device;
-    v->tier = tier;
-    v->peer = peer_device;
     v->nchunks = (virtual_bytes + kCB - 1) / kCB;
     // block size: up to 512 chunks (1 GiB: config 4 pages at 616 / 608 GB/s incl. VMM calls, vs 509 / 285
     // with 256 MiB blocks), but keep >= 16 blocks in a range so that LRU paging has something to choose from
@@ -197,7 +225,17 @@ int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes
     v->bc = std::min(bc, v->nchunks);
     v->nblocks = (v->nchunks + v->bc - 1) / v->bc;
     v->resident_limit = std::max<uint64_t>(1, (resident_bytes + v->block_bytes() - 1) / v->block_bytes());  // whole blocks
-    v->tier_slots = (tier_bytes + v->block_bytes() - 1) / v->block_bytes();
+    for (int k = 0; k < 2; ++k) {  // peer first, then host
+        const uint64_t bytes = k == 0 ? peer_bytes : host_bytes;
+        if (!bytes) continue;
+        Vmem::Tier t;
+        t.kind = k == 0 ? VGPU_TIER_PEER : VGPU_TIER_HOST;
+        t.peer = k == 0 ? peer_device : -1;
+        t.slots = (bytes + v->block_bytes() - 1) / v->block_bytes();
+        t.free_slots.resize(t.slots);
+        for (size_t i = 0; i < t.slots; ++i) t.free_slots[i] = (uint32_t)(t.slots - 1 - i);
+        v->tiers.push_back(std::move(t));
+    }
     v->prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
     v->prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
     v->prop.location.id = device;
@@ -227,8 +265,6 @@ int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes
         return rc;
     }
     v->blocks.resize(v->nblocks);
-    v->free_slots.resize(v->tier_slots);
-    for (size_t i = 0; i < v->tier_slots; ++i) v->free_slots[i] = (uint32_t)(v->tier_slots - 1 - i);
     *handle = v;
     return VGPU_OK;
 }
@@ -297,7 +333,8 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
     for (size_t b : back) {  // map block k+1 on the host while the GPU restores block k
         if (int rc = map_block(v, b)) return rc;
         Block &bl = v->blocks[b];
-        int rc = vgpu_restore(VGPU_XFER_AUTO, v->tier, (const char *)v->tier_slab + (size_t)bl.tier_slot * v->block_bytes(),
+        Vmem::Tier &t = v->tiers[bl.tier_idx];
+        int rc = vgpu_restore(VGPU_XFER_AUTO, t.kind, (const char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(),
                               (void *)(v->base + b * v->block_bytes()), nullptr, nullptr, v->bc, kCB, v->ck + b * v->bc, nullptr,
                               v->res, v->stream);
         if (rc) return rc;
@@ -310,7 +347,7 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
             result = fail(VGPU_E_MISMATCH, "%llu restored chunk(s) failed their checksum", (unsigned long long)v->res->bad_chunks);
         }
         for (size_t b : back) {
-            v->free_slots.push_back(v->blocks[b].tier_slot);
+            v->tiers[v->blocks[b].tier_idx].free_slots.push_back(v->blocks[b].tier_slot);
             v->blocks[b].state = kResident;
         }
         v->resident += back.size();
@@ -330,7 +367,10 @@ int vgpu_vmem_stats(void *handle, vgpu_vmem_stats_t *out) {
     out->chunks_resident = v->resident * v->bc;
     out->chunks_spilled = v->spilled * v->bc;
     out->resident_limit = v->resident_limit * v->bc;
-    out->tier_slots = v->tier_slots * v->bc;
+    out->tier_slots = 0;
+    for (auto &t : v->tiers) out->tier_slots += t.slots * v->bc;
+    out->evictions_peer = out->evictions_host = 0;
+    for (auto &t : v->tiers) (t.kind == VGPU_TIER_PEER ? out->evictions_peer : out->evictions_host) += t.evictions;
     return VGPU_OK;
 }
 
@@ -346,7 +386,8 @@ int vgpu_vmem_destroy(void *handle) {
         }
     for (auto h : v->pool) g_api.Release(h);
     if (v->base) g_api.AddressFree(v->base, v->nblocks * v->block_bytes());
-    if (v->tier_slab) vgpu_slab_free(v->tier, v->device, v->peer, v->tier_slab);
+    for (auto &t : v->tiers)
+        if (t.slab) vgpu_slab_free(t.kind, v->device, t.peer, t.slab);
     if (v->ck) cudaFreeHost(v->ck);
     if (v->res) cudaFreeHost(v->res);
     if (v->stream) cudaStreamDestroy(v->stream);

@@ -207,6 +207,7 @@ typedef struct vgpu_vmem_stats {
     uint64_t evictions, fetches;          /* chunks moved out / in so far */
     uint64_t checksum_failures;           /* chunks whose (X,S) did not match on restore */
     double   evict_ms, fetch_ms;          /* wall time spent in evict / fetch incl. map/unmap */
+    uint64_t evictions_peer, evictions_host; /* chunks sent to each tier */
 } vgpu_vmem_stats_t;
 
 /* Create a range of `virtual_bytes` (rounded up to 2 MiB) on `device`, of which at most
@@ -214,6 +215,10 @@ typedef struct vgpu_vmem_stats {
  * `tier_bytes` (VGPU_TIER_PEER on `peer_device`, or VGPU_TIER_HOST). */
 int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes, int tier,
                      int peer_device, uint64_t tier_bytes, void **handle);
+/* Two tiers in the order the north star asks for: victims go to `peer_device`'s HBM (over NVLink P2P)
+ * while it has room, then to pinned host RAM.  Either size may be 0. */
+int vgpu_vmem_create_tiered(int device, uint64_t virtual_bytes, uint64_t resident_bytes, int peer_device,
+                            uint64_t peer_bytes, uint64_t host_bytes, void **handle);
 int vgpu_vmem_base(void *handle, void **base);
 /* Make chunks [first, first+n) resident: evicts least-recently-used chunks if the resident
  * limit would be exceeded, maps fresh memory for never-touched chunks, restores (and

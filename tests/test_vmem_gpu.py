@@ -97,3 +97,35 @@ def test_limits_are_reported_not_papered_over(vgpu, cuda_dev):
         assert capi.lib.vgpu_vmem_ensure(h, 60, 8) == capi.E_INVAL          # beyond the range
     finally:
         capi.lib.vgpu_vmem_destroy(h)
+
+
+def test_two_tiers_peer_first_then_host(vgpu, cuda_dev):
+    """north_star tier order: victims go to the idle peer GPU's HBM over NVLink while it has room,
+    then to pinned host RAM; everything comes back bit-exact from whichever tier holds it."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("peer tier needs 2 GPUs")
+    import os
+    capi = vgpu.capi
+    os.environ["VGPU_VMEM_BLOCK_CHUNKS"] = "8"
+    total, resident, peer, win = 512, 128, 128, 64     # chunks; host takes what the peer cannot
+    h = C.c_void_p()
+    rc = capi.lib.vgpu_vmem_create_tiered(0, total * CB, resident * CB, 1, peer * CB, total * CB, C.byref(h))
+    os.environ.pop("VGPU_VMEM_BLOCK_CHUNKS", None)
+    assert rc == 0, capi.last_error()
+    base = C.c_void_p()
+    assert capi.lib.vgpu_vmem_base(h, C.byref(base)) == 0
+    res = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+    try:
+        for w in range(total // win):
+            assert capi.lib.vgpu_vmem_ensure(h, w * win, win) == 0, capi.last_error()
+            assert capi.lib.vgpu_memtest_fill(base.value + w * win * CB, win * CB, capi.PAT_RANDOM, w, 7, None) == 0
+        torch.cuda.synchronize()
+        s = _stats(capi, h)
+        assert s.evictions_peer == peer and s.evictions_host == total - resident - peer   # peer filled first, rest to host
+        for w in reversed(range(total // win)):
+            assert capi.lib.vgpu_vmem_ensure(h, w * win, win) == 0, capi.last_error()
+            assert capi.lib.vgpu_memtest_verify(base.value + w * win * CB, win * CB, capi.PAT_RANDOM, w, 7, res.data_ptr(), None) == 0
+        torch.cuda.synchronize()
+        assert res.cpu().tolist() == [0, 0, 0] and _stats(capi, h).checksum_failures == 0
+    finally:
+        capi.lib.vgpu_vmem_destroy(h)
