@@ -787,6 +787,51 @@ EXPORT CUresult cuLaunchKernelEx(const void *config, void *fn, void **params, vo
     return f ? f(config, fn, params, extra) : 3;
 }
 
+/* The suspend gate on the copy / memset entry points, as in the reference (cuda/memory.c runs
+ * wait_status_self in every cuMemcpy / cuMemset hook): while a vGPU is suspended — and, with the VMM
+ * backend, until its data is back behind its pointers — nothing may touch device memory. */
+#define GATED(name, params, args)                                     \
+    EXPORT CUresult name params {                                     \
+        typedef CUresult(*fn_t) params;                               \
+        static fn_t f;                                                \
+        if (!f) f = (fn_t)cuda_sym(#name);                            \
+        if (!tl_bypass) {                                             \
+            ensure_initialized();                                     \
+            wait_running();                                           \
+        }                                                             \
+        return f ? f args : 3;                                        \
+    }
+GATED(cuMemcpy, (CUdeviceptr d, CUdeviceptr s_, size_t n), (d, s_, n))
+GATED(cuMemcpyAsync, (CUdeviceptr d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st))
+GATED(cuMemcpyDtoH_v2, (void *d, CUdeviceptr s_, size_t n), (d, s_, n))
+GATED(cuMemcpyDtoHAsync_v2, (void *d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st))
+GATED(cuMemcpyHtoD_v2, (CUdeviceptr d, const void *s_, size_t n), (d, s_, n))
+GATED(cuMemcpyHtoDAsync_v2, (CUdeviceptr d, const void *s_, size_t n, void *st), (d, s_, n, st))
+GATED(cuMemcpyDtoD_v2, (CUdeviceptr d, CUdeviceptr s_, size_t n), (d, s_, n))
+GATED(cuMemcpyDtoDAsync_v2, (CUdeviceptr d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st))
+GATED(cuMemsetD8_v2, (CUdeviceptr d, unsigned char v, size_t n), (d, v, n))
+GATED(cuMemsetD8Async, (CUdeviceptr d, unsigned char v, size_t n, void *st), (d, v, n, st))
+GATED(cuMemsetD32_v2, (CUdeviceptr d, unsigned v, size_t n), (d, v, n))
+GATED(cuMemsetD32Async, (CUdeviceptr d, unsigned v, size_t n, void *st), (d, v, n, st))
+
+/* cuMipmappedArrayCreate (a20): same allocate-then-check_oom pattern as the host allocations */
+EXPORT CUresult cuMipmappedArrayCreate(void **handle, const void *desc, unsigned levels) {
+    typedef CUresult (*fn_t)(void **, const void *, unsigned);
+    typedef CUresult (*del_t)(void *);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMipmappedArrayCreate");
+    if (tl_bypass) return f ? f(handle, desc, levels) : 3;
+    ensure_initialized();
+    CUresult rc = f ? f(handle, desc, levels) : 3;
+    if (rc != 0) return rc;
+    if (oom_check(-1, 0)) {
+        del_t d = (del_t)cuda_sym("cuMipmappedArrayDestroy");
+        if (d) d(*handle);
+        return 2;
+    }
+    return 0;
+}
+
 /* ------------------------------------------------------------------ NVML (a23) */
 typedef struct { unsigned long long total, free, used; } nvmlMemory_t;
 typedef struct { unsigned version; unsigned long long total, reserved, free, used; } nvmlMemory_v2_t;
@@ -859,6 +904,16 @@ static const hook_t g_hooks[] = {
     {"cuCtxPopCurrent", (void *)cuCtxPopCurrent_v2}, {"cuCtxPopCurrent_v2", (void *)cuCtxPopCurrent_v2},
     {"cuCtxPushCurrent", (void *)cuCtxPushCurrent_v2}, {"cuCtxPushCurrent_v2", (void *)cuCtxPushCurrent_v2},
     {"cuPointerGetAttributes", (void *)cuPointerGetAttributes},
+    {"cuMipmappedArrayCreate", (void *)cuMipmappedArrayCreate},
+    {"cuMemcpy", (void *)cuMemcpy}, {"cuMemcpyAsync", (void *)cuMemcpyAsync},
+    {"cuMemcpyDtoH", (void *)cuMemcpyDtoH_v2}, {"cuMemcpyDtoH_v2", (void *)cuMemcpyDtoH_v2},
+    {"cuMemcpyDtoHAsync", (void *)cuMemcpyDtoHAsync_v2}, {"cuMemcpyDtoHAsync_v2", (void *)cuMemcpyDtoHAsync_v2},
+    {"cuMemcpyHtoD", (void *)cuMemcpyHtoD_v2}, {"cuMemcpyHtoD_v2", (void *)cuMemcpyHtoD_v2},
+    {"cuMemcpyHtoDAsync", (void *)cuMemcpyHtoDAsync_v2}, {"cuMemcpyHtoDAsync_v2", (void *)cuMemcpyHtoDAsync_v2},
+    {"cuMemcpyDtoD", (void *)cuMemcpyDtoD_v2}, {"cuMemcpyDtoD_v2", (void *)cuMemcpyDtoD_v2},
+    {"cuMemcpyDtoDAsync", (void *)cuMemcpyDtoDAsync_v2}, {"cuMemcpyDtoDAsync_v2", (void *)cuMemcpyDtoDAsync_v2},
+    {"cuMemsetD8", (void *)cuMemsetD8_v2}, {"cuMemsetD8_v2", (void *)cuMemsetD8_v2}, {"cuMemsetD8Async", (void *)cuMemsetD8Async},
+    {"cuMemsetD32", (void *)cuMemsetD32_v2}, {"cuMemsetD32_v2", (void *)cuMemsetD32_v2}, {"cuMemsetD32Async", (void *)cuMemsetD32Async},
     {"cuLaunchKernel", (void *)cuLaunchKernel},
     {"cuLaunchKernelEx", (void *)cuLaunchKernelEx},
     {"cuGetProcAddress", (void *)cuGetProcAddress}, {"cuGetProcAddress_v2", (void *)cuGetProcAddress_v2},
@@ -870,6 +925,15 @@ static void *find_hook(const char *name) {
     for (size_t i = 0; i < sizeof(g_hooks) / sizeof(g_hooks[0]); ++i)
         if (strcmp(g_hooks[i].name, name) == 0) return g_hooks[i].fn;
     return NULL;
+}
+
+/* Launch / copy / memset entry points have per-thread-default-stream twins (_ptsz / _ptds) that the
+ * driver selects from the flags of cuGetProcAddress.  Our gates forward to the legacy-stream
+ * functions, so a caller that asks for the per-thread flavour gets the driver's own function (no
+ * gate) rather than a hook that would silently change its stream semantics. */
+static int wants_ptds(const char *symbol, unsigned long long flags) {
+    return (flags & 2ull /* CU_GET_PROC_ADDRESS_PER_THREAD_DEFAULT_STREAM */) &&
+           (strncmp(symbol, "cuMemcpy", 8) == 0 || strncmp(symbol, "cuMemset", 8) == 0 || strncmp(symbol, "cuLaunch", 8) == 0);
 }
 
 /* dlsym@0x12bb6: every cu, nvml lookup that names a hooked symbol lands in the shim */
@@ -884,7 +948,7 @@ EXPORT void *dlsym(void *handle, const char *symbol) {
 
 EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsigned long long flags) {
     ensure_initialized();
-    void *h = symbol ? find_hook(symbol) : NULL;
+    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook(symbol) : NULL;
     if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;
@@ -896,7 +960,7 @@ EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsign
 
 EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, unsigned long long flags, int *status) {
     ensure_initialized();
-    void *h = symbol ? find_hook(symbol) : NULL;
+    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook(symbol) : NULL;
     if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress_v2(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;

@@ -208,6 +208,7 @@ def test_sigusr2_suspends_and_sigusr1_resumes_a_running_vgpu_process(cuda_dev):
             line = sys.stdin.readline().strip()
             if line == "stop":
                 break
+            s = int(a.view(torch.int64)[-1].item()) if line == "copy" else 0   # plain D2H copy: gated like launches
             s = int(a.view(torch.int64).sum().item()); n += 1
             print(json.dumps({"same": s == s0, "n": n}), flush=True)
     """)
@@ -231,8 +232,13 @@ def test_sigusr2_suspends_and_sigusr1_resumes_a_running_vgpu_process(cuda_dev):
             time.sleep(0.2)
         u1 = used_mib()
         assert u0 - u1 >= 4 * 1024 - 64, (u0, u1)     # suspended: the 4 GiB went to pinned host RAM
+        p.stdin.write("copy\n"); p.stdin.flush()       # issued WHILE suspended: must park, not fault
+        time.sleep(1.0)
+        assert p.poll() is None
         os.kill(p.pid, signal.SIGUSR1)
-        r = poke()                                     # parks until the data is back, then computes on it
+        r = json.loads(p.stdout.readline())            # the parked request completes once the data is back
+        assert r["same"]
+        r = poke()
         assert r["same"]
         assert used_mib() - u1 >= 4 * 1024 - 64
     finally:
