@@ -382,10 +382,10 @@ def main():
         cpu_base = None
         if not args.no_cpu and world == 1:  # the CPU baseline is a rank-0, N=1 figure
             cores = len(os.sched_getaffinity(0))
-            v, sec = cpu_memtest_sample(args.cpu_gib, cores, passes_each=12)
+            v, sec = cpu_memtest_sample(args.cpu_gib, cores, passes_each=40)
             v1, _ = cpu_memtest_sample(min(args.cpu_gib, 0.5), 1)
             cpu_base = {"value": round(v, 3), "unit": "GB/s", "cores": cores, "kind": "port",
-                        "sample": f"oracle memtest, {args.cpu_gib} GiB host buffer, 12 walking-ones + 12 random passes ({sec:.1f} s)",
+                        "sample": f"oracle memtest, {args.cpu_gib} GiB host buffer, 40 walking-ones + 40 random passes ({sec:.1f} s)",
                         "one_thread_GBps": round(v1, 3),
                         "host_memcpy_spill_GBps": {"1_thread": round(cpu_spill_sample(64, 1), 2), f"{cores}_threads": round(cpu_spill_sample(256, cores), 2)}}
         line = {
