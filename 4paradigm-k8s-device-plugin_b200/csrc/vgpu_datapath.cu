@@ -139,7 +139,7 @@ int policy_lookup(int tier, size_t nchunks) {
 
 // ---- transfer launch --------------------------------------------------------
 constexpr int kLdstU = 4;                   // 4 x 32 B per thread in flight => 32 KiB tiles
-constexpr int kTmaTile = 32768, kTmaStages = 3, kTmaThreads = 256;  // 96 KiB ring, 2 CTAs/SM: best of the shapes swept
+constexpr int kTmaTile = 32768, kTmaStages = 2, kTmaLag = 1, kTmaConsumerWarps = 4;  // 64 KiB ring, 3 CTAs/SM: best of the shapes swept
 constexpr int kTmaGridMult = 16;  // CTAs per launch = resident CTAs x 16 (grid-stride over the rest)
 
 // CTAs per launch of the LD/ST copy variant: a grid-stride loop over 32 KiB tiles with
@@ -244,7 +244,8 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
         a.tiles_per_chunk = (uint32_t)((chunk_bytes + kTmaTile - 1) / kTmaTile);
         const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
         constexpr size_t smem = (size_t)kTmaTile * kTmaStages;
-        auto kfn = k_xfer_tma<kTmaTile, kTmaStages, kTmaThreads, true>;
+        constexpr int threads = 32 * (kTmaConsumerWarps + 1);
+        auto kfn = k_xfer_tma<kTmaTile, kTmaStages, kTmaLag, kTmaConsumerWarps, true>;
         static bool attr_done[kMaxDev] = {false};
         if (!attr_done[dev]) {
             VGPU_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -252,7 +253,7 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
         }
         constexpr unsigned per_sm = (unsigned)((220 * 1024) / (smem + 1024));  // resident CTAs per SM (shared memory bound)
         const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * per_sm * kTmaGridMult);
-        kfn<<<grid, kTmaThreads, smem, st>>>(a);
+        kfn<<<grid, threads, smem, st>>>(a);
     }
     VGPU_CUDA(cudaGetLastError());
     return VGPU_OK;

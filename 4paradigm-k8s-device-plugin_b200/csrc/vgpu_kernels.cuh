@@ -334,23 +334,34 @@ __device__ __forceinline__ void bulk_wait_read() {
 }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
-// One CTA runs an NS-stage ring of TILE-byte shared-memory buffers.  Thread 0
-// drives the bulk engine: it keeps NS-1 loads in flight, and as each tile
-// lands it issues the bulk store of that same buffer; meanwhile all threads
-// read the buffer for the checksum.  A buffer is reloaded only after (a) the
-// CTA-wide barrier that ends its checksum pass and (b) wait_group.read says
-// the store engine has finished reading it.
-template <int TILE, int NS, int THREADS, bool COPY>
-__global__ void __launch_bounds__(THREADS) k_xfer_tma(const XferArgs a) {
+// One CTA runs an NS-stage ring of TILE-byte shared-memory buffers, warp-specialised.
+// Warp 0 is the producer: one lane keeps D bulk loads in flight, issues the bulk store of each
+// tile as soon as it has landed, and recycles a buffer only when (a) the consumer warps have
+// signalled `done` for it and (b) wait_group.read says the store engine has finished reading it.
+// Warps 1..NCW only checksum out of shared memory and arrive on `done`.  No CTA-wide barrier
+// after set-up; the producer's waits never stall a consumer.  Shape chosen on B200
+// (profiles/r01_memtest_sweeps.md §4b): 2 stages x 32 KiB, store lag 1, 4 consumer warps, 3 CTAs/SM:
+// 3.26 TB/s payload HBM->HBM, level with the LD/ST kernel; deeper rings cost residency and lose.
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int TILE, int NS, int D, int NCW, bool COPY>
+__global__ void __launch_bounds__(32 * (NCW + 1)) k_xfer_tma(const XferArgs a) {
+    static_assert(D >= 1 && D < NS, "store lag must leave at least one spare buffer");
     extern __shared__ __align__(128) unsigned char ring[];
     __shared__ __align__(8) uint64_t full[NS];
+    __shared__ __align__(8) uint64_t done[NS];
     const uint64_t total = (uint64_t)a.nchunks * a.tiles_per_chunk;
     if (blockIdx.x >= total) return;
     const uint64_t my_n = (total - blockIdx.x + gridDim.x - 1) / gridDim.x;
 
     if (threadIdx.x == 0) {
 #pragma unroll
-        for (int i = 0; i < NS; ++i) mbar_init(&full[i], 1);
+        for (int i = 0; i < NS; ++i) {
+            mbar_init(&full[i], 1);
+            mbar_init(&done[i], NCW);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -362,22 +373,40 @@ __global__ void __launch_bounds__(THREADS) k_xfer_tma(const XferArgs a) {
         const uint64_t left = a.chunk_bytes - toff;
         len = left < (uint64_t)TILE ? (uint32_t)left : (uint32_t)TILE;
     };
-    auto issue_load = [&](uint64_t k) {
-        uint32_t c, len;
-        uint64_t toff;
-        tile_geom(k, c, toff, len);
-        const int st = (int)(k % NS);
-        const unsigned char *s =
-            a.src + (uint64_t)(a.src_slot ? a.src_slot[c] : c) * a.chunk_bytes + toff;
-        mbar_expect_tx(&full[st], len);
-        bulk_g2s(ring + (size_t)st * TILE, s, len, &full[st]);
-    };
 
-    if (threadIdx.x == 0) {
-        const uint64_t pre = my_n < (uint64_t)(NS - 1) ? my_n : (uint64_t)(NS - 1);
-        for (uint64_t k = 0; k < pre; ++k) issue_load(k);
+    if (threadIdx.x < 32) {  // ---------------- producer warp
+        if (threadIdx.x != 0) return;
+        for (uint64_t k = 0; k < my_n + D; ++k) {
+            if (k < my_n) {
+                const int st = (int)(k % NS);
+                if (k >= NS) {
+                    mbar_wait(&done[st], (uint32_t)(((k / NS) - 1) & 1));  // consumers are off tile k-NS
+                    if (COPY) bulk_wait_read<NS - 1 - D>();                // and so is the store engine
+                }
+                uint32_t c, len;
+                uint64_t toff;
+                tile_geom(k, c, toff, len);
+                const unsigned char *s = a.src + (uint64_t)(a.src_slot ? a.src_slot[c] : c) * a.chunk_bytes + toff;
+                mbar_expect_tx(&full[st], len);
+                bulk_g2s(ring + (size_t)st * TILE, s, len, &full[st]);
+            }
+            if (COPY && k >= D) {  // tile j = k - D has had D iterations to land
+                const uint64_t j = k - D;
+                const int sj = (int)(j % NS);
+                uint32_t c, len;
+                uint64_t toff;
+                tile_geom(j, c, toff, len);
+                mbar_wait(&full[sj], (uint32_t)((j / NS) & 1));
+                unsigned char *d = a.dst + (uint64_t)(a.dst_slot ? a.dst_slot[c] : c) * a.chunk_bytes + toff;
+                bulk_s2g(d, ring + (size_t)sj * TILE, len);
+                bulk_commit();
+            }
+        }
+        if (COPY) bulk_wait_all();
+        return;
     }
-
+    // ---------------- consumer warps
+    const uint32_t ct = threadIdx.x - 32;
     for (uint64_t k = 0; k < my_n; ++k) {
         uint32_t c, len;
         uint64_t toff;
@@ -385,28 +414,18 @@ __global__ void __launch_bounds__(THREADS) k_xfer_tma(const XferArgs a) {
         const int st = (int)(k % NS);
         const unsigned char *buf = ring + (size_t)st * TILE;
         mbar_wait(&full[st], (uint32_t)((k / NS) & 1));
-        if (threadIdx.x == 0) {
-            if (COPY) {
-                unsigned char *d =
-                    a.dst + (uint64_t)(a.dst_slot ? a.dst_slot[c] : c) * a.chunk_bytes + toff;
-                bulk_s2g(d, buf, len);
-                bulk_commit();
-                bulk_wait_read<1>();  // store of tile k-1 has released its buffer
-            }
-            if (k + NS - 1 < my_n) issue_load(k + NS - 1);  // refills the buffer of tile k-1
-        }
         uint64_t x = 0, sum = 0;
 #pragma unroll 4
-        for (uint32_t off = threadIdx.x * 16u; off < len; off += THREADS * 16u) {
+        for (uint32_t off = ct * 16u; off < len; off += NCW * 32u * 16u) {
             const ulonglong2 w = *reinterpret_cast<const ulonglong2 *>(buf + off);
             const uint32_t i = (uint32_t)((toff + off) >> 3);
             cksum_word(w.x, i + 0, x, sum);
             cksum_word(w.y, i + 1, x, sum);
         }
-        chunk_fold(a, c, x, sum, a.tiles_per_chunk * (THREADS / 32));
-        __syncthreads();  // every thread is done reading buffer `st`
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(&done[st]);  // this warp no longer reads the buffer
+        chunk_fold(a, c, x, sum, a.tiles_per_chunk * NCW);
     }
-    if (COPY && threadIdx.x == 0) bulk_wait_all();
 }
 
 }  // namespace vgpu
