@@ -4,6 +4,7 @@
 // kernels in vgpu_kernels.cuh (or, for VGPU_XFER_CE, the copy engine plus the
 // checksum kernel) or fails.
 #include <cuda_runtime.h>
+#include <sys/mman.h>
 
 #include <algorithm>
 #include <chrono>
@@ -12,6 +13,7 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include "vgpu_internal.h"
@@ -360,6 +362,43 @@ int vgpu_restore_from_host(int variant, int device, const void *host, void *d_ds
 }
 
 // ---- slabs --------------------------------------------------------------------
+// Pinned host slabs: cudaHostAlloc pins at ~2.5 GiB/s on this box (3.2 s for 8 GiB; the first
+// suspend of an 80 GiB vGPU spent 30 s there).  Transparent-huge-page backed anonymous memory,
+// first-touched by several threads and then registered, is pinned at 20+ GiB/s (cudaHostRegister
+// itself: 0.15 s for 8 GiB).  Falls back to cudaHostAlloc whenever a step is not available.
+namespace {
+std::mutex g_slab_mu;
+std::map<void *, size_t> g_registered_slabs;  // host slabs that came from mmap + cudaHostRegister
+
+void *host_slab_fast(int device, size_t bytes) {
+    int can = 0;
+    if (cudaDeviceGetAttribute(&can, cudaDevAttrCanUseHostPointerForRegisteredMem, device) != cudaSuccess || !can) return nullptr;
+    const size_t huge = 2u << 20;
+    const size_t len = (bytes + huge - 1) / huge * huge;
+    void *m = mmap(nullptr, len, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+    if (m == MAP_FAILED) return nullptr;
+    madvise(m, len, MADV_HUGEPAGE);
+    unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    if (len < (64u << 20)) nt = 1;
+    std::vector<std::thread> th;
+    const size_t per = (len / huge + nt - 1) / nt * huge;
+    for (unsigned t = 0; t < nt; ++t)
+        th.emplace_back([=] {
+            const size_t a = std::min(len, per * t), b = std::min(len, per * (t + 1));
+            for (size_t o = a; o < b; o += 4096) static_cast<volatile char *>(m)[o] = 0;  // first touch
+        });
+    for (auto &x : th) x.join();
+    if (cudaHostRegister(m, len, cudaHostRegisterPortable | cudaHostRegisterMapped) != cudaSuccess) {
+        cudaGetLastError();
+        munmap(m, len);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lk(g_slab_mu);
+    g_registered_slabs[m] = len;
+    return m;
+}
+}  // namespace
+
 int vgpu_slab_alloc(int tier, int device, int peer_device, size_t bytes, void **out) {
     if (!out || !bytes) return fail(VGPU_E_INVAL, "bad slab request");
     *out = nullptr;
@@ -384,6 +423,7 @@ int vgpu_slab_alloc(int tier, int device, int peer_device, size_t bytes, void **
         }
         case VGPU_TIER_HOST:
             VGPU_CUDA(cudaSetDevice(device));
+            if ((*out = host_slab_fast(device, bytes)) != nullptr) return VGPU_OK;
             VGPU_CUDA(cudaHostAlloc(out, bytes, cudaHostAllocPortable | cudaHostAllocMapped));
             return VGPU_OK;
     }
@@ -402,9 +442,24 @@ int vgpu_slab_free(int tier, int device, int peer_device, void *p) {
             VGPU_CUDA(cudaFree(p));
             VGPU_CUDA(cudaSetDevice(device));
             return VGPU_OK;
-        case VGPU_TIER_HOST:
-            VGPU_CUDA(cudaFreeHost(p));
+        case VGPU_TIER_HOST: {
+            size_t len = 0;
+            {
+                std::lock_guard<std::mutex> lk(g_slab_mu);
+                auto it = g_registered_slabs.find(p);
+                if (it != g_registered_slabs.end()) {
+                    len = it->second;
+                    g_registered_slabs.erase(it);
+                }
+            }
+            if (len) {
+                VGPU_CUDA(cudaHostUnregister(p));
+                munmap(p, len);
+            } else {
+                VGPU_CUDA(cudaFreeHost(p));
+            }
             return VGPU_OK;
+        }
     }
     return fail(VGPU_E_INVAL, "tier=%d", tier);
 }
