@@ -21,7 +21,7 @@ lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
 OK, E_INVAL, E_CUDA, E_NOMEM, E_UNKNOWN_ID, E_RANGE, E_MISMATCH, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5, -6, -7
 CHUNK_BYTES = 2097152
 NOALLOC_MAX_CHUNKS = 4096
-XFER_AUTO, XFER_LDST, XFER_TMA, XFER_CE = 0, 1, 2, 3
+XFER_AUTO, XFER_LDST, XFER_TMA, XFER_CE, XFER_PULL = 0, 1, 2, 3, 4
 TIER_LOCAL, TIER_PEER, TIER_HOST = 0, 1, 2
 PAT_WALKING_ONES, PAT_RANDOM = 0, 1
 SM_FINE = 1

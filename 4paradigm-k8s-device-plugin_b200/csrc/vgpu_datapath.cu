@@ -186,6 +186,7 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
     if (expect && !result) return fail(VGPU_E_INVAL, "expect given without a result block");
     if (tier < 0 || tier > 2) return fail(VGPU_E_INVAL, "tier=%d", tier);
     if (variant == VGPU_XFER_AUTO) variant = policy_lookup(tier, nchunks);
+    if (variant == VGPU_XFER_PULL) variant = VGPU_XFER_TMA;  // a restore already runs on the reading side
     if (variant < VGPU_XFER_LDST || variant > VGPU_XFER_CE) return fail(VGPU_E_INVAL, "variant=%d", variant);
 
     int dev, sms;
@@ -278,10 +279,70 @@ int vgpu_checksum(const void *src, const uint32_t *src_slot, size_t nchunks, siz
                        nchunks, chunk_bytes, nullptr, cksum, nullptr, stream, false);
 }
 
+// Peer-tier spill as a PULL: the bulk-copy kernel runs on the (idle) GPU that owns the spill slab,
+// reads the victim chunks out of this GPU's HBM over NVLink and stores them locally.  Ordered after
+// the caller's stream through an event, and the caller's stream waits for its completion, so the
+// call keeps its "asynchronous on `stream`" contract.
+namespace {
+struct PullCtx {
+    cudaStream_t stream = nullptr;  // on the peer device
+    cudaEvent_t ready = nullptr;    // recorded on the caller's stream (this device)
+    cudaEvent_t done = nullptr;     // recorded on the peer stream
+};
+std::map<std::pair<int, int>, PullCtx> g_pull;  // (this device, peer device)
+
+int pull_spill(const void *src, void *dst, const uint32_t *src_slot, const uint32_t *dst_slot, size_t nchunks,
+               size_t chunk_bytes, vgpu_cksum_t *cksum, void *stream) {
+    int dev;
+    if (int rc = cur_device(&dev)) return rc;
+    cudaPointerAttributes at{};
+    VGPU_CUDA(cudaPointerGetAttributes(&at, dst));
+    const int peer = at.device;
+    if (at.type != cudaMemoryTypeDevice || peer == dev || peer < 0 || peer >= kMaxDev)
+        return fail(VGPU_E_INVAL, "VGPU_XFER_PULL needs a destination slab in another GPU's memory");
+    PullCtx *pc;
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        pc = &g_pull[{dev, peer}];
+    }
+    if (!pc->stream) {
+        VGPU_CUDA(cudaEventCreateWithFlags(&pc->ready, cudaEventDisableTiming));
+        VGPU_CUDA(cudaSetDevice(peer));
+        cudaError_t e = cudaDeviceEnablePeerAccess(dev, 0);  // the peer must be able to read our HBM
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else if (e != cudaSuccess) {
+            cudaSetDevice(dev);
+            return fail(VGPU_E_CUDA, "cudaDeviceEnablePeerAccess(%d) from %d: %s", dev, peer, cudaGetErrorString(e));
+        }
+        e = cudaStreamCreateWithFlags(&pc->stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&pc->done, cudaEventDisableTiming);
+        cudaSetDevice(dev);
+        if (e != cudaSuccess) return fail(VGPU_E_CUDA, "pull stream: %s", cudaGetErrorString(e));
+    }
+    VGPU_CUDA(cudaEventRecord(pc->ready, static_cast<cudaStream_t>(stream)));
+    VGPU_CUDA(cudaSetDevice(peer));
+    cudaError_t e = cudaStreamWaitEvent(pc->stream, pc->ready, 0);
+    int rc = e == cudaSuccess ? launch_xfer(VGPU_XFER_TMA, VGPU_TIER_PEER, true, src, dst, src_slot, dst_slot, nchunks, chunk_bytes,
+                                            nullptr, cksum, nullptr, pc->stream, false)
+                              : fail(VGPU_E_CUDA, "cudaStreamWaitEvent: %s", cudaGetErrorString(e));
+    if (!rc && cudaEventRecord(pc->done, pc->stream) != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaEventRecord(done)");
+    cudaSetDevice(dev);
+    if (rc) return rc;
+    VGPU_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), pc->done, 0));
+    return VGPU_OK;
+}
+}  // namespace
+
 int vgpu_spill(int variant, int tier, const void *src, void *dst, const uint32_t *src_slot,
                const uint32_t *dst_slot, size_t nchunks, size_t chunk_bytes, vgpu_cksum_t *cksum,
                void *stream) {
     if (!cksum && nchunks) return fail(VGPU_E_INVAL, "cksum is NULL");
+    if (variant == VGPU_XFER_AUTO && tier >= 0 && tier <= 2) variant = policy_lookup(tier, nchunks);
+    if (variant == VGPU_XFER_PULL) {
+        if (nchunks == 0) return VGPU_OK;
+        if (tier != VGPU_TIER_PEER) return fail(VGPU_E_INVAL, "VGPU_XFER_PULL is a peer-tier spill variant");
+        return pull_spill(src, dst, src_slot, dst_slot, nchunks, chunk_bytes, cksum, stream);
+    }
     return launch_xfer(variant, tier, true, src, dst, src_slot, dst_slot, nchunks, chunk_bytes,
                        nullptr, cksum, nullptr, stream, false);
 }
@@ -471,7 +532,7 @@ int vgpu_policy_get(int tier, size_t nchunks) {
 }
 
 int vgpu_policy_set(int tier, size_t min_chunks, int variant) {
-    if (tier < 0 || tier > 2 || variant < VGPU_XFER_LDST || variant > VGPU_XFER_CE)
+    if (tier < 0 || tier > 2 || variant < VGPU_XFER_LDST || variant > VGPU_XFER_PULL || (variant == VGPU_XFER_PULL && tier != VGPU_TIER_PEER))
         return fail(VGPU_E_INVAL, "tier=%d variant=%d", tier, variant);
     std::lock_guard<std::mutex> lk(g_mu);
     for (Rule &r : g_policy[tier])
@@ -499,7 +560,7 @@ int vgpu_calibrate(int device, int tier, int peer_device, size_t max_chunks) {
     for (size_t n = 1; !rc && n <= max_chunks; n *= 8) {
         float best_ms = 0;
         int best = VGPU_XFER_LDST;
-        for (int v = VGPU_XFER_LDST; v <= VGPU_XFER_CE && !rc; ++v) {
+        for (int v = VGPU_XFER_LDST; v <= (tier == VGPU_TIER_PEER ? VGPU_XFER_PULL : VGPU_XFER_CE) && !rc; ++v) {
             float ms_min = 1e30f;
             for (int it = 0; it < 4 && !rc; ++it) {  // first iteration is warm-up
                 cudaEventRecord(e0, 0);

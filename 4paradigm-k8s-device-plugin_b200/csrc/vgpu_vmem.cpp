@@ -105,7 +105,8 @@ struct Vmem {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[2] = {nullptr, nullptr};
     CUmemAllocationProp prop{};
-    CUmemAccessDesc access{};
+    CUmemAccessDesc access[2]{};  // this GPU, and the peer GPU when there is a peer tier (it may pull the spill)
+    size_t access_n = 1;
     vgpu_vmem_stats_t st{};
     std::mutex mu;
     size_t block_bytes() const { return bc * kCB; }
@@ -127,7 +128,7 @@ int map_block(Vmem *v, size_t b) {
     }
     const CUdeviceptr va = v->base + b * v->block_bytes();
     CUresult r = g_api.Map(va, v->block_bytes(), 0, h, 0);
-    if (r == CUDA_SUCCESS) r = g_api.SetAccess(va, v->block_bytes(), &v->access, 1);
+    if (r == CUDA_SUCCESS) r = g_api.SetAccess(va, v->block_bytes(), v->access, v->access_n);
     if (r != CUDA_SUCCESS) {
         v->pool.push_back(h);
         return drv_fail("cuMemMap/cuMemSetAccess", r);
@@ -239,8 +240,14 @@ int vgpu_vmem_create_tiered(int device, uint64_t virtual_bytes, uint64_t residen
     v->prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
     v->prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
     v->prop.location.id = device;
-    v->access.location = v->prop.location;
-    v->access.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    v->access[0].location = v->prop.location;
+    v->access[0].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    if (peer_bytes) {
+        v->access[1].location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        v->access[1].location.id = peer_device;
+        v->access[1].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        v->access_n = 2;
+    }
     size_t gran = 0;
     CUresult r = g_api.GetGranularity(&gran, &v->prop, CU_MEM_ALLOC_GRANULARITY_MINIMUM);
     if (r != CUDA_SUCCESS || gran == 0 || kCB % gran != 0) {

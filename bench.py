@@ -601,11 +601,12 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, barrier, max_over_rank
 
     for tname, (tier, slab, cap) in tiers.items():
         tout = {}
+        tvariants = dict(variants, pull=capi.XFER_PULL) if tname == "peer" else variants
         for n in sizes:
             if cap is not None and n > cap:
                 continue
             row = {}
-            for vname, v in variants.items():
+            for vname, v in tvariants.items():
                 def do_spill():
                     capi.check(capi.lib.vgpu_spill(v, tier, hbm.data_ptr(), slab, None, None, n, cb, ck.data_ptr(), stream))
 
@@ -627,6 +628,34 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, barrier, max_over_rank
             raise SystemExit(f"spill/restore round trip on tier {tname} is not bit-exact")
         tout["round_trip_bit_exact"] = True
         out[tname] = tout
+    # one direction at a time: only rank 0 moves data over its link, the other GPUs are idle
+    if "peer" in tiers:
+        tier, slab, _ = tiers["peer"]
+        n = max(sz for sz in sizes)
+        uni = {}
+        for vname, v in dict(variants, pull=capi.XFER_PULL).items():
+            res_ms = []
+            for direction in ("spill", "restore"):
+                best = 1e30
+                for rep in range(5):
+                    barrier()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    if local == 0:
+                        e0.record()
+                        if direction == "spill":
+                            capi.check(capi.lib.vgpu_spill(v, tier, hbm.data_ptr(), slab, None, None, n, cb, ck.data_ptr(), stream))
+                        else:
+                            capi.check(capi.lib.vgpu_restore(v, tier, slab, back.data_ptr(), None, None, n, cb, ck.data_ptr(), None, res.data_ptr(), stream))
+                        e1.record()
+                        torch.cuda.synchronize()
+                        if rep >= 1:
+                            best = min(best, e0.elapsed_time(e1))
+                    barrier()
+                res_ms.append(best)
+            if local == 0:
+                uni[vname] = {"spill_GBps": round(n * cb / (res_ms[0] * 1e6), 1), "restore_GBps": round(n * cb / (res_ms[1] * 1e6), 1)}
+        out["peer"]["one_direction_only_rank0"] = {"chunks": n, **uni}
+
     # e2e host-buffer entry points (blocking, wall clock): vgpu_spill_to_host / vgpu_restore_from_host
     n = min(nmax, 1024)
     hck = (capi.Cksum * n)()

@@ -114,6 +114,8 @@ int vgpu_allocate_env(const vgpu_plugin_cfg_t *cfg,
 #define VGPU_XFER_LDST 1   /* 256-bit vectorised coalesced loads/stores */
 #define VGPU_XFER_TMA  2   /* cp.async.bulk global->smem->global ring */
 #define VGPU_XFER_CE   3   /* copy engine (cudaMemcpyAsync) + checksum kernel */
+#define VGPU_XFER_PULL 4   /* peer-tier spill only: run the bulk-copy kernel on the GPU that owns `dst`, so NVLink
+                              carries reads (788 GB/s one way on B200) instead of writes (716 GB/s) */
 
 /* tier of the far side of a transfer (used by the AUTO policy and stats) */
 #define VGPU_TIER_LOCAL 0  /* same-GPU HBM */

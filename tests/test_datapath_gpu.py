@@ -241,7 +241,7 @@ def test_peer_tier_round_trip(vgpu, cuda_dev):
     slab = C.c_void_p()
     assert capi.lib.vgpu_slab_alloc(capi.TIER_PEER, 0, 1, n * cb, C.byref(slab)) == 0, capi.last_error()
     try:
-        for v in (capi.XFER_LDST, capi.XFER_TMA, capi.XFER_CE):
+        for v in (capi.XFER_LDST, capi.XFER_TMA, capi.XFER_CE, capi.XFER_PULL):  # PULL: the peer GPU runs the spill kernel
             ck = torch.zeros((n, 2), dtype=torch.int64, device=cuda_dev)
             res = torch.zeros(2, dtype=torch.int64, device=cuda_dev)
             with torch.cuda.device(0):
