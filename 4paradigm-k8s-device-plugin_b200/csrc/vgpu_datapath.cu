@@ -122,8 +122,8 @@ struct Rule {
     int variant;
 };
 std::vector<Rule> g_policy[3] = {
-    {{0, VGPU_XFER_LDST}},                       // local HBM: LD/ST wins at every batch size measured
-    {{0, VGPU_XFER_LDST}},                       // peer HBM: see profiles/ (N>=2 runs)
+    {{0, VGPU_XFER_TMA}, {512, VGPU_XFER_LDST}},  // local HBM: bulk-copy ring up to 64 chunks (+6 %), LD/ST from 512 up (+1 %)
+    {{0, VGPU_XFER_TMA}},                         // peer HBM: bulk-copy ring >= LD/ST at every size (891 vs 851 GB/s at 8 chunks)
     {{0, VGPU_XFER_LDST}, {8, VGPU_XFER_CE}},    // pinned host: copy engine +5 % from 8 chunks up (55.1 vs 52.7 GB/s)
 };
 
