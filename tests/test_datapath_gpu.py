@@ -97,6 +97,32 @@ def test_memtest_rejects_misaligned(vgpu, cuda_dev):
     assert capi.lib.vgpu_memtest_fill(C.c_void_p(buf.data_ptr()), 512, 9, 0, 0, None) == capi.E_INVAL
 
 
+def test_kernels_reproduce_committed_golden_vectors(vgpu, cuda_dev):
+    """tests/golden/datapath_vectors.json: the kernels against committed known answers (no oracle
+    library in the loop), including the last words of a 40 GiB buffer (64-bit word indices)."""
+    import json, os
+    dp, capi = vgpu.datapath, vgpu.capi
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "datapath_vectors.json")))
+    for p in g["patterns"]:
+        buf = torch.zeros(8, dtype=torch.int64, device=cuda_dev)
+        dp.memtest_fill(buf, p["pattern"], p["pass"], p["seed"])
+        assert [hex(int(x)) for x in buf.cpu().numpy().view(np.uint64)] == p["first_words"]
+    big = torch.empty(40 << 30, dtype=torch.uint8, device=cuda_dev)          # config 2's vGPU size
+    for p in g["patterns"]:
+        dp.memtest_fill(big, p["pattern"], p["pass"], p["seed"])
+        tail = big[-32:].cpu().numpy().view(np.uint64)
+        assert [hex(int(x)) for x in tail] == p["words_before_40GiB"]
+        assert dp.memtest_verify(big, p["pattern"], p["pass"], p["seed"]).cpu().tolist() == [0, 0, 0]
+    del big
+    for c in g["checksums"]:
+        src = torch.empty(c["nchunks"] * c["chunk_bytes"], dtype=torch.uint8, device=cuda_dev)
+        dp.memtest_fill(src, capi.PAT_RANDOM, c["pass"], 0)
+        for v in (capi.XFER_LDST, capi.XFER_TMA):
+            ck = dp.spill(src, torch.empty_like(src), c["nchunks"], c["chunk_bytes"], variant=v)
+            got = [[hex(int(x)) for x in row] for row in as_pairs(ck)]
+            assert got == c["xs"], (v, c["source"])
+
+
 # ---------------------------------------------------------------- checksum / spill / restore
 @pytest.mark.parametrize("chunk_bytes,nchunks", [(32, 1), (32, 7), (4096, 3), (32768, 5), (32768 + 32, 4), (2097152, 1), (2097152, 9), (2097152 - 64, 3), (3 * 2097152 + 96, 2)])
 def test_checksum_matches_oracle(vgpu, cuda_dev, chunk_bytes, nchunks):

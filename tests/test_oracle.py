@@ -90,3 +90,20 @@ def test_mt_drivers_agree_with_scalar():
     dst = np.zeros_like(src)
     sec, xs = cpu.spill_mt(src, dst, 16, 4096, 3)
     assert np.array_equal(src, dst) and np.array_equal(xs, cpu.spill(src, np.zeros_like(src), 16, 4096))
+
+
+def test_oracle_reproduces_committed_datapath_vectors():
+    """tests/golden/datapath_vectors.json (oracle/gen_datapath_golden.py): pins the definitions."""
+    import json, os
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "datapath_vectors.json")))
+    for p in g["patterns"]:
+        assert [hex(int(x)) for x in cpu.fill(8, p["pattern"], p["pass"], p["seed"])] == p["first_words"]
+        far = cpu.fill(4, p["pattern"], p["pass"], p["seed"], first=(40 << 30) // 8 - 4)
+        assert [hex(int(x)) for x in far] == p["words_before_40GiB"]
+    for c in g["checksums"]:
+        n = c["chunk_bytes"] // 8
+        words = cpu.fill(c["nchunks"] * n, cpu.PAT_RANDOM, c["pass"], 0)
+        got = [[hex(v) for v in cpu.checksum(words[i * n:(i + 1) * n])] for i in range(c["nchunks"])]
+        assert got == c["xs"]
+    # a hand-checkable one: walking ones, pass 0 -> 1, 2, 4, 8 ...
+    assert g["patterns"][0]["first_words"] == [hex(1 << i) for i in range(8)]
