@@ -46,3 +46,13 @@ def test_argument_errors_need_no_gpu(vgpu):
     assert c.lib.vgpu_spill(1, 0, None, None, None, None, 0, c.CHUNK_BYTES, None, None) == c.OK  # 0 chunks: no-op
     assert c.lib.vgpu_spill(1, 0, None, None, None, None, 4, c.CHUNK_BYTES, None, None) == c.E_INVAL
     assert "cksum" in c.last_error()
+
+
+def test_header_is_valid_c_and_links_from_a_plain_c_caller(vgpu, tmp_path):
+    """What a cgo build does: compile a C translation unit against include/vgpu.h and link libvgpu_dp.so."""
+    exe = tmp_path / "c_abi_smoke"
+    pkg = os.path.dirname(vgpu.capi.LIB_PATH)
+    subprocess.check_call(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "c_abi_smoke.c"), "-o", str(exe), "-L", pkg, "-lvgpu_dp", f"-Wl,-rpath,{pkg}"])
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0 and "c_abi_smoke ok" in out.stdout, out.stdout + out.stderr
