@@ -88,6 +88,7 @@ SIGNATURES = {
     "vgpu_split": (_i, [C.c_char_p, _u64, _u, C.c_double, _pp(Desc), _sz]),
     "vgpu_sm_limit": (_i, [_u, C.c_double]),
     "vgpu_lookup": (_i, [_pp(Desc), _sz, _pp(C.c_char_p), _sz, _pp(_pp(Desc))]),
+    "vgpu_best_effort": (_i, [_pp(_i), _sz, _pp(_i), _sz, _i, _pp(_i), _sz, _pp(_i), _sz]),
     "vgpu_allocate_env": (_i, [_pp(PluginCfg), _pp(_pp(Desc)), _sz, _pp(C.c_char_p), _pp(C.c_char_p), _sz,
                                C.c_char_p, _pp(KV), _pp(_sz), _pp(Mount), _pp(_sz)]),
     "vgpu_checksum": (_i, [_vp, _vp, _sz, _sz, _vp, _vp]),

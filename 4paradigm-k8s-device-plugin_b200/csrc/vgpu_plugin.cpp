@@ -39,7 +39,145 @@ int random_uuid4(char out[37]) {
 
 }  // namespace
 
+namespace {
+
+// ---- best-effort policy (besteffort_policy.go) -----------------------------------------------
+// A device is its index into the score matrix; kPad stands for the reference's nil padding.
+constexpr int kPad = -1;
+using Set = std::vector<int>;
+using Partition = std::vector<Set>;
+
+struct BestEffort {
+    const int *score;
+    size_t n;
+
+    int pair(int a, int b) const { return (a == kPad || b == kPad || a == b) ? 0 : score[(size_t)a * n + (size_t)b]; }
+    int set_score(const Set &s) const {
+        int t = 0;
+        for (size_t i = 0; i < s.size(); ++i)
+            for (size_t j = i + 1; j < s.size(); ++j) t += pair(s[i], s[j]);
+        return t;
+    }
+    int partition_score(const Partition &p) const {
+        int t = 0;
+        for (const Set &s : p) t += set_score(s);
+        return t;
+    }
+    static int padding(const Set &s) {
+        int c = 0;
+        for (int d : s) c += d == kPad;
+        return c;
+    }
+    static bool contains(const Set &s, int d) {
+        for (int x : s)
+            if (x == d) return true;
+        return false;
+    }
+    static bool contains_all(const Set &s, const Set &sub) {
+        for (int d : sub)
+            if (!contains(s, d)) return false;
+        return true;
+    }
+
+    // iterateGPUSets: all combinations of `size` positions, lexicographic
+    template <typename F>
+    static void sets(const Set &devs, int size, F &&cb) {
+        if (size <= 0 || (size_t)size > devs.size()) return;
+        std::vector<size_t> idx((size_t)size);
+        for (size_t i = 0; i < (size_t)size; ++i) idx[i] = i;
+        Set cur((size_t)size);
+        for (;;) {
+            for (size_t i = 0; i < (size_t)size; ++i) cur[i] = devs[idx[i]];
+            cb(cur);
+            int lvl = size - 1;
+            while (lvl >= 0 && idx[(size_t)lvl] == devs.size() - (size_t)(size - lvl)) --lvl;
+            if (lvl < 0) return;
+            ++idx[(size_t)lvl];
+            for (size_t i = (size_t)lvl + 1; i < (size_t)size; ++i) idx[i] = idx[i - 1] + 1;
+        }
+    }
+
+    // iterateGPUPartitions
+    template <typename F>
+    void partitions(Set devices, int size, F &&cb) const {
+        if (size <= 0 || (size_t)size > devices.size()) return;
+        if (size == 1) {
+            for (int d : devices) cb(Partition{Set{d}});
+            return;
+        }
+        while (devices.size() % (size_t)size != 0) devices.push_back(kPad);
+        const int pad = padding(devices);
+        Partition accum;
+        recurse(devices, size, pad, accum, cb);
+    }
+    template <typename F>
+    void recurse(const Set &devices, int size, int pad, Partition &accum, F &&cb) const {
+        if ((size_t)size == devices.size()) {
+            accum.push_back(devices);
+            cb(accum);
+            accum.pop_back();
+            return;
+        }
+        const Set rest(devices.begin() + 1, devices.end());
+        sets(rest, size - 1, [&](const Set &tail) {
+            Set set;
+            set.push_back(devices[0]);
+            set.insert(set.end(), tail.begin(), tail.end());
+            const int p = padding(set);
+            if (!(p == 0 || p == pad)) return;
+            Set remaining;
+            for (int d : devices)
+                if (!contains(set, d)) remaining.push_back(d);
+            accum.push_back(set);
+            recurse(remaining, size, pad, accum, cb);
+            accum.pop_back();
+        });
+    }
+};
+
+}  // namespace
+
 extern "C" {
+
+int vgpu_best_effort(const int *available, size_t n_available, const int *required, size_t n_required, int size,
+                     const int *pair_score, size_t n_dev, int *out, size_t out_cap) {
+    if ((!available && n_available) || (!required && n_required) || !pair_score || !out) return fail(VGPU_E_INVAL, "null argument");
+    for (size_t i = 0; i < n_available; ++i)
+        if (available[i] < 0 || (size_t)available[i] >= n_dev) return fail(VGPU_E_INVAL, "device index %d outside the score matrix", available[i]);
+    for (size_t i = 0; i < n_required; ++i)
+        if (required[i] < 0 || (size_t)required[i] >= n_dev) return fail(VGPU_E_INVAL, "device index %d outside the score matrix", required[i]);
+    if (size <= 0 || n_available < (size_t)size || n_required > (size_t)size) return 0;  // besteffort_policy.go:35-45
+    const BestEffort be{pair_score, n_dev};
+    const Set avail(available, available + n_available), req(required, required + n_required);
+    Partition best;
+    bool have = false;
+    int best_score = 0;
+    be.partitions(avail, size, [&](const Partition &cand) {
+        bool ok = false;  // gpuPartitionContainsSetWithAll: a padding-free set holding every required device
+        for (const Set &s : cand) ok = ok || (BestEffort::contains_all(s, req) && BestEffort::padding(s) == 0);
+        if (!ok) return;
+        const int sc = be.partition_score(cand);
+        if (sc > best_score || !have) {
+            best = cand;
+            best_score = sc;
+            have = true;
+        }
+    });
+    const Set *best_set = nullptr;
+    int set_score = 0;
+    for (const Set &s : best) {
+        if (!BestEffort::contains_all(s, req)) continue;
+        const int sc = be.set_score(s);
+        if (!best_set || sc > set_score) {
+            best_set = &s;
+            set_score = sc;
+        }
+    }
+    if (!best_set) return 0;
+    if (best_set->size() > out_cap) return fail(VGPU_E_RANGE, "need room for %zu devices", best_set->size());
+    for (size_t i = 0; i < best_set->size(); ++i) out[i] = (*best_set)[i];
+    return (int)best_set->size();
+}
 
 int vgpu_split(const char *uuid, uint64_t total_mib, unsigned split, double mem_scaling, vgpu_desc_t *out,
                size_t out_cap) {

@@ -261,6 +261,31 @@ class VDeviceController:
             self.release(usingStr.split(annSep))
 
 
+def bestEffortPolicy(pair_score: Dict[str, Dict[str, int]]) -> Callable[[List[str], List[str], int], List[str]]:
+    """gpuallocator.NewBestEffortPolicy() over physical UUIDs (besteffort_policy.go:34-90) through
+    vgpu_best_effort.  `pair_score[a][b]` is calculateGPUPairScore(a, b) (:296-352): 100 per NVLink
+    between the two GPUs, 10..60 for PCIe proximity — what gpuallocator.NewDevicesFrom would read from
+    NVML; a mock supplies it in tests."""
+    uuids = sorted(pair_score)
+    index = {u: i for i, u in enumerate(uuids)}
+    n = len(uuids)
+    flat = (C.c_int * max(1, n * n))()
+    for a in uuids:
+        for b, v in pair_score[a].items():
+            flat[index[a] * n + index[b]] = int(v)
+
+    def allocate(available: List[str], required: List[str], size: int) -> List[str]:
+        if any(u not in index for u in list(available) + list(required)):
+            return []
+        av = (C.c_int * max(1, len(available)))(*[index[u] for u in available])
+        rq = (C.c_int * max(1, len(required)))(*[index[u] for u in required])
+        out = (C.c_int * max(1, size if size > 0 else 1))()
+        k = capi.check(capi.lib.vgpu_best_effort(av, len(available), rq, len(required), size, flat, n, out, len(out)))
+        return [uuids[out[i]] for i in range(k) if out[i] >= 0]
+
+    return allocate
+
+
 class ResourceManager:
     """nvidia.go:43-46; here a list supplied by the caller (a mock NVML in tests)."""
 
@@ -431,7 +456,10 @@ class NvidiaDevicePlugin:
         return specs
 
 
-def NewNvidiaDevicePlugin(resourceManager: ResourceManager, flags: Optional[Flags] = None) -> NvidiaDevicePlugin:
-    """migStrategyNone.GetPlugins (mig-strategy.go:62-71)."""
-    return NvidiaDevicePlugin("nvidia.com/gpu", resourceManager, "NVIDIA_VISIBLE_DEVICES", simplePolicy,
+def NewNvidiaDevicePlugin(resourceManager: ResourceManager, flags: Optional[Flags] = None,
+                          pair_score: Optional[Dict[str, Dict[str, int]]] = None) -> NvidiaDevicePlugin:
+    """migStrategyNone.GetPlugins (mig-strategy.go:62-71): the best-effort policy when the caller
+    supplies the NVML link scores, else the topology-blind stand-in."""
+    policy = bestEffortPolicy(pair_score) if pair_score else simplePolicy
+    return NvidiaDevicePlugin("nvidia.com/gpu", resourceManager, "NVIDIA_VISIBLE_DEVICES", policy,
                               DevicePluginPath + "nvidia-gpu.sock", flags)

@@ -87,6 +87,18 @@ int vgpu_sm_limit(unsigned split, double cores_scaling);
 int vgpu_lookup(const vgpu_desc_t *all, size_t n_all, const char *const *ids,
                 size_t n_ids, const vgpu_desc_t **out);
 
+/* Replaces gpuallocator.NewBestEffortPolicy().Allocate (vendor/github.com/NVIDIA/go-gpuallocator/
+ * gpuallocator/besteffort_policy.go:34-90): among all ways of dividing `available` into sets of
+ * `size`, take the division with the highest total pair score that has a padding-free set containing
+ * all of `required`, and return that division's best set containing them.  Devices are named by their
+ * index into the n_dev x n_dev symmetric `pair_score` matrix (calculateGPUPairScore, :296-352: 100 per
+ * NVLink, 10..60 for PCIe proximity).  Ties keep the first candidate in the reference's enumeration
+ * order.  Returns the number of devices written to `out` (0 = no allocation) or VGPU_E_*.
+ * (The reference's result for partitions of 6 or more sets depends on Go slice aliasing inside
+ * iterateGPUPartitions; this restatement is exact up to 5 sets, i.e. for every case on <= 10 GPUs.) */
+int vgpu_best_effort(const int *available, size_t n_available, const int *required, size_t n_required,
+                     int size, const int *pair_score, size_t n_dev, int *out, size_t out_cap);
+
 /* Replaces the per-container body of Allocate (server.go:459-524) for the
  * non-MIG, non-monitor, non-legacy path: env map (insertion order is not
  * significant in the reference — Go map — we emit a fixed order) and the

@@ -121,3 +121,67 @@ def preferred_allocation(vdevices, available_ids, must_include_ids, size, policy
                 out.append(vd["ID"])
                 break
     return out
+
+
+# ---- bestEffortPolicy (vendor/github.com/NVIDIA/go-gpuallocator/gpuallocator/besteffort_policy.go) ----
+# Independent restatement (itertools) used to cross-check vgpu_best_effort.  Devices are indices into
+# the pair-score matrix; None is the reference's nil padding.
+import itertools
+
+
+def _pair(score, a, b):
+    return 0 if a is None or b is None or a == b else score[a][b]
+
+
+def _set_score(score, s):
+    return sum(_pair(score, a, b) for a, b in itertools.combinations(s, 2))
+
+
+def _partitions(devices, size):
+    """iterateGPUPartitions (besteffort_policy.go:216-292), same enumeration order."""
+    if size <= 0 or size > len(devices):
+        return
+    if size == 1:
+        for d in devices:
+            yield [[d]]
+        return
+    devices = list(devices)
+    while len(devices) % size:
+        devices.append(None)
+    padding = devices.count(None)
+
+    def rec(devs, accum):
+        if size == len(devs):
+            yield accum + [devs]
+            return
+        for tail in itertools.combinations(devs[1:], size - 1):
+            st = [devs[0]] + list(tail)
+            p = st.count(None)
+            if not (p == 0 or p == padding):
+                continue
+            remaining = [d for d in devs if d not in st]
+            yield from rec(remaining, accum + [st])
+
+    yield from rec(devices, [])
+
+
+def best_effort(available, required, size, score):
+    """bestEffortPolicy.Allocate (besteffort_policy.go:34-90)."""
+    if size <= 0 or len(available) < size or len(required) > size:
+        return []
+    best, best_score = None, 0
+    for cand in _partitions(available, size):
+        if not any(all(r in st for r in required) and st.count(None) == 0 for st in cand):
+            continue
+        sc = sum(_set_score(score, st) for st in cand)
+        if sc > best_score or best is None:
+            best, best_score = cand, sc
+    filtered = [st for st in (best or []) if all(r in st for r in required)]
+    if not filtered:
+        return []
+    best_set, bs = filtered[0], _set_score(score, filtered[0])
+    for st in filtered[1:]:
+        sc = _set_score(score, st)
+        if sc > bs:
+            best_set, bs = st, sc
+    return best_set
