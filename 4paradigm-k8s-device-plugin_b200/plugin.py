@@ -261,6 +261,36 @@ class VDeviceController:
             self.release(usingStr.split(annSep))
 
 
+XidCriticalError = 8  # nvml.XidCriticalError (nvmlEventTypeXidCriticalError)
+
+
+def checkHealth(devices: Sequence[Device], events: Sequence[dict], disable: str = "") -> List[Device]:
+    """nvidia.go:166-237 over an injected event source (NVML's WaitForEvent loop stays with the Go
+    host).  Returns, in order, the devices that would be sent down the `unhealthy` channel.
+    event = {"Etype": int, "Edata": xid, "UUID": str|None, "GpuInstanceId": int, "ComputeInstanceId": int,
+             "err": bool}; `disable` = $DP_DISABLE_HEALTHCHECKS."""
+    disable = disable.lower()
+    if disable == "all":
+        disable = "xids"
+    if "xids" in disable:
+        return []
+    out: List[Device] = []
+    for e in events:
+        if e.get("err") and e.get("Etype") != XidCriticalError:
+            continue
+        if e.get("Edata") in (31, 43, 45):  # application errors: the GPU is still healthy
+            continue
+        uuid = e.get("UUID")
+        if not uuid:
+            out.extend(devices)             # "All devices will go unhealthy."
+            continue
+        for d in devices:
+            # a full-GPU UUID (not a MIG device): gi = ci = 0xFFFFFFFF
+            if d.ID == uuid and e.get("GpuInstanceId", 0xFFFFFFFF) == 0xFFFFFFFF and e.get("ComputeInstanceId", 0xFFFFFFFF) == 0xFFFFFFFF:
+                out.append(d)
+    return out
+
+
 def bestEffortPolicy(pair_score: Dict[str, Dict[str, int]]) -> Callable[[List[str], List[str], int], List[str]]:
     """gpuallocator.NewBestEffortPolicy() over physical UUIDs (besteffort_policy.go:34-90) through
     vgpu_best_effort.  `pair_score[a][b]` is calculateGPUPairScore(a, b) (:296-352): 100 per NVLink

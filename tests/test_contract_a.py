@@ -154,3 +154,25 @@ def test_caller_array_too_small_is_reported(vgpu):
     lib, capi = vgpu.capi.lib, vgpu.capi
     arr = (capi.Desc * 2)()
     assert lib.vgpu_split(UUID.encode(), 1024, 4, 1.0, arr, 2) == capi.E_RANGE
+
+
+def test_check_health_xid_rules(vgpu):
+    """nvidia.go:166-237: XIDs 31/43/45 are application errors; an event without UUID takes every GPU
+    down; otherwise only the GPU it names; health checks can be disabled; unhealthy vGPUs show up in the
+    next ListAndWatch message and never recover."""
+    P = vgpu.plugin
+    devs = [P.Device(f"GPU-{i}", memory_mib=1024) for i in range(3)]
+    ev = lambda xid, uuid=None: {"Etype": P.XidCriticalError, "Edata": xid, "UUID": uuid}  # noqa: E731
+    assert P.checkHealth(devs, [ev(31, "GPU-1"), ev(43, "GPU-1"), ev(45, None)]) == []
+    assert P.checkHealth(devs, [ev(79, "GPU-1")]) == [devs[1]]
+    assert P.checkHealth(devs, [ev(48, None)]) == devs
+    assert P.checkHealth(devs, [ev(79, "GPU-9")]) == []
+    assert P.checkHealth(devs, [{"Etype": 0, "Edata": 79, "UUID": "GPU-1", "err": True}]) == []   # WaitForEvent timeout
+    assert P.checkHealth(devs, [ev(79, "GPU-1")], disable="all") == [] == P.checkHealth(devs, [ev(79, "GPU-1")], disable="XIDS")
+    assert P.checkHealth(devs, [{**ev(79, "GPU-1"), "GpuInstanceId": 3, "ComputeInstanceId": 0}]) == []  # a MIG slice's event
+    p = P.NewNvidiaDevicePlugin(P.ResourceManager(devs), P.Flags(deviceSplitCount=2))
+    p.initialize()
+    for d in P.checkHealth(p.cachedDevices, [ev(79, "GPU-2")]):
+        p.markUnhealthy(d)
+    msgs = list(p.ListAndWatch())
+    assert [d["Health"] for d in msgs[-1]] == ["Healthy"] * 4 + ["Unhealthy"] * 2
