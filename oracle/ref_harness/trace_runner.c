@@ -16,6 +16,8 @@
  *   launch <grid> <block>  cuLaunchKernel                 -> rc
  *   nvmlmem                nvmlDeviceGetMemoryInfo(dev0)  -> rc total free used
  *   ptrattrs <tag>         cuPointerGetAttributes{MEMORY_TYPE, IS_MANAGED} -> rc type managed
+ *   devcount               cuDeviceGetCount                -> rc n
+ *   devget <ordinal>       cuDeviceGet + cuDeviceGetUuid + cuDeviceGetPCIBusId -> rc dev uuid_last_byte busid
  *   setdev <d>             cuDevicePrimaryCtxRetain(d) + cuCtxSetCurrent   -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
  *   quit
@@ -44,6 +46,9 @@ CUresult cuMemHostRegister_v2(void *, size_t, unsigned);
 CUresult cuMemHostUnregister(void *);
 CUresult cuPointerGetAttributes(unsigned, int *, void **, CUdeviceptr);
 CUresult cuDevicePrimaryCtxRetain(void **, int);
+CUresult cuDeviceGetCount(int *);
+CUresult cuDeviceGetUuid(void *, int);
+CUresult cuDeviceGetPCIBusId(char *, int, int);
 CUresult cuCtxSetCurrent(void *);
 CUresult cuLaunchKernel(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **);
 
@@ -114,6 +119,18 @@ int main(void) {
         } else if (!strcmp(op, "launch")) {
             rc = cuLaunchKernel(NULL, (unsigned)a, 1, 1, (unsigned)b, 1, 1, 0, NULL, NULL, NULL);
             printf("%d\n", rc);
+        } else if (!strcmp(op, "devcount")) {
+            int n = -1;
+            rc = cuDeviceGetCount(&n);
+            printf("%d %d\n", rc, n);
+        } else if (!strcmp(op, "devget")) {
+            int dev = -1;
+            unsigned char uuid[16] = {0};
+            char bus[32] = "-";
+            rc = cuDeviceGet(&dev, (int)a);
+            int rc2 = rc == 0 ? cuDeviceGetUuid(uuid, dev) : -1;
+            int rc3 = rc == 0 ? cuDeviceGetPCIBusId(bus, sizeof(bus), dev) : -1;
+            printf("%d %d %d %u %d %s\n", rc, dev, rc2, (unsigned)uuid[15], rc3, bus);
         } else if (!strcmp(op, "setdev")) {
             void *ctx = NULL;
             rc = cuDevicePrimaryCtxRetain(&ctx, (int)a);
