@@ -273,6 +273,14 @@ uint64_t region_limit(int dev) {
 }
 uint64_t region_sm_limit(int dev) { return (dev < 0 || dev >= VGPU_MAX_DEVICES) ? 0 : g_reg->sm_limit[dev]; }
 
+void region_set_hostpid(int hostpid) {
+    if (!g_reg) return;
+    region_lock();
+    vgpu_proc_slot_t *s = my_slot();
+    if (s) s->hostpid = hostpid;
+    region_unlock();
+}
+
 int region_my_status(void) {
     vgpu_proc_slot_t *s = g_reg ? my_slot() : NULL;
     return s ? s->status : 1;

@@ -11,12 +11,14 @@
  * Hooked on the quota path (★ rows of SURVEY §8a):
  *   cuInit, cuDeviceTotalMem_v2, cuMemGetInfo_v2, cuMemAlloc_v2, cuMemAllocManaged,
  *   cuMemAllocPitch_v2, cuMemFree_v2, cuMemAllocHost_v2, cuMemHostAlloc, cuMemHostRegister_v2,
- *   cuDevicePrimaryCtxRetain, cuLaunchKernel, cuGetProcAddress(_v2), nvmlDeviceGetMemoryInfo(_v2),
- *   dlsym.  Everything else resolves straight to the real driver.
+ *   cuDevicePrimaryCtxRetain / Release, cuCtxCreate_v2 (context charge), cuLaunchKernel,
+ *   cuGetProcAddress(_v2), nvmlDeviceGetMemoryInfo(_v2), dlsym.  Everything else resolves straight
+ *   to the real driver.
  */
 #define _GNU_SOURCE
 #include <dlfcn.h>
 #include <errno.h>
+#include <fcntl.h>
 #include <pthread.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -108,6 +110,9 @@ REAL(CUresult, cuMemFreeHost, void *)
 REAL(CUresult, cuMemHostRegister_v2, void *, size_t, unsigned)
 REAL(CUresult, cuMemHostUnregister, void *)
 REAL(CUresult, cuDevicePrimaryCtxRetain, CUcontext *, CUdevice)
+REAL(CUresult, cuDevicePrimaryCtxRelease_v2, CUdevice)
+REAL(CUresult, cuCtxCreate_v2, CUcontext *, unsigned, CUdevice)
+REAL(CUresult, cuDeviceGetUuid, unsigned char *, CUdevice)
 REAL(CUresult, cuCtxSetCurrent, CUcontext)
 REAL(CUresult, cuCtxPushCurrent_v2, CUcontext)
 REAL(CUresult, cuLaunchKernel, void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **)
@@ -575,6 +580,126 @@ EXPORT CUresult cuMemHostRegister_v2(void *p, size_t n, unsigned flags) {
 }
 EXPORT CUresult cuMemHostRegister(void *p, size_t n, unsigned flags) { return cuMemHostRegister_v2(p, n, flags); }
 
+/* ------------------------------------------------------------------ context charge (a27)
+ * On a real node the reference bills every vGPU process for its CUDA context: set_task_pid@0x17de8
+ * lists the GPU's compute processes through NVML, retains the primary context, lists them again; the
+ * pid that appeared is this process as the HOST sees it (stored in the slot: the monitor needs it to
+ * match NVML's per-process figures to containers) and its usedGpuMemory is `context_size`
+ * (store @0x189de).  From then on the first cuDevicePrimaryCtxRetain@0x294bd / cuCtxCreate_v2@0x2a4dd
+ * on a device adds context_size to the usage as kind 0 (@0x29c86, @0x2a80e) and sets a per-device flag;
+ * cuDevicePrimaryCtxRelease_v2@0x29f08 clears the flag WITHOUT giving the bytes back (@0x2a0bf), so a
+ * retain / release / retain sequence is billed twice; cuCtxDestroy gives nothing back either.  All of
+ * that is reproduced (tests/golden/quota_ctx_*.json.gz, captured from the reference with the mock NVML
+ * listing the process).  What differs: the reference probes at cuInit with an extra retain + release
+ * of device 0 (one context creation and teardown per process start, ~0.2 s on a B200); here the probe
+ * wraps the first retain / create the application makes itself, so nothing is created twice. */
+static uint64_t g_context_size;
+static int g_ctx_probed;
+static int g_ctx_flag[VGPU_MAX_DEVICES];  /* vdevices[d].flag (+0x14) */
+static pthread_mutex_t g_ctx_mu = PTHREAD_MUTEX_INITIALIZER;
+
+typedef struct { unsigned pid; unsigned long long used; unsigned gi, ci; } nv_proc_t;  /* _v2/_v3 layout, 24 B */
+#define PROBE_MAX 256
+
+static void *nvml_handle_for(CUdevice dev) {
+    typedef int (*byuuid_t)(const char *, void **);
+    typedef int (*byidx_t)(unsigned, void **);
+    void *h = NULL;
+    unsigned char u[16];
+    byuuid_t byuuid = (byuuid_t)nvml_sym("nvmlDeviceGetHandleByUUID");
+    if (byuuid && get_cuDeviceGetUuid() && real_cuDeviceGetUuid(u, dev) == 0) {
+        char s[64];
+        snprintf(s, sizeof(s), "GPU-%02x%02x%02x%02x-%02x%02x-%02x%02x-%02x%02x-%02x%02x%02x%02x%02x%02x", u[0], u[1], u[2],
+                 u[3], u[4], u[5], u[6], u[7], u[8], u[9], u[10], u[11], u[12], u[13], u[14], u[15]);
+        if (byuuid(s, &h) == 0) return h;
+    }
+    byidx_t byidx = (byidx_t)nvml_sym("nvmlDeviceGetHandleByIndex_v2");
+    if (!byidx) byidx = (byidx_t)nvml_sym("nvmlDeviceGetHandleByIndex");
+    return (byidx && byidx((unsigned)dev, &h) == 0) ? h : NULL;
+}
+
+/* -> number of compute processes on the device (pid / used filled), -1 if NVML cannot tell */
+static int list_procs(void *h, nv_proc_t *out) {
+    typedef int (*procs_t)(void *, unsigned *, void *);
+    unsigned n = PROBE_MAX;
+    procs_t f = (procs_t)nvml_sym("nvmlDeviceGetComputeRunningProcesses_v3");
+    if (!f) f = (procs_t)nvml_sym("nvmlDeviceGetComputeRunningProcesses_v2");
+    if (f) return f(h, &n, out) == 0 ? (int)n : -1;
+    f = (procs_t)nvml_sym("nvmlDeviceGetComputeRunningProcesses");  /* 16-byte entries */
+    struct { unsigned pid; unsigned long long used; } v1[PROBE_MAX];
+    if (!f || f(h, &n, v1) != 0) return -1;
+    for (unsigned i = 0; i < n; ++i) {
+        out[i].pid = v1[i].pid;
+        out[i].used = v1[i].used;
+    }
+    return (int)n;
+}
+
+/* try_lock_unified_lock@0x171ac: /tmp/vgpulock is a host directory every vGPU container mounts, so
+ * probes of different containers on one GPU do not see each other's new process.  The reference spins
+ * on it forever; here a missing directory or a lock nobody releases within 10 s is passed by. */
+static int unified_lock(void) {
+    for (int i = 0; i < 10000; ++i) {
+        int fd = open("/tmp/vgpulock/lock", O_CREAT | O_EXCL | O_WRONLY, 0666);
+        if (fd >= 0) {
+            close(fd);
+            return 1;
+        }
+        if (errno != EEXIST) return 0;
+        usleep(1000);
+    }
+    SHIM_WARN("/tmp/vgpulock/lock held for 10 s: probing without it");
+    return 0;
+}
+
+/* Runs `make_ctx` (the application's own first retain / create) between two NVML process listings. */
+static CUresult probe_around(CUdevice dev, CUresult (*make_ctx)(void *), void *arg) {
+    static nv_proc_t before[PROBE_MAX], after[PROBE_MAX];
+    g_ctx_probed = 1;
+    void *h = nvml_handle_for(dev);
+    int locked = h ? unified_lock() : 0;
+    int nb = h ? list_procs(h, before) : -1;
+    CUresult rc = make_ctx(arg);
+    if (rc == 0 && nb >= 0) {
+        int na = list_procs(h, after);
+        for (int i = 0; i < na; ++i) {
+            int known = 0;
+            for (int j = 0; j < nb; ++j) known |= before[j].pid == after[i].pid;
+            if (known) continue;
+            /* getextrapid@0x17a4f + set_host_pid@0x4497c; ~0ull = NVML_VALUE_NOT_AVAILABLE (e.g. under WDDM / vGPU hosts) */
+            g_context_size = after[i].used == ~0ull ? 0 : after[i].used;
+            region_set_hostpid((int)after[i].pid);
+            SHIM_INFO("host pid %u, context size %lu", after[i].pid, (unsigned long)g_context_size);
+            break;
+        }
+    }
+    if (rc == 0 && !g_context_size) SHIM_WARN("SET_TASK_PID FAILED.");  /* libvgpu.c:905 */
+    if (locked) unlink("/tmp/vgpulock/lock");
+    return rc;
+}
+
+static void charge_context(CUdevice dev, int created) {
+    if (dev < 0 || dev >= VGPU_MAX_DEVICES) return;
+    if (g_ctx_flag[dev]) {
+        if (created) SHIM_ERR("Duplicate cuCtxCreate, this may indicate errors");  /* context.c:144 */
+        return;
+    }
+    if (g_context_size && g_region_ok) region_add_usage(dev, g_context_size, VGPU_USE_CONTEXT);
+    g_ctx_flag[dev] = 1;
+}
+
+struct retain_args { CUcontext *pctx; CUdevice dev; unsigned flags; };
+static CUresult do_retain(void *a) {
+    struct retain_args *r = (struct retain_args *)a;
+    cuDevicePrimaryCtxRetain_t f = get_cuDevicePrimaryCtxRetain();
+    return f ? f(r->pctx, r->dev) : 3;
+}
+static CUresult do_create(void *a) {
+    struct retain_args *r = (struct retain_args *)a;
+    cuCtxCreate_v2_t f = get_cuCtxCreate_v2();
+    return f ? f(r->pctx, r->flags, r->dev) : 3;
+}
+
 /* ------------------------------------------------------------------ SM cap: green contexts
  * Replaces rate_limiter@0x463b1 / utilization_watcher@0x471a7 (a25).  CUDA_DEVICE_SM_LIMIT=p
  * with 0 < p < 100 turns into a green context of floor(SMs*p/100) SMs (stepped down to the
@@ -674,8 +799,12 @@ EXPORT void *cuVGPUPartitionCtx(CUdevice dev) {
 EXPORT CUresult cuDevicePrimaryCtxRetain(CUcontext *pctx, CUdevice dev) {
     ensure_initialized();
     SHIM_DEBUG("cuDevicePrimaryCtxRetain(dev=%d)", dev);
-    cuDevicePrimaryCtxRetain_t f = get_cuDevicePrimaryCtxRetain();
-    CUresult rc = f ? f(pctx, dev) : 3;
+    if (tl_bypass) return get_cuDevicePrimaryCtxRetain()(pctx, dev);
+    struct retain_args a = {pctx, dev, 0};
+    pthread_mutex_lock(&g_ctx_mu);
+    CUresult rc = (!g_ctx_probed && g_region_ok) ? probe_around(dev, do_retain, &a) : do_retain(&a);
+    if (rc == 0) charge_context(dev, 0);
+    pthread_mutex_unlock(&g_ctx_mu);
     if (rc != 0) return rc;
     if (dev >= 0 && dev < VGPU_MAX_DEVICES) {
         g_primary_ctx[dev] = *pctx;
@@ -683,6 +812,30 @@ EXPORT CUresult cuDevicePrimaryCtxRetain(CUcontext *pctx, CUdevice dev) {
     }
     return 0;
 }
+
+EXPORT CUresult cuDevicePrimaryCtxRelease_v2(CUdevice dev) {
+    cuDevicePrimaryCtxRelease_v2_t f = get_cuDevicePrimaryCtxRelease_v2();
+    CUresult rc = f ? f(dev) : 3;
+    if (!tl_bypass && dev >= 0 && dev < VGPU_MAX_DEVICES) {
+        pthread_mutex_lock(&g_ctx_mu);
+        g_ctx_flag[dev] = 0;  /* @0x2a0bf: the flag goes, the bytes stay billed */
+        pthread_mutex_unlock(&g_ctx_mu);
+    }
+    return rc;
+}
+EXPORT CUresult cuDevicePrimaryCtxRelease(CUdevice dev) { return cuDevicePrimaryCtxRelease_v2(dev); }
+
+EXPORT CUresult cuCtxCreate_v2(CUcontext *pctx, unsigned flags, CUdevice dev) {
+    if (tl_bypass) return get_cuCtxCreate_v2()(pctx, flags, dev);
+    ensure_initialized();
+    struct retain_args a = {pctx, dev, flags};
+    pthread_mutex_lock(&g_ctx_mu);
+    CUresult rc = (!g_ctx_probed && g_region_ok) ? probe_around(dev, do_create, &a) : do_create(&a);
+    if (rc == 0) charge_context(dev, 1);
+    pthread_mutex_unlock(&g_ctx_mu);
+    return rc;
+}
+EXPORT CUresult cuCtxCreate(CUcontext *pctx, unsigned flags, CUdevice dev) { return cuCtxCreate_v2(pctx, flags, dev); }
 
 /* cudart keeps its own handle on the primary context (it has it before it ever calls
  * cuDevicePrimaryCtxRetain) and binds THAT.  So: whenever a context is bound, find out whether
@@ -899,6 +1052,8 @@ static const hook_t g_hooks[] = {
     {"cuMemHostAlloc", (void *)cuMemHostAlloc},
     {"cuMemHostRegister", (void *)cuMemHostRegister_v2}, {"cuMemHostRegister_v2", (void *)cuMemHostRegister_v2},
     {"cuDevicePrimaryCtxRetain", (void *)cuDevicePrimaryCtxRetain},
+    {"cuDevicePrimaryCtxRelease", (void *)cuDevicePrimaryCtxRelease_v2}, {"cuDevicePrimaryCtxRelease_v2", (void *)cuDevicePrimaryCtxRelease_v2},
+    {"cuCtxCreate", (void *)cuCtxCreate_v2}, {"cuCtxCreate_v2", (void *)cuCtxCreate_v2},
     {"cuCtxSetCurrent", (void *)cuCtxSetCurrent},
     {"cuCtxGetCurrent", (void *)cuCtxGetCurrent},
     {"cuCtxPopCurrent", (void *)cuCtxPopCurrent_v2}, {"cuCtxPopCurrent_v2", (void *)cuCtxPopCurrent_v2},

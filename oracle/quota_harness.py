@@ -78,6 +78,9 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
                     replies.append(line.strip())
                 trace = []
             for p, op in trace:
+                if op == "@slots":  # answered by the harness: the live process slots of the cache file
+                    replies.append(live_slots(open(cache, "rb").read(), [pr.pid for pr in procs]))
+                    continue
                 procs[p].stdin.write(op + "\n")
                 procs[p].stdin.flush()
                 line = procs[p].stdout.readline()
@@ -107,6 +110,24 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
                 calls.append(line)
         region = open(cache, "rb").read() if keep_region and os.path.exists(cache) else b""
     return {"replies": replies, "oom": sorted(oom), "calls": calls, "region": region}
+
+
+def live_slots(b: bytes, pids) -> str:
+    """One token per live slot, in slot order: runner#:hostpid-is-its-pid:status then per device with any usage
+    d<dev>=context/module/data/total.  Pids become runner numbers so that runs compare."""
+    n = struct.unpack_from("<i", b, 0xC4738)[0]
+    out = []
+    for s in range(n):
+        o = SLOT0 + s * STRIDE
+        pid, hostpid = struct.unpack_from("<ii", b, o)
+        who = pids.index(pid) if pid in pids else -1
+        tok = f"p{who}:{int(hostpid == pid)}:{struct.unpack_from('<i', b, o + 0x308)[0]}"
+        for d in range(16):
+            u = struct.unpack_from("<5Q", b, o + 8 + d * 0x28)
+            if any(u):
+                tok += f" d{d}={u[0]}/{u[1]}/{u[2]}/{u[4]}"
+        out.append(tok)
+    return f"n={n} " + " | ".join(out)
 
 
 def mask_region(b: bytes) -> bytes:
@@ -155,6 +176,57 @@ def appendix_a_trace():
     ops = ["total 0", "info", f"alloc {100 << 20} 1", "info", "freeptr 0xdeadbeef000", "freeptr 0", "free 1", "free 1",
            "alloc 0 2", "info"]
     return [(0, o) for o in ops]
+
+
+def ctx_trace():
+    """Context billing on one device (reference: cuDevicePrimaryCtxRetain@0x294bd, Release_v2@0x29f08,
+    cuCtxCreate_v2@0x2a4dd): first retain billed, second not, release forgets the flag but keeps the bytes,
+    so the next retain is billed again; cuCtxCreate after a retain is a logged duplicate; destroy refunds nothing."""
+    MiB = 1 << 20
+    ops = ["info", "retain 0 1", "@slots", "info", "retain 0 2", "info", "ctxset 1", "ctxget", "ctxdev", f"alloc {MiB} 1", "@slots",
+           "release 0", "info", "release 0", "info", "retain 0 3", "@slots", "info", "ctxcreate 0 4", "info", "ctxget", "ctxdev",
+           "ctxdestroy 4", "info", "ctxget", "release 0", "ctxcreate 0 5", "info", "ctxcreate 0 6", "@slots", "total 0", "nvmlmem",
+           f"alloc {200 * MiB} 2", f"alloc {100 * MiB} 3", "info", "free 1", "free 2", "@slots"]
+    return [(0, o) for o in ops]
+
+
+def ctx_create_first_trace():
+    """A driver-API program whose first context comes from cuCtxCreate.  (No primary retain after it: the
+    reference then hands back the created — here already destroyed — context as the primary one, a remap
+    artefact that is not reproduced.)"""
+    MiB = 1 << 20
+    ops = ["ctxcreate 0 1", "@slots", "info", f"alloc {600 * MiB} 1", f"alloc {200 * MiB} 2", "info", "ctxdestroy 1", "info",
+           "ctxcreate 0 2", "info", "ctxget", "ctxdev", "free 1", f"alloc {200 * MiB} 3", "info", "@slots"]
+    return [(0, o) for o in ops]
+
+
+def ctx_two_devices_trace():
+    """Two devices: each billed on its own first retain; the current context decides whose quota an allocation hits."""
+    MiB = 1 << 20
+    ops = ["retain 1 1", "@slots", "info", "ctxset 1", "ctxdev", "info", f"alloc {MiB} 1", "info", "retain 0 2", "ctxset 2", "info",
+           "ctxpush 1", "ctxdev", "info", "ctxpop", "ctxdev", "info", "total 0", "total 1", f"alloc {800 * MiB} 2", f"alloc {800 * MiB} 3",
+           "ctxset 1", f"alloc {800 * MiB} 4", f"alloc {800 * MiB} 5", f"alloc {800 * MiB} 6", "@slots", "release 1", "retain 1 3", "info",
+           "@slots"]
+    return [(0, o) for o in ops]
+
+
+def ctx_procs_trace(nprocs=4):
+    """Several processes of one vGPU: every one pays for its context; the sum can pass the limit without any
+    allocation (retain is never refused), after which cuMemGetInfo answers 1 and allocations -1."""
+    MiB = 1 << 20
+    out = []
+    for p in range(nprocs):
+        out += [(p, "retain 0 1"), (p, "info"), (p, f"alloc {50 * MiB} 1")]
+    out.append((0, "@slots"))  # after every process has a context: the reference knows its host pid from cuInit on, the shim from the first context on
+    for p in range(nprocs):
+        out += [(p, "free 1"), (p, "info"), (p, "hostalloc 4096 2")]
+    out.append((0, "@slots"))
+    return out
+
+
+def with_contexts(trace, nprocs):
+    """Prefix: every process retains the primary context of device 0 (what any CUDA runtime program does)."""
+    return [(p, "retain 0 1") for p in range(nprocs)] + list(trace)
 
 
 def random_trace(seed, nops, nprocs=1, max_bytes=1 << 30, kinds=True):

@@ -8,6 +8,8 @@
  *   MOCK_GPU_COUNT   number of devices (default 1, max 16)
  *   MOCK_TOTAL_MIB   physical memory per device in MiB (default 16384)
  *   MOCK_CUDA_LOG    append one line per "real" driver call to this file
+ *   MOCK_CTX_MIB     what a live context costs per device, as the mock NVML's process list reports it
+ *                    (default 0: no process is ever listed, the reference's host-pid probe finds nothing)
  *   MOCK_FAIL_ALLOC_OVER  bytes; cuMemAlloc_v2 / cuMemAllocManaged above this size fail with 2 (OOM)
  */
 #define _GNU_SOURCE
@@ -65,10 +67,24 @@ static void logf_(const char *fmt, ...) {
     fclose(f);
 }
 
-static int cur_dev(void) {
+/* contexts made by cuCtxCreate: distinct handles, each bound to a device */
+#define MAXCREATED 32
+static char g_created[MAXCREATED][64];
+static int g_created_dev[MAXCREATED];  /* -1 = free (set in cfg) / destroyed */
+static int g_created_n;
+static CUcontext g_stack[32];
+static int g_top;
+
+static int ctx_dev(CUcontext c) {
     for (int i = 0; i < MAXDEV; ++i)
-        if (g_cur == (CUcontext)g_ctx_storage[i]) return i;
-    return 0;
+        if (c == (CUcontext)g_ctx_storage[i]) return i;
+    for (int i = 0; i < g_created_n; ++i)
+        if (c == (CUcontext)g_created[i]) return g_created_dev[i];
+    return -1;
+}
+static int cur_dev(void) {
+    int d = ctx_dev(g_cur);
+    return d < 0 ? 0 : d;
 }
 
 static CUresult do_alloc(CUdeviceptr *p, uint64_t n, int kind, const char *name, unsigned flags) {
@@ -117,18 +133,60 @@ CUresult cuDeviceGetByPCIBusId(CUdevice *d, const char *s) { (void)s; *d = 0; re
 CUresult cuDeviceTotalMem_v2(size_t *b, CUdevice d) { (void)d; cfg(); *b = g_total; return 0; }
 CUresult cuDeviceTotalMem(size_t *b, CUdevice d) { return cuDeviceTotalMem_v2(b, d); }
 
-CUresult cuDevicePrimaryCtxRetain(CUcontext *c, CUdevice d) { cfg(); *c = g_ctx_storage[d]; logf_("cuDevicePrimaryCtxRetain dev=%d", d); return 0; }
-CUresult cuDevicePrimaryCtxRelease_v2(CUdevice d) { (void)d; return 0; }
-CUresult cuDevicePrimaryCtxRelease(CUdevice d) { (void)d; return 0; }
-CUresult cuDevicePrimaryCtxGetState(CUdevice d, unsigned *flags, int *active) { (void)d; *flags = 0; *active = 1; return 0; }
+/* live contexts per device, read by the mock NVML (same process) to decide whether this process shows up in
+ * nvmlDeviceGetComputeRunningProcesses */
+static int g_ctx_refs[MAXDEV];
+int mock_cuda_ctx_refs(int d) { return (d >= 0 && d < MAXDEV) ? g_ctx_refs[d] : 0; }
+CUresult cuDevicePrimaryCtxRetain(CUcontext *c, CUdevice d) {
+    cfg();
+    if (d < 0 || d >= g_ndev) return 101;
+    *c = g_ctx_storage[d];
+    ++g_ctx_refs[d];
+    logf_("cuDevicePrimaryCtxRetain dev=%d", d);
+    return 0;
+}
+CUresult cuDevicePrimaryCtxRelease_v2(CUdevice d) { if (d >= 0 && d < MAXDEV && g_ctx_refs[d] > 0) --g_ctx_refs[d]; return 0; }
+CUresult cuDevicePrimaryCtxRelease(CUdevice d) { return cuDevicePrimaryCtxRelease_v2(d); }
+CUresult cuDevicePrimaryCtxGetState(CUdevice d, unsigned *flags, int *active) {
+    *flags = 0;
+    *active = (getenv("MOCK_CTX_MIB") && d >= 0 && d < MAXDEV) ? g_ctx_refs[d] > 0 : 1;  /* always-active without MOCK_CTX_MIB, as the first goldens were made */
+    return 0;
+}
 CUresult cuDevicePrimaryCtxSetFlags_v2(CUdevice d, unsigned f) { (void)d; (void)f; return 0; }
 CUresult cuDevicePrimaryCtxReset_v2(CUdevice d) { (void)d; return 0; }
-CUresult cuCtxCreate_v2(CUcontext *c, unsigned f, CUdevice d) { (void)f; cfg(); *c = g_ctx_storage[d]; g_cur = *c; return 0; }
-CUresult cuCtxDestroy_v2(CUcontext c) { (void)c; return 0; }
+CUresult cuCtxCreate_v2(CUcontext *c, unsigned f, CUdevice d) {
+    (void)f;
+    cfg();
+    if (d < 0 || d >= g_ndev) return 101;
+    if (g_created_n >= MAXCREATED) return 2;
+    g_created_dev[g_created_n] = d;
+    *c = g_created[g_created_n++];
+    ++g_ctx_refs[d];
+    if (g_top < 32) g_stack[g_top++] = g_cur;  /* a created context is pushed */
+    g_cur = *c;
+    logf_("cuCtxCreate_v2 dev=%d", d);
+    return 0;
+}
+CUresult cuCtxDestroy_v2(CUcontext c) {
+    for (int i = 0; i < g_created_n; ++i)
+        if (c == (CUcontext)g_created[i] && g_created_dev[i] >= 0) {
+            if (g_ctx_refs[g_created_dev[i]] > 0) --g_ctx_refs[g_created_dev[i]];
+            g_created_dev[i] = -1;
+            if (g_cur == c) g_cur = g_top > 0 ? g_stack[--g_top] : (CUcontext)g_ctx_storage[0];
+            logf_("cuCtxDestroy_v2");
+            return 0;
+        }
+    return 201; /* INVALID_CONTEXT */
+}
 CUresult cuCtxSetCurrent(CUcontext c) { cfg(); if (c) g_cur = c; return 0; }
 CUresult cuCtxGetCurrent(CUcontext *c) { cfg(); *c = g_cur; return 0; }
-CUresult cuCtxPushCurrent_v2(CUcontext c) { cfg(); g_cur = c; return 0; }
-CUresult cuCtxPopCurrent_v2(CUcontext *c) { cfg(); if (c) *c = g_cur; return 0; }
+CUresult cuCtxPushCurrent_v2(CUcontext c) { cfg(); if (g_top < 32) g_stack[g_top++] = g_cur; g_cur = c; return 0; }
+CUresult cuCtxPopCurrent_v2(CUcontext *c) {
+    cfg();
+    if (c) *c = g_cur;
+    if (g_top > 0) g_cur = g_stack[--g_top];
+    return 0;
+}
 CUresult cuCtxGetDevice(CUdevice *d) { cfg(); *d = cur_dev(); return 0; }
 CUresult cuCtxSynchronize(void) { return 0; }
 CUresult cuCtxGetApiVersion(CUcontext c, unsigned *v) { (void)c; *v = 12090; return 0; }

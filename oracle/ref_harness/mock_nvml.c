@@ -1,7 +1,12 @@
 /* mock_nvml.c — fake libnvidia-ml.so.1 for the differential quota harness.
- * TEST INFRASTRUCTURE ONLY.  No running processes are ever
+ * TEST INFRASTRUCTURE ONLY.  By default no running processes are
  * reported, so the reference's set_task_pid finds nothing, context_size stays 0 and its
- * rate limiter is bypassed: deterministic quota traces. */
+ * rate limiter is bypassed: deterministic quota traces.  With MOCK_CTX_MIB=<n> this process is
+ * listed on every device it holds a (mock) context on, using n MiB — which is how a real node
+ * looks to the host-pid probe, and what makes the reference charge the context to the quota. */
+#define _GNU_SOURCE
+#include <dlfcn.h>
+#include <unistd.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -37,9 +42,27 @@ nvmlReturn_t nvmlDeviceGetHandleByUUID(const char *uuid, nvmlDevice_t *d) {
 nvmlReturn_t nvmlDeviceGetIndex(nvmlDevice_t d, unsigned *i) { *i = (unsigned)idx_of(d); return 0; }
 nvmlReturn_t nvmlDeviceGetUUID(nvmlDevice_t d, char *uuid, unsigned len) { uuid_of(idx_of(d), uuid, len); return 0; }
 nvmlReturn_t nvmlDeviceGetName(nvmlDevice_t d, char *name, unsigned len) { (void)d; snprintf(name, len, "Mock B200"); return 0; }
-nvmlReturn_t nvmlDeviceGetComputeRunningProcesses(nvmlDevice_t d, unsigned *count, void *infos) { (void)d; (void)infos; *count = 0; return 0; }
-nvmlReturn_t nvmlDeviceGetComputeRunningProcesses_v2(nvmlDevice_t d, unsigned *count, void *infos) { (void)d; (void)infos; *count = 0; return 0; }
-nvmlReturn_t nvmlDeviceGetComputeRunningProcesses_v3(nvmlDevice_t d, unsigned *count, void *infos) { (void)d; (void)infos; *count = 0; return 0; }
+static uint64_t ctx_bytes(nvmlDevice_t d) {
+    const char *e = getenv("MOCK_CTX_MIB");
+    uint64_t mib = e ? strtoull(e, NULL, 0) : 0;
+    if (!mib) return 0;
+    int (*refs)(int) = (int (*)(int))dlsym(RTLD_DEFAULT, "mock_cuda_ctx_refs");
+    return (refs && refs(idx_of(d)) > 0) ? mib << 20 : 0;
+}
+/* v1 layout {u32 pid; u64 usedGpuMemory} = 16 B; v2/v3 add {u32 gpuInstanceId, computeInstanceId} = 24 B */
+static nvmlReturn_t procs(nvmlDevice_t d, unsigned *count, void *infos, size_t stride) {
+    uint64_t b = ctx_bytes(d);
+    if (!b) { *count = 0; return 0; }
+    if (*count < 1 || !infos) { *count = 1; return 7; /* INSUFFICIENT_SIZE */ }
+    memset(infos, 0, stride);
+    *(unsigned *)infos = (unsigned)getpid();
+    *(unsigned long long *)((char *)infos + 8) = b;
+    *count = 1;
+    return 0;
+}
+nvmlReturn_t nvmlDeviceGetComputeRunningProcesses(nvmlDevice_t d, unsigned *count, void *infos) { return procs(d, count, infos, 16); }
+nvmlReturn_t nvmlDeviceGetComputeRunningProcesses_v2(nvmlDevice_t d, unsigned *count, void *infos) { return procs(d, count, infos, 24); }
+nvmlReturn_t nvmlDeviceGetComputeRunningProcesses_v3(nvmlDevice_t d, unsigned *count, void *infos) { return procs(d, count, infos, 24); }
 nvmlReturn_t nvmlDeviceGetProcessUtilization(nvmlDevice_t d, void *u, unsigned *count, unsigned long long ts) { (void)d; (void)u; (void)ts; *count = 0; return 0; }
 typedef struct { unsigned long long total, free, used; } nvmlMemory_t;
 nvmlReturn_t nvmlDeviceGetMemoryInfo(nvmlDevice_t d, nvmlMemory_t *m) { (void)d; m->total = total(); m->free = total(); m->used = 0; return 0; }

@@ -19,6 +19,15 @@
  *   devcount               cuDeviceGetCount                -> rc n
  *   devget <ordinal>       cuDeviceGet + cuDeviceGetUuid + cuDeviceGetPCIBusId -> rc dev uuid_last_byte busid
  *   setdev <d>             cuDevicePrimaryCtxRetain(d) + cuCtxSetCurrent   -> rc
+ *   retain <d> <ctag>      cuDevicePrimaryCtxRetain(d), context remembered as <ctag> -> rc ctx#  (ctx# = order of first
+ *                          appearance of the handle in this run, 0 = NULL: handles compare across runs)
+ *   release <d>            cuDevicePrimaryCtxRelease_v2(d)                 -> rc
+ *   ctxcreate <d> <ctag>   cuCtxCreate_v2(flags 0, d)                      -> rc ctx#
+ *   ctxdestroy <ctag>      cuCtxDestroy_v2                                 -> rc
+ *   ctxset <ctag>          cuCtxSetCurrent(context <ctag>; tag 0 = NULL)   -> rc
+ *   ctxpush <ctag> / ctxpop   cuCtxPushCurrent_v2 / cuCtxPopCurrent_v2     -> rc [ctx#]
+ *   ctxget                 cuCtxGetCurrent                                 -> rc ctx#
+ *   ctxdev                 cuCtxGetDevice                                  -> rc dev
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
  *   quit
  */
@@ -50,11 +59,30 @@ CUresult cuDeviceGetCount(int *);
 CUresult cuDeviceGetUuid(void *, int);
 CUresult cuDeviceGetPCIBusId(char *, int, int);
 CUresult cuCtxSetCurrent(void *);
+CUresult cuCtxGetCurrent(void **);
+CUresult cuCtxGetDevice(int *);
+CUresult cuCtxCreate_v2(void **, unsigned, int);
+CUresult cuCtxDestroy_v2(void *);
+CUresult cuCtxPushCurrent_v2(void *);
+CUresult cuCtxPopCurrent_v2(void **);
+CUresult cuDevicePrimaryCtxRelease_v2(int);
 CUresult cuLaunchKernel(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **);
 
 #define MAXTAG 200000
 static CUdeviceptr tags[MAXTAG];
 static void *htags[MAXTAG];
+
+#define MAXCTX 64
+static void *ctags[MAXCTX];
+static void *seen[MAXCTX];
+static int nseen;
+static int ctx_no(void *c) {
+    if (!c) return 0;
+    for (int i = 0; i < nseen; ++i)
+        if (seen[i] == c) return i + 1;
+    if (nseen < MAXCTX) seen[nseen++] = c;
+    return nseen;
+}
 
 int main(void) {
     char line[256];
@@ -136,6 +164,31 @@ int main(void) {
             rc = cuDevicePrimaryCtxRetain(&ctx, (int)a);
             if (rc == 0) rc = cuCtxSetCurrent(ctx);
             printf("%d\n", rc);
+        } else if (!strcmp(op, "retain") || !strcmp(op, "ctxcreate")) {
+            void *ctx = NULL;
+            rc = op[0] == 'r' ? cuDevicePrimaryCtxRetain(&ctx, (int)a) : cuCtxCreate_v2(&ctx, 0, (int)a);
+            if (rc == 0 && b < MAXCTX) ctags[b] = ctx;
+            printf("%d %d\n", rc, rc == 0 ? ctx_no(ctx) : -1);
+        } else if (!strcmp(op, "release")) {
+            printf("%d\n", cuDevicePrimaryCtxRelease_v2((int)a));
+        } else if (!strcmp(op, "ctxdestroy")) {
+            printf("%d\n", cuCtxDestroy_v2(a < MAXCTX ? ctags[a] : NULL));
+        } else if (!strcmp(op, "ctxset")) {
+            printf("%d\n", cuCtxSetCurrent(a && a < MAXCTX ? ctags[a] : NULL));
+        } else if (!strcmp(op, "ctxpush")) {
+            printf("%d\n", cuCtxPushCurrent_v2(a < MAXCTX ? ctags[a] : NULL));
+        } else if (!strcmp(op, "ctxpop")) {
+            void *ctx = NULL;
+            rc = cuCtxPopCurrent_v2(&ctx);
+            printf("%d %d\n", rc, rc == 0 ? ctx_no(ctx) : -1);
+        } else if (!strcmp(op, "ctxget")) {
+            void *ctx = NULL;
+            rc = cuCtxGetCurrent(&ctx);
+            printf("%d %d\n", rc, rc == 0 ? ctx_no(ctx) : -1);
+        } else if (!strcmp(op, "ctxdev")) {
+            int dev = -1;
+            rc = cuCtxGetDevice(&dev);
+            printf("%d %d\n", rc, dev);
         } else if (!strcmp(op, "loop")) {
             struct timespec t0, t1;
             size_t f = 0, t = 0;
