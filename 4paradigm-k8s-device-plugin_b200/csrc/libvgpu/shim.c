@@ -24,6 +24,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <strings.h>
 #include <unistd.h>
 
 #include "region.h"
@@ -180,6 +181,8 @@ static int count_device_map(void) {
     return n;
 }
 
+static int device_map_uuids(char out[][VGPU_UUID_LEN], int max);
+
 static void pre_init(void) {
     vgpu_region_init_t init;
     memset(&init, 0, sizeof(init));
@@ -209,10 +212,20 @@ static void pre_init(void) {
     if (nv_init && nv_byidx && nv_uuid && nv_init() == 0) {
         unsigned n = 0;
         if (g_virtual_devices <= 0 && nv_count && nv_count(&n) == 0) g_virtual_devices = (int)n;
-        for (int i = 0; i < g_virtual_devices && i < VGPU_MAX_DEVICES; ++i) {
+        char want[VGPU_MAX_DEVICES][VGPU_UUID_LEN];
+        const int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
+        int nreal = g_virtual_devices;
+        if (nwant > 0 && nv_count && nv_count(&n) == 0) nreal = (int)n;
+        for (int i = 0, v = 0; i < nreal && i < VGPU_MAX_DEVICES && v < VGPU_MAX_DEVICES; ++i) {
             void *h = NULL;
-            if (nv_byidx((unsigned)i, &h) != 0) break;
-            if (nv_uuid(h, init.uuids[i], VGPU_UUID_LEN) != 0) break;
+            char u[VGPU_UUID_LEN];
+            if (nv_byidx((unsigned)i, &h) != 0 || nv_uuid(h, u, VGPU_UUID_LEN) != 0) break;
+            if (nwant == 0) {
+                memcpy(init.uuids[v++], u, VGPU_UUID_LEN);
+                continue;
+            }
+            for (int k = 0; k < nwant && v < VGPU_MAX_DEVICES; ++k)  /* one line per virtual device, physical order */
+                if (strcasecmp(want[k], u) == 0) memcpy(init.uuids[v++], u, VGPU_UUID_LEN);
         }
     }
     init.device_num = g_virtual_devices > 0 ? (uint64_t)g_virtual_devices : 0;
@@ -296,6 +309,105 @@ static void load_vmm_backend(void) {
     else start_mover();
 }
 
+/* ------------------------------------------------------------------ virtual devices (a28)
+ * NVIDIA_DEVICE_MAP="0:<UUID> 1:<UUID> ..." (Contract A, server.go:487-496) names the vGPUs of this
+ * container.  Two of them may sit on the same physical GPU (a pod that asked for two vGPUs usually gets
+ * neighbours of one split), and the container may see GPUs it was not given.  Observed from the
+ * reference (nvml/util.c parser@0x28a39, initial_virtual_devices@0x27f0d, cuda/device.c, cuda/context.c)
+ * under the mock driver, vectors in tests/golden/quota_remap_*.json.gz:
+ *   - the application sees one CUDA device per map entry, enumerated in physical order whatever the
+ *     order of the map; unlisted GPUs disappear;
+ *   - the 2nd, 3rd ... entry of one physical GPU is a device of its own: same UUID and attributes, PCI
+ *     function .1, .2 ... in its bus id, its own CUDA_DEVICE_MEMORY_LIMIT_<i> / SM limit / usage
+ *     column, and — because a physical device has one primary context — a context of its own, made
+ *     with cuCtxCreate the first time its "primary context" is retained (cuDevicePrimaryCtxRetain
+ *     @0x297be) and billed like any first context.
+ * CUdevice values handed to the application are the virtual ordinals; every entry point below that
+ * takes or returns one translates.  With no map, or a map that is the identity, nothing is translated.
+ * Not reproduced: the reference's rewritten UUID for the duplicate, its crash on an out-of-range
+ * ordinal (here CUDA_ERROR_INVALID_DEVICE), and its virtual NVML handles (here NVML keeps physical
+ * devices; memory info of a shared GPU is the sum of its vGPUs). */
+typedef struct {
+    int phys;       /* real CUDA ordinal */
+    int dup;        /* 0 = first vGPU of that GPU (owns the primary context), k = k-th further one */
+    CUcontext ctx;  /* dup > 0: the context standing in for a primary context */
+    int refs;
+} vdev_t;
+static vdev_t g_vdev[VGPU_MAX_DEVICES];
+static int g_nvdev;
+static int g_remap;  /* 0: identity, nothing to translate */
+static pthread_once_t g_vdev_once = PTHREAD_ONCE_INIT;
+
+static void uuid_text(const unsigned char *u, char *s, size_t n) {
+    snprintf(s, n, "GPU-%02x%02x%02x%02x-%02x%02x-%02x%02x-%02x%02x-%02x%02x%02x%02x%02x%02x", u[0], u[1], u[2], u[3], u[4],
+             u[5], u[6], u[7], u[8], u[9], u[10], u[11], u[12], u[13], u[14], u[15]);
+}
+
+/* the UUIDs of NVIDIA_DEVICE_MAP in map order; -> count */
+static int device_map_uuids(char out[][VGPU_UUID_LEN], int max) {
+    const char *m = getenv("NVIDIA_DEVICE_MAP");
+    int n = 0;
+    while (m && *m && n < max) {
+        while (*m == ' ') ++m;
+        if (!*m) break;
+        const char *end = m;
+        while (*end && *end != ' ') ++end;
+        const char *colon = memchr(m, ':', (size_t)(end - m));
+        const char *u = colon ? colon + 1 : m;
+        size_t len = (size_t)(end - u);
+        if (len > 0 && len < VGPU_UUID_LEN) {
+            memcpy(out[n], u, len);
+            out[n][len] = 0;
+            ++n;
+        }
+        m = end;
+    }
+    return n;
+}
+
+static void build_vdev(void) {  /* needs a successful cuInit */
+    int real = 0;
+    if (!get_cuDeviceGetCount() || real_cuDeviceGetCount(&real) != 0) real = 0;
+    if (real > VGPU_MAX_DEVICES) real = VGPU_MAX_DEVICES;
+    char want[VGPU_MAX_DEVICES][VGPU_UUID_LEN];
+    int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
+    g_nvdev = 0;
+    for (int p = 0; p < real && nwant > 0; ++p) {  /* physical order, whatever the order of the map */
+        unsigned char u[16];
+        char text[64];
+        if (!get_cuDeviceGetUuid() || real_cuDeviceGetUuid(u, p) != 0) continue;
+        uuid_text(u, text, sizeof(text));
+        int k = 0;
+        for (int i = 0; i < nwant && g_nvdev < VGPU_MAX_DEVICES; ++i)
+            if (strcasecmp(want[i], text) == 0) g_vdev[g_nvdev++] = (vdev_t){p, k++, NULL, 0};
+    }
+    if (g_nvdev == 0) {
+        if (nwant > 0) SHIM_ERR("NVIDIA_DEVICE_MAP names no GPU this container can see: devices are not remapped");
+        for (int p = 0; p < real; ++p) g_vdev[g_nvdev++] = (vdev_t){p, 0, NULL, 0};
+    }
+    g_remap = g_nvdev != real;
+    for (int i = 0; i < g_nvdev; ++i) g_remap |= g_vdev[i].phys != i;
+    if (g_remap)
+        for (int i = 0; i < g_nvdev; ++i) SHIM_INFO("virtual device %d -> GPU %d%s", i, g_vdev[i].phys, g_vdev[i].dup ? " (shared)" : "");
+}
+static void ensure_vdev(void) { pthread_once(&g_vdev_once, build_vdev); }
+
+/* virtual ordinal -> real ordinal, in place; 0 when there is no such device */
+static int to_phys(CUdevice *d) {
+    ensure_vdev();
+    if (!g_remap) return 1;
+    if (*d < 0 || *d >= g_nvdev) return 0;
+    *d = g_vdev[*d].phys;
+    return 1;
+}
+static int phys_of(int vdev) { return (g_remap && vdev >= 0 && vdev < g_nvdev) ? g_vdev[vdev].phys : vdev; }
+static int first_vdev_of(int phys) {
+    if (!g_remap) return phys;
+    for (int i = 0; i < g_nvdev; ++i)
+        if (g_vdev[i].phys == phys) return i;
+    return -1;
+}
+
 /* ------------------------------------------------------------------ allocation list (a13, a15) */
 typedef struct alloc_node {
     CUdeviceptr addr;
@@ -321,10 +433,22 @@ static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
     ++g_nalloc;
 }
 
+static int vdev_of_ctx(CUcontext ctx, int phys);
+/* the (virtual) device of the current context */
 static int cur_dev(int *dev) {
     cuCtxGetDevice_t f = get_cuCtxGetDevice();
     if (!f) return 3;
-    return f(dev);
+    int rc = f(dev);
+    if (rc != 0) return rc;
+    ensure_vdev();
+    if (g_remap) {
+        CUcontext ctx = NULL;
+        if (get_cuCtxGetCurrent()) real_cuCtxGetCurrent(&ctx);
+        int v = vdev_of_ctx(ctx, *dev);
+        if (v < 0) return 101;  /* a context on a GPU that is not ours */
+        *dev = v;
+    }
+    return 0;
 }
 
 static void track(CUdeviceptr p, size_t n, int dev) { track_vmem(p, n, dev, NULL); }
@@ -332,8 +456,8 @@ static void track(CUdeviceptr p, size_t n, int dev) { track_vmem(p, n, dev, NULL
 /* oom_check@0x40528 */
 static int oom_check(int dev, size_t addon) {
     if (!g_region_ok) return 0;
-    int count = 0;
-    if (get_cuDeviceGetCount() && real_cuDeviceGetCount(&count) == 0 && count != g_virtual_devices) return 0;
+    ensure_vdev();
+    if (g_nvdev != g_virtual_devices) return 0;  /* the (virtual) device count must be the map's, @0x40567 */
     if (dev == -1 && cur_dev(&dev) != 0) return 0;
     for (;;) {
         uint64_t limit = region_limit(dev);
@@ -364,8 +488,8 @@ static int add_chunk(CUdeviceptr *p, size_t n) {
         /* spill tiers: VGPU_OVERSUB_PEER=<gpu> puts an idle peer GPU's HBM (NVLink P2P) in front of pinned host RAM */
         const char *pe = getenv("VGPU_OVERSUB_PEER");
         int vrc = (pe && *pe && g_dp.create_tiered)
-                      ? g_dp.create_tiered(dev, n, chunks * IPCSIZE, atoi(pe), chunks * IPCSIZE, chunks * IPCSIZE, &h)
-                      : g_dp.create(dev, n, chunks * IPCSIZE, 2 /* VGPU_TIER_HOST */, -1, chunks * IPCSIZE, &h);
+                      ? g_dp.create_tiered(phys_of(dev), n, chunks * IPCSIZE, atoi(pe), chunks * IPCSIZE, chunks * IPCSIZE, &h)
+                      : g_dp.create(phys_of(dev), n, chunks * IPCSIZE, 2 /* VGPU_TIER_HOST */, -1, chunks * IPCSIZE, &h);
         if (vrc == 0) vrc = g_dp.ensure(h, 0, chunks);
         if (vrc == 0) vrc = g_dp.base(h, &base);
         if (vrc != 0) {
@@ -512,9 +636,11 @@ EXPORT CUresult cuMemGetInfo(size_t *free_b, size_t *total_b) { return cuMemGetI
 
 EXPORT CUresult cuDeviceTotalMem_v2(size_t *bytes, CUdevice dev) {
     ensure_initialized();
+    CUdevice phys = dev;
+    if (!to_phys(&phys)) return 101;
     if (!g_region_ok) {
         cuDeviceTotalMem_v2_t f = get_cuDeviceTotalMem_v2();
-        return f ? f(bytes, dev) : 3;
+        return f ? f(bytes, phys) : 3;
     }
     *bytes = region_limit(dev);  /* quirk a18: the limit, unconditionally (0 when unlimited) */
     return 0;
@@ -724,6 +850,28 @@ static int g_green_state[VGPU_MAX_DEVICES];  /* 0 untried, 1 active, -1 unavaila
 static unsigned g_green_sms[VGPU_MAX_DEVICES];
 static pthread_mutex_t g_green_mu = PTHREAD_MUTEX_INITIALIZER;
 
+/* contexts the application made with cuCtxCreate on a virtual device */
+#define CTX_REG_MAX 64
+static struct { CUcontext ctx; int vdev; } g_ctx_reg[CTX_REG_MAX];
+static int g_ctx_reg_n;
+static void ctx_register(CUcontext ctx, int vdev) {
+    for (int i = 0; i < g_ctx_reg_n; ++i)
+        if (g_ctx_reg[i].ctx == ctx) { g_ctx_reg[i].vdev = vdev; return; }
+    if (g_ctx_reg_n < CTX_REG_MAX) {
+        g_ctx_reg[g_ctx_reg_n].ctx = ctx;
+        g_ctx_reg[g_ctx_reg_n++].vdev = vdev;
+    }
+}
+static int vdev_of_ctx(CUcontext ctx, int phys) {
+    if (ctx) {
+        for (int i = 0; i < g_nvdev; ++i)
+            if (g_vdev[i].ctx == ctx || (g_green_state[i] == 1 && g_green_ctx[i] == ctx)) return i;
+        for (int i = 0; i < g_ctx_reg_n; ++i)
+            if (g_ctx_reg[i].ctx == ctx) return g_ctx_reg[i].vdev;
+    }
+    return first_vdev_of(phys);
+}
+
 static unsigned partition_pick(unsigned nb) {
     const char *e = getenv("VGPU_SM_PARTITION_INDEX");
     if (e && *e) return (unsigned)strtoul(e, NULL, 0) % nb;
@@ -752,7 +900,7 @@ static CUcontext green_ctx_for(CUdevice dev) {
         create_t create = (create_t)cuda_sym("cuGreenCtxCreate");
         fromg_t fromg = (fromg_t)cuda_sym("cuCtxFromGreenCtx");
         shim_dev_resource_t all, groups[64], rest;
-        if (getres && split && gendesc && create && fromg && getres(dev, &all, 1 /* CU_DEV_RESOURCE_TYPE_SM */) == 0) {
+        if (getres && split && gendesc && create && fromg && getres(phys_of(dev), &all, 1 /* CU_DEV_RESOURCE_TYPE_SM */) == 0) {
             unsigned total = all.sm.smCount, share = (unsigned)(total * pct / 100), nb = 0, want;
             /* VGPU_SM_PARTITION_GRANULE=fine: SM-granular groups (IGNORE_SM_COSCHEDULING = 1), e.g.
              * 10 % of 148 SMs -> 14 instead of 8; default keeps cluster co-scheduling inside the vGPU */
@@ -768,7 +916,7 @@ static CUcontext green_ctx_for(CUdevice dev) {
                 CUdevResourceDesc desc;
                 CUgreenCtx g;
                 CUcontext c;
-                if (gendesc(&desc, &groups[k], 1) == 0 && create(&g, desc, dev, 1 /* CU_GREEN_CTX_DEFAULT_STREAM */) == 0 &&
+                if (gendesc(&desc, &groups[k], 1) == 0 && create(&g, desc, phys_of(dev), 1 /* CU_GREEN_CTX_DEFAULT_STREAM */) == 0 &&
                     fromg(&c, g) == 0) {
                     g_green_ctx[dev] = c;
                     g_green_sms[dev] = groups[k].sm.smCount;
@@ -796,14 +944,34 @@ EXPORT void *cuVGPUPartitionCtx(CUdevice dev) {
     return (dev >= 0 && dev < VGPU_MAX_DEVICES && g_green_state[dev] == 1) ? g_green_ctx[dev] : NULL;
 }
 
+REAL(CUresult, cuCtxPopCurrent_v2, CUcontext *)
 EXPORT CUresult cuDevicePrimaryCtxRetain(CUcontext *pctx, CUdevice dev) {
     ensure_initialized();
     SHIM_DEBUG("cuDevicePrimaryCtxRetain(dev=%d)", dev);
     if (tl_bypass) return get_cuDevicePrimaryCtxRetain()(pctx, dev);
-    struct retain_args a = {pctx, dev, 0};
+    CUdevice phys = dev;
+    if (!to_phys(&phys)) return 101;
+    const int shared = g_remap && g_vdev[dev].dup > 0;
+    struct retain_args a = {pctx, phys, 0};
+    CUresult rc = 0;
     pthread_mutex_lock(&g_ctx_mu);
-    CUresult rc = (!g_ctx_probed && g_region_ok) ? probe_around(dev, do_retain, &a) : do_retain(&a);
-    if (rc == 0) charge_context(dev, 0);
+    if (shared && g_vdev[dev].ctx) {
+        *pctx = g_vdev[dev].ctx;
+    } else {
+        /* a further vGPU of a GPU whose primary context belongs to the first one gets a context of its own
+         * (@0x297be); cuCtxCreate makes it current, a primary retain must not: pop it again */
+        CUresult (*make)(void *) = shared ? do_create : do_retain;
+        rc = (!g_ctx_probed && g_region_ok) ? probe_around(phys, make, &a) : make(&a);
+        if (rc == 0 && shared) {
+            CUcontext popped;
+            if (get_cuCtxPopCurrent_v2()) real_cuCtxPopCurrent_v2(&popped);
+            g_vdev[dev].ctx = *pctx;
+        }
+    }
+    if (rc == 0) {
+        if (shared) ++g_vdev[dev].refs;
+        charge_context(dev, 0);
+    }
     pthread_mutex_unlock(&g_ctx_mu);
     if (rc != 0) return rc;
     if (dev >= 0 && dev < VGPU_MAX_DEVICES) {
@@ -814,9 +982,19 @@ EXPORT CUresult cuDevicePrimaryCtxRetain(CUcontext *pctx, CUdevice dev) {
 }
 
 EXPORT CUresult cuDevicePrimaryCtxRelease_v2(CUdevice dev) {
-    cuDevicePrimaryCtxRelease_v2_t f = get_cuDevicePrimaryCtxRelease_v2();
-    CUresult rc = f ? f(dev) : 3;
-    if (!tl_bypass && dev >= 0 && dev < VGPU_MAX_DEVICES) {
+    if (tl_bypass) return get_cuDevicePrimaryCtxRelease_v2()(dev);
+    CUdevice phys = dev;
+    if (!to_phys(&phys)) return 101;
+    CUresult rc = 0;
+    if (g_remap && g_vdev[dev].dup > 0) {  /* the stand-in context lives as long as the process */
+        pthread_mutex_lock(&g_ctx_mu);
+        if (g_vdev[dev].refs > 0) --g_vdev[dev].refs; else rc = 201;
+        pthread_mutex_unlock(&g_ctx_mu);
+    } else {
+        cuDevicePrimaryCtxRelease_v2_t f = get_cuDevicePrimaryCtxRelease_v2();
+        rc = f ? f(phys) : 3;
+    }
+    if (dev >= 0 && dev < VGPU_MAX_DEVICES) {
         pthread_mutex_lock(&g_ctx_mu);
         g_ctx_flag[dev] = 0;  /* @0x2a0bf: the flag goes, the bytes stay billed */
         pthread_mutex_unlock(&g_ctx_mu);
@@ -828,10 +1006,15 @@ EXPORT CUresult cuDevicePrimaryCtxRelease(CUdevice dev) { return cuDevicePrimary
 EXPORT CUresult cuCtxCreate_v2(CUcontext *pctx, unsigned flags, CUdevice dev) {
     if (tl_bypass) return get_cuCtxCreate_v2()(pctx, flags, dev);
     ensure_initialized();
-    struct retain_args a = {pctx, dev, flags};
+    CUdevice phys = dev;
+    if (!to_phys(&phys)) return 101;
+    struct retain_args a = {pctx, phys, flags};
     pthread_mutex_lock(&g_ctx_mu);
-    CUresult rc = (!g_ctx_probed && g_region_ok) ? probe_around(dev, do_create, &a) : do_create(&a);
-    if (rc == 0) charge_context(dev, 1);
+    CUresult rc = (!g_ctx_probed && g_region_ok) ? probe_around(phys, do_create, &a) : do_create(&a);
+    if (rc == 0) {
+        charge_context(dev, 1);
+        if (g_remap) ctx_register(*pctx, dev);
+    }
     pthread_mutex_unlock(&g_ctx_mu);
     return rc;
 }
@@ -848,7 +1031,9 @@ static CUcontext partition_after_bind(CUcontext ctx) {
     if (g_green_state[dev] == 0) {
         CUcontext p = NULL;
         cuDevicePrimaryCtxRetain_t f = get_cuDevicePrimaryCtxRetain();
-        if (f && f(&p, dev) == 0) {
+        if (g_remap && g_vdev[dev].dup > 0) p = g_vdev[dev].ctx;  /* its stand-in for a primary context, if made yet */
+        else if (!f || f(&p, phys_of(dev)) != 0) p = NULL;
+        if (p) {
             g_primary_ctx[dev] = p;
             green_ctx_for(dev);
         }
@@ -997,6 +1182,78 @@ static int nvml_dev_index(void *handle) {
     return (int)i;
 }
 
+/* NVML's side of the virtual devices.  Frameworks count GPUs through NVML before they touch CUDA (PyTorch's
+ * device_count does), so the count and index -> handle follow the map as well, built from NVML's own UUIDs because
+ * cuInit may not have happened yet.  Handles stay the real ones: two vGPUs of one GPU share a handle (the reference
+ * makes up virtual handles and wraps all 247 NVML entry points to translate them). */
+static int g_nv_phys[VGPU_MAX_DEVICES], g_nv_n, g_nv_remap;
+static pthread_once_t g_nv_once = PTHREAD_ONCE_INIT;
+static void build_nvml_view(void) {
+    typedef int (*count_t)(unsigned *);
+    typedef int (*byidx_t)(unsigned, void **);
+    typedef int (*uuid_t)(void *, char *, unsigned);
+    count_t cnt = (count_t)nvml_sym("nvmlDeviceGetCount_v2");
+    byidx_t byidx = (byidx_t)nvml_sym("nvmlDeviceGetHandleByIndex_v2");
+    uuid_t uuid = (uuid_t)nvml_sym("nvmlDeviceGetUUID");
+    char want[VGPU_MAX_DEVICES][VGPU_UUID_LEN];
+    const int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
+    unsigned n = 0;
+    if (nwant == 0 || !cnt || !byidx || !uuid || cnt(&n) != 0) return;
+    for (unsigned i = 0; i < n && i < VGPU_MAX_DEVICES; ++i) {
+        void *h;
+        char u[VGPU_UUID_LEN];
+        if (byidx(i, &h) != 0 || uuid(h, u, sizeof(u)) != 0) continue;
+        for (int k = 0; k < nwant && g_nv_n < VGPU_MAX_DEVICES; ++k)
+            if (strcasecmp(want[k], u) == 0) g_nv_phys[g_nv_n++] = (int)i;
+    }
+    g_nv_remap = g_nv_n > 0 && g_nv_n != (int)n;
+    for (int i = 0; i < g_nv_n; ++i) g_nv_remap |= g_nv_phys[i] != i;
+}
+
+EXPORT int nvmlDeviceGetCount_v2(unsigned *count) {
+    typedef int (*fn_t)(unsigned *);
+    fn_t f = (fn_t)nvml_sym("nvmlDeviceGetCount_v2");
+    int rc = f ? f(count) : 3;
+    if (rc != 0) return rc;
+    pthread_once(&g_nv_once, build_nvml_view);
+    if (g_nv_remap) *count = (unsigned)g_nv_n;
+    return 0;
+}
+EXPORT int nvmlDeviceGetCount(unsigned *count) { return nvmlDeviceGetCount_v2(count); }
+
+EXPORT int nvmlDeviceGetHandleByIndex_v2(unsigned index, void **handle) {
+    typedef int (*fn_t)(unsigned, void **);
+    fn_t f = (fn_t)nvml_sym("nvmlDeviceGetHandleByIndex_v2");
+    if (!f) return 3;
+    pthread_once(&g_nv_once, build_nvml_view);
+    if (g_nv_remap) {
+        if (index >= (unsigned)g_nv_n) return 2;  /* NVML_ERROR_INVALID_ARGUMENT */
+        index = (unsigned)g_nv_phys[index];
+    }
+    return f(index, handle);
+}
+EXPORT int nvmlDeviceGetHandleByIndex(unsigned index, void **handle) { return nvmlDeviceGetHandleByIndex_v2(index, handle); }
+
+/* usage / limit as NVML should show them for a physical GPU: with several vGPUs of this container on it
+ * (virtual devices) the sums; a GPU with any unlimited vGPU counts as unlimited */
+static void nvml_quota(int nvml_index, uint64_t *usage, uint64_t *limit) {
+    ensure_vdev();
+    if (!g_remap) {
+        *usage = region_usage(nvml_index);
+        *limit = region_limit(nvml_index);
+        return;
+    }
+    int unlimited = 0;
+    *usage = *limit = 0;
+    for (int i = 0; i < g_nvdev; ++i)
+        if (g_vdev[i].phys == nvml_index) {
+            *usage += region_usage(i);
+            *limit += region_limit(i);
+            unlimited |= region_limit(i) == 0;
+        }
+    if (unlimited) *limit = 0;
+}
+
 EXPORT int nvmlDeviceGetMemoryInfo(void *handle, nvmlMemory_t *m) {
     ensure_initialized();
     typedef int (*fn_t)(void *, nvmlMemory_t *);
@@ -1005,7 +1262,8 @@ EXPORT int nvmlDeviceGetMemoryInfo(void *handle, nvmlMemory_t *m) {
     if (rc != 0 || !g_region_ok) return rc;
     int dev = nvml_dev_index(handle);
     if (dev < 0) return rc;
-    uint64_t usage = region_usage(dev), limit = region_limit(dev);
+    uint64_t usage, limit;
+    nvml_quota(dev, &usage, &limit);
     if (limit == 0) {
         m->used = usage;  /* hook.c:328-334: only `used` is overwritten when unlimited */
     } else {
@@ -1024,7 +1282,8 @@ EXPORT int nvmlDeviceGetMemoryInfo_v2(void *handle, nvmlMemory_v2_t *m) {
     if (rc != 0 || !g_region_ok) return rc;
     int dev = nvml_dev_index(handle);
     if (dev < 0) return rc;
-    uint64_t usage = region_usage(dev), limit = region_limit(dev);
+    uint64_t usage, limit;
+    nvml_quota(dev, &usage, &limit);
     if (limit == 0) {
         m->used = usage;
     } else {
@@ -1033,6 +1292,203 @@ EXPORT int nvmlDeviceGetMemoryInfo_v2(void *handle, nvmlMemory_v2_t *m) {
         m->used = usage;
     }
     return 0;
+}
+
+/* ------------------------------------------------------------------ virtual devices: the entry points
+ * Everything in the driver API that takes or returns a device ordinal.  With an identity map each of
+ * these is one predictable branch in front of the driver's function. */
+EXPORT CUresult cuDeviceGetCount(int *count) {
+    cuDeviceGetCount_t f = get_cuDeviceGetCount();
+    CUresult rc = f ? f(count) : 3;
+    if (rc != 0 || tl_bypass) return rc;
+    ensure_vdev();
+    if (g_remap) *count = g_nvdev;
+    return 0;
+}
+
+EXPORT CUresult cuDeviceGet(CUdevice *dev, int ordinal) {
+    typedef CUresult (*fn_t)(CUdevice *, int);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuDeviceGet");
+    if (!tl_bypass) {
+        ensure_vdev();
+        if (g_remap) {
+            if (ordinal < 0 || ordinal >= g_nvdev) return 101;
+            *dev = ordinal;  /* the handle IS the virtual ordinal */
+            return 0;
+        }
+    }
+    return f ? f(dev, ordinal) : 3;
+}
+
+EXPORT CUresult cuCtxGetDevice(CUdevice *dev) {
+    if (tl_bypass) return get_cuCtxGetDevice()(dev);
+    return cur_dev(dev);
+}
+
+/* name(params) forwards with `d` (and `d2` when the call has two devices) translated */
+#define VDEV1(name, params, args, d)                                  \
+    EXPORT CUresult name params {                                     \
+        typedef CUresult(*fn_t) params;                               \
+        static fn_t f;                                                \
+        if (!f) f = (fn_t)cuda_sym(#name);                            \
+        if (!tl_bypass && !to_phys(&d)) return 101;                   \
+        return f ? f args : 3;                                        \
+    }
+#define VDEV2(name, params, args, d, d2)                              \
+    EXPORT CUresult name params {                                     \
+        typedef CUresult(*fn_t) params;                               \
+        static fn_t f;                                                \
+        if (!f) f = (fn_t)cuda_sym(#name);                            \
+        if (!tl_bypass && (!to_phys(&d) || !to_phys(&d2))) return 101; \
+        return f ? f args : 3;                                        \
+    }
+VDEV1(cuDeviceGetName, (char *name, int len, CUdevice d), (name, len, d), d)
+VDEV1(cuDeviceGetAttribute, (int *pi, int attrib, CUdevice d), (pi, attrib, d), d)
+VDEV1(cuDeviceGetUuid, (unsigned char *uuid, CUdevice d), (uuid, d), d)
+VDEV1(cuDeviceGetUuid_v2, (unsigned char *uuid, CUdevice d), (uuid, d), d)
+VDEV1(cuDeviceGetLuid, (char *luid, unsigned *mask, CUdevice d), (luid, mask, d), d)
+VDEV1(cuDeviceComputeCapability, (int *major, int *minor, CUdevice d), (major, minor, d), d)
+VDEV1(cuDeviceGetProperties, (void *prop, CUdevice d), (prop, d), d)
+VDEV1(cuDeviceGetTexture1DLinearMaxWidth, (size_t *w, int fmt, unsigned ch, CUdevice d), (w, fmt, ch, d), d)
+VDEV1(cuDeviceGetExecAffinitySupport, (int *pi, int type, CUdevice d), (pi, type, d), d)
+VDEV1(cuDeviceGetDefaultMemPool, (void **pool, CUdevice d), (pool, d), d)
+VDEV1(cuDeviceGetMemPool, (void **pool, CUdevice d), (pool, d), d)
+VDEV1(cuDeviceSetMemPool, (CUdevice d, void *pool), (d, pool), d)
+VDEV1(cuDeviceGetGraphMemAttribute, (CUdevice d, int attr, void *v), (d, attr, v), d)
+VDEV1(cuDeviceSetGraphMemAttribute, (CUdevice d, int attr, void *v), (d, attr, v), d)
+VDEV1(cuDeviceGraphMemTrim, (CUdevice d), (d), d)
+VDEV1(cuDeviceGetDevResource, (CUdevice d, void *res, int type), (d, res, type), d)
+VDEV1(cuDevicePrimaryCtxGetState, (CUdevice d, unsigned *flags, int *active), (d, flags, active), d)
+VDEV1(cuDevicePrimaryCtxSetFlags_v2, (CUdevice d, unsigned flags), (d, flags), d)
+VDEV1(cuDevicePrimaryCtxReset_v2, (CUdevice d), (d), d)
+VDEV1(cuGreenCtxCreate, (void **g, void *desc, CUdevice d, unsigned flags), (g, desc, d, flags), d)
+VDEV2(cuDeviceCanAccessPeer, (int *can, CUdevice d, CUdevice d2), (can, d, d2), d, d2)
+VDEV2(cuDeviceGetP2PAttribute, (int *v, int attr, CUdevice d, CUdevice d2), (v, attr, d, d2), d, d2)
+EXPORT CUresult cuDevicePrimaryCtxSetFlags(CUdevice d, unsigned flags) { return cuDevicePrimaryCtxSetFlags_v2(d, flags); }
+EXPORT CUresult cuDevicePrimaryCtxReset(CUdevice d) { return cuDevicePrimaryCtxReset_v2(d); }
+
+/* VMM / pool entry points carry the device inside a CUmemLocation {type, id}; type 1 = DEVICE */
+typedef struct { int type, id; } shim_mem_location_t;
+static int loc_to_phys(shim_mem_location_t *l) { return l->type != 1 || to_phys(&l->id); }
+
+/* cuMemPrefetchAsync / cuMemAdvise: the device argument may also be CU_DEVICE_CPU (-1) */
+EXPORT CUresult cuMemPrefetchAsync(CUdeviceptr p, size_t n, CUdevice d, void *stream) {
+    typedef CUresult (*fn_t)(CUdeviceptr, size_t, CUdevice, void *);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemPrefetchAsync");
+    if (!tl_bypass && d >= 0 && !to_phys(&d)) return 101;
+    return f ? f(p, n, d, stream) : 3;
+}
+EXPORT CUresult cuMemAdvise(CUdeviceptr p, size_t n, int advice, CUdevice d) {
+    typedef CUresult (*fn_t)(CUdeviceptr, size_t, int, CUdevice);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemAdvise");
+    if (!tl_bypass && d >= 0 && !to_phys(&d)) return 101;
+    return f ? f(p, n, advice, d) : 3;
+}
+
+EXPORT CUresult cuMemPrefetchAsync_v2(CUdeviceptr p, size_t n, shim_mem_location_t loc, unsigned flags, void *stream) {
+    typedef CUresult (*fn_t)(CUdeviceptr, size_t, shim_mem_location_t, unsigned, void *);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemPrefetchAsync_v2");
+    if (!tl_bypass && !loc_to_phys(&loc)) return 101;
+    return f ? f(p, n, loc, flags, stream) : 3;
+}
+EXPORT CUresult cuMemAdvise_v2(CUdeviceptr p, size_t n, int advice, shim_mem_location_t loc) {
+    typedef CUresult (*fn_t)(CUdeviceptr, size_t, int, shim_mem_location_t);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemAdvise_v2");
+    if (!tl_bypass && !loc_to_phys(&loc)) return 101;
+    return f ? f(p, n, advice, loc) : 3;
+}
+/* newer context constructors: translated, not billed (the reference knows cuCtxCreate_v2 only) */
+VDEV1(cuCtxCreate_v3, (CUcontext *pctx, void *params, int nparams, unsigned flags, CUdevice d), (pctx, params, nparams, flags, d), d)
+VDEV1(cuCtxCreate_v4, (CUcontext *pctx, void *params, unsigned flags, CUdevice d), (pctx, params, flags, d), d)
+
+/* The k-th further vGPU of a GPU shows PCI function .k (assigning_virtual_pcibusID@0x2c5c1: "0000:10:00.1") */
+EXPORT CUresult cuDeviceGetPCIBusId(char *id, int len, CUdevice dev) {
+    typedef CUresult (*fn_t)(char *, int, CUdevice);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuDeviceGetPCIBusId");
+    CUdevice phys = dev;
+    if (!tl_bypass && !to_phys(&phys)) return 101;
+    CUresult rc = f ? f(id, len, phys) : 3;
+    if (rc == 0 && !tl_bypass && g_remap && g_vdev[dev].dup > 0) {
+        char *dot = strrchr(id, '.');
+        if (dot && dot[1]) dot[1] = "0123456789abcdef"[g_vdev[dev].dup & 15];
+    }
+    return rc;
+}
+EXPORT CUresult cuDeviceGetByPCIBusId(CUdevice *dev, const char *id) {
+    typedef CUresult (*fn_t)(CUdevice *, const char *);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuDeviceGetByPCIBusId");
+    if (tl_bypass) return f ? f(dev, id) : 3;
+    ensure_vdev();
+    if (!g_remap) return f ? f(dev, id) : 3;
+    char real[64];
+    snprintf(real, sizeof(real), "%s", id ? id : "");
+    char *dot = strrchr(real, '.');
+    int k = 0;
+    if (dot && dot[1]) {
+        k = (int)strtol(dot + 1, NULL, 16);
+        dot[1] = '0';
+        dot[2] = 0;
+    }
+    CUdevice phys = -1;
+    CUresult rc = f ? f(&phys, real) : 3;
+    if (rc != 0) return rc;
+    for (int i = 0; i < g_nvdev; ++i)
+        if (g_vdev[i].phys == phys && g_vdev[i].dup == k) {
+            *dev = i;
+            return 0;
+        }
+    return 101;
+}
+
+typedef struct { int type, handle_types; shim_mem_location_t location; void *win32; unsigned char flags[8]; } shim_alloc_prop_t;
+_Static_assert(sizeof(shim_alloc_prop_t) == 32, "CUmemAllocationProp ABI");
+typedef struct { shim_mem_location_t location; int flags; } shim_access_desc_t;
+
+EXPORT CUresult cuMemCreate(unsigned long long *handle, size_t size, const shim_alloc_prop_t *prop, unsigned long long flags) {
+    typedef CUresult (*fn_t)(unsigned long long *, size_t, const shim_alloc_prop_t *, unsigned long long);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemCreate");
+    shim_alloc_prop_t p2;
+    if (!tl_bypass && prop) {
+        p2 = *prop;
+        if (!loc_to_phys(&p2.location)) return 101;
+        prop = &p2;
+    }
+    return f ? f(handle, size, prop, flags) : 3;
+}
+EXPORT CUresult cuMemGetAllocationGranularity(size_t *g, const shim_alloc_prop_t *prop, int option) {
+    typedef CUresult (*fn_t)(size_t *, const shim_alloc_prop_t *, int);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemGetAllocationGranularity");
+    shim_alloc_prop_t p2;
+    if (!tl_bypass && prop) {
+        p2 = *prop;
+        if (!loc_to_phys(&p2.location)) return 101;
+        prop = &p2;
+    }
+    return f ? f(g, prop, option) : 3;
+}
+EXPORT CUresult cuMemSetAccess(CUdeviceptr ptr, size_t size, const shim_access_desc_t *desc, size_t count) {
+    typedef CUresult (*fn_t)(CUdeviceptr, size_t, const shim_access_desc_t *, size_t);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemSetAccess");
+    shim_access_desc_t d2[VGPU_MAX_DEVICES];
+    ensure_vdev();
+    if (!tl_bypass && g_remap && desc && count <= VGPU_MAX_DEVICES) {
+        for (size_t i = 0; i < count; ++i) {
+            d2[i] = desc[i];
+            if (!loc_to_phys(&d2[i].location)) return 101;
+        }
+        desc = d2;
+    }
+    return f ? f(ptr, size, desc, count) : 3;
 }
 
 /* ------------------------------------------------------------------ dispatch: dlsym / cuGetProcAddress */
@@ -1071,7 +1527,31 @@ static const hook_t g_hooks[] = {
     {"cuMemsetD32", (void *)cuMemsetD32_v2}, {"cuMemsetD32_v2", (void *)cuMemsetD32_v2}, {"cuMemsetD32Async", (void *)cuMemsetD32Async},
     {"cuLaunchKernel", (void *)cuLaunchKernel},
     {"cuLaunchKernelEx", (void *)cuLaunchKernelEx},
+    {"cuDeviceGetCount", (void *)cuDeviceGetCount}, {"cuDeviceGet", (void *)cuDeviceGet}, {"cuCtxGetDevice", (void *)cuCtxGetDevice},
+    {"cuDeviceGetName", (void *)cuDeviceGetName}, {"cuDeviceGetAttribute", (void *)cuDeviceGetAttribute},
+    {"cuDeviceGetUuid", (void *)cuDeviceGetUuid}, {"cuDeviceGetUuid_v2", (void *)cuDeviceGetUuid_v2},
+    {"cuDeviceGetLuid", (void *)cuDeviceGetLuid}, {"cuDeviceComputeCapability", (void *)cuDeviceComputeCapability},
+    {"cuDeviceGetProperties", (void *)cuDeviceGetProperties},
+    {"cuDeviceGetTexture1DLinearMaxWidth", (void *)cuDeviceGetTexture1DLinearMaxWidth},
+    {"cuDeviceGetExecAffinitySupport", (void *)cuDeviceGetExecAffinitySupport},
+    {"cuDeviceGetDefaultMemPool", (void *)cuDeviceGetDefaultMemPool}, {"cuDeviceGetMemPool", (void *)cuDeviceGetMemPool},
+    {"cuDeviceSetMemPool", (void *)cuDeviceSetMemPool},
+    {"cuDeviceGetGraphMemAttribute", (void *)cuDeviceGetGraphMemAttribute},
+    {"cuDeviceSetGraphMemAttribute", (void *)cuDeviceSetGraphMemAttribute}, {"cuDeviceGraphMemTrim", (void *)cuDeviceGraphMemTrim},
+    {"cuDeviceGetDevResource", (void *)cuDeviceGetDevResource}, {"cuGreenCtxCreate", (void *)cuGreenCtxCreate},
+    {"cuDevicePrimaryCtxGetState", (void *)cuDevicePrimaryCtxGetState},
+    {"cuDevicePrimaryCtxSetFlags", (void *)cuDevicePrimaryCtxSetFlags_v2}, {"cuDevicePrimaryCtxSetFlags_v2", (void *)cuDevicePrimaryCtxSetFlags_v2},
+    {"cuDevicePrimaryCtxReset", (void *)cuDevicePrimaryCtxReset_v2}, {"cuDevicePrimaryCtxReset_v2", (void *)cuDevicePrimaryCtxReset_v2},
+    {"cuDeviceCanAccessPeer", (void *)cuDeviceCanAccessPeer}, {"cuDeviceGetP2PAttribute", (void *)cuDeviceGetP2PAttribute},
+    {"cuMemPrefetchAsync", (void *)cuMemPrefetchAsync}, {"cuMemAdvise", (void *)cuMemAdvise},
+    {"cuMemPrefetchAsync_v2", (void *)cuMemPrefetchAsync_v2}, {"cuMemAdvise_v2", (void *)cuMemAdvise_v2},
+    {"cuCtxCreate_v3", (void *)cuCtxCreate_v3}, {"cuCtxCreate_v4", (void *)cuCtxCreate_v4},
+    {"cuDeviceGetPCIBusId", (void *)cuDeviceGetPCIBusId}, {"cuDeviceGetByPCIBusId", (void *)cuDeviceGetByPCIBusId},
+    {"cuMemCreate", (void *)cuMemCreate}, {"cuMemGetAllocationGranularity", (void *)cuMemGetAllocationGranularity},
+    {"cuMemSetAccess", (void *)cuMemSetAccess},
     {"cuGetProcAddress", (void *)cuGetProcAddress}, {"cuGetProcAddress_v2", (void *)cuGetProcAddress_v2},
+    {"nvmlDeviceGetCount", (void *)nvmlDeviceGetCount_v2}, {"nvmlDeviceGetCount_v2", (void *)nvmlDeviceGetCount_v2},
+    {"nvmlDeviceGetHandleByIndex", (void *)nvmlDeviceGetHandleByIndex_v2}, {"nvmlDeviceGetHandleByIndex_v2", (void *)nvmlDeviceGetHandleByIndex_v2},
     {"nvmlDeviceGetMemoryInfo", (void *)nvmlDeviceGetMemoryInfo},
     {"nvmlDeviceGetMemoryInfo_v2", (void *)nvmlDeviceGetMemoryInfo_v2},
 };
@@ -1082,13 +1562,30 @@ static void *find_hook(const char *name) {
     return NULL;
 }
 
+/* cuGetProcAddress(symbol, cudaVersion): an unsuffixed name means the newest ABI that version knows, and for a
+ * few of the hooked names that ABI has a different signature than the hook registered under the bare name */
+static void *find_hook_for_version(const char *name, int ver) {
+    static const struct { const char *name; int since; const char *use; } newer[] = {
+        {"cuGetProcAddress", 12000, "cuGetProcAddress_v2"},
+        {"cuDeviceGetUuid", 11040, "cuDeviceGetUuid_v2"},
+        {"cuCtxCreate", 12050, "cuCtxCreate_v4"},
+        {"cuCtxCreate", 11040, "cuCtxCreate_v3"},
+        {"cuMemPrefetchAsync", 12020, "cuMemPrefetchAsync_v2"},
+        {"cuMemAdvise", 12020, "cuMemAdvise_v2"},
+    };
+    for (size_t i = 0; i < sizeof(newer) / sizeof(newer[0]); ++i)
+        if (ver >= newer[i].since && strcmp(name, newer[i].name) == 0) return find_hook(newer[i].use);
+    return find_hook(name);
+}
+
 /* Launch / copy / memset entry points have per-thread-default-stream twins (_ptsz / _ptds) that the
  * driver selects from the flags of cuGetProcAddress.  Our gates forward to the legacy-stream
  * functions, so a caller that asks for the per-thread flavour gets the driver's own function (no
  * gate) rather than a hook that would silently change its stream semantics. */
 static int wants_ptds(const char *symbol, unsigned long long flags) {
     return (flags & 2ull /* CU_GET_PROC_ADDRESS_PER_THREAD_DEFAULT_STREAM */) &&
-           (strncmp(symbol, "cuMemcpy", 8) == 0 || strncmp(symbol, "cuMemset", 8) == 0 || strncmp(symbol, "cuLaunch", 8) == 0);
+           (strncmp(symbol, "cuMemcpy", 8) == 0 || strncmp(symbol, "cuMemset", 8) == 0 || strncmp(symbol, "cuLaunch", 8) == 0 ||
+            strncmp(symbol, "cuMemPrefetch", 13) == 0);
 }
 
 /* dlsym@0x12bb6: every cu, nvml lookup that names a hooked symbol lands in the shim */
@@ -1103,7 +1600,7 @@ EXPORT void *dlsym(void *handle, const char *symbol) {
 
 EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsigned long long flags) {
     ensure_initialized();
-    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook(symbol) : NULL;
+    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver) : NULL;
     if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;
@@ -1115,7 +1612,7 @@ EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsign
 
 EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, unsigned long long flags, int *status) {
     ensure_initialized();
-    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook(symbol) : NULL;
+    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver) : NULL;
     if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress_v2(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;
@@ -1175,7 +1672,7 @@ static void *mover_main(void *arg) {
             CUcontext ctx = NULL;
             cuDevicePrimaryCtxRetain_t r = get_cuDevicePrimaryCtxRetain();
             cuCtxSetCurrent_t set = get_cuCtxSetCurrent();
-            if (r && set && r(&ctx, 0) == 0 && set(ctx) == 0) bound = 1;
+            if (r && set && r(&ctx, phys_of(0)) == 0 && set(ctx) == 0) bound = 1;
         }
         const int target = g_mover_target;
         if (target == 2 && !out) {

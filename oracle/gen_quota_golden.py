@@ -46,10 +46,26 @@ CASES = [
      {"CUDA_DEVICE_MEMORY_LIMIT_0": "4g", "MOCK_CTX_MIB": "517", **MAP}, 4),
     ("ctx_random_4p_oversub", H.with_contexts(H.random_trace(0x5EED + 4, 3000, 4, 1 << 27), 4),
      {"CUDA_DEVICE_MEMORY_LIMIT_0": "3g", "MOCK_CTX_MIB": "517", "CUDA_OVERSUBSCRIBE": "true", **MAP}, 4),
+    # virtual devices: NVIDIA_DEVICE_MAP with a GPU named twice / a subset / another order
+    ("remap_shared_gpu", H.remap_shared_gpu_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "CUDA_DEVICE_MEMORY_LIMIT_1": "2g", **CTX,
+                                                    "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{H.UUID0}"}, 1),
+    ("remap_three_on_two", H.remap_three_on_two_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "CUDA_DEVICE_MEMORY_LIMIT_1": "2g",
+                                                        "CUDA_DEVICE_MEMORY_LIMIT_2": "3g", **CTX, "MOCK_GPU_COUNT": "2",
+                                                        "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{H.UUID0[:-1]}2 2:{H.UUID0}"}, 1),
+    ("remap_subset_queries", H.remap_queries_trace(1), {"CUDA_DEVICE_MEMORY_LIMIT_0": "50m", "MOCK_GPU_COUNT": "2",
+                                                       "NVIDIA_DEVICE_MAP": f"0:{H.UUID0[:-1]}2"}, 1),
+    ("remap_swapped_queries", H.remap_queries_trace(2), {"CUDA_DEVICE_MEMORY_LIMIT_0": "50m", "CUDA_DEVICE_MEMORY_LIMIT_1": "60m",
+                                                        "MOCK_GPU_COUNT": "2", "NVIDIA_DEVICE_MAP": f"0:{H.UUID0[:-1]}2 1:{H.UUID0}"}, 1),
+    ("remap_shared_queries", H.remap_queries_trace(2), {"CUDA_DEVICE_MEMORY_LIMIT_0": "50m", "CUDA_DEVICE_MEMORY_LIMIT_1": "60m",
+                                                       "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{H.UUID0}"}, 1),
 ]
-# the reference writes device 0's UUID into uuids[1] of the cache file under the mock (its NVML handle remap
-# answers 0 for every mock handle); not reproduced, so the byte-level checksum is left out for these
-NO_REGION_CRC = {"ctx_two_devices"}
+# Parts of the final cache file that are left out of a vector.  Under the mock the reference's NVML handle remap
+# answers device 0 for every mock handle, so with several GPUs it writes device 0's UUID into the other uuids[] lines
+# (and, for a map that names only the second GPU, into uuids[0]); for a GPU named twice it writes a made-up UUID for
+# the second entry.  The shim writes the real UUID of each virtual device, so the byte-level checksum is not compared.
+REGION_SKIP = {"ctx_two_devices": ("masked_crc",), "remap_shared_gpu": ("masked_crc",), "remap_three_on_two": ("masked_crc",),
+               "remap_subset_queries": ("masked_crc", "uuid0"), "remap_swapped_queries": ("masked_crc",),
+               "remap_shared_queries": ("masked_crc",)}
 
 
 def main():
@@ -60,8 +76,8 @@ def main():
     for name, trace, env, nprocs in CASES:
         env = {"MOCK_TOTAL_MIB": "184320", **env}
         r = H.run_trace(H.REFERENCE_LIB, trace, env, nprocs)
-        if name in NO_REGION_CRC:
-            r["region_summary"] = {k: v for k, v in H.region_summary(r["region"]).items() if k != "masked_crc"}
+        if name in REGION_SKIP:
+            r["region_summary"] = {k: v for k, v in H.region_summary(r["region"]).items() if k not in REGION_SKIP[name]}
         doc = {"name": name, "source": "vgpu/libvgpu.so (sha256 d48e2b4c...c0c1ff1) under oracle/ref_harness mocks",
                "env": env, "nprocs": nprocs, "trace": trace, "replies": r["replies"], "oom": r["oom"], "calls": r["calls"],
                "region": r.get("region_summary") or H.region_summary(r["region"])}

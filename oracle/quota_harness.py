@@ -224,6 +224,34 @@ def ctx_procs_trace(nprocs=4):
     return out
 
 
+def remap_shared_gpu_trace():
+    """NVIDIA_DEVICE_MAP names one physical GPU twice (a pod holding two vGPUs of one split): two CUDA devices,
+    the second with PCI function .1, its own limit and usage column and a context of its own.  Allocations stay
+    inside the limits here: past them the reference stops enforcing in this mode (its oom_check@0x40567 compares the
+    REAL device count with the map's and gives up) — tests/test_quota_parity.py pins that difference separately."""
+    MiB = 1 << 20
+    ops = ["devcount", "devget 0", "devget 1", "total 0", "total 1", "retain 0 1", "ctxset 1", "ctxdev", "info", f"alloc {MiB} 1", "info",
+           "retain 1 2", "ctxset 2", "ctxget", "ctxdev", "info", f"alloc {4 * MiB} 2", "info", "@slots", "ctxset 1", "ctxdev", "info",
+           f"alloc {500 * MiB} 3", "info", "ctxset 2", f"alloc {800 * MiB} 4", f"alloc {800 * MiB} 5", "info", "@slots",
+           "retain 1 3", "release 1", "retain 1 4", "info", "free 4", "info", "ctxset 1", "free 3", "free 1", "info", "ctxset 2", "free 2", "free 5",
+           "info", "@slots"]
+    return [(0, o) for o in ops]
+
+
+def remap_three_on_two_trace():
+    """Map "0:A 1:B 2:A" on GPUs A, B: enumerated in physical order — A, A', B — whatever the order of the map."""
+    MiB = 1 << 20
+    ops = ["devcount", "devget 0", "devget 1", "devget 2", "total 0", "total 1", "total 2", "retain 2 1", "ctxset 1", "ctxdev", "info",
+           f"alloc {MiB} 1", "retain 1 2", "ctxset 2", "ctxdev", "info", f"alloc {64 * MiB} 2", "info", "retain 0 3", "ctxset 3", "ctxdev",
+           f"alloc {32 * MiB} 3", "info", "@slots", "ctxset 1", "free 1", "info", "ctxset 2", "free 2", "info", "@slots"]
+    return [(0, o) for o in ops]
+
+
+def remap_queries_trace(n):
+    """Device-level queries only (no context): count, handle, UUID byte, bus id, total memory of every virtual device."""
+    return [(0, "devcount")] + [(0, f"devget {i}") for i in range(n)] + [(0, f"total {i}") for i in range(n)]
+
+
 def with_contexts(trace, nprocs):
     """Prefix: every process retains the primary context of device 0 (what any CUDA runtime program does)."""
     return [(p, "retain 0 1") for p in range(nprocs)] + list(trace)

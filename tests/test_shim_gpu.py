@@ -94,6 +94,100 @@ def test_context_is_billed_to_the_vgpu_and_host_pid_recorded(cuda_dev):
     assert o["nvml"][str(o["hostpid"])] >= o["ctx"]          # ... and its memory only grew since the probe
 
 
+def _gpu0_uuid():
+    o = subprocess.run(["nvidia-smi", "--query-gpu=uuid", "--format=csv,noheader", "-i", "0"], capture_output=True, text=True).stdout
+    return o.strip().splitlines()[0].strip()
+
+
+def test_two_vgpus_on_one_physical_gpu_are_two_cuda_devices(cuda_dev):
+    """NVIDIA_DEVICE_MAP names the GPU twice (reference: initial_virtual_devices@0x27f0d, cuDevicePrimaryCtxRetain
+    @0x297be, assigning_virtual_pcibusID@0x2c5c1): two CUDA devices, the second with PCI function .1, a context of its
+    own and its own quota — here on the real driver, through the driver API, with a kernel-free data check (memset +
+    copy back) inside the second device's context."""
+    code = """
+        import ctypes, json
+        cu = ctypes.CDLL("libcuda.so.1")            # resolved through the preloaded shim first
+        out = {}
+        assert cu.cuInit(0) == 0
+        n = ctypes.c_int(); cu.cuDeviceGetCount(ctypes.byref(n)); out["count"] = n.value
+        devs = []
+        for i in range(n.value):
+            d = ctypes.c_int(-1); rc = cu.cuDeviceGet(ctypes.byref(d), i)
+            name = ctypes.create_string_buffer(64); cu.cuDeviceGetName(name, 64, d)
+            bus = ctypes.create_string_buffer(32); cu.cuDeviceGetPCIBusId(bus, 32, d)
+            tot = ctypes.c_size_t(); cu.cuDeviceTotalMem_v2(ctypes.byref(tot), d)
+            sms = ctypes.c_int(); cu.cuDeviceGetAttribute(ctypes.byref(sms), 16, d)
+            back = ctypes.c_int(-1); cu.cuDeviceGetByPCIBusId(ctypes.byref(back), bus.value)
+            devs.append({"rc": rc, "dev": d.value, "name": name.value.decode(), "bus": bus.value.decode(), "total": tot.value,
+                         "sms": sms.value, "by_bus": back.value})
+        out["devs"] = devs
+        d2 = ctypes.c_int(-1); out["get_oob"] = cu.cuDeviceGet(ctypes.byref(d2), n.value)
+        ctxs = []
+        for i in range(n.value):
+            c = ctypes.c_void_p(); rc = cu.cuDevicePrimaryCtxRetain(ctypes.byref(c), i); ctxs.append(c)
+            assert rc == 0, rc
+        out["distinct_ctx"] = len({c.value for c in ctxs}) == n.value
+        res = []
+        for i in range(n.value):
+            assert cu.cuCtxSetCurrent(ctxs[i]) == 0
+            cur = ctypes.c_int(-1); cu.cuCtxGetDevice(ctypes.byref(cur))
+            f, t = ctypes.c_size_t(), ctypes.c_size_t(); cu.cuMemGetInfo_v2(ctypes.byref(f), ctypes.byref(t))
+            p = ctypes.c_ulonglong(); rc_fit = cu.cuMemAlloc_v2(ctypes.byref(p), ctypes.c_size_t(t.value // 2))
+            q = ctypes.c_ulonglong(); rc_over = cu.cuMemAlloc_v2(ctypes.byref(q), ctypes.c_size_t(t.value // 2 + (64 << 20)))
+            f2 = ctypes.c_size_t(); cu.cuMemGetInfo_v2(ctypes.byref(f2), ctypes.byref(t))
+            # the memory is real and usable from this context
+            cu.cuMemsetD32_v2(ctypes.c_ulonglong(p.value), ctypes.c_uint(0xC0FFEE00 + i), ctypes.c_size_t(1 << 20))
+            host = (ctypes.c_uint * 4)(); rc_cp = cu.cuMemcpyDtoH_v2(host, ctypes.c_ulonglong(p.value + (1 << 21)), ctypes.c_size_t(16))
+            res.append({"cur": cur.value, "free": f.value, "total": t.value, "rc_fit": rc_fit, "rc_over": ctypes.c_int(rc_over).value,
+                        "free_after": f2.value, "rc_cp": rc_cp, "word": host[0]})
+        out["ctx"] = res
+        print(json.dumps(out))
+    """
+    uuid = _gpu0_uuid()
+    p = run_under_shim(code, {"NVIDIA_DEVICE_MAP": f"0:{uuid} 1:{uuid}", "CUDA_DEVICE_MEMORY_LIMIT_0": "4g", "CUDA_DEVICE_MEMORY_LIMIT_1": "8g"})
+    o = last_json(p)
+    print("virtual devices:", o)
+    assert o["count"] == 2 and o["get_oob"] == 101 and o["distinct_ctx"]
+    a, b = o["devs"]
+    assert (a["dev"], b["dev"]) == (0, 1) and a["name"] == b["name"] and a["sms"] == b["sms"] > 0
+    assert a["bus"].endswith(".0") and b["bus"] == a["bus"][:-1] + "1" and (a["by_bus"], b["by_bus"]) == (0, 1)
+    assert (a["total"], b["total"]) == (4 * GiB, 8 * GiB)
+    for i, (r, lim) in enumerate(zip(o["ctx"], (4 * GiB, 8 * GiB))):
+        assert r["cur"] == i and r["total"] == lim and r["free"] <= lim
+        assert r["rc_fit"] == 0 and r["rc_over"] == -1                       # each vGPU enforces ITS limit
+        assert r["free"] - r["free_after"] == lim // 2
+        assert r["rc_cp"] == 0 and r["word"] == 0xC0FFEE00 + i
+    assert "Device 0 OOM" in p.stderr and "Device 1 OOM" in p.stderr
+
+
+def test_pytorch_sees_both_vgpus_of_a_shared_gpu(cuda_dev):
+    """Through the runtime API and PyTorch (which counts devices via NVML first): two devices, separate quotas."""
+    code = """
+        import json, torch
+        out = {"count": torch.cuda.device_count()}
+        res = []
+        for i in range(out["count"]):
+            with torch.cuda.device(i):
+                f, t = torch.cuda.mem_get_info()
+                x = torch.full((1 << 20,), float(i + 1), device=f"cuda:{i}")
+                try:
+                    big = torch.empty(t, dtype=torch.uint8, device=f"cuda:{i}"); over = "allocated"
+                except Exception as e:
+                    over = type(e).__name__
+                res.append({"total": t, "free": f, "sum": float(x.sum().item()), "over": over,
+                            "prop_total": torch.cuda.get_device_properties(i).total_memory})
+        out["res"] = res
+        print(json.dumps(out))
+    """
+    uuid = _gpu0_uuid()
+    p = run_under_shim(code, {"NVIDIA_DEVICE_MAP": f"0:{uuid} 1:{uuid}", "CUDA_DEVICE_MEMORY_LIMIT_0": "4g", "CUDA_DEVICE_MEMORY_LIMIT_1": "8g"})
+    o = last_json(p)
+    print("pytorch on a shared GPU:", o)
+    assert o["count"] == 2
+    for i, (r, lim) in enumerate(zip(o["res"], (4 * GiB, 8 * GiB))):
+        assert r["total"] == lim == r["prop_total"] and r["sum"] == float((i + 1) * (1 << 20)) and r["over"] != "allocated"
+
+
 def test_nvml_memory_info_shows_the_limit(cuda_dev):
     code = """
         import json, torch, pynvml
