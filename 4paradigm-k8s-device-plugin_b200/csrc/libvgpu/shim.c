@@ -214,18 +214,34 @@ static void pre_init(void) {
         if (g_virtual_devices <= 0 && nv_count && nv_count(&n) == 0) g_virtual_devices = (int)n;
         char want[VGPU_MAX_DEVICES][VGPU_UUID_LEN];
         const int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
-        int nreal = g_virtual_devices;
+        int nreal = g_virtual_devices, nvisible = 0;
+        char visible[VGPU_MAX_DEVICES * VGPU_UUID_LEN] = "";
         if (nwant > 0 && nv_count && nv_count(&n) == 0) nreal = (int)n;
         for (int i = 0, v = 0; i < nreal && i < VGPU_MAX_DEVICES && v < VGPU_MAX_DEVICES; ++i) {
             void *h = NULL;
-            char u[VGPU_UUID_LEN];
+            char u[VGPU_UUID_LEN] = {0};  /* copied whole into the cache file: no stack bytes after the terminator */
             if (nv_byidx((unsigned)i, &h) != 0 || nv_uuid(h, u, VGPU_UUID_LEN) != 0) break;
             if (nwant == 0) {
                 memcpy(init.uuids[v++], u, VGPU_UUID_LEN);
                 continue;
             }
+            int named = 0;
             for (int k = 0; k < nwant && v < VGPU_MAX_DEVICES; ++k)  /* one line per virtual device, physical order */
-                if (strcasecmp(want[k], u) == 0) memcpy(init.uuids[v++], u, VGPU_UUID_LEN);
+                if (strcasecmp(want[k], u) == 0) {
+                    memcpy(init.uuids[v++], u, VGPU_UUID_LEN);
+                    ++named;
+                }
+            if (named) {
+                snprintf(visible + strlen(visible), sizeof(visible) - strlen(visible), "%s%s", *visible ? "," : "", u);
+                ++nvisible;
+            }
+        }
+        /* GPUs the container can see but was not given: let the DRIVER hide them (it reads CUDA_VISIBLE_DEVICES at
+         * cuInit, which has not run yet), so that the private driver paths of the CUDA runtime agree with what the
+         * device hooks answer.  The hooks still translate where this has no effect (a variable the user set wins). */
+        if (nwant > 0 && nvisible > 0 && nvisible < nreal && !getenv("CUDA_VISIBLE_DEVICES")) {
+            setenv("CUDA_VISIBLE_DEVICES", visible, 0);
+            SHIM_INFO("CUDA_VISIBLE_DEVICES=%s (from NVIDIA_DEVICE_MAP)", visible);
         }
     }
     init.device_num = g_virtual_devices > 0 ? (uint64_t)g_virtual_devices : 0;
@@ -332,11 +348,28 @@ typedef struct {
     int dup;        /* 0 = first vGPU of that GPU (owns the primary context), k = k-th further one */
     CUcontext ctx;  /* dup > 0: the context standing in for a primary context */
     int refs;
+    int col0, ncols; /* its columns (limit[], sm_limit[], used[]) of the cache file: one, or — merged — all of that GPU's */
 } vdev_t;
 static vdev_t g_vdev[VGPU_MAX_DEVICES];
 static int g_nvdev;
+static int g_ncols;  /* map entries that found their GPU = columns of the cache file in use */
 static int g_remap;  /* 0: identity, nothing to translate */
 static pthread_once_t g_vdev_once = PTHREAD_ONCE_INIT;
+
+/* The CUDA runtime cannot live with two devices on one GPU: besides the public API it asks the driver about
+ * devices through private tables (cuGetExportTable) that no interposer sees, and fails to initialise when those
+ * disagree with the public answers (seen on CUDA 12.9: "CUDA driver initialization failed").  So a process that
+ * fetches an export table before it enumerates devices — every runtime-API program does, first thing after cuInit —
+ * gets the vGPUs of one GPU MERGED into one device that owns all their columns: limit = the sum, usage = the sum,
+ * SM share = the sum.  Pure driver-API programs get them split, as the reference does.
+ * VGPU_SHARED_GPU=split|merge overrides the detection. */
+static int g_runtime_client;
+static int merge_shared(void) {
+    const char *e = getenv("VGPU_SHARED_GPU");
+    if (e && strcmp(e, "split") == 0) return 0;
+    if (e && strcmp(e, "merge") == 0) return 1;
+    return g_runtime_client;
+}
 
 static void uuid_text(const unsigned char *u, char *s, size_t n) {
     snprintf(s, n, "GPU-%02x%02x%02x%02x-%02x%02x-%02x%02x-%02x%02x-%02x%02x%02x%02x%02x%02x", u[0], u[1], u[2], u[3], u[4],
@@ -371,24 +404,33 @@ static void build_vdev(void) {  /* needs a successful cuInit */
     if (real > VGPU_MAX_DEVICES) real = VGPU_MAX_DEVICES;
     char want[VGPU_MAX_DEVICES][VGPU_UUID_LEN];
     int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
-    g_nvdev = 0;
+    const int merge = merge_shared();
+    g_nvdev = g_ncols = 0;
     for (int p = 0; p < real && nwant > 0; ++p) {  /* physical order, whatever the order of the map */
         unsigned char u[16];
         char text[64];
         if (!get_cuDeviceGetUuid() || real_cuDeviceGetUuid(u, p) != 0) continue;
         uuid_text(u, text, sizeof(text));
         int k = 0;
-        for (int i = 0; i < nwant && g_nvdev < VGPU_MAX_DEVICES; ++i)
-            if (strcasecmp(want[i], text) == 0) g_vdev[g_nvdev++] = (vdev_t){p, k++, NULL, 0};
+        for (int i = 0; i < nwant && g_ncols < VGPU_MAX_DEVICES; ++i) {
+            if (strcasecmp(want[i], text) != 0) continue;
+            if (merge && k > 0) ++g_vdev[g_nvdev - 1].ncols;
+            else g_vdev[g_nvdev++] = (vdev_t){p, k, NULL, 0, g_ncols, 1};
+            ++k;
+            ++g_ncols;
+        }
     }
     if (g_nvdev == 0) {
         if (nwant > 0) SHIM_ERR("NVIDIA_DEVICE_MAP names no GPU this container can see: devices are not remapped");
-        for (int p = 0; p < real; ++p) g_vdev[g_nvdev++] = (vdev_t){p, 0, NULL, 0};
+        for (int p = 0; p < real; ++p) g_vdev[g_nvdev++] = (vdev_t){p, 0, NULL, 0, p, 1};
+        g_ncols = nwant > 0 ? 0 : real;  /* a map that matches nothing: the column count differs from the map's, quota off */
     }
     g_remap = g_nvdev != real;
-    for (int i = 0; i < g_nvdev; ++i) g_remap |= g_vdev[i].phys != i;
+    for (int i = 0; i < g_nvdev; ++i) g_remap |= g_vdev[i].phys != i || g_vdev[i].col0 != i || g_vdev[i].ncols != 1;
     if (g_remap)
-        for (int i = 0; i < g_nvdev; ++i) SHIM_INFO("virtual device %d -> GPU %d%s", i, g_vdev[i].phys, g_vdev[i].dup ? " (shared)" : "");
+        for (int i = 0; i < g_nvdev; ++i)
+            SHIM_INFO("virtual device %d -> GPU %d%s, columns %d..%d", i, g_vdev[i].phys, g_vdev[i].dup ? " (shared)" : "", g_vdev[i].col0,
+                      g_vdev[i].col0 + g_vdev[i].ncols - 1);
 }
 static void ensure_vdev(void) { pthread_once(&g_vdev_once, build_vdev); }
 
@@ -406,6 +448,34 @@ static int first_vdev_of(int phys) {
     for (int i = 0; i < g_nvdev; ++i)
         if (g_vdev[i].phys == phys) return i;
     return -1;
+}
+
+/* limit / usage / SM share of a virtual device = those of its columns */
+static int col_of(int vdev) { return (g_remap && vdev >= 0 && vdev < g_nvdev) ? g_vdev[vdev].col0 : vdev; }
+static uint64_t q_limit(int vdev) {
+    if (!g_remap || vdev < 0 || vdev >= g_nvdev) return region_limit(vdev);
+    uint64_t t = 0;
+    for (int c = g_vdev[vdev].col0; c < g_vdev[vdev].col0 + g_vdev[vdev].ncols; ++c) {
+        if (region_limit(c) == 0) return 0;  /* one unlimited vGPU makes the merged device unlimited */
+        t += region_limit(c);
+    }
+    return t;
+}
+static uint64_t q_usage(int vdev) {
+    if (!g_remap || vdev < 0 || vdev >= g_nvdev) return region_usage(vdev);
+    uint64_t t = 0;
+    for (int c = g_vdev[vdev].col0; c < g_vdev[vdev].col0 + g_vdev[vdev].ncols; ++c) t += region_usage(c);
+    return t;
+}
+static uint64_t q_sm_limit(int vdev) {
+    if (!g_remap || vdev < 0 || vdev >= g_nvdev) return region_sm_limit(vdev);
+    uint64_t t = 0;
+    for (int c = g_vdev[vdev].col0; c < g_vdev[vdev].col0 + g_vdev[vdev].ncols; ++c) {
+        uint64_t p = region_sm_limit(c);
+        if (p == 0 || p >= 100) return 100;
+        t += p;
+    }
+    return t > 100 ? 100 : t;
 }
 
 /* ------------------------------------------------------------------ allocation list (a13, a15) */
@@ -457,12 +527,12 @@ static void track(CUdeviceptr p, size_t n, int dev) { track_vmem(p, n, dev, NULL
 static int oom_check(int dev, size_t addon) {
     if (!g_region_ok) return 0;
     ensure_vdev();
-    if (g_nvdev != g_virtual_devices) return 0;  /* the (virtual) device count must be the map's, @0x40567 */
+    if (g_ncols != g_virtual_devices) return 0;  /* every map entry must have found its GPU (the reference compares device counts, @0x40567) */
     if (dev == -1 && cur_dev(&dev) != 0) return 0;
     for (;;) {
-        uint64_t limit = region_limit(dev);
+        uint64_t limit = q_limit(dev);
         if (limit == 0) return 0;
-        uint64_t usage = region_usage(dev);
+        uint64_t usage = q_usage(dev);
         if (usage + addon > limit) {  /* u64 add, no overflow guard, as in the reference */
             SHIM_ERR("Device %d OOM %lu / %lu", dev, (unsigned long)(usage + addon), (unsigned long)limit);
             if (region_reap_dead() > 0) continue;  /* rm_quitted_process: retry once per reaped process */
@@ -500,7 +570,7 @@ static int add_chunk(CUdeviceptr *p, size_t n) {
         if (vrc != 0) return 2;
         *p = (CUdeviceptr)(uintptr_t)base;
         track_vmem(*p, n, dev, h);
-        region_add_usage(dev, n, VGPU_USE_DATA);
+        region_add_usage(col_of(dev), n, VGPU_USE_DATA);
         return 0;
     } else {
         /* cuMemoryAllocate@0x32146, allocmode 0.  The reference hands the allocation to
@@ -511,7 +581,7 @@ static int add_chunk(CUdeviceptr *p, size_t n) {
     }
     if (rc != 0) return rc;
     track(*p, n, dev);
-    region_add_usage(dev, n, VGPU_USE_DATA);
+    region_add_usage(col_of(dev), n, VGPU_USE_DATA);
     return 0;
 }
 
@@ -520,7 +590,7 @@ static int add_chunk_only(CUdeviceptr p, size_t n) {
     CUresult rc = cur_dev(&dev);
     if (rc != 0) return rc;
     track(p, n, dev);
-    region_add_usage(dev, n, VGPU_USE_DATA);
+    region_add_usage(col_of(dev), n, VGPU_USE_DATA);
     return 0;
 }
 
@@ -607,7 +677,7 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
     size_t len = a->len;
     free(a);
     pthread_mutex_unlock(&g_alloc_mu);
-    region_rm_usage(dev, len, VGPU_USE_DATA);
+    region_rm_usage(col_of(dev), len, VGPU_USE_DATA);
     return rc;
 }
 EXPORT CUresult cuMemFree(CUdeviceptr dptr) { return cuMemFree_v2(dptr); }
@@ -618,8 +688,8 @@ EXPORT CUresult cuMemGetInfo_v2(size_t *free_b, size_t *total_b) {
     int dev = 0;
     CUresult rc = cur_dev(&dev);
     if (rc != 0) return rc;
-    uint64_t usage = g_region_ok ? region_usage(dev) : 0;
-    uint64_t limit = g_region_ok ? region_limit(dev) : 0;
+    uint64_t usage = g_region_ok ? q_usage(dev) : 0;
+    uint64_t limit = g_region_ok ? q_limit(dev) : 0;
     cuMemGetInfo_v2_t f = get_cuMemGetInfo_v2();
     if (limit == 0) {
         rc = f ? f(free_b, total_b) : 3;
@@ -642,7 +712,7 @@ EXPORT CUresult cuDeviceTotalMem_v2(size_t *bytes, CUdevice dev) {
         cuDeviceTotalMem_v2_t f = get_cuDeviceTotalMem_v2();
         return f ? f(bytes, phys) : 3;
     }
-    *bytes = region_limit(dev);  /* quirk a18: the limit, unconditionally (0 when unlimited) */
+    *bytes = q_limit(dev);  /* quirk a18: the limit, unconditionally (0 when unlimited) */
     return 0;
 }
 EXPORT CUresult cuDeviceTotalMem(size_t *bytes, CUdevice dev) { return cuDeviceTotalMem_v2(bytes, dev); }
@@ -810,7 +880,7 @@ static void charge_context(CUdevice dev, int created) {
         if (created) SHIM_ERR("Duplicate cuCtxCreate, this may indicate errors");  /* context.c:144 */
         return;
     }
-    if (g_context_size && g_region_ok) region_add_usage(dev, g_context_size, VGPU_USE_CONTEXT);
+    if (g_context_size && g_region_ok) region_add_usage(col_of(dev), g_context_size, VGPU_USE_CONTEXT);
     g_ctx_flag[dev] = 1;
 }
 
@@ -883,7 +953,7 @@ static unsigned partition_pick(unsigned nb) {
 
 static CUcontext green_ctx_for(CUdevice dev) {
     if (dev < 0 || dev >= VGPU_MAX_DEVICES || !g_region_ok) return NULL;
-    uint64_t pct = region_sm_limit(dev);
+    uint64_t pct = q_sm_limit(dev);
     const char *sw = getenv("VGPU_SM_PARTITION");
     if (pct == 0 || pct >= 100 || (sw && strcmp(sw, "off") == 0)) return NULL;
     pthread_mutex_lock(&g_green_mu);
@@ -1182,10 +1252,11 @@ static int nvml_dev_index(void *handle) {
     return (int)i;
 }
 
-/* NVML's side of the virtual devices.  Frameworks count GPUs through NVML before they touch CUDA (PyTorch's
- * device_count does), so the count and index -> handle follow the map as well, built from NVML's own UUIDs because
- * cuInit may not have happened yet.  Handles stay the real ones: two vGPUs of one GPU share a handle (the reference
- * makes up virtual handles and wraps all 247 NVML entry points to translate them). */
+/* NVML's side of the map.  Frameworks count GPUs through NVML before they touch CUDA (PyTorch's device_count
+ * does), so NVML's count and index -> handle are narrowed to the GPUs the map names, in physical order, built from
+ * NVML's own UUIDs because cuInit may not have happened yet.  NVML keeps PHYSICAL devices: a GPU named twice is one
+ * NVML device whose memory info is the sum of its vGPUs — which is also what the CUDA runtime sees (merged device,
+ * above).  (The reference makes up virtual NVML handles and wraps all 247 NVML entry points to translate them.) */
 static int g_nv_phys[VGPU_MAX_DEVICES], g_nv_n, g_nv_remap;
 static pthread_once_t g_nv_once = PTHREAD_ONCE_INIT;
 static void build_nvml_view(void) {
@@ -1204,7 +1275,10 @@ static void build_nvml_view(void) {
         char u[VGPU_UUID_LEN];
         if (byidx(i, &h) != 0 || uuid(h, u, sizeof(u)) != 0) continue;
         for (int k = 0; k < nwant && g_nv_n < VGPU_MAX_DEVICES; ++k)
-            if (strcasecmp(want[k], u) == 0) g_nv_phys[g_nv_n++] = (int)i;
+            if (strcasecmp(want[k], u) == 0) {
+                g_nv_phys[g_nv_n++] = (int)i;
+                break;  /* a GPU named twice is still one NVML device */
+            }
     }
     g_nv_remap = g_nv_n > 0 && g_nv_n != (int)n;
     for (int i = 0; i < g_nv_n; ++i) g_nv_remap |= g_nv_phys[i] != i;
@@ -1247,9 +1321,9 @@ static void nvml_quota(int nvml_index, uint64_t *usage, uint64_t *limit) {
     *usage = *limit = 0;
     for (int i = 0; i < g_nvdev; ++i)
         if (g_vdev[i].phys == nvml_index) {
-            *usage += region_usage(i);
-            *limit += region_limit(i);
-            unlimited |= region_limit(i) == 0;
+            *usage += q_usage(i);
+            *limit += q_limit(i);
+            unlimited |= q_limit(i) == 0;
         }
     if (unlimited) *limit = 0;
 }
@@ -1297,6 +1371,15 @@ EXPORT int nvmlDeviceGetMemoryInfo_v2(void *handle, nvmlMemory_v2_t *m) {
 /* ------------------------------------------------------------------ virtual devices: the entry points
  * Everything in the driver API that takes or returns a device ordinal.  With an identity map each of
  * these is one predictable branch in front of the driver's function. */
+/* the runtime API announces itself (see merge_shared) */
+EXPORT CUresult cuGetExportTable(const void **table, const void *id) {
+    typedef CUresult (*fn_t)(const void **, const void *);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuGetExportTable");
+    if (!tl_bypass) g_runtime_client = 1;
+    return f ? f(table, id) : 3;
+}
+
 EXPORT CUresult cuDeviceGetCount(int *count) {
     cuDeviceGetCount_t f = get_cuDeviceGetCount();
     CUresult rc = f ? f(count) : 3;
@@ -1527,6 +1610,7 @@ static const hook_t g_hooks[] = {
     {"cuMemsetD32", (void *)cuMemsetD32_v2}, {"cuMemsetD32_v2", (void *)cuMemsetD32_v2}, {"cuMemsetD32Async", (void *)cuMemsetD32Async},
     {"cuLaunchKernel", (void *)cuLaunchKernel},
     {"cuLaunchKernelEx", (void *)cuLaunchKernelEx},
+    {"cuGetExportTable", (void *)cuGetExportTable},
     {"cuDeviceGetCount", (void *)cuDeviceGetCount}, {"cuDeviceGet", (void *)cuDeviceGet}, {"cuCtxGetDevice", (void *)cuCtxGetDevice},
     {"cuDeviceGetName", (void *)cuDeviceGetName}, {"cuDeviceGetAttribute", (void *)cuDeviceGetAttribute},
     {"cuDeviceGetUuid", (void *)cuDeviceGetUuid}, {"cuDeviceGetUuid_v2", (void *)cuDeviceGetUuid_v2},

@@ -28,6 +28,8 @@
  *   ctxpush <ctag> / ctxpop   cuCtxPushCurrent_v2 / cuCtxPopCurrent_v2     -> rc [ctx#]
  *   ctxget                 cuCtxGetCurrent                                 -> rc ctx#
  *   ctxdev                 cuCtxGetDevice                                  -> rc dev
+ *   cvd                    getenv("CUDA_VISIBLE_DEVICES") as the process sees it now -> 0 value|-
+ *   exporttable            cuGetExportTable (what every CUDA-runtime program does right after cuInit) -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
  *   quit
  */
@@ -66,6 +68,7 @@ CUresult cuCtxDestroy_v2(void *);
 CUresult cuCtxPushCurrent_v2(void *);
 CUresult cuCtxPopCurrent_v2(void **);
 CUresult cuDevicePrimaryCtxRelease_v2(int);
+CUresult cuGetExportTable(const void **, const void *);
 CUresult cuLaunchKernel(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **);
 
 #define MAXTAG 200000
@@ -185,6 +188,13 @@ int main(void) {
             void *ctx = NULL;
             rc = cuCtxGetCurrent(&ctx);
             printf("%d %d\n", rc, rc == 0 ? ctx_no(ctx) : -1);
+        } else if (!strcmp(op, "cvd")) {
+            const char *v = getenv("CUDA_VISIBLE_DEVICES");
+            printf("0 %s\n", v ? v : "-");
+        } else if (!strcmp(op, "exporttable")) {
+            const void *table = NULL;
+            static const unsigned char id[16] = {0x6b};
+            printf("%d\n", cuGetExportTable(&table, id));
         } else if (!strcmp(op, "ctxdev")) {
             int dev = -1;
             rc = cuCtxGetDevice(&dev);

@@ -174,6 +174,35 @@ def test_nvml_shows_a_shared_gpu_as_the_sum_of_its_vgpus():
     assert rep[4] == f"0 {3 << 30} {(3 << 30) - used} {used}"
 
 
+def test_runtime_api_clients_get_the_vgpus_of_a_shared_gpu_merged():
+    """A process that fetches a driver export table before enumerating devices is a CUDA-runtime program; the runtime
+    cannot initialise with two devices on one GPU, so it gets ONE device owning both vGPUs' columns: limit 1g + 2g,
+    one context billed, allocations larger than either vGPU alone.  VGPU_SHARED_GPU=split keeps them apart."""
+    ops = ["exporttable", "devcount", "devget 1", "total 0", "retain 0 1", "ctxset 1", "info", f"alloc {2000 << 20} 1", f"alloc {800 << 20} 2",
+           "info", "nvmlmem", "@slots"]
+    rep = H.run_trace(H.NEW_LIB, [(0, o) for o in ops], SHARED)["replies"]
+    C, A = 300 << 20, 2000 << 20
+    assert rep[1] == "0 1" and rep[2].startswith("101 ") and rep[3] == f"0 {3 << 30}"
+    assert rep[6] == f"0 {(3 << 30) - C} {3 << 30}" and rep[7:9] == ["0", "-1"]
+    assert rep[9] == f"0 {(3 << 30) - C - A} {3 << 30}" and rep[10] == f"0 {3 << 30} {(3 << 30) - C - A} {C + A}"
+    assert rep[11] == f"n=1 p0:1:1 d0={C}/0/{A}/{C + A}"
+    rep = H.run_trace(H.NEW_LIB, [(0, o) for o in ops], {**SHARED, "VGPU_SHARED_GPU": "split"})["replies"]
+    assert rep[1] == "0 2" and rep[3] == f"0 {1 << 30}" and rep[7] == "-1"
+    rep = H.run_trace(H.NEW_LIB, [(0, o) for o in ops[1:]], {**SHARED, "VGPU_SHARED_GPU": "merge"})["replies"]
+    assert rep[0] == "0 1" and rep[2] == f"0 {3 << 30}"
+
+
+def test_unlisted_gpus_are_hidden_from_the_driver_too():
+    """Map names the second of two visible GPUs: CUDA_VISIBLE_DEVICES is set (before the real cuInit) so that the
+    driver's private paths agree with the hooks; a value the user set is left alone."""
+    u2 = H.UUID0[:-1] + "2"
+    env = {"MOCK_GPU_COUNT": "2", "NVIDIA_DEVICE_MAP": f"0:{u2}", "CUDA_DEVICE_MEMORY_LIMIT_0": "1g"}
+    assert H.run_trace(H.NEW_LIB, [(0, "cvd")], env)["replies"] == [f"0 {u2}"]
+    assert H.run_trace(H.NEW_LIB, [(0, "cvd")], {**env, "CUDA_VISIBLE_DEVICES": "1"})["replies"] == ["0 1"]
+    full = {"MOCK_GPU_COUNT": "2", "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{u2}"}
+    assert H.run_trace(H.NEW_LIB, [(0, "cvd")], full)["replies"] == ["0 -"]       # nothing to hide
+
+
 def test_two_processes_share_one_cache_file():
     """SURVEY c.3: A holds 500 MiB, B allocates 100 MiB and reads free = 1024-500-100 MiB;
     managed 900 MiB -> 2 in both; after both exit a third process sees everything free."""
