@@ -1376,7 +1376,16 @@ EXPORT CUresult cuGetExportTable(const void **table, const void *id) {
     typedef CUresult (*fn_t)(const void **, const void *);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuGetExportTable");
-    if (!tl_bypass) g_runtime_client = 1;
+    if (!tl_bypass && !g_runtime_client) {
+        /* the driver's own libraries fetch tables through the same (interposable) symbol — libcuda during cuInit,
+         * libnvidia-ml during nvmlInit (seen on 580.x): only a caller outside the driver stack counts */
+        Dl_info di;
+        const int known = dladdr(__builtin_return_address(0), &di) && di.dli_fname;
+        if (!known || !(strstr(di.dli_fname, "libcuda.so") || strstr(di.dli_fname, "libnvidia-"))) {
+            g_runtime_client = 1;
+            SHIM_INFO("cuGetExportTable from %s: CUDA-runtime client", known ? di.dli_fname : "?");
+        }
+    }
     return f ? f(table, id) : 3;
 }
 
