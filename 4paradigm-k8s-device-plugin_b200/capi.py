@@ -91,6 +91,8 @@ SIGNATURES = {
     "vgpu_best_effort": (_i, [_pp(_i), _sz, _pp(_i), _sz, _i, _pp(_i), _sz, _pp(_i), _sz]),
     "vgpu_allocate_env": (_i, [_pp(PluginCfg), _pp(_pp(Desc)), _sz, _pp(C.c_char_p), _pp(C.c_char_p), _sz,
                                C.c_char_p, _pp(KV), _pp(_sz), _pp(Mount), _pp(_sz)]),
+    "vgpu_allocate_env_monitor": (_i, [_pp(PluginCfg), _pp(_pp(Desc)), _sz, _pp(C.c_char_p), _pp(C.c_char_p), _sz,
+                                       C.c_char_p, C.c_char_p, _pp(KV), _pp(_sz), _pp(Mount), _pp(_sz)]),
     "vgpu_checksum": (_i, [_vp, _vp, _sz, _sz, _vp, _vp]),
     "vgpu_spill": (_i, [_i, _i, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _vp]),
     "vgpu_restore": (_i, [_i, _i, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _vp, _vp, _vp]),

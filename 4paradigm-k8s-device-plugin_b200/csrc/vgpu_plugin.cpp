@@ -225,6 +225,16 @@ int vgpu_allocate_env(const vgpu_plugin_cfg_t *cfg, const vgpu_desc_t *const *re
                       const char *const *phys_uuids, const char *const *phys_index, size_t n_phys,
                       const char *cache_uuid, vgpu_kv_t *envs, size_t *n_envs, vgpu_mount_t *mounts,
                       size_t *n_mounts) {
+    return vgpu_allocate_env_monitor(cfg, req, n_req, phys_uuids, phys_index, n_phys, cache_uuid, NULL, envs, n_envs,
+                                     mounts, n_mounts);
+}
+
+int vgpu_allocate_env_monitor(const vgpu_plugin_cfg_t *cfg, const vgpu_desc_t *const *req, size_t n_req,
+                              const char *const *phys_uuids, const char *const *phys_index, size_t n_phys,
+                              const char *cache_uuid, const char *shared_name, vgpu_kv_t *envs, size_t *n_envs,
+                              vgpu_mount_t *mounts, size_t *n_mounts) {
+    if (shared_name && (!*shared_name || strchr(shared_name, '/')))
+        return fail(VGPU_E_INVAL, "shared_name must be a non-empty name without '/'");
     if (!cfg || (!req && n_req) || !envs || !n_envs || !mounts || !n_mounts)
         return fail(VGPU_E_INVAL, "null argument");
     const int sm = vgpu_sm_limit(cfg->split, cfg->cores_scaling);
@@ -292,7 +302,13 @@ int vgpu_allocate_env(const vgpu_plugin_cfg_t *cfg, const vgpu_desc_t *const *re
     } else if (int rc = random_uuid4(u4)) {
         return rc;
     }
-    kv.emplace_back("CUDA_DEVICE_MEMORY_SHARED_CACHE", std::string("/tmp/") + u4 + ".cache");  // server.go:503
+    if (shared_name) {  // VGPU_MONITOR_MODE, server.go:494-501: the cache file lives in a directory the host can read
+        const std::string dir = std::string("/") + shared_name;
+        if (!add_mount(dir, std::string("/usr/local/vgpu/shared/") + shared_name, false)) return fail(VGPU_E_RANGE, "path too long");
+        kv.emplace_back("CUDA_DEVICE_MEMORY_SHARED_CACHE", dir + "/" + u4 + ".cache");
+    } else {
+        kv.emplace_back("CUDA_DEVICE_MEMORY_SHARED_CACHE", std::string("/tmp/") + u4 + ".cache");  // server.go:503
+    }
     if (cfg->mem_scaling > 1) kv.emplace_back("CUDA_OVERSUBSCRIBE", "true");                  // server.go:505-507
 
     // server.go:511-522, in this order, all read-only

@@ -47,6 +47,21 @@ def read_region(path: str) -> Dict:
     return out
 
 
+def scan(shared_root: str = "/usr/local/vgpu/shared") -> Dict[str, Dict]:
+    """VGPU_MONITOR_MODE (server.go:494-501): every container's cache file sits in <shared_root>/<pod>_<container>/
+    on the host.  -> {"<pod>_<container>": region dict} for every directory holding an initialised cache file."""
+    import glob
+    import os
+    out = {}
+    for d in sorted(glob.glob(os.path.join(shared_root, "*"))):
+        for f in sorted(glob.glob(os.path.join(d, "*.cache"))):
+            try:
+                out[os.path.basename(d)] = read_region(f)
+            except (OSError, ValueError):
+                continue
+    return out
+
+
 def pids(path: str) -> List[int]:
     return [p["pid"] for p in read_region(path)["procs"] if p["pid"] > 0]
 

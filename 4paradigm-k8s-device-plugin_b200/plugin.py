@@ -316,6 +316,41 @@ def bestEffortPolicy(pair_score: Dict[str, Dict[str, int]]) -> Callable[[List[st
     return allocate
 
 
+def matchPendingPod(pods: Sequence[dict], containerRequests: Sequence[Sequence[str]], resourceName: str = "nvidia.com/gpu") -> Optional[dict]:
+    """server.go:380-405 (VGPU_MONITOR_MODE): the pod this AllocateRequest is for = the LAST pending pod whose
+    GPU-requesting containers, in order, ask for exactly as many devices as the request's container entries
+    (containers without the resource are skipped).  Pods are plain dicts in client-go's JSON shape.  The reference
+    indexes past the end of ContainerRequests (a Go panic) when a pending pod has more GPU containers than the
+    request, and when the last "matching" pod has no GPU container at all; here such pods simply do not match."""
+    target = None
+    for pod in pods:
+        if pod.get("status", {}).get("phase") != "Pending":
+            continue
+        match, minus, gpu_ctrs = True, 0, 0
+        for ctridx, ctr in enumerate(pod.get("spec", {}).get("containers", [])):
+            limits = (ctr.get("resources") or {}).get("limits") or {}
+            if resourceName not in limits:
+                minus += 1
+                continue
+            k = ctridx - minus
+            gpu_ctrs += 1
+            if k >= len(containerRequests) or int(limits[resourceName]) != len(containerRequests[k]):
+                match = False
+                break
+        if match and gpu_ctrs > 0:  # the reference also "matches" pending pods without any GPU container, then panics at :419
+            target = pod
+    return target
+
+
+def gpuContainerNames(pod: dict, n: int, resourceName: str = "nvidia.com/gpu") -> List[str]:
+    """server.go:416-431: the names of the pod's first n containers that request the resource."""
+    names = [c["name"] for c in pod.get("spec", {}).get("containers", [])
+             if resourceName in ((c.get("resources") or {}).get("limits") or {})]
+    if len(names) < n:
+        raise PluginError("pod has fewer GPU containers than the allocate request")  # Go: index out of range
+    return names[:n]
+
+
 class ResourceManager:
     """nvidia.go:43-46; here a list supplied by the caller (a mock NVML in tests)."""
 
@@ -327,7 +362,7 @@ class ResourceManager:
 
 
 class NvidiaDevicePlugin:
-    """server.go:62-655, non-MIG / non-monitor / non-legacy path."""
+    """server.go:62-655, non-MIG path (legacy controller and VGPU_MONITOR_MODE included)."""
 
     def __init__(self, resourceName: str, resourceManager: ResourceManager, deviceListEnvvar: str,
                  allocatePolicy: Optional[Callable[[List[str], List[str], int], List[str]]], socket: str,
@@ -343,6 +378,7 @@ class NvidiaDevicePlugin:
         self.vDeviceController: Optional["VDeviceController"] = None  # --enable-legacy-preferred
         self._podLister: Optional[Callable[[], List[dict]]] = None     # injected: client-go lister stand-in
         self._checkpointDir = DevicePluginPath
+        self._sharedRoot = "/usr/local/vgpu/shared"  # server.go:496, host side of the monitor-mode mount
         self.cachedDevices: List[Device] = []
         self.vDevices: List[VDevice] = []
         self._health_events: List[Device] = []
@@ -432,9 +468,20 @@ class NvidiaDevicePlugin:
         phys_uuid = (C.c_char_p * max(1, n_phys))(*[d.ID.encode() for d in self.cachedDevices])
         phys_idx = (C.c_char_p * max(1, n_phys))(*[d.Index.encode() for d in self.cachedDevices])
         responses = []
+        import os
+        monitorMode = os.environ.get("VGPU_MONITOR_MODE", "")
+        ctrNames: List[str] = []
+        targetPod = None
+        if monitorMode:  # server.go:365-406
+            if self._podLister is None:
+                raise PluginError("VGPU_MONITOR_MODE needs a pod lister")  # the reference panics without in-cluster config
+            targetPod = matchPendingPod(self._podLister(), containerRequests, self.resourceName)
+            if targetPod is None:
+                raise PluginError("no pending pod matches the allocate request")  # Go: nil-slice index panic at :419
+            ctrNames = gpuContainerNames(targetPod, len(containerRequests), self.resourceName)
         if self.vDeviceController is not None:
             self.vDeviceController.updateFromCheckpoint()  # server.go:408-413: release devices of finished pods
-        for ids in containerRequests:
+        for reqidx, ids in enumerate(containerRequests):
             reqDeviceIDs = list(ids)
             if self.vDeviceController is not None:  # server.go:433-457
                 c = self.vDeviceController
@@ -453,9 +500,14 @@ class NvidiaDevicePlugin:
             envs = (capi.KV * 64)()
             mounts = (capi.Mount * 64)()
             n_envs, n_mounts = C.c_size_t(64), C.c_size_t(64)
-            capi.check(capi.lib.vgpu_allocate_env(C.byref(cfg), req, len(vdevices), phys_uuid, phys_idx, n_phys,
-                                                  _cache_uuid.encode() if _cache_uuid else None,
-                                                  envs, C.byref(n_envs), mounts, C.byref(n_mounts)))
+            shared = None
+            if monitorMode:  # server.go:494-501
+                shared = targetPod["metadata"]["name"] + "_" + ctrNames[reqidx]
+                os.makedirs(os.path.join(self._sharedRoot, shared), exist_ok=True)
+            capi.check(capi.lib.vgpu_allocate_env_monitor(C.byref(cfg), req, len(vdevices), phys_uuid, phys_idx, n_phys,
+                                                          _cache_uuid.encode() if _cache_uuid else None,
+                                                          shared.encode() if shared else None,
+                                                          envs, C.byref(n_envs), mounts, C.byref(n_mounts)))
             resp = ContainerAllocateResponse()
             for i in range(n_envs.value):
                 resp.Envs[envs[i].key.decode()] = envs[i].val.decode()

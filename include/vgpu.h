@@ -113,6 +113,18 @@ int vgpu_allocate_env(const vgpu_plugin_cfg_t *cfg,
                       vgpu_kv_t *envs, size_t *n_envs,      /* in: capacity, out: count */
                       vgpu_mount_t *mounts, size_t *n_mounts);
 
+/* The same with VGPU_MONITOR_MODE set (server.go:365-406 find the pending pod, 494-501 build the response):
+ * `shared_name` is the reference's `<pod name>_<container name>`; the response then carries, BEFORE the five fixed
+ * mounts, a read-write mount of /usr/local/vgpu/shared/<shared_name> at /<shared_name>, and the cache file moves
+ * from /tmp into that directory, where a host-side monitor reads it.  NULL = vgpu_allocate_env.  Creating the host
+ * directory (os.MkdirAll, :496) and finding the pod stay with the caller. */
+int vgpu_allocate_env_monitor(const vgpu_plugin_cfg_t *cfg,
+                              const vgpu_desc_t *const *req, size_t n_req,
+                              const char *const *phys_uuids, const char *const *phys_index, size_t n_phys,
+                              const char *cache_uuid, const char *shared_name,
+                              vgpu_kv_t *envs, size_t *n_envs,
+                              vgpu_mount_t *mounts, size_t *n_mounts);
+
 /* ======================================================================== *
  *  Virtual-device-memory data path: 2 MiB chunk spill / restore
  *  (new mechanism behind CUDA_OVERSUBSCRIBE, server.go:505-507; the reference
