@@ -354,7 +354,7 @@ static vdev_t g_vdev[VGPU_MAX_DEVICES];
 static int g_nvdev;
 static int g_ncols;  /* map entries that found their GPU = columns of the cache file in use */
 static int g_remap;  /* 0: identity, nothing to translate */
-static pthread_once_t g_vdev_once = PTHREAD_ONCE_INIT;
+static int g_vdev_built;
 
 /* The CUDA runtime cannot live with two devices on one GPU: besides the public API it asks the driver about
  * devices through private tables (cuGetExportTable) that no interposer sees, and fails to initialise when those
@@ -398,9 +398,9 @@ static int device_map_uuids(char out[][VGPU_UUID_LEN], int max) {
     return n;
 }
 
-static void build_vdev(void) {  /* needs a successful cuInit */
+static int build_vdev(void) {  /* needs a successful cuInit: -> 0 (and nothing latched) before that */
     int real = 0;
-    if (!get_cuDeviceGetCount() || real_cuDeviceGetCount(&real) != 0) real = 0;
+    if (!get_cuDeviceGetCount() || real_cuDeviceGetCount(&real) != 0) return 0;
     if (real > VGPU_MAX_DEVICES) real = VGPU_MAX_DEVICES;
     char want[VGPU_MAX_DEVICES][VGPU_UUID_LEN];
     int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
@@ -431,8 +431,16 @@ static void build_vdev(void) {  /* needs a successful cuInit */
         for (int i = 0; i < g_nvdev; ++i)
             SHIM_INFO("virtual device %d -> GPU %d%s, columns %d..%d", i, g_vdev[i].phys, g_vdev[i].dup ? " (shared)" : "", g_vdev[i].col0,
                       g_vdev[i].col0 + g_vdev[i].ncols - 1);
+    return 1;
 }
-static void ensure_vdev(void) { pthread_once(&g_vdev_once, build_vdev); }
+/* built once, by the first caller that comes after cuInit (an NVML-only call before that must not freeze an empty table) */
+static void ensure_vdev(void) {
+    static pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+    if (__atomic_load_n(&g_vdev_built, __ATOMIC_ACQUIRE)) return;
+    pthread_mutex_lock(&mu);
+    if (!g_vdev_built && build_vdev()) __atomic_store_n(&g_vdev_built, 1, __ATOMIC_RELEASE);
+    pthread_mutex_unlock(&mu);
+}
 
 /* virtual ordinal -> real ordinal, in place; 0 when there is no such device */
 static int to_phys(CUdevice *d) {
@@ -527,7 +535,7 @@ static void track(CUdeviceptr p, size_t n, int dev) { track_vmem(p, n, dev, NULL
 static int oom_check(int dev, size_t addon) {
     if (!g_region_ok) return 0;
     ensure_vdev();
-    if (g_ncols != g_virtual_devices) return 0;  /* every map entry must have found its GPU (the reference compares device counts, @0x40567) */
+    if (!g_vdev_built || g_ncols != g_virtual_devices) return 0;  /* every map entry must have found its GPU (the reference compares device counts, @0x40567) */
     if (dev == -1 && cur_dev(&dev) != 0) return 0;
     for (;;) {
         uint64_t limit = q_limit(dev);
@@ -933,13 +941,16 @@ static void ctx_register(CUcontext ctx, int vdev) {
     }
 }
 static int vdev_of_ctx(CUcontext ctx, int phys) {
+    int v = -1;
     if (ctx) {
-        for (int i = 0; i < g_nvdev; ++i)
-            if (g_vdev[i].ctx == ctx || (g_green_state[i] == 1 && g_green_ctx[i] == ctx)) return i;
-        for (int i = 0; i < g_ctx_reg_n; ++i)
-            if (g_ctx_reg[i].ctx == ctx) return g_ctx_reg[i].vdev;
+        pthread_mutex_lock(&g_ctx_mu);  /* the tables grow under it (retain / create hooks) */
+        for (int i = 0; i < g_nvdev && v < 0; ++i)
+            if (g_vdev[i].ctx == ctx || (g_green_state[i] == 1 && g_green_ctx[i] == ctx)) v = i;
+        for (int i = 0; i < g_ctx_reg_n && v < 0; ++i)
+            if (g_ctx_reg[i].ctx == ctx) v = g_ctx_reg[i].vdev;
+        pthread_mutex_unlock(&g_ctx_mu);
     }
-    return first_vdev_of(phys);
+    return v >= 0 ? v : first_vdev_of(phys);
 }
 
 static unsigned partition_pick(unsigned nb) {
