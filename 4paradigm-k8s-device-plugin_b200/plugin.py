@@ -316,6 +316,63 @@ def bestEffortPolicy(pair_score: Dict[str, Dict[str, int]]) -> Callable[[List[st
     return allocate
 
 
+# NVML_TOPOLOGY_* -> points (besteffort_policy.go:313-325 through nvml.go:592-615 GetP2PLink)
+_TOPOLOGY_POINTS = {0: 60,    # INTERNAL   -> P2PLinkSameBoard
+                    10: 50,   # SINGLE     -> P2PLinkSingleSwitch
+                    20: 40,   # MULTIPLE   -> P2PLinkMultiSwitch
+                    30: 30,   # HOSTBRIDGE -> P2PLinkHostBridge
+                    40: 20,   # NODE / CPU -> P2PLinkSameCPU
+                    50: 10}   # SYSTEM     -> P2PLinkCrossCPU
+
+
+def pairScoresFromNvml(uuids: Sequence[str], nvml=None, max_links: int = 18) -> Dict[str, Dict[str, int]]:
+    """gpuallocator.NewDevicesFrom (device.go:33-95) + calculateGPUPairScore (besteffort_policy.go:296-352) for the
+    GPUs `uuids`: per ordered pair, the PCIe-proximity points of nvmlDeviceGetTopologyCommonAncestor plus 100 per
+    NVLink whose remote end is the other GPU (nvml.go:617-660 GetNVLink compares nvmlDeviceGetNvLinkRemotePciInfo bus
+    ids; capped at 12 links as there).  Behind an NVSwitch every remote end is a switch, so — as in the reference,
+    whose GetNVLink carries a TODO for it — no NVLink points are scored and the PCIe tree decides.
+    `nvml` defaults to pynvml (already initialised by the caller or initialised here)."""
+    if nvml is None:
+        import pynvml as nvml
+        nvml.nvmlInit()
+    handles = {}
+    for u in uuids:
+        try:
+            handles[u] = nvml.nvmlDeviceGetHandleByUUID(u.encode() if isinstance(u, str) else u)
+        except Exception as e:  # NewDevicesFrom: "no device with uuid"
+            raise PluginError(f"no device with uuid: {u}") from e
+
+    def bus_id(h):
+        b = nvml.nvmlDeviceGetPciInfo(h).busId
+        return (b.decode() if isinstance(b, bytes) else b).lower()
+
+    def remote_bus_ids(h):
+        out = []
+        for link in range(max_links):
+            try:
+                b = nvml.nvmlDeviceGetNvLinkRemotePciInfo(h, link).busId
+            except Exception:  # link not present / not supported: skipped, as deviceGetAllNvLinkRemotePciInfo does
+                continue
+            out.append((b.decode() if isinstance(b, bytes) else b).lower())
+        return out
+
+    bus = {u: bus_id(h) for u, h in handles.items()}
+    remotes = {u: remote_bus_ids(h) for u, h in handles.items()}
+    score: Dict[str, Dict[str, int]] = {u: {} for u in uuids}
+    for a in uuids:
+        for b in uuids:
+            if a == b:
+                continue
+            pts = 0
+            try:
+                pts += _TOPOLOGY_POINTS.get(int(nvml.nvmlDeviceGetTopologyCommonAncestor(handles[a], handles[b])), 0)
+            except Exception:
+                pass  # P2PLinkUnknown: no points
+            pts += 100 * min(12, sum(1 for r in remotes[a] if r == bus[b]))
+            score[a][b] = pts
+    return score
+
+
 def matchPendingPod(pods: Sequence[dict], containerRequests: Sequence[Sequence[str]], resourceName: str = "nvidia.com/gpu") -> Optional[dict]:
     """server.go:380-405 (VGPU_MONITOR_MODE): the pod this AllocateRequest is for = the LAST pending pod whose
     GPU-requesting containers, in order, ask for exactly as many devices as the request's container entries
@@ -457,7 +514,34 @@ class NvidiaDevicePlugin:
         return responses
 
     # server.go:361-533
+    # server.go:328-358
+    def MIGAllocate(self, containerRequests: Sequence[Sequence[str]]) -> List[ContainerAllocateResponse]:
+        f = self.flags
+        known = {d.ID for d in self.cachedDevices}
+        responses = []
+        for ids in containerRequests:
+            for i in ids:
+                if i not in known:  # deviceExists, server.go:333
+                    raise PluginError(f"invalid allocation request for '{self.resourceName}': unknown device: {i}")
+            resp = ContainerAllocateResponse()
+            if f.deviceIDStrategy == DeviceIDStrategyUUID:  # deviceIDsFromUUIDs, server.go:565-581
+                deviceIDs = list(ids)
+            else:
+                deviceIDs = [d.Index for d in self.cachedDevices if d.ID in ids]
+            root = "/var/run/nvidia-container-devices"
+            if f.deviceListStrategy == DeviceListStrategyEnvvar:
+                resp.Envs[self.deviceListEnvvar] = ",".join(deviceIDs)
+            else:
+                resp.Envs[self.deviceListEnvvar] = root
+                resp.Mounts = [Mount(f"{root}/{i}", "/dev/null", False) for i in deviceIDs]
+            if f.passDeviceSpecs:
+                resp.Devices = self.apiDeviceSpecs(f.nvidiaDriverRoot, list(ids))
+            responses.append(resp)
+        return responses
+
     def Allocate(self, containerRequests: Sequence[Sequence[str]], _cache_uuid: Optional[str] = None) -> List[ContainerAllocateResponse]:
+        if self.migStrategy == "mixed":  # server.go:362-364 (set on the per-MIG-resource plugins only, mig-strategy.go:205)
+            return self.MIGAllocate(containerRequests)
         f = self.flags
         cfg = capi.PluginCfg(split=f.deviceSplitCount, mem_scaling=f.deviceMemoryScaling,
                              cores_scaling=f.deviceCoresScaling,
@@ -545,3 +629,100 @@ def NewNvidiaDevicePlugin(resourceManager: ResourceManager, flags: Optional[Flag
     policy = bestEffortPolicy(pair_score) if pair_score else simplePolicy
     return NvidiaDevicePlugin("nvidia.com/gpu", resourceManager, "NVIDIA_VISIBLE_DEVICES", policy,
                               DevicePluginPath + "nvidia-gpu.sock", flags)
+
+
+# ------------------------------------------------------------------ MIG strategies (mig-strategy.go, mig.go, nvidia.go:62-137)
+@dataclass
+class MigDevice:
+    """What the strategies read from a MIG device: nvml.Device.GetAttributes() and its node paths."""
+    ID: str
+    GpuInstanceSliceCount: int
+    ComputeInstanceSliceCount: int
+    MemorySizeMB: int
+    Paths: List[str] = field(default_factory=list)
+
+
+@dataclass
+class NodeGpu:
+    """One physical GPU as NVML lists it: index order is NVML's."""
+    ID: str
+    Path: str
+    migEnabled: bool = False
+    migs: List[MigDevice] = field(default_factory=list)
+    memory_mib: int = 0
+
+
+def migResourceName(mig: MigDevice) -> str:
+    """getResourceName (mig-strategy.go:139-154 / 218-233): mig-<g>g.<gb>gb, or mig-<c>c.<g>g.<gb>gb when the compute
+    slice count differs; gb = ceil(MemorySizeMB / 1024)."""
+    g, c = mig.GpuInstanceSliceCount, mig.ComputeInstanceSliceCount
+    gb = (mig.MemorySizeMB + 1024 - 1) // 1024
+    return f"mig-{g}g.{gb}gb" if g == c else f"mig-{c}c.{g}g.{gb}gb"
+
+
+def validMigDevice(mig: MigDevice) -> bool:
+    """mig-strategy.go:132-137 / 211-216."""
+    return mig.GpuInstanceSliceCount == mig.ComputeInstanceSliceCount
+
+
+class GpuDeviceManager(ResourceManager):
+    """nvidia.go:66-102: every GPU, optionally skipping the MIG-enabled ones; Index = NVML index."""
+
+    def __init__(self, node: Sequence[NodeGpu], skipMigEnabledGPUs: bool):
+        super().__init__([Device(g.ID, Index=str(i), Paths=[g.Path], memory_mib=g.memory_mib)
+                          for i, g in enumerate(node) if not (g.migEnabled and skipMigEnabledGPUs)])
+
+
+class MigDeviceManager(ResourceManager):
+    """nvidia.go:104-137: the MIG devices of MIG-enabled GPUs that match `resource`; Index = "<gpu>:<mig>"."""
+
+    def __init__(self, node: Sequence[NodeGpu], matches: Callable[[MigDevice, str], bool], resource: str):
+        super().__init__([Device(m.ID, Index=f"{i}:{j}", Paths=list(m.Paths), memory_mib=m.MemorySizeMB)
+                          for i, g in enumerate(node) if g.migEnabled for j, m in enumerate(g.migs) if matches(m, resource)])
+
+
+def migPlugins(strategy: str, node: Sequence[NodeGpu], flags: Optional[Flags] = None,
+               pair_score: Optional[Dict[str, Dict[str, int]]] = None) -> List[NvidiaDevicePlugin]:
+    """NewMigStrategy(strategy).GetPlugins() (mig-strategy.go:46-209) over an explicit node description instead of live
+    NVML.  Go panics become PluginError with the reference's message."""
+    policy = bestEffortPolicy(pair_score) if pair_score else simplePolicy
+    sock = DevicePluginPath
+    if strategy == "none":  # :62-71 — "Enumerate device even if MIG enabled"
+        return [NvidiaDevicePlugin("nvidia.com/gpu", GpuDeviceManager(node, False), "NVIDIA_VISIBLE_DEVICES", policy,
+                                   sock + "nvidia-gpu.sock", flags)]
+    if strategy not in ("single", "mixed"):
+        raise PluginError(f"Unknown strategy: {strategy}")
+    enabled = [g for g in node if g.migEnabled]
+    if strategy == "single":  # :78-130
+        if not enabled:
+            return migPlugins("none", node, flags, pair_score)  # "No MIG devices found. Falling back to mig.strategy=none"
+        if any(not g.migEnabled for g in node):
+            raise PluginError("For mig.strategy=single all devices on the node must all be configured with the same migEnabled value")
+    for g in enabled:  # AssertAllMigEnabledDevicesAreValid, mig.go:84-100
+        if not g.migs:
+            raise PluginError(f"At least one device with migEnabled=true was not configured correctly: No MIG devices associated with {g.Path}: {g.ID}")
+    resources: List[str] = []
+    for g in enabled:
+        for m in g.migs:
+            r = migResourceName(m)
+            if not validMigDevice(m):
+                if strategy == "single":
+                    raise PluginError("Unsupported MIG device found: " + r)
+                continue  # mixed: "Skipping unsupported MIG device"
+            if r not in resources:
+                resources.append(r)
+    if strategy == "single":
+        if not resources:
+            raise PluginError("No MIG devices present on node")
+        if len(resources) != 1:
+            raise PluginError("More than one MIG device type present on node")
+        return [NvidiaDevicePlugin("nvidia.com/gpu", MigDeviceManager(node, lambda m, r: True, "gpu"), "NVIDIA_VISIBLE_DEVICES", None,
+                                   sock + "nvidia-gpu.sock", flags)]
+    plugins = [NvidiaDevicePlugin("nvidia.com/gpu", GpuDeviceManager(node, True), "NVIDIA_VISIBLE_DEVICES", policy,
+                                  sock + "nvidia-gpu.sock", flags)]
+    for r in sorted(resources):  # Go iterates a map: order unspecified; sorted here
+        p = NvidiaDevicePlugin("nvidia.com/" + r, MigDeviceManager(node, lambda m, res: migResourceName(m) == res, r),
+                               "NVIDIA_VISIBLE_DEVICES", None, sock + "nvidia-" + r + ".sock", flags)
+        p.migStrategy = "mixed"
+        plugins.append(p)
+    return plugins

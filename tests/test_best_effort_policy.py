@@ -84,3 +84,69 @@ def test_preferred_allocation_with_the_real_policy(vgpu):
     avail = [f"{uu[1]}-1", f"{uu[2]}-0", f"{uu[3]}-1", f"{uu[2]}-1"]        # GPU 0 fully taken
     assert p.GetPreferredAllocation([{"AvailableDeviceIDs": avail, "AllocationSize": 2}]) == [[f"{uu[2]}-0", f"{uu[3]}-1"]]
     assert p.GetPreferredAllocation([{"AvailableDeviceIDs": avail, "MustIncludeDeviceIDs": [f"{uu[1]}-1"], "AllocationSize": 2}]) == [[f"{uu[1]}-1", f"{uu[2]}-0"]]
+
+
+class _FakeNvml:
+    """Four GPUs: 0-1 and 2-3 joined by two NVLinks each, 0/1 under one PCIe switch, 2/3 under another CPU."""
+    class _Pci:
+        def __init__(self, bus):
+            self.busId = bus.encode()
+
+    def __init__(self):
+        self.bus = {f"GPU-{i}": f"00000000:{0x10 + i:02X}:00.0" for i in range(4)}
+        self.links = {"GPU-0": ["GPU-1", "GPU-1"], "GPU-1": ["GPU-0", "GPU-0"], "GPU-2": ["GPU-3", "GPU-3"], "GPU-3": ["GPU-2", "GPU-2"]}
+
+    def nvmlDeviceGetHandleByUUID(self, u):
+        u = u.decode()
+        if u not in self.bus:
+            raise RuntimeError("not found")
+        return u
+
+    def nvmlDeviceGetPciInfo(self, h):
+        return self._Pci(self.bus[h])
+
+    def nvmlDeviceGetNvLinkRemotePciInfo(self, h, link):
+        if link >= len(self.links[h]):
+            raise RuntimeError("NVML_ERROR_INVALID_ARGUMENT")
+        return self._Pci(self.bus[self.links[h][link]].lower())      # case differs from GetPciInfo on purpose
+
+    def nvmlDeviceGetTopologyCommonAncestor(self, a, b):
+        same_side = (a in ("GPU-0", "GPU-1")) == (b in ("GPU-0", "GPU-1"))
+        return 10 if same_side else 50                               # SINGLE switch / SYSTEM
+
+
+def test_pair_scores_from_nvml_follow_calculateGPUPairScore(vgpu):
+    P = vgpu.plugin
+    uuids = [f"GPU-{i}" for i in range(4)]
+    s = P.pairScoresFromNvml(uuids, nvml=_FakeNvml())
+    assert s["GPU-0"]["GPU-1"] == s["GPU-1"]["GPU-0"] == 50 + 200    # single switch + two NVLinks
+    assert s["GPU-2"]["GPU-3"] == 250 and s["GPU-0"]["GPU-2"] == s["GPU-3"]["GPU-1"] == 10
+    assert "GPU-0" not in s["GPU-0"]
+    alloc = P.bestEffortPolicy(s)
+    assert alloc(uuids, [], 2) == ["GPU-0", "GPU-1"]
+    assert alloc(uuids, ["GPU-3"], 2) == ["GPU-2", "GPU-3"]
+    assert alloc(["GPU-0", "GPU-2", "GPU-3"], [], 2) == ["GPU-2", "GPU-3"]
+    with pytest.raises(P.PluginError):
+        P.pairScoresFromNvml(["GPU-9"], nvml=_FakeNvml())
+
+
+@pytest.mark.gpu
+def test_pair_scores_on_the_real_topology(vgpu):
+    """Real NVML: symmetric scores, PCIe points in the reference's table, preferred allocation picks the best pair."""
+    import pynvml
+    pynvml.nvmlInit()
+    n = pynvml.nvmlDeviceGetCount()
+    uuids = []
+    for i in range(n):
+        u = pynvml.nvmlDeviceGetUUID(pynvml.nvmlDeviceGetHandleByIndex(i))
+        uuids.append(u.decode() if isinstance(u, bytes) else u)
+    s = vgpu.plugin.pairScoresFromNvml(uuids)
+    print("pair scores:", s)
+    for a in uuids:
+        for b in uuids:
+            if a != b:
+                assert s[a][b] == s[b][a] and s[a][b] % 10 == 0 and 0 <= s[a][b] <= 1260
+    if n >= 2:
+        best = max(s[a][b] for a in uuids for b in uuids if a != b)
+        got = vgpu.plugin.bestEffortPolicy(s)(uuids, [], 2)
+        assert len(got) == 2 and s[got[0]][got[1]] == best
