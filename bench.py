@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--vgpus", type=int, default=4, help="vGPUs per GPU (config 2: 4)")
     ap.add_argument("--vgpu-gib", type=float, default=40.0, help="memtest buffer per vGPU in GiB (config 2: 40)")
     ap.add_argument("--spill-chunks", type=int, default=4096, help="largest batch of the 2 MiB chunk sweep (config 4: 4096)")
-    ap.add_argument("--partition", default="green", choices=["green", "streams"],
+    ap.add_argument("--partition", default="green", choices=["green", "green-fine", "streams"],
                     help="green: one 25%% green-context SM partition per vGPU (default); streams: plain streams "
                          "(ncu cannot profile launches into green contexts)")
     ap.add_argument("--no-spill", action="store_true", help="skip the spill/restore sweep")
@@ -260,13 +260,19 @@ def main():
 
     parts = (capi.SmPartition * nv)()
     pct = int(100 / nv)
-    rc = capi.lib.vgpu_sm_partition_create(local, pct, nv, parts) if args.partition == "green" else 1
+    if args.partition == "green":
+        rc = capi.lib.vgpu_sm_partition_create(local, pct, nv, parts)
+    elif args.partition == "green-fine":  # SM-granular groups: fine for the cluster-free memtest kernels
+        rc = capi.lib.vgpu_sm_partition_create_ex(local, pct, nv, 1, parts)
+    else:
+        rc = 1
     if rc == 0:
         streams = [torch.cuda.ExternalStream(p.stream, device=dev) for p in parts]
-        partition = {"kind": "green_ctx", "percent": pct, "sm_per_vgpu": [p.sm_count for p in parts], "sm_total": parts[0].sm_total}
+        partition = {"kind": "green_ctx" if args.partition == "green" else "green_ctx_sm_granular", "percent": pct,
+                     "sm_per_vgpu": [p.sm_count for p in parts], "sm_total": parts[0].sm_total}
     else:  # measured and reported as such, not hidden
         streams = [torch.cuda.Stream(device=dev) for _ in range(nv)]
-        partition = {"kind": "plain_streams", "why": capi.last_error() if args.partition == "green" else "--partition streams"}
+        partition = {"kind": "plain_streams", "why": capi.last_error() if args.partition != "streams" else "--partition streams"}
     results = [torch.zeros(3, dtype=torch.int64, device=dev) for _ in range(nv)]
 
     main_stream = torch.cuda.current_stream()
