@@ -183,6 +183,53 @@ static int count_device_map(void) {
 
 static int device_map_uuids(char out[][VGPU_UUID_LEN], int max);
 
+/* GPUs the container can see but was not given: let the DRIVER hide them (it reads CUDA_VISIBLE_DEVICES at cuInit,
+ * which has not run yet), so that the private driver paths of the CUDA runtime agree with what the device hooks
+ * answer — with the hooks alone the runtime fails to start ("Error 103: integrity checks failed", seen on a 2-GPU
+ * box).  A CUDA_VISIBLE_DEVICES the user (or the container runtime) already set is read the way it is meant inside a
+ * vGPU container — ordinals count the container's OWN devices, i.e. the map's — and rewritten as UUIDs; as with the
+ * driver, the list ends at the first entry that names nothing.  (Reference: parse_cuda_visible_env@0x18b15.) */
+static void list_append(char *out, size_t cap, const char *s) {
+    const size_t l = strlen(out);
+    if (l + strlen(s) + 2 > cap) return;
+    if (l) strcat(out, ",");
+    strcat(out, s);
+}
+static void narrow_visible_devices(char vis[][VGPU_UUID_LEN], int nvis, int nreal) {
+    if (nvis <= 0) return;
+    const char *user = getenv("CUDA_VISIBLE_DEVICES");
+    char out[VGPU_MAX_DEVICES * VGPU_UUID_LEN] = "";
+    if (!user) {
+        if (nvis >= nreal) return;  /* nothing to hide */
+        for (int i = 0; i < nvis; ++i) list_append(out, sizeof(out), vis[i]);
+    } else {
+        if (strstr(user, "MIG-")) return;  /* MIG instances are not vGPUs of this plugin: left alone */
+        int used[VGPU_MAX_DEVICES] = {0}, n = 0;
+        const char *p = user;
+        while (*p && n < VGPU_MAX_DEVICES) {
+            const char *end = strchr(p, ',');
+            size_t len = end ? (size_t)(end - p) : strlen(p);
+            int pick = -1;
+            if (len > 0 && len < 8 && strspn(p, "0123456789") == len) {
+                int idx = atoi(p);
+                if (idx < nvis) pick = idx;
+            } else if (len >= 5 && strncasecmp(p, "GPU-", 4) == 0) {
+                for (int i = 0; i < nvis && pick < 0; ++i)
+                    if (strncasecmp(vis[i], p, len) == 0) pick = i;  /* the driver accepts unique prefixes */
+            }
+            if (pick < 0 || used[pick]) break;
+            used[pick] = 1;
+            list_append(out, sizeof(out), vis[pick]);
+            ++n;
+            if (!end) break;
+            p = end + 1;
+        }
+        if (strcmp(out, user) == 0) return;
+    }
+    setenv("CUDA_VISIBLE_DEVICES", out, 1);
+    SHIM_INFO("CUDA_VISIBLE_DEVICES=%s (from NVIDIA_DEVICE_MAP%s%s)", out, user ? " and " : "", user ? user : "");
+}
+
 static void pre_init(void) {
     vgpu_region_init_t init;
     memset(&init, 0, sizeof(init));
@@ -215,7 +262,7 @@ static void pre_init(void) {
         char want[VGPU_MAX_DEVICES][VGPU_UUID_LEN];
         const int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
         int nreal = g_virtual_devices, nvisible = 0;
-        char visible[VGPU_MAX_DEVICES * VGPU_UUID_LEN] = "";
+        char visible[VGPU_MAX_DEVICES][VGPU_UUID_LEN];  /* the distinct GPUs the map names, physical order */
         if (nwant > 0 && nv_count && nv_count(&n) == 0) nreal = (int)n;
         for (int i = 0, v = 0; i < nreal && i < VGPU_MAX_DEVICES && v < VGPU_MAX_DEVICES; ++i) {
             void *h = NULL;
@@ -231,18 +278,9 @@ static void pre_init(void) {
                     memcpy(init.uuids[v++], u, VGPU_UUID_LEN);
                     ++named;
                 }
-            if (named) {
-                snprintf(visible + strlen(visible), sizeof(visible) - strlen(visible), "%s%s", *visible ? "," : "", u);
-                ++nvisible;
-            }
+            if (named && nvisible < VGPU_MAX_DEVICES) memcpy(visible[nvisible++], u, VGPU_UUID_LEN);
         }
-        /* GPUs the container can see but was not given: let the DRIVER hide them (it reads CUDA_VISIBLE_DEVICES at
-         * cuInit, which has not run yet), so that the private driver paths of the CUDA runtime agree with what the
-         * device hooks answer.  The hooks still translate where this has no effect (a variable the user set wins). */
-        if (nwant > 0 && nvisible > 0 && nvisible < nreal && !getenv("CUDA_VISIBLE_DEVICES")) {
-            setenv("CUDA_VISIBLE_DEVICES", visible, 0);
-            SHIM_INFO("CUDA_VISIBLE_DEVICES=%s (from NVIDIA_DEVICE_MAP)", visible);
-        }
+        narrow_visible_devices(visible, nvisible, nreal);
     }
     init.device_num = g_virtual_devices > 0 ? (uint64_t)g_virtual_devices : 0;
 

@@ -198,9 +198,16 @@ def test_unlisted_gpus_are_hidden_from_the_driver_too():
     u2 = H.UUID0[:-1] + "2"
     env = {"MOCK_GPU_COUNT": "2", "NVIDIA_DEVICE_MAP": f"0:{u2}", "CUDA_DEVICE_MEMORY_LIMIT_0": "1g"}
     assert H.run_trace(H.NEW_LIB, [(0, "cvd")], env)["replies"] == [f"0 {u2}"]
-    assert H.run_trace(H.NEW_LIB, [(0, "cvd")], {**env, "CUDA_VISIBLE_DEVICES": "1"})["replies"] == ["0 1"]
+    # a preset list counts the container's OWN devices (the map's) and is rewritten as UUIDs; it ends at the first bad entry
+    def cvd(user, extra=env):
+        return H.run_trace(H.NEW_LIB, [(0, "cvd")], {**extra, "CUDA_VISIBLE_DEVICES": user})["replies"][0]
+    assert cvd("0,1") == f"0 {u2}"            # what a 2-GPU host hands down: virtual 0 exists, virtual 1 does not
+    assert cvd("0") == f"0 {u2}" and cvd(u2) == f"0 {u2}" and cvd(u2[:12]) == f"0 {u2}"
+    assert cvd("1") == "0" and cvd(H.UUID0) == "0"              # names nothing of ours: no device, as the driver would answer
+    assert cvd("MIG-GPU-abc/1/0") == "0 MIG-GPU-abc/1/0"      # not ours to interpret
     full = {"MOCK_GPU_COUNT": "2", "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{u2}"}
     assert H.run_trace(H.NEW_LIB, [(0, "cvd")], full)["replies"] == ["0 -"]       # nothing to hide
+    assert cvd("1,0", full) == f"0 {u2},{H.UUID0}"            # the user's order is kept
 
 
 def test_two_processes_share_one_cache_file():

@@ -191,6 +191,56 @@ def test_pytorch_gets_the_vgpus_of_a_shared_gpu_as_one_device(cuda_dev):
     assert o["nvml_used"] == 12 * GiB - o["free2"]
 
 
+def test_subset_map_hides_the_other_gpu_from_driver_runtime_and_nvml(cuda_dev):
+    """Container sees two GPUs, NVIDIA_DEVICE_MAP gives it the second: one device everywhere — driver API, the CUDA
+    runtime (PyTorch) and NVML — and it IS the second GPU, with the map's quota (needs a 2-GPU box)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    o = subprocess.run(["nvidia-smi", "--query-gpu=uuid,pci.bus_id", "--format=csv,noheader"], capture_output=True, text=True).stdout
+    gpus = [tuple(x.strip() for x in line.split(",")) for line in o.strip().splitlines()]
+    uuid1, bus1 = gpus[1]
+    code = """
+        import ctypes, json, os, subprocess, torch, pynvml
+        out = {"count": torch.cuda.device_count()}
+        f, t = torch.cuda.mem_get_info()
+        x = torch.ones(1 << 28, dtype=torch.uint8, device="cuda")      # 256 MiB on "device 0"
+        torch.cuda.synchronize()
+        env = {k: v for k, v in os.environ.items() if k != "LD_PRELOAD"}
+        smi = subprocess.run(["nvidia-smi", "--query-compute-apps=gpu_uuid,pid", "--format=csv,noheader"], capture_output=True, text=True, env=env).stdout
+        cu = ctypes.CDLL("libcuda.so.1")
+        n = ctypes.c_int(); cu.cuDeviceGetCount(ctypes.byref(n))
+        bus = ctypes.create_string_buffer(32); cu.cuDeviceGetPCIBusId(bus, 32, 0)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(0)
+        u = pynvml.nvmlDeviceGetUUID(h)
+        out.update(total=t, sum=int(x.sum().item()), drv_count=n.value, bus=bus.value.decode(), nvml_count=pynvml.nvmlDeviceGetCount(),
+                   nvml_uuid=u.decode() if isinstance(u, bytes) else u, nvml_total=pynvml.nvmlDeviceGetMemoryInfo(h).total,
+                   where=[l.split(",")[0].strip() for l in smi.strip().splitlines() if l.strip().endswith(str(os.getpid()))],
+                   cvd=os.environ.get("CUDA_VISIBLE_DEVICES"))
+        print(json.dumps(out))
+    """
+    # (a) nothing preset: the shim hides the other GPU; (b) the host's "0,1" handed down: read as the container's own
+    # ordinals (virtual 0 exists, virtual 1 does not) and rewritten; either way the runtime must come up
+    saved = os.environ.pop("CUDA_VISIBLE_DEVICES", None)
+    try:
+        for preset in (None, "0,1"):
+            extra = {"NVIDIA_DEVICE_MAP": f"0:{uuid1}", "CUDA_DEVICE_MEMORY_LIMIT_0": "6g"}
+            if preset:
+                extra["CUDA_VISIBLE_DEVICES"] = preset
+            p = run_under_shim(code, extra)
+            o = last_json(p)
+            print("subset map, preset", preset, ":", o)
+            assert o["cvd"] == uuid1
+            assert o["count"] == 1 == o["drv_count"] == o["nvml_count"]
+            assert o["total"] == 6 * GiB == o["nvml_total"] and o["sum"] == 1 << 28
+            assert o["nvml_uuid"] == uuid1 and o["bus"].lower().endswith(bus1.lower()[-10:])
+            assert o["where"] == [uuid1]                              # the process lives on the second GPU only
+    finally:
+        if saved is not None:
+            os.environ["CUDA_VISIBLE_DEVICES"] = saved
+
+
 def test_nvml_memory_info_shows_the_limit(cuda_dev):
     code = """
         import json, torch, pynvml
