@@ -1307,6 +1307,7 @@ static int nvml_dev_index(void *handle) {
  * NVML device whose memory info is the sum of its vGPUs — which is also what the CUDA runtime sees (merged device,
  * above).  (The reference makes up virtual NVML handles and wraps all 247 NVML entry points to translate them.) */
 static int g_nv_phys[VGPU_MAX_DEVICES], g_nv_n, g_nv_remap;
+static int g_nv_col0[VGPU_MAX_DEVICES], g_nv_ncols[VGPU_MAX_DEVICES];  /* the cache-file columns of each listed GPU's vGPUs */
 static pthread_once_t g_nv_once = PTHREAD_ONCE_INIT;
 static void build_nvml_view(void) {
     typedef int (*count_t)(unsigned *);
@@ -1319,18 +1320,22 @@ static void build_nvml_view(void) {
     const int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
     unsigned n = 0;
     if (nwant == 0 || !cnt || !byidx || !uuid || cnt(&n) != 0) return;
+    int col = 0;
     for (unsigned i = 0; i < n && i < VGPU_MAX_DEVICES; ++i) {
         void *h;
         char u[VGPU_UUID_LEN];
         if (byidx(i, &h) != 0 || uuid(h, u, sizeof(u)) != 0) continue;
-        for (int k = 0; k < nwant && g_nv_n < VGPU_MAX_DEVICES; ++k)
-            if (strcasecmp(want[k], u) == 0) {
-                g_nv_phys[g_nv_n++] = (int)i;
-                break;  /* a GPU named twice is still one NVML device */
-            }
+        int named = 0;
+        for (int k = 0; k < nwant; ++k) named += strcasecmp(want[k], u) == 0;
+        if (named && g_nv_n < VGPU_MAX_DEVICES) {  /* a GPU named twice is still one NVML device, with two columns */
+            g_nv_phys[g_nv_n] = (int)i;
+            g_nv_col0[g_nv_n] = col;
+            g_nv_ncols[g_nv_n++] = named;
+            col += named;
+        }
     }
     g_nv_remap = g_nv_n > 0 && g_nv_n != (int)n;
-    for (int i = 0; i < g_nv_n; ++i) g_nv_remap |= g_nv_phys[i] != i;
+    for (int i = 0; i < g_nv_n; ++i) g_nv_remap |= g_nv_phys[i] != i || g_nv_ncols[i] != 1;
 }
 
 EXPORT int nvmlDeviceGetCount_v2(unsigned *count) {
@@ -1357,23 +1362,26 @@ EXPORT int nvmlDeviceGetHandleByIndex_v2(unsigned index, void **handle) {
 }
 EXPORT int nvmlDeviceGetHandleByIndex(unsigned index, void **handle) { return nvmlDeviceGetHandleByIndex_v2(index, handle); }
 
-/* usage / limit as NVML should show them for a physical GPU: with several vGPUs of this container on it
- * (virtual devices) the sums; a GPU with any unlimited vGPU counts as unlimited */
+/* usage / limit as NVML should show them for a physical GPU (by its NVML index, whatever the CUDA side enumerates):
+ * the sums over the cache-file columns of this container's vGPUs on it; any unlimited vGPU makes it unlimited */
 static void nvml_quota(int nvml_index, uint64_t *usage, uint64_t *limit) {
-    ensure_vdev();
-    if (!g_remap) {
-        *usage = region_usage(nvml_index);
-        *limit = region_limit(nvml_index);
-        return;
+    pthread_once(&g_nv_once, build_nvml_view);
+    int col0 = nvml_index, ncols = 1;
+    if (g_nv_remap) {
+        ncols = 0;  /* a GPU the map does not name: no quota of ours applies */
+        for (int i = 0; i < g_nv_n; ++i)
+            if (g_nv_phys[i] == nvml_index) {
+                col0 = g_nv_col0[i];
+                ncols = g_nv_ncols[i];
+            }
     }
-    int unlimited = 0;
+    int unlimited = ncols == 0;
     *usage = *limit = 0;
-    for (int i = 0; i < g_nvdev; ++i)
-        if (g_vdev[i].phys == nvml_index) {
-            *usage += q_usage(i);
-            *limit += q_limit(i);
-            unlimited |= q_limit(i) == 0;
-        }
+    for (int c = col0; c < col0 + ncols; ++c) {
+        *usage += region_usage(c);
+        *limit += region_limit(c);
+        unlimited |= region_limit(c) == 0;
+    }
     if (unlimited) *limit = 0;
 }
 

@@ -161,9 +161,11 @@ def test_subset_map_enforces_the_quota_on_the_mapped_gpu():
     """Container sees two GPUs, the map gives it the second: its limit applies to allocations made there (the
     reference gives up on the quota whenever the real device count differs from the map's)."""
     env = {"MOCK_GPU_COUNT": "2", "NVIDIA_DEVICE_MAP": f"0:{H.UUID0[:-1]}2", "CUDA_DEVICE_MEMORY_LIMIT_0": "1g"}
-    ops = ["retain 0 1", "ctxset 1", f"alloc {600 << 20} 1", f"alloc {600 << 20} 2", "info", "total 0"]
+    ops = ["retain 0 1", "ctxset 1", f"alloc {600 << 20} 1", f"alloc {600 << 20} 2", "info", "total 0", "nvmlmem"]
     r = H.run_trace(H.NEW_LIB, [(0, o) for o in ops], env)
-    assert r["replies"][2:] == ["0", "-1", f"0 {(1 << 30) - (600 << 20)} {1 << 30}", f"0 {1 << 30}"]
+    assert r["replies"][2:6] == ["0", "-1", f"0 {(1 << 30) - (600 << 20)} {1 << 30}", f"0 {1 << 30}"]
+    # NVML index 0 is the mapped (second) GPU too, and shows column 0's quota
+    assert r["replies"][6] == f"0 {1 << 30} {(1 << 30) - (600 << 20)} {600 << 20}"
     assert any(c.startswith("cuMemAlloc_v2 size=629145600") for c in r["calls"])
 
 

@@ -209,6 +209,7 @@ def test_subset_map_hides_the_other_gpu_from_driver_runtime_and_nvml(cuda_dev):
         env = {k: v for k, v in os.environ.items() if k != "LD_PRELOAD"}
         smi = subprocess.run(["nvidia-smi", "--query-compute-apps=gpu_uuid,pid", "--format=csv,noheader"], capture_output=True, text=True, env=env).stdout
         cu = ctypes.CDLL("libcuda.so.1")
+        libc_getenv = ctypes.CDLL(None).getenv; libc_getenv.restype = ctypes.c_void_p   # os.environ is Python's start-up copy
         n = ctypes.c_int(); cu.cuDeviceGetCount(ctypes.byref(n))
         bus = ctypes.create_string_buffer(32); cu.cuDeviceGetPCIBusId(bus, 32, 0)
         pynvml.nvmlInit()
@@ -217,7 +218,7 @@ def test_subset_map_hides_the_other_gpu_from_driver_runtime_and_nvml(cuda_dev):
         out.update(total=t, sum=int(x.sum().item()), drv_count=n.value, bus=bus.value.decode(), nvml_count=pynvml.nvmlDeviceGetCount(),
                    nvml_uuid=u.decode() if isinstance(u, bytes) else u, nvml_total=pynvml.nvmlDeviceGetMemoryInfo(h).total,
                    where=[l.split(",")[0].strip() for l in smi.strip().splitlines() if l.strip().endswith(str(os.getpid()))],
-                   cvd=os.environ.get("CUDA_VISIBLE_DEVICES"))
+                   cvd=ctypes.string_at(ctypes.cast(libc_getenv(b"CUDA_VISIBLE_DEVICES"), ctypes.c_char_p)).decode())
         print(json.dumps(out))
     """
     # (a) nothing preset: the shim hides the other GPU; (b) the host's "0,1" handed down: read as the container's own
