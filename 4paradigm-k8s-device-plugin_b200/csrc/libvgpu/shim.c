@@ -165,6 +165,7 @@ static void init_limits(vgpu_region_init_t *init) {
 static pthread_once_t g_pre_once = PTHREAD_ONCE_INIT, g_post_once = PTHREAD_ONCE_INIT;
 static int g_virtual_devices = -1;  /* entries of NVIDIA_DEVICE_MAP, else the real device count */
 static int g_allocmode = 2;         /* 0: oversubscribe route, 2: plain cuMemAlloc (postInit@0x16ded) */
+static int g_strict;                /* VGPU_STRICT_QUOTA=1: also meter the allocation paths the reference lets through */
 static int g_region_ok = 0;
 
 static int count_device_map(void) {
@@ -296,6 +297,8 @@ static void start_mover(void);
 static void post_init(void) {
     const char *o = getenv("CUDA_OVERSUBSCRIBE");
     g_allocmode = (o && strcmp(o, "true") == 0) ? 0 : 2;
+    const char *st = getenv("VGPU_STRICT_QUOTA");
+    g_strict = st && *st && strcmp(st, "0") != 0;
     if (g_allocmode == 0) load_vmm_backend();
     if (g_virtual_devices <= 0 && get_cuDeviceGetCount()) {
         int n = 0;
@@ -1600,18 +1603,177 @@ typedef struct { int type, handle_types; shim_mem_location_t location; void *win
 _Static_assert(sizeof(shim_alloc_prop_t) == 32, "CUmemAllocationProp ABI");
 typedef struct { shim_mem_location_t location; int flags; } shim_access_desc_t;
 
+/* ------------------------------------------------------------------ strict quota (opt-in, no reference counterpart)
+ * The reference meters cuMemAlloc / Managed / Pitch only: a tenant that allocates through the stream-ordered
+ * allocator (cudaMallocAsync, PyTorch backend:cudaMallocAsync) or the VMM API (cuMemCreate + cuMemMap, PyTorch
+ * expandable_segments) is outside its quota altogether.  With VGPU_STRICT_QUOTA=1 those paths are billed as well:
+ *   cuMemAllocAsync / cuMemAllocFromPoolAsync  checked like cuMemAllocManaged (-> 2 = OUT_OF_MEMORY when over), tracked in
+ *                                              the allocation list, so cuMemFreeAsync and cuMemFree both give them back;
+ *   cuMemCreate                                checked and billed to the vGPU of prop->location; the bytes come back
+ *                                              when the handle has been released AND unmapped everywhere (physical
+ *                                              memory outlives cuMemRelease while a mapping exists).
+ * Off by default so that recorded traces decide exactly as the reference does. */
+typedef struct { unsigned long long h; size_t n; int vdev, released, maps; } vmm_handle_t;
+typedef struct { CUdeviceptr p; size_t n; unsigned long long h; } vmm_map_t;
+static vmm_handle_t *g_vh;
+static vmm_map_t *g_vm;
+static size_t g_nvh, g_capvh, g_nvm, g_capvm;
+
+static vmm_handle_t *vh_find(unsigned long long h) {
+    for (size_t i = 0; i < g_nvh; ++i)
+        if (g_vh[i].h == h) return &g_vh[i];
+    return NULL;
+}
+static void vh_settle(vmm_handle_t *v) {  /* with g_alloc_mu held */
+    if (!v->released || v->maps > 0) return;
+    const int vdev = v->vdev;
+    const size_t n = v->n;
+    *v = g_vh[--g_nvh];
+    region_rm_usage(col_of(vdev), n, VGPU_USE_DATA);
+}
+
 EXPORT CUresult cuMemCreate(unsigned long long *handle, size_t size, const shim_alloc_prop_t *prop, unsigned long long flags) {
     typedef CUresult (*fn_t)(unsigned long long *, size_t, const shim_alloc_prop_t *, unsigned long long);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuMemCreate");
-    shim_alloc_prop_t p2;
-    if (!tl_bypass && prop) {
-        p2 = *prop;
-        if (!loc_to_phys(&p2.location)) return 101;
-        prop = &p2;
+    if (tl_bypass || !prop) return f ? f(handle, size, prop, flags) : 3;
+    shim_alloc_prop_t p2 = *prop;
+    const int vdev = prop->location.id;
+    if (!loc_to_phys(&p2.location)) return 101;
+    const int metered = g_strict && g_region_ok && prop->location.type == 1;
+    if (metered) {
+        ensure_initialized();
+        wait_running();
+        if (oom_check(vdev, size)) return 2;
     }
-    return f ? f(handle, size, prop, flags) : 3;
+    CUresult rc = f ? f(handle, size, &p2, flags) : 3;
+    if (rc == 0 && metered) {
+        pthread_mutex_lock(&g_alloc_mu);
+        if (g_nvh == g_capvh) {
+            g_capvh = g_capvh ? 2 * g_capvh : 64;
+            g_vh = (vmm_handle_t *)realloc(g_vh, g_capvh * sizeof(*g_vh));
+        }
+        g_vh[g_nvh++] = (vmm_handle_t){*handle, size, vdev, 0, 0};
+        pthread_mutex_unlock(&g_alloc_mu);
+        region_add_usage(col_of(vdev), size, VGPU_USE_DATA);
+    }
+    return rc;
 }
+
+EXPORT CUresult cuMemRelease(unsigned long long handle) {
+    typedef CUresult (*fn_t)(unsigned long long);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemRelease");
+    CUresult rc = f ? f(handle) : 3;
+    if (rc == 0 && !tl_bypass && g_strict) {
+        pthread_mutex_lock(&g_alloc_mu);
+        vmm_handle_t *v = vh_find(handle);
+        if (v) {
+            v->released = 1;
+            vh_settle(v);
+        }
+        pthread_mutex_unlock(&g_alloc_mu);
+    }
+    return rc;
+}
+
+EXPORT CUresult cuMemMap(CUdeviceptr ptr, size_t size, size_t offset, unsigned long long handle, unsigned long long flags) {
+    typedef CUresult (*fn_t)(CUdeviceptr, size_t, size_t, unsigned long long, unsigned long long);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemMap");
+    CUresult rc = f ? f(ptr, size, offset, handle, flags) : 3;
+    if (rc == 0 && !tl_bypass && g_strict) {
+        pthread_mutex_lock(&g_alloc_mu);
+        vmm_handle_t *v = vh_find(handle);
+        if (v) {
+            if (g_nvm == g_capvm) {
+                g_capvm = g_capvm ? 2 * g_capvm : 64;
+                g_vm = (vmm_map_t *)realloc(g_vm, g_capvm * sizeof(*g_vm));
+            }
+            g_vm[g_nvm++] = (vmm_map_t){ptr, size, handle};
+            ++v->maps;
+        }
+        pthread_mutex_unlock(&g_alloc_mu);
+    }
+    return rc;
+}
+
+EXPORT CUresult cuMemUnmap(CUdeviceptr ptr, size_t size) {
+    typedef CUresult (*fn_t)(CUdeviceptr, size_t);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemUnmap");
+    CUresult rc = f ? f(ptr, size) : 3;
+    if (rc == 0 && !tl_bypass && g_strict) {
+        pthread_mutex_lock(&g_alloc_mu);
+        for (size_t i = 0; i < g_nvm;) {  /* the range covers whole mappings (driver rule) */
+            if (g_vm[i].p >= ptr && g_vm[i].p + g_vm[i].n <= ptr + size) {
+                vmm_handle_t *v = vh_find(g_vm[i].h);
+                g_vm[i] = g_vm[--g_nvm];
+                if (v) {
+                    --v->maps;
+                    vh_settle(v);
+                }
+            } else {
+                ++i;
+            }
+        }
+        pthread_mutex_unlock(&g_alloc_mu);
+    }
+    return rc;
+}
+
+/* stream-ordered allocations: legacy-stream and per-thread-stream flavours share the accounting */
+static CUresult alloc_async(CUdeviceptr *dptr, size_t n, void *pool, void *stream, int from_pool, int ptsz) {
+    typedef CUresult (*a_t)(CUdeviceptr *, size_t, void *);
+    typedef CUresult (*p_t)(CUdeviceptr *, size_t, void *, void *);
+    static void *fn[4];
+    static const char *names[4] = {"cuMemAllocAsync", "cuMemAllocAsync_ptsz", "cuMemAllocFromPoolAsync", "cuMemAllocFromPoolAsync_ptsz"};
+    const int k = 2 * from_pool + ptsz;
+    if (!fn[k]) fn[k] = cuda_sym(names[k]);
+    if (!fn[k]) return 3;
+    const int metered = !tl_bypass && g_strict;
+    if (metered) {
+        ensure_initialized();
+        pthread_once(&g_post_once, post_init);
+        wait_running();
+        if (oom_check(-1, n)) return 2;
+    }
+    CUresult rc = from_pool ? ((p_t)fn[k])(dptr, n, pool, stream) : ((a_t)fn[k])(dptr, n, stream);
+    if (rc == 0 && metered) {
+        pthread_mutex_lock(&g_alloc_mu);
+        add_chunk_only(*dptr, n);
+        pthread_mutex_unlock(&g_alloc_mu);
+    }
+    return rc;
+}
+EXPORT CUresult cuMemAllocAsync(CUdeviceptr *dptr, size_t n, void *stream) { return alloc_async(dptr, n, NULL, stream, 0, 0); }
+EXPORT CUresult cuMemAllocAsync_ptsz(CUdeviceptr *dptr, size_t n, void *stream) { return alloc_async(dptr, n, NULL, stream, 0, 1); }
+EXPORT CUresult cuMemAllocFromPoolAsync(CUdeviceptr *dptr, size_t n, void *pool, void *stream) { return alloc_async(dptr, n, pool, stream, 1, 0); }
+EXPORT CUresult cuMemAllocFromPoolAsync_ptsz(CUdeviceptr *dptr, size_t n, void *pool, void *stream) { return alloc_async(dptr, n, pool, stream, 1, 1); }
+
+static CUresult free_async(CUdeviceptr dptr, void *stream, int ptsz) {
+    typedef CUresult (*fn_t)(CUdeviceptr, void *);
+    static fn_t fn[2];
+    if (!fn[ptsz]) fn[ptsz] = (fn_t)cuda_sym(ptsz ? "cuMemFreeAsync_ptsz" : "cuMemFreeAsync");
+    if (!fn[ptsz]) return 3;
+    if (!tl_bypass && g_strict && dptr) {
+        pthread_mutex_lock(&g_alloc_mu);
+        alloc_node_t *a = g_head;
+        while (a && a->addr != dptr) a = a->next;
+        if (a) {
+            if (a->prev) a->prev->next = a->next; else g_head = a->next;
+            if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
+            --g_nalloc;
+            region_rm_usage(col_of(a->dev), a->len, VGPU_USE_DATA);
+            free(a);
+        }
+        pthread_mutex_unlock(&g_alloc_mu);
+    }
+    return fn[ptsz](dptr, stream);
+}
+EXPORT CUresult cuMemFreeAsync(CUdeviceptr dptr, void *stream) { return free_async(dptr, stream, 0); }
+EXPORT CUresult cuMemFreeAsync_ptsz(CUdeviceptr dptr, void *stream) { return free_async(dptr, stream, 1); }
+
 EXPORT CUresult cuMemGetAllocationGranularity(size_t *g, const shim_alloc_prop_t *prop, int option) {
     typedef CUresult (*fn_t)(size_t *, const shim_alloc_prop_t *, int);
     static fn_t f;
@@ -1698,6 +1860,11 @@ static const hook_t g_hooks[] = {
     {"cuCtxCreate_v3", (void *)cuCtxCreate_v3}, {"cuCtxCreate_v4", (void *)cuCtxCreate_v4},
     {"cuDeviceGetPCIBusId", (void *)cuDeviceGetPCIBusId}, {"cuDeviceGetByPCIBusId", (void *)cuDeviceGetByPCIBusId},
     {"cuMemCreate", (void *)cuMemCreate}, {"cuMemGetAllocationGranularity", (void *)cuMemGetAllocationGranularity},
+    {"cuMemRelease", (void *)cuMemRelease}, {"cuMemMap", (void *)cuMemMap}, {"cuMemUnmap", (void *)cuMemUnmap},
+    {"cuMemAllocAsync", (void *)cuMemAllocAsync}, {"cuMemAllocFromPoolAsync", (void *)cuMemAllocFromPoolAsync},
+    {"cuMemFreeAsync", (void *)cuMemFreeAsync},
+    {"cuMemAllocAsync_ptsz", (void *)cuMemAllocAsync_ptsz}, {"cuMemAllocFromPoolAsync_ptsz", (void *)cuMemAllocFromPoolAsync_ptsz},
+    {"cuMemFreeAsync_ptsz", (void *)cuMemFreeAsync_ptsz},
     {"cuMemSetAccess", (void *)cuMemSetAccess},
     {"cuGetProcAddress", (void *)cuGetProcAddress}, {"cuGetProcAddress_v2", (void *)cuGetProcAddress_v2},
     {"nvmlDeviceGetCount", (void *)nvmlDeviceGetCount_v2}, {"nvmlDeviceGetCount_v2", (void *)nvmlDeviceGetCount_v2},
@@ -1714,7 +1881,16 @@ static void *find_hook(const char *name) {
 
 /* cuGetProcAddress(symbol, cudaVersion): an unsuffixed name means the newest ABI that version knows, and for a
  * few of the hooked names that ABI has a different signature than the hook registered under the bare name */
-static void *find_hook_for_version(const char *name, int ver) {
+static void *find_hook_for_version(const char *name, int ver, unsigned long long flags) {
+    if (flags & 2ull) {  /* per-thread default stream: the stream-ordered allocator hooks have their own _ptsz twins */
+        static const char *const ptsz[] = {"cuMemAllocAsync", "cuMemAllocFromPoolAsync", "cuMemFreeAsync"};
+        for (size_t i = 0; i < sizeof(ptsz) / sizeof(ptsz[0]); ++i)
+            if (strcmp(name, ptsz[i]) == 0) {
+                char twin[64];
+                snprintf(twin, sizeof(twin), "%s_ptsz", name);
+                return find_hook(twin);
+            }
+    }
     static const struct { const char *name; int since; const char *use; } newer[] = {
         {"cuGetProcAddress", 12000, "cuGetProcAddress_v2"},
         {"cuDeviceGetUuid", 11040, "cuDeviceGetUuid_v2"},
@@ -1750,7 +1926,7 @@ EXPORT void *dlsym(void *handle, const char *symbol) {
 
 EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsigned long long flags) {
     ensure_initialized();
-    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver) : NULL;
+    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver, flags) : NULL;
     if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;
@@ -1762,7 +1938,7 @@ EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsign
 
 EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, unsigned long long flags, int *status) {
     ensure_initialized();
-    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver) : NULL;
+    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver, flags) : NULL;
     if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress_v2(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;

@@ -230,10 +230,92 @@ CUresult cuLaunchKernel(void *f, unsigned gx, unsigned gy, unsigned gz, unsigned
     return 0;
 }
 CUresult cuArray3DGetDescriptor_v2(void *d, void *a) { (void)d; (void)a; return 0; }
+/* stream-ordered allocations: same bookkeeping as cuMemAlloc, logged under their own names */
+CUresult cuMemAllocAsync(CUdeviceptr *p, size_t n, void *stream) { (void)stream; return do_alloc(p, n, 3, "cuMemAllocAsync", 0); }
+CUresult cuMemAllocFromPoolAsync(CUdeviceptr *p, size_t n, void *pool, void *stream) { (void)pool; (void)stream; return do_alloc(p, n, 3, "cuMemAllocFromPoolAsync", 0); }
+CUresult cuMemFreeAsync(CUdeviceptr p, void *stream) {
+    (void)stream;
+    cfg();
+    for (int i = 0; i < g_nalloc; ++i)
+        if (g_alloc[i].p == p) {
+            g_used[g_alloc[i].dev] -= g_alloc[i].n;
+            logf_("cuMemFreeAsync size=%llu -> rc=0", (unsigned long long)g_alloc[i].n);
+            g_alloc[i] = g_alloc[--g_nalloc];
+            return 0;
+        }
+    return 1;
+}
+/* VMM: physical memory lives from cuMemCreate until it is released AND unmapped everywhere */
+#define MAXVMM 4096
+static struct { unsigned long long h; uint64_t n; int dev, released, maps; } g_vmm[MAXVMM];
+static struct { CUdeviceptr p; uint64_t n; int slot; } g_vmap[MAXVMM];
+static int g_nvmm, g_nvmap;
+static void vmm_maybe_free(int slot) {
+    if (g_vmm[slot].h && g_vmm[slot].released && g_vmm[slot].maps == 0) {
+        g_used[g_vmm[slot].dev] -= g_vmm[slot].n;
+        logf_("vmm physical free size=%llu", (unsigned long long)g_vmm[slot].n);
+        g_vmm[slot].h = 0;
+    }
+}
+typedef struct { int type, handle_types, loc_type, loc_id; void *win32; unsigned char flags[8]; } mock_alloc_prop_t;
+CUresult cuMemCreate(unsigned long long *h, size_t n, const mock_alloc_prop_t *prop, unsigned long long flags) {
+    (void)flags;
+    cfg();
+    if (!prop || prop->loc_type != 1 || prop->loc_id < 0 || prop->loc_id >= g_ndev) return 1;
+    if (g_fail_over && n > g_fail_over) return 2;
+    if (g_nvmm >= MAXVMM) return 2;
+    g_vmm[g_nvmm].h = 0xabc000ull + (unsigned long long)g_nvmm;
+    g_vmm[g_nvmm].n = n;
+    g_vmm[g_nvmm].dev = prop->loc_id;
+    g_vmm[g_nvmm].released = g_vmm[g_nvmm].maps = 0;
+    g_used[prop->loc_id] += n;
+    *h = g_vmm[g_nvmm++].h;
+    logf_("cuMemCreate size=%llu dev=%d -> rc=0", (unsigned long long)n, prop->loc_id);
+    return 0;
+}
+static int vmm_slot(unsigned long long h) {
+    for (int i = 0; i < g_nvmm; ++i)
+        if (g_vmm[i].h == h && h) return i;
+    return -1;
+}
+CUresult cuMemRelease(unsigned long long h) {
+    int s = vmm_slot(h);
+    if (s < 0) return 0;  /* handles this mock never made (the data-path library's): accepted as before */
+    g_vmm[s].released = 1;
+    vmm_maybe_free(s);
+    return 0;
+}
+CUresult cuMemAddressReserve(CUdeviceptr *p, size_t n, size_t align, CUdeviceptr addr, unsigned long long flags) {
+    (void)align; (void)addr; (void)flags;
+    *p = g_next;
+    g_next += (n + 0x1fffffull) & ~0x1fffffull;
+    return 0;
+}
 CUresult cuMemAddressFree(CUdeviceptr p, size_t n) { (void)p; (void)n; return 0; }
-CUresult cuMemRelease(unsigned long long h) { (void)h; return 0; }
+CUresult cuMemMap(CUdeviceptr p, size_t n, size_t off, unsigned long long h, unsigned long long flags) {
+    (void)off; (void)flags;
+    int s = vmm_slot(h);
+    if (s < 0 || g_nvmap >= MAXVMM) return 1;
+    g_vmap[g_nvmap].p = p;
+    g_vmap[g_nvmap].n = n;
+    g_vmap[g_nvmap++].slot = s;
+    ++g_vmm[s].maps;
+    return 0;
+}
+CUresult cuMemUnmap(CUdeviceptr p, size_t n) {
+    for (int i = 0; i < g_nvmap;)
+        if (g_vmap[i].p >= p && g_vmap[i].p + g_vmap[i].n <= p + n) {
+            int s = g_vmap[i].slot;
+            g_vmap[i] = g_vmap[--g_nvmap];
+            --g_vmm[s].maps;
+            vmm_maybe_free(s);
+        } else {
+            ++i;
+        }
+    return 0;
+}
 CUresult cuMemSetAccess(CUdeviceptr p, size_t n, const void *d, size_t c) { (void)p; (void)n; (void)d; (void)c; return 0; }
-CUresult cuMemUnmap(CUdeviceptr p, size_t n) { (void)p; (void)n; return 0; }
+CUresult cuMemGetAllocationGranularity(size_t *g, const void *prop, int opt) { (void)prop; (void)opt; *g = 0x200000; return 0; }
 CUresult cuPointerGetAttribute(void *data, int attr, CUdeviceptr p) { (void)p; if (attr == 8) *(unsigned *)data = 1; else memset(data, 0, 8); return 0; }
 CUresult cuPointerGetAttributes(unsigned n, int *attrs, void **data, CUdeviceptr p) {
     (void)p;

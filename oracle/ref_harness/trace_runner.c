@@ -28,6 +28,11 @@
  *   ctxpush <ctag> / ctxpop   cuCtxPushCurrent_v2 / cuCtxPopCurrent_v2     -> rc [ctx#]
  *   ctxget                 cuCtxGetCurrent                                 -> rc ctx#
  *   ctxdev                 cuCtxGetDevice                                  -> rc dev
+ *   allocasync <bytes> <tag> / freeasync <tag>   cuMemAllocAsync / cuMemFreeAsync (stream 0)      -> rc
+ *   vcreate <bytes> <htag> [dev]   cuMemCreate (pinned device memory on dev, default: current)  -> rc
+ *   vmap <htag> <tag>      cuMemAddressReserve + cuMemMap + cuMemSetAccess of the whole handle   -> rc
+ *   vunmap <tag>           cuMemUnmap + cuMemAddressFree                                         -> rc
+ *   vrelease <htag>        cuMemRelease                                                          -> rc
  *   cvd                    getenv("CUDA_VISIBLE_DEVICES") as the process sees it now -> 0 value|-
  *   exporttable            cuGetExportTable (what every CUDA-runtime program does right after cuInit) -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
@@ -69,12 +74,27 @@ CUresult cuCtxPushCurrent_v2(void *);
 CUresult cuCtxPopCurrent_v2(void **);
 CUresult cuDevicePrimaryCtxRelease_v2(int);
 CUresult cuGetExportTable(const void **, const void *);
+CUresult cuMemAllocAsync(CUdeviceptr *, size_t, void *);
+CUresult cuMemFreeAsync(CUdeviceptr, void *);
+typedef struct { int type, handle_types, loc_type, loc_id; void *win32; unsigned char flags[8]; } alloc_prop_t;
+typedef struct { int loc_type, loc_id, flags; } access_desc_t;
+CUresult cuMemCreate(unsigned long long *, size_t, const alloc_prop_t *, unsigned long long);
+CUresult cuMemRelease(unsigned long long);
+CUresult cuMemAddressReserve(CUdeviceptr *, size_t, size_t, CUdeviceptr, unsigned long long);
+CUresult cuMemAddressFree(CUdeviceptr, size_t);
+CUresult cuMemMap(CUdeviceptr, size_t, size_t, unsigned long long, unsigned long long);
+CUresult cuMemUnmap(CUdeviceptr, size_t);
+CUresult cuMemSetAccess(CUdeviceptr, size_t, const access_desc_t *, size_t);
 CUresult cuLaunchKernel(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **);
 
 #define MAXTAG 200000
 static CUdeviceptr tags[MAXTAG];
 static void *htags[MAXTAG];
 
+#define MAXH 4096
+static unsigned long long htab[MAXH];
+static size_t hsize[MAXH];
+static size_t tagsize[MAXH];
 #define MAXCTX 64
 static void *ctags[MAXCTX];
 static void *seen[MAXCTX];
@@ -188,6 +208,44 @@ int main(void) {
             void *ctx = NULL;
             rc = cuCtxGetCurrent(&ctx);
             printf("%d %d\n", rc, rc == 0 ? ctx_no(ctx) : -1);
+        } else if (!strcmp(op, "allocasync")) {
+            CUdeviceptr p = 0;
+            rc = cuMemAllocAsync(&p, (size_t)a, NULL);
+            if (rc == 0 && b < MAXTAG) tags[b] = p;
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "freeasync")) {
+            printf("%d\n", cuMemFreeAsync(a < MAXTAG ? tags[a] : 0, NULL));
+        } else if (!strcmp(op, "vcreate")) {
+            int dev = 0;
+            if (n >= 4) dev = (int)c; else cuCtxGetDevice(&dev);
+            alloc_prop_t prop;
+            memset(&prop, 0, sizeof(prop));
+            prop.type = 1;      /* CU_MEM_ALLOCATION_TYPE_PINNED */
+            prop.loc_type = 1;  /* CU_MEM_LOCATION_TYPE_DEVICE */
+            prop.loc_id = dev;
+            unsigned long long h = 0;
+            rc = cuMemCreate(&h, (size_t)a, &prop, 0);
+            if (rc == 0 && b < MAXH) { htab[b] = h; hsize[b] = (size_t)a; }
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "vmap")) {
+            CUdeviceptr p = 0;
+            rc = (a < MAXH && b < MAXH && htab[a]) ? cuMemAddressReserve(&p, hsize[a], 0, 0, 0) : 1;
+            if (rc == 0) rc = cuMemMap(p, hsize[a], 0, htab[a], 0);
+            if (rc == 0) {
+                int dev = 0;
+                cuCtxGetDevice(&dev);
+                access_desc_t d = {1, dev, 3};
+                rc = cuMemSetAccess(p, hsize[a], &d, 1);
+                tags[b] = p;
+                tagsize[b] = hsize[a];
+            }
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "vunmap")) {
+            rc = a < MAXH ? cuMemUnmap(tags[a], tagsize[a]) : 1;
+            if (rc == 0) rc = cuMemAddressFree(tags[a], tagsize[a]);
+            printf("%d\n", rc);
+        } else if (!strcmp(op, "vrelease")) {
+            printf("%d\n", a < MAXH ? cuMemRelease(htab[a]) : 1);
         } else if (!strcmp(op, "cvd")) {
             const char *v = getenv("CUDA_VISIBLE_DEVICES");
             printf("0 %s\n", v ? v : "-");

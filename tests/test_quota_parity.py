@@ -212,6 +212,41 @@ def test_unlisted_gpus_are_hidden_from_the_driver_too():
     assert cvd("1,0", full) == f"0 {u2},{H.UUID0}"            # the user's order is kept
 
 
+M = 1 << 20
+UNMETERED_OPS = ["info", f"allocasync {600 * M} 1", "info", f"allocasync {600 * M} 2", "freeasync 1", "info", f"vcreate {512 * M} 1", "vmap 1 10", "info",
+                 f"vcreate {600 * M} 2", "vrelease 1", "info", "vunmap 10", "info", f"alloc {900 * M} 3", f"allocasync {100 * M} 4", "free 4", "info",
+                 "@slots"]
+
+
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+def test_stream_ordered_and_vmm_allocations_are_outside_the_quota_as_in_the_reference():
+    """cuMemAllocAsync / cuMemCreate are not metered by the reference: same replies, same driver
+    calls, 1.2 GiB of async allocations inside a 1 GiB vGPU."""
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}
+    a = H.run_trace(H.REFERENCE_LIB, [(0, o) for o in UNMETERED_OPS], env)
+    b = H.run_trace(H.NEW_LIB, [(0, o) for o in UNMETERED_OPS], env)
+    assert a["replies"] == b["replies"] and a["calls"] == b["calls"]
+    assert a["replies"][1] == a["replies"][3] == "0" and a["replies"][2] == f"0 {1 << 30} {1 << 30}"
+    assert a["replies"][16] == "-1"                     # cuMemFree of a pointer the library never tracked
+
+
+def test_strict_quota_also_meters_the_async_allocator_and_the_vmm_api():
+    """VGPU_STRICT_QUOTA=1 (no reference counterpart): the same trace with the holes closed."""
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "VGPU_STRICT_QUOTA": "1", **MAP}
+    r = H.run_trace(H.NEW_LIB, [(0, o) for o in UNMETERED_OPS], env)
+    G = 1 << 30
+    assert r["replies"] == [
+        f"0 {G} {G}", "0", f"0 {G - 600 * M} {G}",     # the first async allocation is billed
+        "2", "0", f"0 {G} {G}",                         # the second does not fit (OUT_OF_MEMORY); freeing gives the bytes back
+        "0", "0", f"0 {G - 512 * M} {G}",               # cuMemCreate is billed to the vGPU it is located on
+        "2", "0", f"0 {G - 512 * M} {G}",               # a second handle does not fit; a released handle stays billed while mapped
+        "0", f"0 {G} {G}",                              # unmapped: the physical memory is gone, so is the bill
+        "0", "0", "0", f"0 {G - 900 * M} {G}",          # cuMemFree of a stream-ordered allocation is known now
+        f"n=1 p0:0:1 d0=0/0/{900 * M}/{900 * M}"]
+    assert r["oom"] == [(0, 1200 * M, G), (0, 1112 * M, G)]
+    assert "cuMemCreate size=629145600 dev=0 -> rc=0" not in r["calls"]      # refused before the driver was asked
+
+
 def test_two_processes_share_one_cache_file():
     """SURVEY c.3: A holds 500 MiB, B allocates 100 MiB and reads free = 1024-500-100 MiB;
     managed 900 MiB -> 2 in both; after both exit a third process sees everything free."""

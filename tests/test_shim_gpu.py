@@ -242,6 +242,36 @@ def test_subset_map_hides_the_other_gpu_from_driver_runtime_and_nvml(cuda_dev):
             os.environ["CUDA_VISIBLE_DEVICES"] = saved
 
 
+@pytest.mark.parametrize("conf", ["expandable_segments:True", "backend:cudaMallocAsync"])
+def test_strict_quota_closes_the_allocator_paths_the_reference_leaves_open(cuda_dev, conf):
+    """PyTorch with expandable segments allocates through cuMemCreate + cuMemMap, with backend:cudaMallocAsync through
+    cuMemAllocAsync; neither is metered by the reference (nor here by default): a 4 GiB vGPU hands out 6 GiB.  With
+    VGPU_STRICT_QUOTA=1 the same program is held to its quota."""
+    code = """
+        import json, torch
+        out = {}
+        torch.cuda.init()
+        try:
+            a = torch.empty(6 << 30, dtype=torch.uint8, device="cuda"); a[-1] = 1; out["six"] = "allocated"
+        except Exception as e:
+            out["six"] = type(e).__name__
+        try:
+            b = torch.empty(2 << 30, dtype=torch.uint8, device="cuda"); b[-1] = 1; out["two"] = "allocated"
+        except Exception as e:
+            out["two"] = type(e).__name__
+        f, t = torch.cuda.mem_get_info()
+        out.update(free=f, total=t)
+        print(json.dumps(out))
+    """
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "4096m", "PYTORCH_CUDA_ALLOC_CONF": conf}
+    loose = last_json(run_under_shim(code, env))
+    strict = last_json(run_under_shim(code, {**env, "VGPU_STRICT_QUOTA": "1"}))
+    print(conf, "default:", loose, "strict:", strict)
+    assert loose["six"] == "allocated"                                   # the reference's hole, reproduced
+    assert strict["six"] != "allocated" and strict["two"] == "allocated"
+    assert strict["total"] == 4 * GiB and 1 * GiB <= strict["total"] - strict["free"] <= 3 * GiB + (512 << 20)
+
+
 def test_nvml_memory_info_shows_the_limit(cuda_dev):
     code = """
         import json, torch, pynvml
