@@ -243,7 +243,7 @@ def test_strict_quota_also_meters_the_async_allocator_and_the_vmm_api():
         "0", f"0 {G} {G}",                              # unmapped: the physical memory is gone, so is the bill
         "0", "0", "0", f"0 {G - 900 * M} {G}",          # cuMemFree of a stream-ordered allocation is known now
         f"n=1 p0:0:1 d0=0/0/{900 * M}/{900 * M}"]
-    assert r["oom"] == [(0, 1200 * M, G), (0, 1112 * M, G)]
+    assert r["oom"] == [(0, 1112 * M, G), (0, 1200 * M, G)]     # sorted by the harness: the handle, then the async allocation
     assert "cuMemCreate size=629145600 dev=0 -> rc=0" not in r["calls"]      # refused before the driver was asked
 
 

@@ -251,14 +251,12 @@ def test_strict_quota_closes_the_allocator_paths_the_reference_leaves_open(cuda_
         import json, torch
         out = {}
         torch.cuda.init()
-        try:
-            a = torch.empty(6 << 30, dtype=torch.uint8, device="cuda"); a[-1] = 1; out["six"] = "allocated"
-        except Exception as e:
-            out["six"] = type(e).__name__
-        try:
-            b = torch.empty(2 << 30, dtype=torch.uint8, device="cuda"); b[-1] = 1; out["two"] = "allocated"
-        except Exception as e:
-            out["two"] = type(e).__name__
+        keep = []
+        for name in ("first", "second"):       # 3 GiB each: together more than the 4 GiB vGPU
+            try:
+                x = torch.empty(3 << 30, dtype=torch.uint8, device="cuda"); x[-1] = 1; keep.append(x); out[name] = "allocated"
+            except Exception as e:
+                out[name] = type(e).__name__
         f, t = torch.cuda.mem_get_info()
         out.update(free=f, total=t)
         print(json.dumps(out))
@@ -267,9 +265,9 @@ def test_strict_quota_closes_the_allocator_paths_the_reference_leaves_open(cuda_
     loose = last_json(run_under_shim(code, env))
     strict = last_json(run_under_shim(code, {**env, "VGPU_STRICT_QUOTA": "1"}))
     print(conf, "default:", loose, "strict:", strict)
-    assert loose["six"] == "allocated"                                   # the reference's hole, reproduced
-    assert strict["six"] != "allocated" and strict["two"] == "allocated"
-    assert strict["total"] == 4 * GiB and 1 * GiB <= strict["total"] - strict["free"] <= 3 * GiB + (512 << 20)
+    assert loose["first"] == loose["second"] == "allocated"              # the reference's hole, reproduced: 6 GiB in a 4 GiB vGPU
+    assert strict["first"] == "allocated" and strict["second"] != "allocated"
+    assert strict["total"] == 4 * GiB and 3 * GiB <= strict["total"] - strict["free"] <= 4 * GiB
 
 
 def test_nvml_memory_info_shows_the_limit(cuda_dev):
