@@ -1619,6 +1619,16 @@ static vmm_handle_t *g_vh;
 static vmm_map_t *g_vm;
 static size_t g_nvh, g_capvh, g_nvm, g_capvm;
 
+/* room for one more element; 0 when the host is out of memory (the caller then refuses the allocation) */
+static int grow(void **arr, size_t *cap, size_t n, size_t elem) {
+    if (n < *cap) return 1;
+    const size_t ncap = *cap ? 2 * *cap : 64;
+    void *p = realloc(*arr, ncap * elem);
+    if (!p) return 0;
+    *arr = p;
+    *cap = ncap;
+    return 1;
+}
 static vmm_handle_t *vh_find(unsigned long long h) {
     for (size_t i = 0; i < g_nvh; ++i)
         if (g_vh[i].h == h) return &g_vh[i];
@@ -1641,22 +1651,19 @@ EXPORT CUresult cuMemCreate(unsigned long long *handle, size_t size, const shim_
     const int vdev = prop->location.id;
     if (!loc_to_phys(&p2.location)) return 101;
     const int metered = g_strict && g_region_ok && prop->location.type == 1;
-    if (metered) {
-        ensure_initialized();
-        wait_running();
-        if (oom_check(vdev, size)) return 2;
-    }
-    CUresult rc = f ? f(handle, size, &p2, flags) : 3;
-    if (rc == 0 && metered) {
-        pthread_mutex_lock(&g_alloc_mu);
-        if (g_nvh == g_capvh) {
-            g_capvh = g_capvh ? 2 * g_capvh : 64;
-            g_vh = (vmm_handle_t *)realloc(g_vh, g_capvh * sizeof(*g_vh));
+    if (!metered) return f ? f(handle, size, &p2, flags) : 3;
+    ensure_initialized();
+    wait_running();
+    pthread_mutex_lock(&g_alloc_mu);  /* check, allocate and bill as one step, like cuMemAlloc */
+    CUresult rc = 2;
+    if (!oom_check(vdev, size) && grow((void **)&g_vh, &g_capvh, g_nvh, sizeof(*g_vh))) {
+        rc = f ? f(handle, size, &p2, flags) : 3;
+        if (rc == 0) {
+            g_vh[g_nvh++] = (vmm_handle_t){*handle, size, vdev, 0, 0};
+            region_add_usage(col_of(vdev), size, VGPU_USE_DATA);
         }
-        g_vh[g_nvh++] = (vmm_handle_t){*handle, size, vdev, 0, 0};
-        pthread_mutex_unlock(&g_alloc_mu);
-        region_add_usage(col_of(vdev), size, VGPU_USE_DATA);
     }
+    pthread_mutex_unlock(&g_alloc_mu);
     return rc;
 }
 
@@ -1685,11 +1692,7 @@ EXPORT CUresult cuMemMap(CUdeviceptr ptr, size_t size, size_t offset, unsigned l
     if (rc == 0 && !tl_bypass && g_strict) {
         pthread_mutex_lock(&g_alloc_mu);
         vmm_handle_t *v = vh_find(handle);
-        if (v) {
-            if (g_nvm == g_capvm) {
-                g_capvm = g_capvm ? 2 * g_capvm : 64;
-                g_vm = (vmm_map_t *)realloc(g_vm, g_capvm * sizeof(*g_vm));
-            }
+        if (v && grow((void **)&g_vm, &g_capvm, g_nvm, sizeof(*g_vm))) {
             g_vm[g_nvm++] = (vmm_map_t){ptr, size, handle};
             ++v->maps;
         }
@@ -1731,19 +1734,17 @@ static CUresult alloc_async(CUdeviceptr *dptr, size_t n, void *pool, void *strea
     const int k = 2 * from_pool + ptsz;
     if (!fn[k]) fn[k] = cuda_sym(names[k]);
     if (!fn[k]) return 3;
-    const int metered = !tl_bypass && g_strict;
-    if (metered) {
-        ensure_initialized();
-        pthread_once(&g_post_once, post_init);
-        wait_running();
-        if (oom_check(-1, n)) return 2;
+    if (tl_bypass || !g_strict) return from_pool ? ((p_t)fn[k])(dptr, n, pool, stream) : ((a_t)fn[k])(dptr, n, stream);
+    ensure_initialized();
+    pthread_once(&g_post_once, post_init);
+    wait_running();
+    pthread_mutex_lock(&g_alloc_mu);
+    CUresult rc = 2;
+    if (!oom_check(-1, n)) {
+        rc = from_pool ? ((p_t)fn[k])(dptr, n, pool, stream) : ((a_t)fn[k])(dptr, n, stream);
+        if (rc == 0) add_chunk_only(*dptr, n);
     }
-    CUresult rc = from_pool ? ((p_t)fn[k])(dptr, n, pool, stream) : ((a_t)fn[k])(dptr, n, stream);
-    if (rc == 0 && metered) {
-        pthread_mutex_lock(&g_alloc_mu);
-        add_chunk_only(*dptr, n);
-        pthread_mutex_unlock(&g_alloc_mu);
-    }
+    pthread_mutex_unlock(&g_alloc_mu);
     return rc;
 }
 EXPORT CUresult cuMemAllocAsync(CUdeviceptr *dptr, size_t n, void *stream) { return alloc_async(dptr, n, NULL, stream, 0, 0); }
