@@ -8,12 +8,23 @@
  * real dlsym is found with dlvsym (glibc >= 2.34 has no _dl_sym@GLIBC_PRIVATE, which is why the
  * reference binary needs a helper to even start on this image).
  *
- * Hooked on the quota path (★ rows of SURVEY §8a):
- *   cuInit, cuDeviceTotalMem_v2, cuMemGetInfo_v2, cuMemAlloc_v2, cuMemAllocManaged,
- *   cuMemAllocPitch_v2, cuMemFree_v2, cuMemAllocHost_v2, cuMemHostAlloc, cuMemHostRegister_v2,
- *   cuDevicePrimaryCtxRetain / Release, cuCtxCreate_v2 (context charge), cuLaunchKernel,
- *   cuGetProcAddress(_v2), nvmlDeviceGetMemoryInfo(_v2), dlsym.  Everything else resolves straight
- *   to the real driver.
+ * Sections, in file order (every hook is also listed in g_hooks[] at the end, which is what dlsym and
+ * cuGetProcAddress consult):
+ *   real entry points, env, init      how the driver's own functions are found; limits from the environment;
+ *                                     pre_init (before the real cuInit: NVML, cache file, CUDA_VISIBLE_DEVICES)
+ *   oversubscribe backend             CUDA_OVERSUBSCRIBE route: managed memory (reference) or the VMM data path
+ *   virtual devices                   NVIDIA_DEVICE_MAP as a device table: ordinals, cache-file columns, merged mode
+ *   allocation list, hooks            the quota path proper (★ rows of SURVEY §8a): cuMemAlloc_v2, cuMemAllocManaged,
+ *                                     cuMemAllocPitch_v2, cuMemFree_v2, cuMemGetInfo_v2, cuDeviceTotalMem_v2, host
+ *                                     allocations, cuPointerGetAttributes
+ *   context charge                    host pid probe, context billing (cuDevicePrimaryCtxRetain / Release, cuCtxCreate_v2)
+ *   SM cap: green contexts            CUDA_DEVICE_SM_LIMIT as a spatial partition; cuCtx* hooks that swap it in;
+ *                                     launch / copy / memset gates for suspend
+ *   NVML                              count / handle narrowing, memory info with the quota
+ *   virtual devices: entry points     every driver call that takes or returns a device ordinal
+ *   strict quota                      opt-in metering of cuMemAllocAsync / cuMemCreate
+ *   dispatch                          g_hooks[], versioned lookup, dlsym, cuGetProcAddress(_v2), suspend / resume
+ * Calls not listed in g_hooks[] resolve straight to the real driver.
  */
 #define _GNU_SOURCE
 #include <dlfcn.h>
