@@ -138,15 +138,24 @@ def test_two_vgpus_on_one_physical_gpu_are_two_cuda_devices(cuda_dev):
             # the memory is real and usable from this context
             cu.cuMemsetD32_v2(ctypes.c_ulonglong(p.value), ctypes.c_uint(0xC0FFEE00 + i), ctypes.c_size_t(1 << 20))
             host = (ctypes.c_uint * 4)(); rc_cp = cu.cuMemcpyDtoH_v2(host, ctypes.c_ulonglong(p.value + (1 << 21)), ctypes.c_size_t(16))
+            seen = ctypes.c_void_p(); cu.cuCtxGetCurrent(ctypes.byref(seen))
+            shim = ctypes.CDLL(None)
+            shim.cuVGPUPartitionCtx.restype = ctypes.c_void_p
             res.append({"cur": cur.value, "free": f.value, "total": t.value, "rc_fit": rc_fit, "rc_over": ctypes.c_int(rc_over).value,
-                        "free_after": f2.value, "rc_cp": rc_cp, "word": host[0]})
+                        "free_after": f2.value, "rc_cp": rc_cp, "word": host[0], "same_handle": seen.value == ctxs[i].value,
+                        "sms": shim.cuVGPUPartitionSmCount(i), "partition_ctx": shim.cuVGPUPartitionCtx(i) or 0})
         out["ctx"] = res
         print(json.dumps(out))
     """
     uuid = _gpu0_uuid()
-    p = run_under_shim(code, {"NVIDIA_DEVICE_MAP": f"0:{uuid} 1:{uuid}", "CUDA_DEVICE_MEMORY_LIMIT_0": "4g", "CUDA_DEVICE_MEMORY_LIMIT_1": "8g"})
+    p = run_under_shim(code, {"NVIDIA_DEVICE_MAP": f"0:{uuid} 1:{uuid}", "CUDA_DEVICE_MEMORY_LIMIT_0": "4g", "CUDA_DEVICE_MEMORY_LIMIT_1": "8g",
+                              "CUDA_DEVICE_SM_LIMIT_0": "25", "CUDA_DEVICE_SM_LIMIT_1": "50"})
     o = last_json(p)
     print("virtual devices:", o)
+    # each vGPU also gets ITS SM share as a green-context partition, bound behind the handle the application holds
+    assert [r["same_handle"] for r in o["ctx"]] == [True, True]
+    assert 0 < o["ctx"][0]["sms"] <= 37 and 37 < o["ctx"][1]["sms"] <= 74
+    assert o["ctx"][0]["partition_ctx"] and o["ctx"][1]["partition_ctx"] and o["ctx"][0]["partition_ctx"] != o["ctx"][1]["partition_ctx"]
     assert o["count"] == 2 and o["get_oob"] == 101 and o["distinct_ctx"]
     a, b = o["devs"]
     assert (a["dev"], b["dev"]) == (0, 1) and a["name"] == b["name"] and a["sms"] == b["sms"] > 0
