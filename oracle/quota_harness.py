@@ -68,14 +68,34 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
                     raise RuntimeError(f"runner {p} did not start: {first!r}")
                 procs.append(pr)
             if parallel:
+                # replies are drained by one reader thread per process while the ops are being written: with the pipes
+                # only, a long trace fills the runner's stdout pipe and both sides block
+                import threading
+                per_proc = [[] for _ in procs]
+                want = [sum(1 for p, _ in trace if p == i) for i in range(nprocs)]
+
+                def drain(i):
+                    for _ in range(want[i]):
+                        line = procs[i].stdout.readline()
+                        if not line:
+                            break
+                        per_proc[i].append(line.strip())
+
+                readers = [threading.Thread(target=drain, args=(i,), daemon=True) for i in range(nprocs)]
+                for t in readers:
+                    t.start()
                 for p, op in trace:
                     procs[p].stdin.write(op + "\n")
-                    procs[p].stdin.flush()
+                for pr in procs:
+                    pr.stdin.flush()
+                for t in readers:
+                    t.join(timeout=300)
+                nxt = [0] * nprocs
                 for p, op in trace:
-                    line = procs[p].stdout.readline()
-                    if not line:
+                    if nxt[p] >= len(per_proc[p]):
                         raise RuntimeError(f"runner {p} died on {op!r}")
-                    replies.append(line.strip())
+                    replies.append(per_proc[p][nxt[p]])
+                    nxt[p] += 1
                 trace = []
             for p, op in trace:
                 if op == "@slots":  # answered by the harness: the live process slots of the cache file
