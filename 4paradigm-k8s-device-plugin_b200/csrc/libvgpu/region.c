@@ -94,11 +94,31 @@ static int kick_dead_nolock(int self) {
     return kicked;
 }
 
+/* rm_quitted_process@0x425b6, the OOM path's sweep.  Not the same compaction as the one at start-up: survivors keep
+ * their order and are moved down slot by slot, and only `pid` and `used[]` travel (memcpy of 0x280 bytes @0x42900) —
+ * hostpid, monitorused and status of the slot they land in stay what they were; slots past the new proc_num keep
+ * their bytes.  The reference decides "alive" by finding the pid in the output of `ps ax`; here /proc/<pid>/stat. */
 int region_reap_dead(void) {
     region_lock();
-    int n = kick_dead_nolock(g_pid);
+    vgpu_region_t *r = g_reg;
+    int j = 0, any = 0;
+    for (int i = 0; i < r->proc_num; ++i) {
+        const int pid = r->procs[i].pid;
+        if (pid == 0 || (pid != g_pid && proc_is_dead(pid))) {
+            SHIM_WARN("Kick dead proc %d", pid);
+            any = 1;
+            continue;
+        }
+        if (j != i) {
+            r->procs[j].pid = pid;
+            memcpy(r->procs[j].used, r->procs[i].used, sizeof(r->procs[j].used));
+        }
+        ++j;
+    }
+    r->proc_num = j;
+    __sync_synchronize();
     region_unlock();
-    return n;
+    return any;
 }
 
 void (*region_status_hook)(int status);  /* set by the shim; must be async-signal-safe */

@@ -46,6 +46,10 @@ CASES = [
      {"CUDA_DEVICE_MEMORY_LIMIT_0": "4g", "MOCK_CTX_MIB": "517", **MAP}, 4),
     ("ctx_random_4p_oversub", H.with_contexts(H.random_trace(0x5EED + 4, 3000, 4, 1 << 27), 4),
      {"CUDA_DEVICE_MEMORY_LIMIT_0": "3g", "MOCK_CTX_MIB": "517", "CUDA_OVERSUBSCRIBE": "true", **MAP}, 4),
+    # processes that die without their exit handler: swept by the OOM path (rm_quitted_process@0x425b6)
+    ("dead_process", H.dead_process_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}, 3),
+    ("dead_process_ctx", H.with_contexts(H.dead_process_trace(), 3), {"CUDA_DEVICE_MEMORY_LIMIT_0": "2g", **CTX, **MAP}, 3),
+    ("dead_random_6p", H.with_kills(H.random_trace(0x5EED + 5, 4000, 6, 1 << 27), 0xD1E, 6, 3), {"CUDA_DEVICE_MEMORY_LIMIT_0": "2g", **MAP}, 6),
     # virtual devices: NVIDIA_DEVICE_MAP with a GPU named twice / a subset / another order
     ("remap_shared_gpu", H.remap_shared_gpu_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "CUDA_DEVICE_MEMORY_LIMIT_1": "2g", **CTX,
                                                     "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{H.UUID0}"}, 1),

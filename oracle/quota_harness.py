@@ -101,6 +101,11 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
                 if op == "@slots":  # answered by the harness: the live process slots of the cache file
                     replies.append(live_slots(open(cache, "rb").read(), [pr.pid for pr in procs]))
                     continue
+                if op == "@kill":   # the process dies without running its exit handler (SIGKILL): its slot stays behind
+                    procs[p].kill()
+                    procs[p].wait(timeout=20)
+                    replies.append("killed")
+                    continue
                 procs[p].stdin.write(op + "\n")
                 procs[p].stdin.flush()
                 line = procs[p].stdout.readline()
@@ -108,6 +113,8 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
                     raise RuntimeError(f"runner {p} died on {op!r}")
                 replies.append(line.strip())
             for pr in procs:  # deterministic exit order
+                if pr.poll() is not None:
+                    continue
                 pr.stdin.write("quit\n")
                 pr.stdin.flush()
                 pr.wait(timeout=20)
@@ -270,6 +277,34 @@ def remap_three_on_two_trace():
 def remap_queries_trace(n):
     """Device-level queries only (no context): count, handle, UUID byte, bus id, total memory of every virtual device."""
     return [(0, "devcount")] + [(0, f"devget {i}") for i in range(n)] + [(0, f"total {i}") for i in range(n)]
+
+
+def dead_process_trace():
+    """A process is killed while it holds memory (no exit handler runs).  Its bytes stay in the cache file until some
+    survivor runs into the limit: oom_check@0x40528 then looks for dead pids (rm_quitted_process@0x425b6), clears their
+    slots and tries again — so the allocation that first looked like an OOM succeeds."""
+    M = 1 << 20
+    return [(0, f"alloc {600 * M} 1"), (1, f"alloc {300 * M} 1"), (2, "info"), (0, "@kill"), (2, "info"), (2, "@slots"),
+            (1, f"alloc {100 * M} 2"), (1, "info"),                    # fits anyway: nobody looks for the dead yet
+            (2, f"alloc {500 * M} 1"),                                  # 600 + 400 + 500 > 1 GiB: reap, retry, fits
+            (2, "info"), (2, "@slots"), (1, f"alloc {200 * M} 3"), (1, "info"), (1, "@kill"), (2, f"alloc {500 * M} 2"), (2, "info"),
+            (2, "@slots")]
+
+
+def with_kills(trace, seed, nprocs, nkill):
+    """`nkill` of the processes die by SIGKILL at random points of the trace; what they were going to do afterwards is dropped."""
+    rng = random.Random(seed)
+    victims = rng.sample(range(1, nprocs), min(nkill, nprocs - 1))   # process 0 survives to the end
+    when = {v: rng.randrange(len(trace) // 4, 3 * len(trace) // 4) for v in victims}
+    out, dead = [], set()
+    for i, (p, op) in enumerate(trace):
+        for v in victims:
+            if when[v] == i and v not in dead:
+                out.append((v, "@kill"))
+                dead.add(v)
+        if p not in dead:
+            out.append((p, op))
+    return out
 
 
 def with_contexts(trace, nprocs):

@@ -49,8 +49,8 @@ def test_new_shim_reproduces_reference_golden(path):
 @pytest.mark.parametrize("path", GOLD, ids=lambda p: os.path.basename(p)[6:-8])
 def test_python_model_reproduces_reference_golden(path):
     g = load(path)
-    if g["name"].startswith("remap_"):
-        pytest.skip("the Python model restates the quota arithmetic, not the virtual-device table")
+    if g["name"].startswith(("remap_", "dead_")):
+        pytest.skip("the Python model restates the quota arithmetic, not the virtual-device table / the dead-process sweep")
     m = Model(g["env"], int(g["env"].get("MOCK_TOTAL_MIB", "16384")) << 20, g["nprocs"])
     for i, (p, op) in enumerate(g["trace"]):
         got = m.op(p, op)
@@ -290,6 +290,27 @@ def test_live_differential_against_reference_binary(seed, nprocs, env):
     assert a["replies"] == b["replies"]
     assert a["oom"] == b["oom"]
     assert a["calls"] == b["calls"]
+    assert H.mask_region(a["region"]) == H.mask_region(b["region"]), "final shared-cache bytes differ"
+
+
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+@pytest.mark.parametrize("seed,nprocs,nkill,env", [
+    (201, 4, 2, {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g"}),
+    (202, 6, 4, {"CUDA_DEVICE_MEMORY_LIMIT_0": "3g", "CUDA_OVERSUBSCRIBE": "true"}),
+    (203, 5, 3, {"CUDA_DEVICE_MEMORY_LIMIT_0": "4g", "MOCK_CTX_MIB": "300"}),
+])
+def test_killed_processes_are_swept_like_the_reference_does(seed, nprocs, nkill, env):
+    """SIGKILLed processes leave their slots behind; the survivors' OOM path sweeps them.  Replies, OOM lines, driver
+    calls and the final cache file (which slot each survivor ends up in, stale bytes included) must match."""
+    trace = H.random_trace(seed, 2500, nprocs, 1 << 27)
+    if "MOCK_CTX_MIB" in env:
+        trace = H.with_contexts(trace, nprocs)
+    trace = H.with_kills(trace, seed, nprocs, nkill)
+    env = {**env, **MAP}
+    a = H.run_trace(H.REFERENCE_LIB, trace, env, nprocs)
+    b = H.run_trace(H.NEW_LIB, trace, env, nprocs)
+    assert a["replies"] == b["replies"]
+    assert a["oom"] == b["oom"] and a["calls"] == b["calls"]
     assert H.mask_region(a["region"]) == H.mask_region(b["region"]), "final shared-cache bytes differ"
 
 
