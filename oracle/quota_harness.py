@@ -59,14 +59,17 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
         procs = []
         replies = []
         try:
-            for p in range(nprocs):
+            def start(p):
                 plib = lib[p] if isinstance(lib, (list, tuple)) else lib
                 pr = subprocess.Popen([os.path.join(REF_DIR, "trace_runner")], stdin=subprocess.PIPE, stdout=subprocess.PIPE,
                                       stderr=errs[p], env=_env(plib, cache, env_extra, mock_log), text=True, bufsize=1)
                 first = pr.stdout.readline().strip()  # "init <rc>"
                 if not first.startswith("init"):
                     raise RuntimeError(f"runner {p} did not start: {first!r}")
-                procs.append(pr)
+                return pr
+
+            late = {p for p, op in trace if op == "@start"}  # these come up when the trace says so, the others now
+            procs = [None if p in late else start(p) for p in range(nprocs)]
             if parallel:
                 # replies are drained by one reader thread per process while the ops are being written: with the pipes
                 # only, a long trace fills the runner's stdout pipe and both sides block
@@ -99,7 +102,18 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
                 trace = []
             for p, op in trace:
                 if op == "@slots":  # answered by the harness: the live process slots of the cache file
-                    replies.append(live_slots(open(cache, "rb").read(), [pr.pid for pr in procs]))
+                    replies.append(live_slots(open(cache, "rb").read(), [pr.pid if pr else -1 for pr in procs]))
+                    continue
+                if op == "@start":  # a process that joins later: it claims a slot in a file that already has history
+                    procs[p] = start(p)
+                    replies.append("started")
+                    continue
+                if op in ("@usr1", "@usr2"):  # the monitor's suspend (SIGUSR2) / resume (SIGUSR1) protocol
+                    import signal
+                    import time
+                    procs[p].send_signal(signal.SIGUSR2 if op == "@usr2" else signal.SIGUSR1)
+                    time.sleep(0.05)  # handlers only write the status word
+                    replies.append("signalled")
                     continue
                 if op == "@kill":   # the process dies without running its exit handler (SIGKILL): its slot stays behind
                     procs[p].kill()
@@ -113,14 +127,14 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
                     raise RuntimeError(f"runner {p} died on {op!r}")
                 replies.append(line.strip())
             for pr in procs:  # deterministic exit order
-                if pr.poll() is not None:
+                if pr is None or pr.poll() is not None:
                     continue
                 pr.stdin.write("quit\n")
                 pr.stdin.flush()
                 pr.wait(timeout=20)
         finally:
             for pr in procs:
-                if pr.poll() is None:
+                if pr is not None and pr.poll() is None:
                     pr.kill()
         oom = []
         for f in errs:
@@ -289,6 +303,16 @@ def dead_process_trace():
             (2, f"alloc {500 * M} 1"),                                  # 600 + 400 + 500 > 1 GiB: reap, retry, fits
             (2, "info"), (2, "@slots"), (1, f"alloc {200 * M} 3"), (1, "info"), (1, "@kill"), (2, f"alloc {500 * M} 2"), (2, "info"),
             (2, "@slots")]
+
+
+def late_joiner_trace():
+    """A process starts when the cache file already holds a dead process's slot: init_proc_slot_withlock@0x44820 claims a
+    slot, then clear_proc_slot_nolock@0x4468b kicks the dead (the LAST slot is copied over the dead one — another
+    compaction than the OOM path's).  Then the monitor protocol: SIGUSR2 / SIGUSR1 flip the status word of a slot."""
+    M = 1 << 20
+    return [(0, f"alloc {300 * M} 1"), (1, f"alloc {200 * M} 1"), (2, f"alloc {100 * M} 1"), (0, "@slots"), (0, "@kill"), (1, "@slots"),
+            (3, "@start"), (3, "@slots"), (3, "info"), (3, f"alloc {50 * M} 1"), (3, "@slots"), (1, "@kill"), (4, "@start"), (4, "@slots"),
+            (4, "info"), (2, "@usr2"), (2, "@slots"), (2, "@usr1"), (2, "@slots"), (2, "info")]
 
 
 def with_kills(trace, seed, nprocs, nkill):
