@@ -50,6 +50,7 @@ CASES = [
     ("dead_process", H.dead_process_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}, 3),
     ("dead_process_ctx", H.with_contexts(H.dead_process_trace(), 3), {"CUDA_DEVICE_MEMORY_LIMIT_0": "2g", **CTX, **MAP}, 3),
     ("dead_random_6p", H.with_kills(H.random_trace(0x5EED + 5, 4000, 6, 1 << 27), 0xD1E, 6, 3), {"CUDA_DEVICE_MEMORY_LIMIT_0": "2g", **MAP}, 6),
+    ("fork_children", H.fork_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}, 1),
     ("late_joiner", H.late_joiner_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}, 5),
     # virtual devices: NVIDIA_DEVICE_MAP with a GPU named twice / a subset / another order
     ("remap_shared_gpu", H.remap_shared_gpu_trace(), {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "CUDA_DEVICE_MEMORY_LIMIT_1": "2g", **CTX,

@@ -315,6 +315,16 @@ def late_joiner_trace():
             (4, "info"), (2, "@usr2"), (2, "@slots"), (2, "@usr1"), (2, "@slots"), (2, "info")]
 
 
+def fork_trace():
+    """fork(): the child is a process of its own in the cache file (child_reinit_flag@0x449eb: it claims a slot at its
+    first hooked call), its exit handler gives the slot back, `_exit` leaves it behind until some OOM sweep finds it."""
+    M = 1 << 20
+    ops = [f"alloc {100 * M} 1", "@slots", f"forkalloc {50 * M} 0", "@slots", "info", f"forkalloc {60 * M} 1", "@slots", "info",
+           f"alloc {900 * M} 2", "@slots", "info", f"forkalloc {2000 * M} 0", "@slots", f"forkalloc {10 * M} 1", f"forkalloc {10 * M} 1", "@slots",
+           "free 2", "info", f"forkalloc {900 * M} 0", "@slots"]
+    return [(0, o) for o in ops]
+
+
 def with_kills(trace, seed, nprocs, nkill):
     """`nkill` of the processes die by SIGKILL at random points of the trace; what they were going to do afterwards is dropped."""
     rng = random.Random(seed)

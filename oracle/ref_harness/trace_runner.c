@@ -33,6 +33,8 @@
  *   vmap <htag> <tag>      cuMemAddressReserve + cuMemMap + cuMemSetAccess of the whole handle   -> rc
  *   vunmap <tag>           cuMemUnmap + cuMemAddressFree                                         -> rc
  *   vrelease <htag>        cuMemRelease                                                          -> rc
+ *   forkalloc <bytes> <how>  fork(); the child allocates <bytes>, asks cuMemGetInfo, reports through a pipe and leaves with
+ *                          exit() (how=0: exit handlers run) or _exit() (how=1: they do not); the parent waits -> rc free total
  *   cvd                    getenv("CUDA_VISIBLE_DEVICES") as the process sees it now -> 0 value|-
  *   exporttable            cuGetExportTable (what every CUDA-runtime program does right after cuInit) -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
@@ -43,7 +45,9 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/wait.h>
 #include <time.h>
+#include <unistd.h>
 
 typedef int CUresult;
 typedef unsigned long long CUdeviceptr;
@@ -246,6 +250,30 @@ int main(void) {
             printf("%d\n", rc);
         } else if (!strcmp(op, "vrelease")) {
             printf("%d\n", a < MAXH ? cuMemRelease(htab[a]) : 1);
+        } else if (!strcmp(op, "forkalloc")) {
+            int fds[2];
+            if (pipe(fds) != 0) { printf("-100 0 0\n"); fflush(stdout); continue; }
+            fflush(stdout);
+            pid_t child = fork();
+            if (child == 0) {
+                CUdeviceptr p = 0;
+                size_t f = 0, t = 0;
+                long long out[3];
+                out[0] = cuMemAlloc_v2(&p, (size_t)a);
+                out[0] = out[0] * 1000 + cuMemGetInfo_v2(&f, &t);
+                out[1] = (long long)f;
+                out[2] = (long long)t;
+                if (write(fds[1], out, sizeof(out)) != (ssize_t)sizeof(out)) _exit(3);
+                if (b) _exit(0);
+                exit(0);
+            }
+            long long in[3] = {-100, 0, 0};
+            close(fds[1]);
+            if (read(fds[0], in, sizeof(in)) != (ssize_t)sizeof(in)) in[0] = -101;
+            close(fds[0]);
+            int st = 0;
+            waitpid(child, &st, 0);
+            printf("%lld %lld %lld\n", in[0], in[1], in[2]);
         } else if (!strcmp(op, "cvd")) {
             const char *v = getenv("CUDA_VISIBLE_DEVICES");
             printf("0 %s\n", v ? v : "-");

@@ -49,7 +49,7 @@ def test_new_shim_reproduces_reference_golden(path):
 @pytest.mark.parametrize("path", GOLD, ids=lambda p: os.path.basename(p)[6:-8])
 def test_python_model_reproduces_reference_golden(path):
     g = load(path)
-    if g["name"].startswith(("remap_", "dead_", "late_")):
+    if g["name"].startswith(("remap_", "dead_", "late_", "fork_")):
         pytest.skip("the Python model restates the quota arithmetic, not the virtual-device table / the dead-process sweep")
     m = Model(g["env"], int(g["env"].get("MOCK_TOTAL_MIB", "16384")) << 20, g["nprocs"])
     for i, (p, op) in enumerate(g["trace"]):
