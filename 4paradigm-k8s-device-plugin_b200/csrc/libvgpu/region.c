@@ -288,7 +288,10 @@ uint64_t region_usage(int dev) {
 }
 
 uint64_t region_limit(int dev) {
-    if (dev < 0 || dev >= VGPU_MAX_DEVICES) { SHIM_ERR("Illegal device id: %d", dev); return 0; }
+    /* get_current_device_memory_limit@0x45ae1 rejects dev > 16, not >= 16: for dev == 16 it reads one element past
+     * limit[], which is sm_limit[0] in the file layout.  Same answer here, without the out-of-bounds access. */
+    if (dev == VGPU_MAX_DEVICES) return g_reg->sm_limit[0];
+    if (dev < 0 || dev > VGPU_MAX_DEVICES) { SHIM_ERR("Illegal device id: %d", dev); return 0; }
     return g_reg->limit[dev];
 }
 uint64_t region_sm_limit(int dev) { return (dev < 0 || dev >= VGPU_MAX_DEVICES) ? 0 : g_reg->sm_limit[dev]; }

@@ -314,6 +314,28 @@ def test_killed_processes_are_swept_like_the_reference_does(seed, nprocs, nkill,
     assert H.mask_region(a["region"]) == H.mask_region(b["region"]), "final shared-cache bytes differ"
 
 
+ODD_OPS = ["total 5", "total 15", "total 16", "total 100", "total -1", "info", "pitch 1 1 1 1", "pitch 4097 3 4 2", "pitch 100 0 8 3", "info",
+           "managed 0 4", "info", "alloc 1 5", "alloc 2097152 6", "alloc 2097153 7", "info", "hostreg 0", "hostalloc 0 8", "freehost 8",
+           "ptrattrs 5", "ptrattrs 0", "nvmlmem", "free 6", "free 7", "free 5", "info"]
+
+
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+@pytest.mark.parametrize("env", [
+    {"CUDA_DEVICE_MEMORY_LIMIT": "1g", "CUDA_DEVICE_MEMORY_LIMIT_5": "2g"},
+    {"CUDA_DEVICE_MEMORY_LIMIT_0": "16m", "CUDA_OVERSUBSCRIBE": "true"},
+])
+def test_odd_arguments_get_the_reference_answers(env):
+    """Device ordinals nobody has (5, 15, 16 — where the reference reads one past limit[] into sm_limit[0] —, 100, -1),
+    zero-sized and one-byte allocations, the 2 MiB boundary of the oversubscribe route, zero-height pitch."""
+    env = {**env, **MAP}
+    tr = [(0, o) for o in ODD_OPS]
+    a = H.run_trace(H.REFERENCE_LIB, tr, env)
+    b = H.run_trace(H.NEW_LIB, tr, env)
+    assert a["replies"] == b["replies"] and a["oom"] == b["oom"] and a["calls"] == b["calls"]
+    assert a["replies"][2] == "0 100"                        # limit[16] is sm_limit[0]
+    assert H.mask_region(a["region"]) == H.mask_region(b["region"])
+
+
 def _slots_clean(region):
     """(proc_num, no live slot holds memory).  Slots beyond proc_num may hold stale bytes: the exit
     handler moves the last slot into the leaver's and does not wipe the source (as in the reference)."""
