@@ -45,7 +45,8 @@ def _env(lib, cache, extra, mock_log):
 
 def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False):
     """-> dict(replies=[str...] in trace order, oom=[(dev,need,limit)...], calls=[str...], region=bytes)
-    `lib` may be a list with one library per process (old and new library sharing one cache file).
+    `lib` may be a list with one library per process (old and new library sharing one cache file), and so may
+    `env_extra` (processes of one cache file that were started with different limits).
     parallel=True sends every op before reading any reply (processes really run concurrently)."""
     os.makedirs("/tmp/vgpulock", exist_ok=True)  # the reference spins forever without this dir
     try:
@@ -62,7 +63,8 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
             def start(p):
                 plib = lib[p] if isinstance(lib, (list, tuple)) else lib
                 pr = subprocess.Popen([os.path.join(REF_DIR, "trace_runner")], stdin=subprocess.PIPE, stdout=subprocess.PIPE,
-                                      stderr=errs[p], env=_env(plib, cache, env_extra, mock_log), text=True, bufsize=1)
+                                      stderr=errs[p], env=_env(plib, cache, env_extra[p] if isinstance(env_extra, (list, tuple)) else env_extra, mock_log),
+                                      text=True, bufsize=1)
                 first = pr.stdout.readline().strip()  # "init <rc>"
                 if not first.startswith("init"):
                     raise RuntimeError(f"runner {p} did not start: {first!r}")

@@ -314,6 +314,23 @@ def test_killed_processes_are_swept_like_the_reference_does(seed, nprocs, nkill,
     assert H.mask_region(a["region"]) == H.mask_region(b["region"]), "final shared-cache bytes differ"
 
 
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+def test_first_process_decides_the_limits_of_a_cache_file():
+    """Processes of one cache file started with different limits / SM limits / priority: the file keeps what its first
+    process wrote (the others log "Limit inconsistency detected" and live with it)."""
+    envs = [{**MAP, "CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "CUDA_DEVICE_SM_LIMIT": "30"},
+            {**MAP, "CUDA_DEVICE_MEMORY_LIMIT_0": "2g", "CUDA_DEVICE_SM_LIMIT": "50", "CUDA_TASK_PRIORITY": "0"}, {**MAP}]
+    tr = [(0, "info"), (1, "info"), (2, "info"), (1, f"alloc {1500 * M} 1"), (1, "total 0"), (2, f"alloc {900 * M} 1"), (2, "total 0"),
+          (0, "nvmlmem"), (0, "@slots")]
+    a = H.run_trace(H.REFERENCE_LIB, tr, envs, 3)
+    b = H.run_trace(H.NEW_LIB, tr, envs, 3)
+    assert a["replies"] == b["replies"] and a["oom"] == b["oom"] and a["calls"] == b["calls"]
+    assert b["replies"][3] == "-1" and b["replies"][4] == f"0 {1 << 30}"          # the 2g process is held to 1g
+    assert H.mask_region(a["region"]) == H.mask_region(b["region"])
+    s = H.region_summary(b["region"])
+    assert s["limit"][0] == 1 << 30 and s["sm_limit"][0] == 30 and s["priority"] == 1
+
+
 ODD_OPS = ["total 5", "total 15", "total 16", "total 100", "total -1", "info", "pitch 1 1 1 1", "pitch 4097 3 4 2", "pitch 100 0 8 3", "info",
            "managed 0 4", "info", "alloc 1 5", "alloc 2097152 6", "alloc 2097153 7", "info", "hostreg 0", "hostalloc 0 8", "freehost 8",
            "ptrattrs 5", "ptrattrs 0", "nvmlmem", "free 6", "free 7", "free 5", "info"]
