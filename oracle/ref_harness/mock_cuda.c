@@ -15,6 +15,7 @@
 #define _GNU_SOURCE
 #include <dlfcn.h>
 #include <stdarg.h>
+#include <pthread.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -87,7 +88,15 @@ static int cur_dev(void) {
     return d < 0 ? 0 : d;
 }
 
+static pthread_mutex_t g_mock_mu = PTHREAD_MUTEX_INITIALIZER;  /* the allocation table is shared by the caller's threads */
+static CUresult do_alloc_locked(CUdeviceptr *p, uint64_t n, int kind, const char *name, unsigned flags);
 static CUresult do_alloc(CUdeviceptr *p, uint64_t n, int kind, const char *name, unsigned flags) {
+    pthread_mutex_lock(&g_mock_mu);
+    CUresult rc = do_alloc_locked(p, n, kind, name, flags);
+    pthread_mutex_unlock(&g_mock_mu);
+    return rc;
+}
+static CUresult do_alloc_locked(CUdeviceptr *p, uint64_t n, int kind, const char *name, unsigned flags) {
     cfg();
     int dev = cur_dev();
     if (g_fail_over && n > g_fail_over) {
@@ -202,13 +211,16 @@ CUresult cuMemAllocPitch_v2(CUdeviceptr *p, size_t *pitch, size_t w, size_t h, u
 }
 CUresult cuMemFree_v2(CUdeviceptr p) {
     cfg();
+    pthread_mutex_lock(&g_mock_mu);
     for (int i = 0; i < g_nalloc; ++i)
         if (g_alloc[i].p == p) {
             g_used[g_alloc[i].dev] -= g_alloc[i].n;
             logf_("cuMemFree_v2 size=%llu -> rc=0", (unsigned long long)g_alloc[i].n);
             g_alloc[i] = g_alloc[--g_nalloc];
+            pthread_mutex_unlock(&g_mock_mu);
             return 0;
         }
+    pthread_mutex_unlock(&g_mock_mu);
     logf_("cuMemFree_v2 unknown -> rc=1");
     return 1;
 }

@@ -35,6 +35,7 @@
  *   vrelease <htag>        cuMemRelease                                                          -> rc
  *   forkalloc <bytes> <how>  fork(); the child allocates <bytes>, asks cuMemGetInfo, reports through a pipe and leaves with
  *                          exit() (how=0: exit handlers run) or _exit() (how=1: they do not); the parent waits -> rc free total
+ *   mtloop <threads> <n> <bytes>   every thread does n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2)  -> OR of all rc
  *   cvd                    getenv("CUDA_VISIBLE_DEVICES") as the process sees it now -> 0 value|-
  *   exporttable            cuGetExportTable (what every CUDA-runtime program does right after cuInit) -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
@@ -45,6 +46,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <pthread.h>
 #include <sys/wait.h>
 #include <time.h>
 #include <unistd.h>
@@ -109,6 +111,19 @@ static int ctx_no(void *c) {
         if (seen[i] == c) return i + 1;
     if (nseen < MAXCTX) seen[nseen++] = c;
     return nseen;
+}
+
+struct mt_arg { unsigned long long n, bytes; int rc; };
+static void *mt_body(void *p) {
+    struct mt_arg *a = (struct mt_arg *)p;
+    size_t f = 0, t = 0;
+    CUdeviceptr d = 0;
+    for (unsigned long long i = 0; i < a->n; ++i) {
+        a->rc |= cuMemAlloc_v2(&d, (size_t)a->bytes);
+        a->rc |= cuMemGetInfo_v2(&f, &t);
+        a->rc |= cuMemFree_v2(d);
+    }
+    return NULL;
 }
 
 int main(void) {
@@ -274,6 +289,17 @@ int main(void) {
             int st = 0;
             waitpid(child, &st, 0);
             printf("%lld %lld %lld\n", in[0], in[1], in[2]);
+        } else if (!strcmp(op, "mtloop")) {
+            pthread_t th[64];
+            struct mt_arg args[64];
+            int nt = a > 64 ? 64 : (int)a;
+            for (int i = 0; i < nt; ++i) {
+                args[i].n = b; args[i].bytes = c; args[i].rc = 0;
+                pthread_create(&th[i], NULL, mt_body, &args[i]);
+            }
+            rc = 0;
+            for (int i = 0; i < nt; ++i) { pthread_join(th[i], NULL); rc |= args[i].rc; }
+            printf("%d\n", rc);
         } else if (!strcmp(op, "cvd")) {
             const char *v = getenv("CUDA_VISIBLE_DEVICES");
             printf("0 %s\n", v ? v : "-");

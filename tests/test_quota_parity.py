@@ -331,6 +331,18 @@ def test_first_process_decides_the_limits_of_a_cache_file():
     assert s["limit"][0] == 1 << 30 and s["sm_limit"][0] == 30 and s["priority"] == 1
 
 
+def test_threads_of_one_process_hammer_the_hooks():
+    """16 threads x 500 x (alloc, info, free) in each of two processes sharing a cache file: every call succeeds, nothing is
+    left billed, the allocation list is empty again (thread safety of the list, the region lock and the mover gate)."""
+    tr = [(0, "info"), (0, "mtloop 16 500 1048576"), (1, "mtloop 16 500 65536"), (0, "info"), (1, "info"), (0, "@slots"),
+          (0, f"alloc {1000 * M} 1"), (1, "mtloop 8 50 33554432"), (1, "@slots")]      # 8 x 32 MiB does not always fit next to 1000 MiB
+    r = H.run_trace(H.NEW_LIB, tr, {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "MOCK_CUDA_LOG": "", **MAP}, 2)
+    rep = r["replies"]
+    assert rep[1] == rep[2] == "0" and rep[0] == rep[3] == rep[4] == f"0 {1 << 30} {1 << 30}"
+    assert rep[5] == "n=2 p0:0:1 | p1:0:1"
+    assert rep[8] == f"n=2 p0:0:1 d0=0/0/{1000 * M}/{1000 * M} | p1:0:1"             # refused or freed: nothing of process 1 stays billed
+
+
 ODD_OPS = ["total 5", "total 15", "total 16", "total 100", "total -1", "info", "pitch 1 1 1 1", "pitch 4097 3 4 2", "pitch 100 0 8 3", "info",
            "managed 0 4", "info", "alloc 1 5", "alloc 2097152 6", "alloc 2097153 7", "info", "hostreg 0", "hostalloc 0 8", "freehost 8",
            "ptrattrs 5", "ptrattrs 0", "nvmlmem", "free 6", "free 7", "free 5", "info"]
