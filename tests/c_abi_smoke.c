@@ -56,6 +56,13 @@ int main(void) {
     CHECK(strcmp(mounts[3].host_path, "/usr/local/vgpu/vgpuvalidator") == 0);
     ne = 2;  /* caller array too small: reports what is needed */
     CHECK(vgpu_allocate_env(&cfg, req, 2, pu, pi, 1, NULL, envs, &ne, mounts, &nm) == VGPU_E_RANGE && ne == 7);
+    /* VGPU_MONITOR_MODE form (server.go:494-501): one more mount, in front, and the cache file inside it */
+    ne = 16; nm = 16;
+    CHECK(vgpu_allocate_env_monitor(&cfg, req, 2, pu, pi, 1, "01234567-89ab-4def-8123-456789abcdef", "train-0_worker", envs, &ne, mounts, &nm) == VGPU_OK);
+    CHECK(nm == 6 && strcmp(mounts[0].container_path, "/train-0_worker") == 0 && mounts[0].read_only == 0);
+    CHECK(strcmp(mounts[0].host_path, "/usr/local/vgpu/shared/train-0_worker") == 0 && strcmp(mounts[2].container_path, "/etc/ld.so.preload") == 0);
+    CHECK(strcmp(env(envs, ne, "CUDA_DEVICE_MEMORY_SHARED_CACHE"), "/train-0_worker/01234567-89ab-4def-8123-456789abcdef.cache") == 0);
+    CHECK(vgpu_allocate_env_monitor(&cfg, req, 2, pu, pi, 1, NULL, "a/b", envs, &ne, mounts, &nm) == VGPU_E_INVAL);
     /* data-path argument checks need no GPU either */
     CHECK(vgpu_spill(VGPU_XFER_LDST, VGPU_TIER_LOCAL, NULL, NULL, NULL, NULL, 0, VGPU_CHUNK_BYTES, NULL, NULL) == VGPU_OK);
     CHECK(vgpu_spill_noalloc(NULL, NULL, NULL, NULL, VGPU_NOALLOC_MAX_CHUNKS + 1, 32, NULL, NULL) == VGPU_E_RANGE);
