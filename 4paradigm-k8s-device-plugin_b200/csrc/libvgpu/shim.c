@@ -1284,6 +1284,27 @@ GATED(cuMemsetD8_v2, (CUdeviceptr d, unsigned char v, size_t n), (d, v, n))
 GATED(cuMemsetD8Async, (CUdeviceptr d, unsigned char v, size_t n, void *st), (d, v, n, st))
 GATED(cuMemsetD32_v2, (CUdeviceptr d, unsigned v, size_t n), (d, v, n))
 GATED(cuMemsetD32Async, (CUdeviceptr d, unsigned v, size_t n, void *st), (d, v, n, st))
+/* the rest of the family: descriptor-based, peer, 16-bit and 2-D forms, cooperative and graph launches */
+GATED(cuMemcpy2D_v2, (const void *p), (p))
+GATED(cuMemcpy2DUnaligned_v2, (const void *p), (p))
+GATED(cuMemcpy2DAsync_v2, (const void *p, void *st), (p, st))
+GATED(cuMemcpy3D_v2, (const void *p), (p))
+GATED(cuMemcpy3DAsync_v2, (const void *p, void *st), (p, st))
+GATED(cuMemcpy3DPeer, (const void *p), (p))
+GATED(cuMemcpy3DPeerAsync, (const void *p, void *st), (p, st))
+GATED(cuMemcpyPeer, (CUdeviceptr d, CUcontext dc, CUdeviceptr s_, CUcontext sc, size_t n), (d, dc, s_, sc, n))
+GATED(cuMemcpyPeerAsync, (CUdeviceptr d, CUcontext dc, CUdeviceptr s_, CUcontext sc, size_t n, void *st), (d, dc, s_, sc, n, st))
+GATED(cuMemsetD16_v2, (CUdeviceptr d, unsigned short v, size_t n), (d, v, n))
+GATED(cuMemsetD16Async, (CUdeviceptr d, unsigned short v, size_t n, void *st), (d, v, n, st))
+GATED(cuMemsetD2D8_v2, (CUdeviceptr d, size_t pitch, unsigned char v, size_t w, size_t h), (d, pitch, v, w, h))
+GATED(cuMemsetD2D8Async, (CUdeviceptr d, size_t pitch, unsigned char v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st))
+GATED(cuMemsetD2D16_v2, (CUdeviceptr d, size_t pitch, unsigned short v, size_t w, size_t h), (d, pitch, v, w, h))
+GATED(cuMemsetD2D16Async, (CUdeviceptr d, size_t pitch, unsigned short v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st))
+GATED(cuMemsetD2D32_v2, (CUdeviceptr d, size_t pitch, unsigned v, size_t w, size_t h), (d, pitch, v, w, h))
+GATED(cuMemsetD2D32Async, (CUdeviceptr d, size_t pitch, unsigned v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st))
+GATED(cuLaunchCooperativeKernel, (void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz, unsigned shm, void *st, void **params),
+      (fn, gx, gy, gz, bx, by, bz, shm, st, params))
+GATED(cuGraphLaunch, (void *graph, void *st), (graph, st))
 
 /* cuMipmappedArrayCreate (a20): same allocate-then-check_oom pattern as the host allocations */
 EXPORT CUresult cuMipmappedArrayCreate(void **handle, const void *desc, unsigned levels) {
@@ -1848,6 +1869,18 @@ static const hook_t g_hooks[] = {
     {"cuMemcpyDtoDAsync", (void *)cuMemcpyDtoDAsync_v2}, {"cuMemcpyDtoDAsync_v2", (void *)cuMemcpyDtoDAsync_v2},
     {"cuMemsetD8", (void *)cuMemsetD8_v2}, {"cuMemsetD8_v2", (void *)cuMemsetD8_v2}, {"cuMemsetD8Async", (void *)cuMemsetD8Async},
     {"cuMemsetD32", (void *)cuMemsetD32_v2}, {"cuMemsetD32_v2", (void *)cuMemsetD32_v2}, {"cuMemsetD32Async", (void *)cuMemsetD32Async},
+    {"cuMemcpy2D", (void *)cuMemcpy2D_v2}, {"cuMemcpy2D_v2", (void *)cuMemcpy2D_v2},
+    {"cuMemcpy2DUnaligned", (void *)cuMemcpy2DUnaligned_v2}, {"cuMemcpy2DUnaligned_v2", (void *)cuMemcpy2DUnaligned_v2},
+    {"cuMemcpy2DAsync", (void *)cuMemcpy2DAsync_v2}, {"cuMemcpy2DAsync_v2", (void *)cuMemcpy2DAsync_v2},
+    {"cuMemcpy3D", (void *)cuMemcpy3D_v2}, {"cuMemcpy3D_v2", (void *)cuMemcpy3D_v2},
+    {"cuMemcpy3DAsync", (void *)cuMemcpy3DAsync_v2}, {"cuMemcpy3DAsync_v2", (void *)cuMemcpy3DAsync_v2},
+    {"cuMemcpy3DPeer", (void *)cuMemcpy3DPeer}, {"cuMemcpy3DPeerAsync", (void *)cuMemcpy3DPeerAsync},
+    {"cuMemcpyPeer", (void *)cuMemcpyPeer}, {"cuMemcpyPeerAsync", (void *)cuMemcpyPeerAsync},
+    {"cuMemsetD16", (void *)cuMemsetD16_v2}, {"cuMemsetD16_v2", (void *)cuMemsetD16_v2}, {"cuMemsetD16Async", (void *)cuMemsetD16Async},
+    {"cuMemsetD2D8", (void *)cuMemsetD2D8_v2}, {"cuMemsetD2D8_v2", (void *)cuMemsetD2D8_v2}, {"cuMemsetD2D8Async", (void *)cuMemsetD2D8Async},
+    {"cuMemsetD2D16", (void *)cuMemsetD2D16_v2}, {"cuMemsetD2D16_v2", (void *)cuMemsetD2D16_v2}, {"cuMemsetD2D16Async", (void *)cuMemsetD2D16Async},
+    {"cuMemsetD2D32", (void *)cuMemsetD2D32_v2}, {"cuMemsetD2D32_v2", (void *)cuMemsetD2D32_v2}, {"cuMemsetD2D32Async", (void *)cuMemsetD2D32Async},
+    {"cuLaunchCooperativeKernel", (void *)cuLaunchCooperativeKernel}, {"cuGraphLaunch", (void *)cuGraphLaunch},
     {"cuLaunchKernel", (void *)cuLaunchKernel},
     {"cuLaunchKernelEx", (void *)cuLaunchKernelEx},
     {"cuGetExportTable", (void *)cuGetExportTable},
@@ -1923,7 +1956,7 @@ static void *find_hook_for_version(const char *name, int ver, unsigned long long
 static int wants_ptds(const char *symbol, unsigned long long flags) {
     return (flags & 2ull /* CU_GET_PROC_ADDRESS_PER_THREAD_DEFAULT_STREAM */) &&
            (strncmp(symbol, "cuMemcpy", 8) == 0 || strncmp(symbol, "cuMemset", 8) == 0 || strncmp(symbol, "cuLaunch", 8) == 0 ||
-            strncmp(symbol, "cuMemPrefetch", 13) == 0);
+            strncmp(symbol, "cuMemPrefetch", 13) == 0 || strncmp(symbol, "cuGraphLaunch", 13) == 0);
 }
 
 /* dlsym@0x12bb6: every cu, nvml lookup that names a hooked symbol lands in the shim */
