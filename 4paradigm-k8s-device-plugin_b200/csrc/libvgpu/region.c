@@ -214,8 +214,8 @@ int region_attach(const char *path, const vgpu_region_init_t *init) {
     vgpu_region_t *r = g_reg;
     /* put_device_info@0x41e2e runs before the magic check, on every attach */
     r->device_num = init->device_num;
-    for (uint64_t i = 0; i < init->device_num && i < VGPU_MAX_DEVICES; ++i)
-        memcpy(r->uuids[i], init->uuids[i], VGPU_UUID_LEN);
+    for (uint64_t i = 0; i < init->device_num && i < VGPU_MAX_DEVICES; ++i)  /* NVML writes the string only: bytes after its terminator stay */
+        memcpy(r->uuids[i], init->uuids[i], strnlen(init->uuids[i], VGPU_UUID_LEN - 1) + 1);
     if (r->initialized_flag != VGPU_REGION_MAGIC) {
         memcpy(r->limit, init->limit, sizeof(r->limit));
         memcpy(r->sm_limit, init->sm_limit, sizeof(r->sm_limit));

@@ -43,7 +43,7 @@ def _env(lib, cache, extra, mock_log):
     return env
 
 
-def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False):
+def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False, pre_cache=None):
     """-> dict(replies=[str...] in trace order, oom=[(dev,need,limit)...], calls=[str...], region=bytes)
     `lib` may be a list with one library per process (old and new library sharing one cache file), and so may
     `env_extra` (processes of one cache file that were started with different limits).
@@ -55,6 +55,9 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False)
         pass
     with tempfile.TemporaryDirectory(prefix="vgpuq") as td:
         cache = os.path.join(td, "shr.cache")
+        if pre_cache is not None:  # a cache file with history (or garbage) that the first process finds
+            with open(cache, "wb") as f:
+                f.write(pre_cache)
         mock_log = os.path.join(td, "mock.log")
         errs = [open(os.path.join(td, f"err{p}"), "w+") for p in range(nprocs)]
         procs = []
@@ -178,7 +181,7 @@ def mask_region(b: bytes) -> bytes:
     if not b:
         return b
     a = bytearray(b[:REGION_SIZE])
-    for s in range(NSLOT):
+    for s in range(-1, NSLOT):  # -1: where both libraries put their slot when a garbage file says proc_num = -1
         o = SLOT0 + s * STRIDE
         a[o:o + 8] = b"\0" * 8
     return bytes(a)

@@ -343,6 +343,42 @@ def test_threads_of_one_process_hammer_the_hooks():
     assert rep[8] == f"n=2 p0:0:1 d0=0/0/{1000 * M}/{1000 * M} | p1:0:1"             # refused or freed: nothing of process 1 stays billed
 
 
+def _planted(clean, pids, used, limit0=None):
+    import struct
+    b = bytearray(clean)
+    if limit0 is not None:
+        struct.pack_into("<Q", b, 0x638, limit0)
+    for i, (pid, u) in enumerate(zip(pids, used)):
+        o = 0x738 + i * 0x310
+        struct.pack_into("<ii", b, o, pid, pid)
+        struct.pack_into("<5Q", b, o + 8, 0, 0, u, 0, u)
+        struct.pack_into("<i", b, o + 0x308, 1)
+    struct.pack_into("<i", b, 0xC4738, len(pids))
+    return bytes(b)
+
+
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+@pytest.mark.parametrize("case", ["zeros", "short", "garbage", "stale_slots", "stale_limit"])
+def test_a_cache_file_with_history_is_taken_over_like_the_reference_does(case):
+    """The cache file may outlive its container (monitor mode keeps it in a host directory): an all-zero file, a
+    truncated one, 0xFF garbage (the reference never resets proc_num and claims slot -1 — so does this library),
+    slots of processes that are gone, a limit that is not the one in the environment."""
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}
+    clean = H.run_trace(H.NEW_LIB, [(0, "info")], env)["region"]
+    pre = {"zeros": b"\0" * (H.REGION_SIZE + 1), "short": b"abc" * 33, "garbage": b"\xff" * (H.REGION_SIZE + 1),
+           "stale_slots": _planted(clean, [4000001, 4000002, 4000003], [300 * M, 200 * M, 100 * M]),
+           "stale_limit": _planted(clean, [4000001], [100 * M], limit0=512 * M)}[case]
+    tr = [(0, "info"), (0, "@slots"), (0, f"alloc {900 * M} 1"), (0, "info"), (0, "@slots")]
+    a = H.run_trace(H.REFERENCE_LIB, tr, env, pre_cache=pre)
+    b = H.run_trace(H.NEW_LIB, tr, env, pre_cache=pre)
+    assert a["replies"] == b["replies"] and a["oom"] == b["oom"] and a["calls"] == b["calls"]
+    assert H.mask_region(a["region"]) == H.mask_region(b["region"])
+    if case == "stale_slots":
+        assert b["replies"][1] == "n=1 p0:0:1" and b["replies"][2] == "0"          # the dead are kicked at start-up
+    if case == "stale_limit":
+        assert b["replies"][0] == f"0 {512 * M} {512 * M}" and b["replies"][2] == "-1"   # the file's limit wins
+
+
 ODD_OPS = ["total 5", "total 15", "total 16", "total 100", "total -1", "info", "pitch 1 1 1 1", "pitch 4097 3 4 2", "pitch 100 0 8 3", "info",
            "managed 0 4", "info", "alloc 1 5", "alloc 2097152 6", "alloc 2097153 7", "info", "hostreg 0", "hostalloc 0 8", "freehost 8",
            "ptrattrs 5", "ptrattrs 0", "nvmlmem", "free 6", "free 7", "free 5", "info"]
