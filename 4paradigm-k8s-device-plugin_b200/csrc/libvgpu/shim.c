@@ -299,7 +299,13 @@ static void pre_init(void) {
     const char *path = getenv("CUDA_DEVICE_MEMORY_SHARED_CACHE");
     if (!path) path = "/tmp/cudevshr.cache";  /* .rodata@0x56ac0 */
     g_region_ok = region_attach(path, &init) == 0;
-    if (!g_region_ok) SHIM_ERR("shared cache %s unavailable: quota disabled", path);
+    if (!g_region_ok) {
+        /* Fail closed.  The path is the tenant's to tamper with (an environment variable); carrying on without the
+         * file would mean carrying on without a quota.  The reference logs the same errors and then crashes in its
+         * init (multiprocess_memory_limit.c:680-697, segfault); here the process ends with a message. */
+        SHIM_ERR("shared cache %s unavailable: refusing to run CUDA without the vGPU quota", path);
+        exit(-1);
+    }
 }
 
 static void load_vmm_backend(void);

@@ -379,6 +379,16 @@ def test_a_cache_file_with_history_is_taken_over_like_the_reference_does(case):
         assert b["replies"][0] == f"0 {512 * M} {512 * M}" and b["replies"][2] == "-1"   # the file's limit wins
 
 
+def test_an_unusable_cache_path_fails_closed():
+    """CUDA_DEVICE_MEMORY_SHARED_CACHE is an environment variable the tenant can change: pointing it somewhere unusable
+    must not buy a process without a quota.  (The reference crashes in its init in that case.)"""
+    import subprocess
+    env = H._env(H.NEW_LIB, "/nonexistent_dir/x.cache", {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}, "")
+    p = subprocess.run([os.path.join(H.REF_DIR, "trace_runner")], input="info\nalloc 2097152000 1\nquit\n", env=env, capture_output=True, text=True, timeout=30)
+    assert p.returncode != 0 and "init 0" not in p.stdout and "alloc" not in p.stdout
+    assert "refusing to run CUDA without the vGPU quota" in p.stderr
+
+
 ODD_OPS = ["total 5", "total 15", "total 16", "total 100", "total -1", "info", "pitch 1 1 1 1", "pitch 4097 3 4 2", "pitch 100 0 8 3", "info",
            "managed 0 4", "info", "alloc 1 5", "alloc 2097152 6", "alloc 2097153 7", "info", "hostreg 0", "hostalloc 0 8", "freehost 8",
            "ptrattrs 5", "ptrattrs 0", "nvmlmem", "free 6", "free 7", "free 5", "info"]
