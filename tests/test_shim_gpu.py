@@ -279,6 +279,22 @@ def test_strict_quota_closes_the_allocator_paths_the_reference_leaves_open(cuda_
     assert strict["total"] == 4 * GiB and 3 * GiB <= strict["total"] - strict["free"] <= 4 * GiB
 
 
+def test_nvidia_smi_in_the_pod_shows_the_quota(cuda_dev):
+    """nvidia-smi itself under the shim (it is what people run inside the pod): the vGPU's quota as total memory — and,
+    with the GPU named twice in the map, still ONE row, carrying the sum."""
+    uuid = _gpu0_uuid()
+    td = tempfile.mkdtemp(prefix="vgpushim")
+    q = ["nvidia-smi", "--query-gpu=uuid,memory.total,memory.used", "--format=csv,noheader,nounits"]
+    for extra, total_mib in (({"CUDA_DEVICE_MEMORY_LIMIT_0": "8g", "NVIDIA_DEVICE_MAP": f"0:{uuid}"}, 8192),
+                             ({"CUDA_DEVICE_MEMORY_LIMIT_0": "4g", "CUDA_DEVICE_MEMORY_LIMIT_1": "8g", "NVIDIA_DEVICE_MAP": f"0:{uuid} 1:{uuid}"}, 12288)):
+        env = {**os.environ, "LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": os.path.join(td, f"c{total_mib}"), "LIBCUDA_LOG_LEVEL": "0", **extra}
+        p = subprocess.run(q, env=env, capture_output=True, text=True, timeout=120)
+        assert p.returncode == 0, p.stderr[-2000:]
+        rows = [[x.strip() for x in line.split(",")] for line in p.stdout.strip().splitlines()]
+        print("nvidia-smi under the shim:", rows)
+        assert len(rows) == 1 and rows[0][0] == uuid and int(rows[0][1]) == total_mib and int(rows[0][2]) == 0
+
+
 def test_nvml_memory_info_shows_the_limit(cuda_dev):
     code = """
         import json, torch, pynvml
