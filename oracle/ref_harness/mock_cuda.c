@@ -358,10 +358,16 @@ CUresult cuGetExportTable(const void **table, const void *id) {
 
 static CUresult proc_lookup(const char *sym, void **pfn) {
     char buf[256];
+    /* libc's own dlsym, not whatever is preloaded: the real driver does not look its entry points up through dlsym */
+    typedef void *(*dlsym_t)(void *, const char *);
+    static dlsym_t real;
+    if (!real) real = (dlsym_t)dlvsym(RTLD_NEXT, "dlsym", "GLIBC_2.2.5");
+    if (!real) real = (dlsym_t)dlvsym(RTLD_NEXT, "dlsym", "GLIBC_2.34");
+    if (!real) real = dlsym;
     void *self = dlopen("libcuda.so.1", RTLD_LAZY | RTLD_NOLOAD);
     snprintf(buf, sizeof(buf), "%s_v2", sym);
-    void *f = self ? dlsym(self, buf) : NULL;
-    if (!f && self) f = dlsym(self, sym);
+    void *f = self ? real(self, buf) : NULL;
+    if (!f && self) f = real(self, sym);
     *pfn = f;
     return f ? 0 : 500;
 }

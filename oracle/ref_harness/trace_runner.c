@@ -36,6 +36,7 @@
  *   forkalloc <bytes> <how>  fork(); the child allocates <bytes>, asks cuMemGetInfo, reports through a pipe and leaves with
  *                          exit() (how=0: exit handlers run) or _exit() (how=1: they do not); the parent waits -> rc free total
  *   mtloop <threads> <n> <bytes>   every thread does n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2)  -> OR of all rc
+ *   procaddr <ver> <flags> <name>   cuGetProcAddress_v2(name, ver, flags) -> rc <symbol the pointer belongs to>@<library>
  *   cvd                    getenv("CUDA_VISIBLE_DEVICES") as the process sees it now -> 0 value|-
  *   exporttable            cuGetExportTable (what every CUDA-runtime program does right after cuInit) -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
@@ -80,6 +81,7 @@ CUresult cuCtxPushCurrent_v2(void *);
 CUresult cuCtxPopCurrent_v2(void **);
 CUresult cuDevicePrimaryCtxRelease_v2(int);
 CUresult cuGetExportTable(const void **, const void *);
+CUresult cuGetProcAddress_v2(const char *, void **, int, unsigned long long, int *);
 CUresult cuMemAllocAsync(CUdeviceptr *, size_t, void *);
 CUresult cuMemFreeAsync(CUdeviceptr, void *);
 typedef struct { int type, handle_types, loc_type, loc_id; void *win32; unsigned char flags[8]; } alloc_prop_t;
@@ -300,6 +302,17 @@ int main(void) {
             rc = 0;
             for (int i = 0; i < nt; ++i) { pthread_join(th[i], NULL); rc |= args[i].rc; }
             printf("%d\n", rc);
+        } else if (!strcmp(op, "procaddr")) {
+            char name[96] = {0};
+            void *pfn = NULL;
+            int status = -1;
+            sscanf(line, "%*s %*s %*s %95s", name);
+            rc = cuGetProcAddress_v2(name, &pfn, (int)a, b, &status);
+            Dl_info di;
+            memset(&di, 0, sizeof(di));
+            if (rc == 0 && pfn) dladdr(pfn, &di);
+            const char *lib = di.dli_fname ? strrchr(di.dli_fname, '/') : NULL;
+            printf("%d %s@%s\n", rc, di.dli_sname ? di.dli_sname : "?", lib ? lib + 1 : (di.dli_fname ? di.dli_fname : "?"));
         } else if (!strcmp(op, "cvd")) {
             const char *v = getenv("CUDA_VISIBLE_DEVICES");
             printf("0 %s\n", v ? v : "-");

@@ -389,6 +389,24 @@ def test_an_unusable_cache_path_fails_closed():
     assert "refusing to run CUDA without the vGPU quota" in p.stderr
 
 
+def test_cuGetProcAddress_hands_out_the_hook_with_the_abi_the_caller_asked_for():
+    """An unsuffixed name asks for the newest ABI the given CUDA version knows: cuCtxCreate is _v2 / _v3 / _v4 depending
+    on it, cuMemPrefetchAsync and cuMemAdvise change signature at 12.2, cuGetProcAddress itself at 12.0; per-thread
+    default stream callers get the driver's own copy / launch entry points and the _ptsz twins of the async allocator."""
+    q = [("11030 0 cuCtxCreate", "cuCtxCreate_v2"), ("11040 0 cuCtxCreate", "cuCtxCreate_v3"), ("12090 0 cuCtxCreate", "cuCtxCreate_v4"),
+         ("12010 0 cuMemPrefetchAsync", "cuMemPrefetchAsync"), ("12090 0 cuMemPrefetchAsync", "cuMemPrefetchAsync_v2"),
+         ("12090 0 cuMemAdvise", "cuMemAdvise_v2"), ("11080 0 cuGetProcAddress", "cuGetProcAddress"), ("12000 0 cuGetProcAddress", "cuGetProcAddress_v2"),
+         ("11030 0 cuDeviceGetUuid", "cuDeviceGetUuid"), ("12090 0 cuDeviceGetUuid", "cuDeviceGetUuid_v2"),
+         ("12090 0 cuMemAlloc", "cuMemAlloc_v2"), ("12090 0 cuMemAllocAsync", "cuMemAllocAsync"), ("12090 2 cuMemAllocAsync", "cuMemAllocAsync_ptsz"),
+         ("12090 2 cuMemFreeAsync", "cuMemFreeAsync_ptsz"), ("12090 0 cuLaunchKernel", "cuLaunchKernel"), ("12090 0 cuMemcpy2DAsync", "cuMemcpy2DAsync_v2")]
+    rep = H.run_trace(H.NEW_LIB, [(0, "procaddr " + a) for a, _ in q], {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP})["replies"]
+    assert rep == [f"0 {sym}@libvgpu.so" for _, sym in q]
+    # per-thread-stream flavours of copies and launches, and anything not hooked, come straight from the driver
+    rep = H.run_trace(H.NEW_LIB, [(0, "procaddr 12090 2 cuLaunchKernel"), (0, "procaddr 12090 0 cuDriverGetVersion")],
+                      {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP})["replies"]
+    assert all(r.endswith("@libcuda.so.1") for r in rep), rep
+
+
 ODD_OPS = ["total 5", "total 15", "total 16", "total 100", "total -1", "info", "pitch 1 1 1 1", "pitch 4097 3 4 2", "pitch 100 0 8 3", "info",
            "managed 0 4", "info", "alloc 1 5", "alloc 2097152 6", "alloc 2097153 7", "info", "hostreg 0", "hostalloc 0 8", "freehost 8",
            "ptrattrs 5", "ptrattrs 0", "nvmlmem", "free 6", "free 7", "free 5", "info"]
