@@ -783,6 +783,23 @@ EXPORT CUresult cuDeviceTotalMem_v2(size_t *bytes, CUdevice dev) {
 }
 EXPORT CUresult cuDeviceTotalMem(size_t *bytes, CUdevice dev) { return cuDeviceTotalMem_v2(bytes, dev); }
 
+/* which virtual device a pointer belongs to: the one it was allocated on if the allocation is tracked, else the
+ * first vGPU of the physical GPU the driver names */
+static int vdev_of_pointer(CUdeviceptr ptr, int phys) {
+    ensure_vdev();
+    if (!g_remap) return phys;
+    int v = -1;
+    pthread_mutex_lock(&g_alloc_mu);
+    for (alloc_node_t *a = g_head; a; a = a->next)
+        if (ptr >= a->addr && ptr < a->addr + (a->len ? a->len : 1)) {
+            v = a->dev;
+            break;
+        }
+    pthread_mutex_unlock(&g_alloc_mu);
+    if (v < 0) v = first_vdev_of(phys);
+    return v < 0 ? phys : v;
+}
+
 /* cuPointerGetAttributes@0x33cf3 (a24): after the real call, IS_MANAGED (8) is forced to 0 so
  * that frameworks do not notice the managed memory behind oversubscribed allocations. */
 EXPORT CUresult cuPointerGetAttributes(unsigned n, int *attrs, void **data, CUdeviceptr ptr) {
@@ -795,8 +812,20 @@ EXPORT CUresult cuPointerGetAttributes(unsigned n, int *attrs, void **data, CUde
     }
     CUresult rc = f ? f(n, attrs, data, ptr) : 3;
     if (!tl_bypass)
-        for (unsigned i = 0; i < n; ++i)
+        for (unsigned i = 0; i < n; ++i) {
             if (attrs[i] == 8 && data[i]) *(unsigned *)data[i] = 0;
+            if (attrs[i] == 9 && data[i] && rc == 0) *(int *)data[i] = vdev_of_pointer(ptr, *(int *)data[i]);
+        }
+    return rc;
+}
+
+/* CU_POINTER_ATTRIBUTE_DEVICE_ORDINAL (9) answers with a virtual ordinal as well */
+EXPORT CUresult cuPointerGetAttribute(void *data, int attr, CUdeviceptr ptr) {
+    typedef CUresult (*fn_t)(void *, int, CUdeviceptr);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuPointerGetAttribute");
+    CUresult rc = f ? f(data, attr, ptr) : 3;
+    if (rc == 0 && !tl_bypass && attr == 9 && data) *(int *)data = vdev_of_pointer(ptr, *(int *)data);
     return rc;
 }
 
@@ -1864,7 +1893,7 @@ static const hook_t g_hooks[] = {
     {"cuCtxGetCurrent", (void *)cuCtxGetCurrent},
     {"cuCtxPopCurrent", (void *)cuCtxPopCurrent_v2}, {"cuCtxPopCurrent_v2", (void *)cuCtxPopCurrent_v2},
     {"cuCtxPushCurrent", (void *)cuCtxPushCurrent_v2}, {"cuCtxPushCurrent_v2", (void *)cuCtxPushCurrent_v2},
-    {"cuPointerGetAttributes", (void *)cuPointerGetAttributes},
+    {"cuPointerGetAttributes", (void *)cuPointerGetAttributes}, {"cuPointerGetAttribute", (void *)cuPointerGetAttribute},
     {"cuMipmappedArrayCreate", (void *)cuMipmappedArrayCreate},
     {"cuMemcpy", (void *)cuMemcpy}, {"cuMemcpyAsync", (void *)cuMemcpyAsync},
     {"cuMemcpyDtoH", (void *)cuMemcpyDtoH_v2}, {"cuMemcpyDtoH_v2", (void *)cuMemcpyDtoH_v2},

@@ -328,7 +328,14 @@ CUresult cuMemUnmap(CUdeviceptr p, size_t n) {
 }
 CUresult cuMemSetAccess(CUdeviceptr p, size_t n, const void *d, size_t c) { (void)p; (void)n; (void)d; (void)c; return 0; }
 CUresult cuMemGetAllocationGranularity(size_t *g, const void *prop, int opt) { (void)prop; (void)opt; *g = 0x200000; return 0; }
-CUresult cuPointerGetAttribute(void *data, int attr, CUdeviceptr p) { (void)p; if (attr == 8) *(unsigned *)data = 1; else memset(data, 0, 8); return 0; }
+CUresult cuPointerGetAttribute(void *data, int attr, CUdeviceptr p) {
+    if (attr == 8) { *(unsigned *)data = 1; return 0; }
+    memset(data, 0, 8);
+    if (attr == 9)  /* DEVICE_ORDINAL: where the allocation lives */
+        for (int i = 0; i < g_nalloc; ++i)
+            if (p >= g_alloc[i].p && p < g_alloc[i].p + (g_alloc[i].n ? g_alloc[i].n : 1)) *(int *)data = g_alloc[i].dev;
+    return 0;
+}
 CUresult cuPointerGetAttributes(unsigned n, int *attrs, void **data, CUdeviceptr p) {
     (void)p;
     for (unsigned i = 0; i < n; ++i) {

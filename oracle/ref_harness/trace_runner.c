@@ -37,6 +37,7 @@
  *                          exit() (how=0: exit handlers run) or _exit() (how=1: they do not); the parent waits -> rc free total
  *   mtloop <threads> <n> <bytes>   every thread does n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2)  -> OR of all rc
  *   procaddr <ver> <flags> <name>   cuGetProcAddress_v2(name, ver, flags) -> rc <symbol the pointer belongs to>@<library>
+ *   ptrdev <tag>           cuPointerGetAttribute(DEVICE_ORDINAL) of the tagged pointer -> rc ordinal
  *   cvd                    getenv("CUDA_VISIBLE_DEVICES") as the process sees it now -> 0 value|-
  *   exporttable            cuGetExportTable (what every CUDA-runtime program does right after cuInit) -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
@@ -68,6 +69,7 @@ CUresult cuMemHostAlloc(void **, size_t, unsigned);
 CUresult cuMemHostRegister_v2(void *, size_t, unsigned);
 CUresult cuMemHostUnregister(void *);
 CUresult cuPointerGetAttributes(unsigned, int *, void **, CUdeviceptr);
+CUresult cuPointerGetAttribute(void *, int, CUdeviceptr);
 CUresult cuDevicePrimaryCtxRetain(void **, int);
 CUresult cuDeviceGetCount(int *);
 CUresult cuDeviceGetUuid(void *, int);
@@ -313,6 +315,10 @@ int main(void) {
             if (rc == 0 && pfn) dladdr(pfn, &di);
             const char *lib = di.dli_fname ? strrchr(di.dli_fname, '/') : NULL;
             printf("%d %s@%s\n", rc, di.dli_sname ? di.dli_sname : "?", lib ? lib + 1 : (di.dli_fname ? di.dli_fname : "?"));
+        } else if (!strcmp(op, "ptrdev")) {
+            long long ord = -1;
+            rc = cuPointerGetAttribute(&ord, 9, a < MAXTAG ? tags[a] : 0);
+            printf("%d %d\n", rc, (int)ord);
         } else if (!strcmp(op, "cvd")) {
             const char *v = getenv("CUDA_VISIBLE_DEVICES");
             printf("0 %s\n", v ? v : "-");

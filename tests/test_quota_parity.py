@@ -169,6 +169,20 @@ def test_subset_map_enforces_the_quota_on_the_mapped_gpu():
     assert any(c.startswith("cuMemAlloc_v2 size=629145600") for c in r["calls"])
 
 
+def test_pointer_device_ordinal_is_the_virtual_device_it_was_allocated_on():
+    """Map "A B A" on two GPUs = virtual devices A, A', B.  cuPointerGetAttribute(DEVICE_ORDINAL) names the virtual device
+    the application allocated on — consistent with cuCtxGetDevice.  (The reference passes the driver's physical answer
+    through: 0, 0, 1 — which is not even a valid index for the third device's neighbours.)"""
+    u2 = H.UUID0[:-1] + "2"
+    env = {"MOCK_GPU_COUNT": "2", "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{u2} 2:{H.UUID0}", "CUDA_DEVICE_MEMORY_LIMIT_0": "1g",
+           "CUDA_DEVICE_MEMORY_LIMIT_1": "1g", "CUDA_DEVICE_MEMORY_LIMIT_2": "1g", "MOCK_CTX_MIB": "300"}
+    ops = ["retain 0 1", "retain 1 2", "retain 2 3", "ctxset 1", f"alloc {1 << 20} 1", "ctxset 2", f"alloc {1 << 20} 2", "ctxset 3", f"alloc {1 << 20} 3",
+           "ptrdev 1", "ptrdev 2", "ptrdev 3"]
+    assert H.run_trace(H.NEW_LIB, [(0, o) for o in ops], env)["replies"][-3:] == ["0 0", "0 1", "0 2"]
+    if H.have_reference():
+        assert H.run_trace(H.REFERENCE_LIB, [(0, o) for o in ops], env)["replies"][-3:] == ["0 0", "0 0", "0 1"]
+
+
 def test_nvml_shows_a_shared_gpu_as_the_sum_of_its_vgpus():
     ops = ["retain 0 1", "retain 1 2", "ctxset 2", f"alloc {100 << 20} 1", "nvmlmem"]
     rep = H.run_trace(H.NEW_LIB, [(0, o) for o in ops], SHARED)["replies"]
