@@ -304,6 +304,14 @@ void region_set_hostpid(int hostpid) {
     region_unlock();
 }
 
+void region_set_my_status(int status) {
+    if (!g_reg) return;
+    region_lock();
+    vgpu_proc_slot_t *s = my_slot();
+    if (s) s->status = status;
+    region_unlock();
+}
+
 int region_my_status(void) {
     vgpu_proc_slot_t *s = g_reg ? my_slot() : NULL;
     return s ? s->status : 1;

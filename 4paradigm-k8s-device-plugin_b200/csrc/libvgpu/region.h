@@ -77,6 +77,7 @@ uint64_t region_limit(int dev);                  /* get_current_device_memory_li
 uint64_t region_sm_limit(int dev);
 int  region_reap_dead(void);                     /* rm_quitted_process@0x425b6; returns #reaped */
 int  region_my_status(void);
+void region_set_my_status(int status);           /* set_current_gpu_status@0x45c9d */
 void region_set_hostpid(int hostpid);            /* set_host_pid@0x4497c */
 extern void (*region_status_hook)(int status);  /* called from the SIGUSR1/2 handlers */
 

@@ -31,6 +31,7 @@
 #include <errno.h>
 #include <fcntl.h>
 #include <pthread.h>
+#include <signal.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -176,6 +177,7 @@ static void init_limits(vgpu_region_init_t *init) {
 static pthread_once_t g_pre_once = PTHREAD_ONCE_INIT, g_post_once = PTHREAD_ONCE_INIT;
 static int g_virtual_devices = -1;  /* entries of NVIDIA_DEVICE_MAP, else the real device count */
 static int g_allocmode = 2;         /* 0: oversubscribe route, 2: plain cuMemAlloc (postInit@0x16ded) */
+static int g_map_has_duplicates;    /* duplicate_devices: a GPU named twice in NVIDIA_DEVICE_MAP */
 static int g_strict;                /* VGPU_STRICT_QUOTA=1: also meter the allocation paths the reference lets through */
 static int g_region_ok = 0;
 
@@ -273,6 +275,8 @@ static void pre_init(void) {
         if (g_virtual_devices <= 0 && nv_count && nv_count(&n) == 0) g_virtual_devices = (int)n;
         char want[VGPU_MAX_DEVICES][VGPU_UUID_LEN];
         const int nwant = device_map_uuids(want, VGPU_MAX_DEVICES);
+        for (int i = 0; i < nwant; ++i)
+            for (int k = 0; k < i; ++k) g_map_has_duplicates |= strcasecmp(want[i], want[k]) == 0;
         int nreal = g_virtual_devices, nvisible = 0;
         char visible[VGPU_MAX_DEVICES][VGPU_UUID_LEN];  /* the distinct GPUs the map names, physical order */
         if (nwant > 0 && nv_count && nv_count(&n) == 0) nreal = (int)n;
@@ -1868,6 +1872,129 @@ EXPORT CUresult cuMemSetAccess(CUdeviceptr ptr, size_t size, const shim_access_d
         desc = d2;
     }
     return f ? f(ptr, size, desc, count) : 3;
+}
+
+/* ------------------------------------------------------------------ the monitor's entry points
+ * An outside monitor (the "vgpu monitor" that VGPU_MONITOR_MODE exists for) loads libvgpu.so next to a container's
+ * cache file and drives it through plain exported helpers: read usage / limits, report what NVML says a process really
+ * uses, resize a quota, suspend and resume the vGPU's processes.  Same names, arguments and answers as the
+ * reference's (multiprocess_memory_limit.c; pinned against the reference binary in tests/test_monitor_abi.py):
+ *   set_gpu_device_memory_monitor@0x42e29   first slot whose hostpid matches: monitorused[dev] = bytes; with
+ *       MEMORY_OVERRIDE (set to anything but "0" / "false") the slot's total BECOMES that figure (offset = bytes - total),
+ *       so allocations the hooks never saw count too; and unless ACTIVE_OOM_KILLER is "0" / "false", a process seen
+ *       above 1.1 x its limit gets every process of the vGPU killed (SIGKILL; not with an unlimited vGPU, not with a
+ *       GPU named twice in the map).  Always answers 1.
+ *   suspend_all@0x45ddf / resume_all@0x45eea   SIGUSR2 / SIGUSR1 to every process in the file. */
+static int env_switch_on(const char *name, int when_unset) {
+    const char *v = getenv(name);
+    if (!v) return when_unset;
+    return !(strcmp(v, "0") == 0 || strcmp(v, "false") == 0);
+}
+
+EXPORT uint64_t get_gpu_memory_usage(int dev) { ensure_initialized(); return region_usage(dev); }
+EXPORT uint64_t get_current_device_memory_usage(int dev) { return get_gpu_memory_usage(dev); }
+EXPORT uint64_t get_current_device_memory_limit(int dev) { ensure_initialized(); return region_limit(dev); }
+EXPORT int set_current_device_memory_limit(int dev, uint64_t bytes) {
+    ensure_initialized();
+    if (dev >= 0 && dev < VGPU_MAX_DEVICES) region_get()->limit[dev] = bytes;
+    return 0;
+}
+EXPORT int get_current_device_sm_limit(int dev) { ensure_initialized(); return (int)region_sm_limit(dev); }
+EXPORT int set_current_device_sm_limit_scale(int dev, int scale) {
+    /* @0x457a2: multiplies (30 x 50 = 1500), and only the first call per cache file does anything (sm_init_flag) */
+    ensure_initialized();
+    vgpu_region_t *r = region_get();
+    if (r->sm_init_flag == 1 || dev < 0 || dev >= VGPU_MAX_DEVICES) return 0;
+    r->sm_limit[dev] *= (uint64_t)scale;
+    r->sm_init_flag = 1;
+    return 0;
+}
+EXPORT int get_current_priority(void) { ensure_initialized(); return region_get()->priority; }
+EXPORT int get_recent_kernel(void) { ensure_initialized(); return region_get()->recent_kernel; }
+EXPORT int set_recent_kernel(int v) { ensure_initialized(); region_get()->recent_kernel = v; return 0; }
+EXPORT int get_utilization_switch(void) { ensure_initialized(); return region_get()->utilization_switch; }
+
+EXPORT uint64_t get_gpu_memory_monitor(int dev) {
+    ensure_initialized();
+    if (dev < 0 || dev >= VGPU_MAX_DEVICES) return 0;
+    vgpu_region_t *r = region_get();
+    uint64_t t = 0;
+    region_lock();
+    for (int i = 0; i < r->proc_num; ++i) t += r->procs[i].monitorused[dev];
+    region_unlock();
+    return t;
+}
+EXPORT uint64_t get_current_device_memory_monitor(int dev) { return get_gpu_memory_monitor(dev); }
+
+EXPORT void *find_proc_by_hostpid(int hostpid) {
+    ensure_initialized();
+    vgpu_region_t *r = region_get();
+    for (int i = 0; i < r->proc_num; ++i)
+        if (r->procs[i].hostpid == hostpid) return &r->procs[i];
+    return NULL;
+}
+
+EXPORT int set_gpu_device_memory_monitor(int hostpid, int dev, uint64_t bytes) {
+    ensure_initialized();
+    if (dev < 0 || dev >= VGPU_MAX_DEVICES) return 1;
+    vgpu_region_t *r = region_get();
+    int kill_all = 0;
+    region_lock();
+    for (int i = 0; i < r->proc_num; ++i) {
+        vgpu_proc_slot_t *s = &r->procs[i];
+        if (s->hostpid != hostpid) continue;
+        s->monitorused[dev] = bytes;
+        if (env_switch_on("MEMORY_OVERRIDE", 0)) {  /* what NVML sees replaces what the hooks counted */
+            s->used[dev].offset = bytes - s->used[dev].total;
+            s->used[dev].total = bytes;
+        }
+        const uint64_t limit = r->limit[dev];
+        if (!g_map_has_duplicates && limit != 0 && (double)bytes > (double)limit * 1.1 && env_switch_on("ACTIVE_OOM_KILLER", 1)) {
+            SHIM_ERR("hostpid %d uses %lu of %lu on device %d: killing the vGPU's processes", hostpid, (unsigned long)bytes,
+                     (unsigned long)limit, dev);
+            kill_all = 1;
+        }
+        break;
+    }
+    if (kill_all)  /* active_oom_killer@0x4297d */
+        for (int i = 0; i < r->proc_num; ++i) kill(r->procs[i].pid, SIGKILL);
+    region_unlock();
+    return 1;
+}
+
+static int signal_all(int sig) {
+    ensure_initialized();
+    vgpu_region_t *r = region_get();
+    int n = 0;
+    region_lock();
+    for (int i = 0; i < r->proc_num; ++i, ++n) kill(r->procs[i].pid, sig);
+    region_unlock();
+    return n;
+}
+EXPORT int suspend_all(void) { return signal_all(SIGUSR2); }
+EXPORT int resume_all(void) { return signal_all(SIGUSR1); }
+
+EXPORT int set_current_gpu_status(int status) {
+    ensure_initialized();
+    region_set_my_status(status);
+    return status;
+}
+EXPORT int wait_status_self(int status) {
+    ensure_initialized();
+    while (region_my_status() != status) usleep(1000);
+    return 1;
+}
+EXPORT int wait_status_all(int status) {
+    ensure_initialized();
+    vgpu_region_t *r = region_get();
+    for (;;) {
+        int all = 1;
+        region_lock();
+        for (int i = 0; i < r->proc_num; ++i) all &= r->procs[i].status == status;
+        region_unlock();
+        if (all) return 1;
+        usleep(1000);
+    }
 }
 
 /* ------------------------------------------------------------------ dispatch: dlsym / cuGetProcAddress */

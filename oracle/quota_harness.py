@@ -125,6 +125,10 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False,
                     procs[p].wait(timeout=20)
                     replies.append("killed")
                     continue
+                if "$pid" in op:  # "$pid<k>" = the pid of runner k (what an outside monitor would pass)
+                    for k, pr in enumerate(procs):
+                        if pr is not None:
+                            op = op.replace(f"$pid{k}", str(pr.pid))
                 procs[p].stdin.write(op + "\n")
                 procs[p].stdin.flush()
                 line = procs[p].stdout.readline()
@@ -171,7 +175,10 @@ def live_slots(b: bytes, pids) -> str:
         for d in range(16):
             u = struct.unpack_from("<5Q", b, o + 8 + d * 0x28)
             if any(u):
-                tok += f" d{d}={u[0]}/{u[1]}/{u[2]}/{u[4]}"
+                tok += f" d{d}={u[0]}/{u[1]}/{u[2]}/{u[4]}" + (f"+off{u[3]}" if u[3] else "")  # offset: MEMORY_OVERRIDE only
+        mon = struct.unpack_from("<16Q", b, o + 0x288)
+        if any(mon):
+            tok += " mon=" + ",".join(str(m) for m in mon[:max(i for i, m in enumerate(mon) if m) + 1])
         out.append(tok)
     return f"n={n} " + " | ".join(out)
 

@@ -38,6 +38,8 @@
  *   mtloop <threads> <n> <bytes>   every thread does n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2)  -> OR of all rc
  *   procaddr <ver> <flags> <name>   cuGetProcAddress_v2(name, ver, flags) -> rc <symbol the pointer belongs to>@<library>
  *   ptrdev <tag>           cuPointerGetAttribute(DEVICE_ORDINAL) of the tagged pointer -> rc ordinal
+ *   libcall <a> <b> <c> <name>   calls the preloaded library's exported helper name(a, b, c) (the entry points an outside
+ *                          monitor links: get_gpu_memory_usage, set_gpu_device_memory_monitor ...) -> 0 result | -100 if absent
  *   cvd                    getenv("CUDA_VISIBLE_DEVICES") as the process sees it now -> 0 value|-
  *   exporttable            cuGetExportTable (what every CUDA-runtime program does right after cuInit) -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
@@ -319,6 +321,13 @@ int main(void) {
             long long ord = -1;
             rc = cuPointerGetAttribute(&ord, 9, a < MAXTAG ? tags[a] : 0);
             printf("%d %d\n", rc, (int)ord);
+        } else if (!strcmp(op, "libcall")) {
+            char name[96] = {0};
+            sscanf(line, "%*s %*s %*s %*s %95s", name);
+            typedef long long (*fn3_t)(long long, long long, long long);
+            fn3_t f = (fn3_t)dlsym(RTLD_DEFAULT, name);
+            if (!f) printf("-100 0\n");
+            else printf("0 %lld\n", f((long long)a, (long long)b, (long long)c));
         } else if (!strcmp(op, "cvd")) {
             const char *v = getenv("CUDA_VISIBLE_DEVICES");
             printf("0 %s\n", v ? v : "-");

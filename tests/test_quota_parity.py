@@ -554,7 +554,8 @@ def test_shim_exports_the_hooked_driver_symbols():
     for n in ["cuInit", "cuMemAlloc_v2", "cuMemAllocManaged", "cuMemAllocPitch_v2", "cuMemFree_v2", "cuMemGetInfo_v2",
               "cuDeviceTotalMem_v2", "cuMemAllocHost_v2", "cuMemHostAlloc", "cuMemHostRegister_v2", "cuLaunchKernel",
               "cuGetProcAddress", "cuGetProcAddress_v2", "cuDevicePrimaryCtxRetain", "nvmlDeviceGetMemoryInfo", "dlsym",
-              "cuVGPUViewAllocator"]:
+              "cuVGPUViewAllocator", "get_gpu_memory_usage", "set_gpu_device_memory_monitor", "get_current_device_memory_limit",
+              "set_current_device_memory_limit", "suspend_all", "resume_all", "wait_status_self"]:
         assert n in names, n
     internal = [n for n in names if n.startswith(("region_", "shim_", "oom_", "add_chunk"))]
     assert not internal, f"internal helpers leak into the dynamic symbol table: {internal}"
