@@ -1436,6 +1436,8 @@ EXPORT int nvmlDeviceGetHandleByIndex_v2(unsigned index, void **handle) {
 }
 EXPORT int nvmlDeviceGetHandleByIndex(unsigned index, void **handle) { return nvmlDeviceGetHandleByIndex_v2(index, handle); }
 
+static int env_switch_on(const char *name, int when_unset);
+EXPORT uint64_t get_gpu_memory_monitor(int dev);
 /* usage / limit as NVML should show them for a physical GPU (by its NVML index, whatever the CUDA side enumerates):
  * the sums over the cache-file columns of this container's vGPUs on it; any unlimited vGPU makes it unlimited */
 static void nvml_quota(int nvml_index, uint64_t *usage, uint64_t *limit) {
@@ -1450,13 +1452,17 @@ static void nvml_quota(int nvml_index, uint64_t *usage, uint64_t *limit) {
             }
     }
     int unlimited = ncols == 0;
+    uint64_t monitored = 0;
     *usage = *limit = 0;
     for (int c = col0; c < col0 + ncols; ++c) {
         *usage += region_usage(c);
         *limit += region_limit(c);
         unlimited |= region_limit(c) == 0;
+        monitored += get_gpu_memory_monitor(c);
     }
     if (unlimited) *limit = 0;
+    /* nvmlDeviceGetMemoryInfo@0x25052 with MEMORY_OVERRIDE (read @0x2546a): what the outside monitor measured wins when it is more */
+    if (env_switch_on("MEMORY_OVERRIDE", 0) && monitored > *usage) *usage = monitored;
 }
 
 EXPORT int nvmlDeviceGetMemoryInfo(void *handle, nvmlMemory_t *m) {

@@ -119,3 +119,16 @@ def test_quota_resize_and_suspend_resume_from_the_monitor():
     assert rep[9] == "0 2" and rep[10].count(":1:2") == 2                            # SIGUSR2 reached both processes
     assert rep[11] == "0 2" and rep[12].count(":1:1") == 2
     assert rep[13] == "0 2" and rep[14].startswith("n=2 p0:1:2") and rep[15] == "0 1" and rep[16] == rep[17] == "0 1"
+
+
+def test_nvml_shows_the_monitor_figure_when_it_is_larger_and_override_is_on():
+    """nvmlDeviceGetMemoryInfo in a process started with MEMORY_OVERRIDE: used = max(hook-counted usage, what the monitor
+    reported); a process without it keeps the counted usage.  The quota itself (cuMemGetInfo) is not touched by this."""
+    envs = [{**ENV, "MEMORY_OVERRIDE": "1"}, ENV]
+    tr = [(0, "retain 0 1"), (1, "retain 0 1"), (0, f"alloc {100 * M} 1"), (0, "nvmlmem"),
+          (1, f"libcall $pid0 0 {900 * M} set_gpu_device_memory_monitor"), (0, "nvmlmem"), (1, "nvmlmem"), (0, "info"),
+          (1, f"libcall $pid0 0 {200 * M} set_gpu_device_memory_monitor"), (0, "nvmlmem")]
+    rep = both(tr, envs, 2)
+    counted = 2 * C + 100 * M
+    assert rep[3] == rep[6] == rep[9] == f"0 {G} {G - counted} {counted}"
+    assert rep[5] == f"0 {G} {G - 900 * M} {900 * M}" and rep[7] == f"0 {G - counted} {G}"
