@@ -244,9 +244,29 @@ static void narrow_visible_devices(char vis[][VGPU_UUID_LEN], int nvis, int nrea
     SHIM_INFO("CUDA_VISIBLE_DEVICES=%s (from NVIDIA_DEVICE_MAP%s%s)", out, user ? " and " : "", user ? user : "");
 }
 
+/* load_env_from_file@0x420cc (the reference calls it with "/overrideEnv" from its NVML pre-init): KEY=VALUE lines, each
+ * put into the environment over whatever is there (setenv(.., 1)); the value is everything after the FIRST '=', the
+ * trailing newline goes; reading stops at the first line that has no '='.  Always answers 0. */
+EXPORT int load_env_from_file(const char *path) {
+    FILE *f = path ? fopen(path, "r") : NULL;
+    if (!f) return 0;
+    char line[10000];
+    while (fgets(line, sizeof(line), f)) {
+        char *eq = strchr(line, '=');
+        if (!eq) break;
+        size_t n = strlen(line);
+        if (n && line[n - 1] == '\n') line[n - 1] = 0;
+        *eq = 0;
+        setenv(line, eq + 1, 1);
+    }
+    fclose(f);
+    return 0;
+}
+
 static void pre_init(void) {
     vgpu_region_init_t init;
     memset(&init, 0, sizeof(init));
+    load_env_from_file("/overrideEnv");  /* an admin-provided file in the container wins over the pod's environment */
     init_limits(&init);
     const char *prio = getenv("CUDA_TASK_PRIORITY");
     init.priority = prio ? atoi(prio) : 1;

@@ -40,6 +40,8 @@
  *   ptrdev <tag>           cuPointerGetAttribute(DEVICE_ORDINAL) of the tagged pointer -> rc ordinal
  *   libcall <a> <b> <c> <name>   calls the preloaded library's exported helper name(a, b, c) (the entry points an outside
  *                          monitor links: get_gpu_memory_usage, set_gpu_device_memory_monitor ...) -> 0 result | -100 if absent
+ *   libcalls <name> <string>   calls the preloaded library's name(const char *) -> 0 result | -100 if absent
+ *   getenv <NAME>          -> 0 value|-
  *   cvd                    getenv("CUDA_VISIBLE_DEVICES") as the process sees it now -> 0 value|-
  *   exporttable            cuGetExportTable (what every CUDA-runtime program does right after cuInit) -> rc
  *   loop <n> <bytes>       n x (cuMemAlloc_v2, cuMemGetInfo_v2, cuMemFree_v2), timed -> rc ns_total
@@ -328,6 +330,18 @@ int main(void) {
             fn3_t f = (fn3_t)dlsym(RTLD_DEFAULT, name);
             if (!f) printf("-100 0\n");
             else printf("0 %lld\n", f((long long)a, (long long)b, (long long)c));
+        } else if (!strcmp(op, "libcalls")) {
+            char name[96] = {0}, arg[160] = {0};
+            sscanf(line, "%*s %95s %159s", name, arg);
+            typedef long long (*fns_t)(const char *);
+            fns_t f = (fns_t)dlsym(RTLD_DEFAULT, name);
+            if (!f) printf("-100 0\n");
+            else printf("0 %lld\n", f(arg));
+        } else if (!strcmp(op, "getenv")) {
+            char name[96] = {0};
+            sscanf(line, "%*s %95s", name);
+            const char *v = getenv(name);
+            printf("0 %s\n", v ? v : "-");
         } else if (!strcmp(op, "cvd")) {
             const char *v = getenv("CUDA_VISIBLE_DEVICES");
             printf("0 %s\n", v ? v : "-");

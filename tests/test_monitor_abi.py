@@ -132,3 +132,16 @@ def test_nvml_shows_the_monitor_figure_when_it_is_larger_and_override_is_on():
     counted = 2 * C + 100 * M
     assert rep[3] == rep[6] == rep[9] == f"0 {G} {G - counted} {counted}"
     assert rep[5] == f"0 {G} {G - 900 * M} {900 * M}" and rep[7] == f"0 {G - counted} {G}"
+
+
+def test_override_env_file_is_parsed_like_the_reference(tmp_path):
+    """load_env_from_file@0x420cc ("/overrideEnv" in the container): KEY=VALUE per line, over the existing environment,
+    value = everything after the first '=', stops at the first line without '=', a last line without newline counts."""
+    e1, e2 = tmp_path / "e1", tmp_path / "e2"
+    e1.write_text("A=1\nB=x=y=z\nC=\nSTOPS_AFTER_ME=1\n\nNEVER=reached\n")
+    e2.write_text("LAST=nonl")
+    ops = ["getenv A", f"libcalls load_env_from_file {e1}", "getenv A", "getenv B", "getenv C", "getenv STOPS_AFTER_ME", "getenv NEVER",
+           f"libcalls load_env_from_file {e2}", "getenv LAST", f"libcalls load_env_from_file {tmp_path / 'missing'}"]
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "NVIDIA_DEVICE_MAP": "0:" + H.UUID0, "A": "old"}
+    rep = both([(0, o) for o in ops], env, 1)
+    assert rep == ["0 old", "0 0", "0 1", "0 x=y=z", "0", "0 1", "0 -", "0 0", "0 nonl", "0 0"]
