@@ -1064,6 +1064,14 @@ static int vdev_of_ctx(CUcontext ctx, int phys) {
     return v >= 0 ? v : first_vdev_of(phys);
 }
 
+/* GPU_CORE_UTILIZATION_POLICY (set_env_utilization_switch@0x44b3b): DISABLE / disable switches the reference's launch
+ * throttle off, FORCE / force keeps it on whatever the monitor says.  The cap here is spatial and always on, so FORCE
+ * is the normal case and DISABLE means: no partition. */
+static int sm_policy_disabled(void) {
+    const char *p = getenv("GPU_CORE_UTILIZATION_POLICY");
+    return p && (strcmp(p, "DISABLE") == 0 || strcmp(p, "disable") == 0);
+}
+
 static unsigned partition_pick(unsigned nb) {
     const char *e = getenv("VGPU_SM_PARTITION_INDEX");
     if (e && *e) return (unsigned)strtoul(e, NULL, 0) % nb;
@@ -1077,7 +1085,7 @@ static CUcontext green_ctx_for(CUdevice dev) {
     if (dev < 0 || dev >= VGPU_MAX_DEVICES || !g_region_ok) return NULL;
     uint64_t pct = q_sm_limit(dev);
     const char *sw = getenv("VGPU_SM_PARTITION");
-    if (pct == 0 || pct >= 100 || (sw && strcmp(sw, "off") == 0)) return NULL;
+    if (pct == 0 || pct >= 100 || (sw && strcmp(sw, "off") == 0) || sm_policy_disabled()) return NULL;
     pthread_mutex_lock(&g_green_mu);
     if (g_green_state[dev] == 0) {
         g_green_state[dev] = -1;
@@ -1238,7 +1246,7 @@ static int caps_possible(void) {
     if (v < 0) {
         const char *sw = getenv("VGPU_SM_PARTITION");
         v = 0;
-        if (g_region_ok && !(sw && strcmp(sw, "off") == 0))
+        if (g_region_ok && !(sw && strcmp(sw, "off") == 0) && !sm_policy_disabled())
             for (int d = 0; d < VGPU_MAX_DEVICES; ++d) {
                 uint64_t p = region_sm_limit(d);
                 if (p > 0 && p < 100) v = 1;

@@ -373,6 +373,22 @@ def test_sm_limit_becomes_a_green_context_partition(cuda_dev):
     assert capped["tflops"] < 0.6 * free["tflops"], (capped, free)
 
 
+def test_core_utilization_policy_disable_lifts_the_sm_cap(cuda_dev):
+    """GPU_CORE_UTILIZATION_POLICY=DISABLE (reference: set_env_utilization_switch@0x44b3b turns the throttle off): no
+    green-context partition; FORCE, like no policy at all, keeps the 25 % cap."""
+    code = """
+        import ctypes, json, torch
+        torch.cuda.init()
+        torch.ones(1, device="cuda").sum().item()
+        print(json.dumps({"sms": ctypes.CDLL(None).cuVGPUPartitionSmCount(0)}))
+    """
+    base = {"CUDA_DEVICE_SM_LIMIT": "25", "CUDA_DEVICE_MEMORY_LIMIT_0": "8g"}
+    assert last_json(run_under_shim(code, {**base, "GPU_CORE_UTILIZATION_POLICY": "DISABLE"}))["sms"] == 0
+    assert last_json(run_under_shim(code, {**base, "GPU_CORE_UTILIZATION_POLICY": "disable"}))["sms"] == 0
+    assert 0 < last_json(run_under_shim(code, {**base, "GPU_CORE_UTILIZATION_POLICY": "FORCE"}))["sms"] <= 37
+    assert 0 < last_json(run_under_shim(code, base))["sms"] <= 37
+
+
 def test_vgpuvalidator_cli_memtest_and_quota(cuda_dev):
     exe = os.path.join(ROOT, "4paradigm-k8s-device-plugin_b200", "vgpuvalidator")
     p = subprocess.run([exe, "--memtest", "--gib", "1", "--random-passes", "2"], capture_output=True, text=True, timeout=300)
