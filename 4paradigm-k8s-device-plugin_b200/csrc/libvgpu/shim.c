@@ -857,6 +857,7 @@ EXPORT CUresult cuPointerGetAttribute(void *data, int attr, CUdeviceptr ptr) {
 EXPORT CUresult cuMemAllocHost_v2(void **pp, size_t n) {
     if (tl_bypass) return get_cuMemAllocHost_v2()(pp, n);
     ensure_initialized();
+    wait_running();  /* host allocations park while the vGPU is suspended, as in the reference */
     cuMemAllocHost_v2_t f = get_cuMemAllocHost_v2();
     CUresult rc = f ? f(pp, n) : 3;
     if (rc != 0) return rc;
@@ -871,6 +872,7 @@ EXPORT CUresult cuMemAllocHost(void **pp, size_t n) { return cuMemAllocHost_v2(p
 EXPORT CUresult cuMemHostAlloc(void **pp, size_t n, unsigned flags) {
     if (tl_bypass) return get_cuMemHostAlloc()(pp, n, flags);
     ensure_initialized();
+    wait_running();  /* host allocations park while the vGPU is suspended, as in the reference */
     cuMemHostAlloc_t f = get_cuMemHostAlloc();
     CUresult rc = f ? f(pp, n, flags) : 3;
     if (rc != 0) return rc;
@@ -884,6 +886,7 @@ EXPORT CUresult cuMemHostAlloc(void **pp, size_t n, unsigned flags) {
 EXPORT CUresult cuMemHostRegister_v2(void *p, size_t n, unsigned flags) {
     if (tl_bypass) return get_cuMemHostRegister_v2()(p, n, flags);
     ensure_initialized();
+    wait_running();  /* host allocations park while the vGPU is suspended, as in the reference */
     cuMemHostRegister_v2_t f = get_cuMemHostRegister_v2();
     CUresult rc = f ? f(p, n, flags) : 3;
     if (rc != 0) return rc;

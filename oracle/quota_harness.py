@@ -120,6 +120,19 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False,
                     time.sleep(0.05)  # handlers only write the status word
                     replies.append("signalled")
                     continue
+                if op.startswith("@send "):  # an op whose reply is not awaited (it may park at the suspend gate)
+                    procs[p].stdin.write(op[6:] + "\n")
+                    procs[p].stdin.flush()
+                    replies.append("sent")
+                    continue
+                if op == "@poll":   # is the reply of the last @send there yet? (0.4 s of patience)
+                    import select
+                    ready, _, _ = select.select([procs[p].stdout], [], [], 0.4)
+                    replies.append("ready" if ready else "blocked")
+                    continue
+                if op == "@recv":
+                    replies.append(procs[p].stdout.readline().strip())
+                    continue
                 if op == "@kill":   # the process dies without running its exit handler (SIGKILL): its slot stays behind
                     procs[p].kill()
                     procs[p].wait(timeout=20)

@@ -421,6 +421,27 @@ def test_cuGetProcAddress_hands_out_the_hook_with_the_abi_the_caller_asked_for()
     assert all(r.endswith("@libcuda.so.1") for r in rep), rep
 
 
+GATE_PROBES = [("launch 4 128", True), (f"alloc {M} 9", True), (f"managed {M} 9", True), ("pitch 64 4 4 9", True), ("hostalloc 4096 9", True),
+               ("hostalloc2 4096 9", True), ("hostreg 4096", True), ("ptrattrs 1", True), ("info", False), ("total 0", False), ("free 1", False),
+               ("freehost 2", False), ("nvmlmem", False), ("devcount", False), ("ctxget", False)]
+
+
+@pytest.mark.parametrize("probe,parks", GATE_PROBES, ids=[p.split()[0] for p, _ in GATE_PROBES])
+def test_which_calls_park_while_the_vgpu_is_suspended(probe, parks):
+    """SIGUSR2 sets the status word to 2 (suspended): launches and allocations (device, managed, pitch, pinned host,
+    pointer queries) wait at the gate until SIGUSR1, frees and read-only queries go through — call by call as the
+    reference does (wait_status_self@0x45ff5 in its hooks)."""
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}
+    tr = [(0, f"alloc {M} 1"), (0, "hostalloc 4096 2"), (0, "@usr2"), (0, "@send " + probe), (0, "@poll"), (0, "@usr1"), (0, "@recv"), (0, "info")]
+    libs = [H.NEW_LIB] + ([H.REFERENCE_LIB] if H.have_reference() else [])
+    seen = []
+    for lib in libs:
+        r = H.run_trace(lib, tr, env)["replies"]
+        assert r[4] == ("blocked" if parks else "ready"), (lib, probe, r)
+        seen.append(r[6:])
+    assert all(x == seen[0] for x in seen)                     # and the parked call completes with the same answer afterwards
+
+
 ODD_OPS = ["total 5", "total 15", "total 16", "total 100", "total -1", "info", "pitch 1 1 1 1", "pitch 4097 3 4 2", "pitch 100 0 8 3", "info",
            "managed 0 4", "info", "alloc 1 5", "alloc 2097152 6", "alloc 2097153 7", "info", "hostreg 0", "hostalloc 0 8", "freehost 8",
            "ptrattrs 5", "ptrattrs 0", "nvmlmem", "free 6", "free 7", "free 5", "info"]
