@@ -912,6 +912,7 @@ EXPORT CUresult cuMemHostRegister(void *p, size_t n, unsigned flags) { return cu
  * of device 0 (one context creation and teardown per process start, ~0.2 s on a B200); here the probe
  * wraps the first retain / create the application makes itself, so nothing is created twice. */
 static uint64_t g_context_size;
+static int g_hostpid_known;  /* pidfound: the monitor can see this process, so its launch lever applies */
 static int g_ctx_probed;
 static int g_ctx_flag[VGPU_MAX_DEVICES];  /* vdevices[d].flag (+0x14) */
 static pthread_mutex_t g_ctx_mu = PTHREAD_MUTEX_INITIALIZER;
@@ -987,6 +988,7 @@ static CUresult probe_around(CUdevice dev, CUresult (*make_ctx)(void *), void *a
             /* getextrapid@0x17a4f + set_host_pid@0x4497c; ~0ull = NVML_VALUE_NOT_AVAILABLE (e.g. under WDDM / vGPU hosts) */
             g_context_size = after[i].used == ~0ull ? 0 : after[i].used;
             region_set_hostpid((int)after[i].pid);
+            g_hostpid_known = 1;
             SHIM_INFO("host pid %u, context size %lu", after[i].pid, (unsigned long)g_context_size);
             break;
         }
@@ -1308,11 +1310,23 @@ EXPORT CUresult cuCtxPushCurrent(CUcontext ctx) { return cuCtxPushCurrent_v2(ctx
 
 /* cuLaunchKernel@0x37c2b: the suspend gate stays; rate_limiter@0x463b1 is gone — the SM cap is
  * spatial (green context), so there is nothing to do per launch. */
+/* What is left of rate_limiter@0x463b1 at every launch once the host pid is known (pidfound): the monitor's lever
+ * and its activity mark.  recent_kernel < 0 in the cache file holds every launch of the vGPU (the monitor parks
+ * low-priority tasks that way), and a launch writes recent_kernel = 2 ("was active a moment ago"; the monitor counts
+ * it down).  The token bucket that followed is what the green context replaces. */
+static void launch_mark(void) {
+    if (!g_hostpid_known || !g_region_ok) return;
+    vgpu_region_t *r = region_get();
+    while (*(volatile int32_t *)&r->recent_kernel < 0) sleep(1);
+    if (r->recent_kernel != 2) r->recent_kernel = 2;  /* no write when it is already there: the line is shared by every process */
+}
+
 EXPORT CUresult cuLaunchKernel(void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by,
                                unsigned bz, unsigned shm, void *stream, void **params, void **extra) {
     if (tl_bypass) return get_cuLaunchKernel()(fn, gx, gy, gz, bx, by, bz, shm, stream, params, extra);
     ensure_initialized();
     wait_running();
+    launch_mark();
     cuLaunchKernel_t f = get_cuLaunchKernel();
     return f ? f(fn, gx, gy, gz, bx, by, bz, shm, stream, params, extra) : 3;
 }
@@ -1324,6 +1338,7 @@ EXPORT CUresult cuLaunchKernelEx(const void *config, void *fn, void **params, vo
     if (!tl_bypass) {
         ensure_initialized();
         wait_running();
+        launch_mark();
     }
     return f ? f(config, fn, params, extra) : 3;
 }

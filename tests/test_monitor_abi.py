@@ -145,3 +145,18 @@ def test_override_env_file_is_parsed_like_the_reference(tmp_path):
     env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "NVIDIA_DEVICE_MAP": "0:" + H.UUID0, "A": "old"}
     rep = both([(0, o) for o in ops], env, 1)
     assert rep == ["0 old", "0 0", "0 1", "0 x=y=z", "0", "0 1", "0 -", "0 0", "0 nonl", "0 0"]
+
+
+def test_recent_kernel_is_the_activity_mark_and_the_monitors_brake():
+    """rate_limiter@0x463b1, first lines: while recent_kernel < 0 every launch of the vGPU waits (the monitor parks
+    low-priority tasks that way), and a launch leaves recent_kernel = 2 — once the host pid is known; a process NVML does
+    not list is left alone."""
+    tr = [(0, "retain 0 1"), (1, "retain 0 1"), (1, "libcall 0 0 0 set_recent_kernel"), (0, "launch 4 128"), (1, "libcall 0 0 0 get_recent_kernel"),
+          (1, "libcall -1 0 0 set_recent_kernel"), (0, "@send launch 4 128"), (0, "@poll"), (1, "libcall 0 0 0 set_recent_kernel"), (0, "@recv"),
+          (1, "libcall 0 0 0 get_recent_kernel")]
+    rep = both(tr, ENV, 2)
+    assert rep[4] == "0 2" and rep[7] == "blocked" and rep[9] == "0" and rep[10] == "0 2"
+    unseen = {k: v for k, v in ENV.items() if k != "MOCK_CTX_MIB"}      # NVML lists no process: no host pid, no lever
+    rep = both([(0, "libcall 0 0 0 set_recent_kernel"), (0, "launch 4 128"), (0, "libcall 0 0 0 get_recent_kernel"),
+                (0, "libcall -1 0 0 set_recent_kernel"), (0, "launch 4 128"), (0, "libcall 0 0 0 get_recent_kernel")], unseen, 1)
+    assert rep == ["0 0", "0", "0 0", "0 0", "0", "0 4294967295"]
