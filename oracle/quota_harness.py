@@ -133,6 +133,11 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False,
                 if op == "@recv":
                     replies.append(procs[p].stdout.readline().strip())
                     continue
+                if op == "@sleep":  # lets signals sent to OTHER processes be delivered before the file is looked at
+                    import time
+                    time.sleep(0.15)
+                    replies.append("slept")
+                    continue
                 if op == "@kill":   # the process dies without running its exit handler (SIGKILL): its slot stays behind
                     procs[p].kill()
                     procs[p].wait(timeout=20)

@@ -110,15 +110,15 @@ def test_quota_resize_and_suspend_resume_from_the_monitor():
           (1, f"libcall 0 {2048 * M} 0 set_current_device_memory_limit"), (0, "info"), (0, "total 0"),   # takes effect at once, for everybody
           (1, "libcall 0 50 0 set_current_device_sm_limit_scale"), (0, "libcall 0 3 0 set_current_device_sm_limit_scale"),   # once per file
           (0, "libcall 0 0 0 get_current_device_sm_limit"),
-          (1, "libcall 0 0 0 suspend_all"), (0, "@slots"), (1, "libcall 0 0 0 resume_all"), (0, "@slots"),
+          (1, "libcall 0 0 0 suspend_all"), (0, "@sleep"), (0, "@slots"), (1, "libcall 0 0 0 resume_all"), (0, "@sleep"), (0, "@slots"),
           (0, "libcall 2 0 0 set_current_gpu_status"), (1, "@slots"), (0, "libcall 1 0 0 set_current_gpu_status"),
           (0, "libcall 1 0 0 wait_status_self"), (1, "libcall 1 0 0 wait_status_all")]
     rep = both(tr, ENV, 2)
     assert rep[3] == "0 0" and rep[4] == f"0 {2 * G - 2 * C - 100 * M} {2 * G}" and rep[5] == f"0 {2 * G}"
     assert rep[8] == "0 1500"                                                        # 30 x 50: a multiplication, and the x 3 is ignored
-    assert rep[9] == "0 2" and rep[10].count(":1:2") == 2                            # SIGUSR2 reached both processes
-    assert rep[11] == "0 2" and rep[12].count(":1:1") == 2
-    assert rep[13] == "0 2" and rep[14].startswith("n=2 p0:1:2") and rep[15] == "0 1" and rep[16] == rep[17] == "0 1"
+    assert rep[9] == "0 2" and rep[11].count(":1:2") == 2                            # SIGUSR2 reached both processes
+    assert rep[12] == "0 2" and rep[14].count(":1:1") == 2
+    assert rep[15] == "0 2" and rep[16].startswith("n=2 p0:1:2") and rep[17] == "0 1" and rep[18] == rep[19] == "0 1"
 
 
 def test_nvml_shows_the_monitor_figure_when_it_is_larger_and_override_is_on():
