@@ -295,6 +295,60 @@ def test_nvidia_smi_in_the_pod_shows_the_quota(cuda_dev):
         assert len(rows) == 1 and rows[0][0] == uuid and int(rows[0][1]) == total_mib and int(rows[0][2]) == 0
 
 
+def test_outside_monitor_closes_the_async_allocator_hole_with_memory_override(cuda_dev):
+    """The monitor plane end to end on the real driver: a tenant allocates 3 GiB through cudaMallocAsync (not metered, as
+    in the reference).  A monitor process loads libvgpu.so next to the tenant's cache file with MEMORY_OVERRIDE, reads what
+    NVML says the tenant's host pid really uses and reports it (set_gpu_device_memory_monitor): from then on the tenant's
+    quota counts it — cuMemGetInfo shrinks and a metered 2 GiB cuMemAlloc is refused."""
+    td = tempfile.mkdtemp(prefix="vgpushim")
+    cache = os.path.join(td, "tenant.cache")
+    tenant = subprocess.Popen([sys.executable, "-c", textwrap.dedent("""
+        import ctypes, json, sys, torch
+        torch.cuda.init()
+        a = torch.empty(3 << 30, dtype=torch.uint8, device="cuda"); a[-1] = 1; torch.cuda.synchronize()
+        cu = ctypes.CDLL("libcuda.so.1")
+        def info():
+            f, t = ctypes.c_size_t(), ctypes.c_size_t(); rc = cu.cuMemGetInfo_v2(ctypes.byref(f), ctypes.byref(t)); return rc, f.value, t.value
+        print(json.dumps({"before": info()}), flush=True)
+        sys.stdin.readline()                          # the monitor does its round
+        p = ctypes.c_ulonglong()
+        rc = ctypes.c_int(cu.cuMemAlloc_v2(ctypes.byref(p), ctypes.c_size_t(2 << 30))).value
+        print(json.dumps({"after": info(), "alloc_2g": rc}), flush=True)
+    """)], env={**os.environ, "LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": cache, "CUDA_DEVICE_MEMORY_LIMIT_0": "4096m",
+                "PYTORCH_CUDA_ALLOC_CONF": "backend:cudaMallocAsync", "LIBCUDA_LOG_LEVEL": "0"},
+        stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True)
+    try:
+        before = json.loads(tenant.stdout.readline())["before"]
+        monitor = subprocess.run([sys.executable, "-c", textwrap.dedent("""
+            import ctypes, json, os, sys
+            sys.path.insert(0, os.environ["VGPU_PKG"])
+            import importlib; mon = importlib.import_module("monitor")
+            import pynvml; pynvml.nvmlInit()
+            lib = ctypes.CDLL(os.environ["VGPU_SHIM"])
+            lib.set_gpu_device_memory_monitor.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_uint64]
+            lib.get_gpu_memory_usage.restype = ctypes.c_uint64
+            r = mon.read_region(os.environ["CUDA_DEVICE_MEMORY_SHARED_CACHE"])
+            tenant = [p for p in r["procs"] if p["used"][0]["total"] > 0][0]
+            real = {p.pid: p.usedGpuMemory for p in pynvml.nvmlDeviceGetComputeRunningProcesses(pynvml.nvmlDeviceGetHandleByIndex(0))}
+            used = real[tenant["hostpid"]]
+            rc = lib.set_gpu_device_memory_monitor(tenant["hostpid"], 0, used)
+            print(json.dumps({"hostpid": tenant["hostpid"], "counted": tenant["used"][0]["total"], "nvml": used, "rc": rc,
+                              "usage_after": lib.get_gpu_memory_usage(0)}))
+        """)], env={**os.environ, "CUDA_DEVICE_MEMORY_SHARED_CACHE": cache, "MEMORY_OVERRIDE": "1", "ACTIVE_OOM_KILLER": "0", "LIBCUDA_LOG_LEVEL": "0",
+                    "VGPU_PKG": os.path.join(ROOT, "4paradigm-k8s-device-plugin_b200"), "VGPU_SHIM": SHIM}, capture_output=True, text=True, timeout=120)
+        assert monitor.returncode == 0, monitor.stderr[-2000:]
+        m = json.loads(monitor.stdout.strip().splitlines()[-1])
+        tenant.stdin.write("\n"); tenant.stdin.flush()
+        after = json.loads(tenant.stdout.readline())
+    finally:
+        tenant.kill()
+    print("monitor round:", m, "tenant before:", before, "after:", after)
+    assert m["rc"] == 1 and m["counted"] < 1 * GiB < 3 * GiB < m["nvml"] and m["usage_after"] == m["nvml"]
+    assert before[0] == 0 and before[2] == 4 * GiB and before[1] > 3 * GiB           # the 3 GiB went unnoticed
+    assert after["after"][0] == 0 and after["after"][1] == 4 * GiB - m["nvml"]       # now they count
+    assert after["alloc_2g"] == -1                                                   # and the quota holds
+
+
 def test_nvml_memory_info_shows_the_limit(cuda_dev):
     code = """
         import json, torch, pynvml
