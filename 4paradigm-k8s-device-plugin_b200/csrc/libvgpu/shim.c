@@ -2176,7 +2176,7 @@ static int wants_ptds(const char *symbol, unsigned long long flags) {
 /* dlsym@0x12bb6: every cu, nvml lookup that names a hooked symbol lands in the shim */
 EXPORT void *dlsym(void *handle, const char *symbol) {
     find_real_dlsym();
-    if (symbol && ((symbol[0] == 'c' && symbol[1] == 'u') || strncmp(symbol, "nvml", 4) == 0)) {
+    if ((symbol[0] == 'c' && symbol[1] == 'u') || strncmp(symbol, "nvml", 4) == 0) {
         void *h = find_hook(symbol);
         if (h) return h;
     }
