@@ -1648,10 +1648,49 @@ typedef struct { int type, id; } shim_mem_location_t;
 static int loc_to_phys(shim_mem_location_t *l) { return l->type != 1 || to_phys(&l->id); }
 
 /* cuMemPrefetchAsync / cuMemAdvise: the device argument may also be CU_DEVICE_CPU (-1) */
+/* With the VMM oversubscribe backend the application's "managed" allocations are explicit ranges of the data path, and
+ * the prefetch calls a UVM program already makes become its paging controls: prefetch to the CPU = spill the allocation
+ * to the tier and give its HBM back (only when the call covers the whole allocation: the manager moves whole blocks, and
+ * unlike UVM nothing faults back in — the data is out until it is prefetched to the device again); prefetch to the
+ * device = make the range resident again, checksum-verified.  Synchronous with respect to `stream`.
+ * -> 1 handled (rc set), 0 not one of ours */
+typedef CUresult (*stream_sync_t)(void *);
+static int vmm_prefetch(CUdeviceptr p, size_t n, int to_device, void *stream, CUresult *rc) {
+    if (!g_backend_vmm || tl_bypass) return 0;
+    pthread_mutex_lock(&g_alloc_mu);
+    alloc_node_t *a = g_head;
+    while (a && !(a->vmem && p >= a->addr && p < a->addr + a->len)) a = a->next;
+    if (!a) {
+        pthread_mutex_unlock(&g_alloc_mu);
+        return 0;
+    }
+    const uint64_t chunks = (a->len + IPCSIZE - 1) / IPCSIZE;
+    int vrc = 0;
+    tl_bypass = 1;
+    if (to_device) {
+        const uint64_t first = (p - a->addr) / IPCSIZE;
+        uint64_t last = (p + (n ? n : 1) - 1 - a->addr) / IPCSIZE;
+        if (last >= chunks) last = chunks - 1;
+        vrc = g_dp.ensure(a->vmem, first, last - first + 1);
+    } else if (p == a->addr && n >= a->len) {
+        static stream_sync_t sync;
+        if (!sync) sync = (stream_sync_t)cuda_sym("cuStreamSynchronize");
+        if (sync) sync(stream);  /* what was queued on it may still use the data */
+        vrc = g_dp.evict(a->vmem, 0, chunks);
+    }
+    if (vrc != 0) SHIM_ERR("vmm backend prefetch: %s", g_dp.last_error());
+    tl_bypass = 0;
+    pthread_mutex_unlock(&g_alloc_mu);
+    *rc = vrc == 0 ? 0 : 999;
+    return 1;
+}
+
 EXPORT CUresult cuMemPrefetchAsync(CUdeviceptr p, size_t n, CUdevice d, void *stream) {
     typedef CUresult (*fn_t)(CUdeviceptr, size_t, CUdevice, void *);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuMemPrefetchAsync");
+    CUresult rc;
+    if (vmm_prefetch(p, n, d >= 0, stream, &rc)) return rc;
     if (!tl_bypass && d >= 0 && !to_phys(&d)) return 101;
     return f ? f(p, n, d, stream) : 3;
 }
@@ -1667,6 +1706,8 @@ EXPORT CUresult cuMemPrefetchAsync_v2(CUdeviceptr p, size_t n, shim_mem_location
     typedef CUresult (*fn_t)(CUdeviceptr, size_t, shim_mem_location_t, unsigned, void *);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuMemPrefetchAsync_v2");
+    CUresult rc;
+    if (vmm_prefetch(p, n, loc.type == 1 /* DEVICE; HOST / HOST_NUMA = out */, stream, &rc)) return rc;
     if (!tl_bypass && !loc_to_phys(&loc)) return 101;
     return f ? f(p, n, loc, flags, stream) : 3;
 }

@@ -498,6 +498,44 @@ def test_oversubscribe_vmm_backend_suspend_releases_hbm_and_resume_restores(cuda
     assert o["same"] and o["small"] == 1024.0
 
 
+def test_prefetch_calls_page_vmm_backed_allocations_out_and_in(cuda_dev):
+    """With the VMM backend the prefetch calls of a UVM-style program are its paging controls: prefetch to the CPU (device
+    -1) spills the allocation to pinned host RAM and gives the HBM back, prefetch to the device brings it back behind the
+    same pointer, checksum-verified.  A prefetch of part of an allocation towards the CPU is a hint that is not taken."""
+    code = """
+        import ctypes, json, os, subprocess, torch
+        cu = ctypes.CDLL("libcuda.so.1")
+        torch.cuda.init()
+        n = 4 << 30
+        a = torch.empty(n, dtype=torch.uint8, device="cuda")
+        a.view(torch.int64).copy_(torch.arange(n // 8, device="cuda", dtype=torch.int64) * 2654435761)
+        s0 = int(a.view(torch.int64).sum().item())
+        torch.cuda.synchronize(); torch.cuda.empty_cache()
+        def used_mib():
+            env = {k: v for k, v in os.environ.items() if k != "LD_PRELOAD"}
+            o = subprocess.run(["nvidia-smi", "--query-gpu=memory.used", "--format=csv,noheader,nounits", "-i", "0"], capture_output=True, text=True, env=env).stdout
+            return int(o.strip().splitlines()[0])
+        def prefetch(ptr, size, dev):
+            return cu.cuMemPrefetchAsync(ctypes.c_ulonglong(ptr), ctypes.c_size_t(size), ctypes.c_int(dev), None)
+        u0 = used_mib()
+        rc_part = prefetch(a.data_ptr() + (1 << 30), 1 << 30, -1); u_part = used_mib()     # part of it: not taken
+        rc_out = prefetch(a.data_ptr(), n, -1); u1 = used_mib()
+        rc_in = prefetch(a.data_ptr() + (1 << 20), 1 << 20, 0); u2 = used_mib()            # any part towards the device: its blocks come back
+        rc_all = prefetch(a.data_ptr(), n, 0); u3 = used_mib()
+        s1 = int(a.view(torch.int64).sum().item())
+        print(json.dumps({"rc": [rc_part, rc_out, rc_in, rc_all], "used_mib": [u0, u_part, u1, u2, u3], "same": s0 == s1}))
+    """
+    p = run_under_shim(code, {"CUDA_DEVICE_MEMORY_LIMIT_0": "40g", "CUDA_OVERSUBSCRIBE": "true", "VGPU_OVERSUB_BACKEND": "vmm"})
+    o = last_json(p)
+    print("prefetch paging:", o)
+    assert o["rc"] == [0, 0, 0, 0], p.stderr[-2000:]
+    u0, u_part, u1, u2, u3 = o["used_mib"]
+    assert abs(u_part - u0) < 64                     # the partial prefetch towards the CPU moved nothing
+    assert u0 - u1 >= 4 * 1024 - 64                  # the whole-allocation one released the 4 GiB
+    assert 0 < u2 - u1 <= 4 * 1024 + 64              # a block came back
+    assert u3 - u1 >= 4 * 1024 - 64 and o["same"]    # all of it, bit-exact
+
+
 def test_sigusr2_suspends_and_sigusr1_resumes_a_running_vgpu_process(cuda_dev):
     """The reference's monitor protocol (SIGUSR2 -> suspended, SIGUSR1 -> running) now also moves
     the data: while suspended the process holds (almost) no HBM; after resume it carries on."""
