@@ -1694,10 +1694,21 @@ EXPORT CUresult cuMemPrefetchAsync(CUdeviceptr p, size_t n, CUdevice d, void *st
     if (!tl_bypass && d >= 0 && !to_phys(&d)) return 101;
     return f ? f(p, n, d, stream) : 3;
 }
+/* advice about a VMM-backed allocation has nothing to act on (no fault-driven migration): accepted, ignored */
+static int vmm_backed(CUdeviceptr p) {
+    if (!g_backend_vmm || tl_bypass) return 0;
+    pthread_mutex_lock(&g_alloc_mu);
+    alloc_node_t *a = g_head;
+    while (a && !(a->vmem && p >= a->addr && p < a->addr + a->len)) a = a->next;
+    pthread_mutex_unlock(&g_alloc_mu);
+    return a != NULL;
+}
+
 EXPORT CUresult cuMemAdvise(CUdeviceptr p, size_t n, int advice, CUdevice d) {
     typedef CUresult (*fn_t)(CUdeviceptr, size_t, int, CUdevice);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuMemAdvise");
+    if (vmm_backed(p)) return 0;
     if (!tl_bypass && d >= 0 && !to_phys(&d)) return 101;
     return f ? f(p, n, advice, d) : 3;
 }
@@ -1715,6 +1726,7 @@ EXPORT CUresult cuMemAdvise_v2(CUdeviceptr p, size_t n, int advice, shim_mem_loc
     typedef CUresult (*fn_t)(CUdeviceptr, size_t, int, shim_mem_location_t);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuMemAdvise_v2");
+    if (vmm_backed(p)) return 0;
     if (!tl_bypass && !loc_to_phys(&loc)) return 101;
     return f ? f(p, n, advice, loc) : 3;
 }
