@@ -125,9 +125,9 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False,
                     procs[p].stdin.flush()
                     replies.append("sent")
                     continue
-                if op == "@poll":   # is the reply of the last @send there yet? (0.4 s of patience)
-                    import select
-                    ready, _, _ = select.select([procs[p].stdout], [], [], 0.4)
+                if op in ("@poll", "@pollready"):  # is the reply of the last @send there yet?  0.4 s of patience; @pollready
+                    import select                  # (used where a reply is expected) waits up to 5 s, so a busy machine is not a failure
+                    ready, _, _ = select.select([procs[p].stdout], [], [], 0.4 if op == "@poll" else 5.0)
                     replies.append("ready" if ready else "blocked")
                     continue
                 if op == "@recv":

@@ -432,7 +432,8 @@ def test_which_calls_park_while_the_vgpu_is_suspended(probe, parks):
     pointer queries) wait at the gate until SIGUSR1, frees and read-only queries go through — call by call as the
     reference does (wait_status_self@0x45ff5 in its hooks)."""
     env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP}
-    tr = [(0, f"alloc {M} 1"), (0, "hostalloc 4096 2"), (0, "@usr2"), (0, "@send " + probe), (0, "@poll"), (0, "@usr1"), (0, "@recv"), (0, "info")]
+    tr = [(0, f"alloc {M} 1"), (0, "hostalloc 4096 2"), (0, "@usr2"), (0, "@send " + probe), (0, "@poll" if parks else "@pollready"), (0, "@usr1"),
+          (0, "@recv"), (0, "info")]
     libs = [H.NEW_LIB] + ([H.REFERENCE_LIB] if H.have_reference() else [])
     seen = []
     for lib in libs:
