@@ -117,7 +117,7 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False,
                     import signal
                     import time
                     procs[p].send_signal(signal.SIGUSR2 if op == "@usr2" else signal.SIGUSR1)
-                    time.sleep(0.05)  # handlers only write the status word
+                    time.sleep(0.2)  # handlers only write the status word; generous for a busy machine
                     replies.append("signalled")
                     continue
                 if op.startswith("@send "):  # an op whose reply is not awaited (it may park at the suspend gate)
@@ -135,7 +135,7 @@ def run_trace(lib, trace, env_extra, nprocs=1, keep_region=True, parallel=False,
                     continue
                 if op == "@sleep":  # lets signals sent to OTHER processes be delivered before the file is looked at
                     import time
-                    time.sleep(0.15)
+                    time.sleep(0.3)
                     replies.append("slept")
                     continue
                 if op == "@kill":   # the process dies without running its exit handler (SIGKILL): its slot stays behind
