@@ -1,0 +1,102 @@
+#!/usr/bin/env python
+"""Kitchen-sink differential fuzzer for the quota path: random traces mixing every op the runner knows (device,
+managed, pitch and pinned-host allocations, frees, queries, context retain / release, the monitor's helpers, fork,
+SIGKILL, launches, live quota resizes) are played through the reference binary and the new shim; replies, OOM log
+lines, the mock driver's call log and the final cache file must be identical.  Needs /root/reference.
+
+  python scripts/quota_fuzz.py [first_seed] [last_seed]
+"""
+import math
+import os
+import random
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import quota_harness as H  # noqa: E402
+
+M = 1 << 20
+ENVS = ({}, {"MEMORY_OVERRIDE": "1"}, {"CUDA_OVERSUBSCRIBE": "true"})
+
+
+def gen(seed, nprocs=4, nops=600):
+    rng = random.Random(seed)
+    alive = set(range(nprocs))
+    live = [[] for _ in range(nprocs)]
+    tag = [1] * nprocs
+    tr = [(p, "retain 0 1") for p in range(nprocs)]
+    for _ in range(nops):
+        p = rng.choice(sorted(alive))
+        r = rng.random()
+        if r < 0.35:
+            size = int(math.exp(rng.uniform(math.log(4096), math.log(300 * M))))
+            t = tag[p]
+            tag[p] += 1
+            k = rng.random()
+            if k < 0.7:
+                tr.append((p, f"alloc {size} {t}"))
+            elif k < 0.8:
+                tr.append((p, f"managed {size} {t}"))
+            elif k < 0.9:
+                tr.append((p, f"pitch {rng.randrange(1, 60000)} {rng.randrange(1, 500)} {rng.choice([4, 8, 16])} {t}"))
+            else:
+                tr.append((p, f"hostalloc {min(size, 1 << 20)} {t}"))
+                continue
+            live[p].append(t)
+        elif r < 0.55 and live[p]:
+            tr.append((p, f"free {live[p].pop(rng.randrange(len(live[p])))}"))
+        elif r < 0.70:
+            tr.append((p, rng.choice(["info", "total 0", "nvmlmem", "@slots", "ctxdev", "ctxget"])))
+        elif r < 0.76:
+            tr.append((p, rng.choice(["release 0", "retain 0 1", "retain 0 1"])))
+        elif r < 0.84:
+            q = rng.choice(sorted(alive))
+            tr.append((p, f"libcall $pid{q} 0 {rng.randrange(0, 900) * M} set_gpu_device_memory_monitor"))
+        elif r < 0.90:
+            tr.append((p, "libcall 0 0 0 " + rng.choice(["get_gpu_memory_usage", "get_gpu_memory_monitor", "get_current_device_memory_limit",
+                                                          "get_recent_kernel"])))
+        elif r < 0.94:
+            tr.append((p, f"forkalloc {rng.randrange(1, 100) * M} {rng.randrange(2)}"))
+        elif r < 0.96 and len(alive) > 1 and p != 0:
+            tr.append((p, "@kill"))
+            alive.discard(p)
+        elif r < 0.98:
+            tr.append((p, "launch 8 128"))
+        else:
+            tr.append((p, f"libcall 0 {rng.randrange(500, 3000) * M} 0 set_current_device_memory_limit"))
+    return tr
+
+
+def differences(seed, extra, nprocs=4):
+    """-> list of human-readable differences between the two libraries on this seed (empty = identical)."""
+    env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "2g", "NVIDIA_DEVICE_MAP": "0:" + H.UUID0, "MOCK_CTX_MIB": "200", "ACTIVE_OOM_KILLER": "0", **extra}
+    tr = gen(seed, nprocs)
+    a = H.run_trace(H.REFERENCE_LIB, tr, env, nprocs)
+    b = H.run_trace(H.NEW_LIB, tr, env, nprocs)
+    out = [f"op {i} {tr[i]}: reference {a['replies'][i]!r}, new {b['replies'][i]!r}" for i in range(len(tr)) if a["replies"][i] != b["replies"][i]]
+    if a["oom"] != b["oom"]:
+        out.append("OOM log lines differ")
+    if a["calls"] != b["calls"]:
+        out.append("driver call logs differ")
+    if H.mask_region(a["region"]) != H.mask_region(b["region"]):
+        out.append("final cache files differ")
+    return out
+
+
+def main():
+    first = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+    last = int(sys.argv[2]) if len(sys.argv) > 2 else first + 10
+    H.build()
+    bad = 0
+    for seed in range(first, last):
+        for extra in ENVS:
+            d = differences(seed, extra)
+            if d:
+                bad += 1
+                print(seed, extra, d[:3])
+    print(f"seeds {first}..{last - 1} x {len(ENVS)} environments: {bad} with differences")
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

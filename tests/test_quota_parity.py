@@ -465,6 +465,19 @@ def test_odd_arguments_get_the_reference_answers(env):
     assert H.mask_region(a["region"]) == H.mask_region(b["region"])
 
 
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+@pytest.mark.parametrize("seed", [3, 17])
+def test_kitchen_sink_fuzz_against_the_reference(seed):
+    """scripts/quota_fuzz.py: every op the runner knows in one random trace (allocations of all kinds, contexts, the
+    monitor's helpers, fork, SIGKILL, launches, live quota resizes), three environments, four processes."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("quota_fuzz", os.path.join(os.path.dirname(os.path.dirname(__file__)), "scripts", "quota_fuzz.py"))
+    fuzz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fuzz)
+    for extra in fuzz.ENVS:
+        assert fuzz.differences(seed, extra) == []
+
+
 def _slots_clean(region):
     """(proc_num, no live slot holds memory).  Slots beyond proc_num may hold stale bytes: the exit
     handler moves the last slot into the leaver's and does not wipe the source (as in the reference)."""
