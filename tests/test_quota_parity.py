@@ -183,6 +183,24 @@ def test_pointer_device_ordinal_is_the_virtual_device_it_was_allocated_on():
         assert H.run_trace(H.REFERENCE_LIB, [(0, o) for o in ops], env)["replies"][-3:] == ["0 0", "0 0", "0 1"]
 
 
+def test_free_with_another_device_current():
+    """cuMemFree of a device-0 allocation while device 1's context is current: the bytes go back to device 0, where they
+    were billed.  (The reference un-bills the CURRENT device — remove_chunk@0x413dd asks cuCtxGetDevice at free time — so
+    device 0 stays charged for ever and device 1's counter wraps below zero; shown when the reference can run.)"""
+    u2 = H.UUID0[:-1] + "2"
+    env = {"MOCK_GPU_COUNT": "2", "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{u2}", "CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "CUDA_DEVICE_MEMORY_LIMIT_1": "1g",
+           "MOCK_CTX_MIB": "200"}
+    C2 = 200 << 20
+    ops = ["retain 0 1", "retain 1 2", "ctxset 1", f"alloc {100 << 20} 1", "ctxset 2", "free 1", "@slots", "info", "ctxset 1", "info"]
+    rep = H.run_trace(H.NEW_LIB, [(0, o) for o in ops], env)["replies"]
+    assert rep[6] == f"n=1 p0:1:1 d0={C2}/0/0/{C2} d1={C2}/0/0/{C2}"
+    assert rep[7] == rep[9] == f"0 {(1 << 30) - C2} {1 << 30}"
+    if H.have_reference():
+        ref = H.run_trace(H.REFERENCE_LIB, [(0, o) for o in ops], env)["replies"]
+        wrapped = (1 << 64) - (100 << 20)
+        assert ref[6] == f"n=1 p0:1:1 d0={C2}/0/{100 << 20}/{C2 + (100 << 20)} d1={C2}/0/{wrapped}/{C2 - (100 << 20)}"
+
+
 def test_nvml_shows_a_shared_gpu_as_the_sum_of_its_vgpus():
     ops = ["retain 0 1", "retain 1 2", "ctxset 2", f"alloc {100 << 20} 1", "nvmlmem"]
     rep = H.run_trace(H.NEW_LIB, [(0, o) for o in ops], SHARED)["replies"]
