@@ -484,8 +484,8 @@ def test_odd_arguments_get_the_reference_answers(env):
 
 
 @pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
-@pytest.mark.parametrize("seed", [3, 17])
-def test_kitchen_sink_fuzz_against_the_reference(seed):
+@pytest.mark.parametrize("seed,ndev", [(3, 1), (17, 1), (5, 2), (7, 2)])
+def test_kitchen_sink_fuzz_against_the_reference(seed, ndev):
     """scripts/quota_fuzz.py: every op the runner knows in one random trace (allocations of all kinds, contexts, the
     monitor's helpers, fork, SIGKILL, launches, live quota resizes), three environments, four processes."""
     import importlib.util
@@ -493,7 +493,7 @@ def test_kitchen_sink_fuzz_against_the_reference(seed):
     fuzz = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(fuzz)
     for extra in fuzz.ENVS:
-        assert fuzz.differences(seed, extra) == []
+        assert fuzz.differences(seed, extra, ndev=ndev) == []
 
 
 def _slots_clean(region):
