@@ -300,7 +300,11 @@ void region_set_hostpid(int hostpid) {
     if (!g_reg) return;
     region_lock();
     vgpu_proc_slot_t *s = my_slot();
-    if (s) s->hostpid = hostpid;
+    if (s) {
+        s->hostpid = hostpid;
+        /* set_host_pid@0x455d8 also wipes what a monitor had reported for whoever held this slot before (loop @0x456d1) */
+        memset(s->monitorused, 0, sizeof(s->monitorused));
+    }
     region_unlock();
 }
 

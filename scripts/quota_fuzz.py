@@ -19,17 +19,29 @@ M = 1 << 20
 ENVS = ({}, {"MEMORY_OVERRIDE": "1"}, {"CUDA_OVERSUBSCRIBE": "true"})
 
 
-def gen(seed, nprocs=4, nops=600, ndev=1):
+def gen(seed, nprocs=4, nops=600, ndev=1, nlate=0):
+    """`nlate` of the processes (the highest numbers) join at random points: they claim a slot in a file with history."""
     rng = random.Random(seed)
-    alive = set(range(nprocs))
+    early = nprocs - nlate
+    alive = set(range(early))
     live = [[] for _ in range(nprocs)]
     tag = [1] * nprocs
-    tr = [(p, "retain 0 1") for p in range(nprocs)]
-    if ndev == 2:  # context tag d+1 = primary context of device d; every process starts on device 0
-        tr += [(p, "retain 1 2") for p in range(nprocs)] + [(p, "ctxset 1") for p in range(nprocs)]
+
+    def prologue(p):
+        out = [(p, "retain 0 1")]
+        if ndev == 2:  # context tag d+1 = primary context of device d; every process starts on device 0
+            out += [(p, "retain 1 2"), (p, "ctxset 1")]
+        return out
+
+    tr = [op for p in range(early) for op in prologue(p)]
+    joins = {p: rng.randrange(nops // 5, 4 * nops // 5) for p in range(early, nprocs)}
     cur = [0] * nprocs   # current device of each process
     where = [dict() for _ in range(nprocs)]
-    for _ in range(nops):
+    for step in range(nops):
+        for q, when in joins.items():
+            if when == step:
+                tr += [(q, "@start")] + prologue(q)
+                alive.add(q)
         p = rng.choice(sorted(alive))
         r = rng.random()
         if ndev == 2 and rng.random() < 0.08:
@@ -83,12 +95,12 @@ def gen(seed, nprocs=4, nops=600, ndev=1):
     return tr
 
 
-def differences(seed, extra, nprocs=4, ndev=1):
+def differences(seed, extra, nprocs=4, ndev=1, nlate=0):
     """-> list of human-readable differences between the two libraries on this seed (empty = identical)."""
     env = {"CUDA_DEVICE_MEMORY_LIMIT_0": "2g", "NVIDIA_DEVICE_MAP": "0:" + H.UUID0, "MOCK_CTX_MIB": "200", "ACTIVE_OOM_KILLER": "0", **extra}
     if ndev == 2:
         env.update({"MOCK_GPU_COUNT": "2", "CUDA_DEVICE_MEMORY_LIMIT_1": "1g", "NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{H.UUID0[:-1]}2"})
-    tr = gen(seed, nprocs, ndev=ndev)
+    tr = gen(seed, nprocs, ndev=ndev, nlate=nlate)
     a = H.run_trace(H.REFERENCE_LIB, tr, env, nprocs)
     b = H.run_trace(H.NEW_LIB, tr, env, nprocs)
     out = [f"op {i} {tr[i]}: reference {a['replies'][i]!r}, new {b['replies'][i]!r}" for i in range(len(tr)) if a["replies"][i] != b["replies"][i]]
@@ -110,13 +122,13 @@ def main():
     H.build()
     bad = 0
     for seed in range(first, last):
-        for ndev in (1, 2):
+        for ndev, nprocs, nlate in ((1, 4, 0), (2, 4, 0), (1, 6, 2)):
             for extra in ENVS:
-                d = differences(seed, extra, ndev=ndev)
+                d = differences(seed, extra, nprocs=nprocs, ndev=ndev, nlate=nlate)
                 if d:
                     bad += 1
-                    print(seed, ndev, extra, d[:3])
-    print(f"seeds {first}..{last - 1} x {len(ENVS)} environments x 1 and 2 devices: {bad} with differences")
+                    print(seed, (ndev, nprocs, nlate), extra, d[:3])
+    print(f"seeds {first}..{last - 1} x {len(ENVS)} environments x (1 device, 2 devices, 2 late joiners): {bad} with differences")
     return 1 if bad else 0
 
 

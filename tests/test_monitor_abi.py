@@ -160,3 +160,14 @@ def test_recent_kernel_is_the_activity_mark_and_the_monitors_brake():
     rep = both([(0, "libcall 0 0 0 set_recent_kernel"), (0, "launch 4 128"), (0, "libcall 0 0 0 get_recent_kernel"),
                 (0, "libcall -1 0 0 set_recent_kernel"), (0, "launch 4 128"), (0, "libcall 0 0 0 get_recent_kernel")], unseen, 1)
     assert rep == ["0 0", "0", "0 0", "0 0", "0", "0 4294967295"]
+
+
+def test_a_new_tenant_of_a_slot_does_not_inherit_the_monitor_figure():
+    """set_host_pid@0x455d8 wipes monitorused[] of the slot it writes the host pid into: a process that takes over the
+    slot of one that died starts with nothing reported."""
+    tr = [(0, "retain 0 1"), (1, "retain 0 1"), (0, f"libcall $pid1 0 {400 * M} set_gpu_device_memory_monitor"), (0, "@slots"), (1, "@kill"),
+          (0, f"alloc {1000 * M} 1"),                       # over the limit: the sweep removes the dead process, then it fits
+          (2, "@start"), (2, "retain 0 1"), (0, "@slots"), (0, "libcall 0 0 0 get_gpu_memory_monitor")]
+    rep = both(tr, ENV, 3)
+    assert rep[3].endswith(f"| p1:1:1 d0={C}/0/0/{C} mon={400 * M}")
+    assert rep[8].endswith(f"| p2:1:1 d0={C}/0/0/{C}") and rep[9] == "0 0"
