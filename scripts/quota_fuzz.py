@@ -74,7 +74,7 @@ def gen(seed, nprocs=4, nops=600, ndev=1, nlate=0):
                 tr.append((p, f"ctxset {cur[p] + 1}"))
             tr.append((p, f"free {t}"))
         elif r < 0.70:
-            q = rng.choice(["info", "total 0", "nvmlmem", "@slots", "ctxdev", "ctxget", "devcount", "ptr", "host", "async", "vmm", "ctx"])
+            q = rng.choice(["info", "total 0", "nvmlmem", "@slots", "ctxdev", "ctxget", "devcount", "ptr", "host", "async", "vmm", "ctx", "sig"])
             t = tag[p]
             if q == "ptr":
                 q = rng.choice(["ptrattrs", "ptrdev"]) + f" {rng.choice(live[p]) if live[p] else 0}"
@@ -89,6 +89,9 @@ def gen(seed, nprocs=4, nops=600, ndev=1, nlate=0):
             elif q == "vmm":        # VMM API: outside the quota in both libraries
                 tag[p] += 2
                 tr += [(p, f"vcreate {rng.randrange(1, 32) * 2 * M} {t}"), (p, f"vmap {t} {t + 1}"), (p, f"vrelease {t}"), (p, f"vunmap {t + 1}")]
+                continue
+            elif q == "sig":        # suspended for a moment: only calls that do not park at the gate in between
+                tr += [(p, "@usr2"), (p, "info"), (p, "@slots"), (p, "total 0"), (p, "nvmlmem"), (p, "@usr1"), (p, "@slots")]
                 continue
             elif q == "ctx":        # a context of the application's own on the current device, entered and left again
                 tag[p] += 1
