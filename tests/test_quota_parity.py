@@ -484,7 +484,7 @@ def test_odd_arguments_get_the_reference_answers(env):
 
 
 @pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
-@pytest.mark.parametrize("seed,ndev,nprocs,nlate", [(3, 1, 4, 0), (17, 1, 4, 0), (5, 2, 4, 0), (7, 2, 4, 0), (9, 1, 6, 2), (4, 1, 6, 2)])
+@pytest.mark.parametrize("seed,ndev,nprocs,nlate", [(3, 1, 4, 0), (7, 2, 4, 0), (9, 1, 6, 2)])
 def test_kitchen_sink_fuzz_against_the_reference(seed, ndev, nprocs, nlate):
     """scripts/quota_fuzz.py: every op the runner knows in one random trace (allocations of all kinds, contexts, the
     monitor's helpers, fork, SIGKILL, launches, live quota resizes), three environments, four processes."""
