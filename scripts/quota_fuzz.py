@@ -16,7 +16,7 @@ sys.path.insert(0, ROOT)
 from oracle import quota_harness as H  # noqa: E402
 
 M = 1 << 20
-ENVS = ({}, {"MEMORY_OVERRIDE": "1"}, {"CUDA_OVERSUBSCRIBE": "true"})
+ENVS = ({}, {"MEMORY_OVERRIDE": "1"}, {"CUDA_OVERSUBSCRIBE": "true", "CUDA_DEVICE_SM_LIMIT": "40", "CUDA_TASK_PRIORITY": "0"})
 
 
 def gen(seed, nprocs=4, nops=600, ndev=1, nlate=0):
