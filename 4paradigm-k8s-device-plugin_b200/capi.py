@@ -44,7 +44,8 @@ class Mount(C.Structure):
 
 class PluginCfg(C.Structure):
     _fields_ = [("split", C.c_uint32), ("mem_scaling", C.c_double), ("cores_scaling", C.c_double),
-                ("id_strategy", C.c_int32), ("list_strategy", C.c_int32), ("pcibusfile", C.c_char * PATH_LEN)]
+                ("id_strategy", C.c_int32), ("list_strategy", C.c_int32), ("pcibusfile", C.c_char * PATH_LEN),
+                ("emit_partition_index", C.c_uint32)]
 
 
 class Cksum(C.Structure):
@@ -70,7 +71,7 @@ class VmemStats(C.Structure):
     _fields_ = [("chunks_total", C.c_uint64), ("chunks_resident", C.c_uint64), ("chunks_spilled", C.c_uint64),
                 ("resident_limit", C.c_uint64), ("tier_slots", C.c_uint64), ("evictions", C.c_uint64),
                 ("fetches", C.c_uint64), ("checksum_failures", C.c_uint64), ("evict_ms", C.c_double), ("fetch_ms", C.c_double),
-                ("evictions_peer", C.c_uint64), ("evictions_host", C.c_uint64)]
+                ("evictions_peer", C.c_uint64), ("evictions_host", C.c_uint64), ("restore_retries", C.c_uint64)]
 
 
 class SmPartition(C.Structure):
@@ -102,13 +103,16 @@ SIGNATURES = {
     "vgpu_slab_alloc": (_i, [_i, _i, _i, _sz, _pp(_vp)]),
     "vgpu_slab_free": (_i, [_i, _i, _i, _vp]),
     "vgpu_calibrate": (_i, [_i, _i, _i, _sz]),
+    "vgpu_link_rate": (_i, [_i, _i, _i, _sz, _pp(C.c_double), _pp(C.c_double)]),
     "vgpu_policy_get": (_i, [_i, _sz]),
     "vgpu_policy_set": (_i, [_i, _sz, _i]),
+    "vgpu_policy_set_grid": (_i, [_i, _u]),
     "vgpu_vmem_create": (_i, [_i, _u64, _u64, _i, _i, _u64, _pp(_vp)]),
     "vgpu_vmem_create_tiered": (_i, [_i, _u64, _u64, _i, _u64, _u64, _pp(_vp)]),
     "vgpu_vmem_base": (_i, [_vp, _pp(_vp)]),
     "vgpu_vmem_ensure": (_i, [_vp, _u64, _u64]),
     "vgpu_vmem_evict": (_i, [_vp, _u64, _u64]),
+    "vgpu_vmem_locate": (_i, [_vp, _u64, _pp(_i), _pp(_vp)]),
     "vgpu_vmem_stats": (_i, [_vp, _pp(VmemStats)]),
     "vgpu_vmem_destroy": (_i, [_vp]),
     "vgpu_memtest_fill": (_i, [_vp, _u64, _i, _u64, _u64, _vp]),
@@ -118,6 +122,7 @@ SIGNATURES = {
     "vgpu_sm_partition_create": (_i, [_i, _u, _u, _pp(SmPartition)]),
     "vgpu_sm_partition_create_ex": (_i, [_i, _u, _u, _u, _pp(SmPartition)]),
     "vgpu_sm_partition_destroy": (_i, [_pp(SmPartition), _u]),
+    "vgpu_sm_probe": (_i, [_vp, _pp(_u64), _pp(_u)]),
 }
 for _name, (_res, _args) in SIGNATURES.items():
     _fn = getattr(lib, _name)  # AttributeError here == library does not export what the header declares

@@ -1026,8 +1026,8 @@ static CUresult do_create(void *a) {
  * driver's granule so the vGPU never exceeds its share); its CUcontext is handed to the
  * application wherever it asks for the device's primary context, so the runtime API and
  * every library on top of it run inside the partition.  Which of the disjoint partitions a
- * container gets: VGPU_SM_PARTITION_INDEX if the plugin provides it, else a hash of the
- * container's shared-cache path (Contract A carries no vGPU index into the pod).
+ * container gets: VGPU_SM_PARTITION_INDEX[_<dev>] from the plugin (vgpu_plugin_cfg_t.emit_partition_index); without it
+ * the placement is not coordinated (Contract A carries no vGPU index into the pod) and the shim says so.
  * VGPU_SM_PARTITION=off disables the cap. */
 typedef struct {
     int type;
@@ -1077,13 +1077,19 @@ static int sm_policy_disabled(void) {
     return p && (strcmp(p, "DISABLE") == 0 || strcmp(p, "disable") == 0);
 }
 
-static unsigned partition_pick(unsigned nb) {
-    const char *e = getenv("VGPU_SM_PARTITION_INDEX");
+/* Which of the nb disjoint groups is this vGPU's?  VGPU_SM_PARTITION_INDEX_<dev> (emitted by the plugin when
+ * vgpu_plugin_cfg_t.emit_partition_index is set: the i of "<UUID>-<i>"), else VGPU_SM_PARTITION_INDEX for all
+ * devices.  Without either nothing in the pod says which vGPU of the GPU this is (Contract A carries no index),
+ * and guessing would put containers on top of each other while claiming isolation: say so and take group 0. */
+static unsigned partition_pick(int dev, unsigned nb) {
+    char name[64];
+    snprintf(name, sizeof(name), "VGPU_SM_PARTITION_INDEX_%d", dev);
+    const char *e = getenv(name);
+    if (!e || !*e) e = getenv("VGPU_SM_PARTITION_INDEX");
     if (e && *e) return (unsigned)strtoul(e, NULL, 0) % nb;
-    const char *path = getenv("CUDA_DEVICE_MEMORY_SHARED_CACHE");
-    unsigned h = 2166136261u;
-    for (const char *c = path ? path : ""; *c; ++c) h = (h ^ (unsigned char)*c) * 16777619u;
-    return h % nb;
+    SHIM_ERR("device %d: no VGPU_SM_PARTITION_INDEX: SM partition placement is NOT coordinated with the other vGPUs "
+             "of this GPU (all such containers share group 0); the size of the cap holds, the isolation does not", dev);
+    return 0;
 }
 
 static CUcontext green_ctx_for(CUdevice dev) {
@@ -1117,7 +1123,7 @@ static CUcontext green_ctx_for(CUdevice dev) {
                 nb = 0;
             }
             if (nb) {
-                unsigned k = partition_pick(nb);
+                unsigned k = partition_pick(dev, nb);
                 CUdevResourceDesc desc;
                 CUgreenCtx g;
                 CUcontext c;

@@ -8,6 +8,9 @@
 //   vgpuvalidator --memtest [--gib G | --bytes N] [--patterns walking,random] [--random-passes K]
 //                 [--device i] [--seed S]
 //   vgpuvalidator --roundtrip [--chunks N]      spill -> erase -> restore self-test (host tier)
+//   vgpuvalidator --smids                       the SMs this vGPU's kernels run on (its green-context partition)
+// Its kernels use no thread-block clusters, so under the shim it asks for the SM-granular partition split
+// (VGPU_SM_PARTITION_GRANULE=fine unless the pod sets the variable itself): 10 % of 148 SMs = 14 instead of 8.
 // exit code: 0 clean, 1 mismatches found, 2 usage or CUDA error.
 #include <cstdint>
 #include <cstdio>
@@ -20,12 +23,14 @@
 static int usage() {
     fprintf(stderr,
             "usage: vgpuvalidator --memtest [--gib G|--bytes N] [--patterns walking,random] [--random-passes K] [--device i] [--seed S]\n"
-            "       vgpuvalidator --roundtrip [--chunks N] [--device i]\n");
+            "       vgpuvalidator --roundtrip [--chunks N] [--device i]\n"
+            "       vgpuvalidator --smids [--device i]\n");
     return 2;
 }
 
 int main(int argc, char **argv) {
-    bool memtest = false, roundtrip = false;
+    bool memtest = false, roundtrip = false, smids = false;
+    setenv("VGPU_SM_PARTITION_GRANULE", "fine", 0);  // read by the shim when it forms this process's partition
     uint64_t bytes = 1ull << 30, random_passes = 4, seed = 0, chunks = 64;
     unsigned patterns = 3;
     int device = 0;
@@ -40,6 +45,7 @@ int main(int argc, char **argv) {
         };
         if (a == "--memtest") memtest = true;
         else if (a == "--roundtrip") roundtrip = true;
+        else if (a == "--smids") smids = true;
         else if (a == "--gib") bytes = (uint64_t)(atof(next("--gib")) * (double)(1ull << 30));
         else if (a == "--bytes") bytes = strtoull(next("--bytes"), nullptr, 0);
         else if (a == "--random-passes") random_passes = strtoull(next("--random-passes"), nullptr, 0);
@@ -53,7 +59,26 @@ int main(int argc, char **argv) {
             if (p.find("random") != std::string::npos) patterns |= 1u << VGPU_PAT_RANDOM;
         } else return usage();
     }
-    if (memtest == roundtrip) return usage();
+    if ((int)memtest + (int)roundtrip + (int)smids != 1) return usage();
+    if (smids) {
+        void *one = nullptr;  // any allocation brings up the device's context (the shim binds the partition there)
+        uint64_t mask[4] = {0, 0, 0, 0};
+        unsigned count = 0;
+        if (vgpu_slab_alloc(VGPU_TIER_LOCAL, device, -1, 4096, &one) || vgpu_sm_probe(nullptr, mask, &count)) {
+            fprintf(stderr, "vgpuvalidator: %s\n", vgpu_last_error());
+            return 2;
+        }
+        vgpu_slab_free(VGPU_TIER_LOCAL, device, -1, one);
+        printf("{\"device\": %d, \"sm_count\": %u, \"sm_ids\": [", device, count);
+        bool first = true;
+        for (unsigned sm = 0; sm < 256; ++sm)
+            if (mask[sm >> 6] >> (sm & 63) & 1) {
+                printf("%s%u", first ? "" : ", ", sm);
+                first = false;
+            }
+        printf("]}\n");
+        return 0;
+    }
     if (memtest) {
         bytes &= ~7ull;
         vgpu_memtest_result_t r;

@@ -37,9 +37,6 @@ struct Scratch {
     vgpu_memtest_dev_result_t *mt_host = nullptr;  // pinned: a pageable D2H copy would hold the
                                                    // context lock until the stream drains and
                                                    // serialise the other vGPUs' host threads
-    vgpu_cksum_t *cksum = nullptr;  // staging for the host-buffer forms
-    size_t cksum_cap = 0;
-    vgpu_restore_result_t *rr = nullptr;
 };
 
 struct DevState {
@@ -97,22 +94,6 @@ int get_mt(int dev, void *stream, vgpu_memtest_dev_result_t **out, vgpu_memtest_
     return VGPU_OK;
 }
 
-int get_stage(int dev, void *stream, size_t nchunks, vgpu_cksum_t **ck, vgpu_restore_result_t **rr) {
-    std::lock_guard<std::mutex> lk(g_mu);
-    Scratch &s = g_dev[dev].scratch[stream];
-    if (s.cksum_cap < nchunks) {
-        if (s.cksum) VGPU_CUDA(cudaFree(s.cksum));
-        s.cksum = nullptr;
-        size_t cap = std::max<size_t>(4096, nchunks);
-        VGPU_CUDA(cudaMalloc(&s.cksum, cap * sizeof(vgpu_cksum_t)));
-        s.cksum_cap = cap;
-    }
-    if (!s.rr) VGPU_CUDA(cudaMalloc(&s.rr, sizeof(*s.rr)));
-    *ck = s.cksum;
-    *rr = s.rr;
-    return VGPU_OK;
-}
-
 // ---- AUTO policy ----------------------------------------------------------
 // policy[tier] is a list of (min_chunks, variant), highest matching min wins.
 // Defaults come from profiles/ (first GPU measurements); vgpu_calibrate
@@ -143,18 +124,37 @@ int policy_lookup(int tier, size_t nchunks) {
 constexpr int kLdstU = 4;                   // 4 x 32 B per thread in flight => 32 KiB tiles
 constexpr int kTmaTile = 32768, kTmaStages = 2, kTmaLag = 1, kTmaConsumerWarps = 4;  // 64 KiB ring, 3 CTAs/SM: best of the shapes swept
 constexpr int kTmaGridMult = 16;  // CTAs per launch = resident CTAs x 16 (grid-stride over the rest)
+// link tiers: CTAs per launch (see grid_cap).
+// Measured on B200 beside ten busy memtest partitions (profiles/r02_concurrency.md): the host tier is at the PCIe rate
+// from 16-32 CTAs on (51-52 GB/s) and from 64 CTAs on it takes the SMs from the tenants (memtest 7.0 -> 3.2 TB/s);
+// the peer tier needs the wide grid for the last 2 % of NVLink (592 CTAs: 696 / 736 GB/s, 4736: 714 / 781).
+constexpr uint64_t kGridHostLdst = 32, kGridHostTma = 16, kGridPeerLdst = 4736, kGridPeerTma = 7104;
 
-// CTAs per launch of the LD/ST copy variant: a grid-stride loop over 32 KiB tiles with
-// 32 CTAs per SM (4 waves of the 8 resident).  Unlike the write-only / read-only memtest
-// kernels, the mixed read+write copy is FASTER with some persistence: 3276 GB/s payload at
-// 32/SM vs 2520 GB/s with one tile per CTA (4096 chunks, profiles/r01_memtest_sweeps.md).
-// VGPU_XFER_CTAS_PER_SM overrides for experiments.
-uint64_t ldst_grid_cap(int sms) {
+// CTAs per launch.  Local tier (HBM -> HBM): a grid-stride loop over 32 KiB tiles with 32 CTAs per SM (4 waves
+// of the 8 resident).  Unlike the write-only / read-only memtest kernels, the mixed read+write copy is FASTER with
+// some persistence: 3276 GB/s payload at 32/SM vs 2520 GB/s with one tile per CTA (4096 chunks,
+// profiles/r01_memtest_sweeps.md).  Link tiers (peer HBM over NVLink, pinned host over PCIe) are bound by the link,
+// not by the SMs: their grid only has to cover the link's bandwidth-delay product, and every CTA beyond that just
+// sits on an SM waiting for the link — on SMs that belong to the tenants' partitions when the transfer runs in
+// the primary context (a whole-GPU grid of host-tier CTAs halved a concurrent memtest, profiles/r02_concurrency.md).
+// vgpu_policy_set_grid overrides per tier; VGPU_XFER_CTAS_PER_SM overrides the local tier for experiments.
+unsigned g_grid_override[3] = {0, 0, 0};  // CTAs per launch per tier, 0 = default (under g_mu)
+
+uint64_t grid_cap(int tier, int variant, int sms) {
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (g_grid_override[tier]) return g_grid_override[tier];
+    }
     static const long cap = [] {
         const char *e = getenv("VGPU_XFER_CTAS_PER_SM");
         return e ? atol(e) : 0L;
     }();
-    return (uint64_t)sms * (uint64_t)(cap > 0 ? cap : 32);
+    const uint64_t tma_local = (uint64_t)sms * 3 * kTmaGridMult;  // 3 resident CTAs per SM (shared-memory bound)
+    switch (tier) {
+        case VGPU_TIER_HOST: return variant == VGPU_XFER_TMA ? kGridHostTma : kGridHostLdst;
+        case VGPU_TIER_PEER: return variant == VGPU_XFER_TMA ? kGridPeerTma : kGridPeerLdst;
+        default: return variant == VGPU_XFER_TMA ? tma_local : (uint64_t)sms * (uint64_t)(cap > 0 ? cap : 32);
+    }
 }
 
 bool aligned32(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 31u) == 0; }
@@ -240,7 +240,7 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
         constexpr uint32_t tile = LdstTile<kLdstU>::bytes;
         a.tiles_per_chunk = (uint32_t)((chunk_bytes + tile - 1) / tile);
         const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
-        const unsigned grid = (unsigned)std::min<uint64_t>(total, ldst_grid_cap(sms));
+        const unsigned grid = (unsigned)std::min<uint64_t>(total, grid_cap(copy ? tier : VGPU_TIER_LOCAL, VGPU_XFER_LDST, sms));
         if (copy) k_xfer_ldst<kLdstU, true><<<grid, kXfThreads, 0, st>>>(a);
         else k_xfer_ldst<kLdstU, false><<<grid, kXfThreads, 0, st>>>(a);
     } else {  // VGPU_XFER_TMA
@@ -249,13 +249,16 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
         constexpr size_t smem = (size_t)kTmaTile * kTmaStages;
         constexpr int threads = 32 * (kTmaConsumerWarps + 1);
         auto kfn = k_xfer_tma<kTmaTile, kTmaStages, kTmaLag, kTmaConsumerWarps, true>;
-        static bool attr_done[kMaxDev] = {false};
-        if (!attr_done[dev]) {
-            VGPU_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr_done[dev] = true;
+        {
+            static bool attr_done[kMaxDev] = {false};  // per device, under g_mu: callers come in from several host threads
+            std::lock_guard<std::mutex> lk(g_mu);
+            if (!attr_done[dev]) {
+                VGPU_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                attr_done[dev] = true;
+            }
         }
-        constexpr unsigned per_sm = (unsigned)((220 * 1024) / (smem + 1024));  // resident CTAs per SM (shared memory bound)
-        const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * per_sm * kTmaGridMult);
+        static_assert((220 * 1024) / (smem + 1024) == 3, "grid_cap assumes 3 resident CTAs per SM");
+        const unsigned grid = (unsigned)std::min<uint64_t>(total, grid_cap(tier, VGPU_XFER_TMA, sms));
         kfn<<<grid, threads, smem, st>>>(a);
     }
     VGPU_CUDA(cudaGetLastError());
@@ -290,6 +293,7 @@ struct PullCtx {
     cudaEvent_t done = nullptr;     // recorded on the peer stream
 };
 std::map<std::pair<int, int>, PullCtx> g_pull;  // (this device, peer device)
+std::mutex g_pull_mu;
 
 int pull_spill(const void *src, void *dst, const uint32_t *src_slot, const uint32_t *dst_slot, size_t nchunks,
                size_t chunk_bytes, vgpu_cksum_t *cksum, void *stream) {
@@ -302,22 +306,31 @@ int pull_spill(const void *src, void *dst, const uint32_t *src_slot, const uint3
         return fail(VGPU_E_INVAL, "VGPU_XFER_PULL needs a destination slab in another GPU's memory");
     PullCtx *pc;
     {
-        std::lock_guard<std::mutex> lk(g_mu);
+        // one-time set-up per (device, peer) pair, under the lock: the entry may be reached from several host threads
+        std::lock_guard<std::mutex> lk(g_pull_mu);
         pc = &g_pull[{dev, peer}];
-    }
-    if (!pc->stream) {
-        VGPU_CUDA(cudaEventCreateWithFlags(&pc->ready, cudaEventDisableTiming));
-        VGPU_CUDA(cudaSetDevice(peer));
-        cudaError_t e = cudaDeviceEnablePeerAccess(dev, 0);  // the peer must be able to read our HBM
-        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
-        else if (e != cudaSuccess) {
+        if (!pc->stream) {
+            PullCtx fresh;
+            VGPU_CUDA(cudaEventCreateWithFlags(&fresh.ready, cudaEventDisableTiming));
+            cudaError_t e = cudaSetDevice(peer);
+            if (e == cudaSuccess) {
+                e = cudaDeviceEnablePeerAccess(dev, 0);  // the peer must be able to read our HBM
+                if (e == cudaErrorPeerAccessAlreadyEnabled) {
+                    cudaGetLastError();  // clear the sticky "already enabled"
+                    e = cudaSuccess;
+                }
+            }
+            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&fresh.stream, cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&fresh.done, cudaEventDisableTiming);
             cudaSetDevice(dev);
-            return fail(VGPU_E_CUDA, "cudaDeviceEnablePeerAccess(%d) from %d: %s", dev, peer, cudaGetErrorString(e));
+            if (e != cudaSuccess) {
+                if (fresh.stream) cudaStreamDestroy(fresh.stream);
+                if (fresh.done) cudaEventDestroy(fresh.done);
+                cudaEventDestroy(fresh.ready);
+                return fail(VGPU_E_CUDA, "pull set-up %d <- %d: %s", peer, dev, cudaGetErrorString(e));
+            }
+            *pc = fresh;
         }
-        e = cudaStreamCreateWithFlags(&pc->stream, cudaStreamNonBlocking);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&pc->done, cudaEventDisableTiming);
-        cudaSetDevice(dev);
-        if (e != cudaSuccess) return fail(VGPU_E_CUDA, "pull stream: %s", cudaGetErrorString(e));
     }
     VGPU_CUDA(cudaEventRecord(pc->ready, static_cast<cudaStream_t>(stream)));
     VGPU_CUDA(cudaSetDevice(peer));
@@ -367,23 +380,62 @@ static int pin_if_needed(const void *host, size_t bytes, bool *registered) {
     return VGPU_OK;
 }
 
+// The host-buffer calls run on a stream of their own (non-blocking, one per device) and stage checksums and the
+// result block through pinned memory: on the legacy stream, with a pageable read-back, the call would hold the
+// context lock for the length of the transfer and stall every other host thread's launches (measured: a memtest
+// running beside it in four threads lost a third of its rate).  Calls on one device are serialised.
+namespace {
+struct HostIo {
+    std::mutex mu;
+    cudaStream_t st = nullptr;
+    vgpu_cksum_t *d_ck = nullptr, *h_ck = nullptr;
+    size_t cap = 0;
+    vgpu_restore_result_t *d_rr = nullptr, *h_rr = nullptr;
+};
+HostIo g_hio[kMaxDev];
+
+int hio_prepare(HostIo &h, size_t nchunks) {
+    if (!h.st) VGPU_CUDA(cudaStreamCreateWithFlags(&h.st, cudaStreamNonBlocking));
+    if (!h.d_rr) VGPU_CUDA(cudaMalloc(&h.d_rr, sizeof(*h.d_rr)));
+    if (!h.h_rr) VGPU_CUDA(cudaHostAlloc(&h.h_rr, sizeof(*h.h_rr), cudaHostAllocDefault));
+    if (h.cap < nchunks) {
+        VGPU_CUDA(cudaStreamSynchronize(h.st));
+        if (h.d_ck) cudaFree(h.d_ck);
+        if (h.h_ck) cudaFreeHost(h.h_ck);
+        h.d_ck = h.h_ck = nullptr;
+        h.cap = 0;
+        const size_t cap = std::max<size_t>(4096, nchunks);
+        VGPU_CUDA(cudaMalloc(&h.d_ck, cap * sizeof(vgpu_cksum_t)));
+        VGPU_CUDA(cudaHostAlloc(&h.h_ck, cap * sizeof(vgpu_cksum_t), cudaHostAllocDefault));
+        h.cap = cap;
+    }
+    return VGPU_OK;
+}
+}  // namespace
+
 int vgpu_spill_to_host(int variant, int device, const void *d_src, void *host, size_t nchunks,
                        size_t chunk_bytes, vgpu_cksum_t *h_cksum) {
     if (!host || !h_cksum) return fail(VGPU_E_INVAL, "null host pointer");
+    if (device < 0 || device >= kMaxDev) return fail(VGPU_E_INVAL, "device %d out of range", device);
+    if (nchunks == 0) return VGPU_OK;
     VGPU_CUDA(cudaSetDevice(device));
+    HostIo &h = g_hio[device];
+    std::lock_guard<std::mutex> lk(h.mu);
+    if (int rc = hio_prepare(h, nchunks)) return rc;
     bool reg = false;
     if (int rc = pin_if_needed(host, nchunks * chunk_bytes, &reg)) return rc;
     void *h_dev = nullptr;
-    vgpu_cksum_t *ck;
-    vgpu_restore_result_t *rr;
     int rc = VGPU_OK;
     cudaError_t e = cudaHostGetDevicePointer(&h_dev, host, 0);
     if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaHostGetDevicePointer: %s", cudaGetErrorString(e));
-    if (!rc) rc = get_stage(device, nullptr, nchunks, &ck, &rr);
-    if (!rc) rc = vgpu_spill(variant, VGPU_TIER_HOST, d_src, h_dev, nullptr, nullptr, nchunks, chunk_bytes, ck, nullptr);
+    if (!rc) rc = vgpu_spill(variant, VGPU_TIER_HOST, d_src, h_dev, nullptr, nullptr, nchunks, chunk_bytes, h.d_ck, h.st);
     if (!rc) {
-        e = cudaMemcpy(h_cksum, ck, nchunks * sizeof(vgpu_cksum_t), cudaMemcpyDeviceToHost);  // syncs stream 0
-        if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaMemcpy cksum: %s", cudaGetErrorString(e));
+        e = cudaMemcpyAsync(h.h_ck, h.d_ck, nchunks * sizeof(vgpu_cksum_t), cudaMemcpyDeviceToHost, h.st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h.st);
+        if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "spill to host: %s", cudaGetErrorString(e));
+        else memcpy(h_cksum, h.h_ck, nchunks * sizeof(vgpu_cksum_t));
+    } else {
+        cudaStreamSynchronize(h.st);
     }
     if (reg) cudaHostUnregister(host);
     return rc;
@@ -392,27 +444,34 @@ int vgpu_spill_to_host(int variant, int device, const void *d_src, void *host, s
 int vgpu_restore_from_host(int variant, int device, const void *host, void *d_dst, size_t nchunks,
                            size_t chunk_bytes, const vgpu_cksum_t *h_expect, uint64_t *bad_chunks) {
     if (!host || !h_expect || !bad_chunks) return fail(VGPU_E_INVAL, "null host pointer");
+    if (device < 0 || device >= kMaxDev) return fail(VGPU_E_INVAL, "device %d out of range", device);
+    *bad_chunks = 0;
+    if (nchunks == 0) return VGPU_OK;
     VGPU_CUDA(cudaSetDevice(device));
+    HostIo &h = g_hio[device];
+    std::lock_guard<std::mutex> lk(h.mu);
+    if (int rc = hio_prepare(h, nchunks)) return rc;
     bool reg = false;
     if (int rc = pin_if_needed(host, nchunks * chunk_bytes, &reg)) return rc;
     void *h_dev = nullptr;
-    vgpu_cksum_t *ck;
-    vgpu_restore_result_t *rr;
-    vgpu_restore_result_t hres{};
     int rc = VGPU_OK;
     cudaError_t e = cudaHostGetDevicePointer(&h_dev, const_cast<void *>(host), 0);
     if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaHostGetDevicePointer: %s", cudaGetErrorString(e));
-    if (!rc) rc = get_stage(device, nullptr, nchunks, &ck, &rr);
     if (!rc) {
-        e = cudaMemcpyAsync(ck, h_expect, nchunks * sizeof(vgpu_cksum_t), cudaMemcpyHostToDevice, 0);
-        if (e == cudaSuccess) e = cudaMemsetAsync(rr, 0, sizeof(*rr), 0);
+        memcpy(h.h_ck, h_expect, nchunks * sizeof(vgpu_cksum_t));
+        e = cudaMemcpyAsync(h.d_ck, h.h_ck, nchunks * sizeof(vgpu_cksum_t), cudaMemcpyHostToDevice, h.st);
+        if (e == cudaSuccess) e = cudaMemsetAsync(h.d_rr, 0, sizeof(*h.d_rr), h.st);
         if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "stage expect: %s", cudaGetErrorString(e));
     }
-    if (!rc) rc = vgpu_restore(variant, VGPU_TIER_HOST, h_dev, d_dst, nullptr, nullptr, nchunks, chunk_bytes, ck, nullptr, rr, nullptr);
+    if (!rc) rc = vgpu_restore(variant, VGPU_TIER_HOST, h_dev, d_dst, nullptr, nullptr, nchunks, chunk_bytes, h.d_ck, nullptr, h.d_rr, h.st);
     if (!rc) {
-        e = cudaMemcpy(&hres, rr, sizeof(hres), cudaMemcpyDeviceToHost);
-        if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaMemcpy result: %s", cudaGetErrorString(e));
+        e = cudaMemcpyAsync(h.h_rr, h.d_rr, sizeof(*h.h_rr), cudaMemcpyDeviceToHost, h.st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h.st);
+        if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "restore from host: %s", cudaGetErrorString(e));
+    } else {
+        cudaStreamSynchronize(h.st);
     }
+    const vgpu_restore_result_t hres = rc ? vgpu_restore_result_t{} : *h.h_rr;
     if (reg) cudaHostUnregister(const_cast<void *>(host));
     if (rc) return rc;
     *bad_chunks = hres.bad_chunks;
@@ -544,6 +603,13 @@ int vgpu_policy_set(int tier, size_t min_chunks, int variant) {
     return VGPU_OK;
 }
 
+int vgpu_policy_set_grid(int tier, unsigned ctas) {
+    if (tier < 0 || tier > 2) return fail(VGPU_E_INVAL, "tier=%d", tier);
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_grid_override[tier] = ctas;
+    return VGPU_OK;
+}
+
 int vgpu_calibrate(int device, int tier, int peer_device, size_t max_chunks) {
     if (tier < 0 || tier > 2) return fail(VGPU_E_INVAL, "tier=%d", tier);
     if (max_chunks == 0) max_chunks = 512;
@@ -584,6 +650,61 @@ int vgpu_calibrate(int device, int tier, int peer_device, size_t max_chunks) {
     vgpu_slab_free(tier, device, peer_device, far_slab);
     vgpu_slab_free(VGPU_TIER_LOCAL, device, -1, near_slab);
     return rc;
+}
+
+// SM ids that kernels launched on `stream` in the CURRENT context run on (a green-context partition shows its own
+// SMs only): mask[i] bit b = SM 64*i+b.  Synchronous; 4096 CTAs of 128 threads, a few microseconds each.
+int vgpu_sm_probe(void *stream, uint64_t mask[4], unsigned *count) {
+    if (!mask) return fail(VGPU_E_INVAL, "null mask");
+    unsigned long long *d = nullptr;
+    VGPU_CUDA(cudaMalloc(&d, 32));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    cudaError_t e = cudaMemsetAsync(d, 0, 32, st);
+    if (e == cudaSuccess) {
+        k_smid_mask<<<4096, 128, 0, st>>>(d);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(mask, d, 32, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(VGPU_E_CUDA, "sm probe: %s", cudaGetErrorString(e));
+    if (count) {
+        *count = 0;
+        for (int i = 0; i < 4; ++i) *count += (unsigned)__builtin_popcountll(mask[i]);
+    }
+    return VGPU_OK;
+}
+
+// Copy-engine rate of the link behind a tier: plain cudaMemcpyAsync of `bytes` from this GPU's HBM to a
+// slab of the tier (out) and back (in), best of 3 after a warm-up, CUDA events.  This is the
+// "measured practical peak" the kernel rates are reported against next to the nominal link rate.
+int vgpu_link_rate(int device, int tier, int peer_device, size_t bytes, double *out_gbps, double *in_gbps) {
+    if (tier < 0 || tier > 2 || !bytes || !out_gbps || !in_gbps) return fail(VGPU_E_INVAL, "bad link-rate request");
+    void *near_slab = nullptr, *far_slab = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    int rc = vgpu_slab_alloc(VGPU_TIER_LOCAL, device, -1, bytes, &near_slab);
+    if (!rc) rc = vgpu_slab_alloc(tier, device, peer_device, bytes, &far_slab);
+    if (!rc && (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess)) rc = fail(VGPU_E_CUDA, "event create");
+    double best[2] = {0, 0};
+    for (int dir = 0; dir < 2 && !rc; ++dir)
+        for (int it = 0; it < 4 && !rc; ++it) {  // first iteration is warm-up
+            cudaEventRecord(e0, 0);
+            cudaError_t e = dir == 0 ? cudaMemcpyAsync(far_slab, near_slab, bytes, cudaMemcpyDefault, 0)
+                                     : cudaMemcpyAsync(near_slab, far_slab, bytes, cudaMemcpyDefault, 0);
+            cudaEventRecord(e1, 0);
+            if (e != cudaSuccess || cudaEventSynchronize(e1) != cudaSuccess) rc = fail(VGPU_E_CUDA, "link-rate copy: %s", cudaGetErrorString(e));
+            float ms = 0;
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (it && ms > 0) best[dir] = std::max(best[dir], (double)bytes / (ms * 1e6));
+        }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    vgpu_slab_free(tier, device, peer_device, far_slab);
+    vgpu_slab_free(VGPU_TIER_LOCAL, device, -1, near_slab);
+    if (rc) return rc;
+    *out_gbps = best[0];
+    *in_gbps = best[1];
+    return VGPU_OK;
 }
 
 // ---- memtest ------------------------------------------------------------------
@@ -658,8 +779,13 @@ int vgpu_memtest_run(void *buf, uint64_t bytes, int pattern, uint64_t first_pass
     vgpu_memtest_dev_result_t *d_res, *h_res;
     if (int rc = get_mt(dev, stream, &d_res, &h_res)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    cudaEvent_t ev[3];
-    for (auto &e : ev) VGPU_CUDA(cudaEventCreate(&e));
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+    for (auto &e : ev)
+        if (cudaError_t ce = cudaEventCreate(&e); ce != cudaSuccess) {
+            for (auto &d : ev)
+                if (d) cudaEventDestroy(d);
+            return fail(VGPU_E_CUDA, "cudaEventCreate: %s", cudaGetErrorString(ce));
+        }
     vgpu_memtest_result_t r{};
     r.bytes = bytes;
     r.first_bad_word = ~0ull;

@@ -178,6 +178,17 @@ k_memtest_verify(const uint64_t *__restrict__ buf, uint64_t head, uint64_t nvec,
     if (acc) memtest_verify_slow<PAT>(buf, head, nvec, tail, key, base, T, res);  // rare
 }
 
+// Which SMs does a launch in the current context land on?  Every CTA ORs its %smid into a 256-bit mask and spins a
+// little so that the grid really spreads over everything it may use.
+static __global__ void k_smid_mask(unsigned long long *mask) {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    if (threadIdx.x == 0) atomicOr(&mask[(smid >> 6) & 3], 1ull << (smid & 63));
+    const long long t0 = clock64();
+    while (clock64() - t0 < 20000) {
+    }
+}
+
 // ---------------------------------------------------------------------------
 // chunk transfer + checksum
 // ---------------------------------------------------------------------------

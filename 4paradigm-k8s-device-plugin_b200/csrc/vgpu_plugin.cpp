@@ -310,6 +310,12 @@ int vgpu_allocate_env_monitor(const vgpu_plugin_cfg_t *cfg, const vgpu_desc_t *c
         kv.emplace_back("CUDA_DEVICE_MEMORY_SHARED_CACHE", std::string("/tmp/") + u4 + ".cache");  // server.go:503
     }
     if (cfg->mem_scaling > 1) kv.emplace_back("CUDA_OVERSUBSCRIBE", "true");                  // server.go:505-507
+    // Additive and off by default (Contract A stays byte-identical to server.go:486-507): tell the pod WHICH of the
+    // disjoint SM partitions each of its vGPUs owns — the i of "<UUID>-<i>" — so that the containers sharing a GPU
+    // never land on the same SMs.  One variable per requested vGPU, numbered like CUDA_DEVICE_MEMORY_LIMIT_<n>.
+    if (cfg->emit_partition_index)
+        for (size_t i = 0; i < n_req; ++i)
+            kv.emplace_back("VGPU_SM_PARTITION_INDEX_" + std::to_string(i), std::to_string(req[i]->index));
 
     // server.go:511-522, in this order, all read-only
     if (!add_mount("/usr/local/vgpu/libvgpu.so", "/usr/local/vgpu/libvgpu.so", true) ||

@@ -38,6 +38,8 @@ struct VmmApi {
     CUresult (*SetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t) = nullptr;
     CUresult (*GetGranularity)(size_t *, const CUmemAllocationProp *, CUmemAllocationGranularity_flags) = nullptr;
     CUresult (*GetErrorString)(CUresult, const char **) = nullptr;
+    CUresult (*CtxGetCurrent)(CUcontext *) = nullptr;
+    CUresult (*CtxSetCurrent)(CUcontext) = nullptr;
 };
 VmmApi g_api;
 std::once_flag g_once;
@@ -52,8 +54,22 @@ void load_api() {
     g_api.ok = sym(g_api.AddressReserve, "cuMemAddressReserve") && sym(g_api.AddressFree, "cuMemAddressFree") &&
                sym(g_api.Create, "cuMemCreate") && sym(g_api.Release, "cuMemRelease") && sym(g_api.Map, "cuMemMap") &&
                sym(g_api.Unmap, "cuMemUnmap") && sym(g_api.SetAccess, "cuMemSetAccess") &&
-               sym(g_api.GetGranularity, "cuMemGetAllocationGranularity") && sym(g_api.GetErrorString, "cuGetErrorString");
+               sym(g_api.GetGranularity, "cuMemGetAllocationGranularity") && sym(g_api.GetErrorString, "cuGetErrorString") &&
+               sym(g_api.CtxGetCurrent, "cuCtxGetCurrent") && sym(g_api.CtxSetCurrent, "cuCtxSetCurrent");
 }
+
+// The manager works in the device's primary context (cudaSetDevice), but it is called on the APPLICATION's thread —
+// from inside the shim's cuMemAlloc / cuMemFree / cuMemPrefetchAsync hooks — where the current context may be one
+// made with cuCtxCreate, the stand-in context of a second vGPU of the GPU, or a green context.  Whatever was current
+// when an entry point is entered is current again when it returns.
+struct CtxScope {
+    CUcontext saved = nullptr;
+    bool have = false;
+    CtxScope() { have = g_api.ok && g_api.CtxGetCurrent(&saved) == CUDA_SUCCESS; }
+    ~CtxScope() {
+        if (have) g_api.CtxSetCurrent(saved);
+    }
+};
 
 int drv_fail(const char *what, CUresult r) {
     const char *s = nullptr;
@@ -101,7 +117,7 @@ struct Vmem {
     uint64_t clock = 0;
     vgpu_cksum_t *ck = nullptr;          // pinned + mapped: (X,S) of every chunk, written by the spill kernel,
                                          // read as `expect` by the restore kernel
-    vgpu_restore_result_t *res = nullptr;  // pinned + mapped
+    vgpu_restore_result_t *res = nullptr;  // pinned + mapped, one per block: which block failed is known exactly
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[2] = {nullptr, nullptr};
     CUmemAllocationProp prop{};
@@ -144,12 +160,19 @@ int unmap_block(Vmem *v, size_t b, bool release) {
     if (release) g_api.Release(bl.handle);  // explicit evict: the HBM goes back to the device
     else v->pool.push_back(bl.handle);      // making room inside ensure(): reused within microseconds
     bl.handle = 0;
-    bl.state = kSpilled;
     return VGPU_OK;
 }
 
+void give_slot_back(Vmem *v, Block &bl) {
+    Vmem::Tier &t = v->tiers[bl.tier_idx];
+    t.free_slots.push_back(bl.tier_slot);
+    t.evictions -= v->bc;
+}
+
 // Spill resident blocks `victims` to the tier, then unmap them and park or release their memory.
-// The unmap of block i-1 overlaps the spill kernel of block i.
+// The unmap of block i-1 overlaps the spill kernel of block i.  State and counters move per block, at the moment
+// the block's bytes are safely in the tier AND its HBM is unmapped; whatever fails, every block is afterwards either
+// fully resident (slot returned) or fully spilled, and the counters say so.
 int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
     if (victims.empty()) return VGPU_OK;
     size_t free_total = 0;
@@ -158,12 +181,30 @@ int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
         return fail(VGPU_E_NOMEM, "spill tier full: %zu blocks to evict, %zu free slots", victims.size(), free_total);
     const double t0 = now_ms();
     VGPU_CUDA(cudaDeviceSynchronize());  // whatever the application queued on the victims must be done
-    for (size_t i = 0; i < victims.size(); ++i) {
+    size_t launched = 0, finalized = 0;
+    int rc = VGPU_OK;
+    // block j's spill has completed: release its HBM and book it as spilled
+    auto finalize = [&](size_t j) -> int {
+        Block &bl = v->blocks[victims[j]];
+        if (int urc = unmap_block(v, victims[j], release)) {
+            give_slot_back(v, bl);  // still mapped, still resident: the copy in the tier is simply dropped
+            return urc;
+        }
+        bl.state = kSpilled;
+        v->resident -= 1;
+        v->spilled += 1;
+        v->st.evictions += v->bc;
+        return VGPU_OK;
+    };
+    for (size_t i = 0; i < victims.size() && !rc; ++i) {
         const size_t b = victims[i];
         Block &bl = v->blocks[b];
         size_t ti = 0;
         for (;; ++ti) {  // first tier with room whose slab can be had
-            if (ti == v->tiers.size()) return fail(VGPU_E_NOMEM, "spill tier full: no tier can take block %zu", b);
+            if (ti == v->tiers.size()) {
+                rc = fail(VGPU_E_NOMEM, "spill tier full: no tier can take block %zu", b);
+                break;
+            }
             Vmem::Tier &c = v->tiers[ti];
             if (c.free_slots.empty()) continue;
             if (c.slab) break;
@@ -172,28 +213,39 @@ int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
             c.free_slots.clear();
             c.slots = 0;
         }
+        if (rc) break;
         Vmem::Tier &t = v->tiers[ti];
         bl.tier_idx = (uint8_t)ti;
         bl.tier_slot = t.free_slots.back();
         t.free_slots.pop_back();
         t.evictions += v->bc;
-        int rc = vgpu_spill(VGPU_XFER_AUTO, t.kind, (const void *)(v->base + b * v->block_bytes()),
-                            (char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(), nullptr, nullptr, v->bc, kCB,
-                            v->ck + b * v->bc, v->stream);
-        if (rc) return rc;
-        VGPU_CUDA(cudaEventRecord(v->ev[i & 1], v->stream));
+        rc = vgpu_spill(VGPU_XFER_AUTO, t.kind, (const void *)(v->base + b * v->block_bytes()),
+                        (char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(), nullptr, nullptr, v->bc, kCB,
+                        v->ck + b * v->bc, v->stream);
+        if (!rc && cudaEventRecord(v->ev[i & 1], v->stream) != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaEventRecord (evict)");
+        if (rc) {
+            give_slot_back(v, bl);  // nothing of this block is in flight (or what is gets drained below): it stays resident
+            break;
+        }
+        launched = i + 1;
         if (i > 0) {
-            VGPU_CUDA(cudaEventSynchronize(v->ev[(i - 1) & 1]));
-            if (int urc = unmap_block(v, victims[i - 1], release)) return urc;
+            if (cudaEventSynchronize(v->ev[(i - 1) & 1]) != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaEventSynchronize (evict)");
+            else rc = finalize(i - 1);
+            finalized = i;  // on failure block i-1 was put back to "resident": it is dealt with either way
         }
     }
-    VGPU_CUDA(cudaEventSynchronize(v->ev[(victims.size() - 1) & 1]));
-    if (int urc = unmap_block(v, victims.back(), release)) return urc;
-    v->resident -= victims.size();
-    v->spilled += victims.size();
-    v->st.evictions += victims.size() * v->bc;
+    // drain: every block whose spill was launched is in the tier once the stream is idle
+    if (launched > finalized) {
+        if (cudaStreamSynchronize(v->stream) != cudaSuccess) {
+            if (!rc) rc = fail(VGPU_E_CUDA, "cudaStreamSynchronize (evict)");
+            for (size_t j = finalized; j < launched; ++j) give_slot_back(v, v->blocks[victims[j]]);  // cannot trust the copies
+        } else {
+            for (size_t j = finalized; j < launched; ++j)
+                if (int frc = finalize(j); frc && !rc) rc = frc;
+        }
+    }
     v->st.evict_ms += now_ms() - t0;
-    return VGPU_OK;
+    return rc;
 }
 
 }  // namespace
@@ -213,6 +265,7 @@ int vgpu_vmem_create_tiered(int device, uint64_t virtual_bytes, uint64_t residen
     if (peer_bytes && (peer_device < 0 || peer_device == device)) return fail(VGPU_E_INVAL, "peer tier needs another GPU");
     std::call_once(g_once, load_api);
     if (!g_api.ok) return fail(VGPU_E_UNSUPPORTED, "CUDA VMM driver API not available");
+    CtxScope keep;
     VGPU_CUDA(cudaSetDevice(device));
     VGPU_CUDA(cudaFree(0));
     Vmem *v = new Vmem();
@@ -262,7 +315,7 @@ int vgpu_vmem_create_tiered(int device, uint64_t virtual_bytes, uint64_t residen
     }
     int rc = VGPU_OK;  // the tier slab is allocated at the first eviction, not here
     cudaError_t e = cudaHostAlloc(&v->ck, v->nblocks * v->bc * sizeof(vgpu_cksum_t), cudaHostAllocMapped | cudaHostAllocPortable);
-    if (e == cudaSuccess) e = cudaHostAlloc(&v->res, sizeof(vgpu_restore_result_t), cudaHostAllocMapped | cudaHostAllocPortable);
+    if (e == cudaSuccess) e = cudaHostAlloc(&v->res, v->nblocks * sizeof(vgpu_restore_result_t), cudaHostAllocMapped | cudaHostAllocPortable);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&v->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&v->ev[0], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&v->ev[1], cudaEventDisableTiming);
@@ -287,6 +340,7 @@ int vgpu_vmem_evict(void *handle, uint64_t first, uint64_t n) {
     if (!v || first + n > v->nchunks) return fail(VGPU_E_INVAL, "chunk range out of bounds");
     if (n == 0) return VGPU_OK;
     std::lock_guard<std::mutex> lk(v->mu);
+    CtxScope keep;
     VGPU_CUDA(cudaSetDevice(v->device));
     std::vector<size_t> victims;
     for (size_t b = first / v->bc; b <= (first + n - 1) / v->bc; ++b)
@@ -305,6 +359,7 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
     if (b1 - b0 + 1 > v->resident_limit)
         return fail(VGPU_E_NOMEM, "%llu chunks requested, resident limit is %zu", (unsigned long long)n, v->resident_limit * v->bc);
     std::lock_guard<std::mutex> lk(v->mu);
+    CtxScope keep;
     VGPU_CUDA(cudaSetDevice(v->device));
     const uint64_t stamp = ++v->clock;
     std::vector<size_t> fresh, back;
@@ -330,39 +385,86 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
         if (int rc = evict_blocks(v, cand, false)) return rc;
     }
     const double t0 = now_ms();
-    for (size_t b : fresh) {
-        if (int rc = map_block(v, b)) return rc;
+    int result = VGPU_OK;
+    for (size_t b : fresh) {  // state and counter move together, block by block
+        if ((result = map_block(v, b)) != VGPU_OK) break;
         v->blocks[b].state = kResident;
+        v->resident += 1;
     }
-    v->resident += fresh.size();
-    v->res->bad_chunks = 0;
-    v->res->first_bad_inv = 0;
-    for (size_t b : back) {  // map block k+1 on the host while the GPU restores block k
-        if (int rc = map_block(v, b)) return rc;
+    // Spilled blocks: map block k+1 on the host while the GPU restores block k.  Each launch reports into its own
+    // result slot, so a checksum failure names its block.
+    auto restore_block = [&](size_t b, int variant) -> int {
         Block &bl = v->blocks[b];
         Vmem::Tier &t = v->tiers[bl.tier_idx];
-        int rc = vgpu_restore(VGPU_XFER_AUTO, t.kind, (const char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(),
-                              (void *)(v->base + b * v->block_bytes()), nullptr, nullptr, v->bc, kCB, v->ck + b * v->bc, nullptr,
-                              v->res, v->stream);
-        if (rc) return rc;
+        v->res[b].bad_chunks = 0;
+        v->res[b].first_bad_inv = 0;
+        return vgpu_restore(variant, t.kind, (const char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(),
+                            (void *)(v->base + b * v->block_bytes()), nullptr, nullptr, v->bc, kCB, v->ck + b * v->bc, nullptr,
+                            &v->res[b], v->stream);
+    };
+    std::vector<size_t> launched;
+    for (size_t b : back) {
+        if (result) break;
+        if ((result = map_block(v, b)) != VGPU_OK) break;
+        if ((result = restore_block(b, VGPU_XFER_AUTO)) != VGPU_OK) {
+            unmap_block(v, b, false);  // nothing was launched into it: the block stays spilled, its slot stays taken
+            break;
+        }
+        launched.push_back(b);
     }
-    int result = VGPU_OK;
-    if (!back.empty()) {
-        VGPU_CUDA(cudaStreamSynchronize(v->stream));
-        if (v->res->bad_chunks) {
-            v->st.checksum_failures += v->res->bad_chunks;
-            result = fail(VGPU_E_MISMATCH, "%llu restored chunk(s) failed their checksum", (unsigned long long)v->res->bad_chunks);
+    if (!launched.empty()) {
+        const bool drained = cudaStreamSynchronize(v->stream) == cudaSuccess;
+        if (!drained && !result) result = fail(VGPU_E_CUDA, "cudaStreamSynchronize (ensure)");
+        for (size_t b : launched) {
+            Block &bl = v->blocks[b];
+            bool good = drained && v->res[b].bad_chunks == 0;
+            if (drained && !good) {
+                // What arrived does not match what was spilled.  The tier still holds the only good copy: keep it,
+                // and try once more through the other mover (copy engine + checksum kernel) before giving up.
+                v->st.restore_retries += 1;
+                if (restore_block(b, VGPU_XFER_CE) == VGPU_OK && cudaStreamSynchronize(v->stream) == cudaSuccess)
+                    good = v->res[b].bad_chunks == 0;
+            }
+            if (good) {
+                v->tiers[bl.tier_idx].free_slots.push_back(bl.tier_slot);
+                bl.state = kResident;
+                v->resident += 1;
+                v->spilled -= 1;
+                v->st.fetches += v->bc;
+            } else {
+                // still spilled: HBM unmapped again, tier slot and checksums untouched, so a later ensure() can
+                // succeed once the cause (a flaky link, a repaired slab) is gone
+                if (drained) v->st.checksum_failures += v->res[b].bad_chunks;
+                unmap_block(v, b, false);
+                if (!result)
+                    result = fail(VGPU_E_MISMATCH, "block %zu: %llu restored chunk(s) failed their checksum (first: chunk %llu); the block stays in the tier",
+                                  b, (unsigned long long)v->res[b].bad_chunks,
+                                  (unsigned long long)(b * v->bc + (~v->res[b].first_bad_inv)));
+            }
         }
-        for (size_t b : back) {
-            v->tiers[v->blocks[b].tier_idx].free_slots.push_back(v->blocks[b].tier_slot);
-            v->blocks[b].state = kResident;
-        }
-        v->resident += back.size();
-        v->spilled -= back.size();
-        v->st.fetches += back.size() * v->bc;
     }
     v->st.fetch_ms += now_ms() - t0;
     return result;
+}
+
+// Where a chunk lives right now: *tier = VGPU_TIER_LOCAL and *ptr = its address in the range while its block is
+// resident; the tier kind and the chunk's address inside that tier's slab while it is spilled; *ptr = NULL for a
+// block that was never touched.
+int vgpu_vmem_locate(void *handle, uint64_t chunk, int *tier, void **ptr) {
+    Vmem *v = static_cast<Vmem *>(handle);
+    if (!v || !tier || !ptr || chunk >= v->nchunks) return fail(VGPU_E_INVAL, "bad locate request");
+    std::lock_guard<std::mutex> lk(v->mu);
+    const Block &bl = v->blocks[chunk / v->bc];
+    *tier = VGPU_TIER_LOCAL;
+    *ptr = nullptr;
+    if (bl.state == kResident) {
+        *ptr = (void *)(v->base + chunk * kCB);
+    } else if (bl.state == kSpilled) {
+        const Vmem::Tier &t = v->tiers[bl.tier_idx];
+        *tier = t.kind;
+        *ptr = (char *)t.slab + (size_t)bl.tier_slot * v->block_bytes() + (chunk % v->bc) * kCB;
+    }
+    return VGPU_OK;
 }
 
 int vgpu_vmem_stats(void *handle, vgpu_vmem_stats_t *out) {
@@ -384,6 +486,7 @@ int vgpu_vmem_stats(void *handle, vgpu_vmem_stats_t *out) {
 int vgpu_vmem_destroy(void *handle) {
     Vmem *v = static_cast<Vmem *>(handle);
     if (!v) return VGPU_OK;
+    CtxScope keep;
     cudaSetDevice(v->device);
     cudaDeviceSynchronize();
     for (size_t b = 0; b < v->blocks.size(); ++b)

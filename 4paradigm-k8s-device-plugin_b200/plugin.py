@@ -42,6 +42,7 @@ class Flags:
     deviceCoresScaling: float = 1.0
     enableLegacyPreferred: bool = False
     pcibusfile: str = "/usr/local/vgpu/pciinfo.vgpu"  # $PCIBUSFILE, main.go:164-185
+    smPartitionIndex: bool = False  # no reference flag: add VGPU_SM_PARTITION_INDEX_<n> to the response (vgpu.h, emit_partition_index)
 
 
 def validateFlags(f: Flags) -> None:
@@ -547,7 +548,7 @@ class NvidiaDevicePlugin:
                              cores_scaling=f.deviceCoresScaling,
                              id_strategy=0 if f.deviceIDStrategy == DeviceIDStrategyUUID else 1,
                              list_strategy=0 if f.deviceListStrategy == DeviceListStrategyEnvvar else 1,
-                             pcibusfile=f.pcibusfile.encode())
+                             pcibusfile=f.pcibusfile.encode(), emit_partition_index=1 if f.smPartitionIndex else 0)
         n_phys = len(self.cachedDevices)
         phys_uuid = (C.c_char_p * max(1, n_phys))(*[d.ID.encode() for d in self.cachedDevices])
         phys_idx = (C.c_char_p * max(1, n_phys))(*[d.Index.encode() for d in self.cachedDevices])

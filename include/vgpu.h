@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define VGPU_ABI_VERSION 1
+#define VGPU_ABI_VERSION 2
 
 /* ---- error codes ------------------------------------------------------- */
 #define VGPU_OK            0
@@ -70,6 +70,10 @@ typedef struct vgpu_plugin_cfg {
     int32_t  id_strategy;        /* 0 uuid, 1 index         main.go:84-89   */
     int32_t  list_strategy;      /* 0 envvar, 1 volume-mounts main.go:77-82 */
     char     pcibusfile[VGPU_PATH_LEN]; /* $PCIBUSFILE      server.go:516   */
+    uint32_t emit_partition_index; /* no reference counterpart; 0 (default) keeps the response identical to
+                                      server.go:486-507.  1 adds VGPU_SM_PARTITION_INDEX_<n>=<i of "<UUID>-<i>"> per
+                                      requested vGPU, which the shim uses to pick its green-context partition, so
+                                      the vGPUs of one GPU get disjoint SMs deterministically. */
 } vgpu_plugin_cfg_t;
 
 /* Replaces Device2VDevice (vdevice.go:36-58) for one physical GPU.
@@ -211,6 +215,15 @@ int vgpu_slab_free(int tier, int device, int peer_device, void *p);
 int vgpu_calibrate(int device, int tier, int peer_device, size_t max_chunks);
 int vgpu_policy_get(int tier, size_t nchunks);
 int vgpu_policy_set(int tier, size_t min_chunks, int variant);
+/* CTAs per transfer launch for a tier (0 = the built-in default).  The link tiers default to a grid that just covers
+ * the link's bandwidth-delay product, so that a spill running in the primary context does not park link-bound CTAs on
+ * the SMs of every tenant's partition. */
+int vgpu_policy_set_grid(int tier, unsigned ctas);
+
+/* Copy-engine rate of the link behind `tier` (cudaMemcpyAsync of `bytes` from `device`'s HBM out to a
+ * slab of the tier and back in, best of 3, GB/s): the measured practical peak that the kernel rates
+ * are quoted against beside the nominal 900 GB/s NVLink / 64 GB/s PCIe figures.  Synchronous. */
+int vgpu_link_rate(int device, int tier, int peer_device, size_t bytes, double *out_gbps, double *in_gbps);
 
 /* ======================================================================== *
  *  Virtual device memory manager: a vGPU address range larger than its resident
@@ -234,6 +247,7 @@ typedef struct vgpu_vmem_stats {
     uint64_t checksum_failures;           /* chunks whose (X,S) did not match on restore */
     double   evict_ms, fetch_ms;          /* wall time spent in evict / fetch incl. map/unmap */
     uint64_t evictions_peer, evictions_host; /* chunks sent to each tier */
+    uint64_t restore_retries;             /* blocks restored a second time (copy engine) after a checksum failure */
 } vgpu_vmem_stats_t;
 
 /* Create a range of `virtual_bytes` (rounded up to 2 MiB) on `device`, of which at most
@@ -251,6 +265,12 @@ int vgpu_vmem_base(void *handle, void **base);
  * checksum-verifies) spilled ones.  Synchronous.  VGPU_E_MISMATCH if a restore fails its
  * checksum, VGPU_E_NOMEM if n exceeds the resident limit or the tier is full. */
 int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n);
+/* A block whose restore fails its checksum is restored once more through the copy engine; if it still fails it is
+ * unmapped again and STAYS in the tier (slot, checksums and state untouched), so nothing is lost by the failed call
+ * and a later vgpu_vmem_ensure can succeed.  The other blocks of the call become resident as usual. */
+/* Where chunk `chunk` lives right now: *tier = VGPU_TIER_LOCAL and its address in the range while resident, the tier
+ * kind and its address inside that tier's slab while spilled, *ptr = NULL if never touched.  For tools and tests. */
+int vgpu_vmem_locate(void *handle, uint64_t chunk, int *tier, void **ptr);
 /* Push chunks [first, first+n) that are resident out to the tier and release their HBM. */
 int vgpu_vmem_evict(void *handle, uint64_t first, uint64_t n);
 int vgpu_vmem_stats(void *handle, vgpu_vmem_stats_t *out);
@@ -326,6 +346,10 @@ int vgpu_sm_partition_create(int device, unsigned percent, unsigned n,
 int vgpu_sm_partition_create_ex(int device, unsigned percent, unsigned n, unsigned flags,
                                 vgpu_sm_partition_t *out);
 int vgpu_sm_partition_destroy(vgpu_sm_partition_t *parts, unsigned n);
+/* The SMs that kernels launched on `stream` in the calling thread's current context actually run on: bit b of
+ * mask[i] = SM 64*i+b (read from %smid by a probe kernel).  Inside a pod (under the preload shim, where the current
+ * context is the vGPU's green context) this is the vGPU's partition; `vgpuvalidator --smids` prints it.  Synchronous. */
+int vgpu_sm_probe(void *stream, uint64_t mask[4], unsigned *count);
 
 #ifdef __cplusplus
 }

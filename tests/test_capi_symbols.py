@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol(vgpu):
     for name in header_functions():
         assert hasattr(lib, name), f"libvgpu_dp.so does not export {name}"
     assert set(header_functions()) == set(vgpu.capi.SIGNATURES), "capi.SIGNATURES out of sync with vgpu.h"
-    assert lib.vgpu_abi_version() == 1
+    assert lib.vgpu_abi_version() == 2
 
 
 def test_library_carries_sm100a_code_only(vgpu):

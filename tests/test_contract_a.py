@@ -176,3 +176,16 @@ def test_check_health_xid_rules(vgpu):
         p.markUnhealthy(d)
     msgs = list(p.ListAndWatch())
     assert [d["Health"] for d in msgs[-1]] == ["Healthy"] * 4 + ["Unhealthy"] * 2
+
+
+def test_partition_index_is_opt_in_and_additive(vgpu):
+    """No reference counterpart: with smPartitionIndex the response gains VGPU_SM_PARTITION_INDEX_<n> = the i of
+    "<UUID>-<i>" per requested vGPU and nothing else changes; without it Contract A is what server.go:486-507 builds."""
+    ids = [UUID + "-3", UUID + "-7"]
+    (plain,) = make_plugin(vgpu).Allocate([ids], _cache_uuid="0" * 36)
+    (extra,) = make_plugin(vgpu, smPartitionIndex=True).Allocate([ids], _cache_uuid="0" * 36)
+    assert not any(k.startswith("VGPU_SM_PARTITION_INDEX") for k in plain.Envs)
+    added = {k: v for k, v in extra.Envs.items() if k not in plain.Envs}
+    assert added == {"VGPU_SM_PARTITION_INDEX_0": "3", "VGPU_SM_PARTITION_INDEX_1": "7"}
+    assert {k: v for k, v in extra.Envs.items() if k in plain.Envs} == dict(plain.Envs)
+    assert [(m.ContainerPath, m.HostPath, m.ReadOnly) for m in extra.Mounts] == [(m.ContainerPath, m.HostPath, m.ReadOnly) for m in plain.Mounts]

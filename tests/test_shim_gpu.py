@@ -594,3 +594,41 @@ def test_sigusr2_suspends_and_sigusr1_resumes_a_running_vgpu_process(cuda_dev):
             p.wait(timeout=30)
         except Exception:
             p.kill()
+
+
+def _validator_smids(env_extra):
+    td = tempfile.mkdtemp(prefix="vgpusm")
+    env = dict(os.environ)
+    env.update({"LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": os.path.join(td, "shr.cache"), "LIBCUDA_LOG_LEVEL": "0",
+                "CUDA_DEVICE_SM_LIMIT": "25", "CUDA_DEVICE_MEMORY_LIMIT_0": "8g"})
+    env.update(env_extra)
+    exe = os.path.join(ROOT, "4paradigm-k8s-device-plugin_b200", "vgpuvalidator")
+    p = subprocess.run([exe, "--smids"], env=env, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    return json.loads(p.stdout.strip().splitlines()[-1]), p.stderr
+
+
+def test_partition_index_from_the_plugin_gives_containers_disjoint_sms(cuda_dev):
+    """Four containers of one GPU (split 4 -> CUDA_DEVICE_SM_LIMIT=25), each with the VGPU_SM_PARTITION_INDEX_0 the plugin
+    emits when asked to (vgpu_plugin_cfg_t.emit_partition_index): the SMs their kernels really run on (%smid, read by
+    `vgpuvalidator --smids`) are four disjoint sets of at most 25 % of the GPU.  Without the variable nothing tells a
+    container which vGPU of the GPU it is: both land on group 0 and the shim says that placement is not coordinated."""
+    sets = []
+    for i in range(4):
+        o, err = _validator_smids({"VGPU_SM_PARTITION_INDEX_0": str(i)})
+        assert 0 < o["sm_count"] <= 37 and "NOT coordinated" not in err
+        sets.append(set(o["sm_ids"]))
+    for i in range(4):
+        for j in range(i):
+            assert not (sets[i] & sets[j]), f"vGPU {i} and vGPU {j} share SMs {sorted(sets[i] & sets[j])}"
+    assert sum(len(s) for s in sets) >= 128
+    # the validator's kernels use no clusters: it takes the SM-granular split (36 of 148 for 25 %) unless told otherwise
+    assert len(sets[0]) == 36
+    coarse, _ = _validator_smids({"VGPU_SM_PARTITION_INDEX_0": "0", "VGPU_SM_PARTITION_GRANULE": "coarse"})
+    assert coarse["sm_count"] == 32
+    a, err_a = _validator_smids({})
+    b, err_b = _validator_smids({})
+    assert set(a["sm_ids"]) == set(b["sm_ids"]) and "NOT coordinated" in err_a and "NOT coordinated" in err_b
+    # the legacy single variable still works for every device
+    c, err_c = _validator_smids({"VGPU_SM_PARTITION_INDEX": "2"})
+    assert set(c["sm_ids"]) == sets[2] and "NOT coordinated" not in err_c

@@ -129,3 +129,76 @@ def test_two_tiers_peer_first_then_host(vgpu, cuda_dev):
         assert res.cpu().tolist() == [0, 0, 0] and _stats(capi, h).checksum_failures == 0
     finally:
         capi.lib.vgpu_vmem_destroy(h)
+
+
+def test_failed_restore_keeps_the_tier_copy_and_a_later_ensure_succeeds(vgpu, cuda_dev):
+    """A chunk that comes back from the tier with the wrong checksum must not cost the data: the block is restored once
+    more through the copy engine, and if that fails too it is unmapped again and stays spilled (slot and checksums
+    kept).  Here the tier slab itself is corrupted, so both attempts fail; after the slab is repaired a second ensure
+    succeeds and every byte is back."""
+    capi = vgpu.capi
+    total, bc = 64, 8
+    h, base = _mk(capi, total, total, total, block_chunks=bc)
+    res = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+    try:
+        assert capi.lib.vgpu_vmem_ensure(h, 0, total) == 0, capi.last_error()
+        assert capi.lib.vgpu_memtest_fill(base, total * CB, capi.PAT_RANDOM, 3, 21, None) == 0
+        torch.cuda.synchronize()
+        assert capi.lib.vgpu_vmem_evict(h, 0, total) == 0, capi.last_error()
+        victim = 2 * bc + 5                                   # a chunk of block 2
+        tier, ptr = C.c_int(-1), C.c_void_p()
+        assert capi.lib.vgpu_vmem_locate(h, victim, C.byref(tier), C.byref(ptr)) == 0
+        assert tier.value == capi.TIER_HOST and ptr.value
+        byte = (C.c_ubyte * 1).from_address(ptr.value + 12345)  # the host tier is pinned host memory: reachable from here
+        byte[0] ^= 0x10
+        rc = capi.lib.vgpu_vmem_ensure(h, 0, total)
+        assert rc == capi.E_MISMATCH, capi.last_error()
+        assert f"first: chunk {victim}" in capi.last_error() and "stays in the tier" in capi.last_error()
+        s = _stats(capi, h)
+        assert s.checksum_failures == 1 and s.restore_retries == 1          # one chunk, still bad after the copy-engine retry
+        assert s.chunks_resident == total - bc and s.chunks_spilled == bc   # only the failing block stayed out
+        t2, p2 = C.c_int(-1), C.c_void_p()
+        assert capi.lib.vgpu_vmem_locate(h, victim, C.byref(t2), C.byref(p2)) == 0
+        assert t2.value == capi.TIER_HOST and p2.value == ptr.value         # same slot: the only good copy was not given away
+        byte[0] ^= 0x10                                                      # repair
+        assert capi.lib.vgpu_vmem_ensure(h, 0, total) == 0, capi.last_error()
+        assert capi.lib.vgpu_memtest_verify(base, total * CB, capi.PAT_RANDOM, 3, 21, res.data_ptr(), None) == 0
+        torch.cuda.synchronize()
+        assert res.cpu().tolist() == [0, 0, 0]
+        s = _stats(capi, h)
+        assert s.chunks_resident == total and s.chunks_spilled == 0 and s.checksum_failures == 1
+        # and the freed slots are all usable again
+        assert capi.lib.vgpu_vmem_evict(h, 0, total) == 0, capi.last_error()
+        assert _stats(capi, h).chunks_spilled == total
+    finally:
+        capi.lib.vgpu_vmem_destroy(h)
+
+
+def test_manager_leaves_the_callers_context_current(vgpu, cuda_dev):
+    """The manager is called on application threads from inside the shim's hooks; a thread whose current context is not
+    the primary one (cuCtxCreate, a green context) must find it current again afterwards."""
+    capi = vgpu.capi
+    cuda = C.CDLL("libcuda.so.1")
+    parts = (capi.SmPartition * 2)()
+    assert capi.lib.vgpu_sm_partition_create(0, 25, 2, parts) == 0, capi.last_error()
+    h = C.c_void_p()
+    try:
+        assert cuda.cuCtxPushCurrent_v2(C.c_void_p(parts[1].ctx)) == 0
+        cur = C.c_void_p()
+        h, base = _mk(capi, 32, 16, 32, block_chunks=8)
+        assert cuda.cuCtxGetCurrent(C.byref(cur)) == 0 and cur.value == parts[1].ctx
+        assert capi.lib.vgpu_vmem_ensure(h, 0, 16) == 0, capi.last_error()
+        assert capi.lib.vgpu_vmem_ensure(h, 16, 16) == 0, capi.last_error()   # evicts
+        assert cuda.cuCtxGetCurrent(C.byref(cur)) == 0 and cur.value == parts[1].ctx
+        assert capi.lib.vgpu_vmem_evict(h, 0, 32) == 0, capi.last_error()
+        assert cuda.cuCtxGetCurrent(C.byref(cur)) == 0 and cur.value == parts[1].ctx
+        assert capi.lib.vgpu_vmem_destroy(h) == 0
+        h = C.c_void_p()
+        assert cuda.cuCtxGetCurrent(C.byref(cur)) == 0 and cur.value == parts[1].ctx
+    finally:
+        popped = C.c_void_p()
+        cuda.cuCtxPopCurrent_v2(C.byref(popped))
+        if h:
+            capi.lib.vgpu_vmem_destroy(h)
+        torch.cuda.synchronize()
+        capi.lib.vgpu_sm_partition_destroy(parts, 2)

@@ -5,7 +5,8 @@ Collected last on purpose (file name): if it fails, `pytest -x` has already run 
 test.  It is checked against the existing entry point vgpu_spill(VGPU_XFER_LDST) — same
 kernel, scratch obtained the ordinary way — bit for bit (integer work, no tolerance), on two
 calls in a row that use different batch sizes and data, so that what the first call leaves in
-the shared fixed scratch cannot leak into the second.  Passes alone in a fresh process (the
+the shared fixed scratch cannot leak into the second; both calls are also compared directly
+with the CPU oracle's checksums and bytes.  Passes alone in a fresh process (the
 first call does the per-GPU set-up) and after the rest of the suite."""
 import ctypes as C
 
@@ -13,7 +14,17 @@ import numpy as np
 import pytest
 import torch
 
+from oracle import cpu  # the checker
+
 pytestmark = pytest.mark.gpu
+
+
+def _oracle_spill(src, n, cb, slots=None):
+    """(checksums [n,2] u64, destination bytes) the CPU oracle produces for the same source."""
+    words = src.cpu().numpy().view(np.uint64)
+    o_dst = np.zeros_like(words)
+    want = cpu.spill(words, o_dst, n, cb, *(slots or ()))
+    return want, o_dst.view(np.uint8)
 
 
 def _spill_both_ways(capi, src, n, cb, slots=None):
@@ -47,6 +58,9 @@ def test_noalloc_spill_matches_existing_entry_point_twice_in_a_row(vgpu, cuda_de
     (d_ref, ck_ref), (d_new, ck_new) = _spill_both_ways(capi, src1, 40, cb)
     assert torch.equal(ck_new, ck_ref), "checksums differ from vgpu_spill (call 1)"
     assert torch.equal(d_new, d_ref) and torch.equal(d_new, src1)
+    want, o_dst = _oracle_spill(src1, 40, cb)
+    assert np.array_equal(ck_new.cpu().numpy().view(np.uint64), want), "checksums differ from the oracle (call 1)"
+    assert np.array_equal(d_new.cpu().numpy(), o_dst)
     # call 2, straight after: fewer chunks, other data, ragged chunk size, scattered slots
     cb2 = 65536 + 32
     rng = np.random.default_rng(2)
@@ -56,6 +70,9 @@ def test_noalloc_spill_matches_existing_entry_point_twice_in_a_row(vgpu, cuda_de
     (d_ref, ck_ref), (d_new, ck_new) = _spill_both_ways(capi, src2, 9, cb2, slots)
     assert torch.equal(ck_new, ck_ref), "checksums differ from vgpu_spill (call 2)"
     assert torch.equal(d_new, d_ref)
+    want, o_dst = _oracle_spill(src2, 9, cb2, slots)
+    assert np.array_equal(ck_new.cpu().numpy().view(np.uint64), want), "checksums differ from the oracle (call 2)"
+    assert np.array_equal(d_new.cpu().numpy(), o_dst)
     # and the full capacity of the fixed scratch
     n = capi.NOALLOC_MAX_CHUNKS
     src3 = torch.empty(n * 4096, dtype=torch.uint8, device=cuda_dev)
