@@ -34,9 +34,9 @@ struct Scratch {
     ChunkAcc *acc = nullptr;  // self-cleaning per-chunk accumulators
     size_t acc_cap = 0;
     vgpu_memtest_dev_result_t *mt = nullptr;
-    vgpu_memtest_dev_result_t *mt_host = nullptr;  // pinned: a pageable D2H copy would hold the
-                                                   // context lock until the stream drains and
-                                                   // serialise the other vGPUs' host threads
+    vgpu_memtest_dev_result_t *mt_host = nullptr;  // pinned + mapped: written by k_mt_result_publish (a pageable
+                                                   // D2H copy would hold the context lock until the stream
+                                                   // drains and serialise the other vGPUs' host threads)
 };
 
 struct DevState {
@@ -88,7 +88,7 @@ int get_mt(int dev, void *stream, vgpu_memtest_dev_result_t **out, vgpu_memtest_
     std::lock_guard<std::mutex> lk(g_mu);
     Scratch &s = g_dev[dev].scratch[stream];
     if (!s.mt) VGPU_CUDA(cudaMalloc(&s.mt, sizeof(*s.mt)));
-    if (!s.mt_host) VGPU_CUDA(cudaHostAlloc(&s.mt_host, sizeof(*s.mt_host), cudaHostAllocDefault));
+    if (!s.mt_host) VGPU_CUDA(cudaHostAlloc(&s.mt_host, sizeof(*s.mt_host), cudaHostAllocMapped | cudaHostAllocPortable));
     *out = s.mt;
     *host = s.mt_host;
     return VGPU_OK;
@@ -792,14 +792,15 @@ int vgpu_memtest_run(void *buf, uint64_t bytes, int pattern, uint64_t first_pass
     r.first_bad_pattern = r.first_bad_pass = -1;
     int rc = VGPU_OK;
     for (uint64_t p = first_pass; p < first_pass + npasses && !rc; ++p) {
-        cudaMemsetAsync(d_res, 0, sizeof(*d_res), st);
+        k_mt_result_reset<<<1, 1, 0, st>>>(d_res);
         cudaEventRecord(ev[0], st);
         rc = vgpu_memtest_fill(buf, bytes, pattern, p, seed, stream);
         cudaEventRecord(ev[1], st);
         if (!rc) rc = vgpu_memtest_verify(buf, bytes, pattern, p, seed, d_res, stream);
         cudaEventRecord(ev[2], st);
         if (!rc) {
-            cudaError_t e = cudaMemcpyAsync(h_res, d_res, sizeof(*h_res), cudaMemcpyDeviceToHost, st);
+            k_mt_result_publish<<<1, 1, 0, st>>>(d_res, h_res);  // mapped pinned memory: no copy-engine job (see the kernel)
+            cudaError_t e = cudaGetLastError();
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
             if (e != cudaSuccess) rc = fail(VGPU_E_CUDA, "memtest pass %llu: %s", (unsigned long long)p, cudaGetErrorString(e));
         }

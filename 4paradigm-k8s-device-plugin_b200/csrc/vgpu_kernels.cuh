@@ -178,6 +178,18 @@ k_memtest_verify(const uint64_t *__restrict__ buf, uint64_t head, uint64_t nvec,
     if (acc) memtest_verify_slow<PAT>(buf, head, nvec, tail, key, base, T, res);  // rare
 }
 
+// Result block of a blocking memtest pass: zeroed before the pass and handed to the host after it by one-thread
+// kernels (a store to mapped pinned memory), NOT by cudaMemsetAsync / cudaMemcpyAsync — a 24-byte copy-engine job
+// queues behind whatever bulk spill another vGPU has on the same engine (40 ms for 2 GiB to the host), and every
+// validator pass would wait for it.
+static __global__ void k_mt_result_reset(vgpu_memtest_dev_result_t *res) { *res = vgpu_memtest_dev_result_t{0, 0, 0}; }
+static __global__ void k_mt_result_publish(const vgpu_memtest_dev_result_t *res, volatile vgpu_memtest_dev_result_t *host) {
+    host->mismatches = res->mismatches;
+    host->first_bad_inv = res->first_bad_inv;
+    host->bad_bits = res->bad_bits;
+    __threadfence_system();
+}
+
 // Which SMs does a launch in the current context land on?  Every CTA ORs its %smid into a 256-bit mask and spins a
 // little so that the grid really spreads over everything it may use.
 static __global__ void k_smid_mask(unsigned long long *mask) {

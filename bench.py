@@ -735,6 +735,15 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, peer, ranks):
             raise SystemExit("peer slab: " + capi.last_error())
         tiers["peer"] = (capi.TIER_PEER, peer_slab.value, None)
     out = {"chunk_bytes": cb, "bytes_counted": "payload once per chunk per direction", "timing": "CUDA events on the launch stream, best of 5 after 2 warm-ups, max over ranks"}
+    if "peer" in tiers and world == 1:
+        # An idle peer (nobody else's context on it): let the library measure its variants on this box, as a deployment
+        # does at start-up — "switch ... when measured bandwidth favours it".  With the peer idle the PULL form of the
+        # spill (the bulk-copy kernel runs on the peer and READS our HBM: read responses carry 12.5 % packet overhead,
+        # writes 18.75 %) wins from 64 chunks up.  With N>1 every GPU is busy in another process and the built-in
+        # table (push) stays.
+        capi.check(capi.lib.vgpu_calibrate(local, capi.TIER_PEER, peer, min(nmax, 512)))
+    names = {capi.XFER_LDST: "ldst", capi.XFER_TMA: "tma", capi.XFER_CE: "ce", capi.XFER_PULL: "pull"}
+    out["auto_policy"] = {t: {str(n): names.get(capi.lib.vgpu_policy_get(tiers[t][0], n), "?") for n in sizes} for t in tiers}
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     def time_call(fn, reps=5, warm=2):
@@ -852,14 +861,14 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, peer, ranks):
     if local == 0:
         if "peer" in tiers:
             n = out["peer"]["one_direction_only_rank0"]["chunks"]
-            uni = {k: v for k, v in out["peer"]["one_direction_only_rank0"].items() if k in ("ldst", "tma")}
+            uni = {k: v for k, v in out["peer"]["one_direction_only_rank0"].items() if k in ("ldst", "tma", "pull")}
             sp = max(v["spill_GBps"] for v in uni.values())
             rs = max(v["restore_GBps"] for v in uni.values())
             ring = best_at_max["peer"][1]
             pk = link.get("peer", {})
             out["_roofline_nvlink"] = {
                 "bound": "nvlink", "unit": "GB/s", "peak": NVLINK_NOMINAL, "peak_source": "900 GB/s per direction nominal (north_star)",
-                "kernel": "k_xfer_ldst / k_xfer_tma, best of the two, spill slab in the peer GPU's HBM", "chunks_per_launch": n,
+                "kernel": "k_xfer_ldst / k_xfer_tma (pushed from this GPU, or — spill only — pulled by the idle peer), best variant, spill slab in the peer GPU's HBM", "chunks_per_launch": n,
                 "algorithmic_bytes_per_launch": n * cb,
                 "spill": {"achieved": sp, "frac": round(sp / NVLINK_NOMINAL, 4), "frac_of_copy_engine": round(sp / pk["out_GBps"], 4) if pk.get("out_GBps") else None,
                           "traffic": link_traffic("nvlink", "spill", n * cb)},
