@@ -103,7 +103,7 @@ struct Rule {
     int variant;
 };
 std::vector<Rule> g_policy[3] = {
-    {{0, VGPU_XFER_TMA}, {512, VGPU_XFER_LDST}},  // local HBM: bulk-copy ring up to 64 chunks (+6 %), LD/ST from 512 up (+1 %)
+    {{0, VGPU_XFER_TMA}, {8, VGPU_XFER_LDST}},    // local HBM: bulk-copy ring below 8 chunks (+5-10 %), LD/ST from 8 up (+3-9 %; profiles/r02_small_batches.md)
     {{0, VGPU_XFER_TMA}},                         // peer HBM: bulk-copy ring >= LD/ST at every size (891 vs 851 GB/s at 8 chunks)
     {{0, VGPU_XFER_LDST}, {8, VGPU_XFER_CE}},    // pinned host: copy engine +5 % from 8 chunks up (55.1 vs 52.7 GB/s)
 };
@@ -121,7 +121,6 @@ int policy_lookup(int tier, size_t nchunks) {
 }
 
 // ---- transfer launch --------------------------------------------------------
-constexpr int kLdstU = 4;                   // 4 x 32 B per thread in flight => 32 KiB tiles
 constexpr int kTmaTile = 32768, kTmaStages = 2, kTmaLag = 1, kTmaConsumerWarps = 4;  // 64 KiB ring, 3 CTAs/SM: best of the shapes swept
 constexpr int kTmaGridMult = 16;  // CTAs per launch = resident CTAs x 16 (grid-stride over the rest)
 // link tiers: CTAs per launch (see grid_cap).
@@ -237,12 +236,15 @@ int launch_xfer(int variant, int tier, bool copy, const void *src, void *dst,
     }
 
     if (variant == VGPU_XFER_LDST || !copy) {
-        constexpr uint32_t tile = LdstTile<kLdstU>::bytes;
+        // 32 KiB tiles (4 x 32 B per thread in flight) at every batch size: smaller tiles were tried for small batches
+        // and only add folds (profiles/r02_small_batches.md)
+        constexpr int kU = 4;
+        constexpr uint32_t tile = LdstTile<kU>::bytes;
         a.tiles_per_chunk = (uint32_t)((chunk_bytes + tile - 1) / tile);
         const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
         const unsigned grid = (unsigned)std::min<uint64_t>(total, grid_cap(copy ? tier : VGPU_TIER_LOCAL, VGPU_XFER_LDST, sms));
-        if (copy) k_xfer_ldst<kLdstU, true><<<grid, kXfThreads, 0, st>>>(a);
-        else k_xfer_ldst<kLdstU, false><<<grid, kXfThreads, 0, st>>>(a);
+        if (copy) k_xfer_ldst<kU, true><<<grid, kXfThreads, 0, st>>>(a);
+        else k_xfer_ldst<kU, false><<<grid, kXfThreads, 0, st>>>(a);
     } else {  // VGPU_XFER_TMA
         a.tiles_per_chunk = (uint32_t)((chunk_bytes + kTmaTile - 1) / kTmaTile);
         const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;

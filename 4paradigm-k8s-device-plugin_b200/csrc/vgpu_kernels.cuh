@@ -234,25 +234,50 @@ __device__ __forceinline__ void cksum_word(uint64_t w, uint32_t i, uint64_t &x, 
     s += w * (uint64_t)(2u * i + 1u);
 }
 
-// Warp-level fold + publish.  Called by all 32 lanes.
-__device__ __forceinline__ void chunk_fold(const XferArgs &a, uint32_t c, uint64_t x, uint64_t s,
-                                           uint32_t tickets_per_chunk) {
+// Fold one tile's partial (X,S) into the chunk's accumulator and publish when the chunk is complete.
+// Called by all threads of NW full warps (the whole CTA in the LD/ST kernel, the consumer warps in the bulk-copy
+// kernel).  The warps first combine through shared memory so that ONE lane per tile touches the accumulator: all
+// atomics of a chunk hit the same three addresses and the L2 serialises them — with one fold per warp a 2 MiB chunk
+// cost 1536 same-address atomics (~5 us, the whole run time of a small batch; profiles/r02_small_batches.md), with
+// one per tile it costs 192.  `stage` is NW x 2 u64 of shared memory that the caller alternates between consecutive
+// tiles (so one barrier per tile is enough); `sync` is the barrier over exactly the participating warps.
+template <int NW, typename Sync>
+__device__ __forceinline__ void chunk_fold(const XferArgs &a, uint32_t c, uint64_t x, uint64_t s, uint32_t warp,
+                                           uint64_t (*stage)[2], Sync sync, uint32_t tickets_per_chunk) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         x ^= __shfl_xor_sync(0xffffffffu, x, o);
         s += __shfl_xor_sync(0xffffffffu, s, o);
     }
-    if ((threadIdx.x & 31) == 0) {
+    const uint32_t lane = threadIdx.x & 31;
+    if (lane == 0) {
+        stage[warp][0] = x;
+        stage[warp][1] = s;
+    }
+    sync();
+    if (warp != 0) return;
+    x = lane < NW ? stage[lane][0] : 0;
+    s = lane < NW ? stage[lane][1] : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {  // NW <= 32
+        x ^= __shfl_xor_sync(0xffffffffu, x, o);
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+    }
+    if (lane == 0) {
         ChunkAcc *acc = a.acc + c;
-        atomicXor(&acc->x, (unsigned long long)x);
+        atomicXor(&acc->x, (unsigned long long)x);  // fire-and-forget reductions ...
         atomicAdd(&acc->s, (unsigned long long)s);
-        __threadfence();
-        const unsigned int t = atomicAdd(&acc->ticket, 1u);
+        // ... ordered before the ticket by its release half; the acquire half lets whoever draws the last ticket read
+        // every contribution.  One acq_rel atomic instead of fence + atomic + fence: the serial tail of a one-chunk
+        // transfer is a chain of L2 round trips, and each fence was one more of them.
+        unsigned int t;
+        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(t) : "l"(&acc->ticket) : "memory");
         if (t == tickets_per_chunk - 1) {
-            __threadfence();
-            const uint64_t X = atomicExch(&acc->x, 0ull);
-            const uint64_t S = atomicExch(&acc->s, 0ull);
-            atomicExch(&acc->ticket, 0u);
+            const uint64_t X = __ldcg(&acc->x);  // both loads in flight together (L2 is where the atomics landed)
+            const uint64_t S = __ldcg(&acc->s);
+            __stcg(&acc->x, 0ull);               // clean for the next launch: nobody else touches this slot any more
+            __stcg(&acc->s, 0ull);
+            __stcg(&acc->ticket, 0u);
             if (a.cksum) {
                 a.cksum[c].x = X;
                 a.cksum[c].s = S;
@@ -279,7 +304,9 @@ template <int U, bool COPY>
 __global__ void __launch_bounds__(kXfThreads) k_xfer_ldst(const XferArgs a) {
     constexpr uint32_t kTile = LdstTile<U>::bytes;
     const uint64_t total = (uint64_t)a.nchunks * a.tiles_per_chunk;
-    for (uint64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+    __shared__ uint64_t stage[2][kXfThreads / 32][2];
+    uint32_t flip = 0;
+    for (uint64_t tile = blockIdx.x; tile < total; tile += gridDim.x, flip ^= 1) {
         const uint32_t c = (uint32_t)(tile / a.tiles_per_chunk);
         const uint32_t t = (uint32_t)(tile % a.tiles_per_chunk);
         const uint64_t toff = (uint64_t)t * kTile;
@@ -308,7 +335,7 @@ __global__ void __launch_bounds__(kXfThreads) k_xfer_ldst(const XferArgs a) {
                 cksum_word(v[u].d, i + 3, x, sum);
             }
         }
-        chunk_fold(a, c, x, sum, a.tiles_per_chunk * (kXfThreads / 32));
+        chunk_fold<kXfThreads / 32>(a, c, x, sum, threadIdx.x >> 5, stage[flip], [] { __syncthreads(); }, a.tiles_per_chunk);
     }
 }
 
@@ -430,6 +457,8 @@ __global__ void __launch_bounds__(32 * (NCW + 1)) k_xfer_tma(const XferArgs a) {
     }
     // ---------------- consumer warps
     const uint32_t ct = threadIdx.x - 32;
+    __shared__ uint64_t stage[2][NCW][2];
+    auto consumer_sync = [] { asm volatile("bar.sync 1, %0;" ::"n"(NCW * 32) : "memory"); };  // the consumer warps only
     for (uint64_t k = 0; k < my_n; ++k) {
         uint32_t c, len;
         uint64_t toff;
@@ -447,7 +476,7 @@ __global__ void __launch_bounds__(32 * (NCW + 1)) k_xfer_tma(const XferArgs a) {
         }
         __syncwarp();
         if ((threadIdx.x & 31) == 0) mbar_arrive(&done[st]);  // this warp no longer reads the buffer
-        chunk_fold(a, c, x, sum, a.tiles_per_chunk * NCW);
+        chunk_fold<NCW>(a, c, x, sum, ct >> 5, stage[k & 1], consumer_sync, a.tiles_per_chunk);
     }
 }
 
