@@ -240,6 +240,11 @@ static void narrow_visible_devices(char vis[][VGPU_UUID_LEN], int nvis, int nrea
         }
         if (strcmp(out, user) == 0) return;
     }
+    /* The spill tier's peer GPU (VGPU_OVERSUB_PEER=<UUID>) must stay open to the DRIVER of this process — P2P needs
+     * both ends — so it rides behind the vGPU's own GPUs; the virtual-device table keeps it away from the application
+     * (build_vdev). */
+    const char *peer = getenv("VGPU_OVERSUB_PEER");
+    if (peer && strncasecmp(peer, "GPU-", 4) == 0 && !strcasestr(out, peer)) list_append(out, sizeof(out), peer);
     setenv("CUDA_VISIBLE_DEVICES", out, 1);
     SHIM_INFO("CUDA_VISIBLE_DEVICES=%s (from NVIDIA_DEVICE_MAP%s%s)", out, user ? " and " : "", user ? user : "");
 }
@@ -355,6 +360,19 @@ static volatile int g_data_out;  /* 1 while VMM-backed allocations are (being) s
 static void wait_running(void) {
     while (g_region_ok && (region_my_status() != 1 || g_data_out)) usleep(g_data_out ? 1000 : 1000000);
 }
+/* A real gate for the calls that touch device memory or submit work: a caller announces itself (in-flight count)
+ * AFTER it has seen the gate open and re-checks; the mover closes the gate first and then waits for the count to
+ * reach zero, so nobody can be between "passed the gate" and "called the driver" when the HBM is unmapped. */
+static volatile int g_inflight;
+static void gate_enter(void) {
+    for (;;) {
+        wait_running();
+        __atomic_add_fetch(&g_inflight, 1, __ATOMIC_SEQ_CST);
+        if (!g_data_out) return;
+        __atomic_sub_fetch(&g_inflight, 1, __ATOMIC_SEQ_CST);
+    }
+}
+static void gate_exit(void) { __atomic_sub_fetch(&g_inflight, 1, __ATOMIC_SEQ_CST); }
 
 /* ------------------------------------------------------------------ oversubscribe backend
  * CUDA_OVERSUBSCRIBE=true routes allocations above 2 MiB away from plain cuMemAlloc.  The
@@ -373,6 +391,7 @@ static struct {
     int (*base)(void *, void **);
     int (*ensure)(void *, uint64_t, uint64_t);
     int (*evict)(void *, uint64_t, uint64_t);
+    int (*missing)(void *, uint64_t, uint64_t, uint64_t *);
     int (*destroy)(void *);
     const char *(*last_error)(void);
 } g_dp;
@@ -400,9 +419,10 @@ static void load_vmm_backend(void) {
     g_dp.base = (int (*)(void *, void **))real_dlsym(g_dp.lib, "vgpu_vmem_base");
     g_dp.ensure = (int (*)(void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_ensure");
     g_dp.evict = (int (*)(void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_evict");
+    g_dp.missing = (int (*)(void *, uint64_t, uint64_t, uint64_t *))real_dlsym(g_dp.lib, "vgpu_vmem_missing");
     g_dp.destroy = (int (*)(void *))real_dlsym(g_dp.lib, "vgpu_vmem_destroy");
     g_dp.last_error = (const char *(*)(void))real_dlsym(g_dp.lib, "vgpu_last_error");
-    g_backend_vmm = g_dp.create && g_dp.base && g_dp.ensure && g_dp.evict && g_dp.destroy && g_dp.last_error;
+    g_backend_vmm = g_dp.create && g_dp.create_tiered && g_dp.base && g_dp.ensure && g_dp.evict && g_dp.missing && g_dp.destroy && g_dp.last_error;
     if (!g_backend_vmm) SHIM_ERR("%s lacks the vgpu_vmem_* entry points", path);
     else start_mover();
 }
@@ -431,6 +451,7 @@ typedef struct {
     CUcontext ctx;  /* dup > 0: the context standing in for a primary context */
     int refs;
     int col0, ncols; /* its columns (limit[], sm_limit[], used[]) of the cache file: one, or — merged — all of that GPU's */
+    int spill_only;  /* the peer GPU of the spill tier where it cannot be hidden (see build_vdev): a device with no memory to give */
 } vdev_t;
 static vdev_t g_vdev[VGPU_MAX_DEVICES];
 static int g_nvdev;
@@ -497,14 +518,30 @@ static int build_vdev(void) {  /* needs a successful cuInit: -> 0 (and nothing l
         for (int i = 0; i < nwant && g_ncols < VGPU_MAX_DEVICES; ++i) {
             if (strcasecmp(want[i], text) != 0) continue;
             if (merge && k > 0) ++g_vdev[g_nvdev - 1].ncols;
-            else g_vdev[g_nvdev++] = (vdev_t){p, k, NULL, 0, g_ncols, 1};
+            else g_vdev[g_nvdev++] = (vdev_t){p, k, NULL, 0, g_ncols, 1, 0};
             ++k;
             ++g_ncols;
         }
     }
+    /* The spill tier's peer GPU is open to the driver but is not one of the container's vGPUs.  A driver-API program
+     * simply does not get it (it is not in the table).  The CUDA runtime cannot be lied to about the device count (it
+     * cross-checks private driver tables, see merge_shared), so a runtime client sees it as one more device at the end
+     * with a quota of one byte: nothing can be allocated there, and NVML — which frameworks count GPUs with — still
+     * shows the vGPUs only. */
+    const char *peer = getenv("VGPU_OVERSUB_PEER");
+    if (g_nvdev > 0 && merge && peer && strncasecmp(peer, "GPU-", 4) == 0)
+        for (int p = 0; p < real && g_nvdev < VGPU_MAX_DEVICES; ++p) {
+            unsigned char u[16];
+            char text[64];
+            if (!get_cuDeviceGetUuid() || real_cuDeviceGetUuid(u, p) != 0) continue;
+            uuid_text(u, text, sizeof(text));
+            int named = strcasecmp(text, peer) != 0;
+            for (int i = 0; i < nwant; ++i) named |= strcasecmp(want[i], text) == 0;
+            if (!named) g_vdev[g_nvdev++] = (vdev_t){p, 0, NULL, 0, VGPU_MAX_DEVICES - 1, 0, 1};
+        }
     if (g_nvdev == 0) {
         if (nwant > 0) SHIM_ERR("NVIDIA_DEVICE_MAP names no GPU this container can see: devices are not remapped");
-        for (int p = 0; p < real; ++p) g_vdev[g_nvdev++] = (vdev_t){p, 0, NULL, 0, p, 1};
+        for (int p = 0; p < real; ++p) g_vdev[g_nvdev++] = (vdev_t){p, 0, NULL, 0, p, 1, 0};
         g_ncols = nwant > 0 ? 0 : real;  /* a map that matches nothing: the column count differs from the map's, quota off */
     }
     g_remap = g_nvdev != real;
@@ -544,6 +581,7 @@ static int first_vdev_of(int phys) {
 static int col_of(int vdev) { return (g_remap && vdev >= 0 && vdev < g_nvdev) ? g_vdev[vdev].col0 : vdev; }
 static uint64_t q_limit(int vdev) {
     if (!g_remap || vdev < 0 || vdev >= g_nvdev) return region_limit(vdev);
+    if (g_vdev[vdev].spill_only) return 1;  /* one byte: every allocation is over quota */
     uint64_t t = 0;
     for (int c = g_vdev[vdev].col0; c < g_vdev[vdev].col0 + g_vdev[vdev].ncols; ++c) {
         if (region_limit(c) == 0) return 0;  /* one unlimited vGPU makes the merged device unlimited */
@@ -559,6 +597,7 @@ static uint64_t q_usage(int vdev) {
 }
 static uint64_t q_sm_limit(int vdev) {
     if (!g_remap || vdev < 0 || vdev >= g_nvdev) return region_sm_limit(vdev);
+    if (g_vdev[vdev].spill_only) return 100;
     uint64_t t = 0;
     for (int c = g_vdev[vdev].col0; c < g_vdev[vdev].col0 + g_vdev[vdev].ncols; ++c) {
         uint64_t p = region_sm_limit(c);
@@ -574,11 +613,16 @@ typedef struct alloc_node {
     size_t len;
     int dev;
     void *vmem;  /* VMM-backed (oversubscribe backend) */
+    uint64_t last_use;   /* residency clock (paged mode) */
+    uint64_t epoch;      /* the launch / copy that needs it right now: not a victim */
+    int windowed;        /* larger than the GPU can hold at once: residency by prefetch hints only */
     struct alloc_node *next, *prev;
 } alloc_node_t;
 static alloc_node_t *g_head, *g_tail;
 static size_t g_nalloc;
 static pthread_mutex_t g_alloc_mu = PTHREAD_MUTEX_INITIALIZER;
+static pthread_mutex_t g_res_mu = PTHREAD_MUTEX_INITIALIZER;  /* residency of VMM-backed allocations (taken before g_alloc_mu) */
+static void vmm_quiesce(void);
 
 static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
     alloc_node_t *a = (alloc_node_t *)malloc(sizeof(*a));
@@ -586,6 +630,8 @@ static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
     a->len = n;
     a->dev = dev;
     a->vmem = vmem;
+    a->last_use = a->epoch = 0;
+    a->windowed = 0;
     a->next = NULL;
     a->prev = g_tail;
     if (g_tail) g_tail->next = a; else g_head = a;
@@ -632,6 +678,8 @@ static int oom_check(int dev, size_t addon) {
     }
 }
 
+static int vmm_alloc(int dev, size_t n, CUdeviceptr *p);  /* residency section, below */
+
 /* add_chunk@0x40b73 (route = 0) and add_chunk_only@0x41011 (route = 1: caller already allocated) */
 static int add_chunk(CUdeviceptr *p, size_t n) {
     int dev = 0;
@@ -642,24 +690,7 @@ static int add_chunk(CUdeviceptr *p, size_t n) {
         cuMemAlloc_v2_t f = get_cuMemAlloc_v2();
         rc = f ? f(p, n) : 3;
     } else if (g_backend_vmm) {
-        const uint64_t chunks = (n + IPCSIZE - 1) / IPCSIZE;
-        void *h = NULL, *base = NULL;
-        tl_bypass = 1;
-        /* spill tiers: VGPU_OVERSUB_PEER=<gpu> puts an idle peer GPU's HBM (NVLink P2P) in front of pinned host RAM */
-        const char *pe = getenv("VGPU_OVERSUB_PEER");
-        int vrc = (pe && *pe && g_dp.create_tiered)
-                      ? g_dp.create_tiered(phys_of(dev), n, chunks * IPCSIZE, atoi(pe), chunks * IPCSIZE, chunks * IPCSIZE, &h)
-                      : g_dp.create(phys_of(dev), n, chunks * IPCSIZE, 2 /* VGPU_TIER_HOST */, -1, chunks * IPCSIZE, &h);
-        if (vrc == 0) vrc = g_dp.ensure(h, 0, chunks);
-        if (vrc == 0) vrc = g_dp.base(h, &base);
-        if (vrc != 0) {
-            SHIM_ERR("vmm backend: %s", g_dp.last_error());
-            if (h) g_dp.destroy(h);
-        }
-        tl_bypass = 0;
-        if (vrc != 0) return 2;
-        *p = (CUdeviceptr)(uintptr_t)base;
-        track_vmem(*p, n, dev, h);
+        if (vmm_alloc(dev, n, p) != 0) return 2;
         region_add_usage(col_of(dev), n, VGPU_USE_DATA);
         return 0;
     } else {
@@ -697,10 +728,13 @@ EXPORT CUresult cuMemAlloc_v2(CUdeviceptr *dptr, size_t bytesize) {
     if (tl_bypass) return get_cuMemAlloc_v2()(dptr, bytesize);
     ensure_initialized();
     pthread_once(&g_post_once, post_init);
-    wait_running();
+    gate_enter();
+    if (g_backend_vmm) pthread_mutex_lock(&g_res_mu);  /* lock order: residency, then the allocation list */
     pthread_mutex_lock(&g_alloc_mu);
     int rc = add_chunk(dptr, bytesize);  /* allocate_raw@0x4157c: -1 on quota OOM, returned verbatim */
     pthread_mutex_unlock(&g_alloc_mu);
+    if (g_backend_vmm) pthread_mutex_unlock(&g_res_mu);
+    gate_exit();
     return rc;
 }
 EXPORT CUresult cuMemAlloc(CUdeviceptr *dptr, size_t bytesize) { return cuMemAlloc_v2(dptr, bytesize); }
@@ -744,15 +778,19 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
     if (tl_bypass) return get_cuMemFree_v2()(dptr);
     ensure_initialized();
     if (dptr == 0) return 0;  /* cuMemFree_v2@0x32e5d */
+    const int vmm = g_backend_vmm;
+    if (vmm) pthread_mutex_lock(&g_res_mu);
     pthread_mutex_lock(&g_alloc_mu);
     alloc_node_t *a = g_head;
     while (a && a->addr != dptr) a = a->next;  /* remove_chunk@0x413dd: exact base match */
     if (!a) {
         pthread_mutex_unlock(&g_alloc_mu);
+        if (vmm) pthread_mutex_unlock(&g_res_mu);
         return -1;
     }
     CUresult rc;
     if (a->vmem) {
+        vmm_quiesce();  /* like cuMemFree: what was queued on the memory is done before it goes */
         tl_bypass = 1;
         rc = g_dp.destroy(a->vmem) == 0 ? 0 : 999;
         tl_bypass = 0;
@@ -767,6 +805,7 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
     size_t len = a->len;
     free(a);
     pthread_mutex_unlock(&g_alloc_mu);
+    if (vmm) pthread_mutex_unlock(&g_res_mu);
     region_rm_usage(col_of(dev), len, VGPU_USE_DATA);
     return rc;
 }
@@ -783,8 +822,9 @@ EXPORT CUresult cuMemGetInfo_v2(size_t *free_b, size_t *total_b) {
     cuMemGetInfo_v2_t f = get_cuMemGetInfo_v2();
     if (limit == 0) {
         rc = f ? f(free_b, total_b) : 3;
+        if (rc != 0) return rc;      /* nothing was written: leave the caller's values alone */
         *free_b = *total_b - usage;  /* quirk a17: free = total - usage when unlimited */
-        return rc;
+        return 0;
     }
     if (limit < usage) return 1;
     if (f) f(free_b, total_b);  /* the reference calls through and overwrites (@0x377c9) */
@@ -1314,6 +1354,390 @@ EXPORT CUresult cuCtxPopCurrent_v2(CUcontext *pctx) {
 EXPORT CUresult cuCtxPopCurrent(CUcontext *pctx) { return cuCtxPopCurrent_v2(pctx); }
 EXPORT CUresult cuCtxPushCurrent(CUcontext ctx) { return cuCtxPushCurrent_v2(ctx); }
 
+/* ------------------------------------------------------------------ residency under oversubscription
+ * (VGPU_OVERSUB_BACKEND=vmm)  What the reference gets from UVM page faults — an application whose allocations add up
+ * to more than the HBM it can have — without page faults: every allocation above 2 MiB is a range of the
+ * virtual-device-memory manager, and WHICH ranges are backed by HBM is decided at the calls that can touch them.
+ *   - While everything fits, allocations are backed at once and no call pays anything ("unpaged": one shared lock).
+ *   - From the first allocation that does not fit, the process is "paged": a kernel launch scans its argument
+ *     buffer (cuFuncGetParamInfo gives each parameter's size) for words that point into a managed range — into
+ *     structs passed by value as well — and makes those ranges resident before the launch; the 1-D / 2-D / 3-D copy
+ *     and memset calls do the same for exactly the bytes they name; a graph launch needs every range.  Room is made
+ *     by spilling the least recently used ranges that the call at hand does not need (spill kernel -> tier: the
+ *     named peer GPU's HBM first, pinned host RAM second), after draining the contexts of this process.
+ *   - cuMemPrefetchAsync / cuMemAdvise stay the explicit controls, and are the ONLY way to page a range that is
+ *     larger than the GPU itself ("windowed": a launch cannot know which part of it a kernel will read).
+ * What this cannot see: pointers a kernel finds in device memory (pointer tables of batched BLAS, device-side
+ * linked structures), arguments baked into a captured graph after the ranges moved, and peer / IPC access to the
+ * ranges.  Such a program keeps its working set resident with prefetch hints, or stays on the managed backend.
+ * Locks: g_mode_rw (shared by every unpaged call, exclusive for the switch to paged), then g_res_mu (paged calls,
+ * from the residency decision to the driver call it protects), then g_alloc_mu. */
+REAL(CUresult, cuCtxSynchronize, void)
+static pthread_rwlock_t g_mode_rw = PTHREAD_RWLOCK_INITIALIZER;
+static volatile int g_vmm_paged;
+static uint64_t g_res_clock, g_res_epoch;
+static CUdeviceptr g_vmm_lo = ~0ull, g_vmm_hi;  /* envelope of every managed range ever made: cheap reject for the scan */
+static uint64_t g_peer_left = ~0ull;             /* VGPU_OVERSUB_PEER_MB: what this process may still put on the peer */
+
+static uint64_t env_mb(const char *name, uint64_t dflt) {
+    const char *e = getenv(name);
+    return (e && *e) ? strtoull(e, NULL, 0) << 20 : dflt;
+}
+static uint64_t vmm_reserve(void) { return env_mb("VGPU_OVERSUB_RESERVE_MB", 1ull << 30); }
+
+static int res_begin(void) {  /* 0: no managed ranges in this process, 1: unpaged (shared), 2: paged (g_res_mu held) */
+    if (!g_backend_vmm) return 0;
+    if (!g_vmm_paged) {
+        pthread_rwlock_rdlock(&g_mode_rw);
+        if (!g_vmm_paged) return 1;
+        pthread_rwlock_unlock(&g_mode_rw);
+    }
+    pthread_mutex_lock(&g_res_mu);
+    return 2;
+}
+static void res_end(int m) {
+    if (m == 1) pthread_rwlock_unlock(&g_mode_rw);
+    else if (m == 2) pthread_mutex_unlock(&g_res_mu);
+}
+static void vmm_go_paged(void) {  /* waits for the unpaged calls in flight: after it every call decides residency */
+    if (g_vmm_paged) return;
+    pthread_rwlock_wrlock(&g_mode_rw);
+    g_vmm_paged = 1;
+    pthread_rwlock_unlock(&g_mode_rw);
+    SHIM_INFO("oversubscribed: managed allocations no longer fit the GPU together, residency is decided per call from here on");
+}
+
+/* everything this process has queued, in every context it owns on the GPU, is done */
+static void vmm_quiesce(void) {
+    const int was = tl_bypass;
+    tl_bypass = 1;
+    if (get_cuCtxSynchronize()) real_cuCtxSynchronize();
+    CUcontext cur = NULL, popped;
+    if (get_cuCtxGetCurrent()) real_cuCtxGetCurrent(&cur);
+    CUcontext seen[2 * VGPU_MAX_DEVICES + CTX_REG_MAX];
+    int n = 0;
+    for (int d = 0; d < VGPU_MAX_DEVICES; ++d) {
+        if (g_green_state[d] == 1 && g_green_ctx[d]) seen[n++] = g_green_ctx[d];
+        if (g_primary_ctx[d]) seen[n++] = g_primary_ctx[d];
+    }
+    for (int i = 0; i < g_nvdev; ++i)
+        if (g_vdev[i].ctx) seen[n++] = g_vdev[i].ctx;
+    for (int i = 0; i < g_ctx_reg_n; ++i) seen[n++] = g_ctx_reg[i].ctx;
+    for (int i = 0; i < n; ++i) {
+        int dup = seen[i] == cur;
+        for (int k = 0; k < i; ++k) dup |= seen[k] == seen[i];
+        if (dup || !get_cuCtxPushCurrent_v2() || !get_cuCtxPopCurrent_v2()) continue;
+        if (real_cuCtxPushCurrent_v2(seen[i]) == 0) {
+            real_cuCtxSynchronize();
+            real_cuCtxPopCurrent_v2(&popped);
+        }
+    }
+    tl_bypass = was;
+}
+
+static uint64_t node_chunks(const alloc_node_t *a) { return (a->len + IPCSIZE - 1) / IPCSIZE; }
+static uint64_t node_resident(alloc_node_t *a) {  /* chunks backed by HBM right now */
+    uint64_t miss = 0;
+    g_dp.missing(a->vmem, 0, node_chunks(a), &miss);
+    return node_chunks(a) > miss ? node_chunks(a) - miss : 0;
+}
+/* the managed range that contains p (g_alloc_mu held) */
+static alloc_node_t *vmm_find(CUdeviceptr p) {
+    if (p < g_vmm_lo || p >= g_vmm_hi) return NULL;
+    for (alloc_node_t *a = g_head; a; a = a->next)
+        if (a->vmem && p >= a->addr && p < a->addr + node_chunks(a) * IPCSIZE) return a;
+    return NULL;
+}
+/* least recently used range with something resident that the call at hand (epoch) does not need */
+static alloc_node_t *vmm_victim(uint64_t epoch) {
+    alloc_node_t *best = NULL;
+    for (alloc_node_t *a = g_head; a; a = a->next)
+        if (a->vmem && a->epoch != epoch && (!best || a->last_use < best->last_use) && node_resident(a) > 0) best = a;
+    return best;
+}
+static int vmm_evict_node(alloc_node_t *v) {
+    vmm_quiesce();
+    SHIM_INFO("oversubscribed: spilling range 0x%llx (%zu MiB, last used at tick %lu)", v->addr, v->len >> 20, (unsigned long)v->last_use);
+    int rc = g_dp.evict(v->vmem, 0, node_chunks(v));
+    if (rc != 0) SHIM_ERR("vmm backend evict: %s", g_dp.last_error());
+    return rc;
+}
+
+/* Make chunks [first, first+n) of `a` resident for the call `epoch`.  g_res_mu and g_alloc_mu held.  -> 0 or a VGPU_E_* */
+static int vmm_make_resident(alloc_node_t *a, uint64_t first, uint64_t n, uint64_t epoch) {
+    uint64_t miss = 0;
+    const int was = tl_bypass;
+    tl_bypass = 1;
+    a->last_use = ++g_res_clock;
+    a->epoch = epoch;
+    int rc = g_dp.missing(a->vmem, first, n, &miss);
+    if (rc != 0 || miss == 0) {
+        tl_bypass = was;
+        return rc;
+    }
+    const uint64_t cap = env_mb("VGPU_OVERSUB_RESIDENT_MB", 0);  /* operator's bound on this vGPU's resident managed bytes */
+    for (;;) {
+        size_t fr = 0, tot = 0;
+        if (get_cuMemGetInfo_v2()) real_cuMemGetInfo_v2(&fr, &tot);
+        int tight = fr < miss * IPCSIZE + vmm_reserve();
+        if (!tight && cap) {
+            uint64_t res = 0;
+            for (alloc_node_t *k = g_head; k; k = k->next)
+                if (k->vmem) res += node_resident(k) * IPCSIZE;
+            tight = res + miss * IPCSIZE > cap;
+        }
+        if (tight) {
+            alloc_node_t *v = vmm_victim(epoch);
+            if (v && vmm_evict_node(v) == 0) continue;
+        }
+        rc = g_dp.ensure(a->vmem, first, n);
+        if (rc == -3 /* VGPU_E_NOMEM */) {
+            alloc_node_t *v = vmm_victim(epoch);
+            if (v && vmm_evict_node(v) == 0) continue;
+        }
+        break;
+    }
+    if (rc != 0) SHIM_ERR("vmm backend: cannot make 0x%llx + %lu chunks resident: %s", a->addr, (unsigned long)n, g_dp.last_error());
+    tl_bypass = was;
+    return rc;
+}
+
+/* The peer GPU of the spill tier as a driver ordinal: VGPU_OVERSUB_PEER=<GPU UUID> (kept visible to the driver behind
+ * the vGPU's own GPUs by narrow_visible_devices, hidden from the application by the virtual-device table) or, for
+ * tests, a plain driver ordinal.  -1: none. */
+static int vmm_peer_ordinal(void) {
+    static int cached = -2;
+    if (cached != -2) return cached;
+    cached = -1;
+    const char *pe = getenv("VGPU_OVERSUB_PEER");
+    if (!pe || !*pe) return cached;
+    int n = 0;
+    if (!get_cuDeviceGetCount() || real_cuDeviceGetCount(&n) != 0) return cached;
+    if (strncasecmp(pe, "GPU-", 4) != 0) {
+        int o = atoi(pe);
+        if (o >= 0 && o < n) cached = o;
+    } else if (get_cuDeviceGetUuid()) {
+        for (int i = 0; i < n && cached < 0; ++i) {
+            unsigned char u[16];
+            char txt[VGPU_UUID_LEN];
+            if (real_cuDeviceGetUuid(u, i) != 0) continue;
+            uuid_text(u, txt, sizeof(txt));
+            if (strcasecmp(txt, pe) == 0) cached = i;
+        }
+    }
+    if (cached < 0) SHIM_ERR("VGPU_OVERSUB_PEER=%s names no GPU this process can open: spilling to pinned host RAM only", pe);
+    else g_peer_left = env_mb("VGPU_OVERSUB_PEER_MB", ~0ull);
+    return cached;
+}
+
+/* cuMemAlloc of n > 2 MiB bytes on the managed route.  g_res_mu and g_alloc_mu held. */
+static int vmm_alloc(int dev, size_t n, CUdeviceptr *p) {
+    const uint64_t chunks = (n + IPCSIZE - 1) / IPCSIZE, bytes = chunks * IPCSIZE;
+    size_t fr = 0, tot = 0;
+    if (get_cuMemGetInfo_v2()) real_cuMemGetInfo_v2(&fr, &tot);
+    const uint64_t reserve = vmm_reserve();
+    uint64_t cap = tot > 2 * reserve ? tot - reserve : tot / 2;  /* what a single range may ever have resident */
+    const uint64_t op_cap = env_mb("VGPU_OVERSUB_RESIDENT_MB", 0);
+    if (op_cap && op_cap < cap) cap = op_cap;
+    cap -= cap % IPCSIZE;
+    const int windowed = bytes > cap;
+    const int phys = phys_of(dev), peer = vmm_peer_ordinal();
+    uint64_t peer_bytes = 0;
+    if (peer >= 0 && peer != phys && g_peer_left >= IPCSIZE) {
+        peer_bytes = bytes < g_peer_left ? bytes : g_peer_left - g_peer_left % IPCSIZE;
+        if (g_peer_left != ~0ull) g_peer_left -= peer_bytes;
+    }
+    void *h = NULL, *base = NULL;
+    tl_bypass = 1;
+    int vrc = g_dp.create_tiered(phys, n, windowed ? cap : bytes, peer, peer_bytes, bytes, &h);
+    if (vrc == 0) vrc = g_dp.base(h, &base);
+    if (vrc == 0 && !g_vmm_paged && !windowed && fr >= bytes + reserve && !(op_cap && op_cap < bytes)) {
+        vrc = g_dp.ensure(h, 0, chunks);  /* it fits: back it now, as cuMemAlloc would */
+        if (vrc == -3) vrc = 0;           /* ... it does not after all: page it in at its first use */
+    }
+    tl_bypass = 0;
+    if (vrc != 0) {
+        SHIM_ERR("vmm backend: %s", g_dp.last_error());
+        tl_bypass = 1;
+        if (h) g_dp.destroy(h);
+        tl_bypass = 0;
+        return vrc;
+    }
+    *p = (CUdeviceptr)(uintptr_t)base;
+    track_vmem(*p, n, dev, h);
+    g_tail->windowed = windowed;
+    g_tail->last_use = ++g_res_clock;
+    if (*p < g_vmm_lo) g_vmm_lo = *p;
+    if (*p + bytes > g_vmm_hi) g_vmm_hi = *p + bytes;
+    uint64_t miss = 0;
+    tl_bypass = 1;
+    g_dp.missing(h, 0, chunks, &miss);
+    tl_bypass = 0;
+    if (miss) vmm_go_paged();
+    return 0;
+}
+
+/* ---- what a call needs: launches (argument scan), copies (exact bytes), graphs (everything) */
+typedef CUresult (*paraminfo_t)(void *, size_t, size_t *, size_t *);
+#define PSCAN_MAX 48
+typedef struct { void *fn; int n; unsigned short size[PSCAN_MAX]; } pscan_t;
+static pscan_t g_pscan[1024];  /* by kernel handle, under g_res_mu */
+static const pscan_t *kernel_params(void *fn) {
+    static paraminfo_t by_func, by_kernel;
+    static int looked;
+    if (!looked) {
+        by_func = (paraminfo_t)cuda_sym("cuFuncGetParamInfo");
+        by_kernel = (paraminfo_t)cuda_sym("cuKernelGetParamInfo");
+        looked = 1;
+    }
+    pscan_t *e = &g_pscan[((uintptr_t)fn >> 4) & 1023];
+    if (e->fn == fn) return e;
+    e->fn = fn;
+    e->n = -1;  /* unknown layout: the caller falls back to "every range" */
+    int no_params = 0;
+    const int was = tl_bypass;
+    tl_bypass = 1;
+    for (int pass = 0; pass < 2; ++pass) {  /* a CUfunction first, then the same handle as a CUkernel */
+        paraminfo_t q = pass ? by_kernel : by_func;
+        if (!q) continue;
+        int n = 0;
+        size_t off = 0, size = 0;
+        CUresult r;
+        while (n < PSCAN_MAX && (r = q(fn, (size_t)n, &off, &size)) == 0) e->size[n++] = (unsigned short)(size > 4096 ? 4096 : size);
+        if (n > 0) {
+            e->n = n;
+            break;
+        }
+        no_params |= r == 1;  /* CUDA_ERROR_INVALID_VALUE at index 0: a kernel that takes nothing */
+    }
+    if (e->n < 0 && no_params) e->n = 0;
+    tl_bypass = was;
+    return e;
+}
+
+typedef struct { alloc_node_t *a[64]; int n; } need_t;
+static void need_word(need_t *nd, uint64_t w, uint64_t epoch) {
+    alloc_node_t *a = vmm_find((CUdeviceptr)w);
+    if (!a || a->epoch == epoch) return;
+    a->epoch = epoch;  /* from here on not a victim of this call */
+    if (nd->n < 64) nd->a[nd->n++] = a;
+}
+static int need_commit(need_t *nd, uint64_t epoch) {
+    int rc = 0;
+    for (int i = 0; i < nd->n && rc == 0; ++i)
+        if (!nd->a[i]->windowed) rc = vmm_make_resident(nd->a[i], 0, node_chunks(nd->a[i]), epoch);
+        else nd->a[i]->last_use = ++g_res_clock;
+    return rc;
+}
+static int vmm_need_all(uint64_t epoch) {  /* a graph launch: its kernels' arguments are not ours to see */
+    need_t nd = {.n = 0};
+    for (alloc_node_t *a = g_head; a; a = a->next)
+        if (a->vmem && nd.n < 64) {
+            a->epoch = epoch;
+            nd.a[nd.n++] = a;
+        }
+    return need_commit(&nd, epoch);
+}
+/* g_res_mu held; takes g_alloc_mu.  -> 0, or nonzero when the ranges the launch names cannot all be resident */
+static int vmm_scan_launch(void *fn, void **params, void **extra) {
+    need_t nd = {.n = 0};
+    pthread_mutex_lock(&g_alloc_mu);
+    const uint64_t epoch = ++g_res_epoch;
+    int rc = 0;
+    const unsigned char *buf = NULL;
+    size_t buf_n = 0;
+    for (void **x = extra; x && *x; x += 2) {  /* CU_LAUNCH_PARAM_BUFFER_POINTER = 1, _SIZE = 2, END = 0 */
+        if (*x == (void *)1) buf = (const unsigned char *)x[1];
+        else if (*x == (void *)2) buf_n = *(size_t *)x[1];
+    }
+    if (buf && buf_n) {
+        for (size_t o = 0; o + 8 <= buf_n; o += 8) {
+            uint64_t w;
+            memcpy(&w, buf + o, 8);
+            need_word(&nd, w, epoch);
+        }
+    } else if (params) {
+        const pscan_t *ps = kernel_params(fn);
+        if (ps->n < 0) {
+            rc = vmm_need_all(epoch);  /* no parameter layout for this handle: be safe */
+        } else {
+            for (int i = 0; i < ps->n; ++i)
+                for (size_t o = 0; o + 8 <= ps->size[i]; o += 8) {
+                    uint64_t w;
+                    memcpy(&w, (const unsigned char *)params[i] + o, 8);
+                    need_word(&nd, w, epoch);
+                }
+        }
+    }
+    if (rc == 0) rc = need_commit(&nd, epoch);
+    pthread_mutex_unlock(&g_alloc_mu);
+    return rc;
+}
+/* the bytes [p, p+n) if they lie in a managed range (g_res_mu and g_alloc_mu held) */
+static int vmm_touch(CUdeviceptr p, size_t n, uint64_t epoch) {
+    alloc_node_t *a = vmm_find(p);
+    if (!a) return 0;
+    const uint64_t first = (p - a->addr) / IPCSIZE;
+    uint64_t last = (p + (n ? n : 1) - 1 - a->addr) / IPCSIZE;
+    if (last >= node_chunks(a)) last = node_chunks(a) - 1;
+    return vmm_make_resident(a, first, last - first + 1, epoch);
+}
+/* descriptor-based copies: the whole range around a device pointer (pitches and heights are not worth the parsing) */
+static int vmm_touch_whole(CUdeviceptr p, uint64_t epoch) {
+    alloc_node_t *a = p ? vmm_find(p) : NULL;
+    if (!a || a->windowed) return 0;
+    return vmm_make_resident(a, 0, node_chunks(a), epoch);
+}
+static int vmm_touch_desc(const void *desc, size_t src_type, size_t src_dev, size_t dst_type, size_t dst_dev, uint64_t epoch) {
+    const unsigned char *d = (const unsigned char *)desc;
+    int rc = 0;
+    if (!d) return 0;
+    unsigned st, dt;
+    CUdeviceptr sp, dp;
+    memcpy(&st, d + src_type, 4);
+    memcpy(&dt, d + dst_type, 4);
+    memcpy(&sp, d + src_dev, 8);
+    memcpy(&dp, d + dst_dev, 8);
+    if (st == 2 /* CU_MEMORYTYPE_DEVICE */ || st == 4 /* UNIFIED */) rc = vmm_touch_whole(sp, epoch);
+    if (rc == 0 && (dt == 2 || dt == 4)) rc = vmm_touch_whole(dp, epoch);
+    return rc;
+}
+#define TOUCH_2D(p) vmm_touch_desc(p, 16, 32, 72, 88, ep_)    /* CUDA_MEMCPY2D: srcMemoryType, srcDevice, dstMemoryType, dstDevice */
+#define TOUCH_3D(p) vmm_touch_desc(p, 32, 48, 120, 136, ep_)  /* CUDA_MEMCPY3D (and _PEER: same leading layout) */
+
+/* cuVGPUOversubStats: {chunks spilled to the peer tier, to the host tier, restored, checksum failures, resident now,
+ * managed in total, paged mode} summed over this process's managed ranges — for tests, the validator and the monitor */
+typedef struct {
+    uint64_t chunks_total, chunks_resident, chunks_spilled, resident_limit, tier_slots, evictions, fetches, checksum_failures;
+    double evict_ms, fetch_ms;
+    uint64_t evictions_peer, evictions_host, restore_retries;
+} shim_vmem_stats_t;
+EXPORT int cuVGPUOversubStats(uint64_t out[8]) {
+    typedef int (*stats_t)(void *, shim_vmem_stats_t *);
+    static stats_t st;
+    memset(out, 0, 8 * sizeof(uint64_t));
+    if (!g_backend_vmm) return -1;
+    if (!st) st = (stats_t)real_dlsym(g_dp.lib, "vgpu_vmem_stats");
+    if (!st) return -1;
+    pthread_mutex_lock(&g_res_mu);
+    pthread_mutex_lock(&g_alloc_mu);
+    for (alloc_node_t *a = g_head; a; a = a->next)
+        if (a->vmem) {
+            shim_vmem_stats_t v;
+            if (st(a->vmem, &v) != 0) continue;
+            out[0] += v.evictions_peer;
+            out[1] += v.evictions_host;
+            out[2] += v.fetches;
+            out[3] += v.checksum_failures;
+            out[4] += v.chunks_resident;
+            out[5] += v.chunks_total;
+        }
+    out[6] = (uint64_t)g_vmm_paged;
+    pthread_mutex_unlock(&g_alloc_mu);
+    pthread_mutex_unlock(&g_res_mu);
+    return 0;
+}
+
 /* cuLaunchKernel@0x37c2b: the suspend gate stays; rate_limiter@0x463b1 is gone — the SM cap is
  * spatial (green context), so there is nothing to do per launch. */
 /* What is left of rate_limiter@0x463b1 at every launch once the host pid is known (pidfound): the monitor's lever
@@ -1327,75 +1751,124 @@ static void launch_mark(void) {
     if (r->recent_kernel != 2) r->recent_kernel = 2;  /* no write when it is already there: the line is shared by every process */
 }
 
-EXPORT CUresult cuLaunchKernel(void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by,
-                               unsigned bz, unsigned shm, void *stream, void **params, void **extra) {
-    if (tl_bypass) return get_cuLaunchKernel()(fn, gx, gy, gz, bx, by, bz, shm, stream, params, extra);
-    ensure_initialized();
-    wait_running();
-    launch_mark();
-    cuLaunchKernel_t f = get_cuLaunchKernel();
-    return f ? f(fn, gx, gy, gz, bx, by, bz, shm, stream, params, extra) : 3;
-}
+/* One body for the launch entry points and their per-thread-default-stream twins: gate, activity mark, residency of
+ * what the arguments name (paged mode only), then the driver's function of the same name. */
+#define LAUNCH_BODY(SYM, CALL, FN, PARAMS, EXTRA)                      \
+    if (tl_bypass) return f ? f CALL : 3;                              \
+    ensure_initialized();                                              \
+    launch_mark();                                                     \
+    gate_enter();                                                      \
+    const int m_ = res_begin();                                        \
+    CUresult rc_ = 0;                                                  \
+    if (m_ == 2 && vmm_scan_launch(FN, PARAMS, EXTRA) != 0) rc_ = 2;   \
+    if (rc_ == 0) rc_ = f ? f CALL : 3;                                \
+    res_end(m_);                                                       \
+    gate_exit();                                                       \
+    return rc_;
 
-EXPORT CUresult cuLaunchKernelEx(const void *config, void *fn, void **params, void **extra) {
-    typedef CUresult (*ex_t)(const void *, void *, void **, void **);
-    static ex_t f;
-    if (!f) f = (ex_t)cuda_sym("cuLaunchKernelEx");
-    if (!tl_bypass) {
-        ensure_initialized();
-        wait_running();
-        launch_mark();
+#define LAUNCH_HOOK(name)                                                                                              \
+    EXPORT CUresult name(void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz,       \
+                         unsigned shm, void *stream, void **params, void **extra) {                                    \
+        static cuLaunchKernel_t f;                                                                                     \
+        if (!f) f = (cuLaunchKernel_t)cuda_sym(#name);                                                                 \
+        LAUNCH_BODY(name, (fn, gx, gy, gz, bx, by, bz, shm, stream, params, extra), fn, params, extra)                 \
     }
-    return f ? f(config, fn, params, extra) : 3;
-}
+LAUNCH_HOOK(cuLaunchKernel)
+LAUNCH_HOOK(cuLaunchKernel_ptsz)
+
+#define LAUNCH_EX_HOOK(name)                                                                      \
+    EXPORT CUresult name(const void *config, void *fn, void **params, void **extra) {             \
+        typedef CUresult (*ex_t)(const void *, void *, void **, void **);                         \
+        static ex_t f;                                                                            \
+        if (!f) f = (ex_t)cuda_sym(#name);                                                        \
+        LAUNCH_BODY(name, (config, fn, params, extra), fn, params, extra)                         \
+    }
+LAUNCH_EX_HOOK(cuLaunchKernelEx)
+LAUNCH_EX_HOOK(cuLaunchKernelEx_ptsz)
+
+#define LAUNCH_COOP_HOOK(name)                                                                                          \
+    EXPORT CUresult name(void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz,        \
+                         unsigned shm, void *st, void **params) {                                                       \
+        typedef CUresult (*co_t)(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **); \
+        static co_t f;                                                                                                  \
+        if (!f) f = (co_t)cuda_sym(#name);                                                                              \
+        LAUNCH_BODY(name, (fn, gx, gy, gz, bx, by, bz, shm, st, params), fn, params, NULL)                              \
+    }
+LAUNCH_COOP_HOOK(cuLaunchCooperativeKernel)
+LAUNCH_COOP_HOOK(cuLaunchCooperativeKernel_ptsz)
 
 /* The suspend gate on the copy / memset entry points, as in the reference (cuda/memory.c runs
  * wait_status_self in every cuMemcpy / cuMemset hook): while a vGPU is suspended — and, with the VMM
  * backend, until its data is back behind its pointers — nothing may touch device memory. */
-#define GATED(name, params, args)                                     \
-    EXPORT CUresult name params {                                     \
+/* GATED2(name, twin suffix, parameters, arguments, TOUCH): the entry point and its per-thread-default-stream twin
+ * (name##_ptds for the synchronous forms, name##_ptsz for the stream-ordered ones; the driver exports both and hands
+ * the twin out when cuGetProcAddress is asked with CU_GET_PROC_ADDRESS_PER_THREAD_DEFAULT_STREAM, or when a program is
+ * built with --default-stream per-thread and links it directly).  Both wait at the gate, count themselves in flight,
+ * and — in paged mode — make the device bytes they name resident first (TOUCH, an expression over vmm_touch / TOUCH_2D
+ * / TOUCH_3D with ep_ as the epoch; 0 = nothing to touch). */
+#define GATED_ONE(fname, sym, params, args, TOUCH)                    \
+    EXPORT CUresult fname params {                                    \
         typedef CUresult(*fn_t) params;                               \
         static fn_t f;                                                \
-        if (!f) f = (fn_t)cuda_sym(#name);                            \
-        if (!tl_bypass) {                                             \
-            ensure_initialized();                                     \
-            wait_running();                                           \
+        if (!f) f = (fn_t)cuda_sym(sym);                              \
+        if (tl_bypass) return f ? f args : 3;                         \
+        ensure_initialized();                                         \
+        gate_enter();                                                 \
+        const int m_ = res_begin();                                   \
+        CUresult rc_ = 0;                                             \
+        if (m_ == 2) {                                                \
+            pthread_mutex_lock(&g_alloc_mu);                          \
+            const uint64_t ep_ = ++g_res_epoch;                       \
+            (void)ep_;                                                \
+            if ((TOUCH) != 0) rc_ = 2;                                \
+            pthread_mutex_unlock(&g_alloc_mu);                        \
         }                                                             \
-        return f ? f args : 3;                                        \
+        if (rc_ == 0) rc_ = f ? f args : 3;                           \
+        res_end(m_);                                                  \
+        gate_exit();                                                  \
+        return rc_;                                                   \
     }
-GATED(cuMemcpy, (CUdeviceptr d, CUdeviceptr s_, size_t n), (d, s_, n))
-GATED(cuMemcpyAsync, (CUdeviceptr d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st))
-GATED(cuMemcpyDtoH_v2, (void *d, CUdeviceptr s_, size_t n), (d, s_, n))
-GATED(cuMemcpyDtoHAsync_v2, (void *d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st))
-GATED(cuMemcpyHtoD_v2, (CUdeviceptr d, const void *s_, size_t n), (d, s_, n))
-GATED(cuMemcpyHtoDAsync_v2, (CUdeviceptr d, const void *s_, size_t n, void *st), (d, s_, n, st))
-GATED(cuMemcpyDtoD_v2, (CUdeviceptr d, CUdeviceptr s_, size_t n), (d, s_, n))
-GATED(cuMemcpyDtoDAsync_v2, (CUdeviceptr d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st))
-GATED(cuMemsetD8_v2, (CUdeviceptr d, unsigned char v, size_t n), (d, v, n))
-GATED(cuMemsetD8Async, (CUdeviceptr d, unsigned char v, size_t n, void *st), (d, v, n, st))
-GATED(cuMemsetD32_v2, (CUdeviceptr d, unsigned v, size_t n), (d, v, n))
-GATED(cuMemsetD32Async, (CUdeviceptr d, unsigned v, size_t n, void *st), (d, v, n, st))
-/* the rest of the family: descriptor-based, peer, 16-bit and 2-D forms, cooperative and graph launches */
-GATED(cuMemcpy2D_v2, (const void *p), (p))
-GATED(cuMemcpy2DUnaligned_v2, (const void *p), (p))
-GATED(cuMemcpy2DAsync_v2, (const void *p, void *st), (p, st))
-GATED(cuMemcpy3D_v2, (const void *p), (p))
-GATED(cuMemcpy3DAsync_v2, (const void *p, void *st), (p, st))
-GATED(cuMemcpy3DPeer, (const void *p), (p))
-GATED(cuMemcpy3DPeerAsync, (const void *p, void *st), (p, st))
-GATED(cuMemcpyPeer, (CUdeviceptr d, CUcontext dc, CUdeviceptr s_, CUcontext sc, size_t n), (d, dc, s_, sc, n))
-GATED(cuMemcpyPeerAsync, (CUdeviceptr d, CUcontext dc, CUdeviceptr s_, CUcontext sc, size_t n, void *st), (d, dc, s_, sc, n, st))
-GATED(cuMemsetD16_v2, (CUdeviceptr d, unsigned short v, size_t n), (d, v, n))
-GATED(cuMemsetD16Async, (CUdeviceptr d, unsigned short v, size_t n, void *st), (d, v, n, st))
-GATED(cuMemsetD2D8_v2, (CUdeviceptr d, size_t pitch, unsigned char v, size_t w, size_t h), (d, pitch, v, w, h))
-GATED(cuMemsetD2D8Async, (CUdeviceptr d, size_t pitch, unsigned char v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st))
-GATED(cuMemsetD2D16_v2, (CUdeviceptr d, size_t pitch, unsigned short v, size_t w, size_t h), (d, pitch, v, w, h))
-GATED(cuMemsetD2D16Async, (CUdeviceptr d, size_t pitch, unsigned short v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st))
-GATED(cuMemsetD2D32_v2, (CUdeviceptr d, size_t pitch, unsigned v, size_t w, size_t h), (d, pitch, v, w, h))
-GATED(cuMemsetD2D32Async, (CUdeviceptr d, size_t pitch, unsigned v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st))
-GATED(cuLaunchCooperativeKernel, (void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz, unsigned shm, void *st, void **params),
-      (fn, gx, gy, gz, bx, by, bz, shm, st, params))
-GATED(cuGraphLaunch, (void *graph, void *st), (graph, st))
+#define GATED2(name, sfx, params, args, TOUCH)        \
+    GATED_ONE(name, #name, params, args, TOUCH)       \
+    GATED_ONE(name##sfx, #name #sfx, params, args, TOUCH)
+#define T1(p, n) vmm_touch(p, n, ep_)
+#define T2(p, q, n) (vmm_touch(p, n, ep_) | vmm_touch(q, n, ep_))
+GATED2(cuMemcpy, _ptds, (CUdeviceptr d, CUdeviceptr s_, size_t n), (d, s_, n), T2(d, s_, n))
+GATED2(cuMemcpyAsync, _ptsz, (CUdeviceptr d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st), T2(d, s_, n))
+GATED2(cuMemcpyDtoH_v2, _ptds, (void *d, CUdeviceptr s_, size_t n), (d, s_, n), T1(s_, n))
+GATED2(cuMemcpyDtoHAsync_v2, _ptsz, (void *d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st), T1(s_, n))
+GATED2(cuMemcpyHtoD_v2, _ptds, (CUdeviceptr d, const void *s_, size_t n), (d, s_, n), T1(d, n))
+GATED2(cuMemcpyHtoDAsync_v2, _ptsz, (CUdeviceptr d, const void *s_, size_t n, void *st), (d, s_, n, st), T1(d, n))
+GATED2(cuMemcpyDtoD_v2, _ptds, (CUdeviceptr d, CUdeviceptr s_, size_t n), (d, s_, n), T2(d, s_, n))
+GATED2(cuMemcpyDtoDAsync_v2, _ptsz, (CUdeviceptr d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st), T2(d, s_, n))
+GATED2(cuMemsetD8_v2, _ptds, (CUdeviceptr d, unsigned char v, size_t n), (d, v, n), T1(d, n))
+GATED2(cuMemsetD8Async, _ptsz, (CUdeviceptr d, unsigned char v, size_t n, void *st), (d, v, n, st), T1(d, n))
+GATED2(cuMemsetD32_v2, _ptds, (CUdeviceptr d, unsigned v, size_t n), (d, v, n), T1(d, 4 * n))
+GATED2(cuMemsetD32Async, _ptsz, (CUdeviceptr d, unsigned v, size_t n, void *st), (d, v, n, st), T1(d, 4 * n))
+/* the rest of the family: descriptor-based, peer, array, 16-bit and 2-D forms, graph launches */
+GATED2(cuMemcpy2D_v2, _ptds, (const void *p), (p), TOUCH_2D(p))
+GATED2(cuMemcpy2DUnaligned_v2, _ptds, (const void *p), (p), TOUCH_2D(p))
+GATED2(cuMemcpy2DAsync_v2, _ptsz, (const void *p, void *st), (p, st), TOUCH_2D(p))
+GATED2(cuMemcpy3D_v2, _ptds, (const void *p), (p), TOUCH_3D(p))
+GATED2(cuMemcpy3DAsync_v2, _ptsz, (const void *p, void *st), (p, st), TOUCH_3D(p))
+GATED2(cuMemcpy3DPeer, _ptds, (const void *p), (p), TOUCH_3D(p))
+GATED2(cuMemcpy3DPeerAsync, _ptsz, (const void *p, void *st), (p, st), TOUCH_3D(p))
+GATED2(cuMemcpyPeer, _ptds, (CUdeviceptr d, CUcontext dc, CUdeviceptr s_, CUcontext sc, size_t n), (d, dc, s_, sc, n), T2(d, s_, n))
+GATED2(cuMemcpyPeerAsync, _ptsz, (CUdeviceptr d, CUcontext dc, CUdeviceptr s_, CUcontext sc, size_t n, void *st), (d, dc, s_, sc, n, st), T2(d, s_, n))
+/* device <-> CUDA array: exported and gated by the reference as well (nm -D vgpu/libvgpu.so) */
+GATED2(cuMemcpyAtoD_v2, _ptds, (CUdeviceptr d, void *arr, size_t off, size_t n), (d, arr, off, n), T1(d, n))
+GATED2(cuMemcpyDtoA_v2, _ptds, (void *arr, size_t off, CUdeviceptr s_, size_t n), (arr, off, s_, n), T1(s_, n))
+GATED2(cuMemsetD16_v2, _ptds, (CUdeviceptr d, unsigned short v, size_t n), (d, v, n), T1(d, 2 * n))
+GATED2(cuMemsetD16Async, _ptsz, (CUdeviceptr d, unsigned short v, size_t n, void *st), (d, v, n, st), T1(d, 2 * n))
+GATED2(cuMemsetD2D8_v2, _ptds, (CUdeviceptr d, size_t pitch, unsigned char v, size_t w, size_t h), (d, pitch, v, w, h), T1(d, pitch * h))
+GATED2(cuMemsetD2D8Async, _ptsz, (CUdeviceptr d, size_t pitch, unsigned char v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st), T1(d, pitch * h))
+GATED2(cuMemsetD2D16_v2, _ptds, (CUdeviceptr d, size_t pitch, unsigned short v, size_t w, size_t h), (d, pitch, v, w, h), T1(d, pitch * h))
+GATED2(cuMemsetD2D16Async, _ptsz, (CUdeviceptr d, size_t pitch, unsigned short v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st), T1(d, pitch * h))
+GATED2(cuMemsetD2D32_v2, _ptds, (CUdeviceptr d, size_t pitch, unsigned v, size_t w, size_t h), (d, pitch, v, w, h), T1(d, pitch * h))
+GATED2(cuMemsetD2D32Async, _ptsz, (CUdeviceptr d, size_t pitch, unsigned v, size_t w, size_t h, void *st), (d, pitch, v, w, h, st), T1(d, pitch * h))
+GATED2(cuGraphLaunch, _ptsz, (void *graph, void *st), (graph, st), vmm_need_all(ep_))
+EXPORT CUresult cuMemcpyAtoD(CUdeviceptr d, void *arr, size_t off, size_t n) { return cuMemcpyAtoD_v2(d, arr, off, n); }
+EXPORT CUresult cuMemcpyDtoA(void *arr, size_t off, CUdeviceptr s_, size_t n) { return cuMemcpyDtoA_v2(arr, off, s_, n); }
 
 /* cuMipmappedArrayCreate (a20): same allocate-then-check_oom pattern as the host allocations */
 EXPORT CUresult cuMipmappedArrayCreate(void **handle, const void *desc, unsigned levels) {
@@ -1660,35 +2133,36 @@ static int loc_to_phys(shim_mem_location_t *l) { return l->type != 1 || to_phys(
  * unlike UVM nothing faults back in — the data is out until it is prefetched to the device again); prefetch to the
  * device = make the range resident again, checksum-verified.  Synchronous with respect to `stream`.
  * -> 1 handled (rc set), 0 not one of ours */
-typedef CUresult (*stream_sync_t)(void *);
 static int vmm_prefetch(CUdeviceptr p, size_t n, int to_device, void *stream, CUresult *rc) {
+    (void)stream;
     if (!g_backend_vmm || tl_bypass) return 0;
+    gate_enter();
+    pthread_mutex_lock(&g_res_mu);
     pthread_mutex_lock(&g_alloc_mu);
-    alloc_node_t *a = g_head;
-    while (a && !(a->vmem && p >= a->addr && p < a->addr + a->len)) a = a->next;
-    if (!a) {
-        pthread_mutex_unlock(&g_alloc_mu);
-        return 0;
-    }
-    const uint64_t chunks = (a->len + IPCSIZE - 1) / IPCSIZE;
-    int vrc = 0;
-    tl_bypass = 1;
-    if (to_device) {
+    alloc_node_t *a = vmm_find(p);
+    int handled = a != NULL, vrc = 0;
+    if (a) {
+        const uint64_t chunks = node_chunks(a);
         const uint64_t first = (p - a->addr) / IPCSIZE;
         uint64_t last = (p + (n ? n : 1) - 1 - a->addr) / IPCSIZE;
         if (last >= chunks) last = chunks - 1;
-        vrc = g_dp.ensure(a->vmem, first, last - first + 1);
-    } else if (p == a->addr && n >= a->len) {
-        static stream_sync_t sync;
-        if (!sync) sync = (stream_sync_t)cuda_sym("cuStreamSynchronize");
-        if (sync) sync(stream);  /* what was queued on it may still use the data */
-        vrc = g_dp.evict(a->vmem, 0, chunks);
+        if (to_device) {
+            vrc = vmm_make_resident(a, first, last - first + 1, ++g_res_epoch);
+        } else if ((p == a->addr && n >= a->len) || a->windowed) {
+            /* out: the whole allocation, or — for a range the GPU cannot hold at once — the blocks the call names */
+            vmm_quiesce();  /* what was queued may still use the data */
+            tl_bypass = 1;
+            vrc = g_dp.evict(a->vmem, a->windowed ? first : 0, a->windowed ? last - first + 1 : chunks);
+            if (vrc != 0) SHIM_ERR("vmm backend prefetch: %s", g_dp.last_error());
+            tl_bypass = 0;
+            if (vrc == 0) vmm_go_paged();
+        }
     }
-    if (vrc != 0) SHIM_ERR("vmm backend prefetch: %s", g_dp.last_error());
-    tl_bypass = 0;
     pthread_mutex_unlock(&g_alloc_mu);
+    pthread_mutex_unlock(&g_res_mu);
+    gate_exit();
     *rc = vrc == 0 ? 0 : 999;
-    return 1;
+    return handled;
 }
 
 EXPORT CUresult cuMemPrefetchAsync(CUdeviceptr p, size_t n, CUdevice d, void *stream) {
@@ -1704,8 +2178,7 @@ EXPORT CUresult cuMemPrefetchAsync(CUdeviceptr p, size_t n, CUdevice d, void *st
 static int vmm_backed(CUdeviceptr p) {
     if (!g_backend_vmm || tl_bypass) return 0;
     pthread_mutex_lock(&g_alloc_mu);
-    alloc_node_t *a = g_head;
-    while (a && !(a->vmem && p >= a->addr && p < a->addr + a->len)) a = a->next;
+    alloc_node_t *a = vmm_find(p);
     pthread_mutex_unlock(&g_alloc_mu);
     return a != NULL;
 }
@@ -2156,6 +2629,33 @@ static const hook_t g_hooks[] = {
     {"cuLaunchCooperativeKernel", (void *)cuLaunchCooperativeKernel}, {"cuGraphLaunch", (void *)cuGraphLaunch},
     {"cuLaunchKernel", (void *)cuLaunchKernel},
     {"cuLaunchKernelEx", (void *)cuLaunchKernelEx},
+    {"cuMemcpyAtoD", (void *)cuMemcpyAtoD_v2}, {"cuMemcpyAtoD_v2", (void *)cuMemcpyAtoD_v2},
+    {"cuMemcpyDtoA", (void *)cuMemcpyDtoA_v2}, {"cuMemcpyDtoA_v2", (void *)cuMemcpyDtoA_v2},
+    /* per-thread-default-stream twins (looked up as <name>_ptsz / <name>_ptds, see find_hook_for_version) */
+    {"cuLaunchKernel_ptsz", (void *)cuLaunchKernel_ptsz}, {"cuLaunchKernelEx_ptsz", (void *)cuLaunchKernelEx_ptsz},
+    {"cuLaunchCooperativeKernel_ptsz", (void *)cuLaunchCooperativeKernel_ptsz}, {"cuGraphLaunch_ptsz", (void *)cuGraphLaunch_ptsz},
+    {"cuMemcpy_ptds", (void *)cuMemcpy_ptds}, {"cuMemcpyAsync_ptsz", (void *)cuMemcpyAsync_ptsz},
+    {"cuMemcpyDtoH_ptds", (void *)cuMemcpyDtoH_v2_ptds}, {"cuMemcpyDtoH_v2_ptds", (void *)cuMemcpyDtoH_v2_ptds},
+    {"cuMemcpyDtoHAsync_ptsz", (void *)cuMemcpyDtoHAsync_v2_ptsz}, {"cuMemcpyDtoHAsync_v2_ptsz", (void *)cuMemcpyDtoHAsync_v2_ptsz},
+    {"cuMemcpyHtoD_ptds", (void *)cuMemcpyHtoD_v2_ptds}, {"cuMemcpyHtoD_v2_ptds", (void *)cuMemcpyHtoD_v2_ptds},
+    {"cuMemcpyHtoDAsync_ptsz", (void *)cuMemcpyHtoDAsync_v2_ptsz}, {"cuMemcpyHtoDAsync_v2_ptsz", (void *)cuMemcpyHtoDAsync_v2_ptsz},
+    {"cuMemcpyDtoD_ptds", (void *)cuMemcpyDtoD_v2_ptds}, {"cuMemcpyDtoD_v2_ptds", (void *)cuMemcpyDtoD_v2_ptds},
+    {"cuMemcpyDtoDAsync_ptsz", (void *)cuMemcpyDtoDAsync_v2_ptsz}, {"cuMemcpyDtoDAsync_v2_ptsz", (void *)cuMemcpyDtoDAsync_v2_ptsz},
+    {"cuMemcpyAtoD_ptds", (void *)cuMemcpyAtoD_v2_ptds}, {"cuMemcpyAtoD_v2_ptds", (void *)cuMemcpyAtoD_v2_ptds},
+    {"cuMemcpyDtoA_ptds", (void *)cuMemcpyDtoA_v2_ptds}, {"cuMemcpyDtoA_v2_ptds", (void *)cuMemcpyDtoA_v2_ptds},
+    {"cuMemsetD8_ptds", (void *)cuMemsetD8_v2_ptds}, {"cuMemsetD8_v2_ptds", (void *)cuMemsetD8_v2_ptds}, {"cuMemsetD8Async_ptsz", (void *)cuMemsetD8Async_ptsz},
+    {"cuMemsetD16_ptds", (void *)cuMemsetD16_v2_ptds}, {"cuMemsetD16_v2_ptds", (void *)cuMemsetD16_v2_ptds}, {"cuMemsetD16Async_ptsz", (void *)cuMemsetD16Async_ptsz},
+    {"cuMemsetD32_ptds", (void *)cuMemsetD32_v2_ptds}, {"cuMemsetD32_v2_ptds", (void *)cuMemsetD32_v2_ptds}, {"cuMemsetD32Async_ptsz", (void *)cuMemsetD32Async_ptsz},
+    {"cuMemsetD2D8_ptds", (void *)cuMemsetD2D8_v2_ptds}, {"cuMemsetD2D8_v2_ptds", (void *)cuMemsetD2D8_v2_ptds}, {"cuMemsetD2D8Async_ptsz", (void *)cuMemsetD2D8Async_ptsz},
+    {"cuMemsetD2D16_ptds", (void *)cuMemsetD2D16_v2_ptds}, {"cuMemsetD2D16_v2_ptds", (void *)cuMemsetD2D16_v2_ptds}, {"cuMemsetD2D16Async_ptsz", (void *)cuMemsetD2D16Async_ptsz},
+    {"cuMemsetD2D32_ptds", (void *)cuMemsetD2D32_v2_ptds}, {"cuMemsetD2D32_v2_ptds", (void *)cuMemsetD2D32_v2_ptds}, {"cuMemsetD2D32Async_ptsz", (void *)cuMemsetD2D32Async_ptsz},
+    {"cuMemcpy2D_ptds", (void *)cuMemcpy2D_v2_ptds}, {"cuMemcpy2D_v2_ptds", (void *)cuMemcpy2D_v2_ptds},
+    {"cuMemcpy2DUnaligned_ptds", (void *)cuMemcpy2DUnaligned_v2_ptds}, {"cuMemcpy2DUnaligned_v2_ptds", (void *)cuMemcpy2DUnaligned_v2_ptds},
+    {"cuMemcpy2DAsync_ptsz", (void *)cuMemcpy2DAsync_v2_ptsz}, {"cuMemcpy2DAsync_v2_ptsz", (void *)cuMemcpy2DAsync_v2_ptsz},
+    {"cuMemcpy3D_ptds", (void *)cuMemcpy3D_v2_ptds}, {"cuMemcpy3D_v2_ptds", (void *)cuMemcpy3D_v2_ptds},
+    {"cuMemcpy3DAsync_ptsz", (void *)cuMemcpy3DAsync_v2_ptsz}, {"cuMemcpy3DAsync_v2_ptsz", (void *)cuMemcpy3DAsync_v2_ptsz},
+    {"cuMemcpy3DPeer_ptds", (void *)cuMemcpy3DPeer_ptds}, {"cuMemcpy3DPeerAsync_ptsz", (void *)cuMemcpy3DPeerAsync_ptsz},
+    {"cuMemcpyPeer_ptds", (void *)cuMemcpyPeer_ptds}, {"cuMemcpyPeerAsync_ptsz", (void *)cuMemcpyPeerAsync_ptsz},
     {"cuGetExportTable", (void *)cuGetExportTable},
     {"cuDeviceGetCount", (void *)cuDeviceGetCount}, {"cuDeviceGet", (void *)cuDeviceGet}, {"cuCtxGetDevice", (void *)cuCtxGetDevice},
     {"cuDeviceGetName", (void *)cuDeviceGetName}, {"cuDeviceGetAttribute", (void *)cuDeviceGetAttribute},
@@ -2222,12 +2722,23 @@ static void *find_hook_for_version(const char *name, int ver, unsigned long long
     return find_hook(name);
 }
 
-/* Launch / copy / memset entry points have per-thread-default-stream twins (_ptsz / _ptds) that the
- * driver selects from the flags of cuGetProcAddress.  Our gates forward to the legacy-stream
- * functions, so a caller that asks for the per-thread flavour gets the driver's own function (no
- * gate) rather than a hook that would silently change its stream semantics. */
+/* Launch / copy / memset / graph-launch entry points have per-thread-default-stream twins (_ptsz / _ptds) that the
+ * driver selects from the flags of cuGetProcAddress.  A caller that asks for the per-thread flavour gets OUR twin of
+ * the same name, which gates and forwards to the driver's twin (its stream semantics are the driver's). */
+static void *find_ptds_twin(const char *symbol, unsigned long long flags) {
+    if (!(flags & 2ull /* CU_GET_PROC_ADDRESS_PER_THREAD_DEFAULT_STREAM */)) return NULL;
+    char twin[96];
+    snprintf(twin, sizeof(twin), "%s_ptsz", symbol);
+    void *h = find_hook(twin);
+    if (!h) {
+        snprintf(twin, sizeof(twin), "%s_ptds", symbol);
+        h = find_hook(twin);
+    }
+    return h;
+}
+/* the few per-thread forms we do not wrap go to the driver untouched (never to a legacy-stream hook) */
 static int wants_ptds(const char *symbol, unsigned long long flags) {
-    return (flags & 2ull /* CU_GET_PROC_ADDRESS_PER_THREAD_DEFAULT_STREAM */) &&
+    return (flags & 2ull) &&
            (strncmp(symbol, "cuMemcpy", 8) == 0 || strncmp(symbol, "cuMemset", 8) == 0 || strncmp(symbol, "cuLaunch", 8) == 0 ||
             strncmp(symbol, "cuMemPrefetch", 13) == 0 || strncmp(symbol, "cuGraphLaunch", 13) == 0);
 }
@@ -2244,7 +2755,8 @@ EXPORT void *dlsym(void *handle, const char *symbol) {
 
 EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsigned long long flags) {
     ensure_initialized();
-    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver, flags) : NULL;
+    void *h = symbol ? find_ptds_twin(symbol, flags) : NULL;
+    if (!h) h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver, flags) : NULL;
     if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;
@@ -2256,7 +2768,8 @@ EXPORT CUresult cuGetProcAddress(const char *symbol, void **pfn, int ver, unsign
 
 EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, unsigned long long flags, int *status) {
     ensure_initialized();
-    void *h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver, flags) : NULL;
+    void *h = symbol ? find_ptds_twin(symbol, flags) : NULL;
+    if (!h) h = (symbol && !wants_ptds(symbol, flags)) ? find_hook_for_version(symbol, ver, flags) : NULL;
     if (shim_log_level() > 4) fprintf(stderr, "[4pdvGPU Trace]: cuGetProcAddress_v2(%s, ver=%d) -> %s\n", symbol, ver, h ? "hook" : "driver");
     if (h) {
         *pfn = h;
@@ -2272,16 +2785,17 @@ EXPORT CUresult cuGetProcAddress_v2(const char *symbol, void **pfn, int ver, uns
  * spill every VMM-backed allocation to the host tier and release its HBM.  Resume: map fresh
  * HBM behind the same addresses, restore, verify checksums.  Returns chunks-level errors as
  * CUDA_ERROR_UNKNOWN (999). */
-REAL(CUresult, cuCtxSynchronize, void)
 static CUresult move_all(int out) {
     CUresult rc = 0;
+    pthread_mutex_lock(&g_res_mu);
     pthread_mutex_lock(&g_alloc_mu);
     tl_bypass = 1;
-    if (out && get_cuCtxSynchronize()) real_cuCtxSynchronize();
+    if (out) vmm_quiesce();  /* every context this process owns, not only the one current here */
     for (alloc_node_t *a = g_head; a; a = a->next)
-        if (a->vmem) {
+        if (a->vmem && !(a->windowed && !out)) {  /* a windowed range comes back by its owner's prefetch hints */
             const uint64_t chunks = (a->len + IPCSIZE - 1) / IPCSIZE;
-            int vrc = out ? g_dp.evict(a->vmem, 0, chunks) : g_dp.ensure(a->vmem, 0, chunks);
+            int vrc = out ? g_dp.evict(a->vmem, 0, chunks) : vmm_make_resident(a, 0, chunks, ++g_res_epoch);
+            tl_bypass = 1;
             if (vrc != 0) {
                 SHIM_ERR("vmm backend %s: %s", out ? "suspend" : "resume", g_dp.last_error());
                 rc = 999;
@@ -2289,16 +2803,27 @@ static CUresult move_all(int out) {
         }
     tl_bypass = 0;
     pthread_mutex_unlock(&g_alloc_mu);
+    pthread_mutex_unlock(&g_res_mu);
     return rc;
 }
-EXPORT CUresult cuVGPUSuspend(void) { return g_backend_vmm ? move_all(1) : 801 /* NOT_SUPPORTED */; }
-EXPORT CUresult cuVGPUResume(void) { return g_backend_vmm ? move_all(0) : 801; }
+/* the in-process form: the caller's own threads are its business, but the gate still closes around the move */
+static CUresult move_all_gated(int out) {
+    if (!out) return move_all(0);
+    g_data_out = 1;
+    while (g_inflight > 0) usleep(100);
+    CUresult rc = move_all(1);
+    g_data_out = 0;
+    return rc;
+}
+EXPORT CUresult cuVGPUSuspend(void) { return g_backend_vmm ? move_all_gated(1) : 801 /* NOT_SUPPORTED */; }
+EXPORT CUresult cuVGPUResume(void) { return g_backend_vmm ? move_all_gated(0) : 801; }
 
 /* Signal-driven form of the same (the reference's protocol: an external monitor sends SIGUSR2 to
  * suspend a vGPU process and SIGUSR1 to resume it, sig_swap_stub / sig_restore_stub).  The
- * handlers only flip the status word and post a semaphore; this thread does the work.  New
- * launches and allocations of the application park at the gates (wait_running) from the moment
- * the status turns 2 until the data is back. */
+ * handlers only flip the status word and post a semaphore; this thread does the work.  The gate closes
+ * the moment the status turns 2 (g_data_out); the mover then waits until no call that passed the gate
+ * earlier is still on its way into the driver (g_inflight == 0) before it drains the GPU and unmaps
+ * anything, and opens the gate again only when the data is back. */
 #include <semaphore.h>
 static sem_t g_mover_sem;
 static volatile int g_mover_target = 1;
@@ -2320,7 +2845,7 @@ static void *mover_main(void *arg) {
         }
         const int target = g_mover_target;
         if (target == 2 && !out) {
-            usleep(20000);  /* let threads that were past the gate finish issuing */
+            while (g_inflight > 0) usleep(100);  /* calls that were past the gate have reached the driver and returned */
             move_all(1);
             out = 1;
         } else if (target == 1 && out) {

@@ -447,6 +447,19 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
     return result;
 }
 
+// Chunks of [first, first+n) that a vgpu_vmem_ensure of the same range would have to bring in (their block is not
+// resident): what a caller needs to know to make room BEFORE it asks.
+int vgpu_vmem_missing(void *handle, uint64_t first, uint64_t n, uint64_t *chunks) {
+    Vmem *v = static_cast<Vmem *>(handle);
+    if (!v || !chunks || first + n > v->nchunks) return fail(VGPU_E_INVAL, "chunk range out of bounds");
+    *chunks = 0;
+    if (n == 0) return VGPU_OK;
+    std::lock_guard<std::mutex> lk(v->mu);
+    for (size_t b = first / v->bc; b <= (first + n - 1) / v->bc; ++b)
+        if (v->blocks[b].state != kResident) *chunks += v->bc;
+    return VGPU_OK;
+}
+
 // Where a chunk lives right now: *tier = VGPU_TIER_LOCAL and *ptr = its address in the range while its block is
 // resident; the tier kind and the chunk's address inside that tier's slab while it is spilled; *ptr = NULL for a
 // block that was never touched.

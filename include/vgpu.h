@@ -271,6 +271,9 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n);
 /* Where chunk `chunk` lives right now: *tier = VGPU_TIER_LOCAL and its address in the range while resident, the tier
  * kind and its address inside that tier's slab while spilled, *ptr = NULL if never touched.  For tools and tests. */
 int vgpu_vmem_locate(void *handle, uint64_t chunk, int *tier, void **ptr);
+/* Chunks of [first, first+n) that are not resident now (what an ensure of the range would have to map or restore,
+ * counted in whole blocks): lets a caller that shares the GPU's HBM between several ranges make room first. */
+int vgpu_vmem_missing(void *handle, uint64_t first, uint64_t n, uint64_t *chunks);
 /* Push chunks [first, first+n) that are resident out to the tier and release their HBM. */
 int vgpu_vmem_evict(void *handle, uint64_t first, uint64_t n);
 int vgpu_vmem_stats(void *handle, vgpu_vmem_stats_t *out);

@@ -424,7 +424,7 @@ def test_an_unusable_cache_path_fails_closed():
 def test_cuGetProcAddress_hands_out_the_hook_with_the_abi_the_caller_asked_for():
     """An unsuffixed name asks for the newest ABI the given CUDA version knows: cuCtxCreate is _v2 / _v3 / _v4 depending
     on it, cuMemPrefetchAsync and cuMemAdvise change signature at 12.2, cuGetProcAddress itself at 12.0; per-thread
-    default stream callers get the driver's own copy / launch entry points and the _ptsz twins of the async allocator."""
+    default stream callers get the shim's _ptsz / _ptds twins of the copy / launch entry points and of the async allocator."""
     q = [("11030 0 cuCtxCreate", "cuCtxCreate_v2"), ("11040 0 cuCtxCreate", "cuCtxCreate_v3"), ("12090 0 cuCtxCreate", "cuCtxCreate_v4"),
          ("12010 0 cuMemPrefetchAsync", "cuMemPrefetchAsync"), ("12090 0 cuMemPrefetchAsync", "cuMemPrefetchAsync_v2"),
          ("12090 0 cuMemAdvise", "cuMemAdvise_v2"), ("11080 0 cuGetProcAddress", "cuGetProcAddress"), ("12000 0 cuGetProcAddress", "cuGetProcAddress_v2"),
@@ -433,10 +433,15 @@ def test_cuGetProcAddress_hands_out_the_hook_with_the_abi_the_caller_asked_for()
          ("12090 2 cuMemFreeAsync", "cuMemFreeAsync_ptsz"), ("12090 0 cuLaunchKernel", "cuLaunchKernel"), ("12090 0 cuMemcpy2DAsync", "cuMemcpy2DAsync_v2")]
     rep = H.run_trace(H.NEW_LIB, [(0, "procaddr " + a) for a, _ in q], {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP})["replies"]
     assert rep == [f"0 {sym}@libvgpu.so" for _, sym in q]
-    # per-thread-stream flavours of copies and launches, and anything not hooked, come straight from the driver
-    rep = H.run_trace(H.NEW_LIB, [(0, "procaddr 12090 2 cuLaunchKernel"), (0, "procaddr 12090 0 cuDriverGetVersion")],
+    # per-thread-default-stream flavours of copies and launches are the shim's own twins (they gate, then call the
+    # driver's twin); anything not hooked comes straight from the driver
+    rep = H.run_trace(H.NEW_LIB, [(0, "procaddr 12090 2 cuLaunchKernel"), (0, "procaddr 12090 2 cuMemcpyHtoDAsync"),
+                                  (0, "procaddr 12090 2 cuMemcpyDtoH"), (0, "procaddr 12090 2 cuGraphLaunch"),
+                                  (0, "procaddr 12090 0 cuDriverGetVersion")],
                       {"CUDA_DEVICE_MEMORY_LIMIT_0": "1g", **MAP})["replies"]
-    assert all(r.endswith("@libcuda.so.1") for r in rep), rep
+    assert rep[:4] == ["0 cuLaunchKernel_ptsz@libvgpu.so", "0 cuMemcpyHtoDAsync_v2_ptsz@libvgpu.so", "0 cuMemcpyDtoH_v2_ptds@libvgpu.so",
+                       "0 cuGraphLaunch_ptsz@libvgpu.so"], rep
+    assert rep[4].endswith("@libcuda.so.1"), rep
 
 
 GATE_PROBES = [("launch 4 128", True), (f"alloc {M} 9", True), (f"managed {M} 9", True), ("pitch 64 4 4 9", True), ("hostalloc 4096 9", True),
