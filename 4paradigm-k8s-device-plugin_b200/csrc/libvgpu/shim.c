@@ -1551,7 +1551,12 @@ static int vmm_alloc(int dev, size_t n, CUdeviceptr *p) {
     tl_bypass = 1;
     int vrc = g_dp.create_tiered(phys, n, windowed ? cap : bytes, peer, peer_bytes, bytes, &h);
     if (vrc == 0) vrc = g_dp.base(h, &base);
-    if (vrc == 0 && !g_vmm_paged && !windowed && fr >= bytes + reserve && !(op_cap && op_cap < bytes)) {
+    uint64_t res_now = 0;
+    if (op_cap)
+        for (alloc_node_t *k = g_head; k; k = k->next)
+            if (k->vmem) res_now += node_resident(k) * IPCSIZE;
+    tl_bypass = 1;
+    if (vrc == 0 && !g_vmm_paged && !windowed && fr >= bytes + reserve && !(op_cap && res_now + bytes > op_cap)) {
         vrc = g_dp.ensure(h, 0, chunks);  /* it fits: back it now, as cuMemAlloc would */
         if (vrc == -3) vrc = 0;           /* ... it does not after all: page it in at its first use */
     }

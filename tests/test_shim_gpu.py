@@ -632,3 +632,101 @@ def test_partition_index_from_the_plugin_gives_containers_disjoint_sms(cuda_dev)
     # the legacy single variable still works for every device
     c, err_c = _validator_smids({"VGPU_SM_PARTITION_INDEX": "2"})
     assert set(c["sm_ids"]) == sets[2] and "NOT coordinated" not in err_c
+
+
+OVERSUB_ENV = {"CUDA_OVERSUBSCRIBE": "true", "VGPU_OVERSUB_BACKEND": "vmm"}
+OVERSUB_WALK = """
+    import ctypes, json, torch
+    torch.cuda.init()
+    G = 1 << 30
+    N, SIZE = 10, 2 * G                       # 20 GiB of tensors; at most 6 GiB of them may be resident at once
+    ts = []
+    for i in range(N):
+        t = torch.empty(SIZE // 8, dtype=torch.int64, device="cuda")   # one cudaMalloc each (> the allocator's pooling sizes)
+        t.copy_(torch.arange(SIZE // 8, device="cuda", dtype=torch.int64) * (2654435761 + i))   # a launch that names t
+        ts.append(t)
+    want = [int(((torch.arange(1 << 20, dtype=torch.int64) * (2654435761 + i)).sum()).item()) for i in range(N)]
+    ok = True
+    for rnd in range(2):                      # two passes over everything, the second backwards
+        for i in (range(N) if rnd == 0 else reversed(range(N))):
+            ok &= int(ts[i][: 1 << 20].sum().item()) == want[i]      # a launch whose arguments point into ts[i]
+            ok &= int(ts[i][-1].item()) == (SIZE // 8 - 1) * (2654435761 + i)   # a plain D2H copy of its last bytes
+    two = int((ts[0][: 1 << 20] + ts[N - 1][: 1 << 20]).sum().item()) == want[0] + want[N - 1]   # one kernel, two ranges
+    free, total = torch.cuda.mem_get_info()
+    st = (ctypes.c_uint64 * 8)()
+    rc = ctypes.CDLL(None).cuVGPUOversubStats(st)
+    print(json.dumps({"ok": bool(ok), "two": bool(two), "rc": rc, "to_peer": st[0], "to_host": st[1], "restored": st[2], "bad": st[3],
+                      "resident": st[4], "managed": st[5], "paged": st[6], "free": free, "total": total}))
+"""
+
+
+def test_an_unmodified_program_larger_than_its_resident_share_is_paged_by_the_shim(cuda_dev):
+    """Transparent oversubscription (the reference: cuMemoryAllocate@0x32146 -> cuMemAllocManaged, UVM faults).  A PyTorch
+    program whose tensors add up to 20 GiB runs with 6 GiB of resident HBM for its managed ranges: nothing in the program
+    knows — the shim finds the ranges a launch or copy names (kernel arguments, copy operands), pages them in and spills
+    the least recently used ones to pinned host RAM with the spill / restore kernels.  Every byte checked."""
+    p = run_under_shim(OVERSUB_WALK, {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "30g", "VGPU_OVERSUB_RESIDENT_MB": "6144"}, timeout=900)
+    o = last_json(p)
+    print("transparent oversubscription:", o)
+    assert o["ok"] and o["two"] and o["rc"] == 0 and o["bad"] == 0, p.stderr[-3000:]
+    assert o["paged"] == 1 and o["to_host"] >= 7 * 1024 and o["restored"] >= 7 * 1024 and o["to_peer"] == 0
+    assert o["resident"] * 2 <= 6144 and o["managed"] * 2 >= 20 * 1024      # chunks of 2 MiB
+    assert o["total"] == 30 << 30 and o["total"] - o["free"] >= 20 << 30    # the quota still counts every byte, resident or not
+    assert "Device 0 OOM" not in p.stderr
+
+
+def test_oversubscription_spills_to_the_named_peer_gpu_first_then_to_host(cuda_dev):
+    """north_star tier order through the shim: VGPU_OVERSUB_PEER names an idle GPU by UUID; the shim keeps it open to the
+    driver (P2P needs both ends) and away from the application, spills there while the peer budget lasts, then to host."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("the peer tier needs 2 GPUs")
+    import pynvml
+    pynvml.nvmlInit()
+    uu = [pynvml.nvmlDeviceGetUUID(pynvml.nvmlDeviceGetHandleByIndex(i)) for i in range(2)]
+    uu = [u.decode() if isinstance(u, bytes) else u for u in uu]
+    env = {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "30g", "VGPU_OVERSUB_RESIDENT_MB": "6144", "NVIDIA_DEVICE_MAP": f"0:{uu[0]}",
+           "VGPU_OVERSUB_PEER": uu[1], "VGPU_OVERSUB_PEER_MB": "4096"}
+    p = run_under_shim(OVERSUB_WALK, env, timeout=900)
+    o = last_json(p)
+    print("oversubscription, peer then host:", o)
+    assert o["ok"] and o["two"] and o["bad"] == 0, p.stderr[-3000:]
+    assert o["to_peer"] >= 1024 and o["to_host"] >= 1024 and o["restored"] >= 7 * 1024
+    # the application was not given the peer: NVML (what frameworks count GPUs with) shows the vGPU only
+    q = run_under_shim("import torch, json; print(json.dumps({'n': torch.cuda.device_count()}))", env)
+    assert last_json(q)["n"] == 1
+
+
+def test_vmm_backend_leaves_a_cuCtxCreate_context_current_and_bills_its_device(cuda_dev):
+    """Driver-API program with a context of its own (not the primary one): managed allocations, a suspend and a resume
+    must leave that context current and the data intact (the manager works in the primary context internally)."""
+    code = """
+        import ctypes as C, json
+        cu = C.CDLL("libcuda.so.1")
+        assert cu.cuInit(0) == 0
+        dev, ctx, cur = C.c_int(), C.c_void_p(), C.c_void_p()
+        assert cu.cuDeviceGet(C.byref(dev), 0) == 0
+        assert cu.cuCtxCreate_v2(C.byref(ctx), 0, dev) == 0
+        n = 64 << 20
+        p = C.c_ulonglong()
+        rc_alloc = cu.cuMemAlloc_v2(C.byref(p), C.c_size_t(n))
+        cu.cuCtxGetCurrent(C.byref(cur)); same1 = cur.value == ctx.value
+        assert cu.cuMemsetD32_v2(p, 0x5EED1234, C.c_size_t(n // 4)) == 0
+        shim = C.CDLL(None)                      # the preloaded library's own entry points
+        rc_out = shim.cuVGPUSuspend()
+        cu.cuCtxGetCurrent(C.byref(cur)); same2 = cur.value == ctx.value
+        rc_in = shim.cuVGPUResume()
+        cu.cuCtxGetCurrent(C.byref(cur)); same3 = cur.value == ctx.value
+        host = (C.c_uint32 * (n // 4))()
+        rc_copy = cu.cuMemcpyDtoH_v2(host, p, C.c_size_t(n))
+        good = all(host[i] == 0x5EED1234 for i in range(0, n // 4, 4099))
+        free, total = C.c_size_t(), C.c_size_t()
+        cu.cuMemGetInfo_v2(C.byref(free), C.byref(total))
+        rc_free = cu.cuMemFree_v2(p)
+        print(json.dumps({"rc": [rc_alloc, rc_out, rc_in, rc_copy, rc_free], "same": [same1, same2, same3], "good": good,
+                          "billed": total.value - free.value}))
+    """
+    p = run_under_shim(code, {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "8g"})
+    o = last_json(p)
+    assert o["rc"] == [0, 0, 0, 0, 0] and o["same"] == [True, True, True] and o["good"], (o, p.stderr[-2000:])
+    assert o["billed"] >= 64 << 20
