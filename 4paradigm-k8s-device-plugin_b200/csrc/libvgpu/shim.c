@@ -2103,7 +2103,20 @@ EXPORT CUresult cuCtxGetDevice(CUdevice *dev) {
         return f ? f args : 3;                                        \
     }
 VDEV1(cuDeviceGetName, (char *name, int len, CUdevice d), (name, len, d), d)
-VDEV1(cuDeviceGetAttribute, (int *pi, int attrib, CUdevice d), (pi, attrib, d), d)
+/* CU_DEVICE_ATTRIBUTE_MULTIPROCESSOR_COUNT (16) inside an SM partition is the partition's size: code that sizes a
+ * cooperative or persistent grid as occupancy x SM count must not ask for more CTAs than the green context can
+ * co-schedule (CUDA_ERROR_COOPERATIVE_LAUNCH_TOO_LARGE) — the reference's temporal throttle never had that failure. */
+EXPORT CUresult cuDeviceGetAttribute(int *pi, int attrib, CUdevice d) {
+    typedef CUresult (*fn_t)(int *, int, CUdevice);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuDeviceGetAttribute");
+    const CUdevice v = d;
+    if (!tl_bypass && !to_phys(&d)) return 101;
+    CUresult rc = f ? f(pi, attrib, d) : 3;
+    if (rc == 0 && !tl_bypass && attrib == 16 && pi && v >= 0 && v < VGPU_MAX_DEVICES && g_green_state[v] == 1 && g_green_sms[v])
+        *pi = (int)g_green_sms[v];
+    return rc;
+}
 VDEV1(cuDeviceGetUuid, (unsigned char *uuid, CUdevice d), (uuid, d), d)
 VDEV1(cuDeviceGetUuid_v2, (unsigned char *uuid, CUdevice d), (uuid, d), d)
 VDEV1(cuDeviceGetLuid, (char *luid, unsigned *mask, CUdevice d), (luid, mask, d), d)

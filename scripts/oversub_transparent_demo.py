@@ -1,0 +1,98 @@
+#!/usr/bin/env python
+"""BASELINE config 4 with an UNMODIFIED program: one vGPU whose limit (300 GB) exceeds the GPU (180 GB).
+
+A plain PyTorch script allocates N tensors that add up to ~292 GB, writes every one, then reads all of them back twice
+(forwards, backwards) and checks the contents.  It runs under the preload shim with CUDA_OVERSUBSCRIBE=true and
+VGPU_OVERSUB_BACKEND=vmm; the shim decides at every launch / copy which ranges must be in HBM and spills the least
+recently used ones — to the idle peer GPU named by VGPU_OVERSUB_PEER while the peer budget lasts, then to pinned host
+RAM.  Prints one JSON line with the paging statistics and the rates seen by the program.
+
+    python scripts/oversub_transparent_demo.py [tensors] [GiB each] [peer budget GiB]
+"""
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import textwrap
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SHIM = os.path.join(ROOT, "4paradigm-k8s-device-plugin_b200", "libvgpu.so")
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 17
+GIB_EACH = float(sys.argv[2]) if len(sys.argv) > 2 else 16.0
+PEER_GIB = float(sys.argv[3]) if len(sys.argv) > 3 else 64.0
+
+WORKER = textwrap.dedent("""
+    import ctypes, json, sys, time, torch
+    n_t, gib = int(sys.argv[1]), float(sys.argv[2])
+    words = int(gib * (1 << 30)) // 8
+    torch.cuda.init()
+    step = 1 << 27
+    def fill(t, k):                                   # t[i] = i * (40503 + k), in place, 1 GiB of temporaries at most
+        for i in range(0, words, step):
+            m = min(step, words - i)
+            t[i:i + m] = torch.arange(i, i + m, device="cuda", dtype=torch.int64) * (40503 + k)
+    def bad(t, k):
+        b = 0
+        for i in range(0, words, step):
+            m = min(step, words - i)
+            b += int((t[i:i + m] != torch.arange(i, i + m, device="cuda", dtype=torch.int64) * (40503 + k)).sum().item())
+        return b
+    ts = []
+    t0 = time.perf_counter()
+    for k in range(n_t):
+        t = torch.empty(words, dtype=torch.int64, device="cuda")
+        fill(t, k)
+        ts.append(t)
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    wrong = 0
+    for k in range(n_t):
+        wrong += bad(ts[k], k)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    for k in reversed(range(n_t)):
+        wrong += bad(ts[k], k)
+    torch.cuda.synchronize()
+    t3 = time.perf_counter()
+    st = (ctypes.c_uint64 * 8)()
+    ctypes.CDLL(None).cuVGPUOversubStats(st)
+    free, total = torch.cuda.mem_get_info()
+    gb = n_t * words * 8 / 1e9
+    print(json.dumps({"tensors": n_t, "GiB_each": gib, "program_GB": round(gb, 1), "limit_GB": round(total / 1e9, 1), "wrong_words": wrong,
+                      "chunks_to_peer": st[0], "chunks_to_host": st[1], "chunks_restored": st[2], "checksum_failures": st[3],
+                      "resident_GB_at_end": round(st[4] * 2097152 / 1e9, 1), "paged": st[6],
+                      "write_pass_s": round(t1 - t0, 2), "read_pass_fwd_s": round(t2 - t1, 2), "read_pass_back_s": round(t3 - t2, 2),
+                      "write_pass_GBps": round(gb / (t1 - t0), 1), "read_pass_fwd_GBps": round(gb / (t2 - t1), 1),
+                      "read_pass_back_GBps": round(gb / (t3 - t2), 1)}), flush=True)
+""")
+
+
+def main():
+    import pynvml
+    pynvml.nvmlInit()
+    n_gpu = pynvml.nvmlDeviceGetCount()
+    uu = [pynvml.nvmlDeviceGetUUID(pynvml.nvmlDeviceGetHandleByIndex(i)) for i in range(n_gpu)]
+    uu = [u.decode() if isinstance(u, bytes) else u for u in uu]
+    td = tempfile.mkdtemp(prefix="vgpuover")
+    env = dict(os.environ)
+    env.update({"LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": os.path.join(td, "c.cache"), "LIBCUDA_LOG_LEVEL": "0",
+                "CUDA_OVERSUBSCRIBE": "true", "VGPU_OVERSUB_BACKEND": "vmm", "CUDA_DEVICE_MEMORY_LIMIT_0": "300000m",
+                "NVIDIA_DEVICE_MAP": f"0:{uu[0]}"})
+    if n_gpu > 1:
+        env.update({"VGPU_OVERSUB_PEER": uu[1], "VGPU_OVERSUB_PEER_MB": str(int(PEER_GIB * 1024))})
+    t0 = time.perf_counter()
+    p = subprocess.run([sys.executable, "-c", WORKER, str(N), str(GIB_EACH)], env=env, capture_output=True, text=True, timeout=3000)
+    wall = time.perf_counter() - t0
+    if p.returncode != 0:
+        print(p.stderr[-3000:], file=sys.stderr)
+        raise SystemExit(p.returncode)
+    o = json.loads(p.stdout.strip().splitlines()[-1])
+    o.update({"wall_s": round(wall, 1), "peer_tier": (f"GPU 1, budget {PEER_GIB} GiB" if n_gpu > 1 else None),
+              "host_mem_available_GB": round(int(next(l for l in open("/proc/meminfo") if l.startswith("MemAvailable")).split()[1]) / 1e6, 1)})
+    print(json.dumps(o))
+
+
+if __name__ == "__main__":
+    main()

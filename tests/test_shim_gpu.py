@@ -423,6 +423,7 @@ def test_sm_limit_becomes_a_green_context_partition(cuda_dev):
     free = last_json(run_under_shim(code, {"CUDA_DEVICE_SM_LIMIT": "100", "CUDA_DEVICE_MEMORY_LIMIT_0": "16g"}))
     assert capped["ok"] and free["ok"]
     assert free["sms"] == 0 and 0 < capped["sms"] <= 37            # 25 % of 148, granule-rounded down (32)
+    assert capped["mp"] == capped["sms"] and free["mp"] >= 100     # the SM-count attribute is the partition's inside one
     # spatial cap: a compute-bound GEMM gets roughly sms/148 of the machine, not all of it
     assert capped["tflops"] < 0.6 * free["tflops"], (capped, free)
 
