@@ -1687,6 +1687,10 @@ static int vmm_touch(CUdeviceptr p, size_t n, uint64_t epoch) {
     if (last >= node_chunks(a)) last = node_chunks(a) - 1;
     return vmm_make_resident(a, first, last - first + 1, epoch);
 }
+static int vmm_touch2(CUdeviceptr p, CUdeviceptr q, size_t n, uint64_t epoch) {
+    const int r = vmm_touch(p, n, epoch);
+    return r != 0 ? r : vmm_touch(q, n, epoch);
+}
 /* descriptor-based copies: the whole range around a device pointer (pitches and heights are not worth the parsing) */
 static int vmm_touch_whole(CUdeviceptr p, uint64_t epoch) {
     alloc_node_t *a = p ? vmm_find(p) : NULL;
@@ -1758,18 +1762,37 @@ static void launch_mark(void) {
 
 /* One body for the launch entry points and their per-thread-default-stream twins: gate, activity mark, residency of
  * what the arguments name (paged mode only), then the driver's function of the same name. */
+/* HBM that other tenants of the GPU hold is not ours to take: when the ranges a call needs do not fit and nothing of
+ * our own is left to spill, the call steps out of the gate (so that this process can itself be suspended meanwhile),
+ * waits and tries again — the node's monitor is expected to make room (monitor.Scheduler) — for VGPU_OVERSUB_WAIT_S
+ * seconds (default 60) before it fails with CUDA_ERROR_OUT_OF_MEMORY. */
+static int res_wait_retry(int *tries) {
+    static int max_tries = -1;
+    if (max_tries < 0) {
+        const char *e = getenv("VGPU_OVERSUB_WAIT_S");
+        max_tries = (e && *e ? atoi(e) : 60) * 10;
+    }
+    if (*tries >= max_tries) return 0;
+    if ((*tries)++ == 0) SHIM_WARN("waiting for HBM held by other tenants of this GPU (up to %d s)", max_tries / 10);
+    usleep(100000);
+    return 1;
+}
+
 #define LAUNCH_BODY(SYM, CALL, FN, PARAMS, EXTRA)                      \
     if (tl_bypass) return f ? f CALL : 3;                              \
     ensure_initialized();                                              \
     launch_mark();                                                     \
-    gate_enter();                                                      \
-    const int m_ = res_begin();                                        \
-    CUresult rc_ = 0;                                                  \
-    if (m_ == 2 && vmm_scan_launch(FN, PARAMS, EXTRA) != 0) rc_ = 2;   \
-    if (rc_ == 0) rc_ = f ? f CALL : 3;                                \
-    res_end(m_);                                                       \
-    gate_exit();                                                       \
-    return rc_;
+    for (int tries_ = 0;;) {                                           \
+        gate_enter();                                                  \
+        const int m_ = res_begin();                                    \
+        CUresult rc_ = 0;                                              \
+        const int r_ = m_ == 2 ? vmm_scan_launch(FN, PARAMS, EXTRA) : 0; \
+        if (r_ == 0) rc_ = f ? f CALL : 3;                             \
+        res_end(m_);                                                   \
+        gate_exit();                                                   \
+        if (r_ == -3 /* VGPU_E_NOMEM */ && res_wait_retry(&tries_)) continue; \
+        return r_ != 0 ? 2 : rc_;                                      \
+    }
 
 #define LAUNCH_HOOK(name)                                                                                              \
     EXPORT CUresult name(void *fn, unsigned gx, unsigned gy, unsigned gz, unsigned bx, unsigned by, unsigned bz,       \
@@ -1818,26 +1841,30 @@ LAUNCH_COOP_HOOK(cuLaunchCooperativeKernel_ptsz)
         if (!f) f = (fn_t)cuda_sym(sym);                              \
         if (tl_bypass) return f ? f args : 3;                         \
         ensure_initialized();                                         \
-        gate_enter();                                                 \
-        const int m_ = res_begin();                                   \
-        CUresult rc_ = 0;                                             \
-        if (m_ == 2) {                                                \
-            pthread_mutex_lock(&g_alloc_mu);                          \
-            const uint64_t ep_ = ++g_res_epoch;                       \
-            (void)ep_;                                                \
-            if ((TOUCH) != 0) rc_ = 2;                                \
-            pthread_mutex_unlock(&g_alloc_mu);                        \
+        for (int tries_ = 0;;) {                                      \
+            gate_enter();                                             \
+            const int m_ = res_begin();                               \
+            CUresult rc_ = 0;                                         \
+            int r_ = 0;                                               \
+            if (m_ == 2) {                                            \
+                pthread_mutex_lock(&g_alloc_mu);                      \
+                const uint64_t ep_ = ++g_res_epoch;                   \
+                (void)ep_;                                            \
+                r_ = (TOUCH);                                         \
+                pthread_mutex_unlock(&g_alloc_mu);                    \
+            }                                                         \
+            if (r_ == 0) rc_ = f ? f args : 3;                        \
+            res_end(m_);                                              \
+            gate_exit();                                              \
+            if (r_ == -3 /* VGPU_E_NOMEM */ && res_wait_retry(&tries_)) continue; \
+            return r_ != 0 ? 2 : rc_;                                 \
         }                                                             \
-        if (rc_ == 0) rc_ = f ? f args : 3;                           \
-        res_end(m_);                                                  \
-        gate_exit();                                                  \
-        return rc_;                                                   \
     }
 #define GATED2(name, sfx, params, args, TOUCH)        \
     GATED_ONE(name, #name, params, args, TOUCH)       \
     GATED_ONE(name##sfx, #name #sfx, params, args, TOUCH)
 #define T1(p, n) vmm_touch(p, n, ep_)
-#define T2(p, q, n) (vmm_touch(p, n, ep_) | vmm_touch(q, n, ep_))
+#define T2(p, q, n) vmm_touch2(p, q, n, ep_)
 GATED2(cuMemcpy, _ptds, (CUdeviceptr d, CUdeviceptr s_, size_t n), (d, s_, n), T2(d, s_, n))
 GATED2(cuMemcpyAsync, _ptsz, (CUdeviceptr d, CUdeviceptr s_, size_t n, void *st), (d, s_, n, st), T2(d, s_, n))
 GATED2(cuMemcpyDtoH_v2, _ptds, (void *d, CUdeviceptr s_, size_t n), (d, s_, n), T1(s_, n))
@@ -2867,9 +2894,20 @@ static void *mover_main(void *arg) {
             move_all(1);
             out = 1;
         } else if (target == 1 && out) {
-            move_all(0);
-            out = 0;
-            g_data_out = 0;
+            /* The gate opens only when every range is back.  HBM that the monitor counted as free may still be on
+             * its way out of another tenant: keep trying (the gate stays closed, the application waits) unless we are
+             * told to suspend again meanwhile — then whatever came back goes out again. */
+            int warned = 0;
+            while (move_all(0) != 0 && g_mover_target == 1) {
+                if (!warned++) SHIM_WARN("resume: not all ranges fit yet, waiting for HBM");
+                usleep(200000);
+            }
+            if (g_mover_target == 1) {
+                out = 0;
+                g_data_out = 0;
+            } else {
+                move_all(1);
+            }
         } else if (target == 1) {
             g_data_out = 0;
         }

@@ -573,19 +573,26 @@ def test_monitor_reads_a_live_cache_file(vgpu):
     MiB = 1 << 20
     td = tempfile.mkdtemp(prefix="mon")
     cache = os.path.join(td, "shr.cache")
-    env = H._env(H.NEW_LIB, cache, {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", "CUDA_DEVICE_SM_LIMIT": "25", **MAP}, os.path.join(td, "mock.log"))
+    # MOCK_CTX_MIB: the mock NVML lists the processes, so the shim learns their host pids at the first context (the
+    # monitor signals host pids only: the slot's `pid` means nothing outside the container's pid namespace)
+    env = H._env(H.NEW_LIB, cache, {"CUDA_DEVICE_MEMORY_LIMIT_0": "1024m", "CUDA_DEVICE_SM_LIMIT": "25", "MOCK_CTX_MIB": "10", **MAP},
+                 os.path.join(td, "mock.log"))
     procs = [subprocess.Popen([os.path.join(H.REF_DIR, "trace_runner")], stdin=subprocess.PIPE, stdout=subprocess.PIPE,
                               stderr=subprocess.DEVNULL, env=env, text=True, bufsize=1) for _ in range(2)]
     try:
         for i, p in enumerate(procs):
             assert p.stdout.readline().startswith("init")
-            p.stdin.write(f"alloc {(100 + 50 * i) * MiB} 1\n"); p.stdin.flush()
+            assert monitor.pids(cache) == [q.pid for q in procs[:i]] or i == 0   # no context yet: not reachable
+            p.stdin.write("retain 0 1\n"); p.stdin.flush()
+            assert p.stdout.readline().strip().startswith("0")
+            p.stdin.write(f"alloc {(90 + 50 * i) * MiB} 1\n"); p.stdin.flush()
             assert p.stdout.readline().strip() == "0"
         r = monitor.read_region(cache)
         assert r["device_num"] == 1 and r["uuids"] == [H.UUID0] and r["limit"] == [1024 * MiB] and r["sm_limit"] == [25]
         assert r["proc_num"] == 2 and sorted(p["pid"] for p in r["procs"]) == sorted(p.pid for p in procs)
         assert sorted(p["used"][0]["total"] for p in r["procs"]) == [100 * MiB, 150 * MiB] and r["usage"] == [250 * MiB]
         assert all(p["status"] == 1 for p in r["procs"])
+        assert sorted(monitor.pids(cache)) == sorted(p.pid for p in procs) and monitor.unreachable(cache) == []
         monitor.suspend(cache)                      # SIGUSR2 -> status 2 in every slot
         import time
         for _ in range(50):
