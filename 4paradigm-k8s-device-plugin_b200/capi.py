@@ -94,6 +94,7 @@ SIGNATURES = {
                                C.c_char_p, _pp(KV), _pp(_sz), _pp(Mount), _pp(_sz)]),
     "vgpu_allocate_env_monitor": (_i, [_pp(PluginCfg), _pp(_pp(Desc)), _sz, _pp(C.c_char_p), _pp(C.c_char_p), _sz,
                                        C.c_char_p, C.c_char_p, _pp(KV), _pp(_sz), _pp(Mount), _pp(_sz)]),
+    "vgpu_pcibus_list": (_i, [C.c_char_p, C.c_char_p, _sz]),
     "vgpu_checksum": (_i, [_vp, _vp, _sz, _sz, _vp, _vp]),
     "vgpu_spill": (_i, [_i, _i, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _vp]),
     "vgpu_restore": (_i, [_i, _i, _vp, _vp, _vp, _vp, _sz, _sz, _vp, _vp, _vp, _vp]),

@@ -616,6 +616,7 @@ typedef struct alloc_node {
     uint64_t last_use;   /* residency clock (paged mode) */
     uint64_t epoch;      /* the launch / copy that needs it right now: not a victim */
     int windowed;        /* larger than the GPU can hold at once: residency by prefetch hints only */
+    int raw;             /* made by cuMemoryAllocate (the route under the quota): paged like the others, never billed */
     struct alloc_node *next, *prev;
 } alloc_node_t;
 static alloc_node_t *g_head, *g_tail;
@@ -631,7 +632,7 @@ static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
     a->dev = dev;
     a->vmem = vmem;
     a->last_use = a->epoch = 0;
-    a->windowed = 0;
+    a->windowed = a->raw = 0;
     a->next = NULL;
     a->prev = g_tail;
     if (g_tail) g_tail->next = a; else g_head = a;
@@ -782,7 +783,7 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
     if (vmm) pthread_mutex_lock(&g_res_mu);
     pthread_mutex_lock(&g_alloc_mu);
     alloc_node_t *a = g_head;
-    while (a && a->addr != dptr) a = a->next;  /* remove_chunk@0x413dd: exact base match */
+    while (a && (a->addr != dptr || a->raw)) a = a->next;  /* remove_chunk@0x413dd: exact base match */
     if (!a) {
         pthread_mutex_unlock(&g_alloc_mu);
         if (vmm) pthread_mutex_unlock(&g_res_mu);
@@ -2921,6 +2922,67 @@ static void start_mover(void) {
         pthread_detach(th);
         region_status_hook = mover_wake;
     }
+}
+
+/* The reference also exports the raw allocation route that sits UNDER its quota: cuMemoryAllocate
+ * @0x32146 switches on the allocation mode — 0: cuMemAllocManaged(ATTACH_GLOBAL), 2: cuMemAlloc, 1: a VMM branch whose
+ * helper (getallochandle) is an undefined symbol in the shipped binary — stores the size in *allocated and returns
+ * the driver's code; it neither checks nor bills (add_chunk@0x40b73 does that around it).  cuMemoryFree@0x3849b is
+ * its counterpart.  Same here; mode 1 is the manager's range when the VMM backend is loaded.  cuMapMemory@0x31b28 /
+ * cuUnmapMemory@0x37f8f cannot run in the reference (they end in the undefined helper): NOT_SUPPORTED. */
+EXPORT CUresult cuMemoryAllocate(CUdeviceptr *dptr, size_t bytesize, size_t *allocated, void *data) {
+    (void)data;
+    ensure_initialized();
+    pthread_once(&g_post_once, post_init);
+    if (!dptr) return 1;
+    if (allocated) *allocated = bytesize;
+    if (g_allocmode == 0 && g_backend_vmm && bytesize > IPCSIZE) {
+        int dev = 0;
+        if (cur_dev(&dev) != 0) return 201;
+        pthread_mutex_lock(&g_res_mu);
+        pthread_mutex_lock(&g_alloc_mu);
+        const int rc = vmm_alloc(dev, bytesize, dptr);
+        if (rc == 0) g_tail->raw = 1;  /* tracked for paging and for cuMemoryFree, never billed */
+        pthread_mutex_unlock(&g_alloc_mu);
+        pthread_mutex_unlock(&g_res_mu);
+        return rc == 0 ? 0 : 2;
+    }
+    if (g_allocmode == 0) return get_cuMemAllocManaged() ? real_cuMemAllocManaged(dptr, bytesize, 1) : 3;
+    return get_cuMemAlloc_v2() ? real_cuMemAlloc_v2(dptr, bytesize) : 3;
+}
+EXPORT CUresult cuMemoryFree(CUdeviceptr dptr) {
+    ensure_initialized();
+    if (g_backend_vmm) {
+        pthread_mutex_lock(&g_res_mu);
+        pthread_mutex_lock(&g_alloc_mu);
+        alloc_node_t *a = g_head;
+        while (a && !(a->raw && a->addr == dptr)) a = a->next;
+        if (a) {
+            vmm_quiesce();
+            tl_bypass = 1;
+            const int rc = g_dp.destroy(a->vmem);
+            tl_bypass = 0;
+            if (a->prev) a->prev->next = a->next; else g_head = a->next;
+            if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
+            --g_nalloc;
+            free(a);
+            pthread_mutex_unlock(&g_alloc_mu);
+            pthread_mutex_unlock(&g_res_mu);
+            return rc == 0 ? 0 : 999;
+        }
+        pthread_mutex_unlock(&g_alloc_mu);
+        pthread_mutex_unlock(&g_res_mu);
+    }
+    return get_cuMemFree_v2() ? real_cuMemFree_v2(dptr) : 3;
+}
+EXPORT CUresult cuMapMemory(CUdeviceptr *dptr, size_t bytesize, void *handle, void *data) {
+    (void)dptr; (void)bytesize; (void)handle; (void)data;
+    SHIM_ERR("cuMapMemory: the reference's VMM branch is not callable (its helper is an undefined symbol); use cuMemoryAllocate");
+    return 801;
+}
+EXPORT CUresult cuUnmapMemory(CUdeviceptr dptr, int flag) {
+    (void)dptr; (void)flag;
+    return 801;
 }
 
 /* cuVGPUViewAllocator@0x16c80: dump the tracked allocations */

@@ -221,6 +221,30 @@ int vgpu_lookup(const vgpu_desc_t *all, size_t n_all, const char *const *ids, si
     return VGPU_OK;
 }
 
+// start() in main.go:164-185: the PCI bus ids of the node's NVIDIA devices, one per line, as the plugin writes them
+// to $PCIBUSFILE (mounted read-only at /usr/local/vgpu/pciinfo.vgpu in every vGPU pod, server.go:515-517).  A line of
+// `lspci` output counts when it is longer than one byte and contains "NVIDIA"; its id is everything before the first
+// space.  Returns the number of ids, or VGPU_E_RANGE when `out` is too small.
+int vgpu_pcibus_list(const char *lspci_out, char *out, size_t out_cap) {
+    if (!lspci_out || !out || out_cap == 0) return fail(VGPU_E_INVAL, "null argument");
+    std::string res;
+    int n = 0;
+    const char *p = lspci_out;
+    while (*p) {
+        const char *nl = strchr(p, '\n');
+        const std::string line = nl ? std::string(p, nl) : std::string(p);
+        if (line.size() > 1 && line.find("NVIDIA") != std::string::npos) {
+            res += line.substr(0, line.find(' ')) + "\n";
+            ++n;
+        }
+        if (!nl) break;
+        p = nl + 1;
+    }
+    if (res.size() + 1 > out_cap) return fail(VGPU_E_RANGE, "need %zu bytes", res.size() + 1);
+    memcpy(out, res.c_str(), res.size() + 1);
+    return n;
+}
+
 int vgpu_allocate_env(const vgpu_plugin_cfg_t *cfg, const vgpu_desc_t *const *req, size_t n_req,
                       const char *const *phys_uuids, const char *const *phys_index, size_t n_phys,
                       const char *cache_uuid, vgpu_kv_t *envs, size_t *n_envs, vgpu_mount_t *mounts,

@@ -45,6 +45,26 @@ class Flags:
     smPartitionIndex: bool = False  # no reference flag: add VGPU_SM_PARTITION_INDEX_<n> to the response (vgpu.h, emit_partition_index)
 
 
+def loadPciInfo(lspci_out: Optional[str] = None, pcibusfile: Optional[str] = None) -> str:
+    """start() in main.go:164-185: run `lspci`, keep the bus id of every line that names an NVIDIA device, and write
+    them, one per line, to $PCIBUSFILE (mode 0644) when that is set.  The file is what Allocate mounts at
+    /usr/local/vgpu/pciinfo.vgpu.  `lspci_out` / `pcibusfile` are injectable (tests); -> the string written."""
+    import os
+    import subprocess
+    if lspci_out is None:
+        lspci_out = subprocess.run(["lspci"], capture_output=True, text=True, check=True).stdout   # an error here ends start()
+    buf = C.create_string_buffer(len(lspci_out) + 2)
+    capi.check(capi.lib.vgpu_pcibus_list(lspci_out.encode(), buf, len(buf)))
+    pcibusstr = buf.value.decode()
+    if pcibusfile is None:
+        pcibusfile = os.environ.get("PCIBUSFILE", "")
+    if len(pcibusfile) > 0:
+        fd = os.open(pcibusfile, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
+        with os.fdopen(fd, "w") as f:
+            f.write(pcibusstr)
+    return pcibusstr
+
+
 def validateFlags(f: Flags) -> None:
     """main.go:143-161 — same messages."""
     if f.deviceListStrategy not in (DeviceListStrategyEnvvar, DeviceListStrategyVolumeMounts):
@@ -182,11 +202,50 @@ annSep = ","
 kubeletDeviceManagerCheckpoint = "kubelet_internal_checkpoint"
 
 
+def checkpointDump(data: Optional[dict]) -> str:
+    """What hashutil.DeepHashObject feeds the hash for a device-manager checkpoint
+    (vendor/k8s.io/kubernetes/pkg/util/hash/hash.go:27-36): go-spew's `%#v` of checkpoint.checkpointData
+    (vendor/.../devicemanager/checkpoint/checkpoint.go:35-48) with DisableMethods, SortKeys.  The rules, from
+    vendor/github.com/davecgh/go-spew/spew/format.go:201-371: a value is preceded by `(<Go type>)` unless it is an
+    element of a slice / a key or value of a map; a struct is `{Name:value Name:value}`, a slice `[a b]`, a map
+    `map[k:v k:v]` (keys sorted), a nil slice or map `<nil>`, a string its bytes, a byte its decimal value.
+    `data` is the JSON object under "Data" as encoding/json would have filled the Go struct: JSON null -> nil,
+    AllocResp base64 -> []byte."""
+    import base64
+    data = data or {}
+
+    def strs(v) -> str:          # []string
+        return "<nil>" if v is None else "[" + " ".join(v) + "]"
+
+    def entry(e: dict) -> str:   # checkpoint.PodDevicesEntry, as a slice element (no leading type)
+        ar = e.get("AllocResp")
+        raw = None if ar is None else base64.b64decode(ar)
+        return ("{PodUID:(string)%s ContainerName:(string)%s ResourceName:(string)%s DeviceIDs:([]string)%s AllocResp:([]uint8)%s}" %
+                (e.get("PodUID") or "", e.get("ContainerName") or "", e.get("ResourceName") or "", strs(e.get("DeviceIDs")),
+                 "<nil>" if raw is None else "[" + " ".join(str(b) for b in raw) + "]"))
+
+    pde, reg = data.get("PodDeviceEntries"), data.get("RegisteredDevices")
+    pde_s = "<nil>" if pde is None else "[" + " ".join(entry(e) for e in pde) + "]"
+    reg_s = "<nil>" if reg is None else "map[" + " ".join(f"{k}:{strs(reg[k])}" for k in sorted(reg)) + "]"
+    return ("(checkpoint.checkpointData){PodDeviceEntries:([]checkpoint.PodDevicesEntry)%s "
+            "RegisteredDevices:(map[string][]string)%s}" % (pde_s, reg_s))
+
+
+def checkpointChecksum(data: Optional[dict]) -> int:
+    """checksum.New (vendor/k8s.io/kubernetes/pkg/kubelet/checkpointmanager/checksum/checksum.go:36-45): FNV-1a, 32 bit,
+    over checkpointDump, widened to uint64."""
+    h = 0x811C9DC5
+    for b in checkpointDump(data).encode():
+        h = ((h ^ b) * 0x01000193) & 0xFFFFFFFF
+    return h
+
+
 class VDeviceController:
     """vdevice-controller.go:32-286 — the legacy preferred-allocation bookkeeping used with
     --enable-legacy-preferred: idMap[vdevID] -> the request id it was handed out for ("" = free).
     The pod lister and the kubelet checkpoint are injected (a fake lister and a checkpoint file in
-    tests); the kubelet's checkpoint checksum (a Go spew/fnv object hash) is not verified."""
+    tests).  The checkpoint is read the way the kubelet's checkpoint manager reads it: its checksum is verified
+    (checkpointChecksum) and a mismatch is "checkpoint is corrupted" (checkpointmanager/errors)."""
 
     def __init__(self, deviceIDs: Sequence[str], podLister: Optional[Callable[[], List[dict]]] = None,
                  checkpointDir: str = DevicePluginPath):
@@ -229,6 +288,9 @@ class VDeviceController:
             cp = json.load(open(path))
         except (OSError, ValueError) as e:
             raise PluginError(f"read checkpoint error, {e}")
+        # GetCheckpoint -> VerifyChecksum (vdevice-controller.go:64; checkpoint.go:75-78)
+        if not isinstance(cp, dict) or int(cp.get("Checksum") or 0) != checkpointChecksum(cp.get("Data")):
+            raise PluginError("read checkpoint error, checkpoint is corrupted")
         pods = self.podLister()
         for pde in (cp.get("Data") or {}).get("PodDeviceEntries") or []:
             if pde.get("ResourceName") != "nvidia.com/gpu":

@@ -129,6 +129,11 @@ int vgpu_allocate_env_monitor(const vgpu_plugin_cfg_t *cfg,
                               vgpu_kv_t *envs, size_t *n_envs,
                               vgpu_mount_t *mounts, size_t *n_mounts);
 
+/* Replaces the lspci pass of start() (main.go:164-185): `lspci_out` is the output of `lspci`; `out` receives the PCI
+ * bus ids of the lines that name an NVIDIA device, one per line — the content of $PCIBUSFILE, which Allocate mounts at
+ * /usr/local/vgpu/pciinfo.vgpu (server.go:515-517).  Returns the number of ids or VGPU_E_*. */
+int vgpu_pcibus_list(const char *lspci_out, char *out, size_t out_cap);
+
 /* ======================================================================== *
  *  Virtual-device-memory data path: 2 MiB chunk spill / restore
  *  (new mechanism behind CUDA_OVERSUBSCRIBE, server.go:505-507; the reference

@@ -189,3 +189,20 @@ def test_partition_index_is_opt_in_and_additive(vgpu):
     assert added == {"VGPU_SM_PARTITION_INDEX_0": "3", "VGPU_SM_PARTITION_INDEX_1": "7"}
     assert {k: v for k, v in extra.Envs.items() if k in plain.Envs} == dict(plain.Envs)
     assert [(m.ContainerPath, m.HostPath, m.ReadOnly) for m in extra.Mounts] == [(m.ContainerPath, m.HostPath, m.ReadOnly) for m in plain.Mounts]
+
+
+def test_pci_bus_file_is_what_start_writes_from_lspci(vgpu, tmp_path):
+    """main.go:164-185: every lspci line longer than one byte that contains "NVIDIA" contributes its first
+    space-separated token; the result goes to $PCIBUSFILE, which Allocate mounts at /usr/local/vgpu/pciinfo.vgpu."""
+    lspci = ("00:00.0 Host bridge: Intel Corporation Device 09a2 (rev 04)\n"
+             "1b:00.0 3D controller: NVIDIA Corporation Device 2901 (rev a1)\n"
+             "\n"
+             "1c:00.0 Bridge: NVIDIA Corporation Device 22a3 (rev a1)\n"     # NVSwitch lines count too: the Go code only looks for the word
+             "43:00.0 3D controller: NVIDIA Corporation Device 2901 (rev a1)\n"
+             "x\n"
+             "aa:00.0 Ethernet controller: Mellanox Technologies MT2910 Family [ConnectX-7]")
+    out = tmp_path / "pciinfo.vgpu"
+    s = vgpu.plugin.loadPciInfo(lspci, str(out))
+    assert s == "1b:00.0\n1c:00.0\n43:00.0\n" and out.read_text() == s and (out.stat().st_mode & 0o777) == 0o644
+    assert vgpu.plugin.loadPciInfo("", "") == ""                       # no devices, no $PCIBUSFILE: nothing written
+    assert vgpu.plugin.loadPciInfo("NVIDIA", "") == "NVIDIA\n"         # a line without a space is its own first token (strings.Split)

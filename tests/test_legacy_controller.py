@@ -20,7 +20,8 @@ def make(vgpu, pods, ckpt_entries, split=4):
         r = P.ContainerAllocateResponse(Annotations={P.annRequest: ",".join(request), P.annUsing: ",".join(using)} if using else {})
         entries.append({"PodUID": uid, "ContainerName": "c", "ResourceName": resource, "DeviceIDs": list(request),
                         "AllocResp": base64.b64encode(G.enc_allocate_container(r)).decode()})
-    json.dump({"Data": {"PodDeviceEntries": entries, "RegisteredDevices": {"nvidia.com/gpu": []}}, "Checksum": 0},
+    data = {"PodDeviceEntries": entries, "RegisteredDevices": {"nvidia.com/gpu": []}}
+    json.dump({"Data": data, "Checksum": P.checkpointChecksum(data)},   # as the kubelet writes it (MarshalCheckpoint)
               open(os.path.join(td, P.kubeletDeviceManagerCheckpoint), "w"))
     p = P.NewNvidiaDevicePlugin(P.ResourceManager([P.Device(UUID, memory_mib=184320)]), P.Flags(deviceSplitCount=split, enableLegacyPreferred=True))
     p._podLister = lambda: pods
@@ -81,3 +82,44 @@ def test_allocate_in_legacy_mode_substitutes_free_vdevices_and_annotates(vgpu):
     with pytest.raises(A.PluginError) as e:
         p.Allocate([[f"{UUID}-9"]])
     assert str(e.value) == "no enough devices"
+
+
+def test_checkpoint_checksum_is_the_kubelets_object_hash(vgpu):
+    """checksum.New = FNV-1a/32 over go-spew's `%#v` of checkpoint.checkpointData.  Parity unpinned by a reference
+    vector (Go cannot run here, the tree holds no checkpoint fixture): the dump is written out by hand from the rules of
+    vendor/github.com/davecgh/go-spew/spew/format.go and the hash checked against FNV's published test vectors."""
+    P = vgpu.plugin
+
+    def fnv(b):
+        h = 0x811C9DC5
+        for x in b:
+            h = ((h ^ x) * 0x01000193) & 0xFFFFFFFF
+        return h
+    assert fnv(b"") == 0x811C9DC5 and fnv(b"a") == 0xE40C292C and fnv(b"foobar") == 0xBF9CF968      # FNV-1a 32 known answers
+    # a freshly started kubelet: New(make([]PodDevicesEntry, 0), make(map[string][]string)) marshals [] and {}
+    empty = {"PodDeviceEntries": [], "RegisteredDevices": {}}
+    assert P.checkpointDump(empty) == "(checkpoint.checkpointData){PodDeviceEntries:([]checkpoint.PodDevicesEntry)[] RegisteredDevices:(map[string][]string)map[]}"
+    # JSON null unmarshals to nil slices / maps, which spew prints as <nil>
+    assert P.checkpointDump({"PodDeviceEntries": None, "RegisteredDevices": None}) == \
+        "(checkpoint.checkpointData){PodDeviceEntries:([]checkpoint.PodDevicesEntry)<nil> RegisteredDevices:(map[string][]string)<nil>}"
+    data = {"PodDeviceEntries": [{"PodUID": "u1", "ContainerName": "c", "ResourceName": "nvidia.com/gpu", "DeviceIDs": ["g-0", "g-1"],
+                                  "AllocResp": base64.b64encode(bytes([10, 2, 255])).decode()},
+                                 {"PodUID": "u2", "ContainerName": "d", "ResourceName": "x", "DeviceIDs": None, "AllocResp": None}],
+            "RegisteredDevices": {"z.com/b": ["q"], "nvidia.com/gpu": ["g-0", "g-1", "g-2"]}}
+    want = ("(checkpoint.checkpointData){PodDeviceEntries:([]checkpoint.PodDevicesEntry)["
+            "{PodUID:(string)u1 ContainerName:(string)c ResourceName:(string)nvidia.com/gpu DeviceIDs:([]string)[g-0 g-1] AllocResp:([]uint8)[10 2 255]} "
+            "{PodUID:(string)u2 ContainerName:(string)d ResourceName:(string)x DeviceIDs:([]string)<nil> AllocResp:([]uint8)<nil>}] "
+            "RegisteredDevices:(map[string][]string)map[nvidia.com/gpu:[g-0 g-1 g-2] z.com/b:[q]]}")      # map keys sorted (SortKeys)
+    assert P.checkpointDump(data) == want and P.checkpointChecksum(data) == fnv(want.encode())
+
+
+def test_a_checkpoint_with_a_wrong_checksum_is_corrupted(vgpu):
+    """vdevice-controller.go:64 reads through the checkpoint manager, which verifies (checkpoint.go:75-78)."""
+    p = make(vgpu, [], [("pod-run", [f"{UUID}-0"], [f"{UUID}-2"], "nvidia.com/gpu")])
+    path = os.path.join(p._checkpointDir, vgpu.plugin.kubeletDeviceManagerCheckpoint)
+    cp = json.load(open(path))
+    p.vDeviceController.updateFromCheckpoint()                     # intact: accepted
+    cp["Data"]["PodDeviceEntries"][0]["PodUID"] = "tampered"
+    json.dump(cp, open(path, "w"))
+    with pytest.raises(vgpu.plugin.PluginError, match="checkpoint is corrupted"):
+        p.vDeviceController.updateFromCheckpoint()
