@@ -1187,6 +1187,39 @@ static CUcontext green_ctx_for(CUdevice dev) {
     return c;
 }
 
+/* SMs the partition of `dev` has, or will have once its primary context is retained (0 = no cap): the same split the
+ * creation does, without creating anything — what device attributes must answer before the context exists. */
+static unsigned green_planned_sms(CUdevice dev) {
+    static unsigned planned[VGPU_MAX_DEVICES];
+    static int done[VGPU_MAX_DEVICES];
+    if (dev < 0 || dev >= VGPU_MAX_DEVICES || !g_region_ok) return 0;
+    if (g_green_state[dev] == 1) return g_green_sms[dev];
+    if (g_green_state[dev] == -1) return 0;
+    uint64_t pct = q_sm_limit(dev);
+    const char *sw = getenv("VGPU_SM_PARTITION");
+    if (pct == 0 || pct >= 100 || (sw && strcmp(sw, "off") == 0) || sm_policy_disabled()) return 0;
+    if (done[dev]) return planned[dev];
+    typedef CUresult (*getres_t)(CUdevice, shim_dev_resource_t *, int);
+    typedef CUresult (*split_t)(shim_dev_resource_t *, unsigned *, const shim_dev_resource_t *, shim_dev_resource_t *, unsigned, unsigned);
+    getres_t getres = (getres_t)cuda_sym("cuDeviceGetDevResource");
+    split_t split = (split_t)cuda_sym("cuDevSmResourceSplitByCount");
+    shim_dev_resource_t all, groups[64], rest;
+    if (getres && split && getres(phys_of(dev), &all, 1) == 0) {
+        const unsigned total = all.sm.smCount, share = (unsigned)(total * pct / 100);
+        const char *gr = getenv("VGPU_SM_PARTITION_GRANULE");
+        const unsigned sflags = (gr && strcmp(gr, "fine") == 0) ? 1u : 0u;
+        for (unsigned want = share ? share : 1; want >= 1; --want) {
+            unsigned nb = 64;
+            if (split(groups, &nb, &all, &rest, sflags, want) == 0 && nb >= 1 && (groups[0].sm.smCount <= share || want == 1)) {
+                planned[dev] = groups[0].sm.smCount;
+                break;
+            }
+        }
+        done[dev] = 1;
+    }
+    return planned[dev];
+}
+
 /* exported for tests / vgpuvalidator: SMs of the partition this process runs in (0 = uncapped) */
 EXPORT unsigned cuVGPUPartitionSmCount(CUdevice dev) {
     return (dev >= 0 && dev < VGPU_MAX_DEVICES && g_green_state[dev] == 1) ? g_green_sms[dev] : 0;
@@ -1490,6 +1523,11 @@ static int vmm_make_resident(alloc_node_t *a, uint64_t first, uint64_t n, uint64
         if (tight) {
             alloc_node_t *v = vmm_victim(epoch);
             if (v && vmm_evict_node(v) == 0) continue;
+            /* nothing of ours left to spill: the HBM is held by other tenants.  Do NOT try anyway — the manager maps
+             * block by block until the driver refuses, which would eat the reserve every other allocation on the GPU
+             * (ours below 2 MiB, the other tenants') depends on.  The caller waits and retries. */
+            rc = -3;
+            break;
         }
         rc = g_dp.ensure(a->vmem, first, n);
         if (rc == -3 /* VGPU_E_NOMEM */) {
@@ -2141,8 +2179,10 @@ EXPORT CUresult cuDeviceGetAttribute(int *pi, int attrib, CUdevice d) {
     const CUdevice v = d;
     if (!tl_bypass && !to_phys(&d)) return 101;
     CUresult rc = f ? f(pi, attrib, d) : 3;
-    if (rc == 0 && !tl_bypass && attrib == 16 && pi && v >= 0 && v < VGPU_MAX_DEVICES && g_green_state[v] == 1 && g_green_sms[v])
-        *pi = (int)g_green_sms[v];
+    if (rc == 0 && !tl_bypass && attrib == 16 && pi) {
+        const unsigned sms = green_planned_sms(v);
+        if (sms) *pi = (int)sms;
+    }
     return rc;
 }
 VDEV1(cuDeviceGetUuid, (unsigned char *uuid, CUdevice d), (uuid, d), d)
@@ -2852,6 +2892,14 @@ static CUresult move_all(int out) {
     pthread_mutex_unlock(&g_res_mu);
     return rc;
 }
+static uint64_t managed_bytes(void) {
+    uint64_t n = 0;
+    pthread_mutex_lock(&g_alloc_mu);
+    for (alloc_node_t *a = g_head; a; a = a->next)
+        if (a->vmem && !a->windowed) n += node_chunks(a) * IPCSIZE;
+    pthread_mutex_unlock(&g_alloc_mu);
+    return n;
+}
 /* the in-process form: the caller's own threads are its business, but the gate still closes around the move */
 static CUresult move_all_gated(int out) {
     if (!out) return move_all(0);
@@ -2892,18 +2940,29 @@ static void *mover_main(void *arg) {
         const int target = g_mover_target;
         if (target == 2 && !out) {
             while (g_inflight > 0) usleep(100);  /* calls that were past the gate have reached the driver and returned */
+            struct timespec t0, t1;
+            clock_gettime(CLOCK_MONOTONIC, &t0);
             move_all(1);
+            clock_gettime(CLOCK_MONOTONIC, &t1);
+            SHIM_INFO("suspend: %lu MiB of managed ranges out in %.1f ms", (unsigned long)(managed_bytes() >> 20),
+                      (t1.tv_sec - t0.tv_sec) * 1e3 + (t1.tv_nsec - t0.tv_nsec) / 1e6);
             out = 1;
         } else if (target == 1 && out) {
             /* The gate opens only when every range is back.  HBM that the monitor counted as free may still be on
              * its way out of another tenant: keep trying (the gate stays closed, the application waits) unless we are
              * told to suspend again meanwhile — then whatever came back goes out again. */
             int warned = 0;
+            struct timespec t0, t1;
+            clock_gettime(CLOCK_MONOTONIC, &t0);
             while (move_all(0) != 0 && g_mover_target == 1) {
                 if (!warned++) SHIM_WARN("resume: not all ranges fit yet, waiting for HBM");
                 usleep(200000);
+                clock_gettime(CLOCK_MONOTONIC, &t0);  /* time the attempt that succeeds */
             }
+            clock_gettime(CLOCK_MONOTONIC, &t1);
             if (g_mover_target == 1) {
+                SHIM_INFO("resume: %lu MiB of managed ranges back in %.1f ms", (unsigned long)(managed_bytes() >> 20),
+                          (t1.tv_sec - t0.tv_sec) * 1e3 + (t1.tv_nsec - t0.tv_nsec) / 1e6);
                 out = 0;
                 g_data_out = 0;
             } else {

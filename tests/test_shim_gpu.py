@@ -158,7 +158,9 @@ def test_two_vgpus_on_one_physical_gpu_are_two_cuda_devices(cuda_dev):
     assert o["ctx"][0]["partition_ctx"] and o["ctx"][1]["partition_ctx"] and o["ctx"][0]["partition_ctx"] != o["ctx"][1]["partition_ctx"]
     assert o["count"] == 2 and o["get_oob"] == 101 and o["distinct_ctx"]
     a, b = o["devs"]
-    assert (a["dev"], b["dev"]) == (0, 1) and a["name"] == b["name"] and a["sms"] == b["sms"] > 0
+    assert (a["dev"], b["dev"]) == (0, 1) and a["name"] == b["name"]
+    # the SM-count attribute of a capped vGPU is its partition's size (asked before its context exists: the planned size)
+    assert a["sms"] == o["ctx"][0]["sms"] and b["sms"] == o["ctx"][1]["sms"]
     assert a["bus"].endswith(".0") and b["bus"] == a["bus"][:-1] + "1" and (a["by_bus"], b["by_bus"]) == (0, 1)
     assert (a["total"], b["total"]) == (4 * GiB, 8 * GiB)
     for i, (r, lim) in enumerate(zip(o["ctx"], (4 * GiB, 8 * GiB))):
