@@ -61,7 +61,10 @@ def parse():
     ap.add_argument("--config5-gib", type=float, default=16.0, help="memtest buffer per vGPU in config 5 (16)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-gib", type=float, default=4.0, help="host buffer of the CPU memtest sample")
-    ap.add_argument("--e2e-chunks", type=int, default=1024, help="2 MiB chunks the e2e step spills to / restores from a host buffer")
+    ap.add_argument("--e2e-chunks", type=int, default=256,
+                    help="2 MiB chunks the e2e step spills to / restores from a host buffer (256 = 512 MiB each way per GPU per step: fits inside "
+                         "the memtest step's window even where eight GPUs share one host path at 12 GB/s each; the host rates themselves are in "
+                         "e2e.components and roofline.pcie)")
     ap.add_argument("--e2e-variant", default="auto", choices=["auto", "ldst", "tma", "ce"], help="transfer variant of the e2e step's host-buffer calls")
     return ap.parse_args()
 
