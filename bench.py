@@ -70,10 +70,10 @@ def parse():
 
 
 def traffic_per_launch(kernel, launch_bytes):
-    """DRAM bytes per launch from the committed ncu --set full capture (profiles/r01_traffic.json),
+    """DRAM bytes per launch from the committed ncu --set full capture (profiles/r02_traffic.json),
     scaled from the profiled launch size to this run's launch size."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))["kernels"][kernel]
+        t = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))["kernels"][kernel]
         return int(t["traffic_ratio"] * launch_bytes), t["traffic_ratio"]
     except Exception:
         return None, None
@@ -521,7 +521,7 @@ def main():
                         "host_memcpy_spill_GBps": {"1_thread": round(cpu_spill_sample(64, 1)[0], 2), f"{cores}_threads": round(cpu_spill_sample(256, cores)[0], 2)}}
         roof = {"bound": "hbm", "achieved": whole[dom]["GBps"], "peak": hbm_peak, "unit": "GB/s",
                 "frac": round(whole[dom]["GBps"] / hbm_peak, 4), "traffic": traffic,
-                "traffic_note": f"dram read+write bytes per {per / GIB:.0f} GiB launch = {traffic_ratio} x algorithmic bytes (ncu --set full, profiles/r01_traffic.json)",
+                "traffic_note": f"dram read+write bytes per {per / GIB:.0f} GiB launch = {traffic_ratio} x algorithmic bytes (ncu --set full, profiles/r02_traffic.json)",
                 "algorithmic_bytes_per_launch": per, "kernel": f"k_memtest_{dom} (whole GPU, timed alone)",
                 "peak_source": peak_src, "whole_gpu": whole, "one_partition": kern, "in_step_vgpu0": in_step,
                 "step_aggregate": {"GBps": round(value / world, 1), "frac": round(value / world / hbm_peak, 4),

@@ -5,10 +5,10 @@
 set -u
 TAG=${1:-r1}
 # --partition streams: ncu fails with "Failed to prepare kernel for profiling" on launches into green contexts
-ARGS="--steps 2 --warmup 3 --no-cpu --vgpu-gib 4 --spill-chunks 64 --partition streams"
+ARGS="--steps 2 --warmup 3 --no-cpu --vgpu-gib 4 --spill-chunks 64 --partition streams --config5-gib 1 --e2e-chunks 64"
 mkdir -p gpurun_out
 python bench.py $ARGS > gpurun_out/${TAG}_plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv \
     --log-file gpurun_out/${TAG}_launches.csv python bench.py $ARGS > gpurun_out/${TAG}_ncu_list.log 2>&1
 echo "launch list rc=$?"
 python scripts/prof_kernels.py 4 > gpurun_out/${TAG}_plain2.log 2>&1 &&
