@@ -617,12 +617,14 @@ typedef struct alloc_node {
     uint64_t epoch;      /* the launch / copy that needs it right now: not a victim */
     int windowed;        /* larger than the GPU can hold at once: residency by prefetch hints only */
     int raw;             /* made by cuMemoryAllocate (the route under the quota): paged like the others, never billed */
+    uint64_t peer_bytes; /* its share of the VGPU_OVERSUB_PEER_MB budget, given back when it is freed */
     struct alloc_node *next, *prev;
 } alloc_node_t;
 static alloc_node_t *g_head, *g_tail;
 static size_t g_nalloc;
 static pthread_mutex_t g_alloc_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_mutex_t g_res_mu = PTHREAD_MUTEX_INITIALIZER;  /* residency of VMM-backed allocations (taken before g_alloc_mu) */
+static uint64_t g_peer_left = ~0ull;  /* VGPU_OVERSUB_PEER_MB: what this process may still put on the peer (under g_res_mu) */
 static void vmm_quiesce(void);
 
 static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
@@ -633,6 +635,7 @@ static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
     a->vmem = vmem;
     a->last_use = a->epoch = 0;
     a->windowed = a->raw = 0;
+    a->peer_bytes = 0;
     a->next = NULL;
     a->prev = g_tail;
     if (g_tail) g_tail->next = a; else g_head = a;
@@ -795,6 +798,7 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
         tl_bypass = 1;
         rc = g_dp.destroy(a->vmem) == 0 ? 0 : 999;
         tl_bypass = 0;
+        if (g_peer_left != ~0ull) g_peer_left += a->peer_bytes;
     } else {
         cuMemFree_v2_t f = get_cuMemFree_v2();
         rc = f ? f(dptr) : 3;
@@ -1411,7 +1415,6 @@ static pthread_rwlock_t g_mode_rw = PTHREAD_RWLOCK_INITIALIZER;
 static volatile int g_vmm_paged;
 static uint64_t g_res_clock, g_res_epoch;
 static CUdeviceptr g_vmm_lo = ~0ull, g_vmm_hi;  /* envelope of every managed range ever made: cheap reject for the scan */
-static uint64_t g_peer_left = ~0ull;             /* VGPU_OVERSUB_PEER_MB: what this process may still put on the peer */
 
 static uint64_t env_mb(const char *name, uint64_t dflt) {
     const char *e = getenv(name);
@@ -1594,7 +1597,6 @@ static int vmm_alloc(int dev, size_t n, CUdeviceptr *p) {
     if (op_cap)
         for (alloc_node_t *k = g_head; k; k = k->next)
             if (k->vmem) res_now += node_resident(k) * IPCSIZE;
-    tl_bypass = 1;
     if (vrc == 0 && !g_vmm_paged && !windowed && fr >= bytes + reserve && !(op_cap && res_now + bytes > op_cap)) {
         vrc = g_dp.ensure(h, 0, chunks);  /* it fits: back it now, as cuMemAlloc would */
         if (vrc == -3) vrc = 0;           /* ... it does not after all: page it in at its first use */
@@ -1605,11 +1607,13 @@ static int vmm_alloc(int dev, size_t n, CUdeviceptr *p) {
         tl_bypass = 1;
         if (h) g_dp.destroy(h);
         tl_bypass = 0;
+        if (g_peer_left != ~0ull) g_peer_left += peer_bytes;
         return vrc;
     }
     *p = (CUdeviceptr)(uintptr_t)base;
     track_vmem(*p, n, dev, h);
     g_tail->windowed = windowed;
+    g_tail->peer_bytes = peer_bytes;
     g_tail->last_use = ++g_res_clock;
     if (*p < g_vmm_lo) g_vmm_lo = *p;
     if (*p + bytes > g_vmm_hi) g_vmm_hi = *p + bytes;
@@ -3021,6 +3025,7 @@ EXPORT CUresult cuMemoryFree(CUdeviceptr dptr) {
             tl_bypass = 1;
             const int rc = g_dp.destroy(a->vmem);
             tl_bypass = 0;
+            if (g_peer_left != ~0ull) g_peer_left += a->peer_bytes;
             if (a->prev) a->prev->next = a->next; else g_head = a->next;
             if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
             --g_nalloc;

@@ -882,7 +882,15 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, peer, ranks):
                 "all_gpus_at_once_per_gpu": {"spill": round(ring["spill"], 1), "restore": round(ring["restore"], 1)} if world > 1 else None,
                 "traffic_note": "wire bytes per launch = payload x the ncu nvltx/nvlrx ratio of profiles/r02_link_traffic.json (packet overhead: 18.75 % on writes, 12.5 % on read responses)"}
         else:
-            out["_roofline_nvlink"] = {"bound": "nvlink", "achieved": None, "why": "one GPU visible: no peer tier in this run (see the N>1 lines)"}
+            rec = None
+            try:  # what the same code measured when a second GPU was visible, committed with the repository
+                src = "profiles/r02_bench_n1_idle_peer.json"
+                rec = dict(json.load(open(os.path.join(ROOT, src)))["roofline"]["nvlink"], source=src + " (N=1 on a 2-GPU box, GPU 1 idle)")
+            except Exception:
+                pass
+            out["_roofline_nvlink"] = {"bound": "nvlink", "achieved": None, "peak": NVLINK_NOMINAL, "unit": "GB/s",
+                                       "why": "one GPU visible: no peer tier can be measured in this run (the N>1 lines carry it)",
+                                       "last_recorded": rec}
         n, h = best_at_max["host"]
         pk = link.get("host", {})
         out["_roofline_pcie"] = {
