@@ -209,6 +209,12 @@ int main(void) {
             int rc2 = rc == 0 ? cuDeviceGetUuid(uuid, dev) : -1;
             int rc3 = rc == 0 ? cuDeviceGetPCIBusId(bus, sizeof(bus), dev) : -1;
             printf("%d %d %d %u %d %s\n", rc, dev, rc2, (unsigned)uuid[15], rc3, bus);
+        } else if (!strcmp(op, "uuidfull")) {  /* all 16 bytes of cuDeviceGetUuid, hex */
+            unsigned char uuid[16] = {0};
+            rc = cuDeviceGetUuid(uuid, (int)a);
+            printf("%d ", rc);
+            for (int i = 0; i < 16; ++i) printf("%02x", uuid[i]);
+            printf("\n");
         } else if (!strcmp(op, "setdev")) {
             void *ctx = NULL;
             rc = cuDevicePrimaryCtxRetain(&ctx, (int)a);

@@ -624,3 +624,15 @@ def test_shim_exports_the_hooked_driver_symbols():
         assert n in names, n
     internal = [n for n in names if n.startswith(("region_", "shim_", "oom_", "add_chunk"))]
     assert not internal, f"internal helpers leak into the dynamic symbol table: {internal}"
+
+
+@pytest.mark.skipif(not H.have_reference(), reason="reference binary only exists in the build container")
+def test_device_uuid_of_every_vgpu_is_the_physical_gpus_as_in_the_reference():
+    """cuDeviceGetUuid through the reference answers with the physical GPU's UUID for a plain vGPU and for both vGPUs of
+    a GPU named twice (all 16 bytes compared, not just the last one the `devget` probe prints)."""
+    for env, n in (({"NVIDIA_DEVICE_MAP": "0:" + H.UUID0, "CUDA_DEVICE_MEMORY_LIMIT_0": "1g"}, 1),
+                   ({"NVIDIA_DEVICE_MAP": f"0:{H.UUID0} 1:{H.UUID0}", "CUDA_DEVICE_MEMORY_LIMIT_0": "1g", "CUDA_DEVICE_MEMORY_LIMIT_1": "1g"}, 2)):
+        tr = [(0, "devcount")] + [(0, f"uuidfull {i}") for i in range(n)]
+        a = H.run_trace(H.REFERENCE_LIB, tr, env)["replies"]
+        b = H.run_trace(H.NEW_LIB, tr, env)["replies"]
+        assert a == b and all(r == "0 " + H.UUID0[4:].replace("-", "") for r in b[1:]), (a, b)
