@@ -733,3 +733,50 @@ def test_vmm_backend_leaves_a_cuCtxCreate_context_current_and_bills_its_device(c
     o = last_json(p)
     assert o["rc"] == [0, 0, 0, 0, 0] and o["same"] == [True, True, True] and o["good"], (o, p.stderr[-2000:])
     assert o["billed"] >= 64 << 20
+
+
+def test_cooperative_grid_sized_from_the_sm_count_fits_inside_a_partition(cuda_dev):
+    """A cooperative launch must be co-resident: occupancy x SM count CTAs at most.  Inside a 25 % partition the SM-count
+    attribute answers with the partition's size, so a grid sized the usual way is accepted; sized from the GPU's full
+    148 SMs it is refused (CUDA_ERROR_COOPERATIVE_LAUNCH_TOO_LARGE = 720) — which is what programs hit when the
+    attribute still said 148.  (The reference's temporal throttle never had this failure mode.)"""
+    code = """
+        import ctypes as C, json
+        from cuda.bindings import nvrtc
+        src = b'extern "C" __global__ void k(int *out) { if (threadIdx.x == 0) atomicAdd(out, 1); }'
+        err, prog = nvrtc.nvrtcCreateProgram(src, b"k.cu", 0, [], [])
+        (err,) = nvrtc.nvrtcCompileProgram(prog, 1, [b"--gpu-architecture=compute_100a"])
+        assert int(err) == 0
+        err, n = nvrtc.nvrtcGetPTXSize(prog)
+        ptx = b" " * n
+        (err,) = nvrtc.nvrtcGetPTX(prog, ptx)
+        cu = C.CDLL("libcuda.so.1")
+        assert cu.cuInit(0) == 0
+        dev, ctx, mod, fn = C.c_int(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        cu.cuDeviceGet(C.byref(dev), 0)
+        assert cu.cuDevicePrimaryCtxRetain(C.byref(ctx), dev) == 0 and cu.cuCtxSetCurrent(ctx) == 0
+        sms = C.c_int()
+        cu.cuDeviceGetAttribute(C.byref(sms), 16, dev)
+        assert cu.cuModuleLoadData(C.byref(mod), ptx) == 0 and cu.cuModuleGetFunction(C.byref(fn), mod, b"k") == 0
+        occ = C.c_int()
+        assert cu.cuOccupancyMaxActiveBlocksPerMultiprocessor(C.byref(occ), fn, 256, C.c_size_t(0)) == 0
+        out = C.c_ulonglong()
+        assert cu.cuMemAlloc_v2(C.byref(out), C.c_size_t(4)) == 0 and cu.cuMemsetD32_v2(out, 0, C.c_size_t(1)) == 0
+        arg = C.c_ulonglong(out.value)
+        params = (C.c_void_p * 1)(C.cast(C.byref(arg), C.c_void_p))
+        def coop(grid):
+            rc = cu.cuLaunchCooperativeKernel(fn, grid, 1, 1, 256, 1, 1, 0, None, params)
+            return rc if rc else cu.cuCtxSynchronize()
+        rc_fit = coop(occ.value * sms.value)
+        rc_big = coop(occ.value * 148)
+        got = C.c_int()
+        cu.cuMemcpyDtoH_v2(C.byref(got), out, C.c_size_t(4))
+        print(json.dumps({"sms": sms.value, "occ": occ.value, "rc_fit": rc_fit, "rc_big": rc_big, "ctas_ran": got.value,
+                          "partition": C.CDLL(None).cuVGPUPartitionSmCount(0)}))
+    """
+    o = last_json(run_under_shim(code, {"CUDA_DEVICE_SM_LIMIT": "25", "CUDA_DEVICE_MEMORY_LIMIT_0": "4g"}))
+    assert o["partition"] == o["sms"] == 32 and o["occ"] >= 1
+    assert o["rc_fit"] == 0 and o["ctas_ran"] == o["occ"] * 32
+    assert o["rc_big"] == 720
+    free = last_json(run_under_shim(code, {"CUDA_DEVICE_SM_LIMIT": "100", "CUDA_DEVICE_MEMORY_LIMIT_0": "4g"}))
+    assert free["partition"] == 0 and free["sms"] == 148 and free["rc_fit"] == 0 and free["rc_big"] == 0
