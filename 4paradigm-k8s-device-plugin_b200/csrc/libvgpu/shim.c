@@ -618,6 +618,7 @@ typedef struct alloc_node {
     int windowed;        /* larger than the GPU can hold at once: residency by prefetch hints only */
     int raw;             /* made by cuMemoryAllocate (the route under the quota): paged like the others, never billed */
     uint64_t peer_bytes; /* its share of the VGPU_OVERSUB_PEER_MB budget, given back when it is freed */
+    int prefer;          /* cuMemAdvise: +1 preferred location = the GPU (spilled last), -1 = the CPU (spilled first), 0 none */
     struct alloc_node *next, *prev;
 } alloc_node_t;
 static alloc_node_t *g_head, *g_tail;
@@ -636,6 +637,7 @@ static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
     a->last_use = a->epoch = 0;
     a->windowed = a->raw = 0;
     a->peer_bytes = 0;
+    a->prefer = 0;
     a->next = NULL;
     a->prev = g_tail;
     if (g_tail) g_tail->next = a; else g_head = a;
@@ -1487,9 +1489,13 @@ static alloc_node_t *vmm_find(CUdeviceptr p) {
 }
 /* least recently used range with something resident that the call at hand (epoch) does not need */
 static alloc_node_t *vmm_victim(uint64_t epoch) {
+    /* cuMemAdvise(SET_PREFERRED_LOCATION) ranks before age: ranges that prefer the CPU go first, ranges that prefer
+     * the GPU only when nothing else is left */
     alloc_node_t *best = NULL;
     for (alloc_node_t *a = g_head; a; a = a->next)
-        if (a->vmem && a->epoch != epoch && (!best || a->last_use < best->last_use) && node_resident(a) > 0) best = a;
+        if (a->vmem && a->epoch != epoch &&
+            (!best || a->prefer < best->prefer || (a->prefer == best->prefer && a->last_use < best->last_use)) && node_resident(a) > 0)
+            best = a;
     return best;
 }
 static int vmm_evict_node(alloc_node_t *v) {
@@ -1788,6 +1794,20 @@ EXPORT int cuVGPUOversubStats(uint64_t out[8]) {
     pthread_mutex_unlock(&g_alloc_mu);
     pthread_mutex_unlock(&g_res_mu);
     return 0;
+}
+
+/* cuVGPUResidentBytes: how much of the managed range around `p` is backed by HBM right now (-1: not a managed range) */
+EXPORT long long cuVGPUResidentBytes(CUdeviceptr p) {
+    if (!g_backend_vmm) return -1;
+    pthread_mutex_lock(&g_res_mu);
+    pthread_mutex_lock(&g_alloc_mu);
+    alloc_node_t *a = vmm_find(p);
+    tl_bypass = 1;
+    const long long r = a ? (long long)(node_resident(a) * IPCSIZE) : -1;
+    tl_bypass = 0;
+    pthread_mutex_unlock(&g_alloc_mu);
+    pthread_mutex_unlock(&g_res_mu);
+    return r;
 }
 
 /* cuLaunchKernel@0x37c2b: the suspend gate stays; rate_limiter@0x463b1 is gone — the SM cap is
@@ -2264,11 +2284,16 @@ EXPORT CUresult cuMemPrefetchAsync(CUdeviceptr p, size_t n, CUdevice d, void *st
     if (!tl_bypass && d >= 0 && !to_phys(&d)) return 101;
     return f ? f(p, n, d, stream) : 3;
 }
-/* advice about a VMM-backed allocation has nothing to act on (no fault-driven migration): accepted, ignored */
-static int vmm_backed(CUdeviceptr p) {
+/* Advice about a managed range: there is no fault-driven migration to steer, but the preferred location is a
+ * statement about who should keep its HBM under pressure — SET_PREFERRED_LOCATION (3) towards a device makes the range
+ * the last candidate for spilling, towards the CPU the first; UNSET (4) takes it back.  Everything else is accepted
+ * and ignored.  -> 1 when the pointer is ours */
+static int vmm_advise(CUdeviceptr p, int advice, int to_device) {
     if (!g_backend_vmm || tl_bypass) return 0;
     pthread_mutex_lock(&g_alloc_mu);
     alloc_node_t *a = vmm_find(p);
+    if (a && advice == 3) a->prefer = to_device ? 1 : -1;
+    if (a && advice == 4) a->prefer = 0;
     pthread_mutex_unlock(&g_alloc_mu);
     return a != NULL;
 }
@@ -2277,7 +2302,7 @@ EXPORT CUresult cuMemAdvise(CUdeviceptr p, size_t n, int advice, CUdevice d) {
     typedef CUresult (*fn_t)(CUdeviceptr, size_t, int, CUdevice);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuMemAdvise");
-    if (vmm_backed(p)) return 0;
+    if (vmm_advise(p, advice, d >= 0)) return 0;
     if (!tl_bypass && d >= 0 && !to_phys(&d)) return 101;
     return f ? f(p, n, advice, d) : 3;
 }
@@ -2295,7 +2320,7 @@ EXPORT CUresult cuMemAdvise_v2(CUdeviceptr p, size_t n, int advice, shim_mem_loc
     typedef CUresult (*fn_t)(CUdeviceptr, size_t, int, shim_mem_location_t);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuMemAdvise_v2");
-    if (vmm_backed(p)) return 0;
+    if (vmm_advise(p, advice, loc.type == 1)) return 0;
     if (!tl_bypass && !loc_to_phys(&loc)) return 101;
     return f ? f(p, n, advice, loc) : 3;
 }

@@ -780,3 +780,36 @@ def test_cooperative_grid_sized_from_the_sm_count_fits_inside_a_partition(cuda_d
     assert o["rc_big"] == 720
     free = last_json(run_under_shim(code, {"CUDA_DEVICE_SM_LIMIT": "100", "CUDA_DEVICE_MEMORY_LIMIT_0": "4g"}))
     assert free["partition"] == 0 and free["sms"] == 148 and free["rc_fit"] == 0 and free["rc_big"] == 0
+
+
+def test_preferred_location_advice_decides_who_keeps_the_hbm(cuda_dev):
+    """cuMemAdvise(SET_PREFERRED_LOCATION) on a managed range: towards the GPU it is spilled last, towards the CPU first —
+    ahead of the least-recently-used order.  Four 1 GiB ranges, 2.5 GiB may be resident."""
+    code = """
+        import ctypes as C, json, torch
+        cu, shim = C.CDLL("libcuda.so.1"), C.CDLL(None)
+        shim.cuVGPUResidentBytes.restype = C.c_longlong
+        torch.cuda.init()
+        G = 1 << 30
+        ts = [torch.empty(G // 8, dtype=torch.int64, device="cuda") for _ in range(4)]
+        def advise(t, advice, dev):
+            return cu.cuMemAdvise(C.c_ulonglong(t.data_ptr()), C.c_size_t(G), C.c_int(advice), C.c_int(dev))
+        def resident():
+            return [shim.cuVGPUResidentBytes(C.c_ulonglong(t.data_ptr())) // (1 << 20) for t in ts]
+        rc = [advise(ts[0], 3, 0), advise(ts[3], 3, -1)]      # range 0 prefers the GPU, range 3 the CPU
+        for i, t in enumerate(ts):
+            t.fill_(i + 1)                                     # touched in order 0, 1, 2, 3: range 0 is the oldest
+        torch.cuda.synchronize()
+        after_fill = resident()
+        s = int(ts[1][:1024].sum().item())                     # needs range 1 back: by age the victim would be range 0, by advice it is range 3
+        after_touch = resident()
+        ok = all(int(t[-1].item()) == i + 1 for i, t in enumerate(ts))
+        print(json.dumps({"rc": rc, "after_fill": after_fill, "after_touch": after_touch, "sum": s, "ok": ok}))
+    """
+    o = last_json(run_under_shim(code, {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "8g", "VGPU_OVERSUB_RESIDENT_MB": "2560"}))
+    print("advice:", o)
+    assert o["rc"] == [0, 0] and o["ok"] and o["sum"] == 2 * 1024
+    # after the fills: range 0 (the oldest, but it prefers the GPU) is still there; ranges 1 and 2 went instead
+    assert o["after_fill"] == [1024, 0, 0, 1024]
+    # bringing range 1 back spills range 3 (just used, but it prefers the CPU) and leaves range 0 (the oldest) alone
+    assert o["after_touch"] == [1024, 1024, 0, 0]
