@@ -71,7 +71,7 @@ class VmemStats(C.Structure):
     _fields_ = [("chunks_total", C.c_uint64), ("chunks_resident", C.c_uint64), ("chunks_spilled", C.c_uint64),
                 ("resident_limit", C.c_uint64), ("tier_slots", C.c_uint64), ("evictions", C.c_uint64),
                 ("fetches", C.c_uint64), ("checksum_failures", C.c_uint64), ("evict_ms", C.c_double), ("fetch_ms", C.c_double),
-                ("evictions_peer", C.c_uint64), ("evictions_host", C.c_uint64), ("restore_retries", C.c_uint64)]
+                ("evictions_peer", C.c_uint64), ("evictions_host", C.c_uint64), ("restore_retries", C.c_uint64), ("tier_setup_ms", C.c_double)]
 
 
 class SmPartition(C.Structure):

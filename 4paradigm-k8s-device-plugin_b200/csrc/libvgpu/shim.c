@@ -1769,6 +1769,7 @@ typedef struct {
     uint64_t chunks_total, chunks_resident, chunks_spilled, resident_limit, tier_slots, evictions, fetches, checksum_failures;
     double evict_ms, fetch_ms;
     uint64_t evictions_peer, evictions_host, restore_retries;
+    double tier_setup_ms;
 } shim_vmem_stats_t;
 EXPORT int cuVGPUOversubStats(uint64_t out[8]) {
     typedef int (*stats_t)(void *, shim_vmem_stats_t *);

@@ -124,6 +124,7 @@ struct Vmem {
     CUmemAccessDesc access[2]{};  // this GPU, and the peer GPU when there is a peer tier (it may pull the spill)
     size_t access_n = 1;
     vgpu_vmem_stats_t st{};
+    double t_sync = 0, t_launch = 0, t_wait = 0, t_unmap = 0, t_map = 0;  // where evict / ensure spend their wall time (VGPU_VMEM_TRACE)
     std::mutex mu;
     size_t block_bytes() const { return bc * kCB; }
 };
@@ -132,25 +133,52 @@ double now_ms() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
-int map_block(Vmem *v, size_t b) {
-    Block &bl = v->blocks[b];
-    CUmemGenericAllocationHandle h;
-    if (!v->pool.empty()) {
-        h = v->pool.back();
-        v->pool.pop_back();
-    } else {
-        CUresult r = g_api.Create(&h, v->block_bytes(), &v->prop, 0);
-        if (r != CUDA_SUCCESS) return drv_fail("cuMemCreate", r);
+// Back the blocks `list` (ascending) with physical memory.  cuMemMap costs under a microsecond; cuMemSetAccess costs
+// 0.2 ms per CALL whatever its size and — like cuMemUnmap — waits for the kernels that are running, so it is issued
+// once per run of consecutive blocks and BEFORE any restore kernel is launched, never between two of them
+// (interleaved per block, config 4 restored at 310-510 GB/s; this way the restore kernels run back to back).
+// All or nothing: on failure whatever this call mapped is unmapped again and parked.
+int map_blocks(Vmem *v, const std::vector<size_t> &list) {
+    const double t0 = now_ms();
+    size_t done = 0;
+    int rc = VGPU_OK;
+    for (; done < list.size(); ++done) {
+        const size_t b = list[done];
+        CUmemGenericAllocationHandle h;
+        if (!v->pool.empty()) {
+            h = v->pool.back();
+            v->pool.pop_back();
+        } else {
+            CUresult r = g_api.Create(&h, v->block_bytes(), &v->prop, 0);
+            if (r != CUDA_SUCCESS) {
+                rc = drv_fail("cuMemCreate", r);
+                break;
+            }
+        }
+        CUresult r = g_api.Map(v->base + b * v->block_bytes(), v->block_bytes(), 0, h, 0);
+        if (r != CUDA_SUCCESS) {
+            v->pool.push_back(h);
+            rc = drv_fail("cuMemMap", r);
+            break;
+        }
+        v->blocks[b].handle = h;
     }
-    const CUdeviceptr va = v->base + b * v->block_bytes();
-    CUresult r = g_api.Map(va, v->block_bytes(), 0, h, 0);
-    if (r == CUDA_SUCCESS) r = g_api.SetAccess(va, v->block_bytes(), v->access, v->access_n);
-    if (r != CUDA_SUCCESS) {
-        v->pool.push_back(h);
-        return drv_fail("cuMemMap/cuMemSetAccess", r);
+    for (size_t i = 0; i < done && !rc;) {  // one cuMemSetAccess per run of consecutive blocks
+        size_t j = i + 1;
+        while (j < done && list[j] == list[j - 1] + 1) ++j;
+        CUresult r = g_api.SetAccess(v->base + list[i] * v->block_bytes(), (j - i) * v->block_bytes(), v->access, v->access_n);
+        if (r != CUDA_SUCCESS) rc = drv_fail("cuMemSetAccess", r);
+        i = j;
     }
-    bl.handle = h;
-    return VGPU_OK;
+    if (rc)
+        for (size_t i = 0; i < done; ++i) {
+            Block &bl = v->blocks[list[i]];
+            g_api.Unmap(v->base + list[i] * v->block_bytes(), v->block_bytes());
+            v->pool.push_back(bl.handle);
+            bl.handle = 0;
+        }
+    v->t_map += now_ms() - t0;
+    return rc;
 }
 
 int unmap_block(Vmem *v, size_t b, bool release) {
@@ -169,10 +197,12 @@ void give_slot_back(Vmem *v, Block &bl) {
     t.evictions -= v->bc;
 }
 
-// Spill resident blocks `victims` to the tier, then unmap them and park or release their memory.
-// The unmap of block i-1 overlaps the spill kernel of block i.  State and counters move per block, at the moment
-// the block's bytes are safely in the tier AND its HBM is unmapped; whatever fails, every block is afterwards either
-// fully resident (slot returned) or fully spilled, and the counters say so.
+// Spill resident blocks `victims` to the tier, then unmap them and park or release their memory.  All spill kernels
+// are queued first and run back to back; the unmaps follow when the stream is idle.  (Round 1 unmapped block i-1 while
+// block i was being spilled, to overlap the two.  cuMemUnmap waits for the running kernel — 1.5 ms per 1 GiB block
+// instead of 0.1 ms on an idle GPU — so nothing overlapped and the link idled meanwhile: 525 GB/s; now the NVLink rate.)
+// State and counters move per block, once its bytes are safely in the tier AND its HBM is unmapped; whatever fails,
+// every block is afterwards either fully resident (slot returned) or fully spilled, and the counters say so.
 int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
     if (victims.empty()) return VGPU_OK;
     size_t free_total = 0;
@@ -181,21 +211,9 @@ int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
         return fail(VGPU_E_NOMEM, "spill tier full: %zu blocks to evict, %zu free slots", victims.size(), free_total);
     const double t0 = now_ms();
     VGPU_CUDA(cudaDeviceSynchronize());  // whatever the application queued on the victims must be done
-    size_t launched = 0, finalized = 0;
+    v->t_sync += now_ms() - t0;
+    size_t launched = 0;
     int rc = VGPU_OK;
-    // block j's spill has completed: release its HBM and book it as spilled
-    auto finalize = [&](size_t j) -> int {
-        Block &bl = v->blocks[victims[j]];
-        if (int urc = unmap_block(v, victims[j], release)) {
-            give_slot_back(v, bl);  // still mapped, still resident: the copy in the tier is simply dropped
-            return urc;
-        }
-        bl.state = kSpilled;
-        v->resident -= 1;
-        v->spilled += 1;
-        v->st.evictions += v->bc;
-        return VGPU_OK;
-    };
     for (size_t i = 0; i < victims.size() && !rc; ++i) {
         const size_t b = victims[i];
         Block &bl = v->blocks[b];
@@ -208,7 +226,10 @@ int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
             Vmem::Tier &c = v->tiers[ti];
             if (c.free_slots.empty()) continue;
             if (c.slab) break;
-            if (vgpu_slab_alloc(c.kind, v->device, c.peer, c.slots * v->block_bytes(), &c.slab) == VGPU_OK) break;
+            const double ts = now_ms();
+            const int src = vgpu_slab_alloc(c.kind, v->device, c.peer, c.slots * v->block_bytes(), &c.slab);
+            v->st.tier_setup_ms += now_ms() - ts;  // one-time: a context on the peer and its slab, or pinning the host slab
+            if (src == VGPU_OK) break;
             // e.g. the peer GPU is not idle after all: give this tier up and fall through to the next
             c.free_slots.clear();
             c.slots = 0;
@@ -219,31 +240,43 @@ int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
         bl.tier_slot = t.free_slots.back();
         t.free_slots.pop_back();
         t.evictions += v->bc;
-        rc = vgpu_spill(VGPU_XFER_AUTO, t.kind, (const void *)(v->base + b * v->block_bytes()),
+        const double tl = now_ms();
+        // a range the peer was not given access to (see create) cannot be pulled, whatever the policy says by now
+        const int variant = (t.kind == VGPU_TIER_PEER && v->access_n < 2 && vgpu_policy_get(VGPU_TIER_PEER, v->bc) == VGPU_XFER_PULL)
+                                ? VGPU_XFER_TMA : VGPU_XFER_AUTO;
+        rc = vgpu_spill(variant, t.kind, (const void *)(v->base + b * v->block_bytes()),
                         (char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(), nullptr, nullptr, v->bc, kCB,
                         v->ck + b * v->bc, v->stream);
-        if (!rc && cudaEventRecord(v->ev[i & 1], v->stream) != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaEventRecord (evict)");
+        v->t_launch += now_ms() - tl;
         if (rc) {
-            give_slot_back(v, bl);  // nothing of this block is in flight (or what is gets drained below): it stays resident
+            give_slot_back(v, bl);  // nothing of this block was queued: it stays resident
             break;
         }
         launched = i + 1;
-        if (i > 0) {
-            if (cudaEventSynchronize(v->ev[(i - 1) & 1]) != cudaSuccess) rc = fail(VGPU_E_CUDA, "cudaEventSynchronize (evict)");
-            else rc = finalize(i - 1);
-            finalized = i;  // on failure block i-1 was put back to "resident": it is dealt with either way
-        }
     }
-    // drain: every block whose spill was launched is in the tier once the stream is idle
-    if (launched > finalized) {
-        if (cudaStreamSynchronize(v->stream) != cudaSuccess) {
-            if (!rc) rc = fail(VGPU_E_CUDA, "cudaStreamSynchronize (evict)");
-            for (size_t j = finalized; j < launched; ++j) give_slot_back(v, v->blocks[victims[j]]);  // cannot trust the copies
-        } else {
-            for (size_t j = finalized; j < launched; ++j)
-                if (int frc = finalize(j); frc && !rc) rc = frc;
-        }
+    // every block whose spill was queued is in the tier once the stream is idle
+    const double tw = now_ms();
+    const cudaError_t se = launched ? cudaStreamSynchronize(v->stream) : cudaSuccess;
+    v->t_wait += now_ms() - tw;
+    if (se != cudaSuccess) {
+        if (!rc) rc = fail(VGPU_E_CUDA, "cudaStreamSynchronize (evict): %s", cudaGetErrorString(se));
+        for (size_t j = 0; j < launched; ++j) give_slot_back(v, v->blocks[victims[j]]);  // cannot trust the copies
+        launched = 0;
     }
+    const double tu = now_ms();
+    for (size_t j = 0; j < launched; ++j) {
+        Block &bl = v->blocks[victims[j]];
+        if (int urc = unmap_block(v, victims[j], release)) {
+            give_slot_back(v, bl);  // still mapped, still resident: the copy in the tier is simply dropped
+            if (!rc) rc = urc;
+            continue;
+        }
+        bl.state = kSpilled;
+        v->resident -= 1;
+        v->spilled += 1;
+        v->st.evictions += v->bc;
+    }
+    v->t_unmap += now_ms() - tu;
     v->st.evict_ms += now_ms() - t0;
     return rc;
 }
@@ -295,7 +328,10 @@ int vgpu_vmem_create_tiered(int device, uint64_t virtual_bytes, uint64_t residen
     v->prop.location.id = device;
     v->access[0].location = v->prop.location;
     v->access[0].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
-    if (peer_bytes) {
+    // The peer GPU needs access to OUR range only for the PULL form of the spill (its kernel reads our HBM), i.e. when
+    // the peer tier's policy can select it (after vgpu_calibrate on an idle peer).  Otherwise every map / unmap would
+    // also have to update the peer's page tables for nothing.
+    if (peer_bytes && vgpu_policy_get(VGPU_TIER_PEER, v->bc) == VGPU_XFER_PULL) {
         v->access[1].location.type = CU_MEM_LOCATION_TYPE_DEVICE;
         v->access[1].location.id = peer_device;
         v->access[1].flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
@@ -386,13 +422,18 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
     }
     const double t0 = now_ms();
     int result = VGPU_OK;
-    for (size_t b : fresh) {  // state and counter move together, block by block
-        if ((result = map_block(v, b)) != VGPU_OK) break;
-        v->blocks[b].state = kResident;
-        v->resident += 1;
-    }
-    // Spilled blocks: map block k+1 on the host while the GPU restores block k.  Each launch reports into its own
-    // result slot, so a checksum failure names its block.
+    // never-touched blocks and spilled blocks are backed in one pass (map_blocks: all or nothing) ...
+    std::vector<size_t> to_map(fresh);
+    to_map.insert(to_map.end(), back.begin(), back.end());
+    std::sort(to_map.begin(), to_map.end());
+    result = map_blocks(v, to_map);
+    if (result == VGPU_OK)
+        for (size_t b : fresh) {
+            v->blocks[b].state = kResident;
+            v->resident += 1;
+        }
+    // ... then the restore kernels of the spilled ones run back to back.  Each launch reports into its own result
+    // slot, so a checksum failure names its block.
     auto restore_block = [&](size_t b, int variant) -> int {
         Block &bl = v->blocks[b];
         Vmem::Tier &t = v->tiers[bl.tier_idx];
@@ -403,14 +444,12 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
                             &v->res[b], v->stream);
     };
     std::vector<size_t> launched;
-    for (size_t b : back) {
-        if (result) break;
-        if ((result = map_block(v, b)) != VGPU_OK) break;
-        if ((result = restore_block(b, VGPU_XFER_AUTO)) != VGPU_OK) {
-            unmap_block(v, b, false);  // nothing was launched into it: the block stays spilled, its slot stays taken
+    for (size_t i = 0; i < back.size() && !result; ++i) {
+        if ((result = restore_block(back[i], VGPU_XFER_AUTO)) != VGPU_OK) {
+            for (size_t k = i; k < back.size(); ++k) unmap_block(v, back[k], false);  // nothing was launched into these: they stay spilled, slots taken
             break;
         }
-        launched.push_back(b);
+        launched.push_back(back[i]);
     }
     if (!launched.empty()) {
         const bool drained = cudaStreamSynchronize(v->stream) == cudaSuccess;
@@ -500,6 +539,9 @@ int vgpu_vmem_destroy(void *handle) {
     Vmem *v = static_cast<Vmem *>(handle);
     if (!v) return VGPU_OK;
     CtxScope keep;
+    if (getenv("VGPU_VMEM_TRACE"))
+        fprintf(stderr, "[vgpu_vmem] evict %.1f ms = device sync %.1f + spill launches %.1f + waits %.1f + unmap %.1f + tier set-up %.1f; fetch %.1f ms of which map %.1f\n",
+                v->st.evict_ms, v->t_sync, v->t_launch, v->t_wait, v->t_unmap, v->st.tier_setup_ms, v->st.fetch_ms, v->t_map);
     cudaSetDevice(v->device);
     cudaDeviceSynchronize();
     for (size_t b = 0; b < v->blocks.size(); ++b)

@@ -30,8 +30,10 @@ sys.path.insert(0, ROOT)
 # One hardware work queue per vGPU stream.  CUDA's default is 8 connections per context; the ten partition streams of
 # config 5 (plus the transfer stream) then alias onto shared queues and kernels of DIFFERENT vGPUs serialise behind
 # each other in launch order — measured: 3.9 TB/s instead of 6.5-7.2 TB/s for ten 12-14-SM partitions
-# (profiles/r02_concurrency.md).  Must be set before the CUDA context exists.
-os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+# (profiles/r02_concurrency.md).  Must be set before the CUDA context exists.  12 = ten vGPU streams + the transfer
+# stream + the default stream: every further connection makes context creation slower (the peer tier's one-time
+# set-up: 0.36 s with 8, 0.47 s with 12, 1.8 s with 32) for nothing.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "12")
 
 METRIC = "vGPU spill/restore GB/s per GPU + 8-GPU aggregate; memtest HBM GB/s vs peak"
 GIB = 1 << 30
@@ -604,7 +606,9 @@ def config4_phase(args, capi, torch, local, world, ranks):
             out = {"tier": "peer HBM (GPU 1) over NVLink" if world > 1 else "pinned host over PCIe", "scale": scale,
                    "virtual_GB": round(total * cb / 1e9, 1), "resident_limit_GB": round(resident * cb / 1e9, 1), "window_chunks": win,
                    "chunks_spilled_total": st.evictions, "chunks_restored_total": st.fetches,
-                   "spill_GBps_incl_unmap": round(st.evictions * cb / (st.evict_ms * 1e6), 1) if st.evict_ms else None,
+                   "spill_GBps_incl_unmap": round(st.evictions * cb / ((st.evict_ms - st.tier_setup_ms) * 1e6), 1) if st.evict_ms > st.tier_setup_ms else None,
+                   "tier_setup_ms_once": round(st.tier_setup_ms, 1),
+                   "spill_GBps_incl_unmap_and_setup": round(st.evictions * cb / (st.evict_ms * 1e6), 1) if st.evict_ms else None,
                    "restore_GBps_incl_map": round(st.fetches * cb / (st.fetch_ms * 1e6), 1) if st.fetch_ms and st.fetches else None,
                    "write_pass_GBps": round(total * cb / (t1 - t0) / 1e9, 1), "verify_pass_GBps": round(total * cb / (t2 - t1) / 1e9, 1),
                    "bit_exact": True}
@@ -737,7 +741,7 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, peer, ranks):
         if rc != 0:
             raise SystemExit("peer slab: " + capi.last_error())
         tiers["peer"] = (capi.TIER_PEER, peer_slab.value, None)
-    out = {"chunk_bytes": cb, "bytes_counted": "payload once per chunk per direction", "timing": "CUDA events on the launch stream, best of 5 after 2 warm-ups, max over ranks"}
+    out = {"chunk_bytes": cb, "bytes_counted": "payload once per chunk per direction", "timing": "CUDA events on the launch stream, best of 5 (20 for batches of up to 64 chunks) after 2 warm-ups, max over ranks"}
     if "peer" in tiers and world == 1:
         # An idle peer (nobody else's context on it): let the library measure its variants on this box, as a deployment
         # does at start-up — "switch ... when measured bandwidth favours it".  With the peer idle the PULL form of the
@@ -782,14 +786,16 @@ def spill_sweep(args, capi, dp, torch, dev, local, world, peer, ranks):
             if cap is not None and n > cap:
                 continue
             row = {}
+            hp, bp, ckp, rp = hbm.data_ptr(), back.data_ptr(), ck.data_ptr(), res.data_ptr()   # not inside the timed call
+            reps = 20 if n <= 64 else 5   # a small batch is a ~10 us event: more samples for the minimum
             for vname, v in tvariants.items():
                 def do_spill():
-                    capi.check(capi.lib.vgpu_spill(v, tier, hbm.data_ptr(), slab, None, None, n, cb, ck.data_ptr(), stream))
+                    capi.check(capi.lib.vgpu_spill(v, tier, hp, slab, None, None, n, cb, ckp, stream))
 
                 def do_restore():
-                    capi.check(capi.lib.vgpu_restore(v, tier, slab, back.data_ptr(), None, None, n, cb, ck.data_ptr(), None, res.data_ptr(), stream))
-                ms_s = time_call(do_spill)
-                ms_r = time_call(do_restore)
+                    capi.check(capi.lib.vgpu_restore(v, tier, slab, bp, None, None, n, cb, ckp, None, rp, stream))
+                ms_s = time_call(do_spill, reps=reps)
+                ms_r = time_call(do_restore, reps=reps)
                 row[vname] = {"spill_GBps": round(world * n * cb / (ms_s * 1e6), 1), "restore_GBps": round(world * n * cb / (ms_r * 1e6), 1)}
             tout[str(n)] = row
         n = max(int(k) for k in tout)

@@ -253,6 +253,8 @@ typedef struct vgpu_vmem_stats {
     double   evict_ms, fetch_ms;          /* wall time spent in evict / fetch incl. map/unmap */
     uint64_t evictions_peer, evictions_host; /* chunks sent to each tier */
     uint64_t restore_retries;             /* blocks restored a second time (copy engine) after a checksum failure */
+    double   tier_setup_ms;               /* part of evict_ms spent ONCE per tier: a context on the peer and its slab, or
+                                             pinning the host slab (first eviction that needs the tier) */
 } vgpu_vmem_stats_t;
 
 /* Create a range of `virtual_bytes` (rounded up to 2 MiB) on `device`, of which at most
