@@ -131,6 +131,47 @@ def test_two_tiers_peer_first_then_host(vgpu, cuda_dev):
         capi.lib.vgpu_vmem_destroy(h)
 
 
+@pytest.mark.parametrize("pull", [False, True])
+def test_peer_tier_spills_pushed_or_pulled_by_the_idle_peer(vgpu, cuda_dev, pull):
+    """With an idle peer the policy may select the PULL spill (the kernel runs on the peer and reads our HBM: 788 instead
+    of 717 GB/s); the manager then gives the peer access to the range.  A range created under the push policy is never
+    pulled, even if the policy changes afterwards (the peer has no access to it)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("peer tier needs 2 GPUs")
+    import os
+    capi = vgpu.capi
+    before = capi.lib.vgpu_policy_get(capi.TIER_PEER, 8)
+    os.environ["VGPU_VMEM_BLOCK_CHUNKS"] = "8"
+    total = 64
+    h = C.c_void_p()
+    try:
+        if pull:
+            assert capi.lib.vgpu_policy_set(capi.TIER_PEER, 0, capi.XFER_PULL) == 0
+        rc = capi.lib.vgpu_vmem_create_tiered(0, total * CB, total * CB, 1, total * CB, 0, C.byref(h))
+        assert rc == 0, capi.last_error()
+        if not pull:                                   # the policy turns to PULL after the range exists
+            assert capi.lib.vgpu_policy_set(capi.TIER_PEER, 0, capi.XFER_PULL) == 0
+        base = C.c_void_p()
+        assert capi.lib.vgpu_vmem_base(h, C.byref(base)) == 0
+        res = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+        assert capi.lib.vgpu_vmem_ensure(h, 0, total) == 0, capi.last_error()
+        assert capi.lib.vgpu_memtest_fill(base.value, total * CB, capi.PAT_RANDOM, 9, 3, None) == 0
+        torch.cuda.synchronize()
+        assert capi.lib.vgpu_vmem_evict(h, 0, total) == 0, capi.last_error()
+        tier, ptr = C.c_int(-1), C.c_void_p()
+        assert capi.lib.vgpu_vmem_locate(h, 5, C.byref(tier), C.byref(ptr)) == 0 and tier.value == capi.TIER_PEER
+        assert capi.lib.vgpu_vmem_ensure(h, 0, total) == 0, capi.last_error()
+        assert capi.lib.vgpu_memtest_verify(base.value, total * CB, capi.PAT_RANDOM, 9, 3, res.data_ptr(), None) == 0
+        torch.cuda.synchronize()
+        s = _stats(capi, h)
+        assert res.cpu().tolist() == [0, 0, 0] and s.checksum_failures == 0 and s.evictions_peer == total
+    finally:
+        os.environ.pop("VGPU_VMEM_BLOCK_CHUNKS", None)
+        capi.lib.vgpu_policy_set(capi.TIER_PEER, 0, before)
+        if h:
+            capi.lib.vgpu_vmem_destroy(h)
+
+
 def test_failed_restore_keeps_the_tier_copy_and_a_later_ensure_succeeds(vgpu, cuda_dev):
     """A chunk that comes back from the tier with the wrong checksum must not cost the data: the block is restored once
     more through the copy engine, and if that fails too it is unmapped again and stays spilled (slot and checksums
