@@ -67,6 +67,9 @@ def parse():
                     help="2 MiB chunks the e2e step spills to / restores from a host buffer (256 = 512 MiB each way per GPU per step: fits inside "
                          "the memtest step's window even where eight GPUs share one host path at 12 GB/s each; the host rates themselves are in "
                          "e2e.components and roofline.pcie)")
+    ap.add_argument("--xfer-priority", default="normal", choices=["normal", "high"],
+                    help="config 5: stream priority of the spill / restore loop beside the memtest partitions")
+    ap.add_argument("--peer-grid", type=int, default=0, help="config 5: CTAs per peer-tier transfer launch (0 = the library's default)")
     ap.add_argument("--e2e-variant", default="auto", choices=["auto", "ldst", "tma", "ce"], help="transfer variant of the e2e step's host-buffer calls")
     return ap.parse_args()
 
@@ -640,7 +643,9 @@ def config5_phase(args, capi, dp, torch, dev, local, world, peer, ranks, hbm_pea
     slab = C.c_void_p()
     tier, pd = (capi.TIER_PEER, peer) if peer is not None else (capi.TIER_HOST, -1)
     capi.check(capi.lib.vgpu_slab_alloc(tier, local, pd, n * cb, C.byref(slab)))
-    xs = torch.cuda.Stream(device=dev)
+    if args.peer_grid:
+        capi.check(capi.lib.vgpu_policy_set_grid(capi.TIER_PEER, args.peer_grid))
+    xs = torch.cuda.Stream(device=dev, priority=-1 if args.xfer_priority == "high" else 0)
     mts = torch.cuda.Stream(device=dev)  # carries only the "all memtests done" event
     xstream = C.c_void_p(xs.cuda_stream)
     main = torch.cuda.current_stream()
@@ -706,6 +711,8 @@ def config5_phase(args, capi, dp, torch, dev, local, world, peer, ranks, hbm_pea
            "timing": "CUDA events bracketing all partition streams, max over ranks; aggregate over all GPUs unless marked per_gpu",
            "bit_exact": True}
     torch.cuda.synchronize()
+    if args.peer_grid:
+        capi.lib.vgpu_policy_set_grid(capi.TIER_PEER, 0)
     if parts is not None:
         capi.lib.vgpu_sm_partition_destroy(parts, nv)
     capi.lib.vgpu_slab_free(tier, local, pd, slab)
