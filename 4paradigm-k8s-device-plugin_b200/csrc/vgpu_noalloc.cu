@@ -103,7 +103,17 @@ extern "C" int vgpu_spill_noalloc(const void *src, void *dst, const uint32_t *sr
     a.acc = acc;  // the resolved device address, not the symbol
     a.cksum = cksum;
     const uint64_t total = (uint64_t)nchunks * a.tiles_per_chunk;
-    const unsigned grid = (unsigned)std::min<uint64_t>(total, (uint64_t)sms * 32);
+    // Where the destination lives decides the grid, as in vgpu_spill: pinned host memory is PCIe-bound and 32 CTAs
+    // saturate it — more would only park on the SMs of the tenants this eviction is meant to relieve.  (A query, not
+    // an allocation.)
+    uint64_t cap = (uint64_t)sms * 32;
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, dst) == cudaSuccess) {
+        if (at.type == cudaMemoryTypeHost) cap = 32;
+    } else {
+        cudaGetLastError();
+    }
+    const unsigned grid = (unsigned)std::min<uint64_t>(total, cap);
     k_xfer_ldst<U, true><<<grid, kXfThreads, 0, st>>>(a);
     VGPU_CUDA(cudaGetLastError());
     return VGPU_OK;

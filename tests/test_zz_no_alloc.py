@@ -90,3 +90,21 @@ def test_noalloc_spill_refuses_batches_beyond_its_fixed_scratch(vgpu, cuda_dev):
     assert "exceed the fixed scratch of 4096 chunks" in capi.last_error()
     assert capi.lib.vgpu_spill_noalloc(a.data_ptr(), a.data_ptr(), None, None, 0, 32, None, None) == 0  # empty batch: no-op
     assert capi.lib.vgpu_spill_noalloc(a.data_ptr() + 8, a.data_ptr(), None, None, 1, 32, ck.data_ptr(), None) == capi.E_INVAL
+
+
+def test_noalloc_spill_to_pinned_host_memory(vgpu, cuda_dev):
+    """The usual destination of an eviction made from inside a hook is the host tier: pinned, mapped host memory.  The
+    entry point then launches the small grid a PCIe-bound transfer needs (it asks where `dst` lives; it still allocates
+    nothing).  Bytes and checksums against the oracle."""
+    capi, dp = vgpu.capi, vgpu.datapath
+    cb, n = capi.CHUNK_BYTES, 24
+    src = torch.empty(n * cb, dtype=torch.uint8, device=cuda_dev)
+    dp.memtest_fill(src, capi.PAT_RANDOM, 21)
+    host = torch.zeros(n * cb, dtype=torch.uint8).pin_memory()
+    ck = torch.zeros((n, 2), dtype=torch.int64, device=cuda_dev)
+    rc = capi.lib.vgpu_spill_noalloc(src.data_ptr(), host.data_ptr(), None, None, n, cb, ck.data_ptr(), None)
+    assert rc == 0, capi.last_error()
+    torch.cuda.synchronize()
+    want, o_dst = _oracle_spill(src, n, cb)
+    assert np.array_equal(ck.cpu().numpy().view(np.uint64), want)
+    assert np.array_equal(host.numpy(), o_dst)
