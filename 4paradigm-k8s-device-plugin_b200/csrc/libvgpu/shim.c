@@ -1657,7 +1657,7 @@ static const pscan_t *kernel_params(void *fn) {
         int n = 0;
         size_t off = 0, size = 0;
         CUresult r;
-        while (n < PSCAN_MAX && (r = q(fn, (size_t)n, &off, &size)) == 0) e->size[n++] = (unsigned short)(size > 4096 ? 4096 : size);
+        while (n < PSCAN_MAX && (r = q(fn, (size_t)n, &off, &size)) == 0) e->size[n++] = (unsigned short)(size > 32764 ? 32764 : size);  /* CUDA 12.1+: up to 32 764 B of arguments */
         if (n > 0) {
             e->n = n;
             break;

@@ -813,3 +813,52 @@ def test_preferred_location_advice_decides_who_keeps_the_hbm(cuda_dev):
     assert o["after_fill"] == [1024, 0, 0, 1024]
     # bringing range 1 back spills range 3 (just used, but it prefers the CPU) and leaves range 0 (the oldest) alone
     assert o["after_touch"] == [1024, 1024, 0, 0]
+
+
+TRAIN = """
+    import json, torch
+    torch.manual_seed(0)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dev = "cuda"
+    D, L, B = 8192, 6, 2048                     # 6 layers x 256 MiB of fp32 weights; with grads and momentum ~4.5 GiB + activations
+    layers = [torch.nn.Linear(D, D, bias=True, device=dev) for _ in range(L)]
+    for l in layers:
+        torch.nn.init.kaiming_normal_(l.weight, nonlinearity="relu")         # activations keep their scale, so the loss really moves
+    params = [p for l in layers for p in l.parameters()]
+    opt = torch.optim.SGD(params, lr=2e-2, momentum=0.9, foreach=True)       # multi-tensor kernels: pointer lists inside the argument struct
+    x = torch.randn(B, D, device=dev)
+    y = torch.randn(B, D, device=dev)
+    losses = []
+    for step in range(4):
+        h = x
+        for l in layers:
+            h = torch.relu(l(h))
+        loss = torch.nn.functional.mse_loss(h, y)
+        opt.zero_grad(set_to_none=False)
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    w = sum(float(p.double().sum().item()) for p in params)
+    import ctypes
+    st = (ctypes.c_uint64 * 8)()
+    try:
+        ctypes.CDLL(None).cuVGPUOversubStats(st)
+    except AttributeError:
+        pass
+    print(json.dumps({"losses": losses, "w": w, "to_host": st[1], "restored": st[2], "bad": st[3], "paged": st[6]}))
+"""
+
+
+def test_a_training_loop_gives_the_same_numbers_when_it_is_paged(cuda_dev):
+    """cuBLAS GEMMs, elementwise / reduction kernels, autograd and a multi-tensor optimizer under the residency engine: a
+    6-layer MLP whose weights, gradients and momentum do not fit the 2 GiB its managed ranges may occupy trains for four
+    steps; losses and the final weights equal those of the same program with everything resident, bit for bit."""
+    base = {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "24g"}
+    ref = last_json(run_under_shim(TRAIN, base, timeout=900))
+    p = run_under_shim(TRAIN, {**base, "VGPU_OVERSUB_RESIDENT_MB": "2048"}, timeout=900)
+    got = last_json(p)
+    print("paged training:", got)
+    assert ref["paged"] == 0 and ref["to_host"] == 0
+    assert got["paged"] == 1 and got["to_host"] > 1024 and got["restored"] > 1024 and got["bad"] == 0, p.stderr[-2000:]
+    assert got["losses"] == ref["losses"] and got["w"] == ref["w"]
+    assert len(set(got["losses"])) == 4 and got["losses"][-1] < got["losses"][0]      # it did train
