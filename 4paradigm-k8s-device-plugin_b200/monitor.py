@@ -126,6 +126,22 @@ def publish_memory(path: str, by_hostpid: Dict[int, List[int]]) -> int:
     return n
 
 
+def nvml_process_memory() -> Dict[int, Dict[str, int]]:
+    """{host pid: {GPU UUID (lower case): bytes of HBM NVML attributes to the process}} — what a tenant really holds, as
+    opposed to what it has allocated against its quota (a tenant that pages itself holds less than its usage; a
+    suspended one next to nothing).  Feed it to Scheduler(measured=...) and to publish_memory."""
+    import pynvml
+    pynvml.nvmlInit()
+    out: Dict[int, Dict[str, int]] = {}
+    for i in range(pynvml.nvmlDeviceGetCount()):
+        h = pynvml.nvmlDeviceGetHandleByIndex(i)
+        u = pynvml.nvmlDeviceGetUUID(h)
+        u = (u.decode() if isinstance(u, bytes) else u).lower()
+        for p in pynvml.nvmlDeviceGetComputeRunningProcesses(h):
+            out.setdefault(int(p.pid), {})[u] = int(p.usedGpuMemory or 0)
+    return out
+
+
 # ----------------------------------------------------------------------------- the scheduler
 class Tenant:
     """One container (one cache file) as the scheduler sees it."""
@@ -166,8 +182,12 @@ class Scheduler:
     default); `kill` and `hbm_of` are injectable for tests."""
 
     def __init__(self, shared_root: str = "/usr/local/vgpu/shared", hbm: Dict[str, int] = None, headroom: int = 2 << 30,
-                 quantum: int = 10, kill=os.kill, log=None, hbm_free=None):
+                 quantum: int = 10, kill=os.kill, log=None, hbm_free=None, measured=None):
         self.root, self.hbm, self.headroom, self.quantum, self.kill = shared_root, hbm, headroom, quantum, kill
+        # measured() -> {host pid: {uuid: bytes}} (nvml_process_memory): when given, a RUNNING tenant's demand is what it
+        # really holds in HBM rather than what it has allocated (a self-paging tenant allocates more than it holds); a
+        # tenant about to be resumed is still counted with its allocation — that is what it will want back.
+        self.measured = measured
         # hbm_free(uuid) -> bytes really free on the GPU right now, or None to trust the accounting.  A suspend takes
         # time (the tenant's data is on its way to the tier); nobody is resumed into HBM that is not there yet.
         self.hbm_free = hbm_free
@@ -241,6 +261,16 @@ class Scheduler:
             self._balance(g)
         return self.actions
 
+    def _held(self, t: Tenant, g: str, seen: Dict[int, Dict[str, int]]) -> int:
+        """HBM a running tenant occupies on GPU g: measured when every one of its processes is known to NVML, else its
+        allocation."""
+        if seen is None:
+            return t.usage(g)
+        pids_ = [p["hostpid"] for p in t.region.get("procs", []) if p["pid"] > 0]
+        if not pids_ or any(p <= 0 or p not in seen for p in pids_):
+            return t.usage(g)
+        return min(t.usage(g), sum(seen[p].get(g, 0) for p in pids_))
+
     def _balance(self, g: str) -> None:
         cap = self._hbm(g) - self.headroom
         if cap <= 0:
@@ -248,16 +278,18 @@ class Scheduler:
         here = [t for t in self.tenants.values() if t.usage(g) > 0 or t.limit(g) > 0]
         running = [t for t in here if not t.suspended]
         waiting = [t for t in here if t.suspended]
-        demand = sum(t.usage(g) for t in running)
+        seen = self.measured() if self.measured else None
+        held = {t.name: self._held(t, g, seen) for t in running}
+        demand = sum(held.values())
         # 1. over-committed: the least important, longest idle, largest go first; one tenant always stays
         if demand > cap and len(running) > 1:
-            for t in sorted(running, key=lambda t: (-t.priority, -t.idle_ticks, -t.usage(g), t.name)):
+            for t in sorted(running, key=lambda t: (-t.priority, -t.idle_ticks, -held[t.name], t.name)):
                 if demand <= cap or len(running) <= 1:
                     break
                 self._do("suspend", t)
                 running.remove(t)
                 waiting.append(t)
-                demand -= t.usage(g)
+                demand -= held[t.name]
             return
         # 2. room: the most important, longest waiting come back while they fit
         free_now = self.hbm_free(g) if self.hbm_free else None
@@ -279,14 +311,14 @@ class Scheduler:
                 if r.priority < t.priority or self.now - r.since < self.quantum:
                     continue
                 victims.append(r)
-                freed += r.usage(g)
+                freed += held.get(r.name, r.usage(g))
                 if demand - freed + t.usage(g) <= cap:
                     break
             if victims and demand - freed + t.usage(g) <= cap:
                 for r in victims:
                     self._do("suspend", r)
                     running.remove(r)
-                    demand -= r.usage(g)
+                    demand -= held.get(r.name, r.usage(g))
                 break   # the waiting tenant is resumed by rule 2 on the next tick, once the HBM is really free
 
     def run(self, period: float = 1.0, ticks: int = 0) -> None:
@@ -302,8 +334,17 @@ if __name__ == "__main__":  # python monitor.py list|suspend|resume <cache file>
     import json
     import sys
     cmd = sys.argv[1] if len(sys.argv) > 1 else ""
-    if cmd == "run":
-        Scheduler(sys.argv[2] if len(sys.argv) > 2 else "/usr/local/vgpu/shared",
+    if cmd == "run":  # on a node: demand and free HBM as NVML measures them
+        def _free(uuid):
+            import pynvml
+            pynvml.nvmlInit()
+            for i in range(pynvml.nvmlDeviceGetCount()):
+                h = pynvml.nvmlDeviceGetHandleByIndex(i)
+                u = pynvml.nvmlDeviceGetUUID(h)
+                if (u.decode() if isinstance(u, bytes) else u).lower() == uuid.lower():
+                    return pynvml.nvmlDeviceGetMemoryInfo(h).free
+            return None
+        Scheduler(sys.argv[2] if len(sys.argv) > 2 else "/usr/local/vgpu/shared", hbm_free=_free, measured=nvml_process_memory,
                   log=lambda *a: print(*a, flush=True)).run(float(sys.argv[3]) if len(sys.argv) > 3 else 1.0)
     elif cmd == "list":
         print(json.dumps(read_region(sys.argv[2]), indent=1))

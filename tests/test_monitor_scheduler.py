@@ -158,3 +158,22 @@ def test_nobody_is_resumed_into_hbm_that_is_not_free_yet(tmp_path):
     assert s.tick() == [] and s.tick() == []
     free["v"] = 150 * GiB
     assert s.tick() == [("resume", "b")]
+
+
+def test_measured_hbm_counts_a_self_paging_tenant_by_what_it_holds(tmp_path):
+    """A tenant larger than its resident share pages itself (the shim): it has ALLOCATED 150 GiB but holds 40.  With the
+    NVML figures the scheduler sees that it fits next to a 100 GiB tenant and leaves both alone; by allocation alone it
+    would suspend one of them."""
+    n = Node(tmp_path)
+    n.add("pager", 150, 300, 11, 1011)
+    n.add("plain", 100, 120, 12, 1012)
+    by_alloc = sched(n)
+    assert [a[0] for a in by_alloc.tick()] == ["suspend"]
+    n2 = Node(tmp_path / "again")
+    n2.add("pager", 150, 300, 21, 2021)
+    n2.add("plain", 100, 120, 22, 2022)
+    seen = {2021: {UUID.lower(): 40 * GiB}, 2022: {UUID.lower(): 100 * GiB}}
+    s = M.Scheduler(n2.root, hbm=dict(HBM), headroom=4 * GiB, kill=n2.kill, measured=lambda: seen)
+    assert s.tick() == [] and n2.signals == []
+    seen[2021][UUID.lower()] = 90 * GiB            # the pager grows: 190 GiB held on a 176 GiB budget
+    assert [a[0] for a in s.tick()] == ["suspend"]
