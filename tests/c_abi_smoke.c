@@ -63,9 +63,23 @@ int main(void) {
     CHECK(strcmp(mounts[0].host_path, "/usr/local/vgpu/shared/train-0_worker") == 0 && strcmp(mounts[2].container_path, "/etc/ld.so.preload") == 0);
     CHECK(strcmp(env(envs, ne, "CUDA_DEVICE_MEMORY_SHARED_CACHE"), "/train-0_worker/01234567-89ab-4def-8123-456789abcdef.cache") == 0);
     CHECK(vgpu_allocate_env_monitor(&cfg, req, 2, pu, pi, 1, NULL, "a/b", envs, &ne, mounts, &nm) == VGPU_E_INVAL);
+    /* the one additive variable (no reference counterpart), off unless asked for: which SM partition each vGPU owns */
+    ne = 16; nm = 16;
+    CHECK(vgpu_allocate_env(&cfg, req, 2, pu, pi, 1, NULL, envs, &ne, mounts, &nm) == VGPU_OK && env(envs, ne, "VGPU_SM_PARTITION_INDEX_0") == NULL);
+    cfg.emit_partition_index = 1;
+    ne = 16; nm = 16;
+    CHECK(vgpu_allocate_env(&cfg, req, 2, pu, pi, 1, NULL, envs, &ne, mounts, &nm) == VGPU_OK && ne == 9);
+    CHECK(strcmp(env(envs, ne, "VGPU_SM_PARTITION_INDEX_0"), "3") == 0 && strcmp(env(envs, ne, "VGPU_SM_PARTITION_INDEX_1"), "7") == 0);
+    /* start()'s lspci pass (main.go:164-185) */
+    char bus[64];
+    CHECK(vgpu_pcibus_list("00:00.0 Host bridge: Intel\n1b:00.0 3D controller: NVIDIA Corporation Device 2901\n", bus, sizeof(bus)) == 1);
+    CHECK(strcmp(bus, "1b:00.0\n") == 0);
+    CHECK(vgpu_pcibus_list("1b:00.0 3D controller: NVIDIA Corporation Device 2901\n", bus, 4) == VGPU_E_RANGE);
     /* data-path argument checks need no GPU either */
     CHECK(vgpu_spill(VGPU_XFER_LDST, VGPU_TIER_LOCAL, NULL, NULL, NULL, NULL, 0, VGPU_CHUNK_BYTES, NULL, NULL) == VGPU_OK);
     CHECK(vgpu_spill_noalloc(NULL, NULL, NULL, NULL, VGPU_NOALLOC_MAX_CHUNKS + 1, 32, NULL, NULL) == VGPU_E_RANGE);
+    CHECK(vgpu_policy_set_grid(7, 32) == VGPU_E_INVAL && vgpu_policy_set_grid(VGPU_TIER_HOST, 0) == VGPU_OK);
+    CHECK(vgpu_policy_get(VGPU_TIER_LOCAL, 8) == VGPU_XFER_LDST && vgpu_policy_get(VGPU_TIER_LOCAL, 4) == VGPU_XFER_TMA);
     printf("c_abi_smoke ok\n");
     return 0;
 }
