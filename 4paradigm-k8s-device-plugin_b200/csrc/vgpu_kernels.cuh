@@ -40,12 +40,12 @@ __device__ __forceinline__ void st256(void *p, const U64x4 &v) {
                  : "memory");
 }
 
-__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
-    uint64_t z = x + kGolden;
+__device__ __forceinline__ uint64_t splitmix64_mix(uint64_t z) {  // the output function, z = state + golden
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
     return z ^ (z >> 31);
 }
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) { return splitmix64_mix(x + kGolden); }
 
 // Expected word `i` of a memtest pass.  `key` = pass for walking ones,
 // (kGolden ^ pass ^ seed) for random.
@@ -158,13 +158,33 @@ k_memtest_verify(const uint64_t *__restrict__ buf, uint64_t head, uint64_t nvec,
         if (v < nvec) w[u] = ld256(vbase + 4 * v);
     }
     uint64_t acc = 0;  // OR of got^expected over everything this thread owns
+    // Random pattern: word i is mix(z), z = key + golden + i.  The 16 words of a thread lie within 4*(kMtU-1)*T + 3
+    // indices of each other, so unless the low 32 bits of z wrap inside that span (one thread in ~2.8 million) they all
+    // share the HIGH word of z — and with it half of the first xorshift and a third of the first multiply, which the
+    // compiler then computes once per thread instead of once per word: 20 % fewer ALU-pipe instructions in a kernel that
+    // is bound by that pipe (6.5 -> 7.5 TB/s on the whole GPU, profiles/r02_concurrency.md §6).  Same bits either way.
+    const uint64_t zt = key + kGolden + head + 4 * base;
+    if (PAT == VGPU_PAT_RANDOM && (uint32_t)zt <= 0xFFFFFFFFu - (4u * (kMtU - 1) * T + 3u)) {
+        const uint32_t lo = (uint32_t)zt;
+        const uint64_t hi = zt & 0xFFFFFFFF00000000ull;
 #pragma unroll
-    for (int u = 0; u < kMtU; ++u) {
-        const uint64_t v = base + (uint64_t)u * T;
-        if (v < nvec) {
-            const uint64_t i = head + 4 * v;
-            acc |= (w[u].a ^ pattern_word<PAT>(i + 0, key)) | (w[u].b ^ pattern_word<PAT>(i + 1, key)) |
-                   (w[u].c ^ pattern_word<PAT>(i + 2, key)) | (w[u].d ^ pattern_word<PAT>(i + 3, key));
+        for (int u = 0; u < kMtU; ++u) {
+            const uint64_t v = base + (uint64_t)u * T;
+            if (v < nvec) {
+                const uint32_t c = 4u * u * T;
+                acc |= (w[u].a ^ splitmix64_mix(hi | (uint32_t)(lo + c + 0))) | (w[u].b ^ splitmix64_mix(hi | (uint32_t)(lo + c + 1))) |
+                       (w[u].c ^ splitmix64_mix(hi | (uint32_t)(lo + c + 2))) | (w[u].d ^ splitmix64_mix(hi | (uint32_t)(lo + c + 3)));
+            }
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < kMtU; ++u) {
+            const uint64_t v = base + (uint64_t)u * T;
+            if (v < nvec) {
+                const uint64_t i = head + 4 * v;
+                acc |= (w[u].a ^ pattern_word<PAT>(i + 0, key)) | (w[u].b ^ pattern_word<PAT>(i + 1, key)) |
+                       (w[u].c ^ pattern_word<PAT>(i + 2, key)) | (w[u].d ^ pattern_word<PAT>(i + 3, key));
+            }
         }
     }
     if (blockIdx.x == 0) {

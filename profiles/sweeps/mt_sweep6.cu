@@ -1,0 +1,98 @@
+// Sweep 6 (round 2): the random pattern with the high word of z = K + i hoisted out of the per-word work.
+// A thread's 16 words have indices within 4*(U-1)*T + 3 of each other; unless the low 32 bits of K + i wrap inside that
+// span (1 thread in ~2.8 million), the HIGH word of z is the same for all of them, and so is everything of the first
+// xorshift / multiply that depends on it alone.  Variants: A = product form (64-bit C per word), B = shared high word,
+// 64-bit C (the compiler may CSE), C = shared high word, 32-bit halves with the invariants named.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o mt_sweep6 mt_sweep6.cu && ./mt_sweep6 16
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#define CK(x) do{cudaError_t e=(x); if(e!=cudaSuccess){printf("ERR %s line %d: %s\n",#x,__LINE__,cudaGetErrorString(e)); exit(1);} }while(0)
+constexpr uint64_t kGolden = 0x9E3779B97F4A7C15ull, C1 = 0xBF58476D1CE4E5B9ull, C2 = 0x94D049BB133111EBull;
+constexpr int T = 128, U = 4;
+struct alignas(32) U64x4 { uint64_t a,b,c,d; };
+__device__ __forceinline__ void st256(void*p,const U64x4&v){asm volatile("st.global.L1::no_allocate.v4.u64 [%0], {%1,%2,%3,%4};"::"l"(p),"l"(v.a),"l"(v.b),"l"(v.c),"l"(v.d):"memory");}
+__device__ __forceinline__ U64x4 ld256(const void*p){U64x4 v;asm volatile("ld.global.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];":"=l"(v.a),"=l"(v.b),"=l"(v.c),"=l"(v.d):"l"(p));return v;}
+__device__ __forceinline__ uint64_t mix(uint64_t z){z=(z^(z>>30))*C1;z=(z^(z>>27))*C2;return z^(z>>31);}
+
+// ---- per-thread generator of the 16 expected words: word(c) = splitmix64 of index (thread's first index + c)
+struct GenPlain {  // product form: a full 64-bit add and mix per word
+  uint64_t zt; __device__ GenPlain(uint64_t zt_):zt(zt_){}
+  __device__ __forceinline__ uint64_t word(uint32_t c) const { return mix(zt + c); }
+};
+struct GenHi64 {   // shared high word, 64-bit arithmetic: the compiler is left to find the invariants
+  uint32_t lo, hi; __device__ GenHi64(uint64_t zt):lo((uint32_t)zt),hi((uint32_t)(zt>>32)){}
+  __device__ __forceinline__ uint64_t word(uint32_t c) const { return mix(((uint64_t)hi << 32) | (uint32_t)(lo + c)); }
+};
+struct GenHi32 {   // shared high word, 32-bit halves, invariants named
+  uint32_t lo, hs, h1, m1;
+  __device__ GenHi32(uint64_t zt):lo((uint32_t)zt){
+    const uint32_t hi = (uint32_t)(zt>>32);
+    h1 = hi ^ (hi >> 30);              // high word after the first xorshift
+    hs = hi << 2;                      // what the high word contributes to the low word's shift
+    m1 = h1 * (uint32_t)C1;            // its contribution to the high word of the first product
+  }
+  __device__ __forceinline__ uint64_t word(uint32_t c) const {
+    const uint32_t l0 = lo + c;
+    const uint32_t l1 = l0 ^ ((l0 >> 30) | hs);
+    const uint64_t p = (uint64_t)l1 * (uint32_t)C1;                 // mul.wide.u32
+    uint64_t z = p + ((uint64_t)(l1 * (uint32_t)(C1 >> 32) + m1) << 32);
+    z = (z ^ (z >> 27)) * C2;
+    return z ^ (z >> 31);
+  }
+};
+template<class G> __device__ __forceinline__ void fill_body(uint64_t*buf,uint64_t nvec,uint64_t base,const G g){
+  #pragma unroll
+  for(int u=0;u<U;++u){uint64_t v=base+(uint64_t)u*T; if(v<nvec){const uint32_t c=4u*u*T;U64x4 w;w.a=g.word(c);w.b=g.word(c+1);w.c=g.word(c+2);w.d=g.word(c+3);st256(buf+4*v,w);}}
+}
+template<class G> __device__ __forceinline__ uint64_t ver_body(const U64x4 (&w)[U],uint64_t nvec,uint64_t base,const G g){
+  uint64_t acc=0;
+  #pragma unroll
+  for(int u=0;u<U;++u){uint64_t v=base+(uint64_t)u*T; if(v<nvec){const uint32_t c=4u*u*T;
+    acc|=(w[u].a^g.word(c))|(w[u].b^g.word(c+1))|(w[u].c^g.word(c+2))|(w[u].d^g.word(c+3));}}
+  return acc;
+}
+__device__ __forceinline__ bool no_wrap(uint64_t zt){ return (uint32_t)zt <= 0xFFFFFFFFu - (4u*(U-1)*T+3u); }
+template<int V>
+__global__ void __launch_bounds__(T) k_fill(uint64_t* buf,uint64_t nvec,uint64_t key){
+  const uint64_t base=(uint64_t)blockIdx.x*(T*U)+threadIdx.x;
+  const uint64_t zt = key + kGolden + 4*base;
+  if (V==0 || !no_wrap(zt)) fill_body(buf,nvec,base,GenPlain(zt));     // the rare thread whose span crosses a 2^32 boundary
+  else if (V==1) fill_body(buf,nvec,base,GenHi64(zt));
+  else fill_body(buf,nvec,base,GenHi32(zt));
+}
+template<int V>
+__global__ void __launch_bounds__(T) k_verify(const uint64_t* buf,uint64_t nvec,uint64_t key,unsigned long long* res){
+  const uint64_t base=(uint64_t)blockIdx.x*(T*U)+threadIdx.x;
+  U64x4 w[U];
+  #pragma unroll
+  for(int u=0;u<U;++u){uint64_t v=base+(uint64_t)u*T; if(v<nvec) w[u]=ld256(buf+4*v);}
+  const uint64_t zt = key + kGolden + 4*base;
+  uint64_t acc;
+  if (V==0 || !no_wrap(zt)) acc=ver_body(w,nvec,base,GenPlain(zt));
+  else if (V==1) acc=ver_body(w,nvec,base,GenHi64(zt));
+  else acc=ver_body(w,nvec,base,GenHi32(zt));
+  if(acc) atomicAdd(res,1ull);
+}
+template<int V> float time_fill(uint64_t*buf,uint64_t nvec,uint64_t key){ unsigned g=(unsigned)((nvec+T*U-1)/(T*U)); cudaEvent_t a,b; CK(cudaEventCreate(&a));CK(cudaEventCreate(&b)); float best=1e30f;
+  for(int r=0;r<6;++r){CK(cudaEventRecord(a)); k_fill<V><<<g,T>>>(buf,nvec,key); CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b)); float ms; CK(cudaEventElapsedTime(&ms,a,b)); if(r&&ms<best)best=ms;} CK(cudaGetLastError()); return best;}
+template<int V> float time_ver(const uint64_t*buf,uint64_t nvec,uint64_t key,unsigned long long*res){ unsigned g=(unsigned)((nvec+T*U-1)/(T*U)); cudaEvent_t a,b; CK(cudaEventCreate(&a));CK(cudaEventCreate(&b)); float best=1e30f;
+  for(int r=0;r<6;++r){CK(cudaEventRecord(a)); k_verify<V><<<g,T>>>(buf,nvec,key,res); CK(cudaEventRecord(b)); CK(cudaEventSynchronize(b)); float ms; CK(cudaEventElapsedTime(&ms,a,b)); if(r&&ms<best)best=ms;} CK(cudaGetLastError()); return best;}
+int main(int argc,char**argv){
+  double gib= argc>1? atof(argv[1]):16.0; uint64_t bytes=(uint64_t)(gib*(1ull<<30)); uint64_t nvec=bytes/32;
+  uint64_t*buf; unsigned long long*res; CK(cudaMalloc(&buf,bytes)); CK(cudaMalloc(&res,8)); CK(cudaMemset(res,0,8));
+  // a key whose K + i wraps its low 32 bits INSIDE the buffer (at word 1000), so that the slow path is exercised and checked
+  const uint64_t key = (0x12345678ull << 32 | 0xFFFFFFFFull) - kGolden - 999;
+  auto g=[&](float ms){return bytes/(ms*1e6);};
+  for(int rep=0;rep<2;++rep){
+    float fa=time_fill<0>(buf,nvec,key), va=time_ver<0>(buf,nvec,key,res);    // buffer holds A's words
+    float vb=time_ver<1>(buf,nvec,key,res), vc=time_ver<2>(buf,nvec,key,res);  // B and C verify A's words: bit-exactness
+    float fb=time_fill<1>(buf,nvec,key); float va2=time_ver<0>(buf,nvec,key,res);
+    float fc=time_fill<2>(buf,nvec,key); float va3=time_ver<0>(buf,nvec,key,res);
+    printf("fill  GB/s: product %6.0f | shared-hi 64-bit %6.0f | shared-hi 32-bit halves %6.0f\n",g(fa),g(fb),g(fc));
+    printf("verify GB/s: product %6.0f (%6.0f %6.0f) | shared-hi 64-bit %6.0f | shared-hi 32-bit halves %6.0f\n",g(va),g(va2),g(va3),g(vb),g(vc));
+  }
+  unsigned long long bad=1; CK(cudaMemcpy(&bad,res,8,cudaMemcpyDeviceToHost)); printf("threads that saw a mismatch across all cross-checks: %llu (must be 0)\n",bad);
+  return 0;
+}

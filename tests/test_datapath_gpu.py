@@ -68,6 +68,37 @@ def test_memtest_verify_clean_and_faulty(vgpu, cuda_dev, pattern):
     assert int(res[0]) == cpu.verify(bad, pattern, 10, 77)[0]
 
 
+@pytest.mark.parametrize("wrap_at", [5, 1024, 1537, 262144 + 3])
+def test_random_verify_where_the_word_index_carries_into_the_high_half(vgpu, cuda_dev, wrap_at):
+    """The random verify kernel shares the high 32 bits of (key + golden + index) between the 16 words of a thread and
+    falls back to full 64-bit arithmetic for the rare thread whose span crosses a 2^32 boundary.  Seeds chosen so that
+    the low half wraps `wrap_at` words into the buffer — inside one thread's span, at a vector boundary, in the ragged
+    head — must still agree with the oracle bit for bit, clean and with faults planted around the wrap."""
+    dp = vgpu.datapath
+    G = 0x9E3779B97F4A7C15
+    npass = 3
+    key_low = (0x1_0000_0000 - wrap_at - (G & 0xFFFFFFFF)) & 0xFFFFFFFF          # (key + G + wrap_at) low half == 0
+    key = (0x5A5A5A5A << 32) | key_low
+    seed = key ^ G ^ npass                                                        # key = G ^ pass ^ seed
+    n = (1 << 19) + 7
+    want = cpu.fill(n, cpu.PAT_RANDOM, npass, seed).copy()
+    for off in (0, 1, 3):                                                         # aligned and ragged starts
+        backing = torch.zeros(n + 8, dtype=torch.int64, device=cuda_dev)
+        view = backing[off:off + n]
+        view.copy_(torch.from_numpy(want.view(np.int64)))
+        assert dp.memtest_verify(view, cpu.PAT_RANDOM, npass, seed).cpu().tolist() == [0, 0, 0]
+        dp.memtest_fill(view, cpu.PAT_RANDOM, npass, seed)                        # and what the fill kernel writes is the same
+        torch.cuda.synchronize()
+        assert np.array_equal(view.cpu().numpy().view(np.uint64), want)
+    bad = want.copy()
+    for idx in (wrap_at - 1, wrap_at, wrap_at + 1, n - 1):
+        bad[idx] ^= np.uint64(1 << (idx % 64))
+    buf = torch.from_numpy(bad.view(np.int64)).to(cuda_dev)
+    res = dp.memtest_verify(buf, cpu.PAT_RANDOM, npass, seed).cpu().numpy().view(np.uint64)
+    o_n, o_first, o_bits = cpu.verify(bad, cpu.PAT_RANDOM, npass, seed)
+    assert (int(res[0]), int(~res[1] & np.uint64(cpu.U64_MAX)), int(res[2])) == (o_n, o_first, o_bits) and o_n == 4
+
+
 def test_memtest_run_reports_rates_and_faults(vgpu, cuda_dev):
     dp, capi = vgpu.datapath, vgpu.capi
     buf = torch.empty(256 << 20, dtype=torch.uint8, device=cuda_dev)
