@@ -626,6 +626,8 @@ static size_t g_nalloc;
 static pthread_mutex_t g_alloc_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_mutex_t g_res_mu = PTHREAD_MUTEX_INITIALIZER;  /* residency of VMM-backed allocations (taken before g_alloc_mu) */
 static uint64_t g_peer_left = ~0ull;  /* VGPU_OVERSUB_PEER_MB: what this process may still put on the peer (under g_res_mu) */
+static alloc_node_t *g_find_hit[8];   /* last managed ranges looked up by address (vmm_find), under g_alloc_mu */
+static unsigned g_find_next;
 static void vmm_quiesce(void);
 
 static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
@@ -808,6 +810,7 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
     if (a->prev) a->prev->next = a->next; else g_head = a->next;
     if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
     --g_nalloc;
+    memset(g_find_hit, 0, sizeof(g_find_hit));
     int dev = a->dev;
     size_t len = a->len;
     free(a);
@@ -1480,11 +1483,19 @@ static uint64_t node_resident(alloc_node_t *a) {  /* chunks backed by HBM right 
     g_dp.missing(a->vmem, 0, node_chunks(a), &miss);
     return node_chunks(a) > miss ? node_chunks(a) - miss : 0;
 }
-/* the managed range that contains p (g_alloc_mu held) */
+/* the managed range that contains p (g_alloc_mu held).  A launch names the same few ranges again and again: the last
+ * hits are tried before the list is walked (a framework's allocator holds hundreds of ranges); emptied at every free. */
 static alloc_node_t *vmm_find(CUdeviceptr p) {
     if (p < g_vmm_lo || p >= g_vmm_hi) return NULL;
+    for (int i = 0; i < 8; ++i) {
+        alloc_node_t *a = g_find_hit[i];
+        if (a && p >= a->addr && p < a->addr + node_chunks(a) * IPCSIZE) return a;
+    }
     for (alloc_node_t *a = g_head; a; a = a->next)
-        if (a->vmem && p >= a->addr && p < a->addr + node_chunks(a) * IPCSIZE) return a;
+        if (a->vmem && p >= a->addr && p < a->addr + node_chunks(a) * IPCSIZE) {
+            g_find_hit[g_find_next++ & 7] = a;
+            return a;
+        }
     return NULL;
 }
 /* least recently used range with something resident that the call at hand (epoch) does not need */
@@ -3055,6 +3066,7 @@ EXPORT CUresult cuMemoryFree(CUdeviceptr dptr) {
             if (a->prev) a->prev->next = a->next; else g_head = a->next;
             if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
             --g_nalloc;
+            memset(g_find_hit, 0, sizeof(g_find_hit));
             free(a);
             pthread_mutex_unlock(&g_alloc_mu);
             pthread_mutex_unlock(&g_res_mu);
