@@ -626,8 +626,9 @@ static size_t g_nalloc;
 static pthread_mutex_t g_alloc_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_mutex_t g_res_mu = PTHREAD_MUTEX_INITIALIZER;  /* residency of VMM-backed allocations (taken before g_alloc_mu) */
 static uint64_t g_peer_left = ~0ull;  /* VGPU_OVERSUB_PEER_MB: what this process may still put on the peer (under g_res_mu) */
-static alloc_node_t *g_find_hit[8];   /* last managed ranges looked up by address (vmm_find), under g_alloc_mu */
-static unsigned g_find_next;
+static alloc_node_t **g_idx;           /* the managed ranges sorted by address (vmm_find's binary search), under g_alloc_mu */
+static size_t g_idx_n, g_idx_cap;
+static void idx_del(alloc_node_t *a);
 static void vmm_quiesce(void);
 
 static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
@@ -810,7 +811,7 @@ EXPORT CUresult cuMemFree_v2(CUdeviceptr dptr) {
     if (a->prev) a->prev->next = a->next; else g_head = a->next;
     if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
     --g_nalloc;
-    memset(g_find_hit, 0, sizeof(g_find_hit));
+    idx_del(a);
     int dev = a->dev;
     size_t len = a->len;
     free(a);
@@ -1483,20 +1484,42 @@ static uint64_t node_resident(alloc_node_t *a) {  /* chunks backed by HBM right 
     g_dp.missing(a->vmem, 0, node_chunks(a), &miss);
     return node_chunks(a) > miss ? node_chunks(a) - miss : 0;
 }
-/* the managed range that contains p (g_alloc_mu held).  A launch names the same few ranges again and again: the last
- * hits are tried before the list is walked (a framework's allocator holds hundreds of ranges); emptied at every free. */
+/* the managed range that contains p (g_alloc_mu held): binary search in the address-sorted index, since a launch looks
+ * up every 8-byte word of its arguments and a framework's allocator holds hundreds of ranges */
+static size_t idx_upper(CUdeviceptr p) {  /* number of ranges whose base is <= p */
+    size_t lo = 0, hi = g_idx_n;
+    while (lo < hi) {
+        const size_t mid = (lo + hi) / 2;
+        if (g_idx[mid]->addr <= p) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+static void idx_add(alloc_node_t *a) {
+    if (g_idx_n == g_idx_cap) {
+        const size_t cap = g_idx_cap ? g_idx_cap * 2 : 256;
+        alloc_node_t **n = (alloc_node_t **)realloc(g_idx, cap * sizeof(*n));
+        if (!n) abort();
+        g_idx = n;
+        g_idx_cap = cap;
+    }
+    const size_t at = idx_upper(a->addr);
+    memmove(g_idx + at + 1, g_idx + at, (g_idx_n - at) * sizeof(*g_idx));
+    g_idx[at] = a;
+    ++g_idx_n;
+}
+static void idx_del(alloc_node_t *a) {
+    if (!a->vmem) return;
+    const size_t at = idx_upper(a->addr);
+    if (at == 0 || g_idx[at - 1] != a) return;
+    memmove(g_idx + at - 1, g_idx + at, (g_idx_n - at) * sizeof(*g_idx));
+    --g_idx_n;
+}
 static alloc_node_t *vmm_find(CUdeviceptr p) {
     if (p < g_vmm_lo || p >= g_vmm_hi) return NULL;
-    for (int i = 0; i < 8; ++i) {
-        alloc_node_t *a = g_find_hit[i];
-        if (a && p >= a->addr && p < a->addr + node_chunks(a) * IPCSIZE) return a;
-    }
-    for (alloc_node_t *a = g_head; a; a = a->next)
-        if (a->vmem && p >= a->addr && p < a->addr + node_chunks(a) * IPCSIZE) {
-            g_find_hit[g_find_next++ & 7] = a;
-            return a;
-        }
-    return NULL;
+    const size_t at = idx_upper(p);
+    if (at == 0) return NULL;
+    alloc_node_t *a = g_idx[at - 1];
+    return p < a->addr + node_chunks(a) * IPCSIZE ? a : NULL;
 }
 /* least recently used range with something resident that the call at hand (epoch) does not need */
 static alloc_node_t *vmm_victim(uint64_t epoch) {
@@ -1632,6 +1655,7 @@ static int vmm_alloc(int dev, size_t n, CUdeviceptr *p) {
     g_tail->windowed = windowed;
     g_tail->peer_bytes = peer_bytes;
     g_tail->last_use = ++g_res_clock;
+    idx_add(g_tail);
     if (*p < g_vmm_lo) g_vmm_lo = *p;
     if (*p + bytes > g_vmm_hi) g_vmm_hi = *p + bytes;
     uint64_t miss = 0;
@@ -2539,6 +2563,14 @@ static CUresult free_async(CUdeviceptr dptr, void *stream, int ptsz) {
     static fn_t fn[2];
     if (!fn[ptsz]) fn[ptsz] = (fn_t)cuda_sym(ptsz ? "cuMemFreeAsync_ptsz" : "cuMemFreeAsync");
     if (!fn[ptsz]) return 3;
+    if (!tl_bypass && g_backend_vmm && dptr) {  /* a managed range (made by cuMemAlloc) freed stream-ordered: the plain free */
+        pthread_mutex_lock(&g_alloc_mu);
+        alloc_node_t *a = g_head;
+        while (a && a->addr != dptr) a = a->next;
+        const int managed = a && a->vmem;
+        pthread_mutex_unlock(&g_alloc_mu);
+        if (managed) return cuMemFree_v2(dptr);
+    }
     if (!tl_bypass && g_strict && dptr) {
         pthread_mutex_lock(&g_alloc_mu);
         alloc_node_t *a = g_head;
@@ -3066,7 +3098,7 @@ EXPORT CUresult cuMemoryFree(CUdeviceptr dptr) {
             if (a->prev) a->prev->next = a->next; else g_head = a->next;
             if (a->next) a->next->prev = a->prev; else g_tail = a->prev;
             --g_nalloc;
-            memset(g_find_hit, 0, sizeof(g_find_hit));
+            idx_del(a);
             free(a);
             pthread_mutex_unlock(&g_alloc_mu);
             pthread_mutex_unlock(&g_res_mu);

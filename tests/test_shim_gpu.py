@@ -815,6 +815,46 @@ def test_preferred_location_advice_decides_who_keeps_the_hbm(cuda_dev):
     assert o["after_touch"] == [1024, 1024, 0, 0]
 
 
+
+@pytest.mark.gpu
+def test_range_lookup_with_hundreds_of_ranges_and_a_stream_ordered_free(cuda_dev):
+    """The argument scan finds a range by binary search in an address-sorted index: with 300 ranges alive, some freed
+    in between and new ones made (index insert / delete), a paged process still reads back what it wrote to every
+    range; and cuMemFreeAsync on a managed range (legal for memory from cuMemAlloc) frees it like cuMemFree."""
+    code = """
+        import ctypes as C, json, torch
+        cu, shim = C.CDLL("libcuda.so.1"), C.CDLL(None)
+        torch.cuda.init()
+        M = 1 << 20
+        ts = [torch.full((12 * M // 8,), i, dtype=torch.int64, device="cuda") for i in range(300)]   # 3.5 GiB, 1.5 GiB may be resident
+        for i in range(0, 300, 3):
+            ts[i] = None
+        torch.cuda.empty_cache()                                   # 100 ranges freed: holes in the index
+        for i in range(0, 300, 3):
+            ts[i] = torch.full((14 * M // 8,), 1000 + i, dtype=torch.int64, device="cuda")
+        bad = 0
+        for rnd in range(2):
+            for i, t in enumerate(ts):
+                want = 1000 + i if i % 3 == 0 else i
+                bad += int(t[0].item()) != want or int(t[-1].item()) != want
+        st = (C.c_uint64 * 8)()
+        shim.cuVGPUOversubStats(st)
+        p = C.c_ulonglong(0)
+        rc_alloc = cu.cuMemAlloc_v2(C.byref(p), C.c_size_t(64 * M))
+        free0, tot = C.c_size_t(0), C.c_size_t(0)
+        cu.cuMemGetInfo_v2(C.byref(free0), C.byref(tot))
+        rc_free = cu.cuMemFreeAsync(p, None)
+        free1 = C.c_size_t(0)
+        cu.cuMemGetInfo_v2(C.byref(free1), C.byref(tot))
+        rc_again = cu.cuMemFree_v2(p)                              # already gone
+        print(json.dumps({"bad": bad, "paged": int(st[6]), "rc": [rc_alloc, rc_free], "again": rc_again, "freed_mib": (free1.value - free0.value) // M}))
+    """
+    o = last_json(run_under_shim(code, {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "8g", "VGPU_OVERSUB_RESIDENT_MB": "1536"}, timeout=600))
+    print("many ranges:", o)
+    assert o["bad"] == 0 and o["paged"] == 1
+    assert o["rc"] == [0, 0] and o["again"] != 0 and o["freed_mib"] == 64
+
+
 TRAIN = """
     import json, torch
     torch.manual_seed(0)
