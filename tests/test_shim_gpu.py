@@ -855,6 +855,118 @@ def test_range_lookup_with_hundreds_of_ranges_and_a_stream_ordered_free(cuda_dev
     assert o["rc"] == [0, 0] and o["again"] != 0 and o["freed_mib"] == 64
 
 
+
+RANDOM_PROGRAM = """
+    import ctypes, hashlib, json, random, sys, torch
+    seed = int(sys.argv[1])
+    rng = random.Random(seed)
+    torch.manual_seed(seed)
+    torch.cuda.init()
+    M = 1 << 20
+    def make(i):
+        n = rng.randrange(8, 97) * M // 8
+        return (torch.arange(n, dtype=torch.int64, device="cuda") * (0x9E3779B1 + 2 * i)) ^ (seed << 20)
+    pool = [make(i) for i in range(24)]                    # ~1.2 GiB of int64 tensors, 8..96 MiB each
+    side = torch.cuda.Stream()
+    trace = hashlib.sha256()
+    def pick(k):
+        return rng.sample(range(len(pool)), k)
+    for step in range(220):
+        op = rng.randrange(12)
+        if op == 0:                                        # device-to-device copy of a slice (cudaMemcpyAsync)
+            i, j = pick(2)
+            n = min(pool[i].numel(), pool[j].numel(), rng.randrange(1, 8 * M))
+            o = rng.randrange(0, pool[i].numel() - n + 1)
+            pool[i][o:o + n].copy_(pool[j][:n])
+        elif op == 1:                                      # elementwise kernel over two ranges, in place
+            i, j = pick(2)
+            n = min(pool[i].numel(), pool[j].numel())
+            pool[i][:n].add_(pool[j][:n]).bitwise_xor_(pool[j][:n] >> 3)
+        elif op == 2:                                      # memset
+            i, = pick(1)
+            o = rng.randrange(0, pool[i].numel() // 2)
+            pool[i][o:o + rng.randrange(1, pool[i].numel() // 2)].zero_()
+        elif op == 3:                                      # new tensor from three others: allocation, free of the old one
+            i, j, k = pick(3)
+            n = min(pool[i].numel(), pool[j].numel(), pool[k].numel())
+            pool[i] = torch.cat([pool[j][: n // 3], pool[k][: n // 3], pool[i][: n // 3]])
+        elif op == 4:                                      # strided views: the copy kernel with strides in its argument struct
+            i, j = pick(2)
+            r = min(pool[i].numel(), pool[j].numel()) // 4096
+            pool[i][: r * 4096].view(r, 4096)[:, 7:1000:3].copy_(pool[j][: r * 4096].view(r, 4096)[:, 11:1004:3])
+        elif op == 5:                                      # gather through an index tensor that itself lives in a managed range
+            i, j = pick(2)
+            n = min(pool[i].numel(), pool[j].numel(), 4 * M)
+            idx = (pool[j][:n].abs() % pool[i].numel())
+            pool[i][:n] = pool[i][idx]
+        elif op == 6:                                      # device -> host of a window, hashed
+            i, = pick(1)
+            o = rng.randrange(0, pool[i].numel() - 1024)
+            trace.update(pool[i][o:o + rng.randrange(1, 1 << 18)].cpu().numpy().tobytes())
+        elif op == 7:                                      # host -> device into the middle of a range
+            i, = pick(1)
+            n = rng.randrange(1, 1 << 18)
+            h = torch.randint(-(1 << 40), 1 << 40, (n,), dtype=torch.int64)
+            pool[i][pool[i].numel() - n:].copy_(h)
+        elif op == 8:                                      # work on a second stream, ordered by events
+            i, j = pick(2)
+            n = min(pool[i].numel(), pool[j].numel())
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                pool[i][:n].mul_(3).sub_(pool[j][:n])
+            torch.cuda.current_stream().wait_stream(side)
+        elif op == 9:                                      # reduction with library temporaries (cub) + scalar read-back
+            i, = pick(1)
+            trace.update(str(int(pool[i].sum().item())).encode())
+            trace.update(str(int(pool[i][: 2 * M].max().item())).encode())
+        elif op == 10:                                     # sort of a window (multi-pass radix sort, scratch allocations)
+            i, = pick(1)
+            n = min(pool[i].numel(), 2 * M)
+            pool[i][:n] = torch.sort(pool[i][:n]).values
+        else:                                              # float GEMM over reinterpreted ranges (library kernel, pointers in a struct; values small enough to be exact)
+            i, j = pick(2)
+            a = (pool[i][: 1 << 19] & 0x3F).to(torch.float32).view(512, 1024)
+            b = (pool[j][: 1 << 19] & 0x3F).to(torch.float32).view(1024, 512)
+            c = (a @ b).to(torch.int64)
+            pool[i][: c.numel()].bitwise_xor_(c.view(-1))
+    torch.cuda.synchronize()
+    for t in pool:
+        trace.update(str(int(t.sum().item())).encode())
+        trace.update(t[:: max(1, t.numel() // 4096)].cpu().numpy().tobytes())
+    out = {"digest": trace.hexdigest()}
+    try:
+        st = (ctypes.c_uint64 * 8)()
+        ctypes.CDLL(None).cuVGPUOversubStats(st)
+        out.update({"to_host": int(st[1]), "restored": int(st[2]), "bad": int(st[3]), "paged": int(st[6])})
+    except AttributeError:
+        pass
+    print(json.dumps(out))
+"""
+
+
+@pytest.mark.parametrize("seed", [11, 12])
+def test_a_random_program_gives_the_same_bytes_paged_as_without_the_shim(cuda_dev, seed):
+    """Differential check of the residency engine: 220 random operations over 24 tensors (copies of slices, in-place
+    kernels over two ranges, memsets, cat = allocate + free, strided copies, gathers through an index held in a managed
+    range, H2D / D2H windows, a second stream, cub reductions, radix sort, a float GEMM) run (a) with no shim at all and
+    (b) under the shim with a third of the bytes allowed to be resident.  Every value read back on the way and a sample
+    of every tensor at the end go into one SHA-256: the digests must be equal."""
+    code = textwrap.dedent(RANDOM_PROGRAM)
+    plain = subprocess.run([sys.executable, "-c", code, str(seed)], capture_output=True, text=True, timeout=600)
+    assert plain.returncode == 0, plain.stderr[-3000:]
+    want = json.loads(plain.stdout.strip().splitlines()[-1])
+    td = tempfile.mkdtemp(prefix="vgpushim")
+    env = dict(os.environ)
+    env.update({"LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": os.path.join(td, "shr.cache"), "LIBCUDA_LOG_LEVEL": "0",
+                **OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "8g", "VGPU_OVERSUB_RESIDENT_MB": "640"})
+    paged = subprocess.run([sys.executable, "-c", code, str(seed)], env=env, capture_output=True, text=True, timeout=900)
+    assert paged.returncode == 0, paged.stderr[-3000:]
+    got = json.loads(paged.stdout.strip().splitlines()[-1])
+    print("random program, seed", seed, ":", got)
+    assert got["paged"] == 1 and got["restored"] > 200 and got["bad"] == 0       # it really was paged (chunks of 2 MiB)
+    assert got["digest"] == want["digest"]
+
+
 TRAIN = """
     import json, torch
     torch.manual_seed(0)
