@@ -1704,32 +1704,38 @@ static const pscan_t *kernel_params(void *fn) {
     return e;
 }
 
-typedef struct { alloc_node_t *a[64]; int n; } need_t;
+/* the ranges one call names.  4096 entries hold every word of the largest argument buffer CUDA allows (32 764 B): a
+ * multi-tensor kernel passes a hundred pointers and more in one struct.  One call at a time fills it (g_res_mu). */
+#define NEED_MAX 4096
+typedef struct { alloc_node_t **a; int n; } need_t;
+static alloc_node_t *g_need[NEED_MAX];
 static void need_word(need_t *nd, uint64_t w, uint64_t epoch) {
     alloc_node_t *a = vmm_find((CUdeviceptr)w);
     if (!a || a->epoch == epoch) return;
     a->epoch = epoch;  /* from here on not a victim of this call */
-    if (nd->n < 64) nd->a[nd->n++] = a;
+    if (nd->n < NEED_MAX) nd->a[nd->n++] = a;
+}
+static int need_one(alloc_node_t *a, uint64_t epoch) {
+    if (!a->windowed) return vmm_make_resident(a, 0, node_chunks(a), epoch);
+    a->last_use = ++g_res_clock;
+    return 0;
 }
 static int need_commit(need_t *nd, uint64_t epoch) {
     int rc = 0;
-    for (int i = 0; i < nd->n && rc == 0; ++i)
-        if (!nd->a[i]->windowed) rc = vmm_make_resident(nd->a[i], 0, node_chunks(nd->a[i]), epoch);
-        else nd->a[i]->last_use = ++g_res_clock;
+    for (int i = 0; i < nd->n && rc == 0; ++i) rc = need_one(nd->a[i], epoch);
     return rc;
 }
 static int vmm_need_all(uint64_t epoch) {  /* a graph launch: its kernels' arguments are not ours to see */
-    need_t nd = {.n = 0};
+    int rc = 0;
     for (alloc_node_t *a = g_head; a; a = a->next)
-        if (a->vmem && nd.n < 64) {
-            a->epoch = epoch;
-            nd.a[nd.n++] = a;
-        }
-    return need_commit(&nd, epoch);
+        if (a->vmem) a->epoch = epoch;  /* none of them is a victim of this call */
+    for (alloc_node_t *a = g_head; a && rc == 0; a = a->next)
+        if (a->vmem) rc = need_one(a, epoch);
+    return rc;
 }
 /* g_res_mu held; takes g_alloc_mu.  -> 0, or nonzero when the ranges the launch names cannot all be resident */
 static int vmm_scan_launch(void *fn, void **params, void **extra) {
-    need_t nd = {.n = 0};
+    need_t nd = {.a = g_need, .n = 0};
     pthread_mutex_lock(&g_alloc_mu);
     const uint64_t epoch = ++g_res_epoch;
     int rc = 0;

@@ -856,6 +856,97 @@ def test_range_lookup_with_hundreds_of_ranges_and_a_stream_ordered_free(cuda_dev
 
 
 
+
+def test_a_launch_or_graph_that_names_more_than_64_ranges_gets_all_of_them(cuda_dev):
+    """A multi-tensor kernel passes a hundred pointers in one argument struct, and a graph replay needs every range of
+    the process: 100 ranges of 12 MiB are spilled by touching 1.2 GiB of other tensors (1.6 GiB may be resident), then
+    (a) one torch._foreach_add_ over all 100 and (b) a replay of a graph captured over them must find every one back."""
+    code = """
+        import ctypes as C, json, torch
+        torch.cuda.init()
+        M = 1 << 20
+        shim = C.CDLL(None)
+        shim.cuVGPUResidentBytes.restype = C.c_longlong
+        ts = [torch.zeros(12 * M // 8, dtype=torch.int64, device="cuda") for _ in range(100)]
+        def resident():
+            return sum(shim.cuVGPUResidentBytes(C.c_ulonglong(t.data_ptr())) > 0 for t in ts)
+        def push_out():
+            big = [torch.ones(600 * M // 8, dtype=torch.int64, device="cuda") for _ in range(2)]
+            s = sum(int(b[:1024].sum().item()) for b in big)
+            del big
+            torch.cuda.empty_cache()
+            return s
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):                       # warm-up on the capture stream, everything resident
+            for t in ts:
+                t.add_(1)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            for t in ts:
+                t.add_(1)                                # capture only records: values stay 1
+        push_out()
+        left_a = resident()
+        torch._foreach_add_(ts, 10)                      # multi-tensor apply: pointer lists inside one struct
+        torch.cuda.synchronize()
+        after_a = resident()
+        push_out()
+        left_b = resident()
+        g.replay()
+        torch.cuda.synchronize()
+        after_b = resident()
+        vals = sorted({int(t[0].item()) for t in ts} | {int(t[-1].item()) for t in ts})
+        st = (C.c_uint64 * 8)()
+        shim.cuVGPUOversubStats(st)
+        print(json.dumps({"left": [left_a, left_b], "after": [after_a, after_b], "vals": vals, "bad": int(st[3]), "paged": int(st[6])}))
+    """
+    o = last_json(run_under_shim(code, {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "8g", "VGPU_OVERSUB_RESIDENT_MB": "1600"}, timeout=600))
+    print("more than 64 ranges:", o)
+    assert o["paged"] == 1 and o["bad"] == 0
+    assert max(o["left"]) <= 40                 # most of the 100 really were spilled before each of the two launches
+    assert o["after"] == [100, 100]             # ... and every one was back for it
+    assert o["vals"] == [12]                    # 1 (warm-up) + 10 (foreach) + 1 (replay), first and last word of each
+
+
+
+def test_two_host_threads_whose_working_sets_do_not_fit_together(cuda_dev):
+    """Two threads of one paged process, each adding to its own 1 GiB tensor, 1.5 GiB may be resident: every launch of
+    one thread has to push the other thread's tensor out — after draining that thread's queued kernels.  Both tensors end
+    with exactly the number of additions made, on their first and last words and in total."""
+    code = """
+        import ctypes as C, json, threading, torch
+        torch.cuda.init()
+        G = 1 << 30
+        ts = [torch.zeros(G // 8, dtype=torch.int64, device="cuda") for _ in range(2)]
+        N = 25
+        errs = []
+        def work(k):
+            try:
+                st = torch.cuda.Stream()
+                with torch.cuda.stream(st):
+                    for i in range(N):
+                        ts[k].add_(k + 1)
+                    st.synchronize()
+            except Exception as e:
+                errs.append(repr(e))
+        th = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+        torch.cuda.synchronize()
+        out = [[int(t[0].item()), int(t[-1].item()), int(t.sum().item()) // (G // 8)] for t in ts]
+        st = (C.c_uint64 * 8)()
+        C.CDLL(None).cuVGPUOversubStats(st)
+        print(json.dumps({"out": out, "errs": errs, "to_host": int(st[1]), "bad": int(st[3]), "paged": int(st[6])}))
+    """
+    o = last_json(run_under_shim(code, {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "8g", "VGPU_OVERSUB_RESIDENT_MB": "1536"}, timeout=600))
+    print("two threads:", o)
+    assert not o["errs"] and o["paged"] == 1 and o["bad"] == 0
+    assert o["out"] == [[25, 25, 25], [50, 50, 50]]
+    assert o["to_host"] >= 2 * 512               # the tensors did trade places (chunks of 2 MiB)
+
+
 RANDOM_PROGRAM = """
     import ctypes, hashlib, json, random, sys, torch
     seed = int(sys.argv[1])
