@@ -876,21 +876,34 @@ static int vdev_of_pointer(CUdeviceptr ptr, int phys) {
 }
 
 /* cuPointerGetAttributes@0x33cf3 (a24): after the real call, IS_MANAGED (8) is forced to 0 so
- * that frameworks do not notice the managed memory behind oversubscribed allocations. */
+ * that frameworks do not notice the managed memory behind oversubscribed allocations.
+ * VMM backend: a query about a managed range (cudaPointerGetAttributes of DLPack / array-interface imports, NCCL's
+ * buffer checks) must see device memory whether the range is in HBM or spilled, and one allocation where the driver has
+ * one mapping per block: the chunk asked about is made resident first, RANGE_START_ADDR (11) / RANGE_SIZE (12) are the
+ * allocation's.  vmm_query_begin / _end live with the residency engine. */
+static int vmm_query_begin(CUdeviceptr ptr, CUdeviceptr *base, size_t *len);
+static void vmm_query_end(int mode);
+static void pointer_attr_fix(int attr, void *data, CUresult rc, CUdeviceptr ptr, CUdeviceptr base, size_t len) {
+    if (!data) return;
+    if (attr == 8) *(unsigned *)data = 0;
+    if (rc != 0) return;
+    if (attr == 9) *(int *)data = vdev_of_pointer(ptr, *(int *)data);
+    if (len && attr == 11) *(CUdeviceptr *)data = base;
+    if (len && attr == 12) *(size_t *)data = len;
+}
 EXPORT CUresult cuPointerGetAttributes(unsigned n, int *attrs, void **data, CUdeviceptr ptr) {
     typedef CUresult (*fn_t)(unsigned, int *, void **, CUdeviceptr);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuPointerGetAttributes");
-    if (!tl_bypass) {
-        ensure_initialized();
-        wait_running();
-    }
+    if (tl_bypass) return f ? f(n, attrs, data, ptr) : 3;
+    ensure_initialized();
+    wait_running();
+    CUdeviceptr base = 0;
+    size_t len = 0;
+    const int m = vmm_query_begin(ptr, &base, &len);
     CUresult rc = f ? f(n, attrs, data, ptr) : 3;
-    if (!tl_bypass)
-        for (unsigned i = 0; i < n; ++i) {
-            if (attrs[i] == 8 && data[i]) *(unsigned *)data[i] = 0;
-            if (attrs[i] == 9 && data[i] && rc == 0) *(int *)data[i] = vdev_of_pointer(ptr, *(int *)data[i]);
-        }
+    vmm_query_end(m);
+    for (unsigned i = 0; i < n; ++i) pointer_attr_fix(attrs[i], data[i], rc, ptr, base, len);
     return rc;
 }
 
@@ -899,10 +912,33 @@ EXPORT CUresult cuPointerGetAttribute(void *data, int attr, CUdeviceptr ptr) {
     typedef CUresult (*fn_t)(void *, int, CUdeviceptr);
     static fn_t f;
     if (!f) f = (fn_t)cuda_sym("cuPointerGetAttribute");
+    if (tl_bypass) return f ? f(data, attr, ptr) : 3;
+    CUdeviceptr base = 0;
+    size_t len = 0;
+    const int m = vmm_query_begin(ptr, &base, &len);
     CUresult rc = f ? f(data, attr, ptr) : 3;
-    if (rc == 0 && !tl_bypass && attr == 9 && data) *(int *)data = vdev_of_pointer(ptr, *(int *)data);
+    vmm_query_end(m);
+    if (attr != 8) pointer_attr_fix(attr, data, rc, ptr, base, len);  /* the reference masks IS_MANAGED in the plural form only */
     return rc;
 }
+/* cuMemGetAddressRange of a pointer into a managed range: the allocation, not the block the driver mapped there */
+EXPORT CUresult cuMemGetAddressRange_v2(CUdeviceptr *pbase, size_t *psize, CUdeviceptr ptr) {
+    typedef CUresult (*fn_t)(CUdeviceptr *, size_t *, CUdeviceptr);
+    static fn_t f;
+    if (!f) f = (fn_t)cuda_sym("cuMemGetAddressRange_v2");
+    if (!tl_bypass) {
+        CUdeviceptr base = 0;
+        size_t len = 0;
+        vmm_query_end(vmm_query_begin(ptr, &base, &len));
+        if (len) {
+            if (pbase) *pbase = base;
+            if (psize) *psize = len;
+            return 0;
+        }
+    }
+    return f ? f(pbase, psize, ptr) : 3;
+}
+EXPORT CUresult cuMemGetAddressRange(CUdeviceptr *pbase, size_t *psize, CUdeviceptr ptr) { return cuMemGetAddressRange_v2(pbase, psize, ptr); }
 
 /* host-memory hooks (a20): allocate first, then check_oom@0x311bd == oom_check(cur, 0) */
 EXPORT CUresult cuMemAllocHost_v2(void **pp, size_t n) {
@@ -1668,7 +1704,7 @@ static int vmm_alloc(int dev, size_t n, CUdeviceptr *p) {
 
 /* ---- what a call needs: launches (argument scan), copies (exact bytes), graphs (everything) */
 typedef CUresult (*paraminfo_t)(void *, size_t, size_t *, size_t *);
-#define PSCAN_MAX 48
+#define PSCAN_MAX 96
 typedef struct { void *fn; int n; unsigned short size[PSCAN_MAX]; } pscan_t;
 static pscan_t g_pscan[1024];  /* by kernel handle, under g_res_mu */
 static const pscan_t *kernel_params(void *fn) {
@@ -1694,7 +1730,7 @@ static const pscan_t *kernel_params(void *fn) {
         CUresult r;
         while (n < PSCAN_MAX && (r = q(fn, (size_t)n, &off, &size)) == 0) e->size[n++] = (unsigned short)(size > 32764 ? 32764 : size);  /* CUDA 12.1+: up to 32 764 B of arguments */
         if (n > 0) {
-            e->n = n;
+            if (n < PSCAN_MAX || q(fn, (size_t)n, &off, &size) != 0) e->n = n;  /* more parameters than the table holds: "every range" */
             break;
         }
         no_params |= r == 1;  /* CUDA_ERROR_INVALID_VALUE at index 0: a kernel that takes nothing */
@@ -1768,6 +1804,24 @@ static int vmm_scan_launch(void *fn, void **params, void **extra) {
     pthread_mutex_unlock(&g_alloc_mu);
     return rc;
 }
+/* a pointer query (attributes, address range): the allocation that contains ptr (*len = 0: none), its chunk made
+ * resident when the process is paged so that the driver describes mapped device memory.  -> the mode for vmm_query_end */
+static int vmm_query_begin(CUdeviceptr ptr, CUdeviceptr *base, size_t *len) {
+    *len = 0;
+    if (!g_backend_vmm) return 0;
+    ensure_initialized();
+    const int m = res_begin();
+    pthread_mutex_lock(&g_alloc_mu);
+    alloc_node_t *a = vmm_find(ptr);
+    if (a) {
+        *base = a->addr;
+        *len = a->len;
+        if (m == 2) (void)vmm_make_resident(a, (ptr - a->addr) / IPCSIZE, 1, ++g_res_epoch);
+    }
+    pthread_mutex_unlock(&g_alloc_mu);
+    return m;
+}
+static void vmm_query_end(int mode) { res_end(mode); }
 /* the bytes [p, p+n) if they lie in a managed range (g_res_mu and g_alloc_mu held) */
 static int vmm_touch(CUdeviceptr p, size_t n, uint64_t epoch) {
     alloc_node_t *a = vmm_find(p);
@@ -2770,6 +2824,7 @@ static const hook_t g_hooks[] = {
     {"cuCtxPopCurrent", (void *)cuCtxPopCurrent_v2}, {"cuCtxPopCurrent_v2", (void *)cuCtxPopCurrent_v2},
     {"cuCtxPushCurrent", (void *)cuCtxPushCurrent_v2}, {"cuCtxPushCurrent_v2", (void *)cuCtxPushCurrent_v2},
     {"cuPointerGetAttributes", (void *)cuPointerGetAttributes}, {"cuPointerGetAttribute", (void *)cuPointerGetAttribute},
+    {"cuMemGetAddressRange", (void *)cuMemGetAddressRange_v2}, {"cuMemGetAddressRange_v2", (void *)cuMemGetAddressRange_v2},
     {"cuMipmappedArrayCreate", (void *)cuMipmappedArrayCreate},
     {"cuMemcpy", (void *)cuMemcpy}, {"cuMemcpyAsync", (void *)cuMemcpyAsync},
     {"cuMemcpyDtoH", (void *)cuMemcpyDtoH_v2}, {"cuMemcpyDtoH_v2", (void *)cuMemcpyDtoH_v2},

@@ -947,6 +947,59 @@ def test_two_host_threads_whose_working_sets_do_not_fit_together(cuda_dev):
     assert o["to_host"] >= 2 * 512               # the tensors did trade places (chunks of 2 MiB)
 
 
+
+def test_pointer_queries_on_a_spilled_range_still_describe_device_memory(cuda_dev):
+    """cudaPointerGetAttributes / cuPointerGetAttribute(s) / cuMemGetAddressRange on a managed range that is spilled at
+    that moment: device memory of this device, one allocation from its base over its whole size (the driver itself
+    holds one mapping per 1 GiB block, and none for a spilled block) — what an array-interface import relies on."""
+    code = """
+        import ctypes as C, json, torch
+        torch.cuda.init()
+        cu, shim = C.CDLL("libcuda.so.1"), C.CDLL(None)
+        shim.cuVGPUResidentBytes.restype = C.c_longlong
+        G = 1 << 30
+        t = torch.arange(3 * G // 16, dtype=torch.int64, device="cuda")           # 1.5 GiB: two blocks of the manager
+        others = [torch.ones(G // 8, dtype=torch.int64, device="cuda") for _ in range(2)]
+        s = sum(int(o.sum().item()) for o in others)                              # 2 GiB may be resident: t goes out
+        gone = shim.cuVGPUResidentBytes(C.c_ulonglong(t.data_ptr()))
+        inside = t.data_ptr() + G + 4096                                          # a pointer into the second block
+        mt = C.c_uint(0)
+        rc1 = cu.cuPointerGetAttribute(C.byref(mt), 2, C.c_ulonglong(inside))     # MEMORY_TYPE
+        base, size = C.c_ulonglong(0), C.c_size_t(0)
+        rc2 = cu.cuMemGetAddressRange_v2(C.byref(base), C.byref(size), C.c_ulonglong(inside))
+        vals = (C.c_ulonglong * 4)()
+        attrs = (C.c_int * 4)(11, 12, 9, 8)                                       # RANGE_START_ADDR, RANGE_SIZE, DEVICE_ORDINAL, IS_MANAGED
+        ptrs = (C.c_void_p * 4)(*[C.addressof(vals) + 8 * i for i in range(4)])
+        others = None
+        torch.cuda.empty_cache()
+        for o in [torch.ones(G // 8, dtype=torch.int64, device="cuda") for _ in range(2)]:
+            s += int(o.sum().item())                                              # and out again
+        gone2 = shim.cuVGPUResidentBytes(C.c_ulonglong(t.data_ptr()))
+        rc3 = cu.cuPointerGetAttributes(4, attrs, ptrs, C.c_ulonglong(inside))
+        class Wrap:                                                               # an object that exports device memory by pointer
+            def __init__(self, x):
+                self.keep = x
+                self.__cuda_array_interface__ = x.__cuda_array_interface__
+        del o
+        torch.cuda.empty_cache()
+        for o in [torch.ones(G // 8, dtype=torch.int64, device="cuda") for _ in range(2)]:
+            s += int(o.sum().item())
+        gone3 = shim.cuVGPUResidentBytes(C.c_ulonglong(t.data_ptr()))
+        v = torch.as_tensor(Wrap(t), device="cuda")                               # cudaPointerGetAttributes decides the device
+        ok = v.device.index == 0 and int(v[-1].item()) == 3 * G // 16 - 1 and int(v[G // 8 + 7].item()) == G // 8 + 7
+        print(json.dumps({"gone": [gone, gone2, gone3], "rc": [rc1, rc2, rc3], "memory_type": mt.value, "base_ok": base.value == t.data_ptr(),
+                          "size": size.value, "range": [vals[0] == t.data_ptr(), int(vals[1])], "ordinal": int(vals[2] & 0xFFFFFFFF),
+                          "managed": int(vals[3] & 0xFFFFFFFF), "ok": bool(ok), "s": s}))
+    """
+    o = last_json(run_under_shim(code, {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "8g", "VGPU_OVERSUB_RESIDENT_MB": "2048"}, timeout=600))
+    print("pointer queries:", o)
+    assert o["gone"] == [0, 0, 0]                                   # the range was out of HBM before each query
+    assert o["rc"] == [0, 0, 0] and o["memory_type"] == 2           # CU_MEMORYTYPE_DEVICE
+    assert o["base_ok"] and o["size"] == 3 << 29
+    assert o["range"] == [True, 3 << 29] and o["ordinal"] == 0 and o["managed"] == 0
+    assert o["ok"] and o["s"] == 6 * (1 << 27)
+
+
 RANDOM_PROGRAM = """
     import ctypes, hashlib, json, random, sys, torch
     seed = int(sys.argv[1])
