@@ -630,6 +630,8 @@ static alloc_node_t **g_idx;           /* the managed ranges sorted by address (
 static size_t g_idx_n, g_idx_cap;
 static void idx_del(alloc_node_t *a);
 static void vmm_quiesce(void);
+static int vmm_make_room(void);
+static void vmm_keep_reserve(void);
 
 static void track_vmem(CUdeviceptr p, size_t n, int dev, void *vmem) {
     alloc_node_t *a = (alloc_node_t *)malloc(sizeof(*a));
@@ -698,6 +700,10 @@ static int add_chunk(CUdeviceptr *p, size_t n) {
     if (n <= IPCSIZE || g_allocmode == 2) {
         cuMemAlloc_v2_t f = get_cuMemAlloc_v2();
         rc = f ? f(p, n) : 3;
+        /* VMM backend: small allocations live outside the managed ranges, in the HBM the residency engine keeps free
+         * (VGPU_OVERSUB_RESERVE_MB).  A burst of them can use that up between two launches: spill and try again. */
+        while (rc == 2 && g_backend_vmm && vmm_make_room()) rc = f(p, n);
+        if (rc == 0 && g_backend_vmm) vmm_keep_reserve();
     } else if (g_backend_vmm) {
         if (vmm_alloc(dev, n, p) != 0) return 2;
         region_add_usage(col_of(dev), n, VGPU_USE_DATA);
@@ -1574,6 +1580,31 @@ static int vmm_evict_node(alloc_node_t *v) {
     int rc = g_dp.evict(v->vmem, 0, node_chunks(v));
     if (rc != 0) SHIM_ERR("vmm backend evict: %s", g_dp.last_error());
     return rc;
+}
+
+/* the driver itself ran out of HBM (g_res_mu and g_alloc_mu held): spill one range.  -> 1 if something was spilled */
+static int vmm_make_room(void) {
+    alloc_node_t *v = vmm_victim(++g_res_epoch);
+    if (!v) return 0;
+    vmm_go_paged();
+    const int was = tl_bypass;
+    tl_bypass = 1;
+    const int rc = vmm_evict_node(v);
+    tl_bypass = was;
+    return rc == 0;
+}
+
+/* after an allocation outside the managed ranges: the driver's own needs (module loading at a kernel's first launch,
+ * library workspaces) come out of the same free HBM, and no launch of an unmanaged tensor would restore it */
+static void vmm_keep_reserve(void) {
+    const int was = tl_bypass;
+    for (;;) {
+        size_t fr = 0, tot = 0;
+        tl_bypass = 1;
+        const int have = get_cuMemGetInfo_v2() && real_cuMemGetInfo_v2(&fr, &tot) == 0;
+        tl_bypass = was;
+        if (!have || fr >= vmm_reserve() / 2 || !vmm_make_room()) return;
+    }
 }
 
 /* Make chunks [first, first+n) of `a` resident for the call `epoch`.  g_res_mu and g_alloc_mu held.  -> 0 or a VGPU_E_* */

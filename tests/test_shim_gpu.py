@@ -1000,6 +1000,38 @@ def test_pointer_queries_on_a_spilled_range_still_describe_device_memory(cuda_de
     assert o["ok"] and o["s"] == 6 * (1 << 27)
 
 
+
+def test_small_allocations_get_room_when_the_ranges_fill_the_whole_gpu(cuda_dev):
+    """Allocations of 2 MiB and less stay plain driver allocations.  With the physical GPU full of resident managed
+    ranges (no operator bound: the engine keeps VGPU_OVERSUB_RESERVE_MB free, here 1 GiB), 6 GiB of them in one burst run
+    the driver itself out of HBM: the allocation spills ranges and tries again instead of failing."""
+    code = """
+        import ctypes as C, json, torch
+        torch.cuda.init()
+        shim = C.CDLL(None)
+        G = 1 << 30
+        def stats():
+            st = (C.c_uint64 * 8)()
+            shim.cuVGPUOversubStats(st)
+            return st
+        big = []
+        while not stats()[6] and len(big) < 60:             # 4 GiB ranges until one no longer fits the GPU
+            big.append(torch.full((4 * G // 8,), len(big) + 1, dtype=torch.int64, device="cuda"))
+        before = int(stats()[1])
+        small = [torch.full((1 << 17,), i, dtype=torch.int64, device="cuda") for i in range(6 * 1024)]   # 1 MiB each: 2 MiB plain segments
+        torch.cuda.synchronize()
+        ok_small = all(int(small[i][-1].item()) == i and int(small[i][0].item()) == i for i in range(0, len(small), 97))
+        ok_big = all(int(b[0].item()) == i + 1 and int(b[-1].item()) == i + 1 for i, b in enumerate(big))
+        st = stats()
+        print(json.dumps({"n_big": len(big), "spilled_for_small_mib": (int(st[1]) - before) * 2, "ok_small": ok_small, "ok_big": ok_big, "bad": int(st[3])}))
+    """
+    p = run_under_shim(code, {**OVERSUB_ENV, "CUDA_DEVICE_MEMORY_LIMIT_0": "400g"}, timeout=900)
+    o = last_json(p)
+    print("small allocations on a full GPU:", o)
+    assert o["n_big"] >= 30 and o["ok_small"] and o["ok_big"] and o["bad"] == 0, p.stderr[-2000:]
+    assert o["spilled_for_small_mib"] >= 4096          # the burst did not fit what was left: at least one range went out for it
+
+
 RANDOM_PROGRAM = """
     import ctypes, hashlib, json, random, sys, torch
     seed = int(sys.argv[1])
