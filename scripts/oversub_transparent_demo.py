@@ -7,7 +7,12 @@ VGPU_OVERSUB_BACKEND=vmm; the shim decides at every launch / copy which ranges m
 recently used ones — to the idle peer GPU named by VGPU_OVERSUB_PEER while the peer budget lasts, then to pinned host
 RAM.  Prints one JSON line with the paging statistics and the rates seen by the program.
 
-    python scripts/oversub_transparent_demo.py [tensors] [GiB each] [peer budget GiB]
+    python scripts/oversub_transparent_demo.py [tensors] [GiB each] [peer budget GiB] [vmm|managed] [timeout s] [GiB of HBM left free]
+
+With "managed" the same program runs on the REFERENCE's route instead (cuMemoryAllocate@0x32146 -> cuMemAllocManaged,
+the driver's UVM page faults do the paging; host RAM only): the like-for-like arm of this comparison.  Where the box
+refuses managed allocations beyond a few tens of GiB, the last argument makes the GPU small instead: a second process
+(no shim) holds all HBM but that many GiB for as long as the program runs.
 """
 import json
 import os
@@ -22,6 +27,16 @@ SHIM = os.path.join(ROOT, "4paradigm-k8s-device-plugin_b200", "libvgpu.so")
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 17
 GIB_EACH = float(sys.argv[2]) if len(sys.argv) > 2 else 16.0
 PEER_GIB = float(sys.argv[3]) if len(sys.argv) > 3 else 64.0
+BACKEND = sys.argv[4] if len(sys.argv) > 4 else "vmm"
+TIMEOUT = float(sys.argv[5]) if len(sys.argv) > 5 else 3000
+LEAVE_FREE_GIB = float(sys.argv[6]) if len(sys.argv) > 6 else 0.0
+BALLAST = textwrap.dedent("""
+    import sys, time, torch
+    free, _ = torch.cuda.mem_get_info()
+    t = torch.empty(free - int(float(sys.argv[1]) * (1 << 30)), dtype=torch.uint8, device="cuda")
+    print("ready", torch.cuda.mem_get_info()[0], flush=True)
+    time.sleep(100000)
+""")
 
 WORKER = textwrap.dedent("""
     import ctypes, json, sys, time, torch
@@ -47,11 +62,13 @@ WORKER = textwrap.dedent("""
         ts.append(t)
     torch.cuda.synchronize()
     t1 = time.perf_counter()
+    print("write pass done in %.1f s" % (t1 - t0), flush=True)
     wrong = 0
     for k in range(n_t):
         wrong += bad(ts[k], k)
     torch.cuda.synchronize()
     t2 = time.perf_counter()
+    print("forward read pass done in %.1f s" % (t2 - t1), flush=True)
     for k in reversed(range(n_t)):
         wrong += bad(ts[k], k)
     torch.cuda.synchronize()
@@ -78,18 +95,38 @@ def main():
     td = tempfile.mkdtemp(prefix="vgpuover")
     env = dict(os.environ)
     env.update({"LD_PRELOAD": SHIM, "CUDA_DEVICE_MEMORY_SHARED_CACHE": os.path.join(td, "c.cache"), "LIBCUDA_LOG_LEVEL": "0",
-                "CUDA_OVERSUBSCRIBE": "true", "VGPU_OVERSUB_BACKEND": "vmm", "CUDA_DEVICE_MEMORY_LIMIT_0": "300000m",
-                "NVIDIA_DEVICE_MAP": f"0:{uu[0]}"})
-    if n_gpu > 1:
+                "CUDA_OVERSUBSCRIBE": "true", "CUDA_DEVICE_MEMORY_LIMIT_0": "300000m", "NVIDIA_DEVICE_MAP": f"0:{uu[0]}"})
+    if BACKEND == "vmm":
+        env["VGPU_OVERSUB_BACKEND"] = "vmm"
+    if n_gpu > 1 and BACKEND == "vmm" and PEER_GIB > 0:
         env.update({"VGPU_OVERSUB_PEER": uu[1], "VGPU_OVERSUB_PEER_MB": str(int(PEER_GIB * 1024))})
+    ballast = None
+    if LEAVE_FREE_GIB > 0:
+        ballast = subprocess.Popen([sys.executable, "-c", BALLAST, str(LEAVE_FREE_GIB)], stdout=subprocess.PIPE, text=True)
+        ready = ballast.stdout.readline().split()
+        assert ready and ready[0] == "ready", "the ballast process did not come up"
+    try:
+        run(env, ballast)
+    finally:
+        if ballast is not None:
+            ballast.kill()
+            ballast.wait()
+
+
+def run(env, ballast):
     t0 = time.perf_counter()
-    p = subprocess.run([sys.executable, "-c", WORKER, str(N), str(GIB_EACH)], env=env, capture_output=True, text=True, timeout=3000)
+    try:
+        p = subprocess.run([sys.executable, "-c", WORKER, str(N), str(GIB_EACH)], env=env, capture_output=True, text=True, timeout=TIMEOUT)
+    except subprocess.TimeoutExpired as e:
+        out = (e.stdout or b"").decode() if isinstance(e.stdout, bytes) else (e.stdout or "")
+        print(json.dumps({"backend": BACKEND, "tensors": N, "GiB_each": GIB_EACH, "timed_out_after_s": TIMEOUT, "progress": out.strip().splitlines()[-3:]}))
+        return
     wall = time.perf_counter() - t0
     if p.returncode != 0:
         print(p.stderr[-3000:], file=sys.stderr)
         raise SystemExit(p.returncode)
     o = json.loads(p.stdout.strip().splitlines()[-1])
-    o.update({"wall_s": round(wall, 1), "peer_tier": (f"GPU 1, budget {PEER_GIB} GiB" if n_gpu > 1 else None),
+    o.update({"backend": BACKEND, "hbm_left_free_GiB": LEAVE_FREE_GIB or None, "wall_s": round(wall, 1), "peer_tier": (f"GPU 1, budget {PEER_GIB} GiB" if "VGPU_OVERSUB_PEER" in env else None),
               "host_mem_available_GB": round(int(next(l for l in open("/proc/meminfo") if l.startswith("MemAvailable")).split()[1]) / 1e6, 1)})
     print(json.dumps(o))
 
