@@ -114,6 +114,7 @@ SIGNATURES = {
     "vgpu_vmem_ensure": (_i, [_vp, _u64, _u64]),
     "vgpu_vmem_missing": (_i, [_vp, _u64, _u64, _pp(_u64)]),
     "vgpu_vmem_evict": (_i, [_vp, _u64, _u64]),
+    "vgpu_vmem_swap": (_i, [_vp, _vp, _u64, _u64]),
     "vgpu_vmem_locate": (_i, [_vp, _u64, _pp(_i), _pp(_vp)]),
     "vgpu_vmem_stats": (_i, [_vp, _pp(VmemStats)]),
     "vgpu_vmem_destroy": (_i, [_vp]),

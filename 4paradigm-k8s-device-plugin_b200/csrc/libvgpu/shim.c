@@ -392,6 +392,7 @@ static struct {
     int (*ensure)(void *, uint64_t, uint64_t);
     int (*evict)(void *, uint64_t, uint64_t);
     int (*missing)(void *, uint64_t, uint64_t, uint64_t *);
+    int (*swap)(void *, void *, uint64_t, uint64_t);  /* optional: a data-path library without it evicts, then ensures */
     int (*destroy)(void *);
     const char *(*last_error)(void);
 } g_dp;
@@ -420,6 +421,7 @@ static void load_vmm_backend(void) {
     g_dp.ensure = (int (*)(void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_ensure");
     g_dp.evict = (int (*)(void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_evict");
     g_dp.missing = (int (*)(void *, uint64_t, uint64_t, uint64_t *))real_dlsym(g_dp.lib, "vgpu_vmem_missing");
+    g_dp.swap = getenv("VGPU_OVERSUB_NO_SWAP") ? NULL : (int (*)(void *, void *, uint64_t, uint64_t))real_dlsym(g_dp.lib, "vgpu_vmem_swap");
     g_dp.destroy = (int (*)(void *))real_dlsym(g_dp.lib, "vgpu_vmem_destroy");
     g_dp.last_error = (const char *(*)(void))real_dlsym(g_dp.lib, "vgpu_last_error");
     g_backend_vmm = g_dp.create && g_dp.create_tiered && g_dp.base && g_dp.ensure && g_dp.evict && g_dp.missing && g_dp.destroy && g_dp.last_error;
@@ -1582,6 +1584,15 @@ static int vmm_evict_node(alloc_node_t *v) {
     return rc;
 }
 
+static int vmm_swap_nodes(alloc_node_t *v, alloc_node_t *a, uint64_t first, uint64_t n) {
+    vmm_quiesce();
+    SHIM_INFO("oversubscribed: range 0x%llx (%zu MiB, last used at tick %lu) leaves while 0x%llx arrives", v->addr, v->len >> 20,
+              (unsigned long)v->last_use, a->addr);
+    int rc = g_dp.swap(v->vmem, a->vmem, first, n);
+    if (rc != 0) SHIM_ERR("vmm backend swap: %s", g_dp.last_error());
+    return rc;
+}
+
 /* the driver itself ran out of HBM (g_res_mu and g_alloc_mu held): spill one range.  -> 1 if something was spilled */
 static int vmm_make_room(void) {
     alloc_node_t *v = vmm_victim(++g_res_epoch);
@@ -1632,6 +1643,12 @@ static int vmm_make_resident(alloc_node_t *a, uint64_t first, uint64_t n, uint64
         }
         if (tight) {
             alloc_node_t *v = vmm_victim(epoch);
+            /* the victim leaves while this range arrives, both directions of the link at once, into the HBM the
+             * victim frees block by block; what is still missing afterwards goes round the loop again */
+            if (v && g_dp.swap && v->dev == a->dev && vmm_swap_nodes(v, a, first, n) == 0) {
+                if (g_dp.missing(a->vmem, first, n, &miss) != 0 || miss == 0) break;
+                continue;
+            }
             if (v && vmm_evict_node(v) == 0) continue;
             /* nothing of ours left to spill: the HBM is held by other tenants.  Do NOT try anyway — the manager maps
              * block by block until the driver refuses, which would eat the reserve every other allocation on the GPU

@@ -18,6 +18,7 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <vector>
 
@@ -105,7 +106,8 @@ struct Vmem {
     // then pinned host RAM"): a victim goes to the first tier that still has a free slot.
     struct Tier {
         int kind = 0, peer = -1;
-        void *slab = nullptr;       // allocated at the first eviction that needs it
+        void *slab = nullptr;       // peer tier: one allocation on the peer GPU, made at the first eviction that needs it
+        std::vector<void *> piece;  // host tier: one pinned piece per slot IN USE, from the process-wide pool (host_piece_get)
         size_t slots = 0;           // blocks
         std::vector<uint32_t> free_slots;
         uint64_t evictions = 0;     // chunks
@@ -131,6 +133,64 @@ struct Vmem {
 
 double now_ms() {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// Pinned host memory for the host tier, by the piece (one block).  Pinning costs ~40 ms per GiB (mmap + first touch on
+// 16 threads + cudaHostRegister: 24 GB/s, against 55 GB/s for the transfer itself), so a piece is never given back
+// to the OS while someone may need one again: a restored block's piece goes to a process-wide pool and the next block
+// that leaves — of any range — takes it.  A process that pages in steady state pins nothing after the first round,
+// and what is pinned at any time is what is spilled plus the pool (trimmed to VGPU_VMEM_HOST_POOL_MB, default 8192),
+// not the sum of all ranges.
+struct HostPool {
+    std::mutex mu;
+    std::map<size_t, std::vector<void *>> free_;  // by piece size
+    size_t bytes = 0;
+} g_host_pool;
+
+size_t host_pool_cap() {
+    const char *e = getenv("VGPU_VMEM_HOST_POOL_MB");
+    return (e && *e ? strtoull(e, nullptr, 0) : 8192ull) << 20;
+}
+void *host_piece_get(Vmem *v, size_t bytes) {
+    {
+        std::lock_guard<std::mutex> lk(g_host_pool.mu);
+        auto it = g_host_pool.free_.find(bytes);
+        if (it != g_host_pool.free_.end() && !it->second.empty()) {
+            void *p = it->second.back();
+            it->second.pop_back();
+            g_host_pool.bytes -= bytes;
+            return p;
+        }
+    }
+    void *p = nullptr;
+    const double ts = now_ms();
+    const int rc = vgpu_slab_alloc(VGPU_TIER_HOST, v->device, -1, bytes, &p);
+    v->st.tier_setup_ms += now_ms() - ts;
+    return rc == VGPU_OK ? p : nullptr;
+}
+void host_piece_put(Vmem *v, void *p, size_t bytes) {
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> lk(g_host_pool.mu);
+        if (g_host_pool.bytes + bytes <= host_pool_cap()) {
+            g_host_pool.free_[bytes].push_back(p);
+            g_host_pool.bytes += bytes;
+            return;
+        }
+    }
+    vgpu_slab_free(VGPU_TIER_HOST, v->device, -1, p);
+}
+// where slot `slot` of tier t lives
+char *slot_ptr(Vmem *v, Vmem::Tier &t, uint32_t slot) {
+    return t.kind == VGPU_TIER_HOST ? (char *)t.piece[slot] : (char *)t.slab + (size_t)slot * v->block_bytes();
+}
+// a slot whose block is resident again (or gone) is free; its pinned piece goes back to the pool
+void free_slot(Vmem *v, Vmem::Tier &t, uint32_t slot) {
+    t.free_slots.push_back(slot);
+    if (t.kind == VGPU_TIER_HOST && t.piece[slot]) {
+        host_piece_put(v, t.piece[slot], v->block_bytes());
+        t.piece[slot] = nullptr;
+    }
 }
 
 // Back the blocks `list` (ascending) with physical memory.  cuMemMap costs under a microsecond; cuMemSetAccess costs
@@ -191,6 +251,7 @@ int unmap_block(Vmem *v, size_t b, bool release) {
     return VGPU_OK;
 }
 
+int begin_spill(Vmem *v, size_t b);
 void give_slot_back(Vmem *v, Block &bl) {
     Vmem::Tier &t = v->tiers[bl.tier_idx];
     t.free_slots.push_back(bl.tier_slot);
@@ -215,44 +276,10 @@ int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
     size_t launched = 0;
     int rc = VGPU_OK;
     for (size_t i = 0; i < victims.size() && !rc; ++i) {
-        const size_t b = victims[i];
-        Block &bl = v->blocks[b];
-        size_t ti = 0;
-        for (;; ++ti) {  // first tier with room whose slab can be had
-            if (ti == v->tiers.size()) {
-                rc = fail(VGPU_E_NOMEM, "spill tier full: no tier can take block %zu", b);
-                break;
-            }
-            Vmem::Tier &c = v->tiers[ti];
-            if (c.free_slots.empty()) continue;
-            if (c.slab) break;
-            const double ts = now_ms();
-            const int src = vgpu_slab_alloc(c.kind, v->device, c.peer, c.slots * v->block_bytes(), &c.slab);
-            v->st.tier_setup_ms += now_ms() - ts;  // one-time: a context on the peer and its slab, or pinning the host slab
-            if (src == VGPU_OK) break;
-            // e.g. the peer GPU is not idle after all: give this tier up and fall through to the next
-            c.free_slots.clear();
-            c.slots = 0;
-        }
-        if (rc) break;
-        Vmem::Tier &t = v->tiers[ti];
-        bl.tier_idx = (uint8_t)ti;
-        bl.tier_slot = t.free_slots.back();
-        t.free_slots.pop_back();
-        t.evictions += v->bc;
         const double tl = now_ms();
-        // a range the peer was not given access to (see create) cannot be pulled, whatever the policy says by now
-        const int variant = (t.kind == VGPU_TIER_PEER && v->access_n < 2 && vgpu_policy_get(VGPU_TIER_PEER, v->bc) == VGPU_XFER_PULL)
-                                ? VGPU_XFER_TMA : VGPU_XFER_AUTO;
-        rc = vgpu_spill(variant, t.kind, (const void *)(v->base + b * v->block_bytes()),
-                        (char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(), nullptr, nullptr, v->bc, kCB,
-                        v->ck + b * v->bc, v->stream);
+        rc = begin_spill(v, victims[i]);  // a failed one took nothing: the block stays resident
         v->t_launch += now_ms() - tl;
-        if (rc) {
-            give_slot_back(v, bl);  // nothing of this block was queued: it stays resident
-            break;
-        }
-        launched = i + 1;
+        if (!rc) launched = i + 1;
     }
     // every block whose spill was queued is in the tier once the stream is idle
     const double tw = now_ms();
@@ -279,6 +306,94 @@ int evict_blocks(Vmem *v, const std::vector<size_t> &victims, bool release) {
     v->t_unmap += now_ms() - tu;
     v->st.evict_ms += now_ms() - t0;
     return rc;
+}
+
+
+// ---- one block at a time: the steps evict_blocks / vgpu_vmem_ensure do in bulk, for vgpu_vmem_swap's lock step
+
+// Pick the tier slot for block b (first tier with room whose slab can be had) and queue its spill.  -> VGPU_OK with the
+// slot taken and the kernel on v->stream, or an error with nothing taken.
+int begin_spill(Vmem *v, size_t b) {
+    Block &bl = v->blocks[b];
+    size_t ti = 0;
+    uint32_t slot = 0;
+    for (;; ++ti) {
+        if (ti == v->tiers.size()) return fail(VGPU_E_NOMEM, "spill tier full: no tier can take block %zu", b);
+        Vmem::Tier &c = v->tiers[ti];
+        if (c.free_slots.empty()) continue;
+        slot = c.free_slots.back();
+        if (c.kind == VGPU_TIER_HOST) {  // pinned by the piece, from the pool if it has one
+            if (c.piece[slot] || (c.piece[slot] = host_piece_get(v, v->block_bytes())) != nullptr) break;
+        } else {
+            if (c.slab) break;
+            const double ts = now_ms();
+            const int src = vgpu_slab_alloc(c.kind, v->device, c.peer, c.slots * v->block_bytes(), &c.slab);
+            v->st.tier_setup_ms += now_ms() - ts;  // one-time: a context on the peer and its slab
+            if (src == VGPU_OK) break;
+        }
+        // e.g. the peer GPU is not idle after all, or no more host memory can be pinned: give this tier up
+        c.free_slots.clear();
+        c.slots = 0;
+    }
+    Vmem::Tier &t = v->tiers[ti];
+    bl.tier_idx = (uint8_t)ti;
+    bl.tier_slot = slot;
+    t.free_slots.pop_back();
+    t.evictions += v->bc;
+    // a range the peer was not given access to (see create) cannot be pulled, whatever the policy says by now
+    const int variant = (t.kind == VGPU_TIER_PEER && v->access_n < 2 && vgpu_policy_get(VGPU_TIER_PEER, v->bc) == VGPU_XFER_PULL)
+                            ? VGPU_XFER_TMA : VGPU_XFER_AUTO;
+    const int rc = vgpu_spill(variant, t.kind, (const void *)(v->base + b * v->block_bytes()), slot_ptr(v, t, slot), nullptr, nullptr,
+                              v->bc, kCB, v->ck + b * v->bc, v->stream);
+    if (rc) give_slot_back(v, bl);
+    return rc;
+}
+// The spill of block b has run (ok) or its stream failed (!ok): unmap and release it, or give the slot back.
+int finish_spill(Vmem *v, size_t b, bool ok) {
+    Block &bl = v->blocks[b];
+    if (!ok) {
+        give_slot_back(v, bl);
+        return fail(VGPU_E_CUDA, "spill of block %zu did not complete", b);
+    }
+    if (int urc = unmap_block(v, b, true)) {
+        give_slot_back(v, bl);
+        return urc;
+    }
+    bl.state = kSpilled;
+    v->resident -= 1;
+    v->spilled += 1;
+    v->st.evictions += v->bc;
+    return VGPU_OK;
+}
+int begin_restore(Vmem *v, size_t b, int variant) {
+    Block &bl = v->blocks[b];
+    Vmem::Tier &t = v->tiers[bl.tier_idx];
+    v->res[b].bad_chunks = 0;
+    v->res[b].first_bad_inv = 0;
+    return vgpu_restore(variant, t.kind, slot_ptr(v, t, bl.tier_slot), (void *)(v->base + b * v->block_bytes()), nullptr, nullptr, v->bc,
+                        kCB, v->ck + b * v->bc, nullptr, &v->res[b], v->stream);
+}
+// The restore of block b was queued and its stream is idle (drained) or broken: verdict, one retry through the copy
+// engine, then either resident (slot freed) or unmapped again and still spilled with its tier copy intact.
+int finish_restore(Vmem *v, size_t b, bool drained) {
+    Block &bl = v->blocks[b];
+    bool good = drained && v->res[b].bad_chunks == 0;
+    if (drained && !good) {
+        v->st.restore_retries += 1;
+        if (begin_restore(v, b, VGPU_XFER_CE) == VGPU_OK && cudaStreamSynchronize(v->stream) == cudaSuccess) good = v->res[b].bad_chunks == 0;
+    }
+    if (good) {
+        free_slot(v, v->tiers[bl.tier_idx], bl.tier_slot);
+        bl.state = kResident;
+        v->resident += 1;
+        v->spilled -= 1;
+        v->st.fetches += v->bc;
+        return VGPU_OK;
+    }
+    if (drained) v->st.checksum_failures += v->res[b].bad_chunks;
+    unmap_block(v, b, false);
+    return fail(VGPU_E_MISMATCH, "block %zu: %llu restored chunk(s) failed their checksum (first: chunk %llu); the block stays in the tier", b,
+                (unsigned long long)v->res[b].bad_chunks, (unsigned long long)(b * v->bc + (~v->res[b].first_bad_inv)));
 }
 
 }  // namespace
@@ -320,6 +435,7 @@ int vgpu_vmem_create_tiered(int device, uint64_t virtual_bytes, uint64_t residen
         t.peer = k == 0 ? peer_device : -1;
         t.slots = (bytes + v->block_bytes() - 1) / v->block_bytes();
         t.free_slots.resize(t.slots);
+        if (t.kind == VGPU_TIER_HOST) t.piece.assign(t.slots, nullptr);
         for (size_t i = 0; i < t.slots; ++i) t.free_slots[i] = (uint32_t)(t.slots - 1 - i);
         v->tiers.push_back(std::move(t));
     }
@@ -434,18 +550,9 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
         }
     // ... then the restore kernels of the spilled ones run back to back.  Each launch reports into its own result
     // slot, so a checksum failure names its block.
-    auto restore_block = [&](size_t b, int variant) -> int {
-        Block &bl = v->blocks[b];
-        Vmem::Tier &t = v->tiers[bl.tier_idx];
-        v->res[b].bad_chunks = 0;
-        v->res[b].first_bad_inv = 0;
-        return vgpu_restore(variant, t.kind, (const char *)t.slab + (size_t)bl.tier_slot * v->block_bytes(),
-                            (void *)(v->base + b * v->block_bytes()), nullptr, nullptr, v->bc, kCB, v->ck + b * v->bc, nullptr,
-                            &v->res[b], v->stream);
-    };
     std::vector<size_t> launched;
     for (size_t i = 0; i < back.size() && !result; ++i) {
-        if ((result = restore_block(back[i], VGPU_XFER_AUTO)) != VGPU_OK) {
+        if ((result = begin_restore(v, back[i], VGPU_XFER_AUTO)) != VGPU_OK) {
             for (size_t k = i; k < back.size(); ++k) unmap_block(v, back[k], false);  // nothing was launched into these: they stay spilled, slots taken
             break;
         }
@@ -454,36 +561,111 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
     if (!launched.empty()) {
         const bool drained = cudaStreamSynchronize(v->stream) == cudaSuccess;
         if (!drained && !result) result = fail(VGPU_E_CUDA, "cudaStreamSynchronize (ensure)");
+        // What arrived must match what was spilled.  A block that does not is tried once more through the other mover
+        // (copy engine + checksum kernel); if it still fails it is unmapped again and stays spilled — the tier holds
+        // the only good copy, slot and checksums untouched, so a later ensure() can succeed (finish_restore).
         for (size_t b : launched) {
-            Block &bl = v->blocks[b];
-            bool good = drained && v->res[b].bad_chunks == 0;
-            if (drained && !good) {
-                // What arrived does not match what was spilled.  The tier still holds the only good copy: keep it,
-                // and try once more through the other mover (copy engine + checksum kernel) before giving up.
-                v->st.restore_retries += 1;
-                if (restore_block(b, VGPU_XFER_CE) == VGPU_OK && cudaStreamSynchronize(v->stream) == cudaSuccess)
-                    good = v->res[b].bad_chunks == 0;
-            }
-            if (good) {
-                v->tiers[bl.tier_idx].free_slots.push_back(bl.tier_slot);
-                bl.state = kResident;
-                v->resident += 1;
-                v->spilled -= 1;
-                v->st.fetches += v->bc;
-            } else {
-                // still spilled: HBM unmapped again, tier slot and checksums untouched, so a later ensure() can
-                // succeed once the cause (a flaky link, a repaired slab) is gone
-                if (drained) v->st.checksum_failures += v->res[b].bad_chunks;
-                unmap_block(v, b, false);
-                if (!result)
-                    result = fail(VGPU_E_MISMATCH, "block %zu: %llu restored chunk(s) failed their checksum (first: chunk %llu); the block stays in the tier",
-                                  b, (unsigned long long)v->res[b].bad_chunks,
-                                  (unsigned long long)(b * v->bc + (~v->res[b].first_bad_inv)));
-            }
+            const int f = finish_restore(v, b, drained);
+            if (f != VGPU_OK && !result) result = f;
         }
     }
     v->st.fetch_ms += now_ms() - t0;
     return result;
+}
+
+// One range leaves while another arrives.  A caller whose HBM is full (the shim's residency engine, a monitor) would
+// otherwise evict the victim — the link busy in one direction — and only then ensure the range it needs — the link busy
+// in the other.  PCIe and NVLink are full duplex: here the two transfers run in lock step, one block each way per step,
+// on the two ranges' own streams.  The VMM calls of a step (unmap + release of the block that just left, create + map +
+// set-access of the block that arrives next) are issued while the GPU is idle, because cuMemUnmap / cuMemSetAccess wait
+// for running kernels (see map_blocks); the arriving block only ever takes memory that a leaving block freed in THIS
+// call, so the call never holds more HBM than before it.  All resident blocks of `out` leave; of [first, first+n) of
+// `in` as many missing blocks arrive as that memory allows — vgpu_vmem_missing tells what is left, vgpu_vmem_ensure
+// or another swap brings it.  Per-block state, checksum verification and the failed-restore handling are ensure()'s.
+int vgpu_vmem_swap(void *out_handle, void *in_handle, uint64_t first, uint64_t n) {
+    Vmem *o = static_cast<Vmem *>(out_handle), *v = static_cast<Vmem *>(in_handle);
+    if (!o || !v || o == v) return fail(VGPU_E_INVAL, "swap needs two different ranges");
+    if (first + n > v->nchunks) return fail(VGPU_E_INVAL, "chunk range out of bounds");
+    if (o->device != v->device) return fail(VGPU_E_INVAL, "both ranges must live on one device");
+    std::unique_lock<std::mutex> lo(o->mu, std::defer_lock), lv(v->mu, std::defer_lock);
+    std::lock(lo, lv);
+    CtxScope keep;
+    VGPU_CUDA(cudaSetDevice(v->device));
+    std::vector<size_t> out, in;
+    for (size_t b = 0; b < o->nblocks; ++b)
+        if (o->blocks[b].state == kResident) out.push_back(b);
+    if (n) {
+        const uint64_t stamp = ++v->clock;
+        for (size_t b = first / v->bc; b <= (first + n - 1) / v->bc; ++b) {
+            v->blocks[b].last_use = stamp;
+            if (v->blocks[b].state != kResident) in.push_back(b);
+        }
+    }
+    if (v->resident + in.size() > v->resident_limit)
+        return fail(VGPU_E_NOMEM, "%zu blocks to bring in, resident limit is %zu", in.size(), v->resident_limit);
+    size_t free_total = 0;
+    for (auto &t : o->tiers) free_total += t.free_slots.size();
+    if (out.size() > free_total) return fail(VGPU_E_NOMEM, "spill tier full: %zu blocks to evict, %zu free slots", out.size(), free_total);
+    const double t0 = now_ms();
+    VGPU_CUDA(cudaDeviceSynchronize());  // whatever the application queued on the leaving range must be done
+    size_t oi = 0, ii = 0;
+    uint64_t credit = 0;  // bytes freed by blocks that left, not yet taken by blocks that arrived
+    int rc = VGPU_OK;
+    while (!rc && (oi < out.size() || (ii < in.size() && credit >= v->block_bytes()))) {
+        // -- GPU idle: the VMM calls of this step
+        bool arriving = false;
+        if (ii < in.size() && credit >= v->block_bytes()) {
+            if ((rc = map_blocks(v, std::vector<size_t>{in[ii]})) != VGPU_OK) break;
+            credit -= v->block_bytes();
+            if (v->blocks[in[ii]].state == kUntouched) {  // never written: nothing to copy
+                v->blocks[in[ii]].state = kResident;
+                v->resident += 1;
+                ++ii;
+            } else {
+                arriving = true;
+            }
+        }
+        // -- both directions queued back to back, then both awaited
+        bool leaving = false;
+        const double tl = now_ms();
+        if (oi < out.size()) {
+            if ((rc = begin_spill(o, out[oi])) == VGPU_OK) leaving = true;
+        }
+        if (arriving) {
+            const int r = begin_restore(v, in[ii], VGPU_XFER_AUTO);
+            if (r != VGPU_OK) {
+                unmap_block(v, in[ii], false);  // nothing was launched into it: it stays spilled, slot taken
+                arriving = false;
+                if (!rc) rc = r;
+            }
+        }
+        const double tw = now_ms();
+        o->t_launch += tw - tl;
+        const bool so = !leaving || cudaStreamSynchronize(o->stream) == cudaSuccess;
+        const bool sv = !arriving || cudaStreamSynchronize(v->stream) == cudaSuccess;
+        const double tu = now_ms();
+        o->t_wait += tu - tw;
+        if (leaving) {
+            const int f = finish_spill(o, out[oi], so);
+            if (f == VGPU_OK) credit += o->block_bytes();
+            else if (!rc) rc = f;
+            ++oi;
+        }
+        if (arriving) {
+            const int f = finish_restore(v, in[ii], sv);
+            if (f != VGPU_OK && !rc) rc = f;
+            ++ii;
+        }
+        o->t_unmap += now_ms() - tu;  // unmap + release of the block that left, slot and piece bookkeeping of the one that arrived
+    }
+    for (Vmem *m : {o, v}) {
+        for (auto h : m->pool) g_api.Release(h);
+        m->pool.clear();
+    }
+    const double dt = now_ms() - t0;
+    o->st.evict_ms += dt;
+    v->st.fetch_ms += dt;
+    return rc;
 }
 
 // Chunks of [first, first+n) that a vgpu_vmem_ensure of the same range would have to bring in (their block is not
@@ -514,7 +696,7 @@ int vgpu_vmem_locate(void *handle, uint64_t chunk, int *tier, void **ptr) {
     } else if (bl.state == kSpilled) {
         const Vmem::Tier &t = v->tiers[bl.tier_idx];
         *tier = t.kind;
-        *ptr = (char *)t.slab + (size_t)bl.tier_slot * v->block_bytes() + (chunk % v->bc) * kCB;
+        *ptr = slot_ptr(v, const_cast<Vmem::Tier &>(t), bl.tier_slot) + (chunk % v->bc) * kCB;
     }
     return VGPU_OK;
 }
@@ -551,8 +733,10 @@ int vgpu_vmem_destroy(void *handle) {
         }
     for (auto h : v->pool) g_api.Release(h);
     if (v->base) g_api.AddressFree(v->base, v->nblocks * v->block_bytes());
-    for (auto &t : v->tiers)
+    for (auto &t : v->tiers) {
         if (t.slab) vgpu_slab_free(t.kind, v->device, t.peer, t.slab);
+        for (void *p : t.piece) host_piece_put(v, p, v->block_bytes());  // to the pool for the ranges that remain, up to its cap
+    }
     if (v->ck) cudaFreeHost(v->ck);
     if (v->res) cudaFreeHost(v->res);
     if (v->stream) cudaStreamDestroy(v->stream);

@@ -281,6 +281,14 @@ int vgpu_vmem_locate(void *handle, uint64_t chunk, int *tier, void **ptr);
 /* Chunks of [first, first+n) that are not resident now (what an ensure of the range would have to map or restore,
  * counted in whole blocks): lets a caller that shares the GPU's HBM between several ranges make room first. */
 int vgpu_vmem_missing(void *handle, uint64_t first, uint64_t n, uint64_t *chunks);
+/* One range leaves while another arrives: every resident block of `out` is spilled, and of chunks [first, first+n) of
+ * `in` as many missing blocks are brought in as the memory freed by that allows — in lock step, one block each way per
+ * step, so that a full-duplex link (PCIe, NVLink) carries both transfers at once instead of one after the other as with
+ * vgpu_vmem_evict(out) followed by vgpu_vmem_ensure(in).  The call never holds more HBM than before it.  Both ranges
+ * on one device.  Synchronous.  VGPU_OK also when part of [first, first+n) is still missing (`out` was the smaller
+ * one): ask vgpu_vmem_missing.  Errors and per-block guarantees as for evict / ensure.  (No counterpart in the
+ * reference: UVM's eviction and fault-in are the driver's, /root/reference/vgpu/libvgpu.so@0x32146.) */
+int vgpu_vmem_swap(void *out, void *in, uint64_t first, uint64_t n);
 /* Push chunks [first, first+n) that are resident out to the tier and release their HBM. */
 int vgpu_vmem_evict(void *handle, uint64_t first, uint64_t n);
 int vgpu_vmem_stats(void *handle, vgpu_vmem_stats_t *out);

@@ -83,6 +83,8 @@ WORKER = textwrap.dedent("""
                       "write_pass_s": round(t1 - t0, 2), "read_pass_fwd_s": round(t2 - t1, 2), "read_pass_back_s": round(t3 - t2, 2),
                       "write_pass_GBps": round(gb / (t1 - t0), 1), "read_pass_fwd_GBps": round(gb / (t2 - t1), 1),
                       "read_pass_back_GBps": round(gb / (t3 - t2), 1)}), flush=True)
+    del ts, t
+    torch.cuda.empty_cache()                          # frees the ranges: with VGPU_VMEM_TRACE=1 each one reports its time split
 """)
 
 
@@ -126,6 +128,9 @@ def run(env, ballast):
         print(p.stderr[-3000:], file=sys.stderr)
         raise SystemExit(p.returncode)
     o = json.loads(p.stdout.strip().splitlines()[-1])
+    trace = [l for l in p.stderr.splitlines() if l.startswith("[vgpu_vmem]")]      # VGPU_VMEM_TRACE=1: the manager's time split per range
+    if trace:
+        o["vmem_trace"] = trace
     o.update({"backend": BACKEND, "hbm_left_free_GiB": LEAVE_FREE_GIB or None, "wall_s": round(wall, 1), "peer_tier": (f"GPU 1, budget {PEER_GIB} GiB" if "VGPU_OVERSUB_PEER" in env else None),
               "host_mem_available_GB": round(int(next(l for l in open("/proc/meminfo") if l.startswith("MemAvailable")).split()[1]) / 1e6, 1)})
     print(json.dumps(o))

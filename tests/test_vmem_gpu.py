@@ -243,3 +243,82 @@ def test_manager_leaves_the_callers_context_current(vgpu, cuda_dev):
             capi.lib.vgpu_vmem_destroy(h)
         torch.cuda.synchronize()
         capi.lib.vgpu_sm_partition_destroy(parts, 2)
+
+
+def test_swap_trades_two_ranges_in_lock_step_and_keeps_every_byte(vgpu, cuda_dev):
+    """vgpu_vmem_swap(out, in): A (resident) leaves while B (spilled) arrives, one block each way per step.  Contents
+    of both verified after each trade by the memtest verify kernel (bit-exact or it counts mismatches); the HBM held
+    during the call never exceeds what was held before it (sampled by a thread); a never-touched in-range is only
+    mapped; a smaller `out` brings in only as many blocks as it freed."""
+    import threading
+    import time
+    capi = vgpu.capi
+    n = 1024                                                # 2 GiB each, blocks of 128 chunks = 256 MiB: 8 steps
+    ha, a = _mk(capi, n, n, n, block_chunks=128)
+    hb, b = _mk(capi, n, n, n, block_chunks=128)
+    hc, c = _mk(capi, n // 4, n // 4, n // 4, block_chunks=128)
+    res = torch.zeros(3, dtype=torch.int64, device=cuda_dev)
+    lib = capi.lib
+
+    def verify(base, chunks, seed):
+        assert lib.vgpu_memtest_verify(base, chunks * CB, capi.PAT_RANDOM, seed, 0, res.data_ptr(), None) == 0
+        torch.cuda.synchronize()
+        assert res.cpu().tolist() == [0, 0, 0]
+
+    try:
+        assert lib.vgpu_vmem_ensure(hb, 0, n) == 0, capi.last_error()
+        assert lib.vgpu_memtest_fill(b, n * CB, capi.PAT_RANDOM, 22, 0, None) == 0
+        torch.cuda.synchronize()
+        assert lib.vgpu_vmem_evict(hb, 0, n) == 0, capi.last_error()          # B waits in the host tier
+        assert lib.vgpu_vmem_ensure(ha, 0, n) == 0, capi.last_error()
+        assert lib.vgpu_memtest_fill(a, n * CB, capi.PAT_RANDOM, 11, 0, None) == 0
+        torch.cuda.synchronize()
+        assert lib.vgpu_vmem_evict(ha, 0, n) == 0 and lib.vgpu_vmem_ensure(ha, 0, n) == 0, capi.last_error()   # pinned pieces for A's trip exist now
+        free_before, _ = torch.cuda.mem_get_info()
+        low = [free_before]
+        stop = threading.Event()
+
+        def sample():
+            while not stop.is_set():
+                low[0] = min(low[0], torch.cuda.mem_get_info()[0])
+                time.sleep(0.002)
+        th = threading.Thread(target=sample)
+        th.start()
+        t0 = time.perf_counter()
+        rc = lib.vgpu_vmem_swap(ha, hb, 0, n)
+        t_swap = time.perf_counter() - t0
+        stop.set()
+        th.join()
+        assert rc == 0, capi.last_error()
+        assert low[0] >= free_before - (64 << 20)            # never more HBM than before the call (first-use scratch aside)
+        sa, sb = _stats(capi, ha), _stats(capi, hb)
+        assert sa.chunks_resident == 0 and sa.chunks_spilled == n and sb.chunks_resident == n and sb.chunks_spilled == 0
+        assert sb.checksum_failures == 0
+        verify(b, n, 22)
+        # the same trade the other way with the two calls it replaces, for the time
+        t0 = time.perf_counter()
+        assert lib.vgpu_vmem_evict(hb, 0, n) == 0, capi.last_error()
+        assert lib.vgpu_vmem_ensure(ha, 0, n) == 0, capi.last_error()
+        t_two = time.perf_counter() - t0
+        verify(a, n, 11)
+        print(f"2 GiB out + 2 GiB in over the host tier: swap {t_swap * 1e3:.0f} ms, evict then ensure {t_two * 1e3:.0f} ms")
+        # a never-touched range comes in by mapping alone, taking what A frees
+        assert lib.vgpu_vmem_swap(ha, hc, 0, n // 4) == 0, capi.last_error()
+        sc = _stats(capi, hc)
+        assert sc.chunks_resident == n // 4 and sc.fetches == 0
+        assert lib.vgpu_memtest_fill(c, (n // 4) * CB, capi.PAT_RANDOM, 33, 0, None) == 0
+        torch.cuda.synchronize()
+        # C (2 blocks) leaves, A (8 blocks) wants in: only as many blocks as C freed arrive, the rest is still missing
+        assert lib.vgpu_vmem_swap(hc, ha, 0, n) == 0, capi.last_error()
+        miss = C.c_uint64(0)
+        assert lib.vgpu_vmem_missing(ha, 0, n, C.byref(miss)) == 0
+        assert miss.value == n - n // 4
+        assert lib.vgpu_vmem_ensure(ha, 0, n) == 0, capi.last_error()
+        verify(a, n, 11)
+        assert lib.vgpu_vmem_ensure(hc, 0, n // 4) == 0, capi.last_error()
+        verify(c, n // 4, 33)
+        # argument errors
+        assert lib.vgpu_vmem_swap(ha, ha, 0, n) != 0 and lib.vgpu_vmem_swap(ha, hb, 0, n + 1) != 0
+    finally:
+        for h in (ha, hb, hc):
+            lib.vgpu_vmem_destroy(h)
