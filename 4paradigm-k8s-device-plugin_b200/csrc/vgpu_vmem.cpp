@@ -139,12 +139,15 @@ double now_ms() {
 // 16 threads + cudaHostRegister: 24 GB/s, against 55 GB/s for the transfer itself), so a piece is never given back
 // to the OS while someone may need one again: a restored block's piece goes to a process-wide pool and the next block
 // that leaves — of any range — takes it.  A process that pages in steady state pins nothing after the first round,
-// and what is pinned at any time is what is spilled plus the pool (trimmed to VGPU_VMEM_HOST_POOL_MB, default 8192),
-// not the sum of all ranges.
+// and what is pinned is the high-water mark of what was spilled to the host at one time, not the sum of all ranges
+// that ever left.  Unpinning is as slow as pinning (cudaHostUnregister + munmap: ~1 s for 16 GiB), so a restore never
+// does it; only a range that is destroyed unpins its pieces, and only those the pool does not want
+// (VGPU_VMEM_HOST_POOL_MB, default 8192, or as much as is spilled to the host at that moment if that is more).
 struct HostPool {
     std::mutex mu;
     std::map<size_t, std::vector<void *>> free_;  // by piece size
-    size_t bytes = 0;
+    size_t bytes = 0;                             // idle in the pool
+    size_t in_use = 0;                            // handed out: holding a spilled block
 } g_host_pool;
 
 size_t host_pool_cap() {
@@ -159,6 +162,7 @@ void *host_piece_get(Vmem *v, size_t bytes) {
             void *p = it->second.back();
             it->second.pop_back();
             g_host_pool.bytes -= bytes;
+            g_host_pool.in_use += bytes;
             return p;
         }
     }
@@ -166,13 +170,17 @@ void *host_piece_get(Vmem *v, size_t bytes) {
     const double ts = now_ms();
     const int rc = vgpu_slab_alloc(VGPU_TIER_HOST, v->device, -1, bytes, &p);
     v->st.tier_setup_ms += now_ms() - ts;
-    return rc == VGPU_OK ? p : nullptr;
+    if (rc != VGPU_OK) return nullptr;
+    std::lock_guard<std::mutex> lk(g_host_pool.mu);
+    g_host_pool.in_use += bytes;
+    return p;
 }
-void host_piece_put(Vmem *v, void *p, size_t bytes) {
+void host_piece_put(Vmem *v, void *p, size_t bytes, bool may_unpin) {
     if (!p) return;
     {
         std::lock_guard<std::mutex> lk(g_host_pool.mu);
-        if (g_host_pool.bytes + bytes <= host_pool_cap()) {
+        g_host_pool.in_use -= std::min(g_host_pool.in_use, bytes);
+        if (!may_unpin || g_host_pool.bytes + bytes <= std::max(host_pool_cap(), g_host_pool.in_use)) {
             g_host_pool.free_[bytes].push_back(p);
             g_host_pool.bytes += bytes;
             return;
@@ -188,7 +196,7 @@ char *slot_ptr(Vmem *v, Vmem::Tier &t, uint32_t slot) {
 void free_slot(Vmem *v, Vmem::Tier &t, uint32_t slot) {
     t.free_slots.push_back(slot);
     if (t.kind == VGPU_TIER_HOST && t.piece[slot]) {
-        host_piece_put(v, t.piece[slot], v->block_bytes());
+        host_piece_put(v, t.piece[slot], v->block_bytes(), false);
         t.piece[slot] = nullptr;
     }
 }
@@ -241,12 +249,20 @@ int map_blocks(Vmem *v, const std::vector<size_t> &list) {
     return rc;
 }
 
+double g_t_unmap_call = 0, g_t_release_call = 0, g_t_unmap_max = 0, g_t_release_max = 0;  // VGPU_VMEM_TRACE: process-wide
 int unmap_block(Vmem *v, size_t b, bool release) {
     Block &bl = v->blocks[b];
+    const double t0 = now_ms();
     CUresult r = g_api.Unmap(v->base + b * v->block_bytes(), v->block_bytes());
+    const double t1 = now_ms();
+    g_t_unmap_call += t1 - t0;
+    g_t_unmap_max = std::max(g_t_unmap_max, t1 - t0);
     if (r != CUDA_SUCCESS) return drv_fail("cuMemUnmap", r);
     if (release) g_api.Release(bl.handle);  // explicit evict: the HBM goes back to the device
     else v->pool.push_back(bl.handle);      // making room inside ensure(): reused within microseconds
+    const double t2 = now_ms();
+    g_t_release_call += t2 - t1;
+    g_t_release_max = std::max(g_t_release_max, t2 - t1);
     bl.handle = 0;
     return VGPU_OK;
 }
@@ -348,14 +364,15 @@ int begin_spill(Vmem *v, size_t b) {
     if (rc) give_slot_back(v, bl);
     return rc;
 }
-// The spill of block b has run (ok) or its stream failed (!ok): unmap and release it, or give the slot back.
-int finish_spill(Vmem *v, size_t b, bool ok) {
+// The spill of block b has run (ok) or its stream failed (!ok): unmap it and release its memory (or park the handle in
+// v->pool when the caller has a use for it), or give the slot back.
+int finish_spill(Vmem *v, size_t b, bool ok, bool release) {
     Block &bl = v->blocks[b];
     if (!ok) {
         give_slot_back(v, bl);
         return fail(VGPU_E_CUDA, "spill of block %zu did not complete", b);
     }
-    if (int urc = unmap_block(v, b, true)) {
+    if (int urc = unmap_block(v, b, release)) {
         give_slot_back(v, bl);
         return urc;
     }
@@ -579,7 +596,8 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n) {
 // on the two ranges' own streams.  The VMM calls of a step (unmap + release of the block that just left, create + map +
 // set-access of the block that arrives next) are issued while the GPU is idle, because cuMemUnmap / cuMemSetAccess wait
 // for running kernels (see map_blocks); the arriving block only ever takes memory that a leaving block freed in THIS
-// call, so the call never holds more HBM than before it.  All resident blocks of `out` leave; of [first, first+n) of
+// call — where both ranges have the same block size it takes that very physical block, handed over without a release /
+// create — so the call never holds more HBM than before it.  All resident blocks of `out` leave; of [first, first+n) of
 // `in` as many missing blocks arrive as that memory allows — vgpu_vmem_missing tells what is left, vgpu_vmem_ensure
 // or another swap brings it.  Per-block state, checksum verification and the failed-restore handling are ensure()'s.
 int vgpu_vmem_swap(void *out_handle, void *in_handle, uint64_t first, uint64_t n) {
@@ -646,9 +664,20 @@ int vgpu_vmem_swap(void *out_handle, void *in_handle, uint64_t first, uint64_t n
         const double tu = now_ms();
         o->t_wait += tu - tw;
         if (leaving) {
-            const int f = finish_spill(o, out[oi], so);
-            if (f == VGPU_OK) credit += o->block_bytes();
-            else if (!rc) rc = f;
+            // Same block size on both sides (the usual case: 1 GiB): the physical block that just left is handed to
+            // the range that arrives — unmap there, map here — instead of being released and created anew
+            // (cuMemRelease of 1 GiB takes up to 60 ms, cuMemCreate several).
+            const bool hand_over = o->block_bytes() == v->block_bytes() && ii < in.size();
+            const int f = finish_spill(o, out[oi], so, !hand_over);
+            if (f == VGPU_OK) {
+                credit += o->block_bytes();
+                if (hand_over && !o->pool.empty()) {
+                    v->pool.push_back(o->pool.back());
+                    o->pool.pop_back();
+                }
+            } else if (!rc) {
+                rc = f;
+            }
             ++oi;
         }
         if (arriving) {
@@ -724,6 +753,9 @@ int vgpu_vmem_destroy(void *handle) {
     if (getenv("VGPU_VMEM_TRACE"))
         fprintf(stderr, "[vgpu_vmem] evict %.1f ms = device sync %.1f + spill launches %.1f + waits %.1f + unmap %.1f + tier set-up %.1f; fetch %.1f ms of which map %.1f\n",
                 v->st.evict_ms, v->t_sync, v->t_launch, v->t_wait, v->t_unmap, v->st.tier_setup_ms, v->st.fetch_ms, v->t_map);
+    if (getenv("VGPU_VMEM_TRACE"))
+        fprintf(stderr, "[vgpu_vmem] process so far: cuMemUnmap %.1f ms (longest %.1f), cuMemRelease %.1f ms (longest %.1f)\n", g_t_unmap_call, g_t_unmap_max,
+                g_t_release_call, g_t_release_max);
     cudaSetDevice(v->device);
     cudaDeviceSynchronize();
     for (size_t b = 0; b < v->blocks.size(); ++b)
@@ -735,7 +767,7 @@ int vgpu_vmem_destroy(void *handle) {
     if (v->base) g_api.AddressFree(v->base, v->nblocks * v->block_bytes());
     for (auto &t : v->tiers) {
         if (t.slab) vgpu_slab_free(t.kind, v->device, t.peer, t.slab);
-        for (void *p : t.piece) host_piece_put(v, p, v->block_bytes());  // to the pool for the ranges that remain, up to its cap
+        for (void *p : t.piece) host_piece_put(v, p, v->block_bytes(), true);  // to the pool for the ranges that remain, up to its cap
     }
     if (v->ck) cudaFreeHost(v->ck);
     if (v->res) cudaFreeHost(v->res);
