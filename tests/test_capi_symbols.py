@@ -46,6 +46,8 @@ def test_argument_errors_need_no_gpu(vgpu):
     assert c.lib.vgpu_spill(1, 0, None, None, None, None, 0, c.CHUNK_BYTES, None, None) == c.OK  # 0 chunks: no-op
     assert c.lib.vgpu_spill(1, 0, None, None, None, None, 4, c.CHUNK_BYTES, None, None) == c.E_INVAL
     assert "cksum" in c.last_error()
+    assert c.lib.vgpu_vmem_swap(None, None, 0, 0) == c.E_INVAL and "two different ranges" in c.last_error()
+    assert c.lib.vgpu_vmem_evict(None, 0, 1) == c.E_INVAL and c.lib.vgpu_vmem_ensure(None, 0, 1) == c.E_INVAL
 
 
 def test_header_is_valid_c_and_links_from_a_plain_c_caller(vgpu, tmp_path):
