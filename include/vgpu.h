@@ -253,13 +253,15 @@ typedef struct vgpu_vmem_stats {
     double   evict_ms, fetch_ms;          /* wall time spent in evict / fetch incl. map/unmap */
     uint64_t evictions_peer, evictions_host; /* chunks sent to each tier */
     uint64_t restore_retries;             /* blocks restored a second time (copy engine) after a checksum failure */
-    double   tier_setup_ms;               /* part of evict_ms spent ONCE per tier: a context on the peer and its slab, or
-                                             pinning the host slab (first eviction that needs the tier) */
+    double   tier_setup_ms;               /* part of evict_ms spent on set-up rather than transfer: a context on the peer and
+                                             its slab (once), pinning host memory by the block when the process-wide pool
+                                             of pinned pieces has none to hand out */
 } vgpu_vmem_stats_t;
 
 /* Create a range of `virtual_bytes` (rounded up to 2 MiB) on `device`, of which at most
- * `resident_bytes` are backed by HBM at any time; the rest lives in a tier slab of
- * `tier_bytes` (VGPU_TIER_PEER on `peer_device`, or VGPU_TIER_HOST). */
+ * `resident_bytes` are backed by HBM at any time; the rest lives in a tier of `tier_bytes` (VGPU_TIER_PEER: a slab on
+ * `peer_device`, allocated at the first eviction; VGPU_TIER_HOST: pinned host memory taken block by block as blocks
+ * leave, from a pool shared by all ranges of the process — VGPU_VMEM_HOST_POOL_MB). */
 int vgpu_vmem_create(int device, uint64_t virtual_bytes, uint64_t resident_bytes, int tier,
                      int peer_device, uint64_t tier_bytes, void **handle);
 /* Two tiers in the order the north star asks for: victims go to `peer_device`'s HBM (over NVLink P2P)
@@ -276,7 +278,8 @@ int vgpu_vmem_ensure(void *handle, uint64_t first, uint64_t n);
  * unmapped again and STAYS in the tier (slot, checksums and state untouched), so nothing is lost by the failed call
  * and a later vgpu_vmem_ensure can succeed.  The other blocks of the call become resident as usual. */
 /* Where chunk `chunk` lives right now: *tier = VGPU_TIER_LOCAL and its address in the range while resident, the tier
- * kind and its address inside that tier's slab while spilled, *ptr = NULL if never touched.  For tools and tests. */
+ * kind and its address inside that tier (the peer's slab, or the block's pinned host piece) while spilled, *ptr = NULL
+ * if never touched.  For tools and tests. */
 int vgpu_vmem_locate(void *handle, uint64_t chunk, int *tier, void **ptr);
 /* Chunks of [first, first+n) that are not resident now (what an ensure of the range would have to map or restore,
  * counted in whole blocks): lets a caller that shares the GPU's HBM between several ranges make room first. */
