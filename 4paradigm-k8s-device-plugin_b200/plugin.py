@@ -43,6 +43,8 @@ class Flags:
     enableLegacyPreferred: bool = False
     pcibusfile: str = "/usr/local/vgpu/pciinfo.vgpu"  # $PCIBUSFILE, main.go:164-185
     smPartitionIndex: bool = False  # no reference flag: add VGPU_SM_PARTITION_INDEX_<n> to the response (vgpu.h, emit_partition_index)
+    failOnInitError: bool = True    # main.go:63-69: false = block forever instead of failing when NVML cannot be initialised
+    verbose: int = 0                # main.go:126-132
 
 
 def loadPciInfo(lspci_out: Optional[str] = None, pcibusfile: Optional[str] = None) -> str:
@@ -63,6 +65,78 @@ def loadPciInfo(lspci_out: Optional[str] = None, pcibusfile: Optional[str] = Non
         with os.fdopen(fd, "w") as f:
             f.write(pcibusstr)
     return pcibusstr
+
+
+# main.go:55-133: flag name -> (Flags field, kind, environment variable).  Same names, defaults and env vars, so the
+# daemonset manifest of the reference starts this plugin unchanged.
+_FLAG_TABLE = {
+    "mig-strategy": ("migStrategy", "str", "MIG_STRATEGY"),
+    "fail-on-init-error": ("failOnInitError", "bool", "FAIL_ON_INIT_ERROR"),
+    "pass-device-specs": ("passDeviceSpecs", "bool", "PASS_DEVICE_SPECS"),
+    "device-list-strategy": ("deviceListStrategy", "str", "DEVICE_LIST_STRATEGY"),
+    "device-id-strategy": ("deviceIDStrategy", "str", "DEVICE_ID_STRATEGY"),
+    "nvidia-driver-root": ("nvidiaDriverRoot", "str", "NVIDIA_DRIVER_ROOT"),
+    "device-split-count": ("deviceSplitCount", "uint", "DEVICE_SPLIT_COUNT"),
+    "device-memory-scaling": ("deviceMemoryScaling", "float", "DEVICE_MEMORY_SCALING"),
+    "device-cores-scaling": ("deviceCoresScaling", "float", "DEVICE_CORES_SCALING"),
+    "enable-legacy-preferred": ("enableLegacyPreferred", "bool", "ENABLE_LEGACY_PREFERRED"),
+    "verbose": ("verbose", "int", "VERBOSE"),
+}
+_GO_BOOLS = {"1": True, "t": True, "T": True, "TRUE": True, "true": True, "True": True,
+             "0": False, "f": False, "F": False, "FALSE": False, "false": False, "False": False}  # strconv.ParseBool
+
+
+def _flagValue(name: str, kind: str, text: str, origin: str):
+    try:
+        if kind == "str":
+            return text
+        if kind == "bool":
+            return _GO_BOOLS[text]
+        if kind == "float":
+            return float(text)
+        v = int(text, 10)
+        if kind == "uint" and v < 0:
+            raise ValueError(text)
+        return v
+    except (KeyError, ValueError):
+        raise ValueError(f'invalid value "{text}" for {origin}') from None
+
+
+def parseFlags(argv: List[str], env: Optional[dict] = None) -> Flags:
+    """The command line of main.go (urfave/cli v2): `--name value`, `--name=value`, a bare `--name` for a boolean, one or
+    two dashes; a flag that is not given takes its environment variable, then its default.  validateFlags runs on the
+    result as `c.Before` does.  `argv` without the program name."""
+    import os
+    env = os.environ if env is None else env
+    f = Flags(pcibusfile=env.get("PCIBUSFILE", "") or Flags.pcibusfile)
+    given = set()
+    i = 0
+    while i < len(argv):
+        a = argv[i]
+        i += 1
+        if a == "--":
+            break
+        if not a.startswith("-") or a == "-":
+            raise ValueError(f"unexpected argument: {a}")
+        name, eq, val = a.lstrip("-").partition("=")
+        if name not in _FLAG_TABLE:
+            raise ValueError(f"flag provided but not defined: -{name}")
+        fld, kind, _ = _FLAG_TABLE[name]
+        if not eq:
+            if kind == "bool":
+                val = "true"
+            else:
+                if i >= len(argv):
+                    raise ValueError(f"flag needs an argument: -{name}")
+                val = argv[i]
+                i += 1
+        setattr(f, fld, _flagValue(name, kind, val, f"flag -{name}"))
+        given.add(name)
+    for name, (fld, kind, var) in _FLAG_TABLE.items():
+        if name not in given and env.get(var, "") != "":
+            setattr(f, fld, _flagValue(name, kind, env[var], f"environment variable {var}"))
+    validateFlags(f)
+    return f
 
 
 def validateFlags(f: Flags) -> None:

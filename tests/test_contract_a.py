@@ -134,6 +134,37 @@ def test_flag_validation_messages(vgpu):
         assert str(e.value) == msg
 
 
+def test_command_line_and_environment_of_the_reference(vgpu):
+    """main.go:55-133: the eleven flags, their environment variables and defaults; flag beats environment beats default;
+    booleans the way strconv.ParseBool reads them; validateFlags runs before anything starts."""
+    P = vgpu.plugin
+    d = P.parseFlags([], {})
+    assert (d.migStrategy, d.failOnInitError, d.passDeviceSpecs, d.deviceListStrategy, d.deviceIDStrategy, d.nvidiaDriverRoot,
+            d.deviceSplitCount, d.deviceMemoryScaling, d.deviceCoresScaling, d.enableLegacyPreferred, d.verbose) == \
+        ("none", True, False, "envvar", "uuid", "/", 2, 1.0, 1.0, False, 0)
+    # the daemonset of the reference: everything through the command line
+    f = P.parseFlags(["--fail-on-init-error=false", "--device-split-count=10", "--device-memory-scaling", "1.5", "--device-cores-scaling=1.2",
+                      "--pass-device-specs", "-mig-strategy", "mixed", "--enable-legacy-preferred=T", "--verbose=3"], {})
+    assert (f.failOnInitError, f.deviceSplitCount, f.deviceMemoryScaling, f.deviceCoresScaling, f.passDeviceSpecs, f.migStrategy,
+            f.enableLegacyPreferred, f.verbose) == (False, 10, 1.5, 1.2, True, "mixed", True, 3)
+    # environment only, and a flag that overrides its variable
+    env = {"DEVICE_SPLIT_COUNT": "4", "DEVICE_LIST_STRATEGY": "volume-mounts", "DEVICE_ID_STRATEGY": "index", "PASS_DEVICE_SPECS": "1",
+           "NVIDIA_DRIVER_ROOT": "/run/nvidia/driver", "PCIBUSFILE": "/tmp/pci.vgpu", "MIG_STRATEGY": ""}
+    e = P.parseFlags(["--device-split-count", "8"], env)
+    assert (e.deviceSplitCount, e.deviceListStrategy, e.deviceIDStrategy, e.passDeviceSpecs, e.nvidiaDriverRoot, e.pcibusfile, e.migStrategy) == \
+        (8, "volume-mounts", "index", True, "/run/nvidia/driver", "/tmp/pci.vgpu", "none")
+    for argv, env, msg in [(["--device-split-count=0"], {}, "invalid --device-split-count option: 0"),
+                           ([], {"DEVICE_MEMORY_SCALING": "0"}, "invalid --device-memory-scaling option: 0.0"),
+                           (["--device-id-strategy=serial"], {}, "invalid --device-id-strategy option: serial"),
+                           (["--device-split-count=-1"], {}, 'invalid value "-1" for flag -device-split-count'),
+                           ([], {"PASS_DEVICE_SPECS": "yes"}, 'invalid value "yes" for environment variable PASS_DEVICE_SPECS'),
+                           (["--gpu-count=2"], {}, "flag provided but not defined: -gpu-count"),
+                           (["--verbose"], {}, "flag needs an argument: -verbose")]:
+        with pytest.raises(ValueError) as x:
+            P.parseFlags(argv, env)
+        assert str(x.value) == msg
+
+
 def test_split_arithmetic_matches_model_on_random_flags(vgpu):
     """uint64(float64(MiB)*scaling/float64(split)) and int(100*cores/float64(split)), many inputs."""
     rng = random.Random(0x5EED)
